@@ -1,0 +1,366 @@
+"""ctypes view of the C-ABI declared in include/egs_rasterizer.h.
+
+This is the binding a non-torch host would write (INTEGRATION.md shows the same stub). The parity
+tests and bench.py call the library through it with raw device pointers, so what they exercise is
+exactly the `extern "C"` surface, not the torch extension. torch is used only to own device
+memory and to name the stream.
+
+There is no CPU path: `load()` raises if libegs_rasterizer.so is missing.
+"""
+from __future__ import annotations
+
+import ctypes as C
+from pathlib import Path
+from typing import Optional
+
+_LIB_PATH = Path(__file__).resolve().parent / "libegs_rasterizer.so"
+_lib = None
+
+EGS_OK = 0
+ALLOC_FN = C.CFUNCTYPE(C.c_void_p, C.c_void_p, C.c_size_t)
+
+c_float_p = C.c_void_p  # device pointers are passed as opaque addresses
+
+
+class EgsForwardArgs(C.Structure):
+    _fields_ = [
+        ("P", C.c_int), ("sh_degree", C.c_int), ("sh_coeffs", C.c_int),
+        ("width", C.c_int), ("height", C.c_int),
+        ("background", c_float_p), ("means3D", c_float_p), ("shs", c_float_p),
+        ("colors_precomp", c_float_p), ("opacities", c_float_p), ("scales", c_float_p),
+        ("rotations", c_float_p), ("cov3D_precomp", c_float_p), ("scale_modifier", C.c_float),
+        ("viewmatrix", c_float_p), ("projmatrix", c_float_p), ("campos", c_float_p),
+        ("tan_fovx", C.c_float), ("tan_fovy", C.c_float), ("prefiltered", C.c_int), ("debug", C.c_int),
+        ("out_color", c_float_p), ("out_depth", c_float_p), ("out_alpha", c_float_p), ("radii", C.c_void_p),
+        ("geom_alloc", ALLOC_FN), ("geom_ctx", C.c_void_p),
+        ("binning_alloc", ALLOC_FN), ("binning_ctx", C.c_void_p),
+        ("image_alloc", ALLOC_FN), ("image_ctx", C.c_void_p),
+    ]
+
+
+class EgsBackwardArgs(C.Structure):
+    _fields_ = [
+        ("P", C.c_int), ("sh_degree", C.c_int), ("sh_coeffs", C.c_int), ("num_rendered", C.c_int),
+        ("width", C.c_int), ("height", C.c_int),
+        ("background", c_float_p), ("means3D", c_float_p), ("shs", c_float_p),
+        ("colors_precomp", c_float_p), ("scales", c_float_p), ("rotations", c_float_p),
+        ("cov3D_precomp", c_float_p), ("scale_modifier", C.c_float),
+        ("viewmatrix", c_float_p), ("projmatrix", c_float_p), ("campos", c_float_p),
+        ("tan_fovx", C.c_float), ("tan_fovy", C.c_float),
+        ("radii", C.c_void_p), ("out_alpha", c_float_p),
+        ("geom_buffer", C.c_void_p), ("binning_buffer", C.c_void_p), ("image_buffer", C.c_void_p),
+        ("dL_dout_color", c_float_p), ("dL_dout_depth", c_float_p), ("dL_dout_alpha", c_float_p),
+        ("scratch", C.c_void_p),
+        ("dL_dmeans2D", c_float_p), ("dL_dcolors", c_float_p), ("dL_dopacity", c_float_p),
+        ("dL_dmeans3D", c_float_p), ("dL_dcov3D", c_float_p), ("dL_dsh", c_float_p),
+        ("dL_dscales", c_float_p), ("dL_drotations", c_float_p), ("debug", C.c_int),
+    ]
+
+
+class EgsAdamGroup(C.Structure):
+    _fields_ = [("param", c_float_p), ("grad", c_float_p), ("exp_avg", c_float_p),
+                ("exp_avg_sq", c_float_p), ("n", C.c_longlong), ("lr", C.c_float), ("step", C.c_int)]
+
+
+class EgsGeomView(C.Structure):
+    _fields_ = [("depths", C.c_void_p), ("means2D", C.c_void_p), ("conic_opacity", C.c_void_p),
+                ("rgb_depth", C.c_void_p), ("clamped", C.c_void_p), ("tiles_touched", C.c_void_p),
+                ("point_offsets", C.c_void_p)]
+
+
+class EgsBinningView(C.Structure):
+    _fields_ = [("keys_sorted", C.c_void_p), ("values_sorted", C.c_void_p)]
+
+
+class EgsImageView(C.Structure):
+    _fields_ = [("n_contrib", C.c_void_p), ("ranges", C.c_void_p)]
+
+
+# every symbol include/egs_rasterizer.h declares (the CPU test suite checks they all resolve)
+EXPORTED_SYMBOLS = [
+    "egs_geom_bytes", "egs_binning_bytes", "egs_image_bytes", "egs_forward",
+    "egs_backward_scratch_bytes", "egs_backward", "egs_mark_visible", "egs_adam_step",
+    "egs_se3_apply", "egs_adam_se3_step", "egs_geom_view", "egs_binning_view", "egs_image_view",
+    "egs_launch_count", "egs_last_error", "egs_abi_version",
+    "egs_profile_enable", "egs_profile_read", "egs_profile_stage_name",
+]
+PROFILE_STAGES = 16
+
+
+def load() -> C.CDLL:
+    global _lib
+    if _lib is not None:
+        return _lib
+    if not _LIB_PATH.exists():
+        raise ImportError(f"{_LIB_PATH} not found: build it with `python -m egogaussian_b200.build` "
+                          "(there is no CPU fallback)")
+    lib = C.CDLL(str(_LIB_PATH))
+    lib.egs_geom_bytes.restype = C.c_size_t
+    lib.egs_geom_bytes.argtypes = [C.c_int]
+    lib.egs_binning_bytes.restype = C.c_size_t
+    lib.egs_binning_bytes.argtypes = [C.c_int, C.c_int, C.c_int]
+    lib.egs_image_bytes.restype = C.c_size_t
+    lib.egs_image_bytes.argtypes = [C.c_int, C.c_int]
+    lib.egs_backward_scratch_bytes.restype = C.c_size_t
+    lib.egs_backward_scratch_bytes.argtypes = [C.c_int]
+    lib.egs_forward.restype = C.c_int
+    lib.egs_forward.argtypes = [C.POINTER(EgsForwardArgs), C.c_void_p, C.POINTER(C.c_int)]
+    lib.egs_backward.restype = C.c_int
+    lib.egs_backward.argtypes = [C.POINTER(EgsBackwardArgs), C.c_void_p]
+    lib.egs_mark_visible.restype = C.c_int
+    lib.egs_mark_visible.argtypes = [C.c_int, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]
+    lib.egs_adam_step.restype = C.c_int
+    lib.egs_adam_step.argtypes = [C.POINTER(EgsAdamGroup), C.c_int, C.c_float, C.c_float, C.c_float, C.c_void_p]
+    lib.egs_se3_apply.restype = C.c_int
+    lib.egs_se3_apply.argtypes = [C.c_int, C.c_void_p, C.c_void_p, C.c_int, C.c_void_p, C.c_void_p,
+                                  C.c_void_p, C.c_void_p, C.c_void_p]
+    lib.egs_adam_se3_step.restype = C.c_int
+    lib.egs_adam_se3_step.argtypes = [C.c_int, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p,
+                                      C.c_int, C.c_void_p, C.c_float, C.c_int, C.c_float, C.c_float,
+                                      C.c_float, C.c_void_p]
+    lib.egs_geom_view.restype = C.c_int
+    lib.egs_geom_view.argtypes = [C.c_void_p, C.c_int, C.POINTER(EgsGeomView)]
+    lib.egs_binning_view.restype = C.c_int
+    lib.egs_binning_view.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_int, C.POINTER(EgsBinningView)]
+    lib.egs_image_view.restype = C.c_int
+    lib.egs_image_view.argtypes = [C.c_void_p, C.c_int, C.c_int, C.POINTER(EgsImageView)]
+    lib.egs_launch_count.restype = C.c_ulonglong
+    lib.egs_profile_enable.restype = C.c_int
+    lib.egs_profile_enable.argtypes = [C.c_int]
+    lib.egs_profile_read.restype = C.c_int
+    lib.egs_profile_read.argtypes = [C.POINTER(C.c_double), C.POINTER(C.c_ulonglong)]
+    lib.egs_profile_stage_name.restype = C.c_char_p
+    lib.egs_profile_stage_name.argtypes = [C.c_int]
+    lib.egs_last_error.restype = C.c_char_p
+    lib.egs_abi_version.restype = C.c_int
+    _lib = lib
+    return lib
+
+
+class EgsError(RuntimeError):
+    pass
+
+
+def _check(rc: int, what: str) -> None:
+    if rc != EGS_OK:
+        raise EgsError(f"{what} failed ({rc}): {load().egs_last_error().decode()}")
+
+
+def _ptr(t) -> Optional[int]:
+    """Device address of a tensor, or None (NULL) for an absent / empty one."""
+    if t is None or t.numel() == 0:
+        return None
+    assert t.is_cuda and t.is_contiguous(), "C-ABI inputs must be contiguous CUDA tensors"
+    return t.data_ptr()
+
+
+def _view(addr, shape, dtype, device):
+    """Zero-copy torch view of device memory at `addr` (owned by a workspace blob)."""
+    import numpy as np
+    import torch
+    n = int(np.prod(shape))
+    if n == 0:
+        return torch.empty(shape, dtype=dtype, device=device)
+    itemsize = torch.empty((), dtype=dtype).element_size()
+
+    class _Holder:  # __cuda_array_interface__ provider
+        pass
+    h = _Holder()
+    typestr = {torch.float32: "<f4", torch.int32: "<i4", torch.uint8: "|u1", torch.int64: "<i8"}[dtype]
+    h.__cuda_array_interface__ = {"shape": tuple(shape), "typestr": typestr, "data": (int(addr), False),
+                                  "version": 2, "strides": None}
+    del itemsize
+    return torch.as_tensor(h, device=device)
+
+
+class ForwardResult:
+    """Outputs and workspaces of one egs_forward call (keeps the blobs alive for backward)."""
+
+    def __init__(self):
+        self.num_rendered = 0
+        self.color = self.depth = self.alpha = self.radii = None
+        self.geom = self.binning = self.image = None
+        self.P = self.W = self.H = 0
+
+    # --- introspection of the opaque blobs (tests only) -------------------------------------
+    def geom_view(self):
+        import torch
+        lib = load()
+        v = EgsGeomView()
+        _check(lib.egs_geom_view(self.geom.data_ptr(), self.P, C.byref(v)), "egs_geom_view")
+        d, P = self.geom.device, self.P
+        return {
+            "depths": _view(v.depths, (P,), torch.float32, d),
+            "means2D": _view(v.means2D, (P, 2), torch.float32, d),
+            "conic_opacity": _view(v.conic_opacity, (P, 4), torch.float32, d),
+            "rgb_depth": _view(v.rgb_depth, (P, 4), torch.float32, d),
+            "clamped": _view(v.clamped, (P,), torch.uint8, d),
+            "tiles_touched": _view(v.tiles_touched, (P,), torch.int32, d),
+            "point_offsets": _view(v.point_offsets, (P,), torch.int32, d),
+        }
+
+    def binning_view(self):
+        import torch
+        lib = load()
+        R = self.num_rendered
+        if R == 0:
+            e = torch.empty((0,), dtype=torch.int64, device=self.geom.device)
+            return {"keys": e, "values": e.to(torch.int32)}
+        v = EgsBinningView()
+        _check(lib.egs_binning_view(self.binning.data_ptr(), R, self.W, self.H, C.byref(v)), "egs_binning_view")
+        d = self.binning.device
+        return {"keys": _view(v.keys_sorted, (R,), torch.int64, d),
+                "values": _view(v.values_sorted, (R,), torch.int32, d)}
+
+    def image_view(self):
+        import torch
+        lib = load()
+        v = EgsImageView()
+        _check(lib.egs_image_view(self.image.data_ptr(), self.W, self.H, C.byref(v)), "egs_image_view")
+        d = self.image.device
+        tiles = ((self.W + 15) // 16) * ((self.H + 15) // 16)
+        return {"n_contrib": _view(v.n_contrib, (self.H, self.W), torch.int32, d),
+                "ranges": _view(v.ranges, (tiles, 2), torch.int32, d)}
+
+
+def _stream_handle(stream=None) -> int:
+    import torch
+    s = stream if stream is not None else torch.cuda.current_stream()
+    return s.cuda_stream
+
+
+def forward(*, means3D, opacities, bg, viewmatrix, projmatrix, campos, tanfovx, tanfovy,
+            image_height, image_width, sh_degree=0, shs=None, colors_precomp=None, scales=None,
+            rotations=None, cov3D_precomp=None, scale_modifier=1.0, prefiltered=False, debug=False,
+            stream=None, out=None) -> ForwardResult:
+    """egs_forward on torch-owned device memory. `out` may carry preallocated output tensors."""
+    import torch
+    lib = load()
+    dev = means3D.device
+    P = int(means3D.shape[0])
+    H, W = int(image_height), int(image_width)
+    res = ForwardResult()
+    res.P, res.W, res.H = P, W, H
+    if out is None:
+        res.color = torch.empty((3, H, W), dtype=torch.float32, device=dev)
+        res.depth = torch.empty((1, H, W), dtype=torch.float32, device=dev)
+        res.alpha = torch.empty((1, H, W), dtype=torch.float32, device=dev)
+        res.radii = torch.empty((P,), dtype=torch.int32, device=dev)
+    else:
+        res.color, res.depth, res.alpha, res.radii = out
+
+    blobs = {}
+
+    def make_alloc(name):
+        def alloc(_ctx, nbytes):
+            blobs[name] = torch.empty((int(nbytes),), dtype=torch.uint8, device=dev)
+            return blobs[name].data_ptr()
+        return ALLOC_FN(alloc)
+
+    cb = {n: make_alloc(n) for n in ("geom", "binning", "image")}
+    a = EgsForwardArgs()
+    a.P, a.sh_degree, a.width, a.height = P, int(sh_degree), W, H
+    a.sh_coeffs = int(shs.shape[1]) if shs is not None and shs.numel() else 0
+    a.background = _ptr(bg)
+    a.means3D = _ptr(means3D)
+    a.shs = _ptr(shs)
+    a.colors_precomp = _ptr(colors_precomp)
+    a.opacities = _ptr(opacities)
+    a.scales = _ptr(scales)
+    a.rotations = _ptr(rotations)
+    a.cov3D_precomp = _ptr(cov3D_precomp)
+    a.scale_modifier = float(scale_modifier)
+    a.viewmatrix, a.projmatrix, a.campos = _ptr(viewmatrix), _ptr(projmatrix), _ptr(campos)
+    a.tan_fovx, a.tan_fovy = float(tanfovx), float(tanfovy)
+    a.prefiltered, a.debug = int(prefiltered), int(debug)
+    a.out_color, a.out_depth, a.out_alpha = res.color.data_ptr(), res.depth.data_ptr(), res.alpha.data_ptr()
+    a.radii = res.radii.data_ptr() if P else None
+    a.geom_alloc, a.binning_alloc, a.image_alloc = cb["geom"], cb["binning"], cb["image"]
+    n = C.c_int(0)
+    with torch.cuda.device(dev):
+        _check(lib.egs_forward(C.byref(a), _stream_handle(stream), C.byref(n)), "egs_forward")
+    res.num_rendered = n.value
+    res.geom, res.binning, res.image = blobs.get("geom"), blobs.get("binning"), blobs.get("image")
+    return res
+
+
+def backward(fwd: ForwardResult, *, means3D, bg, viewmatrix, projmatrix, campos, tanfovx,
+             tanfovy, dL_dcolor, dL_ddepth, dL_dalpha, sh_degree=0, shs=None, colors_precomp=None,
+             scales=None, rotations=None, cov3D_precomp=None, scale_modifier=1.0, debug=False,
+             stream=None, scratch=None):
+    """egs_backward; returns a dict of gradient tensors (absent inputs -> None)."""
+    import torch
+    lib = load()
+    dev = means3D.device
+    P, W, H = fwd.P, fwd.W, fwd.H
+    M = int(shs.shape[1]) if shs is not None and shs.numel() else 0
+    f = dict(dtype=torch.float32, device=dev)
+    g = {
+        "means2D": torch.empty((P, 3), **f), "opacity": torch.empty((P, 1), **f),
+        "means3D": torch.empty((P, 3), **f),
+        "colors": torch.empty((P, 3), **f) if colors_precomp is not None else None,
+        "cov3D": torch.empty((P, 6), **f) if cov3D_precomp is not None else None,
+        "sh": torch.empty((P, M, 3), **f) if M else None,
+        "scales": torch.empty((P, 3), **f) if scales is not None else None,
+        "rotations": torch.empty((P, 4), **f) if rotations is not None else None,
+    }
+    if P == 0:
+        return g
+    if scratch is None:
+        scratch = torch.empty((lib.egs_backward_scratch_bytes(P),), dtype=torch.uint8, device=dev)
+    a = EgsBackwardArgs()
+    a.P, a.sh_degree, a.sh_coeffs, a.num_rendered, a.width, a.height = P, int(sh_degree), M, fwd.num_rendered, W, H
+    a.background, a.means3D, a.shs = _ptr(bg), _ptr(means3D), _ptr(shs)
+    a.colors_precomp, a.scales, a.rotations = _ptr(colors_precomp), _ptr(scales), _ptr(rotations)
+    a.cov3D_precomp = _ptr(cov3D_precomp)
+    a.scale_modifier = float(scale_modifier)
+    a.viewmatrix, a.projmatrix, a.campos = _ptr(viewmatrix), _ptr(projmatrix), _ptr(campos)
+    a.tan_fovx, a.tan_fovy = float(tanfovx), float(tanfovy)
+    a.radii, a.out_alpha = fwd.radii.data_ptr(), fwd.alpha.data_ptr()
+    a.geom_buffer = fwd.geom.data_ptr()
+    a.binning_buffer = fwd.binning.data_ptr() if fwd.binning is not None and fwd.num_rendered else None
+    a.image_buffer = fwd.image.data_ptr()
+    a.dL_dout_color, a.dL_dout_depth, a.dL_dout_alpha = _ptr(dL_dcolor), _ptr(dL_ddepth), _ptr(dL_dalpha)
+    a.scratch = scratch.data_ptr()
+    a.dL_dmeans2D, a.dL_dopacity, a.dL_dmeans3D = g["means2D"].data_ptr(), g["opacity"].data_ptr(), g["means3D"].data_ptr()
+    for key, field in (("colors", "dL_dcolors"), ("cov3D", "dL_dcov3D"), ("sh", "dL_dsh"),
+                       ("scales", "dL_dscales"), ("rotations", "dL_drotations")):
+        setattr(a, field, g[key].data_ptr() if g[key] is not None else None)
+    a.debug = int(debug)
+    with torch.cuda.device(dev):
+        _check(lib.egs_backward(C.byref(a), _stream_handle(stream)), "egs_backward")
+    return g
+
+
+def mark_visible(means3D, viewmatrix, projmatrix, stream=None):
+    import torch
+    lib = load()
+    P = int(means3D.shape[0])
+    out = torch.empty((P,), dtype=torch.bool, device=means3D.device)
+    if P:
+        with torch.cuda.device(means3D.device):
+            _check(lib.egs_mark_visible(P, _ptr(means3D), _ptr(viewmatrix), _ptr(projmatrix), out.data_ptr(),
+                                        _stream_handle(stream)), "egs_mark_visible")
+    return out
+
+
+def launch_count() -> int:
+    return int(load().egs_launch_count())
+
+
+def profile_enable(on: bool) -> None:
+    load().egs_profile_enable(int(bool(on)))
+
+
+def profile_read() -> dict:
+    """{stage name: (total milliseconds, kernel launches)} since the last read; waits for the GPU."""
+    lib = load()
+    ms = (C.c_double * PROFILE_STAGES)()
+    cnt = (C.c_ulonglong * PROFILE_STAGES)()
+    _check(lib.egs_profile_read(ms, cnt), "egs_profile_read")
+    out = {}
+    for i in range(PROFILE_STAGES):
+        name = lib.egs_profile_stage_name(i).decode()
+        if name:
+            out[name] = (float(ms[i]), int(cnt[i]))
+    return out

@@ -1,0 +1,293 @@
+// abi.cu -- the extern "C" entry points of include/egs_rasterizer.h: argument validation,
+// workspace carving and stage orchestration on the caller's stream.
+//
+// Orchestration mirrors CudaRasterizer::Rasterizer::forward / backward
+// (DGR/cuda_rasterizer/rasterizer_impl.cu:197-339, 343-447): preprocess -> scan -> one D2H read
+// of num_rendered -> binning workspace -> duplicate -> sort -> ranges -> blend; and for backward
+// tile blend -> per-Gaussian chain. Unlike the reference everything is enqueued on the stream
+// the caller passes (the reference uses the legacy default stream).
+#include "common.cuh"
+
+#include <stdarg.h>
+#include <stdio.h>
+#include <atomic>
+#include <mutex>
+#include <vector>
+
+namespace egs {
+
+static thread_local char g_error[512] = "";
+static std::atomic<unsigned long long> g_launches{0};
+
+void set_error(const char* fmt, ...) {
+  va_list ap;
+  va_start(ap, fmt);
+  vsnprintf(g_error, sizeof(g_error), fmt, ap);
+  va_end(ap);
+}
+void count_launch(unsigned n) { g_launches.fetch_add(n, std::memory_order_relaxed); }
+
+// ---- stage timing ---------------------------------------------------------------------------
+struct ProfRecord {
+  int stage;
+  cudaEvent_t a, b;
+  unsigned long long launches_before;
+  unsigned long long launches;
+};
+static std::atomic<bool> g_prof_on{false};
+static std::mutex g_prof_mu;
+static std::vector<ProfRecord*> g_prof_pending;
+static std::vector<ProfRecord*> g_prof_free;
+
+bool profiling_enabled() { return g_prof_on.load(std::memory_order_relaxed); }
+
+void profile_begin(cudaStream_t stream, int stage, void** token) {
+  ProfRecord* r = nullptr;
+  {
+    std::lock_guard<std::mutex> lk(g_prof_mu);
+    if (!g_prof_free.empty()) {
+      r = g_prof_free.back();
+      g_prof_free.pop_back();
+    }
+  }
+  if (!r) {
+    r = new ProfRecord();
+    if (cudaEventCreate(&r->a) != cudaSuccess || cudaEventCreate(&r->b) != cudaSuccess) {
+      delete r;
+      *token = nullptr;
+      return;
+    }
+  }
+  r->stage = stage;
+  r->launches_before = g_launches.load(std::memory_order_relaxed);
+  cudaEventRecord(r->a, stream);
+  *token = r;
+}
+
+void profile_end(cudaStream_t stream, void* token) {
+  ProfRecord* r = static_cast<ProfRecord*>(token);
+  cudaEventRecord(r->b, stream);
+  r->launches = g_launches.load(std::memory_order_relaxed) - r->launches_before;
+  std::lock_guard<std::mutex> lk(g_prof_mu);
+  g_prof_pending.push_back(r);
+}
+
+static const char* kStageNames[ST_COUNT] = {"preprocess_fwd", "scan", "duplicate_keys", "sort_histogram",
+                                            "sort_passes", "tile_ranges", "blend_fwd", "bwd_zero",
+                                            "blend_bwd", "preprocess_bwd", "adam", "se3"};
+
+static int check_pairs(const char* who, const void* shs, const void* colors, const void* scales,
+                       const void* rotations, const void* cov) {
+  if ((shs == nullptr) == (colors == nullptr)) {
+    set_error("%s: provide exactly one of shs / colors_precomp", who);
+    return EGS_ERR_INVALID_ARGUMENT;
+  }
+  const bool sr = scales != nullptr && rotations != nullptr;
+  const bool sr_any = scales != nullptr || rotations != nullptr;
+  if ((!sr && cov == nullptr) || (sr_any && cov != nullptr)) {
+    set_error("%s: provide exactly one of the scale/rotation pair or cov3D_precomp", who);
+    return EGS_ERR_INVALID_ARGUMENT;
+  }
+  return EGS_OK;
+}
+
+}  // namespace egs
+
+using namespace egs;
+
+extern "C" size_t egs_geom_bytes(int P) { return GeomLayout((size_t)(P < 0 ? 0 : P)).total; }
+extern "C" size_t egs_binning_bytes(int R, int W, int H) {
+  (void)W; (void)H;
+  return BinningLayout((size_t)(R < 0 ? 0 : R)).total;
+}
+extern "C" size_t egs_image_bytes(int W, int H) { return ImageLayout(W, H).total; }
+extern "C" size_t egs_backward_scratch_bytes(int P) { return BackwardScratch::bytes((size_t)(P < 0 ? 0 : P)); }
+
+extern "C" int egs_forward(const EgsForwardArgs* args, void* stream_v, int* num_rendered) {
+  if (!args || !num_rendered) {
+    set_error("egs_forward: NULL args");
+    return EGS_ERR_INVALID_ARGUMENT;
+  }
+  const EgsForwardArgs& a = *args;
+  cudaStream_t stream = static_cast<cudaStream_t>(stream_v);
+  *num_rendered = 0;
+  if (a.P < 0 || a.width <= 0 || a.height <= 0 || a.sh_degree < 0 || a.sh_degree > 3) {
+    set_error("egs_forward: bad P / image size / sh_degree");
+    return EGS_ERR_INVALID_ARGUMENT;
+  }
+  if (!a.out_color || !a.out_depth || !a.out_alpha || !a.background) {
+    set_error("egs_forward: NULL output or background");
+    return EGS_ERR_INVALID_ARGUMENT;
+  }
+  const size_t N = (size_t)a.width * a.height;
+  if (a.P == 0) {
+    // rasterize_points.cu:84 skips the whole pipeline and returns the zero-filled outputs
+    EGS_CUDA_TRY(cudaMemsetAsync(a.out_color, 0, 3 * N * sizeof(float), stream));
+    EGS_CUDA_TRY(cudaMemsetAsync(a.out_depth, 0, N * sizeof(float), stream));
+    EGS_CUDA_TRY(cudaMemsetAsync(a.out_alpha, 0, N * sizeof(float), stream));
+    return EGS_OK;
+  }
+  if (int rc = check_pairs("egs_forward", a.shs, a.colors_precomp, a.scales, a.rotations, a.cov3D_precomp))
+    return rc;
+  if (!a.means3D || !a.opacities || !a.viewmatrix || !a.projmatrix || !a.campos || !a.radii ||
+      !a.geom_alloc || !a.binning_alloc || !a.image_alloc) {
+    set_error("egs_forward: NULL required input");
+    return EGS_ERR_INVALID_ARGUMENT;
+  }
+  if (a.shs && a.sh_coeffs < (a.sh_degree + 1) * (a.sh_degree + 1)) {
+    set_error("egs_forward: sh_coeffs %d too small for degree %d", a.sh_coeffs, a.sh_degree);
+    return EGS_ERR_INVALID_ARGUMENT;
+  }
+
+  void* geom_mem = a.geom_alloc(a.geom_ctx, egs_geom_bytes(a.P));
+  void* img_mem = a.image_alloc(a.image_ctx, egs_image_bytes(a.width, a.height));
+  if (!geom_mem || !img_mem) {
+    set_error("egs_forward: workspace callback returned NULL");
+    return EGS_ERR_ALLOC;
+  }
+  const GeomPtrs g(geom_mem, (size_t)a.P);
+  const ImagePtrs im(img_mem, a.width, a.height);
+
+  if (int rc = launch_preprocess_forward(a, g, stream)) return rc;
+  if (int rc = launch_scan_tiles(g, a.P, stream, a.debug)) return rc;
+
+  uint32_t R_host = 0;
+  EGS_CUDA_TRY(cudaMemcpyAsync(&R_host, g.point_offsets + (a.P - 1), sizeof(uint32_t),
+                               cudaMemcpyDeviceToHost, stream));
+  EGS_CUDA_TRY(cudaStreamSynchronize(stream));
+  if (R_host >= (1u << 30)) {
+    set_error("egs_forward: num_rendered %u exceeds the supported 2^30", R_host);
+    return EGS_ERR_TOO_LARGE;
+  }
+  const int R = (int)R_host;
+
+  void* bin_mem = a.binning_alloc(a.binning_ctx, egs_binning_bytes(R, a.width, a.height));
+  if (!bin_mem) {
+    set_error("egs_forward: binning workspace callback returned NULL");
+    return EGS_ERR_ALLOC;
+  }
+  const BinningPtrs b(bin_mem, (size_t)R);
+  if (int rc = launch_binning(g, b, im, a.radii, a.P, R, a.width, a.height, stream, a.debug)) return rc;
+
+  const uint32_t* point_list = b.vals[sort_passes(a.width, a.height) & 1];
+  if (int rc = launch_blend_forward(a, g, point_list, im, stream)) return rc;
+  *num_rendered = R;
+  return EGS_OK;
+}
+
+extern "C" int egs_backward(const EgsBackwardArgs* args, void* stream_v) {
+  if (!args) {
+    set_error("egs_backward: NULL args");
+    return EGS_ERR_INVALID_ARGUMENT;
+  }
+  const EgsBackwardArgs& a = *args;
+  cudaStream_t stream = static_cast<cudaStream_t>(stream_v);
+  if (a.P < 0 || a.width <= 0 || a.height <= 0 || a.num_rendered < 0) {
+    set_error("egs_backward: bad sizes");
+    return EGS_ERR_INVALID_ARGUMENT;
+  }
+  if (a.P == 0) return EGS_OK;
+  if (int rc = check_pairs("egs_backward", a.shs, a.colors_precomp, a.scales, a.rotations, a.cov3D_precomp))
+    return rc;
+  if (!a.means3D || !a.radii || !a.out_alpha || !a.geom_buffer || !a.image_buffer ||
+      (a.num_rendered > 0 && !a.binning_buffer) || !a.dL_dout_color || !a.dL_dout_depth ||
+      !a.dL_dout_alpha || !a.scratch || !a.dL_dmeans2D || !a.dL_dopacity || !a.dL_dmeans3D ||
+      !a.background || !a.viewmatrix || !a.projmatrix || !a.campos) {
+    set_error("egs_backward: NULL required argument");
+    return EGS_ERR_INVALID_ARGUMENT;
+  }
+  if ((a.colors_precomp && !a.dL_dcolors) || (a.cov3D_precomp && !a.dL_dcov3D) || (a.shs && !a.dL_dsh) ||
+      (a.scales && (!a.dL_dscales || !a.dL_drotations))) {
+    set_error("egs_backward: missing gradient output for a provided input");
+    return EGS_ERR_INVALID_ARGUMENT;
+  }
+  const GeomPtrs g(const_cast<void*>(a.geom_buffer), (size_t)a.P);
+  const ImagePtrs im(const_cast<void*>(a.image_buffer), a.width, a.height);
+  const BackwardScratch s(a.scratch);
+
+  {
+    StageTimer t(stream, ST_BWD_ZERO);
+    EGS_CUDA_TRY(cudaMemsetAsync(s.acc, 0, (size_t)a.P * 48, stream));
+  }
+  if (a.num_rendered > 0) {
+    const BinningPtrs b(const_cast<void*>(a.binning_buffer), (size_t)a.num_rendered);
+    const uint32_t* point_list = b.vals[sort_passes(a.width, a.height) & 1];
+    if (int rc = launch_blend_backward(a, g, point_list, im, s, stream)) return rc;
+  }
+  return launch_preprocess_backward(a, g, s, stream);
+}
+
+extern "C" int egs_mark_visible(int P, const float* means3D, const float* viewmatrix,
+                                const float* projmatrix, unsigned char* present, void* stream) {
+  if (P < 0 || (P > 0 && (!means3D || !viewmatrix || !present))) {
+    set_error("egs_mark_visible: NULL argument");
+    return EGS_ERR_INVALID_ARGUMENT;
+  }
+  if (P == 0) return EGS_OK;
+  return launch_mark_visible(P, means3D, viewmatrix, projmatrix, present, static_cast<cudaStream_t>(stream));
+}
+
+extern "C" int egs_geom_view(const void* geom_buffer, int P, EgsGeomView* out) {
+  if (!geom_buffer || !out || P < 0) return EGS_ERR_INVALID_ARGUMENT;
+  const GeomPtrs g(const_cast<void*>(geom_buffer), (size_t)P);
+  out->depths = g.depths;
+  out->means2D = reinterpret_cast<const float*>(g.means2D);
+  out->conic_opacity = reinterpret_cast<const float*>(g.conic_opacity);
+  out->rgb_depth = reinterpret_cast<const float*>(g.rgb_depth);
+  out->clamped = g.clamped;
+  out->tiles_touched = g.tiles_touched;
+  out->point_offsets = g.point_offsets;
+  return EGS_OK;
+}
+
+extern "C" int egs_binning_view(const void* binning_buffer, int R, int W, int H, EgsBinningView* out) {
+  if (!binning_buffer || !out || R < 0) return EGS_ERR_INVALID_ARGUMENT;
+  const BinningPtrs b(const_cast<void*>(binning_buffer), (size_t)R);
+  const int sel = sort_passes(W, H) & 1;
+  out->keys_sorted = b.keys[sel];
+  out->values_sorted = b.vals[sel];
+  return EGS_OK;
+}
+
+extern "C" int egs_image_view(const void* image_buffer, int W, int H, EgsImageView* out) {
+  if (!image_buffer || !out) return EGS_ERR_INVALID_ARGUMENT;
+  const ImagePtrs im(const_cast<void*>(image_buffer), W, H);
+  out->n_contrib = im.n_contrib;
+  out->ranges = reinterpret_cast<const uint32_t*>(im.ranges);
+  return EGS_OK;
+}
+
+extern "C" int egs_profile_enable(int on) {
+  g_prof_on.store(on != 0, std::memory_order_relaxed);
+  return EGS_OK;
+}
+
+extern "C" int egs_profile_read(double* ms, unsigned long long* count) {
+  if (!ms || !count) return EGS_ERR_INVALID_ARGUMENT;
+  std::vector<ProfRecord*> take;
+  {
+    std::lock_guard<std::mutex> lk(g_prof_mu);
+    take.swap(g_prof_pending);
+  }
+  int rc = EGS_OK;
+  for (ProfRecord* r : take) {
+    float t = 0.f;
+    if (cudaEventSynchronize(r->b) == cudaSuccess && cudaEventElapsedTime(&t, r->a, r->b) == cudaSuccess) {
+      ms[r->stage] += t;
+      count[r->stage] += r->launches;
+    } else {
+      rc = EGS_ERR_CUDA;
+    }
+  }
+  std::lock_guard<std::mutex> lk(g_prof_mu);
+  for (ProfRecord* r : take) g_prof_free.push_back(r);
+  return rc;
+}
+
+extern "C" const char* egs_profile_stage_name(int stage) {
+  return (stage >= 0 && stage < ST_COUNT) ? kStageNames[stage] : "";
+}
+
+extern "C" unsigned long long egs_launch_count(void) { return g_launches.load(std::memory_order_relaxed); }
+extern "C" const char* egs_last_error(void) { return g_error; }
+extern "C" int egs_abi_version(void) { return EGS_ABI_VERSION; }

@@ -1,0 +1,320 @@
+// common.cuh -- shared device helpers, workspace layouts and host-side error plumbing.
+//
+// Workspace layouts replace GeometryState / ImageState / BinningState of the reference
+// (DGR/cuda_rasterizer/rasterizer_impl.h:22-73, rasterizer_impl.cu:155-193). They are our own:
+// the blend kernels want rgb+depth packed in one float4 so that a tile stages 40 B per list
+// entry with three vector loads, and cov3D is never stored (backward recomputes it).
+#pragma once
+
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include <stddef.h>
+#include "../../include/egs_rasterizer.h"
+
+namespace egs {
+
+constexpr int TILE_X = EGS_TILE_X;
+constexpr int TILE_Y = EGS_TILE_Y;
+constexpr int TILE_PIXELS = TILE_X * TILE_Y;
+
+// ---------------------------------------------------------------------------------------------
+// host-side plumbing
+// ---------------------------------------------------------------------------------------------
+void set_error(const char* fmt, ...);
+void count_launch(unsigned n = 1);
+
+#define EGS_CUDA_TRY(expr)                                                              \
+  do {                                                                                  \
+    cudaError_t _e = (expr);                                                            \
+    if (_e != cudaSuccess) {                                                            \
+      egs::set_error("%s failed: %s (%s:%d)", #expr, cudaGetErrorString(_e), __FILE__,  \
+                     __LINE__);                                                         \
+      return EGS_ERR_CUDA;                                                              \
+    }                                                                                   \
+  } while (0)
+
+// After a kernel launch: always pick up launch-configuration errors; in debug mode also
+// synchronise, like CHECK_CUDA in DGR/cuda_rasterizer/auxiliary.h:166-173.
+#define EGS_AFTER_LAUNCH(stream, debug)                                                 \
+  do {                                                                                  \
+    egs::count_launch();                                                                \
+    EGS_CUDA_TRY(cudaGetLastError());                                                   \
+    if (debug) EGS_CUDA_TRY(cudaStreamSynchronize(stream));                             \
+  } while (0)
+
+inline size_t align_up(size_t x, size_t a = 256) { return (x + a - 1) / a * a; }
+
+// Stage ids of the built-in event timing (egs_profile_* in the header).
+enum Stage {
+  ST_PREPROCESS = 0, ST_SCAN, ST_DUPLICATE, ST_SORT_HIST, ST_SORT_PASSES, ST_RANGES, ST_BLEND_FWD,
+  ST_BWD_ZERO, ST_BLEND_BWD, ST_PREPROCESS_BWD, ST_ADAM, ST_SE3, ST_COUNT
+};
+static_assert(ST_COUNT <= EGS_PROFILE_STAGES, "grow EGS_PROFILE_STAGES");
+bool profiling_enabled();
+void profile_begin(cudaStream_t stream, int stage, void** token);
+void profile_end(cudaStream_t stream, void* token);
+// RAII bracket: records an event pair around the launches issued in its scope
+struct StageTimer {
+  cudaStream_t stream;
+  void* token = nullptr;
+  StageTimer(cudaStream_t s, int stage) : stream(s) {
+    if (profiling_enabled()) profile_begin(s, stage, &token);
+  }
+  ~StageTimer() {
+    if (token) profile_end(stream, token);
+  }
+};
+
+// ---------------------------------------------------------------------------------------------
+// workspace carving (pure functions of the sizes, so backward can re-derive the pointers)
+// ---------------------------------------------------------------------------------------------
+constexpr int SCAN_TILE = 4096;   // elements per block of the tiles_touched scan
+
+struct GeomLayout {
+  size_t depths, means2D, conic_opacity, rgb_depth, clamped, tiles_touched, point_offsets,
+      scan_status, total;
+  explicit GeomLayout(size_t P) {
+    size_t o = 0;
+    auto take = [&](size_t bytes) { size_t r = o; o = align_up(o + bytes); return r; };
+    depths = take(P * 4);
+    means2D = take(P * 8);
+    conic_opacity = take(P * 16);
+    rgb_depth = take(P * 16);
+    clamped = take(P);
+    tiles_touched = take(P * 4);
+    point_offsets = take(P * 4);
+    scan_status = take(((P + SCAN_TILE - 1) / SCAN_TILE + 1) * 8 + 256);
+    total = o + 256;
+  }
+};
+
+struct GeomPtrs {
+  float* depths;
+  float2* means2D;
+  float4* conic_opacity;
+  float4* rgb_depth;
+  unsigned char* clamped;
+  uint32_t* tiles_touched;
+  uint32_t* point_offsets;
+  unsigned long long* scan_status;  // [0] ticket, [1..] per-block status words
+  GeomPtrs(void* base, size_t P) {
+    GeomLayout L(P);
+    char* b = static_cast<char*>(base);
+    depths = reinterpret_cast<float*>(b + L.depths);
+    means2D = reinterpret_cast<float2*>(b + L.means2D);
+    conic_opacity = reinterpret_cast<float4*>(b + L.conic_opacity);
+    rgb_depth = reinterpret_cast<float4*>(b + L.rgb_depth);
+    clamped = reinterpret_cast<unsigned char*>(b + L.clamped);
+    tiles_touched = reinterpret_cast<uint32_t*>(b + L.tiles_touched);
+    point_offsets = reinterpret_cast<uint32_t*>(b + L.point_offsets);
+    scan_status = reinterpret_cast<unsigned long long*>(b + L.scan_status);
+  }
+};
+
+inline int tiles_x(int W) { return (W + TILE_X - 1) / TILE_X; }
+inline int tiles_y(int H) { return (H + TILE_Y - 1) / TILE_Y; }
+
+// Number of key bits above the 32 depth bits that take part in the sort: the same count the
+// reference derives with getHigherMsb (rasterizer_impl.cu:35-50): the smallest b with
+// (n >> b) == 0, i.e. bit_length(n).
+inline int tile_id_bits(uint32_t n_tiles) {
+  int b = 0;
+  while (b < 32 && (n_tiles >> b)) ++b;
+  return b;
+}
+
+constexpr int SORT_RADIX_BITS = 8;
+constexpr int SORT_RADIX = 1 << SORT_RADIX_BITS;
+constexpr int SORT_THREADS = 256;
+constexpr int SORT_ITEMS = 16;
+constexpr int SORT_TILE = SORT_THREADS * SORT_ITEMS;
+constexpr int SORT_MAX_PASSES = 8;
+
+inline int sort_passes(int W, int H) {
+  int bits = 32 + tile_id_bits((uint32_t)(tiles_x(W) * tiles_y(H)));
+  return (bits + SORT_RADIX_BITS - 1) / SORT_RADIX_BITS;
+}
+
+struct BinningLayout {
+  size_t keys[2], vals[2], hist, status, ticket, total;
+  size_t sort_blocks;
+  explicit BinningLayout(size_t R) {
+    size_t o = 0;
+    auto take = [&](size_t bytes) { size_t r = o; o = align_up(o + bytes); return r; };
+    sort_blocks = (R + SORT_TILE - 1) / SORT_TILE;
+    keys[0] = take(R * 8);
+    keys[1] = take(R * 8);
+    vals[0] = take(R * 4);
+    vals[1] = take(R * 4);
+    // everything from `hist` to the end is zeroed with one memset per forward
+    hist = take(SORT_MAX_PASSES * SORT_RADIX * 4);
+    ticket = take(SORT_MAX_PASSES * 4);
+    status = take(SORT_MAX_PASSES * sort_blocks * SORT_RADIX * 4);
+    total = o + 256;
+  }
+};
+
+struct BinningPtrs {
+  uint64_t* keys[2];
+  uint32_t* vals[2];
+  uint32_t* hist;
+  uint32_t* ticket;
+  uint32_t* status;
+  size_t sort_blocks;
+  size_t zero_bytes;  // bytes to clear starting at `hist`
+  BinningPtrs(void* base, size_t R) {
+    BinningLayout L(R);
+    char* b = static_cast<char*>(base);
+    keys[0] = reinterpret_cast<uint64_t*>(b + L.keys[0]);
+    keys[1] = reinterpret_cast<uint64_t*>(b + L.keys[1]);
+    vals[0] = reinterpret_cast<uint32_t*>(b + L.vals[0]);
+    vals[1] = reinterpret_cast<uint32_t*>(b + L.vals[1]);
+    hist = reinterpret_cast<uint32_t*>(b + L.hist);
+    ticket = reinterpret_cast<uint32_t*>(b + L.ticket);
+    status = reinterpret_cast<uint32_t*>(b + L.status);
+    sort_blocks = L.sort_blocks;
+    zero_bytes = L.total - 256 - L.hist;
+  }
+};
+
+struct ImageLayout {
+  size_t n_contrib, ranges, total;
+  ImageLayout(int W, int H) {
+    size_t o = 0;
+    auto take = [&](size_t bytes) { size_t r = o; o = align_up(o + bytes); return r; };
+    n_contrib = take((size_t)W * H * 4);
+    ranges = take((size_t)tiles_x(W) * tiles_y(H) * 8);
+    total = o + 256;
+  }
+};
+
+struct ImagePtrs {
+  uint32_t* n_contrib;
+  uint2* ranges;
+  ImagePtrs(void* base, int W, int H) {
+    ImageLayout L(W, H);
+    char* b = static_cast<char*>(base);
+    n_contrib = reinterpret_cast<uint32_t*>(b + L.n_contrib);
+    ranges = reinterpret_cast<uint2*>(b + L.ranges);
+  }
+};
+
+// Backward scratch: one 48-byte accumulator record per Gaussian, three float4 so the tile
+// kernel can use vector reductions:
+//   acc[0] = (dL/dmean2D.x, dL/dmean2D.y, dL/dopacity, dL/ddepth)
+//   acc[1] = (dL/dconic.x, dL/dconic.y, dL/dconic.w, unused)
+//   acc[2] = (dL/dcolor.r, .g, .b, unused)
+struct BackwardScratch {
+  float4* acc;  // [P][3]
+  static size_t bytes(size_t P) { return align_up(P * 48) + 256; }
+  explicit BackwardScratch(void* base) : acc(static_cast<float4*>(base)) {}
+};
+
+// ---------------------------------------------------------------------------------------------
+// stage entry points (each enqueues kernels on `stream`; return EgsStatus)
+// ---------------------------------------------------------------------------------------------
+int launch_preprocess_forward(const EgsForwardArgs& a, const GeomPtrs& g, cudaStream_t stream);
+int launch_scan_tiles(const GeomPtrs& g, int P, cudaStream_t stream, bool debug);
+int launch_binning(const GeomPtrs& g, const BinningPtrs& b, const ImagePtrs& im, const int* radii,
+                   int P, int R, int W, int H, cudaStream_t stream, bool debug);
+int launch_blend_forward(const EgsForwardArgs& a, const GeomPtrs& g, const uint32_t* point_list,
+                         const ImagePtrs& im, cudaStream_t stream);
+int launch_blend_backward(const EgsBackwardArgs& a, const GeomPtrs& g, const uint32_t* point_list,
+                          const ImagePtrs& im, const BackwardScratch& s, cudaStream_t stream);
+int launch_preprocess_backward(const EgsBackwardArgs& a, const GeomPtrs& g,
+                               const BackwardScratch& s, cudaStream_t stream);
+int launch_mark_visible(int P, const float* means3D, const float* view, const float* proj,
+                        unsigned char* present, cudaStream_t stream);
+
+}  // namespace egs
+
+// ---------------------------------------------------------------------------------------------
+// device helpers
+// ---------------------------------------------------------------------------------------------
+#ifdef __CUDACC__
+namespace egs {
+
+// SH basis constants (real spherical harmonics, same values as utils/sh_utils.py:24-54 and
+// DGR/cuda_rasterizer/auxiliary.h:22-39).
+__device__ constexpr float kSH0 = 0.28209479177387814f;
+__device__ constexpr float kSH1 = 0.4886025119029199f;
+__device__ constexpr float kSH2[5] = {1.0925484305920792f, -1.0925484305920792f,
+                                      0.31539156525252005f, -1.0925484305920792f,
+                                      0.5462742152960396f};
+__device__ constexpr float kSH3[7] = {-0.5900435899266435f, 2.890611442640554f,
+                                      -0.4570457994644658f, 0.3731763325901154f,
+                                      -0.4570457994644658f, 1.445305721320277f,
+                                      -0.5900435899266435f};
+
+// Column-major 3x3 with the same storage convention and the same product evaluation order as
+// the reference's matrix library (glm/detail/type_mat3x3.inl:486-520): entry (col c, row r) is
+// c[c][r], and (A*B)[c][r] = A[0][r]*B[c][0] + A[1][r]*B[c][1] + A[2][r]*B[c][2], summed left to
+// right. Bit-exact radii and sort keys depend on this order.
+struct Mat3 {
+  float c[3][3];
+};
+
+__device__ __forceinline__ Mat3 mat3_cols(float a0, float a1, float a2, float b0, float b1,
+                                          float b2, float c0, float c1, float c2) {
+  Mat3 m;
+  m.c[0][0] = a0; m.c[0][1] = a1; m.c[0][2] = a2;
+  m.c[1][0] = b0; m.c[1][1] = b1; m.c[1][2] = b2;
+  m.c[2][0] = c0; m.c[2][1] = c1; m.c[2][2] = c2;
+  return m;
+}
+
+__device__ __forceinline__ Mat3 mul(const Mat3& A, const Mat3& B) {
+  Mat3 R;
+#pragma unroll
+  for (int col = 0; col < 3; ++col)
+#pragma unroll
+    for (int row = 0; row < 3; ++row)
+      R.c[col][row] = A.c[0][row] * B.c[col][0] + A.c[1][row] * B.c[col][1] + A.c[2][row] * B.c[col][2];
+  return R;
+}
+
+__device__ __forceinline__ Mat3 transpose(const Mat3& A) {
+  Mat3 R;
+#pragma unroll
+  for (int col = 0; col < 3; ++col)
+#pragma unroll
+    for (int row = 0; row < 3; ++row) R.c[col][row] = A.c[row][col];
+  return R;
+}
+
+// Row-vector 4x4 transforms on the transposed matrices the reference passes around
+// (auxiliary.h:58-76): memory index 4*c + r.
+__device__ __forceinline__ float3 xform_point_4x3(const float3& p, const float* m) {
+  float3 r;
+  r.x = m[0] * p.x + m[4] * p.y + m[8] * p.z + m[12];
+  r.y = m[1] * p.x + m[5] * p.y + m[9] * p.z + m[13];
+  r.z = m[2] * p.x + m[6] * p.y + m[10] * p.z + m[14];
+  return r;
+}
+
+__device__ __forceinline__ float4 xform_point_4x4(const float3& p, const float* m) {
+  float4 r;
+  r.x = m[0] * p.x + m[4] * p.y + m[8] * p.z + m[12];
+  r.y = m[1] * p.x + m[5] * p.y + m[9] * p.z + m[13];
+  r.z = m[2] * p.x + m[6] * p.y + m[10] * p.z + m[14];
+  r.w = m[3] * p.x + m[7] * p.y + m[11] * p.z + m[15];
+  return r;
+}
+
+// Pixel centre from NDC; evaluated in double like auxiliary.h:41-44 (double literals).
+__device__ __forceinline__ float ndc_to_pix(float v, int S) {
+  return ((v + 1.0) * S - 1.0) * 0.5;
+}
+
+// Tile rectangle covered by a disc of integer radius r around p (auxiliary.h:46-56).
+__device__ __forceinline__ void tile_rect(const float2 p, int r, int gx, int gy, uint2& lo, uint2& hi) {
+  lo.x = min(gx, max(0, (int)((p.x - r) / TILE_X)));
+  lo.y = min(gy, max(0, (int)((p.y - r) / TILE_Y)));
+  hi.x = min(gx, max(0, (int)((p.x + r + TILE_X - 1) / TILE_X)));
+  hi.y = min(gy, max(0, (int)((p.y + r + TILE_Y - 1) / TILE_Y)));
+}
+
+__device__ __forceinline__ unsigned lane_id() { return threadIdx.x & 31; }
+
+}  // namespace egs
+#endif  // __CUDACC__

@@ -1,0 +1,395 @@
+// preprocess_bwd.cu -- per-Gaussian backward stage, one fused kernel.
+//
+// Replaces the reference's two kernels computeCov2DCUDA (DGR/cuda_rasterizer/backward.cu:144-274)
+// and backward preprocessCUDA (:346-412, with the SH backward :20-139 and the scale/rotation
+// backward :278-341), as restated in SURVEY.md App. A.8b / A.8c. Fusing them keeps dL/dcov3D in
+// registers in the scale+rotation mode and sums the four parts of dL/dmean3D in registers in the
+// reference's order (covariance part, projection part, depth part, SH view-direction part).
+//
+// The kernel also unpacks the 48-byte accumulator record written by the tile kernel into the
+// caller-facing dL/dmeans2D, dL/dopacity and dL/dcolors tensors, and writes zeros for culled
+// Gaussians, so none of the outputs needs a prior memset (the reference zero-fills ten tensors,
+// 304 B per Gaussian at SH degree 3, rasterize_points.cu:158-167).
+#include "common.cuh"
+
+namespace egs {
+
+__device__ __forceinline__ float3 xform_vec_4x3_T(const float3& p, const float* m) {
+  float3 r;
+  r.x = m[0] * p.x + m[1] * p.y + m[2] * p.z;
+  r.y = m[4] * p.x + m[5] * p.y + m[6] * p.z;
+  r.z = m[8] * p.x + m[9] * p.y + m[10] * p.z;
+  return r;
+}
+
+// d(v/|v|)/dv applied to dv (auxiliary.h:107-117)
+__device__ __forceinline__ float3 dnormalize(const float3 v, const float3 dv) {
+  const float sum2 = v.x * v.x + v.y * v.y + v.z * v.z;
+  const float invsum32 = 1.0f / sqrtf(sum2 * sum2 * sum2);
+  float3 r;
+  r.x = ((+sum2 - v.x * v.x) * dv.x - v.y * v.x * dv.y - v.z * v.x * dv.z) * invsum32;
+  r.y = (-v.x * v.y * dv.x + (sum2 - v.y * v.y) * dv.y - v.z * v.y * dv.z) * invsum32;
+  r.z = (-v.x * v.z * dv.x - v.y * v.z * dv.y + (sum2 - v.z * v.z) * dv.z) * invsum32;
+  return r;
+}
+
+struct F3 {
+  float x, y, z;
+};
+__device__ __forceinline__ F3 operator*(float s, const F3& a) { return {s * a.x, s * a.y, s * a.z}; }
+__device__ __forceinline__ F3 operator*(const F3& a, float s) { return {a.x * s, a.y * s, a.z * s}; }
+__device__ __forceinline__ F3 operator+(const F3& a, const F3& b) { return {a.x + b.x, a.y + b.y, a.z + b.z}; }
+__device__ __forceinline__ F3 operator-(const F3& a) { return {-a.x, -a.y, -a.z}; }
+__device__ __forceinline__ float dot(const F3& a, const F3& b) { return a.x * b.x + a.y * b.y + a.z * b.z; }
+
+// SH backward: writes dL/dsh[0 .. M) (zeros above the active degree) and returns the part of
+// dL/dmean caused by the view direction.
+__device__ __forceinline__ float3 sh_backward(int deg, int M, const float3 pos, const float3 cam,
+                                              const float* __restrict__ shp, unsigned char clamp_bits,
+                                              F3 dL_dRGB, float* __restrict__ dL_dsh_out) {
+  const float3 dir_orig = make_float3(pos.x - cam.x, pos.y - cam.y, pos.z - cam.z);
+  const float len = sqrtf(dir_orig.x * dir_orig.x + dir_orig.y * dir_orig.y + dir_orig.z * dir_orig.z);
+  const float x = dir_orig.x / len, y = dir_orig.y / len, z = dir_orig.z / len;
+  dL_dRGB.x *= (clamp_bits & 1) ? 0.f : 1.f;
+  dL_dRGB.y *= (clamp_bits & 2) ? 0.f : 1.f;
+  dL_dRGB.z *= (clamp_bits & 4) ? 0.f : 1.f;
+
+  auto sh = [&](int k) -> F3 { return {__ldg(shp + 3 * k), __ldg(shp + 3 * k + 1), __ldg(shp + 3 * k + 2)}; };
+  auto put = [&](int k, float w) {
+    dL_dsh_out[3 * k] = w * dL_dRGB.x;
+    dL_dsh_out[3 * k + 1] = w * dL_dRGB.y;
+    dL_dsh_out[3 * k + 2] = w * dL_dRGB.z;
+  };
+  F3 dRGBdx = {0, 0, 0}, dRGBdy = {0, 0, 0}, dRGBdz = {0, 0, 0};
+  put(0, kSH0);
+  int written = 1;
+  if (deg > 0) {
+    put(1, -kSH1 * y);
+    put(2, kSH1 * z);
+    put(3, -kSH1 * x);
+    written = 4;
+    dRGBdx = -kSH1 * sh(3);
+    dRGBdy = -kSH1 * sh(1);
+    dRGBdz = kSH1 * sh(2);
+    if (deg > 1) {
+      const float xx = x * x, yy = y * y, zz = z * z;
+      const float xy = x * y, yz = y * z, xz = x * z;
+      put(4, kSH2[0] * xy);
+      put(5, kSH2[1] * yz);
+      put(6, kSH2[2] * (2.f * zz - xx - yy));
+      put(7, kSH2[3] * xz);
+      put(8, kSH2[4] * (xx - yy));
+      written = 9;
+      dRGBdx = dRGBdx + kSH2[0] * y * sh(4) + kSH2[2] * 2.f * -x * sh(6) + kSH2[3] * z * sh(7) +
+               kSH2[4] * 2.f * x * sh(8);
+      dRGBdy = dRGBdy + kSH2[0] * x * sh(4) + kSH2[1] * z * sh(5) + kSH2[2] * 2.f * -y * sh(6) +
+               kSH2[4] * 2.f * -y * sh(8);
+      dRGBdz = dRGBdz + kSH2[1] * y * sh(5) + kSH2[2] * 2.f * 2.f * z * sh(6) + kSH2[3] * x * sh(7);
+      if (deg > 2) {
+        put(9, kSH3[0] * y * (3.f * xx - yy));
+        put(10, kSH3[1] * xy * z);
+        put(11, kSH3[2] * y * (4.f * zz - xx - yy));
+        put(12, kSH3[3] * z * (2.f * zz - 3.f * xx - 3.f * yy));
+        put(13, kSH3[4] * x * (4.f * zz - xx - yy));
+        put(14, kSH3[5] * z * (xx - yy));
+        put(15, kSH3[6] * x * (xx - 3.f * yy));
+        written = 16;
+        dRGBdx = dRGBdx + (kSH3[0] * sh(9) * 3.f * 2.f * xy + kSH3[1] * sh(10) * yz +
+                           kSH3[2] * sh(11) * -2.f * xy + kSH3[3] * sh(12) * -3.f * 2.f * xz +
+                           kSH3[4] * sh(13) * (-3.f * xx + 4.f * zz - yy) +
+                           kSH3[5] * sh(14) * 2.f * xz + kSH3[6] * sh(15) * 3.f * (xx - yy));
+        dRGBdy = dRGBdy + (kSH3[0] * sh(9) * 3.f * (xx - yy) + kSH3[1] * sh(10) * xz +
+                           kSH3[2] * sh(11) * (-3.f * yy + 4.f * zz - xx) +
+                           kSH3[3] * sh(12) * -3.f * 2.f * yz + kSH3[4] * sh(13) * -2.f * xy +
+                           kSH3[5] * sh(14) * -2.f * yz + kSH3[6] * sh(15) * -3.f * 2.f * xy);
+        dRGBdz = dRGBdz + (kSH3[1] * sh(10) * xy + kSH3[2] * sh(11) * 4.f * 2.f * yz +
+                           kSH3[3] * sh(12) * 3.f * (2.f * zz - xx - yy) +
+                           kSH3[4] * sh(13) * 4.f * 2.f * xz + kSH3[5] * sh(14) * (xx - yy));
+      }
+    }
+  }
+  for (int k = written; k < M; ++k) {
+    dL_dsh_out[3 * k] = 0.f;
+    dL_dsh_out[3 * k + 1] = 0.f;
+    dL_dsh_out[3 * k + 2] = 0.f;
+  }
+  const float3 dL_ddir = make_float3(dot(dRGBdx, dL_dRGB), dot(dRGBdy, dL_dRGB), dot(dRGBdz, dL_dRGB));
+  return dnormalize(dir_orig, dL_ddir);
+}
+
+// dL/dSigma (6 packed) -> dL/dscale, dL/dquaternion (no normalisation Jacobian; the reference
+// has it commented out, backward.cu:281,340).
+__device__ __forceinline__ void cov3d_backward(const float3 scale, float mod, const float4 rot,
+                                               const float* dL_dcov6, float3& dL_dscale,
+                                               float4& dL_drot) {
+  const float r = rot.x, x = rot.y, y = rot.z, z = rot.w;
+  const Mat3 R = mat3_cols(1.f - 2.f * (y * y + z * z), 2.f * (x * y - r * z), 2.f * (x * z + r * y),
+                           2.f * (x * y + r * z), 1.f - 2.f * (x * x + z * z), 2.f * (y * z - r * x),
+                           2.f * (x * z - r * y), 2.f * (y * z + r * x), 1.f - 2.f * (x * x + y * y));
+  Mat3 S = mat3_cols(1.f, 0.f, 0.f, 0.f, 1.f, 0.f, 0.f, 0.f, 1.f);
+  const float3 s = make_float3(mod * scale.x, mod * scale.y, mod * scale.z);
+  S.c[0][0] = s.x;
+  S.c[1][1] = s.y;
+  S.c[2][2] = s.z;
+  const Mat3 M = mul(S, R);
+  const Mat3 dSigma = mat3_cols(dL_dcov6[0], 0.5f * dL_dcov6[1], 0.5f * dL_dcov6[2],
+                                0.5f * dL_dcov6[1], dL_dcov6[3], 0.5f * dL_dcov6[4],
+                                0.5f * dL_dcov6[2], 0.5f * dL_dcov6[4], dL_dcov6[5]);
+  Mat3 M2 = M;
+#pragma unroll
+  for (int c = 0; c < 3; ++c)
+#pragma unroll
+    for (int rr = 0; rr < 3; ++rr) M2.c[c][rr] = M.c[c][rr] * 2.0f;
+  const Mat3 dL_dM = mul(M2, dSigma);
+  const Mat3 Rt = transpose(R);
+  Mat3 dMt = transpose(dL_dM);
+  dL_dscale.x = Rt.c[0][0] * dMt.c[0][0] + Rt.c[0][1] * dMt.c[0][1] + Rt.c[0][2] * dMt.c[0][2];
+  dL_dscale.y = Rt.c[1][0] * dMt.c[1][0] + Rt.c[1][1] * dMt.c[1][1] + Rt.c[1][2] * dMt.c[1][2];
+  dL_dscale.z = Rt.c[2][0] * dMt.c[2][0] + Rt.c[2][1] * dMt.c[2][1] + Rt.c[2][2] * dMt.c[2][2];
+#pragma unroll
+  for (int k = 0; k < 3; ++k) {
+    dMt.c[0][k] *= s.x;
+    dMt.c[1][k] *= s.y;
+    dMt.c[2][k] *= s.z;
+  }
+  dL_drot.x = 2 * z * (dMt.c[0][1] - dMt.c[1][0]) + 2 * y * (dMt.c[2][0] - dMt.c[0][2]) +
+              2 * x * (dMt.c[1][2] - dMt.c[2][1]);
+  dL_drot.y = 2 * y * (dMt.c[1][0] + dMt.c[0][1]) + 2 * z * (dMt.c[2][0] + dMt.c[0][2]) +
+              2 * r * (dMt.c[1][2] - dMt.c[2][1]) - 4 * x * (dMt.c[2][2] + dMt.c[1][1]);
+  dL_drot.z = 2 * x * (dMt.c[1][0] + dMt.c[0][1]) + 2 * r * (dMt.c[2][0] - dMt.c[0][2]) +
+              2 * z * (dMt.c[1][2] + dMt.c[2][1]) - 4 * y * (dMt.c[2][2] + dMt.c[0][0]);
+  dL_drot.w = 2 * r * (dMt.c[0][1] - dMt.c[1][0]) + 2 * x * (dMt.c[2][0] + dMt.c[0][2]) +
+              2 * y * (dMt.c[1][2] + dMt.c[2][1]) - 4 * z * (dMt.c[1][1] + dMt.c[0][0]);
+}
+
+// forward-side helper shared with preprocess.cu (same arithmetic, kept local to this TU)
+__device__ __forceinline__ void cov3d_recompute(const float3 s, float mod, const float4 q, float* cov6) {
+  Mat3 S = mat3_cols(1.f, 0.f, 0.f, 0.f, 1.f, 0.f, 0.f, 0.f, 1.f);
+  S.c[0][0] = mod * s.x;
+  S.c[1][1] = mod * s.y;
+  S.c[2][2] = mod * s.z;
+  const float r = q.x, x = q.y, y = q.z, z = q.w;
+  const Mat3 R = mat3_cols(1.f - 2.f * (y * y + z * z), 2.f * (x * y - r * z), 2.f * (x * z + r * y),
+                           2.f * (x * y + r * z), 1.f - 2.f * (x * x + z * z), 2.f * (y * z - r * x),
+                           2.f * (x * z - r * y), 2.f * (y * z + r * x), 1.f - 2.f * (x * x + y * y));
+  const Mat3 M = mul(S, R);
+  const Mat3 Sigma = mul(transpose(M), M);
+  cov6[0] = Sigma.c[0][0];
+  cov6[1] = Sigma.c[0][1];
+  cov6[2] = Sigma.c[0][2];
+  cov6[3] = Sigma.c[1][1];
+  cov6[4] = Sigma.c[1][2];
+  cov6[5] = Sigma.c[2][2];
+}
+
+__global__ void __launch_bounds__(256)
+preprocess_backward_kernel(int P, int D, int M, const float* __restrict__ means3D,
+                           const int* __restrict__ radii, const float* __restrict__ shs,
+                           const unsigned char* __restrict__ clamped,
+                           const float* __restrict__ scales, const float* __restrict__ rotations,
+                           const float* __restrict__ cov3D_precomp,
+                           const float* __restrict__ colors_precomp, float scale_modifier,
+                           const float* __restrict__ viewmatrix, const float* __restrict__ projmatrix,
+                           const float* __restrict__ campos, float h_x, float h_y, float tan_fovx,
+                           float tan_fovy, const float4* __restrict__ acc,
+                           float* __restrict__ dL_dmeans2D, float* __restrict__ dL_dcolors,
+                           float* __restrict__ dL_dopacity, float* __restrict__ dL_dmeans3D,
+                           float* __restrict__ dL_dcov3D, float* __restrict__ dL_dsh,
+                           float* __restrict__ dL_dscales, float* __restrict__ dL_drot) {
+  __shared__ float view[16], proj[16], s_cam[3];
+  if (threadIdx.x < 16) {
+    view[threadIdx.x] = viewmatrix[threadIdx.x];
+    proj[threadIdx.x] = projmatrix[threadIdx.x];
+  }
+  if (threadIdx.x < 3) s_cam[threadIdx.x] = campos[threadIdx.x];
+  __syncthreads();
+  const int idx = blockIdx.x * blockDim.x + threadIdx.x;
+  if (idx >= P) return;
+
+  if (!(radii[idx] > 0)) {
+    // culled: every gradient is zero
+#pragma unroll
+    for (int k = 0; k < 3; ++k) {
+      dL_dmeans2D[3 * idx + k] = 0.f;
+      dL_dmeans3D[3 * idx + k] = 0.f;
+    }
+    dL_dopacity[idx] = 0.f;
+    if (colors_precomp != nullptr) {
+#pragma unroll
+      for (int k = 0; k < 3; ++k) dL_dcolors[3 * idx + k] = 0.f;
+    }
+    if (cov3D_precomp != nullptr) {
+#pragma unroll
+      for (int k = 0; k < 6; ++k) dL_dcov3D[6 * idx + k] = 0.f;
+    }
+    if (shs != nullptr) {
+      float* o = dL_dsh + (size_t)idx * M * 3;
+      for (int k = 0; k < 3 * M; ++k) o[k] = 0.f;
+    }
+    if (scales != nullptr) {
+#pragma unroll
+      for (int k = 0; k < 3; ++k) dL_dscales[3 * idx + k] = 0.f;
+      reinterpret_cast<float4*>(dL_drot)[idx] = make_float4(0.f, 0.f, 0.f, 0.f);
+    }
+    return;
+  }
+
+  const float4 a0 = acc[3 * (size_t)idx + 0];  // dmean2D.x, dmean2D.y, dopacity, ddepth
+  const float4 a1 = acc[3 * (size_t)idx + 1];  // dconic.x, .y, .w
+  const float4 a2 = acc[3 * (size_t)idx + 2];  // dcolor rgb
+  dL_dmeans2D[3 * idx + 0] = a0.x;
+  dL_dmeans2D[3 * idx + 1] = a0.y;
+  dL_dmeans2D[3 * idx + 2] = 0.f;
+  dL_dopacity[idx] = a0.z;
+  const float dL_ddepth = a0.w;
+
+  const float3 mean = make_float3(means3D[3 * idx], means3D[3 * idx + 1], means3D[3 * idx + 2]);
+
+  // ---- covariance chain (App. A.8b) --------------------------------------------------------
+  float cov6[6];
+  float3 scl = make_float3(0.f, 0.f, 0.f);
+  float4 rot = make_float4(0.f, 0.f, 0.f, 0.f);
+  if (cov3D_precomp != nullptr) {
+#pragma unroll
+    for (int k = 0; k < 6; ++k) cov6[k] = cov3D_precomp[6 * idx + k];
+  } else {
+    scl = make_float3(scales[3 * idx], scales[3 * idx + 1], scales[3 * idx + 2]);
+    rot = reinterpret_cast<const float4*>(rotations)[idx];
+    cov3d_recompute(scl, scale_modifier, rot, cov6);
+  }
+
+  const float3 dL_dconic = make_float3(a1.x, a1.y, a1.z);
+  float3 t = xform_point_4x3(mean, view);
+  const float limx = 1.3f * tan_fovx;
+  const float limy = 1.3f * tan_fovy;
+  const float txtz = t.x / t.z;
+  const float tytz = t.y / t.z;
+  t.x = min(limx, max(-limx, txtz)) * t.z;
+  t.y = min(limy, max(-limy, tytz)) * t.z;
+  const float x_grad_mul = txtz < -limx || txtz > limx ? 0 : 1;
+  const float y_grad_mul = tytz < -limy || tytz > limy ? 0 : 1;
+
+  const Mat3 J = mat3_cols(h_x / t.z, 0.0f, -(h_x * t.x) / (t.z * t.z),
+                           0.0f, h_y / t.z, -(h_y * t.y) / (t.z * t.z),
+                           0.f, 0.f, 0.f);
+  const Mat3 Wm = mat3_cols(view[0], view[4], view[8], view[1], view[5], view[9], view[2], view[6],
+                            view[10]);
+  const Mat3 Vrk = mat3_cols(cov6[0], cov6[1], cov6[2], cov6[1], cov6[3], cov6[4], cov6[2], cov6[4],
+                             cov6[5]);
+  const Mat3 T = mul(Wm, J);
+  Mat3 cov2D = mul(mul(transpose(T), transpose(Vrk)), T);
+  const float a = cov2D.c[0][0] += 0.3f;
+  const float b = cov2D.c[0][1];
+  const float c = cov2D.c[1][1] += 0.3f;
+
+  const float denom = a * c - b * b;
+  float dL_da = 0, dL_db = 0, dL_dc = 0;
+  const float denom2inv = 1.0f / ((denom * denom) + 0.0000001f);
+  float dcov[6] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+  if (denom2inv != 0) {
+    dL_da = denom2inv * (-c * c * dL_dconic.x + 2 * b * c * dL_dconic.y + (denom - a * c) * dL_dconic.z);
+    dL_dc = denom2inv * (-a * a * dL_dconic.z + 2 * a * b * dL_dconic.y + (denom - a * c) * dL_dconic.x);
+    dL_db = denom2inv * 2 * (b * c * dL_dconic.x - (denom + 2 * b * b) * dL_dconic.y + a * b * dL_dconic.z);
+
+    dcov[0] = (T.c[0][0] * T.c[0][0] * dL_da + T.c[0][0] * T.c[1][0] * dL_db + T.c[1][0] * T.c[1][0] * dL_dc);
+    dcov[3] = (T.c[0][1] * T.c[0][1] * dL_da + T.c[0][1] * T.c[1][1] * dL_db + T.c[1][1] * T.c[1][1] * dL_dc);
+    dcov[5] = (T.c[0][2] * T.c[0][2] * dL_da + T.c[0][2] * T.c[1][2] * dL_db + T.c[1][2] * T.c[1][2] * dL_dc);
+    dcov[1] = 2 * T.c[0][0] * T.c[0][1] * dL_da + (T.c[0][0] * T.c[1][1] + T.c[0][1] * T.c[1][0]) * dL_db + 2 * T.c[1][0] * T.c[1][1] * dL_dc;
+    dcov[2] = 2 * T.c[0][0] * T.c[0][2] * dL_da + (T.c[0][0] * T.c[1][2] + T.c[0][2] * T.c[1][0]) * dL_db + 2 * T.c[1][0] * T.c[1][2] * dL_dc;
+    dcov[4] = 2 * T.c[0][2] * T.c[0][1] * dL_da + (T.c[0][1] * T.c[1][2] + T.c[0][2] * T.c[1][1]) * dL_db + 2 * T.c[1][1] * T.c[1][2] * dL_dc;
+  }
+
+  // dL/dT (upper 2x3), dL/dJ (4 non-zero entries), dL/dt
+  const float dL_dT00 = 2 * (T.c[0][0] * Vrk.c[0][0] + T.c[0][1] * Vrk.c[0][1] + T.c[0][2] * Vrk.c[0][2]) * dL_da +
+                        (T.c[1][0] * Vrk.c[0][0] + T.c[1][1] * Vrk.c[0][1] + T.c[1][2] * Vrk.c[0][2]) * dL_db;
+  const float dL_dT01 = 2 * (T.c[0][0] * Vrk.c[1][0] + T.c[0][1] * Vrk.c[1][1] + T.c[0][2] * Vrk.c[1][2]) * dL_da +
+                        (T.c[1][0] * Vrk.c[1][0] + T.c[1][1] * Vrk.c[1][1] + T.c[1][2] * Vrk.c[1][2]) * dL_db;
+  const float dL_dT02 = 2 * (T.c[0][0] * Vrk.c[2][0] + T.c[0][1] * Vrk.c[2][1] + T.c[0][2] * Vrk.c[2][2]) * dL_da +
+                        (T.c[1][0] * Vrk.c[2][0] + T.c[1][1] * Vrk.c[2][1] + T.c[1][2] * Vrk.c[2][2]) * dL_db;
+  const float dL_dT10 = 2 * (T.c[1][0] * Vrk.c[0][0] + T.c[1][1] * Vrk.c[0][1] + T.c[1][2] * Vrk.c[0][2]) * dL_dc +
+                        (T.c[0][0] * Vrk.c[0][0] + T.c[0][1] * Vrk.c[0][1] + T.c[0][2] * Vrk.c[0][2]) * dL_db;
+  const float dL_dT11 = 2 * (T.c[1][0] * Vrk.c[1][0] + T.c[1][1] * Vrk.c[1][1] + T.c[1][2] * Vrk.c[1][2]) * dL_dc +
+                        (T.c[0][0] * Vrk.c[1][0] + T.c[0][1] * Vrk.c[1][1] + T.c[0][2] * Vrk.c[1][2]) * dL_db;
+  const float dL_dT12 = 2 * (T.c[1][0] * Vrk.c[2][0] + T.c[1][1] * Vrk.c[2][1] + T.c[1][2] * Vrk.c[2][2]) * dL_dc +
+                        (T.c[0][0] * Vrk.c[2][0] + T.c[0][1] * Vrk.c[2][1] + T.c[0][2] * Vrk.c[2][2]) * dL_db;
+
+  const float dL_dJ00 = Wm.c[0][0] * dL_dT00 + Wm.c[0][1] * dL_dT01 + Wm.c[0][2] * dL_dT02;
+  const float dL_dJ02 = Wm.c[2][0] * dL_dT00 + Wm.c[2][1] * dL_dT01 + Wm.c[2][2] * dL_dT02;
+  const float dL_dJ11 = Wm.c[1][0] * dL_dT10 + Wm.c[1][1] * dL_dT11 + Wm.c[1][2] * dL_dT12;
+  const float dL_dJ12 = Wm.c[2][0] * dL_dT10 + Wm.c[2][1] * dL_dT11 + Wm.c[2][2] * dL_dT12;
+
+  const float tz = 1.f / t.z;
+  const float tz2 = tz * tz;
+  const float tz3 = tz2 * tz;
+  const float dL_dtx = x_grad_mul * -h_x * tz2 * dL_dJ02;
+  const float dL_dty = y_grad_mul * -h_y * tz2 * dL_dJ12;
+  const float dL_dtz = -h_x * tz2 * dL_dJ00 - h_y * tz2 * dL_dJ11 + (2 * h_x * t.x) * tz3 * dL_dJ02 +
+                       (2 * h_y * t.y) * tz3 * dL_dJ12;
+  float3 dmean = xform_vec_4x3_T(make_float3(dL_dtx, dL_dty, dL_dtz), view);
+
+  // ---- projection part (App. A.8c (1)) ------------------------------------------------------
+  {
+    const float4 m_hom = xform_point_4x4(mean, proj);
+    const float m_w = 1.0f / (m_hom.w + 0.0000001f);
+    const float mul1 = (proj[0] * mean.x + proj[4] * mean.y + proj[8] * mean.z + proj[12]) * m_w * m_w;
+    const float mul2 = (proj[1] * mean.x + proj[5] * mean.y + proj[9] * mean.z + proj[13]) * m_w * m_w;
+    float3 g;
+    g.x = (proj[0] * m_w - proj[3] * mul1) * a0.x + (proj[1] * m_w - proj[3] * mul2) * a0.y;
+    g.y = (proj[4] * m_w - proj[7] * mul1) * a0.x + (proj[5] * m_w - proj[7] * mul2) * a0.y;
+    g.z = (proj[8] * m_w - proj[11] * mul1) * a0.x + (proj[9] * m_w - proj[11] * mul2) * a0.y;
+    dmean.x += g.x; dmean.y += g.y; dmean.z += g.z;
+  }
+  // ---- depth part (App. A.8c (2)) -----------------------------------------------------------
+  {
+    const float mul3 = view[2] * mean.x + view[6] * mean.y + view[10] * mean.z + view[14];
+    float3 g;
+    g.x = (view[2] - view[3] * mul3) * dL_ddepth;
+    g.y = (view[6] - view[7] * mul3) * dL_ddepth;
+    g.z = (view[10] - view[11] * mul3) * dL_ddepth;
+    dmean.x += g.x; dmean.y += g.y; dmean.z += g.z;
+  }
+  // ---- colour part --------------------------------------------------------------------------
+  if (shs != nullptr) {
+    const float3 g = sh_backward(D, M, mean, make_float3(s_cam[0], s_cam[1], s_cam[2]),
+                                 shs + (size_t)idx * M * 3, clamped[idx], F3{a2.x, a2.y, a2.z},
+                                 dL_dsh + (size_t)idx * M * 3);
+    dmean.x += g.x; dmean.y += g.y; dmean.z += g.z;
+  } else {
+    dL_dcolors[3 * idx + 0] = a2.x;
+    dL_dcolors[3 * idx + 1] = a2.y;
+    dL_dcolors[3 * idx + 2] = a2.z;
+  }
+  dL_dmeans3D[3 * idx + 0] = dmean.x;
+  dL_dmeans3D[3 * idx + 1] = dmean.y;
+  dL_dmeans3D[3 * idx + 2] = dmean.z;
+
+  // ---- covariance parametrisation -------------------------------------------------------------
+  if (cov3D_precomp != nullptr) {
+#pragma unroll
+    for (int k = 0; k < 6; ++k) dL_dcov3D[6 * idx + k] = dcov[k];
+  } else {
+    float3 ds;
+    float4 dq;
+    cov3d_backward(scl, scale_modifier, rot, dcov, ds, dq);
+    dL_dscales[3 * idx + 0] = ds.x;
+    dL_dscales[3 * idx + 1] = ds.y;
+    dL_dscales[3 * idx + 2] = ds.z;
+    reinterpret_cast<float4*>(dL_drot)[idx] = dq;
+  }
+}
+
+int launch_preprocess_backward(const EgsBackwardArgs& a, const GeomPtrs& g,
+                               const BackwardScratch& s, cudaStream_t stream) {
+  const float focal_y = a.height / (2.0f * a.tan_fovy);
+  const float focal_x = a.width / (2.0f * a.tan_fovx);
+  StageTimer timer(stream, ST_PREPROCESS_BWD);
+  preprocess_backward_kernel<<<(a.P + 255) / 256, 256, 0, stream>>>(
+      a.P, a.sh_degree, a.sh_coeffs, a.means3D, a.radii, a.shs, g.clamped, a.scales, a.rotations,
+      a.cov3D_precomp, a.colors_precomp, a.scale_modifier, a.viewmatrix, a.projmatrix, a.campos,
+      focal_x, focal_y, a.tan_fovx, a.tan_fovy, s.acc, a.dL_dmeans2D, a.dL_dcolors, a.dL_dopacity,
+      a.dL_dmeans3D, a.dL_dcov3D, a.dL_dsh, a.dL_dscales, a.dL_drotations);
+  EGS_AFTER_LAUNCH(stream, a.debug);
+  return EGS_OK;
+}
+
+}  // namespace egs

@@ -1,0 +1,311 @@
+// torch_binding.cpp -- thin PyTorch C++ extension over the C-ABI (include/egs_rasterizer.h).
+//
+// Exposes the three functions the reference's Python layer calls, with the same argument order
+// and return tuples, so diff_gaussian_rasterization/__init__.py-style callers work unchanged:
+//   rasterize_gaussians           <- RasterizeGaussiansCUDA          DGR/rasterize_points.cu:35-119
+//   rasterize_gaussians_backward  <- RasterizeGaussiansBackwardCUDA  DGR/rasterize_points.cu:121-208
+//   mark_visible                  <- markVisible                     DGR/rasterize_points.cu:210-229
+// (pybind names as in DGR/ext.cpp:15-18). torch is plumbing only: tensor allocation, the current
+// stream and a device guard. All compute happens behind the C-ABI in libegs_rasterizer.so.
+#include <torch/extension.h>
+#include <ATen/cuda/CUDAContext.h>
+#include <c10/cuda/CUDAGuard.h>
+
+#include <tuple>
+#include <vector>
+
+#include "../../include/egs_rasterizer.h"
+
+namespace {
+
+void check(int rc, const char* what) {
+  TORCH_CHECK(rc == EGS_OK, what, " failed (", rc, "): ", egs_last_error());
+}
+
+// "absent" inputs are empty tensors (the reference passes torch.Tensor([]) on the CPU)
+const float* opt_ptr(const torch::Tensor& t, torch::Tensor& keep, const torch::Device& dev, const char* name) {
+  if (!t.defined() || t.numel() == 0) return nullptr;
+  TORCH_CHECK(t.device() == dev, name, " must be on ", dev);
+  TORCH_CHECK(t.scalar_type() == torch::kFloat32, name, " must be float32");
+  keep = t.contiguous();
+  return keep.data_ptr<float>();
+}
+
+const float* req_ptr(const torch::Tensor& t, torch::Tensor& keep, const torch::Device& dev, const char* name) {
+  TORCH_CHECK(t.defined() && t.numel() > 0, name, " is required");
+  return opt_ptr(t, keep, dev, name);
+}
+
+struct BlobCtx {
+  torch::Tensor blob;
+  torch::Device dev;
+};
+
+void* blob_alloc(void* ctx, size_t bytes) {
+  auto* c = static_cast<BlobCtx*>(ctx);
+  c->blob = torch::empty({(int64_t)bytes}, torch::TensorOptions().dtype(torch::kUInt8).device(c->dev));
+  return c->blob.data_ptr();
+}
+
+std::tuple<int, torch::Tensor, torch::Tensor, torch::Tensor, torch::Tensor, torch::Tensor,
+           torch::Tensor, torch::Tensor>
+rasterize_gaussians(const torch::Tensor& background, const torch::Tensor& means3D,
+                    const torch::Tensor& colors, const torch::Tensor& opacity,
+                    const torch::Tensor& scales, const torch::Tensor& rotations,
+                    const float scale_modifier, const torch::Tensor& cov3D_precomp,
+                    const torch::Tensor& viewmatrix, const torch::Tensor& projmatrix,
+                    const float tan_fovx, const float tan_fovy, const int image_height,
+                    const int image_width, const torch::Tensor& sh, const int degree,
+                    const torch::Tensor& campos, const bool prefiltered, const bool debug) {
+  if (means3D.ndimension() != 2 || means3D.size(1) != 3) {
+    AT_ERROR("means3D must have dimensions (num_points, 3)");
+  }
+  TORCH_CHECK(means3D.is_cuda(), "means3D must be a CUDA tensor (there is no CPU path)");
+  const torch::Device dev = means3D.device();
+  c10::cuda::CUDAGuard guard(dev);
+  const int P = (int)means3D.size(0);
+  const int H = image_height, W = image_width;
+  auto fopt = means3D.options().dtype(torch::kFloat32);
+
+  // every pixel / every Gaussian is written by the kernels, so no zero-fill (the reference
+  // fills all four, rasterize_points.cu:68-71); P == 0 is zeroed inside egs_forward.
+  torch::Tensor out_color = torch::empty({EGS_NUM_CHANNELS, H, W}, fopt);
+  torch::Tensor out_depth = torch::empty({1, H, W}, fopt);
+  torch::Tensor out_alpha = torch::empty({1, H, W}, fopt);
+  torch::Tensor radii = torch::empty({P}, means3D.options().dtype(torch::kInt32));
+
+  BlobCtx geom{torch::empty({0}, torch::TensorOptions().dtype(torch::kUInt8).device(dev)), dev};
+  BlobCtx binning = geom, image = geom;
+
+  torch::Tensor k[12];
+  EgsForwardArgs a{};
+  a.P = P;
+  a.sh_degree = degree;
+  a.sh_coeffs = (sh.defined() && sh.numel() != 0) ? (int)sh.size(1) : 0;
+  a.width = W;
+  a.height = H;
+  a.background = req_ptr(background, k[0], dev, "background");
+  a.means3D = P ? req_ptr(means3D, k[1], dev, "means3D") : nullptr;
+  a.shs = opt_ptr(sh, k[2], dev, "sh");
+  a.colors_precomp = opt_ptr(colors, k[3], dev, "colors_precomp");
+  a.opacities = opt_ptr(opacity, k[4], dev, "opacity");
+  a.scales = opt_ptr(scales, k[5], dev, "scales");
+  a.rotations = opt_ptr(rotations, k[6], dev, "rotations");
+  a.cov3D_precomp = opt_ptr(cov3D_precomp, k[7], dev, "cov3D_precomp");
+  a.scale_modifier = scale_modifier;
+  a.viewmatrix = req_ptr(viewmatrix, k[8], dev, "viewmatrix");
+  a.projmatrix = req_ptr(projmatrix, k[9], dev, "projmatrix");
+  a.campos = req_ptr(campos, k[10], dev, "campos");
+  a.tan_fovx = tan_fovx;
+  a.tan_fovy = tan_fovy;
+  a.prefiltered = prefiltered;
+  a.debug = debug;
+  a.out_color = out_color.data_ptr<float>();
+  a.out_depth = out_depth.data_ptr<float>();
+  a.out_alpha = out_alpha.data_ptr<float>();
+  a.radii = radii.data_ptr<int>();
+  a.geom_alloc = blob_alloc;    a.geom_ctx = &geom;
+  a.binning_alloc = blob_alloc; a.binning_ctx = &binning;
+  a.image_alloc = blob_alloc;   a.image_ctx = &image;
+
+  int rendered = 0;
+  check(egs_forward(&a, at::cuda::getCurrentCUDAStream().stream(), &rendered), "egs_forward");
+  return std::make_tuple(rendered, out_color, out_depth, out_alpha, radii, geom.blob, binning.blob,
+                         image.blob);
+}
+
+std::tuple<torch::Tensor, torch::Tensor, torch::Tensor, torch::Tensor, torch::Tensor, torch::Tensor,
+           torch::Tensor, torch::Tensor>
+rasterize_gaussians_backward(const torch::Tensor& background, const torch::Tensor& means3D,
+                             const torch::Tensor& radii, const torch::Tensor& colors,
+                             const torch::Tensor& scales, const torch::Tensor& rotations,
+                             const float scale_modifier, const torch::Tensor& cov3D_precomp,
+                             const torch::Tensor& viewmatrix, const torch::Tensor& projmatrix,
+                             const float tan_fovx, const float tan_fovy,
+                             const torch::Tensor& dL_dout_color, const torch::Tensor& dL_dout_depth,
+                             const torch::Tensor& dL_dout_alpha, const torch::Tensor& sh,
+                             const int degree, const torch::Tensor& campos,
+                             const torch::Tensor& geomBuffer, const int R,
+                             const torch::Tensor& binningBuffer, const torch::Tensor& imageBuffer,
+                             const torch::Tensor& alphas, const bool debug) {
+  TORCH_CHECK(means3D.is_cuda(), "means3D must be a CUDA tensor (there is no CPU path)");
+  const torch::Device dev = means3D.device();
+  c10::cuda::CUDAGuard guard(dev);
+  const int P = (int)means3D.size(0);
+  const int H = (int)dL_dout_color.size(1);
+  const int W = (int)dL_dout_color.size(2);
+  const int M = (sh.defined() && sh.numel() != 0) ? (int)sh.size(1) : 0;
+  auto fopt = means3D.options().dtype(torch::kFloat32);
+
+  const bool has_sh = M != 0;
+  const bool has_colors = colors.defined() && colors.numel() != 0;
+  const bool has_cov = cov3D_precomp.defined() && cov3D_precomp.numel() != 0;
+  const bool has_sr = scales.defined() && scales.numel() != 0;
+
+  // outputs are fully written by the kernels: empty, not zeros (the reference zero-fills ten
+  // tensors, rasterize_points.cu:158-167). Gradients of absent inputs are zero-size tensors.
+  torch::Tensor dL_dmeans3D = torch::empty({P, 3}, fopt);
+  torch::Tensor dL_dmeans2D = torch::empty({P, 3}, fopt);
+  torch::Tensor dL_dopacity = torch::empty({P, 1}, fopt);
+  torch::Tensor dL_dcolors = torch::empty({has_colors ? P : 0, EGS_NUM_CHANNELS}, fopt);
+  torch::Tensor dL_dcov3D = torch::empty({has_cov ? P : 0, 6}, fopt);
+  torch::Tensor dL_dsh = torch::empty({has_sh ? P : 0, M, 3}, fopt);
+  torch::Tensor dL_dscales = torch::empty({has_sr ? P : 0, 3}, fopt);
+  torch::Tensor dL_drotations = torch::empty({has_sr ? P : 0, 4}, fopt);
+
+  if (P != 0) {
+    torch::Tensor scratch = torch::empty({(int64_t)egs_backward_scratch_bytes(P)},
+                                         torch::TensorOptions().dtype(torch::kUInt8).device(dev));
+    torch::Tensor k[16];
+    EgsBackwardArgs a{};
+    a.P = P;
+    a.sh_degree = degree;
+    a.sh_coeffs = M;
+    a.num_rendered = R;
+    a.width = W;
+    a.height = H;
+    a.background = req_ptr(background, k[0], dev, "background");
+    a.means3D = req_ptr(means3D, k[1], dev, "means3D");
+    a.shs = opt_ptr(sh, k[2], dev, "sh");
+    a.colors_precomp = opt_ptr(colors, k[3], dev, "colors_precomp");
+    a.scales = opt_ptr(scales, k[4], dev, "scales");
+    a.rotations = opt_ptr(rotations, k[5], dev, "rotations");
+    a.cov3D_precomp = opt_ptr(cov3D_precomp, k[6], dev, "cov3D_precomp");
+    a.scale_modifier = scale_modifier;
+    a.viewmatrix = req_ptr(viewmatrix, k[7], dev, "viewmatrix");
+    a.projmatrix = req_ptr(projmatrix, k[8], dev, "projmatrix");
+    a.campos = req_ptr(campos, k[9], dev, "campos");
+    a.tan_fovx = tan_fovx;
+    a.tan_fovy = tan_fovy;
+    TORCH_CHECK(radii.scalar_type() == torch::kInt32 && radii.device() == dev, "radii must be int32 on ", dev);
+    k[10] = radii.contiguous();
+    a.radii = k[10].data_ptr<int>();
+    a.out_alpha = req_ptr(alphas, k[11], dev, "alphas");
+    TORCH_CHECK(geomBuffer.device() == dev && imageBuffer.device() == dev, "workspace blobs on wrong device");
+    a.geom_buffer = geomBuffer.data_ptr();
+    a.binning_buffer = binningBuffer.numel() ? binningBuffer.data_ptr() : nullptr;
+    a.image_buffer = imageBuffer.data_ptr();
+    a.dL_dout_color = req_ptr(dL_dout_color, k[12], dev, "dL_dout_color");
+    a.dL_dout_depth = req_ptr(dL_dout_depth, k[13], dev, "dL_dout_depth");
+    a.dL_dout_alpha = req_ptr(dL_dout_alpha, k[14], dev, "dL_dout_alpha");
+    a.scratch = scratch.data_ptr();
+    a.dL_dmeans2D = dL_dmeans2D.data_ptr<float>();
+    a.dL_dcolors = has_colors ? dL_dcolors.data_ptr<float>() : nullptr;
+    a.dL_dopacity = dL_dopacity.data_ptr<float>();
+    a.dL_dmeans3D = dL_dmeans3D.data_ptr<float>();
+    a.dL_dcov3D = has_cov ? dL_dcov3D.data_ptr<float>() : nullptr;
+    a.dL_dsh = has_sh ? dL_dsh.data_ptr<float>() : nullptr;
+    a.dL_dscales = has_sr ? dL_dscales.data_ptr<float>() : nullptr;
+    a.dL_drotations = has_sr ? dL_drotations.data_ptr<float>() : nullptr;
+    a.debug = debug;
+    check(egs_backward(&a, at::cuda::getCurrentCUDAStream().stream()), "egs_backward");
+  }
+  return std::make_tuple(dL_dmeans2D, dL_dcolors, dL_dopacity, dL_dmeans3D, dL_dcov3D, dL_dsh,
+                         dL_dscales, dL_drotations);
+}
+
+torch::Tensor mark_visible(torch::Tensor& means3D, torch::Tensor& viewmatrix, torch::Tensor& projmatrix) {
+  TORCH_CHECK(means3D.is_cuda(), "means3D must be a CUDA tensor (there is no CPU path)");
+  const torch::Device dev = means3D.device();
+  c10::cuda::CUDAGuard guard(dev);
+  const int P = (int)means3D.size(0);
+  torch::Tensor present = torch::empty({P}, means3D.options().dtype(at::kBool));
+  if (P != 0) {
+    torch::Tensor k[3];
+    check(egs_mark_visible(P, req_ptr(means3D, k[0], dev, "means3D"),
+                           req_ptr(viewmatrix, k[1], dev, "viewmatrix"),
+                           req_ptr(projmatrix, k[2], dev, "projmatrix"),
+                           reinterpret_cast<unsigned char*>(present.data_ptr<bool>()),
+                           at::cuda::getCurrentCUDAStream().stream()),
+          "egs_mark_visible");
+  }
+  return present;
+}
+
+// ---- optimizer step -------------------------------------------------------------------------
+void adam_step(std::vector<torch::Tensor> params, std::vector<torch::Tensor> grads,
+               std::vector<torch::Tensor> exp_avgs, std::vector<torch::Tensor> exp_avg_sqs,
+               std::vector<double> lrs, std::vector<int64_t> steps, double beta1, double beta2, double eps) {
+  const size_t n = params.size();
+  TORCH_CHECK(n <= EGS_ADAM_MAX_GROUPS, "at most ", EGS_ADAM_MAX_GROUPS, " groups per call");
+  TORCH_CHECK(grads.size() == n && exp_avgs.size() == n && exp_avg_sqs.size() == n && lrs.size() == n && steps.size() == n,
+              "adam_step: list lengths differ");
+  if (n == 0) return;
+  c10::cuda::CUDAGuard guard(params[0].device());
+  EgsAdamGroup g[EGS_ADAM_MAX_GROUPS];
+  for (size_t i = 0; i < n; ++i) {
+    for (const torch::Tensor* t : {&params[i], &grads[i], &exp_avgs[i], &exp_avg_sqs[i]}) {
+      TORCH_CHECK(t->is_cuda() && t->scalar_type() == torch::kFloat32 && t->is_contiguous(),
+                  "adam_step: tensors must be contiguous float32 CUDA");
+      TORCH_CHECK(t->numel() == params[i].numel(), "adam_step: size mismatch in group ", i);
+    }
+    g[i].param = params[i].data_ptr<float>();
+    g[i].grad = grads[i].data_ptr<float>();
+    g[i].exp_avg = exp_avgs[i].data_ptr<float>();
+    g[i].exp_avg_sq = exp_avg_sqs[i].data_ptr<float>();
+    g[i].n = params[i].numel();
+    g[i].lr = (float)lrs[i];
+    g[i].step = (int)steps[i];
+  }
+  check(egs_adam_step(g, (int)n, (float)beta1, (float)beta2, (float)eps,
+                      at::cuda::getCurrentCUDAStream().stream()),
+        "egs_adam_step");
+}
+
+std::tuple<torch::Tensor, torch::Tensor> se3_apply(const torch::Tensor& xyz, const torch::Tensor& is_object,
+                                                   int which, const torch::Tensor& Rt,
+                                                   const torch::Tensor& cov) {
+  TORCH_CHECK(xyz.is_cuda() && xyz.scalar_type() == torch::kFloat32, "xyz must be float32 CUDA");
+  TORCH_CHECK(is_object.scalar_type() == torch::kInt32 && is_object.is_cuda(), "is_object must be int32 CUDA");
+  TORCH_CHECK(Rt.numel() == 12 && Rt.is_cuda() && Rt.scalar_type() == torch::kFloat32, "Rt must be 12 float32 CUDA");
+  c10::cuda::CUDAGuard guard(xyz.device());
+  auto x = xyz.contiguous();
+  auto io = is_object.contiguous();
+  auto rt = Rt.contiguous();
+  const int P = (int)x.size(0);
+  torch::Tensor out = torch::empty_like(x);
+  torch::Tensor cov_c, cov_out;
+  const bool has_cov = cov.defined() && cov.numel() != 0;
+  if (has_cov) {
+    cov_c = cov.contiguous();
+    cov_out = torch::empty_like(cov_c);
+  } else {
+    cov_out = torch::empty({0}, x.options());
+  }
+  check(egs_se3_apply(P, x.data_ptr<float>(), io.data_ptr<int>(), which, rt.data_ptr<float>(),
+                      out.data_ptr<float>(), has_cov ? cov_c.data_ptr<float>() : nullptr,
+                      has_cov ? cov_out.data_ptr<float>() : nullptr,
+                      at::cuda::getCurrentCUDAStream().stream()),
+        "egs_se3_apply");
+  return std::make_tuple(out, cov_out);
+}
+
+void adam_se3_step(torch::Tensor xyz, const torch::Tensor& grad, torch::Tensor exp_avg,
+                   torch::Tensor exp_avg_sq, const torch::Tensor& is_object, int which,
+                   const torch::Tensor& Rt, double lr, int64_t step, double beta1, double beta2, double eps) {
+  for (const torch::Tensor* t : {(const torch::Tensor*)&xyz, &grad, (const torch::Tensor*)&exp_avg, (const torch::Tensor*)&exp_avg_sq})
+    TORCH_CHECK(t->is_cuda() && t->scalar_type() == torch::kFloat32 && t->is_contiguous(),
+                "adam_se3_step: tensors must be contiguous float32 CUDA");
+  TORCH_CHECK(is_object.scalar_type() == torch::kInt32 && is_object.is_cuda() && is_object.is_contiguous(),
+              "is_object must be contiguous int32 CUDA");
+  c10::cuda::CUDAGuard guard(xyz.device());
+  auto rt = Rt.contiguous();
+  check(egs_adam_se3_step((int)xyz.size(0), xyz.data_ptr<float>(), grad.data_ptr<float>(),
+                          exp_avg.data_ptr<float>(), exp_avg_sq.data_ptr<float>(), is_object.data_ptr<int>(),
+                          which, rt.data_ptr<float>(), (float)lr, (int)step, (float)beta1, (float)beta2,
+                          (float)eps, at::cuda::getCurrentCUDAStream().stream()),
+        "egs_adam_se3_step");
+}
+
+}  // namespace
+
+PYBIND11_MODULE(TORCH_EXTENSION_NAME, m) {
+  m.def("rasterize_gaussians", &rasterize_gaussians);
+  m.def("rasterize_gaussians_backward", &rasterize_gaussians_backward);
+  m.def("mark_visible", &mark_visible);
+  m.def("adam_step", &adam_step);
+  m.def("se3_apply", &se3_apply);
+  m.def("adam_se3_step", &adam_se3_step);
+  m.def("launch_count", []() { return egs_launch_count(); });
+  m.def("abi_version", []() { return egs_abi_version(); });
+}

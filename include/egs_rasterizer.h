@@ -1,0 +1,224 @@
+/*
+ * egs_rasterizer.h -- C-ABI of the B200-native differentiable Gaussian-splatting rasterizer.
+ *
+ * This is the drop-in boundary for the hot path named by BASELINE.json `north_star`:
+ * the functions below replace, one for one, the inner C++ API of the reference submodule
+ * `submodules/diff-gaussian-rasterization` (abbreviated DGR below):
+ *
+ *   egs_forward        <- CudaRasterizer::Rasterizer::forward      DGR/cuda_rasterizer/rasterizer.h:31-55
+ *                         (impl DGR/cuda_rasterizer/rasterizer_impl.cu:197-339)
+ *   egs_backward       <- CudaRasterizer::Rasterizer::backward     rasterizer.h:57-89 (impl :343-447)
+ *   egs_mark_visible   <- CudaRasterizer::Rasterizer::markVisible  rasterizer.h:24-29 (impl :141-153)
+ *   egs_adam_step      <- torch.optim.Adam.step as configured in scene/gaussian_model.py:180-202
+ *   egs_se3_apply      <- GaussianModel.apply_trans_rot_new        scene/gaussian_model.py:939-986
+ *   egs_adam_se3_step  <- reverse_trans_rot_new + Adam.step        scene/gaussian_model.py:1037-1060
+ *
+ * Conventions
+ *   - plain C, no torch types, no exceptions; every pointer named `d_*` or documented as
+ *     "device" is a CUDA device pointer on the current device; `stream` is a cudaStream_t
+ *     passed as void* (NULL = legacy default stream).
+ *   - all floating point is fp32, contiguous row-major, exactly the reference layouts:
+ *     viewmatrix/projmatrix are the transposed (row-vector) 4x4 matrices, sh is [P,M,3],
+ *     cov3D is [xx,xy,xz,yy,yz,zz], quaternions are (w,x,y,z) and are NOT normalised.
+ *   - an absent optional input is a NULL pointer (the reference's empty tensor).
+ *   - return value: EGS_OK (0) or a negative EgsStatus; egs_last_error() returns a
+ *     thread-local human-readable message for the last failure.
+ *   - there is NO CPU fallback: if no CUDA device is usable the calls fail with
+ *     EGS_ERR_CUDA.
+ */
+#ifndef EGS_RASTERIZER_H_
+#define EGS_RASTERIZER_H_
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define EGS_ABI_VERSION 1
+#define EGS_TILE_X 16          /* DGR/cuda_rasterizer/config.h:16 */
+#define EGS_TILE_Y 16          /* DGR/cuda_rasterizer/config.h:17 */
+#define EGS_NUM_CHANNELS 3     /* DGR/cuda_rasterizer/config.h:15 */
+
+typedef enum EgsStatus {
+  EGS_OK = 0,
+  EGS_ERR_INVALID_ARGUMENT = -1, /* bad shape / both-or-neither of an exclusive input pair */
+  EGS_ERR_CUDA = -2,             /* a CUDA runtime call or kernel launch failed */
+  EGS_ERR_ALLOC = -3,            /* a workspace callback returned NULL */
+  EGS_ERR_TOO_LARGE = -4,        /* num_rendered or P beyond the supported range */
+  EGS_ERR_PREFILTERED = -5       /* debug only: a prefiltered point was culled (auxiliary.h:154-161) */
+} EgsStatus;
+
+/* Workspace callback: must return a device pointer to at least `bytes` bytes, 256-byte
+ * aligned, that stays valid until the matching egs_backward has run. Replaces the three
+ * std::function<char*(size_t)> resizers of rasterize_points.cu:27-33. */
+typedef void* (*EgsAllocFn)(void* ctx, size_t bytes);
+
+typedef struct EgsForwardArgs {
+  int P;                /* number of Gaussians */
+  int sh_degree;        /* active degree D, 0..3 */
+  int sh_coeffs;        /* M = coefficients per channel present in `shs` (0 when shs == NULL) */
+  int width, height;
+  const float* background;     /* device [3] */
+  const float* means3D;        /* device [P,3] */
+  const float* shs;            /* device [P,M,3] or NULL */
+  const float* colors_precomp; /* device [P,3]   or NULL (exactly one of shs / colors_precomp) */
+  const float* opacities;      /* device [P] */
+  const float* scales;         /* device [P,3] or NULL */
+  const float* rotations;      /* device [P,4] or NULL */
+  const float* cov3D_precomp;  /* device [P,6] or NULL (exactly one of scales+rotations / cov3D) */
+  float scale_modifier;
+  const float* viewmatrix;     /* device [16] */
+  const float* projmatrix;     /* device [16] */
+  const float* campos;         /* device [3] */
+  float tan_fovx, tan_fovy;
+  int prefiltered;
+  int debug;                   /* non-zero: synchronise and check after every stage */
+  /* outputs (device, caller-allocated, need not be zeroed) */
+  float* out_color;            /* [3,H,W] */
+  float* out_depth;            /* [1,H,W]  un-normalised sum depth*alpha*T (forward.cu:360) */
+  float* out_alpha;            /* [1,H,W]  sum alpha*T                     (forward.cu:361) */
+  int* radii;                  /* [P] */
+  /* workspaces: three opaque blobs that must be handed unchanged to egs_backward */
+  EgsAllocFn geom_alloc;   void* geom_ctx;    /* size = egs_geom_bytes(P) */
+  EgsAllocFn binning_alloc; void* binning_ctx; /* size = egs_binning_bytes(num_rendered) */
+  EgsAllocFn image_alloc;  void* image_ctx;   /* size = egs_image_bytes(width,height) */
+} EgsForwardArgs;
+
+/* Sizes of the three workspaces; pure functions of their arguments so that backward can
+ * re-derive the internal layout (rasterizer_impl.h:67-73 `required<T>`). */
+size_t egs_geom_bytes(int P);
+size_t egs_binning_bytes(int num_rendered, int width, int height);
+size_t egs_image_bytes(int width, int height);
+
+/* Forward render. On success *num_rendered is the number of (Gaussian, tile) instances.
+ * Performs exactly one device->host read (num_rendered), like rasterizer_impl.cu:281-282. */
+int egs_forward(const EgsForwardArgs* args, void* stream, int* num_rendered);
+
+typedef struct EgsBackwardArgs {
+  int P, sh_degree, sh_coeffs, num_rendered;
+  int width, height;
+  const float* background;
+  const float* means3D;
+  const float* shs;
+  const float* colors_precomp;
+  const float* scales;
+  const float* rotations;
+  const float* cov3D_precomp;
+  float scale_modifier;
+  const float* viewmatrix;
+  const float* projmatrix;
+  const float* campos;
+  float tan_fovx, tan_fovy;
+  const int* radii;            /* [P] from forward */
+  const float* out_alpha;      /* [1,H,W] from forward (T_final = 1 - alpha, backward.cu:463) */
+  const void* geom_buffer;     /* the three blobs filled by egs_forward */
+  const void* binning_buffer;
+  const void* image_buffer;
+  const float* dL_dout_color;  /* [3,H,W] */
+  const float* dL_dout_depth;  /* [1,H,W] */
+  const float* dL_dout_alpha;  /* [1,H,W] */
+  /* scratch: egs_backward_scratch_bytes(P) bytes, device, 256-byte aligned; contents are
+   * overwritten (zeroed by the call, then used as atomic accumulators). */
+  void* scratch;
+  /* outputs (device, caller-allocated, need not be zeroed; every element is written) */
+  float* dL_dmeans2D;          /* [P,3]  z component is always 0 */
+  float* dL_dcolors;           /* [P,3]  written only when colors_precomp != NULL, else may be NULL */
+  float* dL_dopacity;          /* [P] */
+  float* dL_dmeans3D;          /* [P,3] */
+  float* dL_dcov3D;            /* [P,6]  written only when cov3D_precomp != NULL, else may be NULL */
+  float* dL_dsh;               /* [P,M,3] written only when shs != NULL, else may be NULL */
+  float* dL_dscales;           /* [P,3]  written only when scales != NULL, else may be NULL */
+  float* dL_drotations;        /* [P,4]  written only when rotations != NULL, else may be NULL */
+  int debug;
+} EgsBackwardArgs;
+
+size_t egs_backward_scratch_bytes(int P);
+
+int egs_backward(const EgsBackwardArgs* args, void* stream);
+
+/* present[i] = (view-space z of means3D[i] > 0.2), 1 byte per Gaussian (rasterizer_impl.cu:54-66). */
+int egs_mark_visible(int P, const float* means3D, const float* viewmatrix,
+                     const float* projmatrix, unsigned char* present, void* stream);
+
+/* ---- optimizer step (north_star item 5) ------------------------------------------------ */
+
+/* One Adam parameter group: param/grad/exp_avg/exp_avg_sq are device [n] fp32. Follows
+ * torch.optim.Adam(lr, betas, eps) with bias correction, no weight decay, no amsgrad, as
+ * configured at scene/gaussian_model.py:198 (eps = 1e-15). `step` is the 1-based step count
+ * AFTER this update (torch increments before use). */
+typedef struct EgsAdamGroup {
+  float* param;
+  const float* grad;
+  float* exp_avg;
+  float* exp_avg_sq;
+  long long n;
+  float lr;
+  int step;
+} EgsAdamGroup;
+
+/* Fused multi-group Adam: one launch for all groups (host array of up to EGS_ADAM_MAX_GROUPS). */
+#define EGS_ADAM_MAX_GROUPS 16
+int egs_adam_step(const EgsAdamGroup* groups, int n_groups, float beta1, float beta2, float eps,
+                  void* stream);
+
+/* Rigid SE(3) transform of object Gaussians (scene/gaussian_model.py:939-986,
+ * utils/geometry_utils.py:188-193): for rows with is_object[i] == which_object,
+ * out[i] = R * xyz[i] + t, else out[i] = xyz[i]. `Rt` is device [12]: row-major R (9) then t (3).
+ * When cov_in != NULL, also rotates the packed covariance: cov_out = R * cov * R^T. */
+int egs_se3_apply(int P, const float* xyz, const int* is_object, int which_object,
+                  const float* Rt, float* xyz_out, const float* cov_in, float* cov_out,
+                  void* stream);
+
+/* Fused "pull gradient back through the rigid map + Adam on canonical xyz" (SURVEY.md 8a A-24):
+ * g_canonical = R^T * g_moved for object rows, then the Adam update of egs_adam_step. */
+int egs_adam_se3_step(int P, float* xyz, const float* grad_moved, float* exp_avg, float* exp_avg_sq,
+                      const int* is_object, int which_object, const float* Rt, float lr, int step,
+                      float beta1, float beta2, float eps, void* stream);
+
+/* ---- introspection (tests / bench) ----------------------------------------------------- */
+
+/* Views into the opaque blobs, for parity tests against the reference's intermediates
+ * (SURVEY.md App. B). Pointers alias the blobs; nothing is copied. */
+typedef struct EgsGeomView {
+  const float* depths;         /* [P] */
+  const float* means2D;        /* [P,2] */
+  const float* conic_opacity;  /* [P,4] */
+  const float* rgb_depth;      /* [P,4] rgb + depth packed for the blend kernels */
+  const unsigned char* clamped;/* [P] bit c set = channel c clamped */
+  const uint32_t* tiles_touched; /* [P] */
+  const uint32_t* point_offsets; /* [P] inclusive scan */
+} EgsGeomView;
+typedef struct EgsBinningView {
+  const uint64_t* keys_sorted;   /* [R] */
+  const uint32_t* values_sorted; /* [R] */
+} EgsBinningView;
+typedef struct EgsImageView {
+  const uint32_t* n_contrib;     /* [H*W] */
+  const uint32_t* ranges;        /* [tiles,2] */
+} EgsImageView;
+int egs_geom_view(const void* geom_buffer, int P, EgsGeomView* out);
+int egs_binning_view(const void* binning_buffer, int num_rendered, int width, int height,
+                     EgsBinningView* out);
+int egs_image_view(const void* image_buffer, int width, int height, EgsImageView* out);
+
+/* Built-in stage timing (the reference has no profiling hooks). While
+ * enabled, every stage of egs_forward / egs_backward / egs_adam_step is bracketed by CUDA events
+ * on the caller's stream. egs_profile_read waits for the recorded events, adds each stage's
+ * elapsed milliseconds and launch count into ms[] / count[] (arrays of EGS_PROFILE_STAGES), and
+ * forgets them. Stage i is named egs_profile_stage_name(i). */
+#define EGS_PROFILE_STAGES 16
+int egs_profile_enable(int on);
+int egs_profile_read(double* ms, unsigned long long* count);
+const char* egs_profile_stage_name(int stage);
+
+/* Number of kernel launches issued by this library in this process since load (bench `gpu_launches`). */
+unsigned long long egs_launch_count(void);
+const char* egs_last_error(void);
+int egs_abi_version(void);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* EGS_RASTERIZER_H_ */

@@ -1,0 +1,125 @@
+"""Thin caller of the UNMODIFIED reference rasterizer built by oracle/build_ref.py.
+
+TEST INFRASTRUCTURE ONLY (parity checker, golden-vector generator and the `--impl reference`
+bench arm). Needs a GPU: the reference has no CPU path.
+
+`forward` / `backward` pass arguments in the order the reference's own Python layer does
+(DGR/diff_gaussian_rasterization/__init__.py:63-92, 111-144) and additionally decode the
+reference's three opaque byte buffers into named arrays using the `fromChunk` layouts
+(DGR/cuda_rasterizer/rasterizer_impl.cu:155-193): every array starts at the
+next 128-byte boundary, so all arrays that precede the CUB temporary storage can be located
+from (P, R, N) alone.
+"""
+from __future__ import annotations
+
+import importlib.util
+import sys
+from pathlib import Path
+from typing import Dict
+
+HERE = Path(__file__).resolve().parent
+SO = HERE / "_ref" / "ref_dgr_C.so"
+_mod = None
+
+
+def available() -> bool:
+    return SO.exists()
+
+
+def load():
+    global _mod
+    if _mod is None:
+        import torch  # noqa: F401  (libtorch must be loaded before the extension)
+        if not SO.exists():
+            raise ImportError(f"{SO} missing: run `python oracle/build_ref.py` where /root/reference is mounted")
+        spec = importlib.util.spec_from_file_location("ref_dgr_C", str(SO))
+        _mod = importlib.util.module_from_spec(spec)
+        sys.modules["ref_dgr_C"] = _mod
+        spec.loader.exec_module(_mod)
+    return _mod
+
+
+def _absent():
+    import torch
+    return torch.Tensor([])
+
+
+def _al(x: int, a: int = 128) -> int:
+    return (x + a - 1) // a * a
+
+
+def forward(*, means3D, opacities, bg, viewmatrix, projmatrix, campos, tanfovx, tanfovy, image_height,
+            image_width, sh_degree=0, shs=None, colors_precomp=None, scales=None, rotations=None,
+            cov3D_precomp=None, scale_modifier=1.0, prefiltered=False, debug=False) -> Dict:
+    import torch
+    C = load()
+    e = _absent()
+    args = (bg, means3D, e if colors_precomp is None else colors_precomp, opacities,
+            e if scales is None else scales, e if rotations is None else rotations, float(scale_modifier),
+            e if cov3D_precomp is None else cov3D_precomp, viewmatrix, projmatrix, float(tanfovx), float(tanfovy),
+            int(image_height), int(image_width), e if shs is None else shs, int(sh_degree), campos,
+            bool(prefiltered), bool(debug))
+    R, color, depth, alpha, radii, geom, binning, img = C.rasterize_gaussians(*args)
+    return {"num_rendered": int(R), "color": color, "depth": depth, "alpha": alpha, "radii": radii,
+            "geomBuffer": geom, "binningBuffer": binning, "imgBuffer": img,
+            "P": int(means3D.shape[0]), "H": int(image_height), "W": int(image_width)}
+
+
+def backward(fwd: Dict, *, means3D, bg, viewmatrix, projmatrix, campos, tanfovx, tanfovy, dL_dcolor,
+             dL_ddepth, dL_dalpha, sh_degree=0, shs=None, colors_precomp=None, scales=None, rotations=None,
+             cov3D_precomp=None, scale_modifier=1.0, debug=False, **_ignored) -> Dict:
+    C = load()
+    e = _absent()
+    args = (bg, means3D, fwd["radii"], e if colors_precomp is None else colors_precomp,
+            e if scales is None else scales, e if rotations is None else rotations, float(scale_modifier),
+            e if cov3D_precomp is None else cov3D_precomp, viewmatrix, projmatrix, float(tanfovx), float(tanfovy),
+            dL_dcolor, dL_ddepth, dL_dalpha, e if shs is None else shs, int(sh_degree), campos,
+            fwd["geomBuffer"], fwd["num_rendered"], fwd["binningBuffer"], fwd["imgBuffer"], fwd["alpha"], bool(debug))
+    g2d, gcol, gop, g3d, gcov, gsh, gsc, grot = C.rasterize_gaussians_backward(*args)
+    return {"means2D": g2d, "colors": gcol if colors_precomp is not None else None, "opacity": gop,
+            "means3D": g3d, "cov3D": gcov if cov3D_precomp is not None else None,
+            "sh": gsh if shs is not None else None, "scales": gsc if scales is not None else None,
+            "rotations": grot if rotations is not None else None}
+
+
+def mark_visible(means3D, viewmatrix, projmatrix):
+    return load().mark_visible(means3D, viewmatrix, projmatrix)
+
+
+def decode_buffers(fwd: Dict) -> Dict:
+    """Named views of the reference's intermediates (device tensors; copies, not aliases)."""
+    import torch
+    P, R, N = fwd["P"], fwd["num_rendered"], fwd["H"] * fwd["W"]
+    out = {}
+    g = fwd["geomBuffer"]
+    base = g.data_ptr()
+    off = _al(base) - base
+
+    def take(buf, off, nbytes, dtype, shape):
+        t = buf[off:off + nbytes].clone().view(dtype).reshape(shape)
+        return t, _al(buf.data_ptr() + off + nbytes) - buf.data_ptr()
+
+    out["depths"], off = take(g, off, 4 * P, torch.float32, (P,))
+    out["clamped"], off = take(g, off, 3 * P, torch.uint8, (P, 3))
+    _, off = take(g, off, 4 * P, torch.int32, (P,))                       # internal_radii (unused)
+    out["means2D"], off = take(g, off, 8 * P, torch.float32, (P, 2))
+    out["cov3D"], off = take(g, off, 24 * P, torch.float32, (P, 6))
+    out["conic_opacity"], off = take(g, off, 16 * P, torch.float32, (P, 4))
+    out["rgb"], off = take(g, off, 12 * P, torch.float32, (P, 3))
+    out["tiles_touched"], off = take(g, off, 4 * P, torch.int32, (P,))
+    if R > 0:
+        b = fwd["binningBuffer"]
+        off = _al(b.data_ptr()) - b.data_ptr()
+        out["values"], off = take(b, off, 4 * R, torch.int32, (R,))
+        _, off = take(b, off, 4 * R, torch.int32, (R,))                   # unsorted values
+        out["keys"], off = take(b, off, 8 * R, torch.int64, (R,))
+    else:
+        out["values"] = torch.empty(0, dtype=torch.int32, device=g.device)
+        out["keys"] = torch.empty(0, dtype=torch.int64, device=g.device)
+    im = fwd["imgBuffer"]
+    off = _al(im.data_ptr()) - im.data_ptr()
+    out["n_contrib"], off = take(im, off, 4 * N, torch.int32, (fwd["H"], fwd["W"]))
+    tiles = ((fwd["W"] + 15) // 16) * ((fwd["H"] + 15) // 16)
+    ranges, off = take(im, off, 8 * N, torch.int32, (N, 2))
+    out["ranges"] = ranges[:tiles].clone()
+    return out

@@ -1,0 +1,55 @@
+"""Shared helpers for the parity tests: run the CUDA path through the C-ABI, compare results."""
+from __future__ import annotations
+
+import sys
+from pathlib import Path
+from typing import Dict, Optional
+
+import numpy as np
+
+ROOT = Path(__file__).resolve().parents[1]
+if str(ROOT) not in sys.path:
+    sys.path.insert(0, str(ROOT))
+
+# tolerances stated by BASELINE.json `north_star`
+IMAGE_ATOL = 1e-5       # colour / depth / alpha, absolute, fp32
+GRAD_RTOL = 1e-4        # parameter gradients, relative to the tensor's max magnitude
+
+
+def to_np(x):
+    if x is None:
+        return None
+    if hasattr(x, "detach"):
+        return x.detach().cpu().numpy()
+    return np.asarray(x)
+
+
+def run_cuda(kw: Dict, ups: Optional[Dict] = None, debug: bool = False):
+    """Forward (+ backward) of our CUDA path through the C-ABI (egogaussian_b200.cabi)."""
+    from egogaussian_b200 import cabi
+    fwd = cabi.forward(debug=debug, **kw)
+    grads = None
+    if ups is not None:
+        bkw = {k: v for k, v in kw.items() if k not in ("opacities", "image_height", "image_width")}
+        grads = cabi.backward(fwd, debug=debug, dL_dcolor=ups["dL_dcolor"], dL_ddepth=ups["dL_ddepth"],
+                              dL_dalpha=ups["dL_dalpha"], **bkw)
+    return fwd, grads
+
+
+def grad_rel_err(a, b) -> float:
+    """max |a-b| / max |b|  (per-tensor, L-inf normalised: SURVEY.md 8c pass criteria)."""
+    a, b = to_np(a).astype(np.float64), to_np(b).astype(np.float64)
+    scale = np.abs(b).max()
+    if scale == 0:
+        return float(np.abs(a).max())
+    return float(np.abs(a - b).max() / scale)
+
+
+def keys_from(tile_ranges: np.ndarray, values: np.ndarray, depths: np.ndarray) -> np.ndarray:
+    """Rebuild the 64-bit sort keys (tile << 32 | depth bits) from ranges, values and depths."""
+    keys = np.zeros(values.shape[0], np.uint64)
+    dbits = depths.astype(np.float32).view(np.uint32).astype(np.uint64)
+    for t, (a, b) in enumerate(tile_ranges):
+        if b > a:
+            keys[a:b] = (np.uint64(t) << np.uint64(32)) | dbits[values[a:b]]
+    return keys

@@ -1,0 +1,312 @@
+"""GPU parity tests: the CUDA path, called through the C-ABI, against
+  (a) golden vectors produced by the unmodified reference on a B200 (tests/golden/*.npz),
+  (b) the live reference when oracle/_ref/ref_dgr_C.so travelled with the snapshot,
+  (c) the CPU oracle on the same seeded inputs,
+and size-independent properties at BASELINE.json's full sizes.
+
+Bars (BASELINE.json north_star): radii, tile ranges, sorted keys and values bit-exact; colour,
+depth, alpha within 1e-5 absolute; gradients within 1e-4 of the tensor's max magnitude.
+"""
+from pathlib import Path
+
+import numpy as np
+import pytest
+import torch
+
+from helpers import GRAD_RTOL, IMAGE_ATOL, grad_rel_err, run_cuda, to_np
+from golden.make_golden import CASES, case_inputs
+
+pytestmark = pytest.mark.gpu
+GOLDEN = Path(__file__).resolve().parent / "golden"
+
+
+def _assert_images(ours, ref, atol=IMAGE_ATOL, what=""):
+    for k in ("color", "depth", "alpha"):
+        a, b = to_np(getattr(ours, k)), to_np(ref[k])
+        assert a.shape == b.shape
+        err = np.abs(a - b).max()
+        assert err <= atol, f"{what}{k}: max abs err {err}"
+
+
+def _assert_grads(ours, ref, rtol=GRAD_RTOL, what=""):
+    checked = 0
+    for k in ("means2D", "means3D", "opacity", "colors", "cov3D", "sh", "scales", "rotations"):
+        r = ref.get(k) if isinstance(ref, dict) else None
+        if r is None:
+            continue
+        o = ours[k]
+        assert o is not None, f"{what}gradient {k} missing"
+        e = grad_rel_err(to_np(o).reshape(to_np(r).shape), r)
+        assert e <= rtol, f"{what}grad {k}: rel err {e}"
+        checked += 1
+    assert checked >= 4
+
+
+@pytest.mark.parametrize("case", CASES, ids=[c[0] for c in CASES])
+def test_against_golden_reference_vectors(case, built, cuda_device):
+    path = GOLDEN / f"{case[0]}.npz"
+    if not path.exists():
+        pytest.skip("golden vectors not generated yet")
+    gold = np.load(path)
+    kw, ups = case_inputs(case, cuda_device)
+    fwd, grads = run_cuda(kw, ups)
+    torch.cuda.synchronize()
+    assert fwd.num_rendered == int(gold["num_rendered"])
+    assert np.array_equal(to_np(fwd.radii), gold["radii"]), "radii must be bit-exact"
+    bv, iv, gv = fwd.binning_view(), fwd.image_view(), fwd.geom_view()
+    assert np.array_equal(to_np(bv["keys"]), gold["i_keys"]), "sorted keys must be bit-exact"
+    assert np.array_equal(to_np(bv["values"]), gold["i_values"]), "sorted values must be bit-exact"
+    assert np.array_equal(to_np(iv["ranges"]), gold["i_ranges"]), "tile ranges must be bit-exact"
+    vis = gold["radii"] > 0
+    assert np.array_equal(to_np(gv["tiles_touched"]), gold["i_tiles_touched"])
+    assert np.array_equal(to_np(gv["means2D"])[vis].view(np.uint32), gold["i_means2D"][vis].view(np.uint32))
+    assert np.array_equal(to_np(gv["depths"])[vis].view(np.uint32), gold["i_depths"][vis].view(np.uint32))
+    assert np.abs(to_np(gv["conic_opacity"])[vis] - gold["i_conic_opacity"][vis]).max() <= 1e-6 * np.abs(gold["i_conic_opacity"][vis]).max()
+    _assert_images(fwd, gold, what="golden ")
+    assert np.array_equal(to_np(iv["n_contrib"]), gold["i_n_contrib"])
+    _assert_grads(grads, {k[2:]: gold[k] for k in gold.files if k.startswith("g_")}, what="golden ")
+
+
+@pytest.mark.parametrize("case", CASES, ids=[c[0] for c in CASES])
+def test_against_live_reference(case, built, cuda_device):
+    from oracle import ref_dgr
+    if not ref_dgr.available():
+        pytest.skip("oracle/_ref/ref_dgr_C.so not present")
+    kw, ups = case_inputs(case, cuda_device)
+    fwd, grads = run_cuda(kw, ups)
+    rf = ref_dgr.forward(**kw)
+    dec = ref_dgr.decode_buffers(rf)
+    bkw = {k: v for k, v in kw.items() if k not in ("opacities", "image_height", "image_width")}
+    rg = ref_dgr.backward(rf, **bkw, **ups)
+    torch.cuda.synchronize()
+    assert fwd.num_rendered == rf["num_rendered"]
+    assert torch.equal(fwd.radii, rf["radii"])
+    bv, iv = fwd.binning_view(), fwd.image_view()
+    assert torch.equal(bv["keys"], dec["keys"]) and torch.equal(bv["values"], dec["values"])
+    assert torch.equal(iv["ranges"], dec["ranges"])
+    _assert_images(fwd, rf, what="live ref ")
+    _assert_grads(grads, rg, what="live ref ")
+
+
+@pytest.mark.parametrize("case", CASES, ids=[c[0] for c in CASES])
+def test_against_cpu_oracle(case, built, cuda_device):
+    """Stage-wise: the CPU build cannot reproduce nvcc's FMA contraction, so its own radii may
+    differ where 3*sqrt(lambda) sits on an integer; the later stages are therefore fed the GPU's
+    preprocess output, which makes them exactly comparable."""
+    from oracle import cpu_oracle as orc
+    kw, ups = case_inputs(case, cuda_device)
+    fwd, grads = run_cuda(kw, ups)
+    torch.cuda.synchronize()
+    ckw = {k: (v.cpu() if isinstance(v, torch.Tensor) else v) for k, v in kw.items()}
+    own = orc.render_forward(**ckw)
+    # (1) preprocess: radii equal except on rounding boundaries; floats to rounding
+    r_gpu = to_np(fwd.radii)
+    diff = r_gpu != own["radii"]
+    frac = np.abs(own["radius_f"] - np.round(own["radius_f"]))
+    assert np.all(frac[diff] < 1e-3) and diff.mean() < 2e-3, "radii differ away from a rounding boundary"
+    gv = {k: to_np(v) for k, v in fwd.geom_view().items()}
+    vis = (r_gpu > 0) & ~diff
+    assert np.allclose(gv["means2D"][vis], own["means2D"][vis], rtol=0, atol=2e-3)
+    assert np.allclose(gv["conic_opacity"][vis], own["conic_opacity"][vis], rtol=2e-4, atol=1e-6)
+    assert np.allclose(gv["rgb_depth"][vis][:, :3], own["rgb"][vis], rtol=0, atol=1e-5)
+    # (2) binning from the GPU's preprocess output: bit-exact
+    clamped = np.stack([(gv["clamped"] >> c) & 1 for c in range(3)], axis=1).astype(np.uint8)
+    pre = dict(radii=r_gpu, means2D=gv["means2D"], depths=gv["depths"], conic_opacity=gv["conic_opacity"],
+               rgb=np.ascontiguousarray(gv["rgb_depth"][:, :3]), clamped=clamped,
+               tiles_touched=gv["tiles_touched"].astype(np.uint32), cov3D=own["cov3D"], radius_f=own["radius_f"])
+    staged = orc.render_forward(preprocessed=pre, **ckw)
+    bv, iv = fwd.binning_view(), fwd.image_view()
+    assert staged["num_rendered"] == fwd.num_rendered
+    assert np.array_equal(to_np(bv["keys"]).view(np.uint64), staged["keys"])
+    assert np.array_equal(to_np(bv["values"]).view(np.uint32), staged["values"])
+    assert np.array_equal(to_np(iv["ranges"]).view(np.uint32), staged["ranges"])
+    # (3) blend forward
+    _assert_images(fwd, staged, what="oracle ")
+    nc = to_np(iv["n_contrib"]).view(np.uint32)
+    assert (nc != staged["n_contrib"]).mean() < 1e-3
+    # (4) backward from the same forward state
+    bk = {k: v for k, v in ckw.items() if k != "opacities"}
+    og = orc.render_backward(staged, **bk, **{k: v.cpu() for k, v in ups.items()})
+    _assert_grads(grads, og, rtol=5e-4, what="oracle ")
+
+
+def _surface_inputs(case, dev):
+    kw, ups = case_inputs(case, dev)
+    return kw, ups
+
+
+@pytest.mark.parametrize("case", [CASES[0], CASES[2]], ids=[CASES[0][0], CASES[2][0]])
+def test_python_surface_equals_cabi(case, built, cuda_device):
+    """GaussianRasterizer (autograd, torch extension) gives the C-ABI's numbers and gradients."""
+    from egogaussian_b200.diff_gaussian_rasterization import GaussianRasterizationSettings, GaussianRasterizer
+    kw, ups = case_inputs(case, cuda_device)
+    fwd, grads = run_cuda(kw, ups)
+    rs = GaussianRasterizationSettings(kw["image_height"], kw["image_width"], kw["tanfovx"], kw["tanfovy"], kw["bg"],
+                                       1.0, kw["viewmatrix"], kw["projmatrix"], kw["sh_degree"], kw["campos"],
+                                       False, False)
+    leaf = {k: kw[k].clone().requires_grad_(True) for k in ("means3D", "opacities", "shs", "colors_precomp", "scales",
+                                                            "rotations", "cov3D_precomp") if k in kw}
+    means2D = torch.zeros_like(leaf["means3D"], requires_grad=True)
+    color, radii, depth, alpha = GaussianRasterizer(rs)(
+        means3D=leaf["means3D"], means2D=means2D, opacities=leaf["opacities"], shs=leaf.get("shs"),
+        colors_precomp=leaf.get("colors_precomp"), scales=leaf.get("scales"), rotations=leaf.get("rotations"),
+        cov3D_precomp=leaf.get("cov3D_precomp"))
+    assert torch.equal(color, fwd.color) and torch.equal(depth, fwd.depth) and torch.equal(alpha, fwd.alpha)
+    assert torch.equal(radii, fwd.radii)
+    ((color * ups["dL_dcolor"]).sum() + (depth * ups["dL_ddepth"]).sum() + (alpha * ups["dL_dalpha"]).sum()).backward()
+    pairs = {"means3D": "means3D", "opacities": "opacity", "shs": "sh", "colors_precomp": "colors", "scales": "scales",
+             "rotations": "rotations", "cov3D_precomp": "cov3D"}
+    for name, t in leaf.items():
+        assert t.grad is not None, name
+        assert grad_rel_err(t.grad.reshape(grads[pairs[name]].shape), grads[pairs[name]]) <= GRAD_RTOL
+    assert grad_rel_err(means2D.grad, grads["means2D"]) <= GRAD_RTOL
+    assert torch.all(means2D.grad[:, 2] == 0)
+    # alpha-only loss (coarse_obj_pose.py:255-260 style): color / depth grads arrive as None
+    for t in list(leaf.values()) + [means2D]:
+        t.grad = None
+    c2, _, _, a2 = GaussianRasterizer(rs)(
+        means3D=leaf["means3D"], means2D=means2D, opacities=leaf["opacities"], shs=leaf.get("shs"),
+        colors_precomp=leaf.get("colors_precomp"), scales=leaf.get("scales"), rotations=leaf.get("rotations"),
+        cov3D_precomp=leaf.get("cov3D_precomp"))
+    a2.abs().mean().backward()
+    assert leaf["opacities"].grad is not None and torch.isfinite(leaf["opacities"].grad).all()
+
+
+def test_edge_cases(built, cuda_device):
+    from egogaussian_b200 import cabi, scenes
+    dev = cuda_device
+    cam = scenes.make_camera(37, 21)   # not a multiple of the 16x16 tile
+    base = dict(bg=torch.tensor([0.3, 0.5, 0.7], device=dev), viewmatrix=cam.viewmatrix.to(dev),
+                projmatrix=cam.projmatrix.to(dev), campos=cam.campos.to(dev), tanfovx=cam.tanfovx,
+                tanfovy=cam.tanfovy, image_height=21, image_width=37)
+    # P == 0: outputs are zero (rasterize_points.cu:84 skips everything)
+    e3 = torch.empty((0, 3), device=dev)
+    f = cabi.forward(means3D=e3, opacities=torch.empty((0, 1), device=dev), colors_precomp=e3,
+                     cov3D_precomp=torch.empty((0, 6), device=dev), **base)
+    assert f.num_rendered == 0 and float(f.color.abs().max()) == 0.0 and f.radii.numel() == 0
+    # everything culled: background only, num_rendered == 0, backward gives zeros
+    m = torch.tensor([[0.0, 0.0, 0.1], [0.0, 0.0, -3.0]], device=dev)
+    kw = dict(means3D=m, opacities=torch.ones(2, 1, device=dev), colors_precomp=torch.ones(2, 3, device=dev),
+              scales=torch.full((2, 3), 0.1, device=dev),
+              rotations=torch.tensor([[1.0, 0, 0, 0]] * 2, device=dev), **base)
+    ups = dict(dL_dcolor=torch.ones(3, 21, 37, device=dev), dL_ddepth=torch.ones(1, 21, 37, device=dev),
+               dL_dalpha=torch.ones(1, 21, 37, device=dev))
+    f, g = run_cuda(kw, ups)
+    assert f.num_rendered == 0 and torch.all(f.radii == 0)
+    assert torch.allclose(f.color[:, 3, 5], base["bg"]) and float(f.alpha.abs().max()) == 0.0
+    for k in ("means3D", "means2D", "opacity", "colors", "scales", "rotations"):
+        assert float(g[k].abs().max()) == 0.0, k
+    # one huge opaque Gaussian: every pixel saturates at alpha 0.99 after one contributor
+    kw = dict(means3D=torch.tensor([[0.0, 0.0, 2.0]], device=dev), opacities=torch.ones(1, 1, device=dev),
+              colors_precomp=torch.tensor([[1.0, 0.0, 0.0]], device=dev), scales=torch.full((1, 3), 500.0, device=dev),
+              rotations=torch.tensor([[1.0, 0, 0, 0]], device=dev), **base)
+    f, g = run_cuda(kw, ups)
+    assert f.num_rendered == 3 * 2
+    assert torch.all(f.image_view()["n_contrib"] == 1)
+    assert torch.allclose(f.alpha, torch.full_like(f.alpha, 0.99), atol=1e-6)
+    assert torch.allclose(f.depth, torch.full_like(f.depth, 1.98), atol=1e-5)
+    # mark_visible: z_view > 0.2
+    vis = cabi.mark_visible(torch.tensor([[0, 0, 0.2], [0, 0, 0.21], [0, 0, -1.0]], device=dev),
+                            base["viewmatrix"], base["projmatrix"])
+    assert vis.tolist() == [False, True, False]
+    # argument errors come back as EgsError with the library's message
+    with pytest.raises(cabi.EgsError, match="exactly one of shs"):
+        cabi.forward(means3D=kw["means3D"], opacities=kw["opacities"], scales=kw["scales"],
+                     rotations=kw["rotations"], **base)
+
+
+def test_full_size_properties(built, cuda_device):
+    """Config 3 size (1M Gaussians, SH3, 1280x720): properties that need no oracle."""
+    from egogaussian_b200 import cabi, scenes
+    dev = cuda_device
+    sc = scenes.make_scene(1_000_000, 1280, 720, sh_degree=3, seed=3001).to(dev)
+    cam = sc.camera
+    kw = dict(means3D=sc.means3D, opacities=sc.opacities, bg=sc.bg, viewmatrix=cam.viewmatrix,
+              projmatrix=cam.projmatrix, campos=cam.campos, tanfovx=cam.tanfovx, tanfovy=cam.tanfovy,
+              image_height=720, image_width=1280, sh_degree=3, shs=sc.shs, scales=sc.scales, rotations=sc.rotations)
+    f1 = cabi.forward(**kw)
+    gv, bv, iv = f1.geom_view(), f1.binning_view(), f1.image_view()
+    R = f1.num_rendered
+    assert R == int(gv["tiles_touched"].to(torch.int64).sum()) == int(gv["point_offsets"][-1])
+    assert torch.equal(gv["point_offsets"].to(torch.int64), torch.cumsum(gv["tiles_touched"].to(torch.int64), 0))
+    keys, vals = bv["keys"], bv["values"]
+    assert bool((keys[1:] >= keys[:-1]).all()), "sorted"
+    ties = keys[1:] == keys[:-1]
+    assert bool((vals[1:][ties] > vals[:-1][ties]).all()), "stable"
+    # the sorted list is a permutation of what duplication produced: same multiset of values and
+    # the depth bits in each key belong to its value
+    counts = torch.bincount(vals.to(torch.int64), minlength=sc.P)
+    assert torch.equal(counts, gv["tiles_touched"].to(torch.int64))
+    assert torch.equal((keys & 0xFFFFFFFF).to(torch.int32), gv["depths"].view(torch.int32)[vals.to(torch.int64)])
+    tiles = (keys >> 32)
+    rng = iv["ranges"].to(torch.int64)
+    tile_counts = torch.bincount(tiles, minlength=rng.shape[0])
+    assert torch.equal(rng[:, 1] - rng[:, 0], tile_counts)
+    nonempty = tile_counts > 0
+    assert torch.equal(rng[nonempty, 0], (torch.cumsum(tile_counts, 0) - tile_counts)[nonempty])
+    # image sanity: alpha in [0, 1], colour finite, n_contrib within the tile's list
+    assert bool(torch.isfinite(f1.color).all()) and float(f1.alpha.min()) >= 0 and float(f1.alpha.max()) <= 1 + 1e-5
+    # idempotence / determinism of the forward
+    f2 = cabi.forward(**kw)
+    assert torch.equal(f1.color, f2.color) and torch.equal(f1.radii, f2.radii)
+    assert torch.equal(f1.binning_view()["values"], f2.binning_view()["values"])
+    # linearity of backward in the upstream gradient: g(2w) = 2 g(w)
+    wc, wd, wa = [t.to(dev) for t in scenes.upstream_weights(1280, 720, 1)]
+    bkw = {k: v for k, v in kw.items() if k not in ("opacities", "image_height", "image_width")}
+    g1 = cabi.backward(f1, dL_dcolor=wc, dL_ddepth=wd, dL_dalpha=wa, **bkw)
+    g2 = cabi.backward(f1, dL_dcolor=2 * wc, dL_ddepth=2 * wd, dL_dalpha=2 * wa, **bkw)
+    for k in ("means3D", "sh", "opacity", "scales", "rotations"):
+        assert grad_rel_err(g2[k], 2 * g1[k]) <= GRAD_RTOL, k
+    assert bool(torch.all(g1["means3D"][f1.radii == 0] == 0))
+
+
+def test_adam_and_se3(built, cuda_device):
+    from egogaussian_b200 import scenes
+    from egogaussian_b200.diff_gaussian_rasterization import _C
+    dev = cuda_device
+    torch.manual_seed(0)
+    shapes = [(5000, 3), (5000, 1, 3), (5000, 15, 3), (5000, 1), (5000, 3), (5000, 4), (7,)]
+    lrs = [1.6e-4, 2.5e-3, 1.25e-4, 0.05, 5e-3, 1e-3, 1e-4]
+    ref_p = [torch.randn(s, device=dev).requires_grad_(True) for s in shapes]
+    opt = torch.optim.Adam([{"params": [p], "lr": lr} for p, lr in zip(ref_p, lrs)], lr=0.0, eps=1e-15)
+    ours = [p.detach().clone() for p in ref_p]
+    m = [torch.zeros_like(p) for p in ours]
+    v = [torch.zeros_like(p) for p in ours]
+    for step in range(1, 4):
+        grads = [torch.randn(s, device=dev) * (10.0 ** -step) for s in shapes]
+        for p, g in zip(ref_p, grads):
+            p.grad = g.clone()
+        opt.step()
+        _C.adam_step(ours, grads, m, v, lrs, [step] * len(ours), 0.9, 0.999, 1e-15)
+        for a, b in zip(ours, ref_p):
+            assert torch.allclose(a, b.detach(), rtol=2e-6, atol=1e-8)
+    # rigid transform and its pull-back
+    P = 4000
+    xyz = torch.randn(P, 3, device=dev)
+    is_obj = (torch.rand(P, device=dev) < 0.1).to(torch.int32)
+    Rt = scenes.object_pose().to(dev)
+    R, t = Rt[:9].reshape(3, 3), Rt[9:]
+    cov = scenes.build_covariance(torch.rand(P, 3) * 0.1 + 0.01, torch.nn.functional.normalize(torch.randn(P, 4), dim=1)).to(dev)
+    moved, cov_moved = _C.se3_apply(xyz, is_obj, 1, Rt, cov)
+    want = torch.where(is_obj[:, None] == 1, xyz @ R.t() + t, xyz)
+    assert torch.allclose(moved, want, atol=1e-6)
+    S = torch.zeros(P, 3, 3, device=dev)
+    iu = [(0, 0, 0), (0, 1, 1), (0, 2, 2), (1, 1, 3), (1, 2, 4), (2, 2, 5)]
+    for a, b, k in iu:
+        S[:, a, b] = cov[:, k]
+        S[:, b, a] = cov[:, k]
+    S2 = R @ S @ R.t()
+    want_cov = torch.stack([S2[:, a, b] for a, b, _ in iu], dim=1)
+    assert torch.allclose(cov_moved, torch.where(is_obj[:, None] == 1, want_cov, cov), atol=1e-6)
+    # reference semantics: un-move then compare (fine_all.py:116 tolerance 1e-3)
+    back = torch.where(is_obj[:, None] == 1, (moved - t) @ R, moved)
+    assert torch.allclose(back, xyz, atol=1e-3)
+    g_moved = torch.randn(P, 3, device=dev)
+    p_ref = xyz.clone().requires_grad_(True)
+    opt = torch.optim.Adam([p_ref], lr=1.6e-4, eps=1e-15)
+    p_ref.grad = torch.where(is_obj[:, None] == 1, g_moved @ R, g_moved)   # R^T g as rows
+    opt.step()
+    p = xyz.clone()
+    m1, v1 = torch.zeros_like(p), torch.zeros_like(p)
+    _C.adam_se3_step(p, g_moved, m1, v1, is_obj, 1, Rt, 1.6e-4, 1, 0.9, 0.999, 1e-15)
+    assert torch.allclose(p, p_ref.detach(), rtol=2e-6, atol=1e-8)
