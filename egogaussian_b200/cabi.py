@@ -287,8 +287,9 @@ def forward(*, means3D, opacities, bg, viewmatrix, projmatrix, campos, tanfovx, 
 def backward(fwd: ForwardResult, *, means3D, bg, viewmatrix, projmatrix, campos, tanfovx,
              tanfovy, dL_dcolor, dL_ddepth, dL_dalpha, sh_degree=0, shs=None, colors_precomp=None,
              scales=None, rotations=None, cov3D_precomp=None, scale_modifier=1.0, debug=False,
-             stream=None, scratch=None):
-    """egs_backward; returns a dict of gradient tensors (absent inputs -> None)."""
+             stream=None, scratch=None, out=None):
+    """egs_backward; returns a dict of gradient tensors (absent inputs -> None). `out` may carry
+    preallocated gradient tensors under the same keys (e.g. views of one flat all-reduce buffer)."""
     import torch
     lib = load()
     dev = means3D.device
@@ -303,7 +304,9 @@ def backward(fwd: ForwardResult, *, means3D, bg, viewmatrix, projmatrix, campos,
         "sh": torch.empty((P, M, 3), **f) if M else None,
         "scales": torch.empty((P, 3), **f) if scales is not None else None,
         "rotations": torch.empty((P, 4), **f) if rotations is not None else None,
-    }
+    } if out is None else dict(out)
+    for key in ("colors", "cov3D", "sh", "scales", "rotations"):
+        g.setdefault(key, None)
     if P == 0:
         return g
     if scratch is None:

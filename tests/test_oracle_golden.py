@@ -1,0 +1,72 @@
+"""Pins the CPU oracle against golden vectors produced by the UNMODIFIED reference rasterizer
+(oracle/_ref, built from /root/reference for sm_100 and run on a B200 by tests/golden/make_golden.py).
+The reference ships no tests or fixtures of its own, so these outputs of
+the reference itself are the oracle's known-answer tests. Runs on the CPU."""
+from pathlib import Path
+
+import numpy as np
+import pytest
+
+from golden.make_golden import CASES, case_inputs
+from oracle import cpu_oracle as orc
+
+GOLDEN = Path(__file__).resolve().parent / "golden"
+
+
+@pytest.mark.parametrize("case", CASES, ids=[c[0] for c in CASES])
+def test_oracle_reproduces_reference_outputs(case):
+    path = GOLDEN / f"{case[0]}.npz"
+    assert path.exists(), "golden vectors are committed with the repo"
+    gold = np.load(path)
+    kw, ups = case_inputs(case, "cpu")
+    f = orc.render_forward(**kw)
+
+    # integer / index work: bit-exact on these fixtures (no Gaussian sits on a rounding boundary)
+    assert np.array_equal(f["radii"], gold["radii"])
+    assert f["num_rendered"] == int(gold["num_rendered"])
+    assert np.array_equal(f["tiles_touched"], gold["i_tiles_touched"].view(np.uint32))
+    assert np.array_equal(f["keys"], gold["i_keys"].view(np.uint64))
+    assert np.array_equal(f["values"], gold["i_values"].view(np.uint32))
+    assert np.array_equal(f["ranges"], gold["i_ranges"].view(np.uint32))
+    assert np.array_equal(f["n_contrib"], gold["i_n_contrib"].view(np.uint32))
+
+    # floating point: the tolerance north_star states for images (1e-5 absolute)
+    vis = gold["radii"] > 0
+    assert np.abs(f["means2D"][vis] - gold["i_means2D"][vis]).max() <= 1e-3   # pixels; fp32 ulp at ~1e3 px
+    assert np.array_equal(f["depths"][vis].view(np.uint32), gold["i_depths"][vis].view(np.uint32)) or \
+        np.abs(f["depths"][vis] - gold["i_depths"][vis]).max() <= 1e-6
+    scale = np.abs(gold["i_conic_opacity"][vis]).max()
+    assert np.abs(f["conic_opacity"][vis] - gold["i_conic_opacity"][vis]).max() <= 1e-5 * scale
+    if "shs" in kw:   # the reference only fills its rgb array in SH mode
+        assert np.abs(f["rgb"][vis] - gold["i_rgb"][vis]).max() <= 1e-5
+        assert np.array_equal(f["clamped"][vis], gold["i_clamped"][vis])
+    for k in ("color", "depth", "alpha"):
+        assert np.abs(f[k] - gold[k]).max() <= 1e-5, k
+
+    # backward: T_final = 1 - alpha amplifies the last bit of the alpha image (backward.cu:463), so
+    # the oracle's backward is checked from the reference's own forward state, as the reference's
+    # backward is; tolerance 1e-4 of the tensor's max magnitude (north_star)
+    f["alpha"] = gold["alpha"]
+    bk = {k: v for k, v in kw.items() if k != "opacities"}
+    g = orc.render_backward(f, **bk, **ups)
+    checked = 0
+    for k in ("means2D", "opacity", "means3D", "sh", "scales", "rotations", "cov3D", "colors"):
+        if g.get(k) is None or ("g_" + k) not in gold.files:
+            continue
+        a, b = g[k].reshape(gold["g_" + k].shape).astype(np.float64), gold["g_" + k].astype(np.float64)
+        assert np.abs(a - b).max() <= 1e-4 * np.abs(b).max(), k
+        checked += 1
+    assert checked >= 5
+
+
+def test_oracle_backward_from_own_forward_stays_close():
+    """Without borrowing the reference's alpha image the ill-conditioned T_final still leaves the
+    oracle within 1e-2 of the reference gradients (observed ~2e-3); documents the effect."""
+    case = CASES[0]
+    gold = np.load(GOLDEN / f"{case[0]}.npz")
+    kw, ups = case_inputs(case, "cpu")
+    f = orc.render_forward(**kw)
+    g = orc.render_backward(f, **{k: v for k, v in kw.items() if k != "opacities"}, **ups)
+    for k in ("means2D", "means3D", "opacity"):
+        b = gold["g_" + k].astype(np.float64)
+        assert np.abs(g[k].reshape(b.shape) - b).max() <= 1e-2 * np.abs(b).max()
