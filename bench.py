@@ -1,0 +1,436 @@
+"""bench.py -- fwd+bwd render iterations/s of the rasterizer hot path (BASELINE.json metric).
+
+  python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference] [--P ...]
+  torchrun --nnodes=1 --nproc-per-node N ... bench.py --gpus N --steps K --warmup W
+
+One "step" = one forward + one backward of the rasterizer over one camera view of the synthetic
+1M-Gaussian, SH-degree-3, 1280x720 scene (BASELINE.json configs[2]), i.e. one
+training iteration's render work. Rank r renders view r of the 8-view batch (configs[3]); with
+N > 1 the step also contains the data-parallel exchange (one NCCL all-reduce of the flat
+gradient buffer). Weak scaling: per-GPU work is fixed, `value` counts the views of all ranks.
+
+JSON keys (one line, rank 0):
+  value      device-resident inputs, C-ABI calls, CUDA events, max over ranks
+  e2e        same metric through the public Python API (GaussianRasterizer + autograd) with the
+             step's host inputs (camera matrices, upstream-gradient images) copied from pinned
+             memory and the scalar loss read back, all inside the timed region
+  roofline   dominant kernel of the timed region: algorithmic bytes (SURVEY.md 8d formulas,
+             DESIGN.md) / its mean duration from the library's built-in CUDA-event stage timers
+  cpu_baseline  the CPU oracle (oracle/cpu_rasterizer.c, OpenMP) on the host cores, one iteration
+  kernels    every stage: ms per step, achieved GB/s, fraction of the measured HBM peak
+--impl reference runs the UNMODIFIED reference CUDA rasterizer (oracle/_ref, built from
+/root/reference for sm_100) on the same workload; if that binary did not travel, the CPU oracle.
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+from pathlib import Path
+
+ROOT = Path(__file__).resolve().parent
+sys.path.insert(0, str(ROOT))
+
+METRIC = "fwd+bwd render iters/sec @1M Gaussians SH3 1280x720"
+UNIT = "iters/s"
+
+
+def parse():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=30)
+    ap.add_argument("--warmup", type=int, default=5)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--P", type=int, default=1_000_000)
+    ap.add_argument("--width", type=int, default=1280)
+    ap.add_argument("--height", type=int, default=720)
+    ap.add_argument("--sh-degree", type=int, default=3)
+    ap.add_argument("--geom", default="scale_rot", choices=["scale_rot", "cov"])
+    ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
+    ap.add_argument("--no-e2e", action="store_true")
+    return ap.parse_args()
+
+
+# --------------------------------------------------------------------------------------------
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons sampled every 200 ms while the timed region runs."""
+    Q = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,"
+         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
+         "clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index: int):
+        self.lines, self.proc = [], None
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits",
+                                          "-lms", "200", "-i", str(index)], stdout=subprocess.PIPE, text=True)
+            self.t = threading.Thread(target=self._pump, daemon=True)
+            self.t.start()
+        except Exception:
+            self.proc = None
+
+    def _pump(self):
+        for line in self.proc.stdout:
+            self.lines.append(line.strip())
+
+    def stop(self):
+        if not self.proc:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        time.sleep(0.25)
+        self.proc.terminate()
+        sm, mx, reasons = [], None, set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for ln in self.lines:
+            f = [x.strip() for x in ln.split(",")]
+            if len(f) < 7:
+                continue
+            try:
+                sm.append(float(f[0]))
+                mx = float(f[1])
+            except ValueError:
+                continue
+            for n, v in zip(names, f[3:7]):
+                if v.lower().startswith("active"):
+                    reasons.add(n)
+        sm.sort()
+        return {"sm_mhz": sm[len(sm) // 2] if sm else None, "sm_max_mhz": mx, "reasons": sorted(reasons),
+                "samples": len(sm)}
+
+
+def measured_peak_gbs():
+    p = ROOT / "MEASURED_PEAKS.json"
+    if p.exists():
+        try:
+            return float(json.loads(p.read_text())["hbm_gbs"]), "measured (MEASURED_PEAKS.json)"
+        except Exception:
+            pass
+    return 6650.0, "fallback (B200_PROFILING.md)"
+
+
+def algorithmic_bytes(P, V, R, N, Tn, M, D, geom, passes):
+    """Compulsory global traffic per launch, SURVEY.md 8(d) (restated in DESIGN.md)."""
+    c = 12 * (D + 1) ** 2
+    g = 28 if geom == "scale_rot" else 24
+    cov_store = 24 if geom == "scale_rot" else 0
+    return {
+        "preprocess_fwd": 20 * P + V * (g + 4 + c + 4 + 8 + 16 + 12 + 3 + cov_store),
+        "scan": 8 * P,
+        "duplicate_keys": 20 * P + 12 * R,
+        "sort_histogram": 8 * R,
+        "sort_passes": R * 24 * passes,
+        "tile_ranges": 8 * R + 16 * Tn,
+        "blend_fwd": 44 * R + 24 * N + 8 * Tn,
+        "bwd_zero": 48 * P,
+        "blend_bwd": 44 * R + 28 * N + 8 * Tn + 40 * R,
+        "preprocess_bwd": 4 * P + P * (12 + 24 + 16 + 12 + 12 + 4 + 3 + g + c) + P * (12 + 12 + 4 + (28 if geom == "scale_rot" else 24) + 12 * M),
+    }
+
+
+def build_inputs(a, view, device):
+    import torch
+    from egogaussian_b200 import scenes
+    sc = scenes.make_scene(a.P, a.width, a.height, sh_degree=a.sh_degree, seed=3001, view=view)
+    cam = sc.camera
+    kw = dict(means3D=sc.means3D, opacities=sc.opacities, bg=sc.bg, viewmatrix=cam.viewmatrix,
+              projmatrix=cam.projmatrix, campos=cam.campos, tanfovx=cam.tanfovx, tanfovy=cam.tanfovy,
+              image_height=a.height, image_width=a.width, sh_degree=a.sh_degree, shs=sc.shs)
+    if a.geom == "scale_rot":
+        kw["scales"], kw["rotations"] = sc.scales, sc.rotations
+    else:
+        kw["cov3D_precomp"] = sc.cov3D()
+    wc, wd, wa = scenes.upstream_weights(a.width, a.height, 3001 + (view or 0))
+    host = {"viewmatrix": cam.viewmatrix.pin_memory(), "projmatrix": cam.projmatrix.pin_memory(),
+            "campos": cam.campos.pin_memory(), "wc": wc.contiguous().pin_memory(), "wd": wd.contiguous().pin_memory(),
+            "wa": wa.contiguous().pin_memory()} if device.type == "cuda" else None
+    cpu_kw = dict(kw)
+    kw = {k: (v.to(device).contiguous() if isinstance(v, torch.Tensor) else v) for k, v in kw.items()}
+    ups = dict(dL_dcolor=wc.to(device).contiguous(), dL_ddepth=wd.to(device).contiguous(),
+               dL_dalpha=wa.to(device).contiguous())
+    return kw, ups, host, cpu_kw, (wc, wd, wa)
+
+
+def timed_region(step, steps, warmup, dist_on, device):
+    """W untimed steps, then exactly K steps between barrier+synchronize pairs; CUDA events on the
+    launching (current) stream; returns seconds, max over ranks."""
+    import torch
+    import torch.distributed as dist
+    for _ in range(warmup):
+        step()
+    torch.cuda.synchronize()
+    if dist_on:
+        dist.barrier()
+    torch.cuda.synchronize()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(steps):
+        step()
+    e1.record()
+    torch.cuda.synchronize()
+    if dist_on:
+        dist.barrier()
+    torch.cuda.synchronize()
+    sec = e0.elapsed_time(e1) / 1e3
+    if dist_on:
+        t = torch.tensor([sec], device=device, dtype=torch.float64)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        sec = float(t.item())
+    return sec
+
+
+def cpu_baseline(cpu_kw, weights):
+    """One fwd+bwd iteration of the same workload on the host cores with the CPU oracle."""
+    from oracle import cpu_oracle as orc
+    orc.build()
+    t0 = time.time()
+    f = orc.render_forward(**cpu_kw)
+    bk = {k: v for k, v in cpu_kw.items() if k != "opacities"}
+    orc.render_backward(f, dL_dcolor=weights[0], dL_ddepth=weights[1], dL_dalpha=weights[2], **bk)
+    dt = time.time() - t0
+    return {"value": 1.0 / dt, "unit": UNIT, "cores": orc.num_threads(), "kind": "port",
+            "sample": "1 full fwd+bwd iteration of the same workload (%.1f s), C/OpenMP oracle" % dt}
+
+
+# --------------------------------------------------------------------------------------------
+def run_ours(a, rank, world, local_rank):
+    import torch
+    import torch.distributed as dist
+    from egogaussian_b200 import cabi, parallel
+    from egogaussian_b200.diff_gaussian_rasterization import GaussianRasterizationSettings, GaussianRasterizer
+    device = torch.device("cuda", local_rank)
+    torch.cuda.set_device(device)
+    dist_on = world > 1
+    kw, ups, host, cpu_kw, weights = build_inputs(a, rank if dist_on else None, device)
+    P, M = a.P, (a.sh_degree + 1) ** 2
+    bkw = {k: v for k, v in kw.items() if k not in ("opacities", "image_height", "image_width")}
+    flat = parallel.FlatGrads(P, M, device)
+    scratch = torch.empty((cabi.load().egs_backward_scratch_bytes(P),), dtype=torch.uint8, device=device)
+    state = {}
+
+    def step():
+        fwd = cabi.forward(**kw)
+        out = flat.as_backward_out()
+        if a.geom != "scale_rot":
+            out = {"means3D": out["means3D"], "sh": out["sh"], "opacity": out["opacity"], "means2D": out["means2D"],
+                   "cov3D": state.setdefault("cov", torch.empty((P, 6), device=device))}
+        cabi.backward(fwd, out=out, scratch=scratch, **bkw, **ups)
+        if dist_on:
+            parallel.allreduce_gradients(flat.flat)
+        state["fwd"] = fwd
+
+    clocks = ClockSampler(local_rank) if rank == 0 else None
+    cabi.profile_enable(True)
+    for _ in range(a.warmup):       # warm the profiler's event pool too, then drop those records
+        step()
+    torch.cuda.synchronize()
+    cabi.profile_read()
+    l0 = cabi.launch_count()
+    sec = timed_region(step, a.steps, 0, dist_on, device)
+    launches = cabi.launch_count() - l0
+    prof = cabi.profile_read()
+    cabi.profile_enable(False)
+    clk = clocks.stop() if clocks else None
+    value = world * a.steps / sec
+
+    fwd = state["fwd"]
+    R = fwd.num_rendered
+    V = int((fwd.radii > 0).sum())
+    N = a.width * a.height
+    Tn = ((a.width + 15) // 16) * ((a.height + 15) // 16)
+    frag = int(fwd.image_view()["n_contrib"].to(torch.int64).sum())
+    passes = (32 + Tn.bit_length() + 7) // 8
+    alg = algorithmic_bytes(P, V, R, N, Tn, M, a.sh_degree, a.geom, passes)
+    peak, peak_src = measured_peak_gbs()
+    kernels = {}
+    for name, (ms, cnt) in prof.items():
+        if cnt == 0 or name not in alg:
+            continue
+        per = ms / a.steps
+        kernels[name] = {"ms_per_step": round(per, 4), "launches_per_step": cnt / a.steps,
+                         "alg_MB": round(alg[name] / 1e6, 2), "GBps": round(alg[name] / per / 1e6, 1),
+                         "frac_hbm": round(alg[name] / per / 1e6 / peak, 4)}
+    top = max(kernels, key=lambda k: kernels[k]["ms_per_step"])
+    roofline = {"kernel": top, "bound": "hbm", "achieved": kernels[top]["GBps"], "peak": peak, "unit": "GB/s",
+                "frac": kernels[top]["frac_hbm"], "traffic": None, "peak_source": peak_src,
+                "ms_per_launch": kernels[top]["ms_per_step"] / max(kernels[top]["launches_per_step"], 1),
+                "note": "tile-blend kernels are FP32/MUFU/atomic-bound, not HBM-bound; see DESIGN.md"}
+
+    # ---- end-to-end through the public Python API with host inputs -------------------------
+    e2e = None
+    if not a.no_e2e:
+        leaves = {k: kw[k].clone().requires_grad_(True) for k in ("means3D", "opacities", "shs", "scales", "rotations",
+                                                                  "cov3D_precomp") if k in kw}
+        dv = {k: torch.empty_like(v, device=device) for k, v in host.items()}
+        h2d = sum(v.numel() * 4 for v in host.values())
+        loss_host = torch.empty((), dtype=torch.float32).pin_memory()
+
+        def e2e_step():
+            for k in dv:
+                dv[k].copy_(host[k], non_blocking=True)
+            rs = GaussianRasterizationSettings(a.height, a.width, kw["tanfovx"], kw["tanfovy"], kw["bg"], 1.0,
+                                               dv["viewmatrix"], dv["projmatrix"], a.sh_degree, dv["campos"], False, False)
+            means2D = torch.zeros_like(leaves["means3D"], requires_grad=True)
+            color, radii, depth, alpha = GaussianRasterizer(rs)(
+                means3D=leaves["means3D"], means2D=means2D, opacities=leaves["opacities"], shs=leaves["shs"],
+                scales=leaves.get("scales"), rotations=leaves.get("rotations"), cov3D_precomp=leaves.get("cov3D_precomp"))
+            loss = (color * dv["wc"]).sum() + (depth * dv["wd"]).sum() + (alpha * dv["wa"]).sum()
+            loss.backward()
+            if dist_on:
+                for t in leaves.values():
+                    dist.all_reduce(t.grad)
+            loss_host.copy_(loss.detach(), non_blocking=True)
+            torch.cuda.current_stream().synchronize()   # the step's result is on the host
+            for t in leaves.values():
+                t.grad = None
+
+        sec2 = timed_region(e2e_step, a.steps, a.warmup, dist_on, device)
+        e2e = {"value": world * a.steps / sec2, "unit": UNIT, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": 4,
+               "ms_per_step": sec2 / a.steps * 1e3}
+
+    # ---- full training step (adds the fused Adam over all parameter groups), informational ----
+    extra = {}
+    try:
+        from egogaussian_b200.diff_gaussian_rasterization import _C
+        names = ["means3D", "sh", "opacity"] + (["scales", "rotations"] if a.geom == "scale_rot" else [])
+        params = [torch.randn_like(flat.views[n]) for n in names]
+        grads = [flat.views[n] for n in names]
+        ms_ = [torch.zeros_like(p) for p in params]
+        vs_ = [torch.zeros_like(p) for p in params]
+        lrs = [1.6e-4, 2.5e-3, 0.05, 5e-3, 1e-3][:len(names)]
+        stepc = [0]
+
+        def train_step():
+            step()
+            stepc[0] += 1
+            _C.adam_step(params, grads, ms_, vs_, lrs, [stepc[0]] * len(params), 0.9, 0.999, 1e-15)
+
+        sec3 = timed_region(train_step, a.steps, 3, dist_on, device)
+        extra["train_step_iters_per_s"] = world * a.steps / sec3
+        extra["adam_floats"] = int(sum(p.numel() for p in params))
+    except Exception as exc:  # informational only
+        extra["train_step_error"] = str(exc)[:200]
+
+    if rank != 0:
+        return None
+    line = {
+        "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": a.steps, "warmup": a.warmup,
+        "ms_per_step": sec / a.steps * 1e3, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+        "dtype": "f32", "data": "synthetic",
+        "config": {"workload": "configs[2]: 1M-Gaussian SH3 scene, 1280x720, one view per GPU per step "
+                               "(rank r renders view r of the configs[3] 8-view batch when N>1)",
+                   "P": P, "sh_degree": a.sh_degree, "width": a.width, "height": a.height, "geometry": a.geom,
+                   "num_rendered": R, "visible": V, "fragments": frag,
+                   "parallelism": "view-dp%d" % world if dist_on else "single",
+                   "l2": "working set (>300 MB of Gaussian data + sort buffers per step) exceeds the 126 MB L2; no flush"},
+        "e2e": e2e, "gpu_launches": int(launches), "roofline": roofline, "kernels": kernels, "clocks": clk,
+        "mfragments_per_s": {"fwd": frag / (kernels["blend_fwd"]["ms_per_step"] * 1e3),
+                             "bwd": frag / (kernels["blend_bwd"]["ms_per_step"] * 1e3)},
+        "extra": extra,
+    }
+    if not a.no_cpu and world == 1:
+        line["cpu_baseline"] = cpu_baseline(cpu_kw, weights)
+    return line
+
+
+def run_reference(a, rank, world, local_rank):
+    """The unmodified reference on the same workload (rank 0 only)."""
+    if rank != 0:
+        return None
+    from oracle import ref_dgr
+    import torch
+    if not (ref_dgr.available() and torch.cuda.is_available()):
+        # the reference has no CPU implementation; time the CPU restatement instead
+        kw, ups, host, cpu_kw, weights = build_inputs(a, None, torch.device("cpu"))
+        cb = cpu_baseline(cpu_kw, weights)
+        return {"impl": "reference", "metric": METRIC, "value": cb["value"], "unit": UNIT, "n_gpus": world,
+                "steps": 1, "warmup": 0, "ms_per_step": 1e3 / cb["value"], "higher_is_better": True,
+                "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+                "config": {"workload": "configs[2] on host cores (oracle port; oracle/_ref missing)"},
+                "cpu_baseline": cb, "e2e": {"value": cb["value"], "unit": UNIT, "h2d_bytes_per_step": 0,
+                                            "d2h_bytes_per_step": 0}}
+    device = torch.device("cuda", local_rank)
+    torch.cuda.set_device(device)
+    kw, ups, host, cpu_kw, weights = build_inputs(a, None, device)
+    bkw = {k: v for k, v in kw.items() if k not in ("opacities", "image_height", "image_width")}
+    state = {}
+
+    def step():
+        f = ref_dgr.forward(**kw)
+        ref_dgr.backward(f, **bkw, **ups)
+        state["fwd"] = f
+
+    clocks = ClockSampler(local_rank)
+    sec = timed_region(step, a.steps, a.warmup, False, device)
+    clk = clocks.stop()
+    value = a.steps / sec
+
+    rast = ref_dgr.make_autograd_rasterizer()
+    leaves = {k: kw[k].clone().requires_grad_(True) for k in ("means3D", "opacities", "shs", "scales", "rotations",
+                                                              "cov3D_precomp") if k in kw}
+    dv = {k: torch.empty_like(v, device=device) for k, v in host.items()}
+    h2d = sum(v.numel() * 4 for v in host.values())
+    loss_host = torch.empty((), dtype=torch.float32).pin_memory()
+
+    def e2e_step():
+        for k in dv:
+            dv[k].copy_(host[k], non_blocking=True)
+        rs = dict(bg=kw["bg"], scale_modifier=1.0, viewmatrix=dv["viewmatrix"], projmatrix=dv["projmatrix"],
+                  tanfovx=kw["tanfovx"], tanfovy=kw["tanfovy"], image_height=a.height, image_width=a.width,
+                  sh_degree=a.sh_degree, campos=dv["campos"])
+        means2D = torch.zeros_like(leaves["means3D"], requires_grad=True)
+        color, radii, depth, alpha = rast(rs, means3D=leaves["means3D"], means2D=means2D, opacities=leaves["opacities"],
+                                          shs=leaves["shs"], scales=leaves.get("scales"), rotations=leaves.get("rotations"),
+                                          cov3D_precomp=leaves.get("cov3D_precomp"))
+        loss = (color * dv["wc"]).sum() + (depth * dv["wd"]).sum() + (alpha * dv["wa"]).sum()
+        loss.backward()
+        loss_host.copy_(loss.detach(), non_blocking=True)
+        torch.cuda.current_stream().synchronize()
+        for t in leaves.values():
+            t.grad = None
+
+    sec2 = timed_region(e2e_step, a.steps, a.warmup, False, device)
+    return {"impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": 1, "steps": a.steps,
+            "warmup": a.warmup, "ms_per_step": sec / a.steps * 1e3, "higher_is_better": True, "scaling": "weak",
+            "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+            "config": {"workload": "configs[2]: 1M-Gaussian SH3 scene, 1280x720, unmodified reference CUDA "
+                                   "rasterizer built for sm_100 (oracle/_ref)", "P": a.P, "sh_degree": a.sh_degree,
+                       "width": a.width, "height": a.height, "geometry": a.geom,
+                       "num_rendered": state["fwd"]["num_rendered"]},
+            "cpu_baseline": {"value": value, "unit": UNIT, "cores": 0, "kind": "reference",
+                             "sample": "the reference has no CPU implementation: its own CUDA kernels on the same GPU"},
+            "e2e": {"value": a.steps / sec2, "unit": UNIT, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": 4,
+                    "ms_per_step": sec2 / a.steps * 1e3},
+            "clocks": clk}
+
+
+def main():
+    a = parse()
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    if a.impl == "reference" and rank != 0:
+        return 0
+    import torch
+    if a.impl == "ours" and not torch.cuda.is_available():
+        raise SystemExit("bench.py: no CUDA device; the product path has no CPU fallback")
+    dist_on = world > 1 and a.impl == "ours"
+    if dist_on:
+        import torch.distributed as dist
+        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        torch.cuda.set_device(local_rank)
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
+    try:
+        line = run_ours(a, rank, world, local_rank) if a.impl == "ours" else run_reference(a, rank, world, local_rank)
+        if line is not None:
+            print(json.dumps(line), flush=True)
+    finally:
+        if dist_on:
+            import torch.distributed as dist
+            dist.destroy_process_group()
+    return 0
+
+
+if __name__ == "__main__":
+    sys.exit(main())

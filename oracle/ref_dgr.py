@@ -123,3 +123,43 @@ def decode_buffers(fwd: Dict) -> Dict:
     ranges, off = take(im, off, 8 * N, torch.int32, (N, 2))
     out["ranges"] = ranges[:tiles].clone()
     return out
+
+
+def make_autograd_rasterizer():
+    """An autograd Function + callable that drives the reference's compiled functions the way its
+    own Python layer does (DGR/diff_gaussian_rasterization/__init__.py:44-158): used only by the
+    `--impl reference` bench arm so that its end-to-end number goes through the same kind of
+    public call (module(...) -> (color, radii, depth, alpha), loss.backward()) as ours."""
+    import torch
+    C = load()
+
+    class _Ref(torch.autograd.Function):
+        @staticmethod
+        def forward(ctx, means3D, means2D, sh, colors, opac, scales, rots, cov, rs):
+            out = C.rasterize_gaussians(rs["bg"], means3D, colors, opac, scales, rots, rs["scale_modifier"], cov,
+                                        rs["viewmatrix"], rs["projmatrix"], rs["tanfovx"], rs["tanfovy"],
+                                        rs["image_height"], rs["image_width"], sh, rs["sh_degree"], rs["campos"],
+                                        False, False)
+            n, color, depth, alpha, radii, geom, binning, img = out
+            ctx.rs, ctx.n = rs, n
+            ctx.save_for_backward(colors, means3D, scales, rots, cov, radii, sh, geom, binning, img, alpha)
+            return color, radii, depth, alpha
+
+        @staticmethod
+        def backward(ctx, g_color, _g_radii, g_depth, g_alpha):
+            rs = ctx.rs
+            colors, means3D, scales, rots, cov, radii, sh, geom, binning, img, alpha = ctx.saved_tensors
+            g2d, gcol, gop, g3d, gcov, gsh, gsc, grot = C.rasterize_gaussians_backward(
+                rs["bg"], means3D, radii, colors, scales, rots, rs["scale_modifier"], cov, rs["viewmatrix"],
+                rs["projmatrix"], rs["tanfovx"], rs["tanfovy"], g_color, g_depth, g_alpha, sh, rs["sh_degree"],
+                rs["campos"], geom, ctx.n, binning, img, alpha, False)
+            return g3d, g2d, gsh, gcol, gop, gsc, grot, gcov, None
+
+    def rasterize(rs, *, means3D, means2D, opacities, shs=None, colors_precomp=None, scales=None, rotations=None,
+                  cov3D_precomp=None):
+        e = torch.Tensor([])
+        return _Ref.apply(means3D, means2D, e if shs is None else shs, e if colors_precomp is None else colors_precomp,
+                          opacities, e if scales is None else scales, e if rotations is None else rotations,
+                          e if cov3D_precomp is None else cov3D_precomp, rs)
+
+    return rasterize
