@@ -122,6 +122,11 @@ def algorithmic_bytes(P, V, R, N, Tn, M, D, geom, passes):
         "sort_histogram": 8 * R,
         "sort_passes": R * 24 * passes,
         "tile_ranges": 8 * R + 16 * Tn,
+        # tile-bucket path: counts -> ranges; scatter one 8-byte word per instance;
+        # per-tile sort reads it once and writes the index list + the 64-bit keys
+        "tile_scan": 12 * Tn,
+        "tile_scatter": 20 * P + 8 * R,
+        "tile_sort": 8 * R + 12 * R,
         "blend_fwd": 44 * R + 24 * N + 8 * Tn,
         "bwd_zero": 48 * P,
         "blend_bwd": 44 * R + 28 * N + 8 * Tn + 40 * R,

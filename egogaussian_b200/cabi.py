@@ -59,7 +59,7 @@ class EgsBackwardArgs(C.Structure):
 
 class EgsAdamGroup(C.Structure):
     _fields_ = [("param", c_float_p), ("grad", c_float_p), ("exp_avg", c_float_p),
-                ("exp_avg_sq", c_float_p), ("n", C.c_longlong), ("lr", C.c_float), ("step", C.c_int)]
+                ("exp_avg_sq", c_float_p), ("n", C.c_longlong), ("lr", C.c_double), ("step", C.c_int)]
 
 
 class EgsGeomView(C.Structure):
@@ -110,14 +110,14 @@ def load() -> C.CDLL:
     lib.egs_mark_visible.restype = C.c_int
     lib.egs_mark_visible.argtypes = [C.c_int, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]
     lib.egs_adam_step.restype = C.c_int
-    lib.egs_adam_step.argtypes = [C.POINTER(EgsAdamGroup), C.c_int, C.c_float, C.c_float, C.c_float, C.c_void_p]
+    lib.egs_adam_step.argtypes = [C.POINTER(EgsAdamGroup), C.c_int, C.c_double, C.c_double, C.c_double, C.c_void_p]
     lib.egs_se3_apply.restype = C.c_int
     lib.egs_se3_apply.argtypes = [C.c_int, C.c_void_p, C.c_void_p, C.c_int, C.c_void_p, C.c_void_p,
                                   C.c_void_p, C.c_void_p, C.c_void_p]
     lib.egs_adam_se3_step.restype = C.c_int
     lib.egs_adam_se3_step.argtypes = [C.c_int, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p,
-                                      C.c_int, C.c_void_p, C.c_float, C.c_int, C.c_float, C.c_float,
-                                      C.c_float, C.c_void_p]
+                                      C.c_int, C.c_void_p, C.c_double, C.c_int, C.c_double, C.c_double,
+                                      C.c_double, C.c_void_p]
     lib.egs_geom_view.restype = C.c_int
     lib.egs_geom_view.argtypes = [C.c_void_p, C.c_int, C.POINTER(EgsGeomView)]
     lib.egs_binning_view.restype = C.c_int

@@ -79,7 +79,7 @@ __global__ void __launch_bounds__(256) adam_multi_kernel(const AdamLaunch L) {
 
 static bool aligned16(const void* p) { return (reinterpret_cast<uintptr_t>(p) & 15u) == 0; }
 
-static int adam_launch(const EgsAdamGroup* groups, int n_groups, float beta1, float beta2, float eps,
+static int adam_launch(const EgsAdamGroup* groups, int n_groups, double beta1, double beta2, double eps,
                        cudaStream_t stream) {
   if (n_groups < 0 || n_groups > EGS_ADAM_MAX_GROUPS || (n_groups > 0 && !groups)) {
     set_error("egs_adam_step: n_groups must be in [0, %d]", EGS_ADAM_MAX_GROUPS);
@@ -100,19 +100,19 @@ static int adam_launch(const EgsAdamGroup* groups, int n_groups, float beta1, fl
     d.first_chunk = chunks;
     chunks += (s.n + 3) / 4;
     // scalar prologue in double like torch's python-side bias corrections
-    const double bc1 = 1.0 - pow((double)beta1, (double)s.step);
-    const double bc2 = 1.0 - pow((double)beta2, (double)s.step);
-    d.neg_step_size = (float)(-((double)s.lr / bc1));
+    const double bc1 = 1.0 - pow(beta1, (double)s.step);
+    const double bc2 = 1.0 - pow(beta2, (double)s.step);
+    d.neg_step_size = (float)(-(s.lr / bc1));
     d.bc2_sqrt = (float)sqrt(bc2);
     d.inv_bc2_sqrt = (float)(1.0 / sqrt(bc2));
     d.vec_ok = aligned16(s.param) && aligned16(s.grad) && aligned16(s.exp_avg) && aligned16(s.exp_avg_sq);
   }
   if (L.n_groups == 0) return EGS_OK;
   L.total_chunks = chunks;
-  L.one_minus_b1 = (float)(1.0 - (double)beta1);
-  L.b2 = beta2;
-  L.one_minus_b2 = (float)(1.0 - (double)beta2);
-  L.eps = eps;
+  L.one_minus_b1 = (float)(1.0 - beta1);
+  L.b2 = (float)beta2;
+  L.one_minus_b2 = (float)(1.0 - beta2);
+  L.eps = (float)eps;
   long long blocks = (chunks + 255) / 256;
   const long long cap = 148LL * 16;
   if (blocks > cap) blocks = cap;
@@ -189,8 +189,8 @@ adam_se3_kernel(int P, float* __restrict__ xyz, const float* __restrict__ grad, 
 
 }  // namespace egs
 
-extern "C" int egs_adam_step(const EgsAdamGroup* groups, int n_groups, float beta1, float beta2,
-                             float eps, void* stream) {
+extern "C" int egs_adam_step(const EgsAdamGroup* groups, int n_groups, double beta1, double beta2,
+                             double eps, void* stream) {
   return egs::adam_launch(groups, n_groups, beta1, beta2, eps, static_cast<cudaStream_t>(stream));
 }
 
@@ -212,21 +212,21 @@ extern "C" int egs_se3_apply(int P, const float* xyz, const int* is_object, int 
 
 extern "C" int egs_adam_se3_step(int P, float* xyz, const float* grad_moved, float* exp_avg,
                                  float* exp_avg_sq, const int* is_object, int which_object,
-                                 const float* Rt, float lr, int step, float beta1, float beta2,
-                                 float eps, void* stream) {
+                                 const float* Rt, double lr, int step, double beta1, double beta2,
+                                 double eps, void* stream) {
   if (P < 0 || step < 1 || (P > 0 && (!xyz || !grad_moved || !exp_avg || !exp_avg_sq || !is_object || !Rt))) {
     egs::set_error("egs_adam_se3_step: NULL argument or step < 1");
     return EGS_ERR_INVALID_ARGUMENT;
   }
   if (P == 0) return EGS_OK;
-  const double bc1 = 1.0 - pow((double)beta1, (double)step);
-  const double bc2 = 1.0 - pow((double)beta2, (double)step);
+  const double bc1 = 1.0 - pow(beta1, (double)step);
+  const double bc2 = 1.0 - pow(beta2, (double)step);
   cudaStream_t st = static_cast<cudaStream_t>(stream);
   egs::StageTimer timer(st, egs::ST_ADAM);
   egs::adam_se3_kernel<<<(P + 255) / 256, 256, 0, st>>>(
       P, xyz, grad_moved, exp_avg, exp_avg_sq, is_object, which_object, Rt,
-      (float)(1.0 - (double)beta1), beta2, (float)(1.0 - (double)beta2), eps,
-      (float)(-((double)lr / bc1)), (float)sqrt(bc2));
+      (float)(1.0 - beta1), (float)beta2, (float)(1.0 - beta2), (float)eps,
+      (float)(-(lr / bc1)), (float)sqrt(bc2));
   EGS_AFTER_LAUNCH(st, false);
   return EGS_OK;
 }

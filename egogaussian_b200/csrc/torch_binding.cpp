@@ -244,10 +244,10 @@ void adam_step(std::vector<torch::Tensor> params, std::vector<torch::Tensor> gra
     g[i].exp_avg = exp_avgs[i].data_ptr<float>();
     g[i].exp_avg_sq = exp_avg_sqs[i].data_ptr<float>();
     g[i].n = params[i].numel();
-    g[i].lr = (float)lrs[i];
+    g[i].lr = lrs[i];
     g[i].step = (int)steps[i];
   }
-  check(egs_adam_step(g, (int)n, (float)beta1, (float)beta2, (float)eps,
+  check(egs_adam_step(g, (int)n, beta1, beta2, eps,
                       at::cuda::getCurrentCUDAStream().stream()),
         "egs_adam_step");
 }
@@ -292,8 +292,8 @@ void adam_se3_step(torch::Tensor xyz, const torch::Tensor& grad, torch::Tensor e
   auto rt = Rt.contiguous();
   check(egs_adam_se3_step((int)xyz.size(0), xyz.data_ptr<float>(), grad.data_ptr<float>(),
                           exp_avg.data_ptr<float>(), exp_avg_sq.data_ptr<float>(), is_object.data_ptr<int>(),
-                          which, rt.data_ptr<float>(), (float)lr, (int)step, (float)beta1, (float)beta2,
-                          (float)eps, at::cuda::getCurrentCUDAStream().stream()),
+                          which, rt.data_ptr<float>(), lr, (int)step, beta1, beta2,
+                          eps, at::cuda::getCurrentCUDAStream().stream()),
         "egs_adam_se3_step");
 }
 

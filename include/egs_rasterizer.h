@@ -147,20 +147,21 @@ int egs_mark_visible(int P, const float* means3D, const float* viewmatrix,
 /* One Adam parameter group: param/grad/exp_avg/exp_avg_sq are device [n] fp32. Follows
  * torch.optim.Adam(lr, betas, eps) with bias correction, no weight decay, no amsgrad, as
  * configured at scene/gaussian_model.py:198 (eps = 1e-15). `step` is the 1-based step count
- * AFTER this update (torch increments before use). */
+ * AFTER this update (torch increments before use). lr, the betas and eps are doubles because
+ * torch derives 1-beta and the bias corrections in double before rounding to fp32. */
 typedef struct EgsAdamGroup {
   float* param;
   const float* grad;
   float* exp_avg;
   float* exp_avg_sq;
   long long n;
-  float lr;
+  double lr;
   int step;
 } EgsAdamGroup;
 
 /* Fused multi-group Adam: one launch for all groups (host array of up to EGS_ADAM_MAX_GROUPS). */
 #define EGS_ADAM_MAX_GROUPS 16
-int egs_adam_step(const EgsAdamGroup* groups, int n_groups, float beta1, float beta2, float eps,
+int egs_adam_step(const EgsAdamGroup* groups, int n_groups, double beta1, double beta2, double eps,
                   void* stream);
 
 /* Rigid SE(3) transform of object Gaussians (scene/gaussian_model.py:939-986,
@@ -174,8 +175,8 @@ int egs_se3_apply(int P, const float* xyz, const int* is_object, int which_objec
 /* Fused "pull gradient back through the rigid map + Adam on canonical xyz" (SURVEY.md 8a A-24):
  * g_canonical = R^T * g_moved for object rows, then the Adam update of egs_adam_step. */
 int egs_adam_se3_step(int P, float* xyz, const float* grad_moved, float* exp_avg, float* exp_avg_sq,
-                      const int* is_object, int which_object, const float* Rt, float lr, int step,
-                      float beta1, float beta2, float eps, void* stream);
+                      const int* is_object, int which_object, const float* Rt, double lr, int step,
+                      double beta1, double beta2, double eps, void* stream);
 
 /* ---- introspection (tests / bench) ----------------------------------------------------- */
 
@@ -188,7 +189,7 @@ typedef struct EgsGeomView {
   const float* rgb_depth;      /* [P,4] rgb + depth packed for the blend kernels */
   const unsigned char* clamped;/* [P] bit c set = channel c clamped */
   const uint32_t* tiles_touched; /* [P] */
-  const uint32_t* point_offsets; /* [P] inclusive scan */
+  const uint32_t* point_offsets; /* [P] inclusive scan; only filled on the radix-sort path */
 } EgsGeomView;
 typedef struct EgsBinningView {
   const uint64_t* keys_sorted;   /* [R] */
