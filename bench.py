@@ -115,18 +115,17 @@ def algorithmic_bytes(P, V, R, N, Tn, M, D, geom, passes):
     c = 12 * (D + 1) ** 2
     g = 28 if geom == "scale_rot" else 24
     cov_store = 24 if geom == "scale_rot" else 0
+    # binning: packed single-word sort (9-bit digits) when tile|depth|index fits 64 bits, else pairs
+    ib, tb = max(P - 1, 1).bit_length(), Tn.bit_length()
+    packed = ib + 32 + tb <= 64
+    pk_passes = (32 + tb + 8) // 9
     return {
         "preprocess_fwd": 20 * P + V * (g + 4 + c + 4 + 8 + 16 + 12 + 3 + cov_store),
         "scan": 8 * P,
-        "duplicate_keys": 20 * P + 12 * R,
+        "duplicate_keys": 20 * P + (8 if packed else 12) * R,
         "sort_histogram": 8 * R,
-        "sort_passes": R * 24 * passes,
+        "sort_passes": (R * 16 * (pk_passes - 1) + R * 20) if packed else R * 24 * passes,
         "tile_ranges": 8 * R + 16 * Tn,
-        # tile-bucket path: counts -> ranges; scatter one 8-byte word per instance;
-        # per-tile sort reads it once and writes the index list + the 64-bit keys
-        "tile_scan": 12 * Tn,
-        "tile_scatter": 20 * P + 8 * R,
-        "tile_sort": 8 * R + 12 * R,
         "blend_fwd": 44 * R + 24 * N + 8 * Tn,
         "bwd_zero": 48 * P,
         "blend_bwd": 44 * R + 28 * N + 8 * Tn + 40 * R,

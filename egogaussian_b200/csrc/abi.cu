@@ -76,8 +76,7 @@ void profile_end(cudaStream_t stream, void* token) {
 
 static const char* kStageNames[ST_COUNT] = {"preprocess_fwd", "scan", "duplicate_keys", "sort_histogram",
                                             "sort_passes", "tile_ranges", "blend_fwd", "bwd_zero",
-                                            "blend_bwd", "preprocess_bwd", "adam", "se3", "tile_scan",
-                                            "tile_scatter", "tile_sort"};
+                                            "blend_bwd", "preprocess_bwd", "adam", "se3"};
 
 static int check_pairs(const char* who, const void* shs, const void* colors, const void* scales,
                        const void* rotations, const void* cov) {
@@ -151,21 +150,19 @@ extern "C" int egs_forward(const EgsForwardArgs* args, void* stream_v, int* num_
   const GeomPtrs g(geom_mem, (size_t)a.P);
   const ImagePtrs im(img_mem, a.width, a.height);
 
-  // per-tile instance counters, scatter cursors and the (num_rendered, max tile) pair start at 0
-  EGS_CUDA_TRY(cudaMemsetAsync(im.tile_counts, 0, im.counters_bytes, stream));
-  if (int rc = launch_preprocess_forward(a, g, im.tile_counts, stream)) return rc;
-  if (int rc = launch_tile_scan(im, a.width, a.height, stream, a.debug)) return rc;
+  if (int rc = launch_preprocess_forward(a, g, stream)) return rc;
+  if (int rc = launch_scan_tiles(g, a.P, stream, a.debug)) return rc;
 
   // the one device->host read per forward (the reference's is rasterizer_impl.cu:281-282)
-  uint32_t meta_host[2] = {0, 0};
-  EGS_CUDA_TRY(cudaMemcpyAsync(meta_host, im.bin_meta, sizeof(meta_host), cudaMemcpyDeviceToHost, stream));
+  uint32_t R_host = 0;
+  EGS_CUDA_TRY(cudaMemcpyAsync(&R_host, g.point_offsets + (a.P - 1), sizeof(uint32_t),
+                               cudaMemcpyDeviceToHost, stream));
   EGS_CUDA_TRY(cudaStreamSynchronize(stream));
-  if (meta_host[0] >= (1u << 30)) {
-    set_error("egs_forward: num_rendered %u exceeds the supported 2^30", meta_host[0]);
+  if (R_host >= (1u << 30)) {
+    set_error("egs_forward: num_rendered %u exceeds the supported 2^30", R_host);
     return EGS_ERR_TOO_LARGE;
   }
-  const int R = (int)meta_host[0];
-  const int max_tile = (int)meta_host[1];
+  const int R = (int)R_host;
 
   void* bin_mem = a.binning_alloc(a.binning_ctx, egs_binning_bytes(R, a.width, a.height));
   if (!bin_mem) {
@@ -173,19 +170,17 @@ extern "C" int egs_forward(const EgsForwardArgs* args, void* stream_v, int* num_
     return EGS_ERR_ALLOC;
   }
   const BinningPtrs b(bin_mem, (size_t)R);
-  // EGS_SORT=radix forces the general path (tests); it is also taken when a tile's list is too
-  // long for the shared-memory sorter
+  // Packed single-word sort when (tile | depth | index) fits 64 bits, else the pair sort;
+  // EGS_SORT=pairs forces the general path (tests).
   const char* force = getenv("EGS_SORT");
-  const bool radix = max_tile > TILE_SORT_MAX || (force && strcmp(force, "radix") == 0);
-  if (radix) {
-    if (int rc = launch_scan_tiles(g, a.P, stream, a.debug)) return rc;
+  const bool pairs = !packed_path_fits(a.P, a.width, a.height) || (force && strcmp(force, "pairs") == 0);
+  if (pairs) {
     if (int rc = launch_binning(g, b, im, a.radii, a.P, R, a.width, a.height, stream, a.debug)) return rc;
   } else {
-    if (int rc = launch_tile_binning(g, b, im, a.radii, a.P, R, max_tile, a.width, a.height, stream, a.debug))
-      return rc;
+    if (int rc = launch_binning_packed(g, b, im, a.radii, a.P, R, a.width, a.height, stream, a.debug)) return rc;
   }
 
-  const uint32_t* point_list = b.vals[sort_passes(a.width, a.height) & 1];
+  const uint32_t* point_list = b.vals[0];
   if (int rc = launch_blend_forward(a, g, point_list, im, stream)) return rc;
   *num_rendered = R;
   return EGS_OK;
@@ -227,7 +222,7 @@ extern "C" int egs_backward(const EgsBackwardArgs* args, void* stream_v) {
   }
   if (a.num_rendered > 0) {
     const BinningPtrs b(const_cast<void*>(a.binning_buffer), (size_t)a.num_rendered);
-    const uint32_t* point_list = b.vals[sort_passes(a.width, a.height) & 1];
+    const uint32_t* point_list = b.vals[0];
     if (int rc = launch_blend_backward(a, g, point_list, im, s, stream)) return rc;
   }
   return launch_preprocess_backward(a, g, s, stream);
@@ -259,9 +254,9 @@ extern "C" int egs_geom_view(const void* geom_buffer, int P, EgsGeomView* out) {
 extern "C" int egs_binning_view(const void* binning_buffer, int R, int W, int H, EgsBinningView* out) {
   if (!binning_buffer || !out || R < 0) return EGS_ERR_INVALID_ARGUMENT;
   const BinningPtrs b(const_cast<void*>(binning_buffer), (size_t)R);
-  const int sel = sort_passes(W, H) & 1;
-  out->keys_sorted = b.keys[sel];
-  out->values_sorted = b.vals[sel];
+  (void)W; (void)H;
+  out->keys_sorted = b.keys[0];
+  out->values_sorted = b.vals[0];
   return EGS_OK;
 }
 

@@ -300,6 +300,14 @@ tile_ranges_kernel(int n, const uint64_t* __restrict__ keys, uint2* __restrict__
   if (idx == n - 1) ranges[cur].y = n;
 }
 
+int launch_tile_ranges(int R, const uint64_t* sorted_keys, const ImagePtrs& im, cudaStream_t stream,
+                       bool debug) {
+  StageTimer timer(stream, ST_RANGES);
+  tile_ranges_kernel<<<(R + 255) / 256, 256, 0, stream>>>(R, sorted_keys, im.ranges);
+  EGS_AFTER_LAUNCH(stream, debug);
+  return EGS_OK;
+}
+
 template <int PASSES>
 static void launch_hist(const uint64_t* keys, int n, int end_bit, uint32_t* hist,
                         cudaStream_t stream) {
@@ -314,25 +322,27 @@ int launch_binning(const GeomPtrs& g, const BinningPtrs& b, const ImagePtrs& im,
   EGS_CUDA_TRY(cudaMemsetAsync(im.ranges, 0, (size_t)gx * gy * sizeof(uint2), stream));
   if (R == 0) return EGS_OK;
 
+  const int end_bit = 32 + tile_id_bits((uint32_t)(gx * gy));
+  const int passes = (end_bit + SORT_RADIX_BITS - 1) / SORT_RADIX_BITS;
+  // ping-pong so that the sorted lists always end in keys[0] / vals[0]
+  const int first = passes & 1;
   {
     StageTimer timer(stream, ST_DUPLICATE);
     duplicate_keys_kernel<<<(P + 255) / 256, 256, 0, stream>>>(P, g.means2D, g.depths,
-                                                               g.point_offsets, radii, b.keys[0],
-                                                               b.vals[0], gx, gy);
+                                                               g.point_offsets, radii, b.keys[first],
+                                                               b.vals[first], gx, gy);
     EGS_AFTER_LAUNCH(stream, debug);
   }
 
-  const int end_bit = 32 + tile_id_bits((uint32_t)(gx * gy));
-  const int passes = (end_bit + SORT_RADIX_BITS - 1) / SORT_RADIX_BITS;
   {
     StageTimer timer(stream, ST_SORT_HIST);
     EGS_CUDA_TRY(cudaMemsetAsync(b.hist, 0, b.zero_bytes, stream));
     switch (passes) {
-      case 4: launch_hist<4>(b.keys[0], R, end_bit, b.hist, stream); break;
-      case 5: launch_hist<5>(b.keys[0], R, end_bit, b.hist, stream); break;
-      case 6: launch_hist<6>(b.keys[0], R, end_bit, b.hist, stream); break;
-      case 7: launch_hist<7>(b.keys[0], R, end_bit, b.hist, stream); break;
-      default: launch_hist<8>(b.keys[0], R, end_bit, b.hist, stream); break;
+      case 4: launch_hist<4>(b.keys[first], R, end_bit, b.hist, stream); break;
+      case 5: launch_hist<5>(b.keys[first], R, end_bit, b.hist, stream); break;
+      case 6: launch_hist<6>(b.keys[first], R, end_bit, b.hist, stream); break;
+      case 7: launch_hist<7>(b.keys[first], R, end_bit, b.hist, stream); break;
+      default: launch_hist<8>(b.keys[first], R, end_bit, b.hist, stream); break;
     }
     EGS_AFTER_LAUNCH(stream, debug);
     sort_scan_hist_kernel<<<passes, SORT_RADIX, 0, stream>>>(b.hist);
@@ -344,18 +354,14 @@ int launch_binning(const GeomPtrs& g, const BinningPtrs& b, const ImagePtrs& im,
     for (int p = 0; p < passes; ++p) {
       const int shift = p * SORT_RADIX_BITS;
       const int width = (end_bit - shift) < SORT_RADIX_BITS ? (end_bit - shift) : SORT_RADIX_BITS;
-      const int src = p & 1, dst = src ^ 1;
+      const int src = (p + first) & 1, dst = src ^ 1;
       sort_onesweep_kernel<<<blocks, SORT_THREADS, 0, stream>>>(
           b.keys[src], b.vals[src], b.keys[dst], b.vals[dst], R, shift, (1u << width) - 1u,
           b.hist + p * SORT_RADIX, b.ticket + p, b.status + (size_t)p * b.sort_blocks * SORT_RADIX);
       EGS_AFTER_LAUNCH(stream, debug);
     }
   }
-  StageTimer timer(stream, ST_RANGES);
-  const uint64_t* sorted_keys = b.keys[passes & 1];
-  tile_ranges_kernel<<<(R + 255) / 256, 256, 0, stream>>>(R, sorted_keys, im.ranges);
-  EGS_AFTER_LAUNCH(stream, debug);
-  return EGS_OK;
+  return launch_tile_ranges(R, b.keys[0], im, stream, debug);
 }
 
 }  // namespace egs

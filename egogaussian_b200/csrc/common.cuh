@@ -47,8 +47,7 @@ inline size_t align_up(size_t x, size_t a = 256) { return (x + a - 1) / a * a; }
 // Stage ids of the built-in event timing (egs_profile_* in the header).
 enum Stage {
   ST_PREPROCESS = 0, ST_SCAN, ST_DUPLICATE, ST_SORT_HIST, ST_SORT_PASSES, ST_RANGES, ST_BLEND_FWD,
-  ST_BWD_ZERO, ST_BLEND_BWD, ST_PREPROCESS_BWD, ST_ADAM, ST_SE3, ST_TILE_SCAN, ST_TILE_SCATTER,
-  ST_TILE_SORT, ST_COUNT
+  ST_BWD_ZERO, ST_BLEND_BWD, ST_PREPROCESS_BWD, ST_ADAM, ST_SE3, ST_COUNT
 };
 static_assert(ST_COUNT <= EGS_PROFILE_STAGES, "grow EGS_PROFILE_STAGES");
 bool profiling_enabled();
@@ -130,6 +129,8 @@ constexpr int SORT_THREADS = 256;
 constexpr int SORT_ITEMS = 16;
 constexpr int SORT_TILE = SORT_THREADS * SORT_ITEMS;
 constexpr int SORT_MAX_PASSES = 8;
+// status / histogram words per sort block: 8 passes x 256 digits (pair sort) or 6 x 512 (packed sort)
+constexpr int SORT_STATUS_WORDS = 3072;
 
 inline int sort_passes(int W, int H) {
   int bits = 32 + tile_id_bits((uint32_t)(tiles_x(W) * tiles_y(H)));
@@ -148,9 +149,9 @@ struct BinningLayout {
     vals[0] = take(R * 4);
     vals[1] = take(R * 4);
     // everything from `hist` to the end is zeroed with one memset per forward
-    hist = take(SORT_MAX_PASSES * SORT_RADIX * 4);
+    hist = take(SORT_STATUS_WORDS * 4);
     ticket = take(SORT_MAX_PASSES * 4);
-    status = take(SORT_MAX_PASSES * sort_blocks * SORT_RADIX * 4);
+    status = take(sort_blocks * SORT_STATUS_WORDS * 4);
     total = o + 256;
   }
 };
@@ -179,17 +180,12 @@ struct BinningPtrs {
 };
 
 struct ImageLayout {
-  size_t n_contrib, ranges, tile_counts, tile_cursor, bin_meta, total;
+  size_t n_contrib, ranges, total;
   ImageLayout(int W, int H) {
     size_t o = 0;
     auto take = [&](size_t bytes) { size_t r = o; o = align_up(o + bytes); return r; };
-    const size_t tn = (size_t)tiles_x(W) * tiles_y(H);
     n_contrib = take((size_t)W * H * 4);
-    ranges = take(tn * 8);
-    // tile_counts, tile_cursor and bin_meta are contiguous: one memset clears all three
-    tile_counts = take(tn * 4);
-    tile_cursor = take(tn * 4);
-    bin_meta = take(16);
+    ranges = take((size_t)tiles_x(W) * tiles_y(H) * 8);
     total = o + 256;
   }
 };
@@ -197,19 +193,11 @@ struct ImageLayout {
 struct ImagePtrs {
   uint32_t* n_contrib;
   uint2* ranges;
-  uint32_t* tile_counts;   // instances per tile (filled by preprocess with reductions)
-  uint32_t* tile_cursor;   // scatter cursors of the tile-bucket path
-  uint32_t* bin_meta;      // [0] num_rendered, [1] largest tile count
-  size_t counters_bytes;   // bytes from tile_counts to the end of bin_meta
   ImagePtrs(void* base, int W, int H) {
     ImageLayout L(W, H);
     char* b = static_cast<char*>(base);
     n_contrib = reinterpret_cast<uint32_t*>(b + L.n_contrib);
     ranges = reinterpret_cast<uint2*>(b + L.ranges);
-    tile_counts = reinterpret_cast<uint32_t*>(b + L.tile_counts);
-    tile_cursor = reinterpret_cast<uint32_t*>(b + L.tile_cursor);
-    bin_meta = reinterpret_cast<uint32_t*>(b + L.bin_meta);
-    counters_bytes = L.bin_meta + 16 - L.tile_counts;
   }
 };
 
@@ -227,14 +215,14 @@ struct BackwardScratch {
 // ---------------------------------------------------------------------------------------------
 // stage entry points (each enqueues kernels on `stream`; return EgsStatus)
 // ---------------------------------------------------------------------------------------------
-int launch_preprocess_forward(const EgsForwardArgs& a, const GeomPtrs& g, uint32_t* tile_counts,
-                              cudaStream_t stream);
-// tile-bucket binning (binning_tiles.cu): ranges from the per-tile counts, then scatter + per-tile sort
-constexpr int TILE_SORT_MAX = 16384;   // largest tile list the shared-memory sorter takes
-int launch_tile_scan(const ImagePtrs& im, int W, int H, cudaStream_t stream, bool debug);
-int launch_tile_binning(const GeomPtrs& g, const BinningPtrs& b, const ImagePtrs& im, const int* radii,
-                        int P, int R, int max_tile, int W, int H, cudaStream_t stream, bool debug);
+int launch_preprocess_forward(const EgsForwardArgs& a, const GeomPtrs& g, cudaStream_t stream);
 int launch_scan_tiles(const GeomPtrs& g, int P, cudaStream_t stream, bool debug);
+// packed-word fast path (binning_packed.cu) and the shared range kernel
+bool packed_path_fits(int P, int W, int H);
+int launch_binning_packed(const GeomPtrs& g, const BinningPtrs& b, const ImagePtrs& im, const int* radii,
+                          int P, int R, int W, int H, cudaStream_t stream, bool debug);
+int launch_tile_ranges(int R, const uint64_t* sorted_keys, const ImagePtrs& im, cudaStream_t stream,
+                       bool debug);
 int launch_binning(const GeomPtrs& g, const BinningPtrs& b, const ImagePtrs& im, const int* radii,
                    int P, int R, int W, int H, cudaStream_t stream, bool debug);
 int launch_blend_forward(const EgsForwardArgs& a, const GeomPtrs& g, const uint32_t* point_list,

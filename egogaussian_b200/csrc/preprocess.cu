@@ -117,8 +117,7 @@ preprocess_forward_kernel(int P, int D, int M, const float* __restrict__ means3D
                           int* __restrict__ radii, float2* __restrict__ means2D,
                           float* __restrict__ depths, float4* __restrict__ conic_opacity,
                           float4* __restrict__ rgb_depth, unsigned char* __restrict__ clamped,
-                          uint32_t* __restrict__ tiles_touched, uint32_t* __restrict__ tile_counts,
-                          int prefiltered,
+                          uint32_t* __restrict__ tiles_touched, int prefiltered,
                           int* __restrict__ prefilter_fault) {
   __shared__ float s_view[16], s_proj[16], s_cam[3];
   if (threadIdx.x < 16) {
@@ -187,11 +186,6 @@ preprocess_forward_kernel(int P, int D, int M, const float* __restrict__ means3D
         rgb_depth[idx] = make_float4(rgb.x, rgb.y, rgb.z, p_view.z);
         radius_out = (int)my_radius;
         tiles_out = n_tiles;
-        // per-tile instance counts for the tile-bucket binning (reductions, no return value)
-        if (tile_counts != nullptr) {
-          for (uint32_t y = lo.y; y < hi.y; ++y)
-            for (uint32_t x = lo.x; x < hi.x; ++x) atomicAdd(&tile_counts[y * (uint32_t)grid_x + x], 1u);
-        }
       }
     }
   }
@@ -209,8 +203,7 @@ mark_visible_kernel(int P, const float* __restrict__ means3D, const float* __res
   present[idx] = pv.z > 0.2f ? 1 : 0;
 }
 
-int launch_preprocess_forward(const EgsForwardArgs& a, const GeomPtrs& g, uint32_t* tile_counts,
-                              cudaStream_t stream) {
+int launch_preprocess_forward(const EgsForwardArgs& a, const GeomPtrs& g, cudaStream_t stream) {
   const int P = a.P;
   const float focal_y = a.height / (2.0f * a.tan_fovy);
   const float focal_x = a.width / (2.0f * a.tan_fovx);
@@ -221,7 +214,7 @@ int launch_preprocess_forward(const EgsForwardArgs& a, const GeomPtrs& g, uint32
       a.shs, a.cov3D_precomp, a.colors_precomp, a.viewmatrix, a.projmatrix, a.campos, a.width,
       a.height, a.tan_fovx, a.tan_fovy, focal_x, focal_y, tiles_x(a.width), tiles_y(a.height),
       a.radii, g.means2D, g.depths, g.conic_opacity, g.rgb_depth, g.clamped, g.tiles_touched,
-      tile_counts, a.prefiltered, nullptr);
+      a.prefiltered, nullptr);
   EGS_AFTER_LAUNCH(stream, a.debug);
   return EGS_OK;
 }

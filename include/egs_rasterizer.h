@@ -189,7 +189,7 @@ typedef struct EgsGeomView {
   const float* rgb_depth;      /* [P,4] rgb + depth packed for the blend kernels */
   const unsigned char* clamped;/* [P] bit c set = channel c clamped */
   const uint32_t* tiles_touched; /* [P] */
-  const uint32_t* point_offsets; /* [P] inclusive scan; only filled on the radix-sort path */
+  const uint32_t* point_offsets; /* [P] inclusive scan */
 } EgsGeomView;
 typedef struct EgsBinningView {
   const uint64_t* keys_sorted;   /* [R] */

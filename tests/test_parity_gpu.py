@@ -262,9 +262,10 @@ def test_full_size_properties(built, cuda_device):
     assert bool(torch.all(g1["means3D"][f1.radii == 0] == 0))
 
 
-def test_radix_fallback_equals_tile_bucket_path(built, cuda_device, monkeypatch):
-    """The general radix-sort path (taken for tile lists beyond the shared-memory sorter, forced
-    here with EGS_SORT=radix) and the default tile-bucket path give identical lists and images."""
+def test_pair_sort_fallback_equals_packed_path(built, cuda_device, monkeypatch):
+    """The general (u64 key, u32 value) pair sort -- taken when tile | depth | index does not fit one
+    64-bit word, forced here with EGS_SORT=pairs -- and the default packed-word sort give identical
+    lists and images."""
     from egogaussian_b200 import cabi, scenes
     dev = cuda_device
     sc = scenes.make_scene(60_000, 640, 360, sh_degree=1, seed=77).to(dev)
@@ -274,14 +275,14 @@ def test_radix_fallback_equals_tile_bucket_path(built, cuda_device, monkeypatch)
               image_height=360, image_width=640, sh_degree=1, shs=sc.shs, cov3D_precomp=sc.cov3D())
     monkeypatch.delenv("EGS_SORT", raising=False)
     a = cabi.forward(**kw)
-    monkeypatch.setenv("EGS_SORT", "radix")
+    monkeypatch.setenv("EGS_SORT", "pairs")
     b = cabi.forward(**kw)
     assert a.num_rendered == b.num_rendered > 0
     av, bv = a.binning_view(), b.binning_view()
     assert torch.equal(av["keys"], bv["keys"]) and torch.equal(av["values"], bv["values"])
     assert torch.equal(a.image_view()["ranges"], b.image_view()["ranges"])
     assert torch.equal(a.color, b.color) and torch.equal(a.radii, b.radii)
-    gv = b.geom_view()
+    gv = a.geom_view()
     assert torch.equal(gv["point_offsets"].to(torch.int64), torch.cumsum(gv["tiles_touched"].to(torch.int64), 0))
 
 
