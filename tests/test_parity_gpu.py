@@ -304,8 +304,9 @@ def test_adam_and_se3(built, cuda_device):
             p.grad = g.clone()
         opt.step()
         _C.adam_step(ours, grads, m, v, lrs, [step] * len(ours), 0.9, 0.999, 1e-15)
-        for a, b in zip(ours, ref_p):
-            assert torch.allclose(a, b.detach(), rtol=2e-6, atol=1e-8)
+        # each step moves a parameter by about lr; fp32 rounding of that update is ~1e-6 of it
+        for a, b, lr in zip(ours, ref_p, lrs):
+            assert torch.allclose(a, b.detach(), rtol=1e-6, atol=4e-6 * lr * step), (lr, step)
     # rigid transform and its pull-back
     P = 4000
     xyz = torch.randn(P, 3, device=dev)
@@ -335,4 +336,4 @@ def test_adam_and_se3(built, cuda_device):
     p = xyz.clone()
     m1, v1 = torch.zeros_like(p), torch.zeros_like(p)
     _C.adam_se3_step(p, g_moved, m1, v1, is_obj, 1, Rt, 1.6e-4, 1, 0.9, 0.999, 1e-15)
-    assert torch.allclose(p, p_ref.detach(), rtol=2e-6, atol=1e-8)
+    assert torch.allclose(p, p_ref.detach(), rtol=1e-6, atol=4e-6 * 1.6e-4)
