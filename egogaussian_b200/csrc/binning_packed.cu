@@ -101,11 +101,22 @@ constexpr uint32_t PK_VALUE_MASK = (1u << 30) - 1u;
 struct PackedSmem {
   uint32_t warp_hist[PK_WARPS][PK_RADIX];   // 32 KB
   uint64_t exch[PK_TILE];                   // 32 KB
+  uint32_t count[PK_RADIX];                 // this block's digit histogram (published early)
   uint32_t digit_local[PK_RADIX];
   uint32_t digit_global[PK_RADIX];
   uint32_t warp_sums[PK_WARPS];
   uint32_t tile;
 };
+
+// status words carry flag and value together, so relaxed device-scope accesses are enough
+__device__ __forceinline__ uint32_t ld_status(const uint32_t* p) {
+  uint32_t v;
+  asm volatile("ld.relaxed.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+  return v;
+}
+__device__ __forceinline__ void st_status(uint32_t* p, uint32_t v) {
+  asm volatile("st.relaxed.gpu.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
+}
 
 template <bool LAST>
 __global__ void __launch_bounds__(PK_THREADS)
@@ -119,6 +130,7 @@ packed_onesweep_kernel(const uint64_t* __restrict__ in, uint64_t* __restrict__ o
   if (tid == 0) S.tile = atomicAdd(ticket, 1u);
 #pragma unroll
   for (int w = 0; w < PK_WARPS; ++w) S.warp_hist[w][tid] = 0;
+  S.count[tid] = 0;
   __syncthreads();
   const uint32_t tile = S.tile;
   const unsigned lt_mask = (1u << lane) - 1u;
@@ -132,6 +144,19 @@ packed_onesweep_kernel(const uint64_t* __restrict__ in, uint64_t* __restrict__ o
     const size_t g = warp_base + (size_t)i * 32 + lane;
     word[i] = g < (size_t)n ? in[g] : ~0ull;
   }
+  // 1. block histogram (unordered shared-memory atomics) and EARLY publication of the aggregate,
+  //    so that successors' look-backs find it while this block is still ranking
+#pragma unroll
+  for (int i = 0; i < PK_ITEMS; ++i) {
+    const size_t g = warp_base + (size_t)i * 32 + lane;
+    if (g < (size_t)n) atomicAdd(&S.count[(uint32_t)(word[i] >> shift) & digit_mask], 1u);
+  }
+  __syncthreads();
+  uint32_t* st = status_raw + (size_t)tile * PK_RADIX + tid;
+  const uint32_t block_count = S.count[tid];
+  if (tile != 0) st_status(st, PK_FLAG_AGG | block_count);
+
+  // 2. stable ranks inside each warp's contiguous segment
 #pragma unroll
   for (int i = 0; i < PK_ITEMS; ++i) {
     const size_t g = warp_base + (size_t)i * 32 + lane;
@@ -146,7 +171,7 @@ packed_onesweep_kernel(const uint64_t* __restrict__ in, uint64_t* __restrict__ o
   }
   __syncthreads();
 
-  // thread d owns digit d
+  // 3. thread d owns digit d: warp offsets, block-local start, cross-block look-back
   {
     const uint32_t d = tid;
     uint32_t run = 0;
@@ -156,8 +181,6 @@ packed_onesweep_kernel(const uint64_t* __restrict__ in, uint64_t* __restrict__ o
       S.warp_hist[w][d] = run;
       run += c;
     }
-    const uint32_t block_count = run;
-    // exclusive scan of block_count over the digits -> where digit d starts inside this block
     uint32_t incl = block_count;
 #pragma unroll
     for (int s = 1; s < 32; s <<= 1) {
@@ -171,21 +194,18 @@ packed_onesweep_kernel(const uint64_t* __restrict__ in, uint64_t* __restrict__ o
     const uint32_t local_start = woff + incl - block_count;
     S.digit_local[d] = local_start;
 
-    // decoupled look-back over the preceding blocks' status words of this digit
-    volatile uint32_t* st = status_raw + d;
     uint32_t excl = 0;
-    if (tile == 0) {
-      st[0] = PK_FLAG_PREFIX | block_count;
-    } else {
-      st[(size_t)tile * PK_RADIX] = PK_FLAG_AGG | block_count;
-      for (int t = (int)tile - 1;; --t) {
+    if (tile != 0) {
+      const uint32_t* prev = st - PK_RADIX;
+      for (;;) {
         uint32_t s;
-        do { s = st[(size_t)t * PK_RADIX]; } while ((s & (PK_FLAG_AGG | PK_FLAG_PREFIX)) == 0u);
+        do { s = ld_status(prev); } while ((s & (PK_FLAG_AGG | PK_FLAG_PREFIX)) == 0u);
         excl += s & PK_VALUE_MASK;
         if (s & PK_FLAG_PREFIX) break;
+        prev -= PK_RADIX;
       }
-      st[(size_t)tile * PK_RADIX] = PK_FLAG_PREFIX | (excl + block_count);
     }
+    st_status(st, PK_FLAG_PREFIX | (excl + block_count));
     S.digit_global[d] = digit_base[d] + excl - local_start;   // dst = digit_global[d] + local position
   }
   __syncthreads();

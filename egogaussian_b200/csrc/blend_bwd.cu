@@ -17,6 +17,9 @@
 //     reductions (red.global.add.v4.f32) into the 48-byte per-Gaussian record.
 #include "common.cuh"
 
+#include <stdlib.h>
+#include <string.h>
+
 namespace egs {
 
 constexpr int BWD_BATCH = 256;
@@ -243,14 +246,222 @@ blend_backward_kernel(const uint2* __restrict__ ranges, const uint32_t* __restri
   }
 }
 
+// ---------------------------------------------------------------------------------------------
+// v2: two pixels per thread, exp only for fragments that pass a log-domain test
+// ---------------------------------------------------------------------------------------------
+// Same arithmetic per fragment as above, reorganised for throughput:
+//   * 128 threads per tile, each owning the pixels (x, y) and (x, y + 4) of its warp's 8x8 block:
+//     a list entry costs 4 warp reductions per tile instead of 8, every staged entry is read from
+//     shared memory half as often, and the two pixel chains give the scheduler independent work;
+//   * whether a fragment contributes is decided without the exponential:
+//       alpha = o * exp(power) >= 1/255   <=>   power >= -log(255 * o) =: thr (staged per entry),
+//     so exp, the divide and everything after run only on warps where some lane contributes;
+//   * backward is tolerance-checked (1e-4 of the tensor maximum), not bit-checked, so the
+//     exponential and the reciprocal use the fast hardware approximations (ex2.approx, rcp.approx).
+constexpr int BWD2_THREADS = 128;
+constexpr int BWD2_BATCH = 128;
+
+struct PixelState {
+  float T, T_final, accum_rec[3], accum_depth, accum_alpha, last_alpha, last_color[3], last_depth;
+  float dL_dpixel[3], dL_ddepth, dL_dalpha, bg_dot;
+  float px, py;
+  uint32_t last;
+};
+
+__device__ __forceinline__ void pixel_init(PixelState& s, bool inside, uint32_t pix_id, unsigned px, unsigned py,
+                                           int W, int H, const float* __restrict__ alphas,
+                                           const uint32_t* __restrict__ n_contrib,
+                                           const float* __restrict__ dL_dpixels,
+                                           const float* __restrict__ dL_dpixel_depths,
+                                           const float* __restrict__ dL_dalphas, const float* bg) {
+  s.px = (float)px;
+  s.py = (float)py;
+  s.T_final = inside ? (1 - alphas[pix_id]) : 0;
+  s.T = s.T_final;
+  s.last = inside ? n_contrib[pix_id] : 0;
+  const size_t plane = (size_t)H * W;
+#pragma unroll
+  for (int ch = 0; ch < 3; ++ch) {
+    s.dL_dpixel[ch] = inside ? dL_dpixels[ch * plane + pix_id] : 0.f;
+    s.accum_rec[ch] = 0.f;
+    s.last_color[ch] = 0.f;
+  }
+  s.dL_ddepth = inside ? dL_dpixel_depths[pix_id] : 0.f;
+  s.dL_dalpha = inside ? dL_dalphas[pix_id] : 0.f;
+  s.accum_depth = s.accum_alpha = s.last_alpha = s.last_depth = 0.f;
+  s.bg_dot = bg[0] * s.dL_dpixel[0] + bg[1] * s.dL_dpixel[1] + bg[2] * s.dL_dpixel[2];
+}
+
+// one contributing fragment: advances the pixel's recurrences and adds its ten partial sums to q
+__device__ __forceinline__ void fragment_backward(PixelState& s, float dx, float dy, float power,
+                                                  const float4 a4, const float4 b4, const float4 c4,
+                                                  float ddelx_dx, float ddely_dy, float (&q)[10]) {
+  const float opac = a4.w;
+  const float G = __expf(power);
+  const float alpha = fminf(0.99f, opac * G);
+  const float rcp = __fdividef(1.f, 1.f - alpha);
+  s.T = s.T * rcp;
+  const float w = alpha * s.T;
+  float dL_dopa = 0.0f;
+  const float c[3] = {c4.x, c4.y, c4.z};
+#pragma unroll
+  for (int ch = 0; ch < 3; ++ch) {
+    s.accum_rec[ch] = s.last_alpha * s.last_color[ch] + (1.f - s.last_alpha) * s.accum_rec[ch];
+    s.last_color[ch] = c[ch];
+    dL_dopa += (c[ch] - s.accum_rec[ch]) * s.dL_dpixel[ch];
+    q[7 + ch] += w * s.dL_dpixel[ch];
+  }
+  const float c_d = b4.w;
+  s.accum_depth = s.last_alpha * s.last_depth + (1.f - s.last_alpha) * s.accum_depth;
+  s.last_depth = c_d;
+  dL_dopa += (c_d - s.accum_depth) * s.dL_ddepth;
+  q[3] += w * s.dL_ddepth;
+  s.accum_alpha = s.last_alpha + (1.f - s.last_alpha) * s.accum_alpha;
+  dL_dopa += (1 - s.accum_alpha) * s.dL_dalpha;
+  dL_dopa *= s.T;
+  s.last_alpha = alpha;
+  dL_dopa += (-s.T_final * rcp) * s.bg_dot;
+
+  const float dL_dG = opac * dL_dopa;
+  const float gdx = G * dx;
+  const float gdy = G * dy;
+  const float dG_ddelx = -gdx * b4.x - gdy * b4.y;
+  const float dG_ddely = -gdy * b4.z - gdx * b4.y;
+  q[0] += dL_dG * dG_ddelx * ddelx_dx;
+  q[1] += dL_dG * dG_ddely * ddely_dy;
+  q[4] += -0.5f * gdx * dx * dL_dG;
+  q[5] += -0.5f * gdx * dy * dL_dG;
+  q[6] += -0.5f * gdy * dy * dL_dG;
+  q[2] += G * dL_dopa;
+}
+
+__global__ void __launch_bounds__(BWD2_THREADS)
+blend_backward2_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__ point_list,
+                       int W, int H, int grid_x, const float* __restrict__ bg_color,
+                       const float2* __restrict__ means2D, const float4* __restrict__ conic_opacity,
+                       const float4* __restrict__ rgb_depth, const float* __restrict__ alphas,
+                       const uint32_t* __restrict__ n_contrib, const float* __restrict__ dL_dpixels,
+                       const float* __restrict__ dL_dpixel_depths, const float* __restrict__ dL_dalphas,
+                       float4* __restrict__ acc) {
+  __shared__ uint32_t s_id[BWD2_BATCH];
+  __shared__ float4 s_a[BWD2_BATCH];   // mean.x, mean.y, thr = -log(255 o), opacity
+  __shared__ float4 s_b[BWD2_BATCH];   // conic.x, conic.y, conic.z, depth
+  __shared__ float4 s_c[BWD2_BATCH];   // r, g, b, -
+  __shared__ float s_acc[BWD2_BATCH * ACC_PITCH];
+  __shared__ uint32_t s_max_contrib;
+
+  const unsigned tid = threadIdx.x;
+  const unsigned warp = tid >> 5, lane = tid & 31;
+  // 4 warps as 2x2 blocks of 8x8 pixels; a lane owns (lx, ly) and (lx, ly + 4) of its block
+  const unsigned bx = blockIdx.x * TILE_X + (warp & 1) * 8 + (lane & 7);
+  const unsigned by = blockIdx.y * TILE_Y + (warp >> 1) * 8 + (lane >> 3);
+  const float bg[3] = {bg_color[0], bg_color[1], bg_color[2]};
+  PixelState P0, P1;
+  {
+    const bool in0 = bx < (unsigned)W && by < (unsigned)H;
+    const bool in1 = bx < (unsigned)W && (by + 4) < (unsigned)H;
+    pixel_init(P0, in0, (uint32_t)W * by + bx, bx, by, W, H, alphas, n_contrib, dL_dpixels, dL_dpixel_depths,
+               dL_dalphas, bg);
+    pixel_init(P1, in1, (uint32_t)W * (by + 4) + bx, bx, by + 4, W, H, alphas, n_contrib, dL_dpixels,
+               dL_dpixel_depths, dL_dalphas, bg);
+  }
+  const uint2 range = ranges[blockIdx.y * grid_x + blockIdx.x];
+
+  if (tid == 0) s_max_contrib = 0;
+  __syncthreads();
+  uint32_t warp_last = max(P0.last, P1.last);
+#pragma unroll
+  for (int d = 16; d > 0; d >>= 1) warp_last = max(warp_last, __shfl_xor_sync(0xffffffffu, warp_last, d));
+  if (lane == 0 && warp_last) atomicMax(&s_max_contrib, warp_last);
+  __syncthreads();
+  const int walk = (int)s_max_contrib;
+  if (walk == 0) return;
+
+  const float ddelx_dx = 0.5 * W;
+  const float ddely_dy = 0.5 * H;
+  const int my_quantity = quantity_of_lane(lane);
+  const int my_slot = my_quantity >= 0 ? record_slot_of_quantity(my_quantity) : 0;
+  const bool i_add = my_quantity >= 0 && (lane & 1) == 0;
+
+  const int rounds = (walk + BWD2_BATCH - 1) / BWD2_BATCH;
+  for (int r = 0; r < rounds; ++r) {
+    __syncthreads();
+    const int pos = walk - 1 - (r * BWD2_BATCH + (int)tid);
+    if (pos >= 0) {
+      const uint32_t id = point_list[range.x + pos];
+      const float2 xy = means2D[id];
+      const float4 co = conic_opacity[id];
+      const float4 cd = rgb_depth[id];
+      s_id[tid] = id;
+      // alpha >= 1/255  <=>  power >= -log(255 o); o <= 0 can never contribute
+      s_a[tid] = make_float4(xy.x, xy.y, co.w > 0.f ? -__logf(255.f * co.w) : 1.f, co.w);
+      s_b[tid] = make_float4(co.x, co.y, co.z, cd.w);
+      s_c[tid] = cd;
+    }
+#pragma unroll
+    for (int k = 0; k < ACC_PITCH; ++k) s_acc[k * BWD2_BATCH + tid] = 0.f;
+    __syncthreads();
+
+    const int n = min(BWD2_BATCH, walk - r * BWD2_BATCH);
+    for (int j = 0; j < n; ++j) {
+      const uint32_t jpos = (uint32_t)(walk - 1 - (r * BWD2_BATCH + j));
+      if (jpos >= warp_last) continue;   // warp-uniform
+      const float4 a4 = s_a[j];
+      const float4 b4 = s_b[j];
+      const float dx0 = a4.x - P0.px, dy0 = a4.y - P0.py;
+      const float dx1 = a4.x - P1.px, dy1 = a4.y - P1.py;
+      const float power0 = -0.5f * (b4.x * dx0 * dx0 + b4.z * dy0 * dy0) - b4.y * dx0 * dy0;
+      const float power1 = -0.5f * (b4.x * dx1 * dx1 + b4.z * dy1 * dy1) - b4.y * dx1 * dy1;
+      const bool act0 = jpos < P0.last && power0 <= 0.0f && power0 >= a4.z;
+      const bool act1 = jpos < P1.last && power1 <= 0.0f && power1 >= a4.z;
+      if (!__any_sync(0xffffffffu, act0 || act1)) continue;
+
+      float q[10];
+#pragma unroll
+      for (int k = 0; k < 10; ++k) q[k] = 0.f;
+      const float4 c4 = s_c[j];
+      if (act0) fragment_backward(P0, dx0, dy0, power0, a4, b4, c4, ddelx_dx, ddely_dy, q);
+      if (act1) fragment_backward(P1, dx1, dy1, power1, a4, b4, c4, ddelx_dx, ddely_dy, q);
+      const float total = warp_packed_reduce10(q, lane);
+      if (i_add) atomicAdd(&s_acc[j * ACC_PITCH + my_slot], total);
+    }
+    __syncthreads();
+
+    if ((int)tid < n) {
+      float v[ACC_STRIDE];
+      bool any = false;
+#pragma unroll
+      for (int k = 0; k < ACC_STRIDE; ++k) {
+        v[k] = s_acc[tid * ACC_PITCH + k];
+        any = any || (v[k] != 0.f);
+      }
+      if (any) {
+        float4* dst = acc + (size_t)s_id[tid] * 3;
+        atomicAdd(dst + 0, make_float4(v[0], v[1], v[2], v[3]));
+        atomicAdd(dst + 1, make_float4(v[4], v[5], v[6], v[7]));
+        atomicAdd(dst + 2, make_float4(v[8], v[9], v[10], v[11]));
+      }
+    }
+  }
+}
+
 int launch_blend_backward(const EgsBackwardArgs& a, const GeomPtrs& g, const uint32_t* point_list,
                           const ImagePtrs& im, const BackwardScratch& s, cudaStream_t stream) {
   const dim3 grid(tiles_x(a.width), tiles_y(a.height), 1);
   StageTimer timer(stream, ST_BLEND_BWD);
-  blend_backward_kernel<<<grid, TILE_PIXELS, 0, stream>>>(
-      im.ranges, point_list, a.width, a.height, (int)grid.x, a.background, g.means2D,
-      g.conic_opacity, g.rgb_depth, a.out_alpha, im.n_contrib, a.dL_dout_color, a.dL_dout_depth,
-      a.dL_dout_alpha, s.acc);
+  // EGS_BWD=v1 selects the one-pixel-per-thread kernel with the reference's exact exp (A/B runs)
+  const char* sel = getenv("EGS_BWD");
+  if (sel && strcmp(sel, "v1") == 0) {
+    blend_backward_kernel<<<grid, TILE_PIXELS, 0, stream>>>(
+        im.ranges, point_list, a.width, a.height, (int)grid.x, a.background, g.means2D,
+        g.conic_opacity, g.rgb_depth, a.out_alpha, im.n_contrib, a.dL_dout_color, a.dL_dout_depth,
+        a.dL_dout_alpha, s.acc);
+  } else {
+    blend_backward2_kernel<<<grid, BWD2_THREADS, 0, stream>>>(
+        im.ranges, point_list, a.width, a.height, (int)grid.x, a.background, g.means2D,
+        g.conic_opacity, g.rgb_depth, a.out_alpha, im.n_contrib, a.dL_dout_color, a.dL_dout_depth,
+        a.dL_dout_alpha, s.acc);
+  }
   EGS_AFTER_LAUNCH(stream, a.debug);
   return EGS_OK;
 }

@@ -60,13 +60,13 @@ __device__ __forceinline__ float3 cov2d_ewa(const float3& mean, float fx, float 
 
 // SH degree 0..3 -> RGB, +0.5, clamp at 0 with per-channel clamp flags [forward.cu:20-71].
 __device__ __forceinline__ float3 sh_to_rgb(int deg, int M, const float3 pos, const float3 cam,
-                                            const float* __restrict__ sh, unsigned char& clamp_bits) {
+                                            const float* sh, unsigned char& clamp_bits) {
   float3 dir = make_float3(pos.x - cam.x, pos.y - cam.y, pos.z - cam.z);
   const float len = sqrtf(dir.x * dir.x + dir.y * dir.y + dir.z * dir.z);
   dir.x = dir.x / len;
   dir.y = dir.y / len;
   dir.z = dir.z / len;
-#define SH(k, ch) __ldg(sh + 3 * (k) + (ch))
+#define SH(k, ch) sh[3 * (k) + (ch)]
   float res[3];
 #pragma unroll
   for (int ch = 0; ch < 3; ++ch) res[ch] = kSH0 * SH(0, ch);
@@ -105,7 +105,15 @@ __device__ __forceinline__ float3 sh_to_rgb(int deg, int M, const float3 pos, co
   return make_float3(res[0], res[1], res[2]);
 }
 
-__global__ void __launch_bounds__(256)
+// 128-thread blocks. With 16 coefficients per Gaussian the SH rows of a warp's 32 Gaussians (6 KB,
+// contiguous) are staged through shared memory with float4 loads; a thread walking its own
+// 192-byte row in global memory made the kernel L1-bound (ncu: l1tex 86 %, dram 29 %).
+constexpr int PF_THREADS = 128;
+constexpr int PF_SH_ROW = 48;
+constexpr int PF_SH_PITCH = 49;
+
+template <bool STAGED>
+__global__ void __launch_bounds__(PF_THREADS)
 preprocess_forward_kernel(int P, int D, int M, const float* __restrict__ means3D,
                           const float* __restrict__ scales, float scale_modifier,
                           const float* __restrict__ rotations, const float* __restrict__ opacities,
@@ -125,9 +133,29 @@ preprocess_forward_kernel(int P, int D, int M, const float* __restrict__ means3D
     s_proj[threadIdx.x] = projmatrix[threadIdx.x];
   }
   if (threadIdx.x < 3) s_cam[threadIdx.x] = campos[threadIdx.x];
+  __shared__ float s_sh[STAGED ? (PF_THREADS / 32) * 32 * PF_SH_PITCH : 1];
   __syncthreads();
 
   const int idx = blockIdx.x * blockDim.x + threadIdx.x;
+  const float* sh_row = nullptr;
+  if (STAGED) {
+    const unsigned lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int first = blockIdx.x * blockDim.x + warp * 32;
+    const int rows = min(32, P - first);
+    float* tile = s_sh + warp * 32 * PF_SH_PITCH;
+    if (rows > 0) {
+      const float4* src = reinterpret_cast<const float4*>(shs + (size_t)first * PF_SH_ROW);
+      for (int f = lane; f < rows * (PF_SH_ROW / 4); f += 32) {
+        const float4 v = __ldg(src + f);
+        float* d = tile + (f / (PF_SH_ROW / 4)) * PF_SH_PITCH + (f % (PF_SH_ROW / 4)) * 4;
+        d[0] = v.x; d[1] = v.y; d[2] = v.z; d[3] = v.w;
+      }
+    }
+    __syncwarp();
+    sh_row = tile + lane * PF_SH_PITCH;
+  } else if (shs != nullptr && idx < P) {
+    sh_row = shs + (size_t)idx * M * 3;
+  }
   if (idx >= P) return;
 
   int radius_out = 0;
@@ -173,8 +201,7 @@ preprocess_forward_kernel(int P, int D, int M, const float* __restrict__ means3D
         float3 rgb;
         unsigned char cb = 0;
         if (colors_precomp == nullptr) {
-          rgb = sh_to_rgb(D, M, p_orig, make_float3(s_cam[0], s_cam[1], s_cam[2]),
-                          shs + (size_t)idx * M * 3, cb);
+          rgb = sh_to_rgb(D, M, p_orig, make_float3(s_cam[0], s_cam[1], s_cam[2]), sh_row, cb);
           clamped[idx] = cb;
         } else {
           rgb = make_float3(colors_precomp[3 * idx], colors_precomp[3 * idx + 1],
@@ -207,14 +234,20 @@ int launch_preprocess_forward(const EgsForwardArgs& a, const GeomPtrs& g, cudaSt
   const int P = a.P;
   const float focal_y = a.height / (2.0f * a.tan_fovy);
   const float focal_x = a.width / (2.0f * a.tan_fovx);
-  const int blocks = (P + 255) / 256;
+  const int blocks = (P + PF_THREADS - 1) / PF_THREADS;
   StageTimer timer(stream, ST_PREPROCESS);
-  preprocess_forward_kernel<<<blocks, 256, 0, stream>>>(
-      P, a.sh_degree, a.sh_coeffs, a.means3D, a.scales, a.scale_modifier, a.rotations, a.opacities,
-      a.shs, a.cov3D_precomp, a.colors_precomp, a.viewmatrix, a.projmatrix, a.campos, a.width,
-      a.height, a.tan_fovx, a.tan_fovy, focal_x, focal_y, tiles_x(a.width), tiles_y(a.height),
-      a.radii, g.means2D, g.depths, g.conic_opacity, g.rgb_depth, g.clamped, g.tiles_touched,
-      a.prefiltered, nullptr);
+  const bool staged = a.shs != nullptr && a.sh_coeffs == 16 && (reinterpret_cast<uintptr_t>(a.shs) & 15u) == 0;
+#define EGS_PF_ARGS                                                                                     \
+  P, a.sh_degree, a.sh_coeffs, a.means3D, a.scales, a.scale_modifier, a.rotations, a.opacities, a.shs,  \
+      a.cov3D_precomp, a.colors_precomp, a.viewmatrix, a.projmatrix, a.campos, a.width, a.height,       \
+      a.tan_fovx, a.tan_fovy, focal_x, focal_y, tiles_x(a.width), tiles_y(a.height), a.radii,           \
+      g.means2D, g.depths, g.conic_opacity, g.rgb_depth, g.clamped, g.tiles_touched, a.prefiltered,     \
+      nullptr
+  if (staged)
+    preprocess_forward_kernel<true><<<blocks, PF_THREADS, 0, stream>>>(EGS_PF_ARGS);
+  else
+    preprocess_forward_kernel<false><<<blocks, PF_THREADS, 0, stream>>>(EGS_PF_ARGS);
+#undef EGS_PF_ARGS
   EGS_AFTER_LAUNCH(stream, a.debug);
   return EGS_OK;
 }

@@ -43,10 +43,12 @@ __device__ __forceinline__ F3 operator-(const F3& a) { return {-a.x, -a.y, -a.z}
 __device__ __forceinline__ float dot(const F3& a, const F3& b) { return a.x * b.x + a.y * b.y + a.z * b.z; }
 
 // SH backward: writes dL/dsh[0 .. M) (zeros above the active degree) and returns the part of
-// dL/dmean caused by the view direction.
+// dL/dmean caused by the view direction. Coefficient k is read before its gradient is written, so
+// `shp` and `dL_dsh_out` may be the same row (the staged kernel works in place in shared memory).
+// Basis functions and their derivatives are those of backward.cu:20-139, grouped per coefficient.
 __device__ __forceinline__ float3 sh_backward(int deg, int M, const float3 pos, const float3 cam,
-                                              const float* __restrict__ shp, unsigned char clamp_bits,
-                                              F3 dL_dRGB, float* __restrict__ dL_dsh_out) {
+                                              const float* shp, unsigned char clamp_bits, F3 dL_dRGB,
+                                              float* dL_dsh_out) {
   const float3 dir_orig = make_float3(pos.x - cam.x, pos.y - cam.y, pos.z - cam.z);
   const float len = sqrtf(dir_orig.x * dir_orig.x + dir_orig.y * dir_orig.y + dir_orig.z * dir_orig.z);
   const float x = dir_orig.x / len, y = dir_orig.y / len, z = dir_orig.z / len;
@@ -54,57 +56,45 @@ __device__ __forceinline__ float3 sh_backward(int deg, int M, const float3 pos, 
   dL_dRGB.y *= (clamp_bits & 2) ? 0.f : 1.f;
   dL_dRGB.z *= (clamp_bits & 4) ? 0.f : 1.f;
 
-  auto sh = [&](int k) -> F3 { return {__ldg(shp + 3 * k), __ldg(shp + 3 * k + 1), __ldg(shp + 3 * k + 2)}; };
-  auto put = [&](int k, float w) {
-    dL_dsh_out[3 * k] = w * dL_dRGB.x;
-    dL_dsh_out[3 * k + 1] = w * dL_dRGB.y;
-    dL_dsh_out[3 * k + 2] = w * dL_dRGB.z;
-  };
   F3 dRGBdx = {0, 0, 0}, dRGBdy = {0, 0, 0}, dRGBdz = {0, 0, 0};
-  put(0, kSH0);
+  // one coefficient: basis value b and its derivatives (bx, by, bz) with respect to the direction
+  auto term = [&](int k, float b, float bx, float by, float bz) {
+    const F3 c = {shp[3 * k], shp[3 * k + 1], shp[3 * k + 2]};
+    dRGBdx = dRGBdx + bx * c;
+    dRGBdy = dRGBdy + by * c;
+    dRGBdz = dRGBdz + bz * c;
+    dL_dsh_out[3 * k] = b * dL_dRGB.x;
+    dL_dsh_out[3 * k + 1] = b * dL_dRGB.y;
+    dL_dsh_out[3 * k + 2] = b * dL_dRGB.z;
+  };
+  term(0, kSH0, 0.f, 0.f, 0.f);
   int written = 1;
   if (deg > 0) {
-    put(1, -kSH1 * y);
-    put(2, kSH1 * z);
-    put(3, -kSH1 * x);
+    term(1, -kSH1 * y, 0.f, -kSH1, 0.f);
+    term(2, kSH1 * z, 0.f, 0.f, kSH1);
+    term(3, -kSH1 * x, -kSH1, 0.f, 0.f);
     written = 4;
-    dRGBdx = -kSH1 * sh(3);
-    dRGBdy = -kSH1 * sh(1);
-    dRGBdz = kSH1 * sh(2);
     if (deg > 1) {
       const float xx = x * x, yy = y * y, zz = z * z;
       const float xy = x * y, yz = y * z, xz = x * z;
-      put(4, kSH2[0] * xy);
-      put(5, kSH2[1] * yz);
-      put(6, kSH2[2] * (2.f * zz - xx - yy));
-      put(7, kSH2[3] * xz);
-      put(8, kSH2[4] * (xx - yy));
+      term(4, kSH2[0] * xy, kSH2[0] * y, kSH2[0] * x, 0.f);
+      term(5, kSH2[1] * yz, 0.f, kSH2[1] * z, kSH2[1] * y);
+      term(6, kSH2[2] * (2.f * zz - xx - yy), kSH2[2] * 2.f * -x, kSH2[2] * 2.f * -y, kSH2[2] * 2.f * 2.f * z);
+      term(7, kSH2[3] * xz, kSH2[3] * z, 0.f, kSH2[3] * x);
+      term(8, kSH2[4] * (xx - yy), kSH2[4] * 2.f * x, kSH2[4] * 2.f * -y, 0.f);
       written = 9;
-      dRGBdx = dRGBdx + kSH2[0] * y * sh(4) + kSH2[2] * 2.f * -x * sh(6) + kSH2[3] * z * sh(7) +
-               kSH2[4] * 2.f * x * sh(8);
-      dRGBdy = dRGBdy + kSH2[0] * x * sh(4) + kSH2[1] * z * sh(5) + kSH2[2] * 2.f * -y * sh(6) +
-               kSH2[4] * 2.f * -y * sh(8);
-      dRGBdz = dRGBdz + kSH2[1] * y * sh(5) + kSH2[2] * 2.f * 2.f * z * sh(6) + kSH2[3] * x * sh(7);
       if (deg > 2) {
-        put(9, kSH3[0] * y * (3.f * xx - yy));
-        put(10, kSH3[1] * xy * z);
-        put(11, kSH3[2] * y * (4.f * zz - xx - yy));
-        put(12, kSH3[3] * z * (2.f * zz - 3.f * xx - 3.f * yy));
-        put(13, kSH3[4] * x * (4.f * zz - xx - yy));
-        put(14, kSH3[5] * z * (xx - yy));
-        put(15, kSH3[6] * x * (xx - 3.f * yy));
+        term(9, kSH3[0] * y * (3.f * xx - yy), kSH3[0] * 3.f * 2.f * xy, kSH3[0] * 3.f * (xx - yy), 0.f);
+        term(10, kSH3[1] * xy * z, kSH3[1] * yz, kSH3[1] * xz, kSH3[1] * xy);
+        term(11, kSH3[2] * y * (4.f * zz - xx - yy), kSH3[2] * -2.f * xy, kSH3[2] * (-3.f * yy + 4.f * zz - xx),
+             kSH3[2] * 4.f * 2.f * yz);
+        term(12, kSH3[3] * z * (2.f * zz - 3.f * xx - 3.f * yy), kSH3[3] * -3.f * 2.f * xz,
+             kSH3[3] * -3.f * 2.f * yz, kSH3[3] * 3.f * (2.f * zz - xx - yy));
+        term(13, kSH3[4] * x * (4.f * zz - xx - yy), kSH3[4] * (-3.f * xx + 4.f * zz - yy), kSH3[4] * -2.f * xy,
+             kSH3[4] * 4.f * 2.f * xz);
+        term(14, kSH3[5] * z * (xx - yy), kSH3[5] * 2.f * xz, kSH3[5] * -2.f * yz, kSH3[5] * (xx - yy));
+        term(15, kSH3[6] * x * (xx - 3.f * yy), kSH3[6] * 3.f * (xx - yy), kSH3[6] * -3.f * 2.f * xy, 0.f);
         written = 16;
-        dRGBdx = dRGBdx + (kSH3[0] * sh(9) * 3.f * 2.f * xy + kSH3[1] * sh(10) * yz +
-                           kSH3[2] * sh(11) * -2.f * xy + kSH3[3] * sh(12) * -3.f * 2.f * xz +
-                           kSH3[4] * sh(13) * (-3.f * xx + 4.f * zz - yy) +
-                           kSH3[5] * sh(14) * 2.f * xz + kSH3[6] * sh(15) * 3.f * (xx - yy));
-        dRGBdy = dRGBdy + (kSH3[0] * sh(9) * 3.f * (xx - yy) + kSH3[1] * sh(10) * xz +
-                           kSH3[2] * sh(11) * (-3.f * yy + 4.f * zz - xx) +
-                           kSH3[3] * sh(12) * -3.f * 2.f * yz + kSH3[4] * sh(13) * -2.f * xy +
-                           kSH3[5] * sh(14) * -2.f * yz + kSH3[6] * sh(15) * -3.f * 2.f * xy);
-        dRGBdz = dRGBdz + (kSH3[1] * sh(10) * xy + kSH3[2] * sh(11) * 4.f * 2.f * yz +
-                           kSH3[3] * sh(12) * 3.f * (2.f * zz - xx - yy) +
-                           kSH3[4] * sh(13) * 4.f * 2.f * xz + kSH3[5] * sh(14) * (xx - yy));
       }
     }
   }
@@ -182,30 +172,20 @@ __device__ __forceinline__ void cov3d_recompute(const float3 s, float mod, const
   cov6[5] = Sigma.c[2][2];
 }
 
-__global__ void __launch_bounds__(256)
-preprocess_backward_kernel(int P, int D, int M, const float* __restrict__ means3D,
-                           const int* __restrict__ radii, const float* __restrict__ shs,
-                           const unsigned char* __restrict__ clamped,
-                           const float* __restrict__ scales, const float* __restrict__ rotations,
-                           const float* __restrict__ cov3D_precomp,
-                           const float* __restrict__ colors_precomp, float scale_modifier,
-                           const float* __restrict__ viewmatrix, const float* __restrict__ projmatrix,
-                           const float* __restrict__ campos, float h_x, float h_y, float tan_fovx,
-                           float tan_fovy, const float4* __restrict__ acc,
-                           float* __restrict__ dL_dmeans2D, float* __restrict__ dL_dcolors,
-                           float* __restrict__ dL_dopacity, float* __restrict__ dL_dmeans3D,
-                           float* __restrict__ dL_dcov3D, float* __restrict__ dL_dsh,
-                           float* __restrict__ dL_dscales, float* __restrict__ dL_drot) {
-  __shared__ float view[16], proj[16], s_cam[3];
-  if (threadIdx.x < 16) {
-    view[threadIdx.x] = viewmatrix[threadIdx.x];
-    proj[threadIdx.x] = projmatrix[threadIdx.x];
-  }
-  if (threadIdx.x < 3) s_cam[threadIdx.x] = campos[threadIdx.x];
-  __syncthreads();
-  const int idx = blockIdx.x * blockDim.x + threadIdx.x;
-  if (idx >= P) return;
-
+// Everything one Gaussian needs. `sh_in` / `sh_out` are this Gaussian's rows of SH coefficients
+// and of their gradients; they may be the same shared-memory row (staged mode) because every
+// coefficient is read before its gradient is written.
+__device__ __forceinline__ void
+gaussian_backward(int idx, int D, int M, const float* __restrict__ means3D, const int* __restrict__ radii,
+                  const float* sh_in, float* sh_out, bool has_sh,
+                  const unsigned char* __restrict__ clamped, const float* __restrict__ scales,
+                  const float* __restrict__ rotations, const float* __restrict__ cov3D_precomp,
+                  const float* __restrict__ colors_precomp, float scale_modifier, const float* view,
+                  const float* proj, const float* s_cam, float h_x, float h_y, float tan_fovx,
+                  float tan_fovy, const float4* __restrict__ acc, float* __restrict__ dL_dmeans2D,
+                  float* __restrict__ dL_dcolors, float* __restrict__ dL_dopacity,
+                  float* __restrict__ dL_dmeans3D, float* __restrict__ dL_dcov3D,
+                  float* __restrict__ dL_dscales, float* __restrict__ dL_drot) {
   if (!(radii[idx] > 0)) {
     // culled: every gradient is zero
 #pragma unroll
@@ -222,9 +202,8 @@ preprocess_backward_kernel(int P, int D, int M, const float* __restrict__ means3
 #pragma unroll
       for (int k = 0; k < 6; ++k) dL_dcov3D[6 * idx + k] = 0.f;
     }
-    if (shs != nullptr) {
-      float* o = dL_dsh + (size_t)idx * M * 3;
-      for (int k = 0; k < 3 * M; ++k) o[k] = 0.f;
+    if (has_sh) {
+      for (int k = 0; k < 3 * M; ++k) sh_out[k] = 0.f;
     }
     if (scales != nullptr) {
 #pragma unroll
@@ -349,10 +328,9 @@ preprocess_backward_kernel(int P, int D, int M, const float* __restrict__ means3
     dmean.x += g.x; dmean.y += g.y; dmean.z += g.z;
   }
   // ---- colour part --------------------------------------------------------------------------
-  if (shs != nullptr) {
-    const float3 g = sh_backward(D, M, mean, make_float3(s_cam[0], s_cam[1], s_cam[2]),
-                                 shs + (size_t)idx * M * 3, clamped[idx], F3{a2.x, a2.y, a2.z},
-                                 dL_dsh + (size_t)idx * M * 3);
+  if (has_sh) {
+    const float3 g = sh_backward(D, M, mean, make_float3(s_cam[0], s_cam[1], s_cam[2]), sh_in, clamped[idx],
+                                 F3{a2.x, a2.y, a2.z}, sh_out);
     dmean.x += g.x; dmean.y += g.y; dmean.z += g.z;
   } else {
     dL_dcolors[3 * idx + 0] = a2.x;
@@ -378,16 +356,102 @@ preprocess_backward_kernel(int P, int D, int M, const float* __restrict__ means3
   }
 }
 
+// One thread per Gaussian, 128-thread blocks. With 16 coefficients (SH degree 3 storage) the SH rows
+// of a warp's 32 Gaussians -- 6 KB, contiguous in memory -- are staged through shared memory with
+// float4 accesses both ways: a thread reading or writing its own 192-byte row straight from global
+// memory makes every warp instruction touch 32 sectors, which left this kernel bound by L2
+// transactions (ncu: lts 71 %, dram 20 %) instead of by HBM.
+constexpr int PB_THREADS = 128;
+constexpr int PB_WARPS = PB_THREADS / 32;
+constexpr int SH_ROW = 48;        // 16 coefficients x RGB
+constexpr int SH_PITCH = 49;      // odd pitch: a lane walking its own row is conflict-free
+
+template <bool STAGED>
+__global__ void __launch_bounds__(PB_THREADS)
+preprocess_backward_kernel(int P, int D, int M, const float* __restrict__ means3D,
+                           const int* __restrict__ radii, const float* __restrict__ shs,
+                           const unsigned char* __restrict__ clamped,
+                           const float* __restrict__ scales, const float* __restrict__ rotations,
+                           const float* __restrict__ cov3D_precomp,
+                           const float* __restrict__ colors_precomp, float scale_modifier,
+                           const float* __restrict__ viewmatrix, const float* __restrict__ projmatrix,
+                           const float* __restrict__ campos, float h_x, float h_y, float tan_fovx,
+                           float tan_fovy, const float4* __restrict__ acc,
+                           float* __restrict__ dL_dmeans2D, float* __restrict__ dL_dcolors,
+                           float* __restrict__ dL_dopacity, float* __restrict__ dL_dmeans3D,
+                           float* __restrict__ dL_dcov3D, float* __restrict__ dL_dsh,
+                           float* __restrict__ dL_dscales, float* __restrict__ dL_drot) {
+  __shared__ float view[16], proj[16], s_cam[3];
+  __shared__ float s_sh[STAGED ? PB_WARPS * 32 * SH_PITCH : 1];
+  if (threadIdx.x < 16) {
+    view[threadIdx.x] = viewmatrix[threadIdx.x];
+    proj[threadIdx.x] = projmatrix[threadIdx.x];
+  }
+  if (threadIdx.x < 3) s_cam[threadIdx.x] = campos[threadIdx.x];
+  __syncthreads();
+  const int idx = blockIdx.x * blockDim.x + threadIdx.x;
+  const unsigned lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const bool has_sh = shs != nullptr;
+
+  if (STAGED) {
+    // rows [first, first + rows) of this warp, as one contiguous run of rows * 48 floats
+    const int first = blockIdx.x * blockDim.x + warp * 32;
+    const int rows = min(32, P - first);
+    float* tile = s_sh + warp * 32 * SH_PITCH;
+    if (rows > 0) {
+      const float4* src = reinterpret_cast<const float4*>(shs + (size_t)first * SH_ROW);
+      for (int f = lane; f < rows * (SH_ROW / 4); f += 32) {
+        const float4 v = __ldg(src + f);
+        const int row = f / (SH_ROW / 4), k = (f % (SH_ROW / 4)) * 4;
+        float* d = tile + row * SH_PITCH + k;
+        d[0] = v.x; d[1] = v.y; d[2] = v.z; d[3] = v.w;
+      }
+    }
+    __syncwarp();
+    if (idx < P) {
+      float* row = tile + lane * SH_PITCH;
+      gaussian_backward(idx, D, M, means3D, radii, row, row, true, clamped, scales, rotations, cov3D_precomp,
+                        colors_precomp, scale_modifier, view, proj, s_cam, h_x, h_y, tan_fovx, tan_fovy, acc,
+                        dL_dmeans2D, dL_dcolors, dL_dopacity, dL_dmeans3D, dL_dcov3D, dL_dscales, dL_drot);
+    }
+    __syncwarp();
+    if (rows > 0) {
+      float4* dst = reinterpret_cast<float4*>(dL_dsh + (size_t)first * SH_ROW);
+      for (int f = lane; f < rows * (SH_ROW / 4); f += 32) {
+        const int row = f / (SH_ROW / 4), k = (f % (SH_ROW / 4)) * 4;
+        const float* srow = tile + row * SH_PITCH + k;
+        dst[f] = make_float4(srow[0], srow[1], srow[2], srow[3]);
+      }
+    }
+  } else {
+    if (idx >= P) return;
+    const size_t off = (size_t)idx * M * 3;
+    gaussian_backward(idx, D, M, means3D, radii, has_sh ? shs + off : nullptr, has_sh ? dL_dsh + off : nullptr,
+                      has_sh, clamped, scales, rotations, cov3D_precomp, colors_precomp, scale_modifier, view,
+                      proj, s_cam, h_x, h_y, tan_fovx, tan_fovy, acc, dL_dmeans2D, dL_dcolors, dL_dopacity,
+                      dL_dmeans3D, dL_dcov3D, dL_dscales, dL_drot);
+  }
+}
+
 int launch_preprocess_backward(const EgsBackwardArgs& a, const GeomPtrs& g,
                                const BackwardScratch& s, cudaStream_t stream) {
   const float focal_y = a.height / (2.0f * a.tan_fovy);
   const float focal_x = a.width / (2.0f * a.tan_fovx);
   StageTimer timer(stream, ST_PREPROCESS_BWD);
-  preprocess_backward_kernel<<<(a.P + 255) / 256, 256, 0, stream>>>(
-      a.P, a.sh_degree, a.sh_coeffs, a.means3D, a.radii, a.shs, g.clamped, a.scales, a.rotations,
-      a.cov3D_precomp, a.colors_precomp, a.scale_modifier, a.viewmatrix, a.projmatrix, a.campos,
-      focal_x, focal_y, a.tan_fovx, a.tan_fovy, s.acc, a.dL_dmeans2D, a.dL_dcolors, a.dL_dopacity,
-      a.dL_dmeans3D, a.dL_dcov3D, a.dL_dsh, a.dL_dscales, a.dL_drotations);
+  const int blocks = (a.P + PB_THREADS - 1) / PB_THREADS;
+  const bool staged = a.shs != nullptr && a.sh_coeffs == 16 &&
+                      (reinterpret_cast<uintptr_t>(a.shs) & 15u) == 0 &&
+                      (reinterpret_cast<uintptr_t>(a.dL_dsh) & 15u) == 0;
+#define EGS_PB_ARGS                                                                                   \
+  a.P, a.sh_degree, a.sh_coeffs, a.means3D, a.radii, a.shs, g.clamped, a.scales, a.rotations,         \
+      a.cov3D_precomp, a.colors_precomp, a.scale_modifier, a.viewmatrix, a.projmatrix, a.campos,      \
+      focal_x, focal_y, a.tan_fovx, a.tan_fovy, s.acc, a.dL_dmeans2D, a.dL_dcolors, a.dL_dopacity,    \
+      a.dL_dmeans3D, a.dL_dcov3D, a.dL_dsh, a.dL_dscales, a.dL_drotations
+  if (staged)
+    preprocess_backward_kernel<true><<<blocks, PB_THREADS, 0, stream>>>(EGS_PB_ARGS);
+  else
+    preprocess_backward_kernel<false><<<blocks, PB_THREADS, 0, stream>>>(EGS_PB_ARGS);
+#undef EGS_PB_ARGS
   EGS_AFTER_LAUNCH(stream, a.debug);
   return EGS_OK;
 }
