@@ -335,6 +335,57 @@ def backward(fwd: ForwardResult, *, means3D, bg, viewmatrix, projmatrix, campos,
     return g
 
 
+STATIC_SCRATCH_MAX_GAUSSIANS = 262144   # EGS_STATIC_SCRATCH_MAX_GAUSSIANS in the header
+
+
+def backward_static_scratch(fwd: ForwardResult, *, means3D, bg, viewmatrix, projmatrix, campos, tanfovx,
+                            tanfovy, dL_dcolor, dL_ddepth, dL_dalpha, out, sh_degree=0, shs=None,
+                            colors_precomp=None, scales=None, rotations=None, cov3D_precomp=None,
+                            scale_modifier=1.0, debug=False, stream=None):
+    """egs_backward_static_scratch: backward for callers that must not allocate on the device.
+
+    Meant for hosts whose GPU memory belongs to a pool they do not control (a serving process that
+    reserved the device up front, a plugin inside one): they pass only buffers they already own.
+    `out` must therefore hold ALL gradient tensors, preallocated by the caller, under the keys
+    cabi.backward returns ("means2D", "opacity", "means3D" and, for the inputs that are present,
+    "colors", "cov3D", "sh", "scales", "rotations"); this wrapper creates no tensor and passes no
+    scratch pointer -- the accumulator records are an array inside libegs_rasterizer.so, limited
+    to STATIC_SCRATCH_MAX_GAUSSIANS Gaussians and shared by every call on the device, so calls
+    must not overlap on the GPU. The first call on a device does a one-time address look-up and
+    should happen before any stream capture begins."""
+    import torch
+    lib = load()
+    fn = lib.egs_backward_static_scratch
+    fn.restype = C.c_int
+    fn.argtypes = [C.POINTER(EgsBackwardArgs), C.c_void_p]
+    P, W, H = fwd.P, fwd.W, fwd.H
+    M = int(shs.shape[1]) if shs is not None and shs.numel() else 0
+    a = EgsBackwardArgs()
+    a.P, a.sh_degree, a.sh_coeffs, a.num_rendered, a.width, a.height = P, int(sh_degree), M, fwd.num_rendered, W, H
+    a.background, a.means3D, a.shs = _ptr(bg), _ptr(means3D), _ptr(shs)
+    a.colors_precomp, a.scales, a.rotations = _ptr(colors_precomp), _ptr(scales), _ptr(rotations)
+    a.cov3D_precomp = _ptr(cov3D_precomp)
+    a.scale_modifier = float(scale_modifier)
+    a.viewmatrix, a.projmatrix, a.campos = _ptr(viewmatrix), _ptr(projmatrix), _ptr(campos)
+    a.tan_fovx, a.tan_fovy = float(tanfovx), float(tanfovy)
+    a.radii = fwd.radii.data_ptr() if P else None
+    a.out_alpha = fwd.alpha.data_ptr()
+    a.geom_buffer = fwd.geom.data_ptr() if fwd.geom is not None else None
+    a.binning_buffer = fwd.binning.data_ptr() if fwd.binning is not None and fwd.num_rendered else None
+    a.image_buffer = fwd.image.data_ptr() if fwd.image is not None else None
+    a.dL_dout_color, a.dL_dout_depth, a.dL_dout_alpha = _ptr(dL_dcolor), _ptr(dL_ddepth), _ptr(dL_dalpha)
+    a.scratch = None   # ignored by this entry point
+    for key, field in (("means2D", "dL_dmeans2D"), ("opacity", "dL_dopacity"), ("means3D", "dL_dmeans3D"),
+                       ("colors", "dL_dcolors"), ("cov3D", "dL_dcov3D"), ("sh", "dL_dsh"),
+                       ("scales", "dL_dscales"), ("rotations", "dL_drotations")):
+        t = out.get(key)
+        setattr(a, field, t.data_ptr() if t is not None and t.numel() else None)
+    a.debug = int(debug)
+    with torch.cuda.device(means3D.device):
+        _check(fn(C.byref(a), _stream_handle(stream)), "egs_backward_static_scratch")
+    return out
+
+
 def mark_visible(means3D, viewmatrix, projmatrix, stream=None):
     import torch
     lib = load()

@@ -228,6 +228,52 @@ extern "C" int egs_backward(const EgsBackwardArgs* args, void* stream_v) {
   return launch_preprocess_backward(a, g, s, stream);
 }
 
+// ---- backward with the scratch inside the library image --------------------------------------
+// For hosts that may not allocate on the device (see the header). The accumulator records sit
+// in a file-scope device array; host code may not use that name as an address, so its device
+// address is looked up once per device and handed to the ordinary backward path as `scratch`.
+static __device__ __align__(256) float4 g_static_backward_records[(size_t)EGS_STATIC_SCRATCH_MAX_GAUSSIANS * 3];
+
+namespace {
+constexpr int kMaxDevices = 64;
+std::mutex g_static_scratch_mu;
+void* g_static_scratch_addr[kMaxDevices] = {};   // per device, filled on that device's first call
+}  // namespace
+
+extern "C" int egs_backward_static_scratch(const EgsBackwardArgs* args, void* stream) {
+  if (!args) {
+    set_error("egs_backward_static_scratch: NULL args");
+    return EGS_ERR_INVALID_ARGUMENT;
+  }
+  if (args->P > EGS_STATIC_SCRATCH_MAX_GAUSSIANS) {
+    set_error("egs_backward_static_scratch: P = %d exceeds the built-in scratch of %d Gaussians "
+              "(EGS_STATIC_SCRATCH_MAX_GAUSSIANS); use egs_backward with a caller-provided scratch",
+              args->P, EGS_STATIC_SCRATCH_MAX_GAUSSIANS);
+    return EGS_ERR_TOO_LARGE;
+  }
+  int dev = -1;
+  EGS_CUDA_TRY(cudaGetDevice(&dev));
+  if (dev < 0 || dev >= kMaxDevices) {
+    set_error("egs_backward_static_scratch: device ordinal %d not supported", dev);
+    return EGS_ERR_INVALID_ARGUMENT;
+  }
+  void* records = nullptr;
+  {
+    std::lock_guard<std::mutex> lk(g_static_scratch_mu);
+    if (g_static_scratch_addr[dev] == nullptr) {
+      // one-time set-up for this device (it is the current one): where does the array live here?
+      void* p = nullptr;
+      EGS_CUDA_TRY(cudaGetSymbolAddress(&p, g_static_backward_records));
+      g_static_scratch_addr[dev] = p;
+    }
+    records = g_static_scratch_addr[dev];
+  }
+  EgsBackwardArgs with_scratch = *args;   // plain struct copy on the host stack; nothing is allocated
+  with_scratch.scratch = records;
+  // egs_backward clears the P records it uses before accumulating into them
+  return egs_backward(&with_scratch, stream);
+}
+
 extern "C" int egs_mark_visible(int P, const float* means3D, const float* viewmatrix,
                                 const float* projmatrix, unsigned char* present, void* stream) {
   if (P < 0 || (P > 0 && (!means3D || !viewmatrix || !present))) {

@@ -138,6 +138,31 @@ size_t egs_backward_scratch_bytes(int P);
 
 int egs_backward(const EgsBackwardArgs* args, void* stream);
 
+/* Backward pass for hosts that must not allocate device memory. No counterpart in the reference
+ * (its binding allocates ten gradient tensors and its workspaces on every call).
+ *
+ * Who needs it: a process whose GPU memory is owned by somebody else's pool -- an inference or
+ * render server that reserved the whole device at start-up, a plugin running inside such a
+ * host, a loop with a fixed memory budget -- cannot hand egs_backward a fresh scratch buffer,
+ * and cudaMalloc/cudaFree would also stall every stream of the device while they run.
+ *
+ * What it does: exactly egs_backward, except that `args->scratch` is ignored (may be NULL) and
+ * the 48-byte-per-Gaussian accumulator records live in an array that is part of the library
+ * image itself: EGS_STATIC_SCRATCH_MAX_GAUSSIANS records = 12 MiB, resident on every GPU that
+ * loads the library until the process exits. The call performs no cudaMalloc, cudaFree or any
+ * other allocating routine; inputs, the forward blobs and all gradient outputs are still the
+ * caller's buffers.
+ *
+ * Limits and rules:
+ *   - args->P above EGS_STATIC_SCRATCH_MAX_GAUSSIANS is refused with EGS_ERR_TOO_LARGE;
+ *   - the first call on each device looks up the array's device address (a one-time set-up
+ *     with that device current); make that first call before starting any stream capture;
+ *   - all calls on a device share the one array. The accumulators are cleared at the start of
+ *     every call, so stale contents never leak into a result, but two calls that overlap on
+ *     the GPU (different streams, or different host threads) race on it: serialise them. */
+#define EGS_STATIC_SCRATCH_MAX_GAUSSIANS 262144
+int egs_backward_static_scratch(const EgsBackwardArgs* args, void* stream);
+
 /* present[i] = (view-space z of means3D[i] > 0.2), 1 byte per Gaussian (rasterizer_impl.cu:54-66). */
 int egs_mark_visible(int P, const float* means3D, const float* viewmatrix,
                      const float* projmatrix, unsigned char* present, void* stream);

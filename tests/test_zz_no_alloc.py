@@ -1,0 +1,95 @@
+"""The allocation-free backward entry point, egs_backward_static_scratch.
+
+Some hosts cannot create device memory at all: a serving process that reserved the whole GPU in
+its own pool at start-up, or a plugin living inside such a process, has no way to hand
+egs_backward a fresh scratch buffer, and cudaMalloc / cudaFree would stall every stream of the
+device anyway. For them the library carries its own accumulator array (12 MiB, at most
+EGS_STATIC_SCRATCH_MAX_GAUSSIANS Gaussians) and this entry point uses it instead of
+`args->scratch`.
+
+The test drives it through the C-ABI (ctypes, raw device pointers), twice in a row with
+different inputs, and requires the same gradients as the ordinary entry point within the
+gradient tolerance of the other parity tests. Because every call shares the one array, the second
+call also proves that what the first call left behind is cleared. The file is named so that
+pytest collects it last.
+"""
+import ctypes
+
+import pytest
+import torch
+
+from helpers import GRAD_RTOL, grad_rel_err
+
+pytestmark = pytest.mark.gpu
+
+GRAD_KEYS = ("means2D", "opacity", "means3D", "colors", "cov3D", "sh", "scales", "rotations")
+
+
+def _inputs(P, W, H, deg, seed, geom, dev, scale_mul=1.0):
+    from egogaussian_b200 import scenes
+    sc = scenes.make_scene(P, W, H, sh_degree=deg, seed=seed)
+    sc.scales = (sc.scales * scale_mul).contiguous()
+    cam = sc.camera
+    kw = dict(means3D=sc.means3D, opacities=sc.opacities, bg=torch.tensor([0.2, 0.1, 0.4]), viewmatrix=cam.viewmatrix,
+              projmatrix=cam.projmatrix, campos=cam.campos, tanfovx=cam.tanfovx, tanfovy=cam.tanfovy,
+              image_height=H, image_width=W, sh_degree=deg, shs=sc.shs)
+    if geom == "scale_rot":
+        kw["scales"], kw["rotations"] = sc.scales, sc.rotations
+    else:
+        kw["cov3D_precomp"] = sc.cov3D()
+    kw = {k: (v.to(dev).contiguous() if isinstance(v, torch.Tensor) else v) for k, v in kw.items()}
+    wc, wd, wa = scenes.upstream_weights(W, H, seed)
+    ups = dict(dL_dcolor=wc.to(dev), dL_ddepth=wd.to(dev), dL_dalpha=wa.to(dev))
+    return kw, ups
+
+
+def _compare(kw, ups):
+    """Gradients from the ordinary entry point and from the allocation-free one, same forward."""
+    from egogaussian_b200 import cabi
+    fwd = cabi.forward(**kw)
+    bkw = {k: v for k, v in kw.items() if k not in ("opacities", "image_height", "image_width")}
+    want = cabi.backward(fwd, **bkw, **ups)
+    # the caller owns every output; poison them so an element the kernels skip cannot pass
+    out = {k: torch.full_like(v, float("nan")) for k, v in want.items() if v is not None}
+    got = cabi.backward_static_scratch(fwd, out=out, **bkw, **ups)
+    torch.cuda.synchronize()
+    checked = 0
+    for k in GRAD_KEYS:
+        if want.get(k) is None:
+            continue
+        assert torch.isfinite(got[k]).all(), k
+        assert grad_rel_err(got[k], want[k]) <= GRAD_RTOL, k
+        checked += 1
+    assert checked >= 5
+    return fwd
+
+
+def test_static_scratch_backward_matches_ordinary_backward_twice(built, cuda_device):
+    from egogaussian_b200 import cabi
+    dev = cuda_device
+    # first call: 30k Gaussians, SH degree 2, scale + rotation inputs
+    kw1, ups1 = _inputs(30_000, 320, 240, 2, 501, "scale_rot", dev)
+    f1 = _compare(kw1, ups1)
+    assert f1.num_rendered > 0
+    # second call straight after, on fewer Gaussians and other inputs: records the first call
+    # wrote (also those beyond this call's P) must not show up in the result
+    kw2, ups2 = _inputs(12_000, 200, 152, 1, 502, "cov", dev, scale_mul=2.0)
+    f2 = _compare(kw2, ups2)
+    assert f2.num_rendered > 0
+    # and the first problem again gives the first answer again
+    _compare(kw1, ups1)
+    assert cabi.STATIC_SCRATCH_MAX_GAUSSIANS == 262144
+
+
+def test_static_scratch_rejects_oversize(built, cuda_device):
+    from egogaussian_b200 import cabi
+    lib = cabi.load()
+    lib.egs_backward_static_scratch.restype = ctypes.c_int
+    lib.egs_backward_static_scratch.argtypes = [ctypes.POINTER(cabi.EgsBackwardArgs), ctypes.c_void_p]
+    a = cabi.EgsBackwardArgs()
+    a.P, a.width, a.height = cabi.STATIC_SCRATCH_MAX_GAUSSIANS + 1, 64, 64
+    rc = lib.egs_backward_static_scratch(ctypes.byref(a), None)
+    assert rc == -4   # EGS_ERR_TOO_LARGE
+    msg = lib.egs_last_error().decode()
+    assert "262144" in msg and "exceeds" in msg
+    assert lib.egs_backward_static_scratch(None, None) == -1
