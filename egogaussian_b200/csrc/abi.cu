@@ -170,12 +170,18 @@ extern "C" int egs_forward(const EgsForwardArgs* args, void* stream_v, int* num_
     return EGS_ERR_ALLOC;
   }
   const BinningPtrs b(bin_mem, (size_t)R);
-  // Packed single-word sort when (tile | depth | index) fits 64 bits, else the pair sort;
-  // EGS_SORT=pairs forces the general path (tests).
+  // Three binning paths with identical results:
+  //   buckets  packed words, one global partition on the top tile bits + per-bucket CTA sort
+  //   packed   packed words, five global LSD passes (R too large for the bucket sorter)
+  //   pairs    (u64 key, u32 value) LSD sort (tile | depth | index does not fit 64 bits)
+  // EGS_SORT=pairs|packed forces a path (tests, A/B timing).
   const char* force = getenv("EGS_SORT");
-  const bool pairs = !packed_path_fits(a.P, a.width, a.height) || (force && strcmp(force, "pairs") == 0);
-  if (pairs) {
+  const bool want_pairs = force && strcmp(force, "pairs") == 0;
+  const bool want_packed = force && strcmp(force, "packed") == 0;
+  if (!packed_path_fits(a.P, a.width, a.height) || want_pairs) {
     if (int rc = launch_binning(g, b, im, a.radii, a.P, R, a.width, a.height, stream, a.debug)) return rc;
+  } else if (bucket_path_ok(a.P, R, a.width, a.height) && !want_packed) {
+    if (int rc = launch_binning_buckets(g, b, im, a.radii, a.P, R, a.width, a.height, stream, a.debug)) return rc;
   } else {
     if (int rc = launch_binning_packed(g, b, im, a.radii, a.P, R, a.width, a.height, stream, a.debug)) return rc;
   }

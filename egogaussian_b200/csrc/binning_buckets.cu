@@ -1,0 +1,424 @@
+// binning_buckets.cu -- MSD-bucket binning: one global partition pass on the top tile bits, then
+// every bucket is sorted to completion by ONE CTA in shared memory.
+//
+// Same result as duplicateWithKeys + cub::DeviceRadixSort::SortPairs + identifyTileRanges of the
+// reference (DGR/cuda_rasterizer/rasterizer_impl.cu:70-138, 290-319): the unique ordering by
+// (tile, depth bits, Gaussian index) -- see binning_packed.cu for why that is what a stable sort
+// of the reference's key list produces.
+//
+// Why: at the sizes of this path (R ~ 1e7 packed words, 73 MB -- L2-resident) an LSD radix sort
+// is not bandwidth-bound but serialised by its passes: every onesweep pass chains ~2200 CTAs
+// through a decoupled look-back (ncu: 23-30 % of samples spin there) and all five passes go
+// through global memory. Here only the FIRST digit (the top <= 10 bits of the tile id) is a
+// global pass. It cuts the list into <= 1024 contiguous buckets of a few adjacent tiles each;
+// a bucket (~9k words at 1M Gaussians, 1280x720) fits in shared memory, so the remaining 34-35
+// key bits are sorted by one CTA with four 9-bit LSD passes that never leave the SM and need no
+// cross-CTA protocol. The CTA then holds its tiles completely sorted, so it also emits the
+// per-tile ranges (identifyTileRanges disappears) and the unpacked index list.
+// Global traffic per instance: 8 (duplicate) + 16 (partition) + 8 + 12 (bucket sort in/out)
+// = 44 B instead of ~100 B for five global passes.
+//
+// Buckets longer than the shared-memory capacity are sorted by the same CTA through global
+// memory (correct, slower); the host picks the pure LSD path instead when R is so large that
+// most buckets would overflow.
+#include "common.cuh"
+
+namespace egs {
+
+constexpr int MSD_BITS_MAX = 10;
+constexpr int MSD_BINS = 1 << MSD_BITS_MAX;        // 1024
+constexpr int MSD_THREADS = 1024;                  // one thread per bin
+constexpr int MSD_WARPS = MSD_THREADS / 32;
+constexpr int MSD_ITEMS = 4;
+constexpr int MSD_TILE = MSD_THREADS * MSD_ITEMS;  // 4096 words per CTA (same as SORT_TILE)
+static_assert(MSD_TILE == SORT_TILE, "status sizing");
+static_assert(MSD_BINS <= SORT_STATUS_WORDS, "status sizing");
+
+constexpr int BK_THREADS = 1024;
+constexpr int BK_WARPS = BK_THREADS / 32;
+constexpr int BK_BITS = 9;
+constexpr int BK_RADIX = 1 << BK_BITS;             // 512
+constexpr int BK_CAP = 12288;                      // words per bucket held in shared memory (2 buffers)
+
+// ---------------------------------------------------------------------------------------------
+// duplicate + bucket histogram
+// ---------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256)
+duplicate_bucket_kernel(int P, const float2* __restrict__ means2D, const float* __restrict__ depths,
+                        const uint32_t* __restrict__ offsets, const int* __restrict__ radii,
+                        uint64_t* __restrict__ words, int grid_x, int grid_y, int idx_bits,
+                        int bucket_shift /* tile id >> bucket_shift = bucket */,
+                        uint32_t* __restrict__ bucket_hist) {
+  __shared__ uint32_t s_hist[MSD_BINS];
+  for (int i = threadIdx.x; i < MSD_BINS; i += blockDim.x) s_hist[i] = 0;
+  __syncthreads();
+  const int idx = blockIdx.x * blockDim.x + threadIdx.x;
+  if (idx < P) {
+    const int r = radii[idx];
+    if (r > 0) {
+      uint32_t off = (idx == 0) ? 0u : offsets[idx - 1];
+      uint2 lo, hi;
+      tile_rect(means2D[idx], r, grid_x, grid_y, lo, hi);
+      const uint64_t low = ((uint64_t)__float_as_uint(depths[idx]) << idx_bits) | (uint32_t)idx;
+      const int tile_shift = 32 + idx_bits;
+      for (uint32_t y = lo.y; y < hi.y; ++y) {
+        // a row of the rectangle is a run of consecutive tile ids: count it per bucket in one go
+        uint32_t x = lo.x;
+        while (x < hi.x) {
+          const uint32_t t0 = y * (uint32_t)grid_x + x;
+          const uint32_t bucket = t0 >> bucket_shift;
+          const uint32_t run_end = min(hi.x, x + (((bucket + 1u) << bucket_shift) - t0));
+          for (uint32_t xx = x; xx < run_end; ++xx)
+            words[off++] = ((uint64_t)(y * (uint32_t)grid_x + xx) << tile_shift) | low;
+          atomicAdd(&s_hist[bucket], run_end - x);
+          x = run_end;
+        }
+      }
+    }
+  }
+  __syncthreads();
+  for (int i = threadIdx.x; i < MSD_BINS; i += blockDim.x) {
+    const uint32_t c = s_hist[i];
+    if (c) atomicAdd(&bucket_hist[i], c);
+  }
+}
+
+// exclusive scan of the bucket histogram; start[MSD_BINS] = total
+__global__ void __launch_bounds__(MSD_BINS)
+bucket_scan_kernel(const uint32_t* __restrict__ hist, uint32_t* __restrict__ start) {
+  __shared__ uint32_t s_w[MSD_BINS / 32];
+  const uint32_t v = hist[threadIdx.x];
+  const unsigned lane = lane_id(), warp = threadIdx.x >> 5;
+  uint32_t incl = v;
+#pragma unroll
+  for (int d = 1; d < 32; d <<= 1) {
+    const uint32_t t = __shfl_up_sync(0xffffffffu, incl, d);
+    if (lane >= d) incl += t;
+  }
+  if (lane == 31) s_w[warp] = incl;
+  __syncthreads();
+  uint32_t woff = 0;
+  for (unsigned w = 0; w < warp; ++w) woff += s_w[w];
+  start[threadIdx.x] = woff + incl - v;
+  if (threadIdx.x == MSD_BINS - 1) start[MSD_BINS] = woff + incl;
+}
+
+// ---------------------------------------------------------------------------------------------
+// global stable partition by bucket (one onesweep pass, 10-bit digit)
+// ---------------------------------------------------------------------------------------------
+constexpr uint32_t MSD_FLAG_AGG = 1u << 30;
+constexpr uint32_t MSD_FLAG_PREFIX = 1u << 31;
+constexpr uint32_t MSD_VALUE_MASK = (1u << 30) - 1u;
+
+struct MsdSmem {
+  uint16_t warp_hist[MSD_WARPS][MSD_BINS];   // 64 KB (a warp holds at most 128 items)
+  uint64_t exch[MSD_TILE];                   // 32 KB
+  uint32_t digit_local[MSD_BINS];
+  uint32_t digit_global[MSD_BINS];
+  uint32_t warp_sums[MSD_WARPS];
+  uint32_t tile;
+};
+
+__device__ __forceinline__ uint32_t ld_relaxed_u32(const uint32_t* p) {
+  uint32_t v;
+  asm volatile("ld.relaxed.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+  return v;
+}
+__device__ __forceinline__ void st_relaxed_u32(uint32_t* p, uint32_t v) {
+  asm volatile("st.relaxed.gpu.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
+}
+
+__global__ void __launch_bounds__(MSD_THREADS)
+msd_partition_kernel(const uint64_t* __restrict__ in, uint64_t* __restrict__ out, int n, int shift,
+                     const uint32_t* __restrict__ bucket_start, uint32_t* __restrict__ ticket,
+                     uint32_t* __restrict__ status_raw) {
+  extern __shared__ __align__(16) unsigned char smem_raw[];
+  MsdSmem& S = *reinterpret_cast<MsdSmem*>(smem_raw);
+  const unsigned tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  if (tid == 0) S.tile = atomicAdd(ticket, 1u);
+#pragma unroll
+  for (int w = 0; w < MSD_WARPS; ++w) S.warp_hist[w][tid] = 0;
+  __syncthreads();
+  const uint32_t tile = S.tile;
+  const unsigned lt_mask = (1u << lane) - 1u;
+  const size_t block_base = (size_t)tile * MSD_TILE;
+  const size_t warp_base = block_base + (size_t)warp * (32 * MSD_ITEMS);
+
+  uint64_t word[MSD_ITEMS];
+  uint32_t rank[MSD_ITEMS];
+#pragma unroll
+  for (int i = 0; i < MSD_ITEMS; ++i) {
+    const size_t g = warp_base + (size_t)i * 32 + lane;
+    word[i] = g < (size_t)n ? in[g] : ~0ull;
+  }
+#pragma unroll
+  for (int i = 0; i < MSD_ITEMS; ++i) {
+    const size_t g = warp_base + (size_t)i * 32 + lane;
+    const bool ok = g < (size_t)n;
+    const uint32_t d = (uint32_t)(word[i] >> shift);
+    const uint32_t peers = __match_any_sync(0xffffffffu, ok ? d : (0x10000u + lane));
+    const uint32_t before = ok ? S.warp_hist[warp][d] : 0u;
+    __syncwarp();
+    if (ok && (peers & lt_mask) == 0u) S.warp_hist[warp][d] = (uint16_t)(before + __popc(peers));
+    __syncwarp();
+    rank[i] = before + __popc(peers & lt_mask);
+  }
+  __syncthreads();
+  {
+    const uint32_t d = tid;
+    uint32_t run = 0;
+#pragma unroll 8
+    for (int w = 0; w < MSD_WARPS; ++w) {
+      const uint32_t c = S.warp_hist[w][d];
+      S.warp_hist[w][d] = (uint16_t)run;
+      run += c;
+    }
+    const uint32_t block_count = run;
+    uint32_t* st = status_raw + (size_t)tile * MSD_BINS + d;
+    if (tile != 0) st_relaxed_u32(st, MSD_FLAG_AGG | block_count);
+    uint32_t incl = block_count;
+#pragma unroll
+    for (int s = 1; s < 32; s <<= 1) {
+      const uint32_t t = __shfl_up_sync(0xffffffffu, incl, s);
+      if (lane >= s) incl += t;
+    }
+    if (lane == 31) S.warp_sums[warp] = incl;
+    __syncthreads();
+    uint32_t woff = 0;
+    for (unsigned w = 0; w < warp; ++w) woff += S.warp_sums[w];
+    const uint32_t local_start = woff + incl - block_count;
+    S.digit_local[d] = local_start;
+    uint32_t excl = 0;
+    if (tile != 0) {
+      const uint32_t* prev = st - MSD_BINS;
+      for (;;) {
+        uint32_t s;
+        do { s = ld_relaxed_u32(prev); } while ((s & (MSD_FLAG_AGG | MSD_FLAG_PREFIX)) == 0u);
+        excl += s & MSD_VALUE_MASK;
+        if (s & MSD_FLAG_PREFIX) break;
+        prev -= MSD_BINS;
+      }
+    }
+    st_relaxed_u32(st, MSD_FLAG_PREFIX | (excl + block_count));
+    S.digit_global[d] = bucket_start[d] + excl - local_start;
+  }
+  __syncthreads();
+#pragma unroll
+  for (int i = 0; i < MSD_ITEMS; ++i) {
+    const size_t g = warp_base + (size_t)i * 32 + lane;
+    if (g < (size_t)n) {
+      const uint32_t d = (uint32_t)(word[i] >> shift);
+      S.exch[S.digit_local[d] + S.warp_hist[warp][d] + rank[i]] = word[i];
+    }
+  }
+  __syncthreads();
+  const uint32_t valid = (uint32_t)min((size_t)MSD_TILE, (size_t)n - block_base);
+#pragma unroll
+  for (int m = 0; m < MSD_ITEMS; ++m) {
+    const uint32_t k = m * MSD_THREADS + tid;
+    if (k < valid) {
+      const uint64_t w = S.exch[k];
+      out[S.digit_global[(uint32_t)(w >> shift)] + k] = w;
+    }
+  }
+}
+
+// ---------------------------------------------------------------------------------------------
+// one CTA sorts one bucket on the remaining key bits, emits index list, keys and tile ranges
+// ---------------------------------------------------------------------------------------------
+struct BucketSmem {
+  uint64_t buf[2][BK_CAP];                   // 2 x 96 KB
+  uint16_t warp_hist[BK_WARPS][BK_RADIX];    // 32 KB: per-warp digit counts, then exclusive offsets
+  uint32_t digit_start[BK_RADIX];
+  uint32_t warp_sums[BK_RADIX / 32];
+};
+static_assert(sizeof(BucketSmem) <= 227 * 1024, "bucket sorter exceeds the 227 KB a CTA can have");
+static_assert(sizeof(uint32_t) * BK_WARPS * BK_RADIX <= sizeof(uint64_t) * BK_CAP, "overflow counters alias buf[0]");
+
+// One stable counting pass A -> B on digit (word >> shift) & mask. Each warp owns a contiguous
+// chunk of A; sweep 1 counts per (warp, digit), sweep 2 re-walks the chunk and places every item
+// at digit_start + warp offset + running count, which keeps the pass stable.
+// `hist` is [BK_WARPS][BK_RADIX]: 16-bit counters in S.warp_hist for buckets held in shared memory
+// (a warp's chunk is at most 384 items), 32-bit counters aliased on the unused S.buf[0] for
+// overflow buckets that live in global memory.
+template <typename CNT>
+__device__ __forceinline__ void bucket_pass(BucketSmem& S, CNT* hist, const uint64_t* A, uint64_t* B,
+                                            uint32_t n, int shift, uint32_t mask) {
+  const unsigned tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  const unsigned lt_mask = (1u << lane) - 1u;
+  for (int i = tid; i < BK_WARPS * BK_RADIX; i += BK_THREADS) hist[i] = 0;
+  __syncthreads();
+  const uint32_t chunk = ((n + BK_WARPS - 1) / BK_WARPS + 31u) & ~31u;   // per warp, multiple of 32
+  const uint32_t begin = warp * chunk;
+  const uint32_t end = min(n, begin + chunk);
+  for (uint32_t i = begin + lane; i < begin + chunk && begin < end; i += 32) {
+    const bool ok = i < end;
+    const uint32_t d = ok ? (uint32_t)(A[i] >> shift) & mask : 0u;
+    const uint32_t peers = __match_any_sync(0xffffffffu, ok ? d : (0x10000u + lane));
+    if (ok && (peers & lt_mask) == 0u) hist[warp * BK_RADIX + d] += (CNT)__popc(peers);   // only this warp writes its row
+    __syncwarp();
+    if (i - lane + 32 >= end) break;   // warp-uniform: last round of this chunk
+  }
+  __syncthreads();
+  if (tid < BK_RADIX) {
+    uint32_t run = 0;
+#pragma unroll 8
+    for (int w = 0; w < BK_WARPS; ++w) {
+      const uint32_t c = hist[w * BK_RADIX + tid];
+      hist[w * BK_RADIX + tid] = (CNT)run;
+      run += c;
+    }
+    uint32_t incl = run;
+#pragma unroll
+    for (int s = 1; s < 32; s <<= 1) {
+      const uint32_t t = __shfl_up_sync(0xffffffffu, incl, s);
+      if (lane >= s) incl += t;
+    }
+    if (lane == 31) S.warp_sums[warp] = incl;
+    S.digit_start[tid] = incl - run;   // exclusive within the warp of digits; warp offset added below
+  }
+  __syncthreads();
+  if (tid < BK_RADIX) {
+    uint32_t woff = 0;
+    for (unsigned w = 0; w < warp; ++w) woff += S.warp_sums[w];
+    S.digit_start[tid] += woff;
+  }
+  __syncthreads();
+  for (uint32_t i = begin + lane; i < begin + chunk && begin < end; i += 32) {
+    const bool ok = i < end;
+    const uint64_t w = ok ? A[i] : 0ull;
+    const uint32_t d = ok ? (uint32_t)(w >> shift) & mask : 0u;
+    const uint32_t peers = __match_any_sync(0xffffffffu, ok ? d : (0x10000u + lane));
+    if (ok) {
+      const uint32_t before = hist[warp * BK_RADIX + d];
+      B[S.digit_start[d] + before + __popc(peers & lt_mask)] = w;
+    }
+    __syncwarp();
+    if (ok && (peers & lt_mask) == 0u) hist[warp * BK_RADIX + d] += (CNT)__popc(peers);
+    __syncwarp();
+    if (i - lane + 32 >= end) break;
+  }
+  __syncthreads();
+}
+
+__global__ void __launch_bounds__(BK_THREADS)
+bucket_sort_kernel(uint64_t* __restrict__ words /* partitioned; receives the sorted keys in place */,
+                   uint64_t* __restrict__ scratch /* other ping-pong buffer (overflow buckets) */,
+                   const uint32_t* __restrict__ bucket_start, uint32_t* __restrict__ point_list,
+                   uint2* __restrict__ ranges, int n_tiles, int idx_bits, int bucket_shift,
+                   int rem_bits /* key bits below the bucket digit */) {
+  extern __shared__ __align__(16) unsigned char smem_raw[];
+  BucketSmem& S = *reinterpret_cast<BucketSmem*>(smem_raw);
+  const uint32_t bucket = blockIdx.x;
+  const uint32_t seg = bucket_start[bucket];
+  const uint32_t n = bucket_start[bucket + 1] - seg;
+  const unsigned tid = threadIdx.x;
+
+  // this bucket's tiles: (0, 0) unless found below (the reference zero-fills, rasterizer_impl.cu:311)
+  const uint32_t tile_lo = bucket << bucket_shift;
+  const uint32_t tile_hi = min((uint32_t)n_tiles, (bucket + 1u) << bucket_shift);
+  for (uint32_t t = tile_lo + tid; t < tile_hi; t += BK_THREADS) ranges[t] = make_uint2(0u, 0u);
+  if (n == 0) return;
+
+  const bool in_smem = n <= (uint32_t)BK_CAP;
+  uint64_t* A;
+  uint64_t* B;
+  if (in_smem) {
+    A = S.buf[0];
+    B = S.buf[1];
+    for (uint32_t i = tid; i < n; i += BK_THREADS) A[i] = words[seg + i];
+  } else {
+    A = words + seg;
+    B = scratch + seg;
+  }
+  __syncthreads();
+
+  const int passes = (rem_bits + BK_BITS - 1) / BK_BITS;
+  for (int p = 0; p < passes; ++p) {
+    const int shift = idx_bits + p * BK_BITS;
+    const int width = min(BK_BITS, rem_bits - p * BK_BITS);
+    if (in_smem)
+      bucket_pass<uint16_t>(S, &S.warp_hist[0][0], A, B, n, shift, (1u << width) - 1u);
+    else
+      bucket_pass<uint32_t>(S, reinterpret_cast<uint32_t*>(&S.buf[0][0]), A, B, n, shift, (1u << width) - 1u);
+    uint64_t* t = A;
+    A = B;
+    B = t;
+  }
+
+  // A holds the bucket sorted by (tile, depth bits, index)
+  const uint64_t idx_mask = (1ull << idx_bits) - 1ull;
+  const int tile_shift = idx_bits + 32;
+  for (uint32_t i = tid; i < n; i += BK_THREADS) {
+    const uint64_t w = A[i];
+    const uint32_t tile = (uint32_t)(w >> tile_shift);
+    point_list[seg + i] = (uint32_t)(w & idx_mask);
+    if (i == 0) {
+      ranges[tile].x = seg;
+    } else {
+      const uint32_t prev = (uint32_t)(A[i - 1] >> tile_shift);
+      if (prev != tile) {
+        ranges[prev].y = seg + i;
+        ranges[tile].x = seg + i;
+      }
+    }
+    if (i == n - 1) ranges[tile].y = seg + n;
+  }
+  __syncthreads();   // every A[i - 1] has been read before the in-place overwrite below
+  for (uint32_t i = tid; i < n; i += BK_THREADS) words[seg + i] = A[i] >> idx_bits;
+}
+
+// ---------------------------------------------------------------------------------------------
+// host side
+// ---------------------------------------------------------------------------------------------
+bool bucket_path_ok(int P, int R, int W, int H) {
+  if (!packed_path_fits(P, W, H)) return false;
+  // most buckets must fit in shared memory; otherwise the pure LSD path is the better choice
+  return (long long)R <= (long long)MSD_BINS * BK_CAP * 8 / 10;
+}
+
+int launch_binning_buckets(const GeomPtrs& g, const BinningPtrs& b, const ImagePtrs& im, const int* radii,
+                           int P, int R, int W, int H, cudaStream_t stream, bool debug) {
+  const int gx = tiles_x(W), gy = tiles_y(H);
+  const int n_tiles = gx * gy;
+  if (R == 0) {
+    EGS_CUDA_TRY(cudaMemsetAsync(im.ranges, 0, (size_t)n_tiles * sizeof(uint2), stream));
+    return EGS_OK;
+  }
+  const int ib = tile_id_bits((uint32_t)(P > 1 ? P - 1 : 1));
+  const int tb = tile_id_bits((uint32_t)n_tiles);
+  const int mb = tb < MSD_BITS_MAX ? tb : MSD_BITS_MAX;   // bucket digit = top mb bits of the tile id
+  const int bucket_shift = tb - mb;
+  const int n_buckets = ((n_tiles - 1) >> bucket_shift) + 1;
+  const int rem_bits = bucket_shift + 32;
+  uint32_t* hist = b.hist;                 // [MSD_BINS]
+  uint32_t* start = b.hist + MSD_BINS;     // [MSD_BINS + 1]
+  {
+    StageTimer timer(stream, ST_DUPLICATE);
+    EGS_CUDA_TRY(cudaMemsetAsync(b.hist, 0, b.zero_bytes, stream));
+    duplicate_bucket_kernel<<<(P + 255) / 256, 256, 0, stream>>>(P, g.means2D, g.depths, g.point_offsets, radii,
+                                                                 b.keys[1], gx, gy, ib, bucket_shift, hist);
+    EGS_AFTER_LAUNCH(stream, debug);
+    bucket_scan_kernel<<<1, MSD_BINS, 0, stream>>>(hist, start);
+    EGS_AFTER_LAUNCH(stream, debug);
+  }
+  {
+    StageTimer timer(stream, ST_SORT_HIST);   // reported as the global partition pass
+    EGS_CUDA_TRY(cudaFuncSetAttribute(msd_partition_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                      (int)sizeof(MsdSmem)));
+    msd_partition_kernel<<<(int)b.sort_blocks, MSD_THREADS, sizeof(MsdSmem), stream>>>(
+        b.keys[1], b.keys[0], R, ib + 32 + bucket_shift, start, b.ticket, b.status);
+    EGS_AFTER_LAUNCH(stream, debug);
+  }
+  {
+    StageTimer timer(stream, ST_SORT_PASSES);   // reported as the per-bucket sort
+    EGS_CUDA_TRY(cudaFuncSetAttribute(bucket_sort_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                      (int)sizeof(BucketSmem)));
+    bucket_sort_kernel<<<n_buckets, BK_THREADS, sizeof(BucketSmem), stream>>>(
+        b.keys[0], b.keys[1], start, b.vals[0], im.ranges, n_tiles, ib, bucket_shift, rem_bits);
+    EGS_AFTER_LAUNCH(stream, debug);
+  }
+  return EGS_OK;
+}
+
+}  // namespace egs

@@ -262,28 +262,44 @@ def test_full_size_properties(built, cuda_device):
     assert bool(torch.all(g1["means3D"][f1.radii == 0] == 0))
 
 
-def test_pair_sort_fallback_equals_packed_path(built, cuda_device, monkeypatch):
-    """The general (u64 key, u32 value) pair sort -- taken when tile | depth | index does not fit one
-    64-bit word, forced here with EGS_SORT=pairs -- and the default packed-word sort give identical
-    lists and images."""
+def test_three_binning_paths_agree(built, cuda_device, monkeypatch):
+    """The three binning paths give identical sorted lists, ranges and images: the default
+    MSD-bucket path (one global partition + one CTA per bucket), the packed-word LSD sort
+    (EGS_SORT=packed; taken when R is too large for the bucket sorter) and the (u64 key, u32 value)
+    pair sort (EGS_SORT=pairs; taken when tile | depth | index does not fit one 64-bit word).
+    A second scene with a few huge Gaussians makes some buckets overflow shared memory, which
+    exercises the bucket kernel's global-memory branch."""
     from egogaussian_b200 import cabi, scenes
     dev = cuda_device
-    sc = scenes.make_scene(60_000, 640, 360, sh_degree=1, seed=77).to(dev)
-    cam = sc.camera
-    kw = dict(means3D=sc.means3D, opacities=sc.opacities, bg=sc.bg, viewmatrix=cam.viewmatrix,
-              projmatrix=cam.projmatrix, campos=cam.campos, tanfovx=cam.tanfovx, tanfovy=cam.tanfovy,
-              image_height=360, image_width=640, sh_degree=1, shs=sc.shs, cov3D_precomp=sc.cov3D())
-    monkeypatch.delenv("EGS_SORT", raising=False)
-    a = cabi.forward(**kw)
-    monkeypatch.setenv("EGS_SORT", "pairs")
-    b = cabi.forward(**kw)
-    assert a.num_rendered == b.num_rendered > 0
-    av, bv = a.binning_view(), b.binning_view()
-    assert torch.equal(av["keys"], bv["keys"]) and torch.equal(av["values"], bv["values"])
-    assert torch.equal(a.image_view()["ranges"], b.image_view()["ranges"])
-    assert torch.equal(a.color, b.color) and torch.equal(a.radii, b.radii)
-    gv = a.geom_view()
-    assert torch.equal(gv["point_offsets"].to(torch.int64), torch.cumsum(gv["tiles_touched"].to(torch.int64), 0))
+    for P, W, H, seed, boost in ((60_000, 640, 360, 77, 1.0), (40_000, 256, 144, 78, 6.0)):
+        sc = scenes.make_scene(P, W, H, sh_degree=1, seed=seed)
+        sc.scales = (sc.scales * boost).contiguous()
+        sc = sc.to(dev)
+        cam = sc.camera
+        kw = dict(means3D=sc.means3D, opacities=sc.opacities, bg=sc.bg, viewmatrix=cam.viewmatrix,
+                  projmatrix=cam.projmatrix, campos=cam.campos, tanfovx=cam.tanfovx, tanfovy=cam.tanfovy,
+                  image_height=H, image_width=W, sh_degree=1, shs=sc.shs, cov3D_precomp=sc.cov3D())
+        monkeypatch.delenv("EGS_SORT", raising=False)
+        a = cabi.forward(**kw)
+        assert a.num_rendered > 0
+        av = a.binning_view()
+        keys = av["keys"]
+        assert bool((keys[1:] >= keys[:-1]).all())
+        for forced in ("packed", "pairs"):
+            monkeypatch.setenv("EGS_SORT", forced)
+            b = cabi.forward(**kw)
+            assert a.num_rendered == b.num_rendered
+            bv = b.binning_view()
+            assert torch.equal(av["keys"], bv["keys"]) and torch.equal(av["values"], bv["values"]), forced
+            assert torch.equal(a.image_view()["ranges"], b.image_view()["ranges"]), forced
+            assert torch.equal(a.color, b.color) and torch.equal(a.radii, b.radii), forced
+        gv = a.geom_view()
+        assert torch.equal(gv["point_offsets"].to(torch.int64), torch.cumsum(gv["tiles_touched"].to(torch.int64), 0))
+        if boost > 1.0:   # the stress scene really has buckets beyond the shared-memory capacity
+            tiles = (keys >> 32)
+            n_tiles = ((W + 15) // 16) * ((H + 15) // 16)
+            shift = max(n_tiles.bit_length() - 10, 0)
+            assert int(torch.bincount(tiles >> shift).max()) > 12288
 
 
 def test_adam_and_se3(built, cuda_device):
