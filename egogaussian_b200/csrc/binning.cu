@@ -230,7 +230,7 @@ sort_onesweep_kernel(const uint64_t* __restrict__ keys_in, const uint32_t* __res
     const bool ok = g < (size_t)n;
     const uint32_t d = (uint32_t)(key[i] >> shift) & digit_mask;
     // out-of-range lanes get a private pseudo digit so they never join a peer group
-    const uint32_t peers = __match_any_sync(0xffffffffu, ok ? d : (0x10000u + lane));
+    const uint32_t peers = match_digit<SORT_RADIX_BITS>(d, ok);
     const uint32_t before = ok ? s_warp_hist[warp][d] : 0u;
     __syncwarp();
     if (ok && (peers & lt_mask) == 0u) s_warp_hist[warp][d] = before + __popc(peers);

@@ -52,8 +52,9 @@ duplicate_bucket_kernel(int P, const float2* __restrict__ means2D, const float* 
   __shared__ uint32_t s_hist[MSD_BINS];
   for (int i = threadIdx.x; i < MSD_BINS; i += blockDim.x) s_hist[i] = 0;
   __syncthreads();
-  const int idx = blockIdx.x * blockDim.x + threadIdx.x;
-  if (idx < P) {
+  // grid-stride: a fixed, small grid keeps the number of global histogram flushes (up to 1024
+  // reductions per CTA) far below the number of instances
+  for (int idx = blockIdx.x * blockDim.x + threadIdx.x; idx < P; idx += gridDim.x * blockDim.x) {
     const int r = radii[idx];
     if (r > 0) {
       uint32_t off = (idx == 0) ? 0u : offsets[idx - 1];
@@ -156,7 +157,7 @@ msd_partition_kernel(const uint64_t* __restrict__ in, uint64_t* __restrict__ out
     const size_t g = warp_base + (size_t)i * 32 + lane;
     const bool ok = g < (size_t)n;
     const uint32_t d = (uint32_t)(word[i] >> shift);
-    const uint32_t peers = __match_any_sync(0xffffffffu, ok ? d : (0x10000u + lane));
+    const uint32_t peers = match_digit<MSD_BITS_MAX>(d, ok);
     const uint32_t before = ok ? S.warp_hist[warp][d] : 0u;
     __syncwarp();
     if (ok && (peers & lt_mask) == 0u) S.warp_hist[warp][d] = (uint16_t)(before + __popc(peers));
@@ -235,8 +236,80 @@ struct BucketSmem {
 static_assert(sizeof(BucketSmem) <= 227 * 1024, "bucket sorter exceeds the 227 KB a CTA can have");
 static_assert(sizeof(uint32_t) * BK_WARPS * BK_RADIX <= sizeof(uint64_t) * BK_CAP, "overflow counters alias buf[0]");
 
-// One stable counting pass A -> B on digit (word >> shift) & mask. Each warp owns a contiguous
-// chunk of A; sweep 1 counts per (warp, digit), sweep 2 re-walks the chunk and places every item
+// Stable counting pass for a bucket held in shared memory (the common case). Each warp owns a
+// contiguous chunk of at most BK_ROUNDS * 32 items of A and ranks them once: an item's rank among
+// the warp's earlier items with the same digit stays in a register while the per-warp counts are
+// scanned, then the item is placed at digit start + warp offset + rank.
+constexpr int BK_ROUNDS = ((BK_CAP + BK_WARPS - 1) / BK_WARPS + 31) / 32;   // 12
+
+__device__ __forceinline__ void bucket_pass_smem(BucketSmem& S, const uint64_t* A, uint64_t* B, uint32_t n,
+                                                 int shift, uint32_t mask) {
+  const unsigned tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  const unsigned lt_mask = (1u << lane) - 1u;
+  uint16_t* hist = &S.warp_hist[0][0];
+  {
+    uint32_t* z = reinterpret_cast<uint32_t*>(hist);
+    for (int i = tid; i < BK_WARPS * BK_RADIX / 2; i += BK_THREADS) z[i] = 0;
+  }
+  __syncthreads();
+  const uint32_t chunk = ((n + BK_WARPS - 1) / BK_WARPS + 31u) & ~31u;
+  const uint32_t begin = warp * chunk;
+  const uint32_t end = min(n, begin + chunk);
+  uint16_t rank[BK_ROUNDS];
+#pragma unroll
+  for (int r = 0; r < BK_ROUNDS; ++r) {
+    const uint32_t row = begin + r * 32;
+    if (row < end) {   // warp-uniform
+      const uint32_t i = row + lane;
+      const bool ok = i < end;
+      const uint32_t d = ok ? (uint32_t)(A[i] >> shift) & mask : 0u;
+      const uint32_t peers = match_digit<BK_BITS>(d, ok);
+      const uint32_t before = ok ? hist[warp * BK_RADIX + d] : 0u;
+      __syncwarp();
+      if (ok && (peers & lt_mask) == 0u) hist[warp * BK_RADIX + d] = (uint16_t)(before + __popc(peers));
+      __syncwarp();
+      rank[r] = (uint16_t)(before + __popc(peers & lt_mask));
+    }
+  }
+  __syncthreads();
+  if (tid < BK_RADIX) {
+    uint32_t run = 0;
+#pragma unroll 8
+    for (int w = 0; w < BK_WARPS; ++w) {
+      const uint32_t c = hist[w * BK_RADIX + tid];
+      hist[w * BK_RADIX + tid] = (uint16_t)run;
+      run += c;
+    }
+    uint32_t incl = run;
+#pragma unroll
+    for (int s = 1; s < 32; s <<= 1) {
+      const uint32_t t = __shfl_up_sync(0xffffffffu, incl, s);
+      if (lane >= s) incl += t;
+    }
+    if (lane == 31) S.warp_sums[warp] = incl;
+    S.digit_start[tid] = incl - run;
+  }
+  __syncthreads();
+  if (tid < BK_RADIX) {
+    uint32_t woff = 0;
+    for (unsigned w = 0; w < warp; ++w) woff += S.warp_sums[w];
+    S.digit_start[tid] += woff;
+  }
+  __syncthreads();
+#pragma unroll
+  for (int r = 0; r < BK_ROUNDS; ++r) {
+    const uint32_t i = begin + r * 32 + lane;
+    if (i < end) {
+      const uint64_t w = A[i];
+      const uint32_t d = (uint32_t)(w >> shift) & mask;
+      B[S.digit_start[d] + hist[warp * BK_RADIX + d] + rank[r]] = w;
+    }
+  }
+  __syncthreads();
+}
+
+// General form of the same pass, for overflow buckets that stay in global memory: each warp owns a
+// contiguous chunk of A; sweep 1 counts per (warp, digit), sweep 2 re-walks the chunk and places every item
 // at digit_start + warp offset + running count, which keeps the pass stable.
 // `hist` is [BK_WARPS][BK_RADIX]: 16-bit counters in S.warp_hist for buckets held in shared memory
 // (a warp's chunk is at most 384 items), 32-bit counters aliased on the unused S.buf[0] for
@@ -254,7 +327,7 @@ __device__ __forceinline__ void bucket_pass(BucketSmem& S, CNT* hist, const uint
   for (uint32_t i = begin + lane; i < begin + chunk && begin < end; i += 32) {
     const bool ok = i < end;
     const uint32_t d = ok ? (uint32_t)(A[i] >> shift) & mask : 0u;
-    const uint32_t peers = __match_any_sync(0xffffffffu, ok ? d : (0x10000u + lane));
+    const uint32_t peers = match_digit<BK_BITS>(d, ok);
     if (ok && (peers & lt_mask) == 0u) hist[warp * BK_RADIX + d] += (CNT)__popc(peers);   // only this warp writes its row
     __syncwarp();
     if (i - lane + 32 >= end) break;   // warp-uniform: last round of this chunk
@@ -288,7 +361,7 @@ __device__ __forceinline__ void bucket_pass(BucketSmem& S, CNT* hist, const uint
     const bool ok = i < end;
     const uint64_t w = ok ? A[i] : 0ull;
     const uint32_t d = ok ? (uint32_t)(w >> shift) & mask : 0u;
-    const uint32_t peers = __match_any_sync(0xffffffffu, ok ? d : (0x10000u + lane));
+    const uint32_t peers = match_digit<BK_BITS>(d, ok);
     if (ok) {
       const uint32_t before = hist[warp * BK_RADIX + d];
       B[S.digit_start[d] + before + __popc(peers & lt_mask)] = w;
@@ -338,7 +411,7 @@ bucket_sort_kernel(uint64_t* __restrict__ words /* partitioned; receives the sor
     const int shift = idx_bits + p * BK_BITS;
     const int width = min(BK_BITS, rem_bits - p * BK_BITS);
     if (in_smem)
-      bucket_pass<uint16_t>(S, &S.warp_hist[0][0], A, B, n, shift, (1u << width) - 1u);
+      bucket_pass_smem(S, A, B, n, shift, (1u << width) - 1u);
     else
       bucket_pass<uint32_t>(S, reinterpret_cast<uint32_t*>(&S.buf[0][0]), A, B, n, shift, (1u << width) - 1u);
     uint64_t* t = A;
@@ -396,8 +469,10 @@ int launch_binning_buckets(const GeomPtrs& g, const BinningPtrs& b, const ImageP
   {
     StageTimer timer(stream, ST_DUPLICATE);
     EGS_CUDA_TRY(cudaMemsetAsync(b.hist, 0, b.zero_bytes, stream));
-    duplicate_bucket_kernel<<<(P + 255) / 256, 256, 0, stream>>>(P, g.means2D, g.depths, g.point_offsets, radii,
-                                                                 b.keys[1], gx, gy, ib, bucket_shift, hist);
+    int dup_blocks = (P + 255) / 256;
+    if (dup_blocks > 148 * 8) dup_blocks = 148 * 8;
+    duplicate_bucket_kernel<<<dup_blocks, 256, 0, stream>>>(P, g.means2D, g.depths, g.point_offsets, radii,
+                                                            b.keys[1], gx, gy, ib, bucket_shift, hist);
     EGS_AFTER_LAUNCH(stream, debug);
     bucket_scan_kernel<<<1, MSD_BINS, 0, stream>>>(hist, start);
     EGS_AFTER_LAUNCH(stream, debug);

@@ -162,7 +162,7 @@ packed_onesweep_kernel(const uint64_t* __restrict__ in, uint64_t* __restrict__ o
     const size_t g = warp_base + (size_t)i * 32 + lane;
     const bool ok = g < (size_t)n;
     const uint32_t d = (uint32_t)(word[i] >> shift) & digit_mask;
-    const uint32_t peers = __match_any_sync(0xffffffffu, ok ? d : (0x10000u + lane));
+    const uint32_t peers = match_digit<PK_BITS>(d, ok);
     const uint32_t before = ok ? S.warp_hist[warp][d] : 0u;
     __syncwarp();
     if (ok && (peers & lt_mask) == 0u) S.warp_hist[warp][d] = before + __popc(peers);

@@ -328,5 +328,20 @@ __device__ __forceinline__ void tile_rect(const float2 p, int r, int gx, int gy,
 
 __device__ __forceinline__ unsigned lane_id() { return threadIdx.x & 31; }
 
+// Lanes of the warp that are valid and hold the same BITS-bit digit as this lane. One ballot per
+// digit bit (fixed cost, independent ballots pipeline) instead of the match.any instruction, whose
+// cost grows with the number of distinct values in the warp.
+template <int BITS>
+__device__ __forceinline__ uint32_t match_digit(uint32_t d, bool ok) {
+  uint32_t peers = __ballot_sync(0xffffffffu, ok);
+#pragma unroll
+  for (int b = 0; b < BITS; ++b) {
+    const bool bit = (d >> b) & 1u;
+    const uint32_t bal = __ballot_sync(0xffffffffu, bit);
+    peers &= bit ? bal : ~bal;
+  }
+  return peers;
+}
+
 }  // namespace egs
 #endif  // __CUDACC__
