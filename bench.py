@@ -276,8 +276,17 @@ def run_ours(a, rank, world, local_rank):
         h2d = sum(v.numel() * 4 for v in host.values())
         loss_host = torch.empty((), dtype=torch.float32).pin_memory()
 
+        copy_stream, copied = torch.cuda.Stream(device=device), torch.cuda.Event()
+
         def e2e_step():
-            for k in dv:
+            # the big host inputs (the upstream-gradient images, standing in for the ground-truth
+            # frame) are not needed before the loss: prefetch them on a side stream while the
+            # forward runs; the camera matrices are needed at once and go on the main stream
+            with torch.cuda.stream(copy_stream):
+                for k in ("wc", "wd", "wa"):
+                    dv[k].copy_(host[k], non_blocking=True)
+                copied.record()
+            for k in ("viewmatrix", "projmatrix", "campos"):
                 dv[k].copy_(host[k], non_blocking=True)
             rs = GaussianRasterizationSettings(a.height, a.width, kw["tanfovx"], kw["tanfovy"], kw["bg"], 1.0,
                                                dv["viewmatrix"], dv["projmatrix"], a.sh_degree, dv["campos"], False, False)
@@ -285,6 +294,7 @@ def run_ours(a, rank, world, local_rank):
             color, radii, depth, alpha = GaussianRasterizer(rs)(
                 means3D=leaves["means3D"], means2D=means2D, opacities=leaves["opacities"], shs=leaves["shs"],
                 scales=leaves.get("scales"), rotations=leaves.get("rotations"), cov3D_precomp=leaves.get("cov3D_precomp"))
+            torch.cuda.current_stream().wait_event(copied)
             loss = (color * dv["wc"]).sum() + (depth * dv["wd"]).sum() + (alpha * dv["wa"]).sum()
             loss.backward()
             if dist_on:
@@ -383,8 +393,15 @@ def run_reference(a, rank, world, local_rank):
     h2d = sum(v.numel() * 4 for v in host.values())
     loss_host = torch.empty((), dtype=torch.float32).pin_memory()
 
+    copy_stream, copied = torch.cuda.Stream(device=device), torch.cuda.Event()
+
     def e2e_step():
-        for k in dv:
+        # same host-input schedule as our arm: images prefetched on a side stream, camera first
+        with torch.cuda.stream(copy_stream):
+            for k in ("wc", "wd", "wa"):
+                dv[k].copy_(host[k], non_blocking=True)
+            copied.record()
+        for k in ("viewmatrix", "projmatrix", "campos"):
             dv[k].copy_(host[k], non_blocking=True)
         rs = dict(bg=kw["bg"], scale_modifier=1.0, viewmatrix=dv["viewmatrix"], projmatrix=dv["projmatrix"],
                   tanfovx=kw["tanfovx"], tanfovy=kw["tanfovy"], image_height=a.height, image_width=a.width,
@@ -393,6 +410,7 @@ def run_reference(a, rank, world, local_rank):
         color, radii, depth, alpha = rast(rs, means3D=leaves["means3D"], means2D=means2D, opacities=leaves["opacities"],
                                           shs=leaves["shs"], scales=leaves.get("scales"), rotations=leaves.get("rotations"),
                                           cov3D_precomp=leaves.get("cov3D_precomp"))
+        torch.cuda.current_stream().wait_event(copied)
         loss = (color * dv["wc"]).sum() + (depth * dv["wd"]).sum() + (alpha * dv["wa"]).sum()
         loss.backward()
         loss_host.copy_(loss.detach(), non_blocking=True)

@@ -261,6 +261,19 @@ blend_backward_kernel(const uint2* __restrict__ ranges, const uint32_t* __restri
 constexpr int BWD2_THREADS = 128;
 constexpr int BWD2_BATCH = 128;
 
+// single-instruction hardware approximations (MUFU.EX2 / MUFU.RCP, flush-to-zero): the __expf and
+// __fdividef intrinsics wrap them in denormal-range fix-ups that cost more than the operation
+__device__ __forceinline__ float ex2_approx(float x) {
+  float y;
+  asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
+  return y;
+}
+__device__ __forceinline__ float rcp_approx(float x) {
+  float y;
+  asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
+  return y;
+}
+
 struct PixelState {
   float T, T_final, accum_rec[3], accum_depth, accum_alpha, last_alpha, last_color[3], last_depth;
   float dL_dpixel[3], dL_ddepth, dL_dalpha, bg_dot;
@@ -297,9 +310,9 @@ __device__ __forceinline__ void fragment_backward(PixelState& s, float dx, float
                                                   const float4 a4, const float4 b4, const float4 c4,
                                                   float ddelx_dx, float ddely_dy, float (&q)[10]) {
   const float opac = a4.w;
-  const float G = __expf(power);
+  const float G = ex2_approx(power * 1.4426950408889634f);
   const float alpha = fminf(0.99f, opac * G);
-  const float rcp = __fdividef(1.f, 1.f - alpha);
+  const float rcp = rcp_approx(1.f - alpha);
   s.T = s.T * rcp;
   const float w = alpha * s.T;
   float dL_dopa = 0.0f;
@@ -347,7 +360,10 @@ blend_backward2_kernel(const uint2* __restrict__ ranges, const uint32_t* __restr
   __shared__ float4 s_a[BWD2_BATCH];   // mean.x, mean.y, thr = -log(255 o), opacity
   __shared__ float4 s_b[BWD2_BATCH];   // conic.x, conic.y, conic.z, depth
   __shared__ float4 s_c[BWD2_BATCH];   // r, g, b, -
-  __shared__ float s_acc[BWD2_BATCH * ACC_PITCH];
+  // one accumulator row per warp: a warp meets each entry of a batch once, so its total is a plain
+  // store (shared-memory float atomicAdd is a compare-and-swap loop on this architecture)
+  __shared__ float s_acc[(BWD2_THREADS / 32) * BWD2_BATCH * ACC_PITCH];
+  __shared__ uint32_t s_hit[BWD2_BATCH];   // bit w: warp w stored totals for this entry in this batch
   __shared__ uint32_t s_max_contrib;
 
   const unsigned tid = threadIdx.x;
@@ -398,8 +414,7 @@ blend_backward2_kernel(const uint2* __restrict__ ranges, const uint32_t* __restr
       s_b[tid] = make_float4(co.x, co.y, co.z, cd.w);
       s_c[tid] = cd;
     }
-#pragma unroll
-    for (int k = 0; k < ACC_PITCH; ++k) s_acc[k * BWD2_BATCH + tid] = 0.f;
+    s_hit[tid] = 0u;
     __syncthreads();
 
     const int n = min(BWD2_BATCH, walk - r * BWD2_BATCH);
@@ -423,19 +438,26 @@ blend_backward2_kernel(const uint2* __restrict__ ranges, const uint32_t* __restr
       if (act0) fragment_backward(P0, dx0, dy0, power0, a4, b4, c4, ddelx_dx, ddely_dy, q);
       if (act1) fragment_backward(P1, dx1, dy1, power1, a4, b4, c4, ddelx_dx, ddely_dy, q);
       const float total = warp_packed_reduce10(q, lane);
-      if (i_add) atomicAdd(&s_acc[j * ACC_PITCH + my_slot], total);
+      if (i_add) s_acc[(warp * BWD2_BATCH + j) * ACC_PITCH + my_slot] = total;
+      if (lane == 0) atomicOr(&s_hit[j], 1u << warp);
     }
     __syncthreads();
 
     if ((int)tid < n) {
       float v[ACC_STRIDE];
-      bool any = false;
 #pragma unroll
-      for (int k = 0; k < ACC_STRIDE; ++k) {
-        v[k] = s_acc[tid * ACC_PITCH + k];
-        any = any || (v[k] != 0.f);
+      for (int k = 0; k < ACC_STRIDE; ++k) v[k] = 0.f;
+      const uint32_t hit = s_hit[tid];
+#pragma unroll
+      for (int w = 0; w < BWD2_THREADS / 32; ++w) {
+        if (hit & (1u << w)) {
+          const float* row = &s_acc[(w * BWD2_BATCH + tid) * ACC_PITCH];
+#pragma unroll
+          for (int k = 0; k < ACC_STRIDE; ++k)
+            if (k != 7 && k != 11) v[k] += row[k];   // slots 7 and 11 are padding, never written
+        }
       }
-      if (any) {
+      if (hit) {
         float4* dst = acc + (size_t)s_id[tid] * 3;
         atomicAdd(dst + 0, make_float4(v[0], v[1], v[2], v[3]));
         atomicAdd(dst + 1, make_float4(v[4], v[5], v[6], v[7]));

@@ -13,6 +13,9 @@
 //     transmittance thresholds make the image sensitive to the last bit of `power`.
 #include "common.cuh"
 
+#include <stdlib.h>
+#include <string.h>
+
 namespace egs {
 
 constexpr int BLEND_BATCH = 256;
@@ -98,13 +101,145 @@ blend_forward_kernel(const uint2* __restrict__ ranges, const uint32_t* __restric
   }
 }
 
+// ---------------------------------------------------------------------------------------------
+// v2: two pixels per thread + a conservative log-domain pre-filter
+// ---------------------------------------------------------------------------------------------
+// Bit-identical results to the kernel above (and so to the reference): every fragment that is
+// blended goes through the same expression shapes (exact expf, same products and sums). What
+// changes is only how much work surrounds them:
+//   * 128 threads per tile; a thread owns (x, y) and (x, y + 4) of its warp's 8x8 block, so the
+//     staged entry is read from shared memory once per two pixels and the loop overhead halves;
+//   * `alpha = o * exp(power) < 1/255` is decided without the exponential whenever
+//     power < thr - 1e-4 with thr = -log(255 o): expf is accurate to 2 ulp and the threshold to a
+//     few 1e-7, so everything below that margin is certainly skipped by the reference too;
+//     fragments inside the margin take the exact test. No decision can differ.
+constexpr int FWD2_THREADS = 128;
+constexpr int FWD2_BATCH = 256;
+
+struct FwdPixel {
+  float px, py, T, C0, C1, C2, weight, D;
+  uint32_t last;
+  bool done;
+};
+
+__device__ __forceinline__ void fwd_fragment(FwdPixel& s, const float4 a4, const float4 con_o, const float4 cd,
+                                             uint32_t contributor) {
+  const float2 d = make_float2(a4.x - s.px, a4.y - s.py);
+  const float power = -0.5f * (con_o.x * d.x * d.x + con_o.z * d.y * d.y) - con_o.y * d.x * d.y;
+  if (power > 0.0f) return;
+  if (power < a4.z) return;   // certainly alpha < 1/255 (conservative margin, see above)
+  const float alpha = min(0.99f, con_o.w * expf(power));
+  if (alpha < 1.0f / 255.0f) return;
+  const float test_T = s.T * (1 - alpha);
+  if (test_T < 0.0001f) {
+    s.done = true;
+    return;
+  }
+  s.C0 += cd.x * alpha * s.T;
+  s.C1 += cd.y * alpha * s.T;
+  s.C2 += cd.z * alpha * s.T;
+  s.weight += alpha * s.T;
+  s.D += cd.w * alpha * s.T;
+  s.T = test_T;
+  s.last = contributor;
+}
+
+__global__ void __launch_bounds__(FWD2_THREADS)
+blend_forward2_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__ point_list,
+                      int W, int H, int grid_x, const float2* __restrict__ means2D,
+                      const float4* __restrict__ conic_opacity, const float4* __restrict__ rgb_depth,
+                      const float* __restrict__ bg_color, float* __restrict__ out_color,
+                      float* __restrict__ out_depth, float* __restrict__ out_alpha,
+                      uint32_t* __restrict__ n_contrib) {
+  __shared__ float4 s_a[FWD2_BATCH];   // mean.x, mean.y, skip threshold, -
+  __shared__ float4 s_co[FWD2_BATCH];
+  __shared__ float4 s_cd[FWD2_BATCH];
+
+  const unsigned tid = threadIdx.x;
+  const unsigned warp = tid >> 5, lane = tid & 31;
+  const unsigned bx = blockIdx.x * TILE_X + (warp & 1) * 8 + (lane & 7);
+  const unsigned by = blockIdx.y * TILE_Y + (warp >> 1) * 8 + (lane >> 3);
+  FwdPixel P0, P1;
+  const bool in0 = bx < (unsigned)W && by < (unsigned)H;
+  const bool in1 = bx < (unsigned)W && (by + 4) < (unsigned)H;
+  P0 = FwdPixel{(float)bx, (float)by, 1.0f, 0.f, 0.f, 0.f, 0.f, 0.f, 0u, !in0};
+  P1 = FwdPixel{(float)bx, (float)(by + 4), 1.0f, 0.f, 0.f, 0.f, 0.f, 0.f, 0u, !in1};
+
+  const uint2 range = ranges[blockIdx.y * grid_x + blockIdx.x];
+  const int total = (int)(range.y - range.x);
+  const int rounds = (total + FWD2_BATCH - 1) / FWD2_BATCH;
+  int to_do = total;
+  uint32_t contributor = 0;
+
+  for (int r = 0; r < rounds; ++r, to_do -= FWD2_BATCH) {
+    if (__syncthreads_count(P0.done && P1.done) == FWD2_THREADS) break;
+#pragma unroll
+    for (int h = 0; h < FWD2_BATCH / FWD2_THREADS; ++h) {
+      const int slot = h * FWD2_THREADS + (int)tid;
+      const int progress = r * FWD2_BATCH + slot;
+      if (progress < total) {
+        const uint32_t id = point_list[range.x + progress];
+        const float2 xy = means2D[id];
+        const float4 co = conic_opacity[id];
+        // below this power the fragment's alpha is certainly < 1/255; NaN / non-positive opacity
+        // disables the pre-filter (the comparison power < NaN is false) and leaves the exact test
+        const float thr = co.w > 0.f ? -logf(255.f * co.w) - 1e-4f : __int_as_float(0x7fc00000);
+        s_a[slot] = make_float4(xy.x, xy.y, thr, 0.f);
+        s_co[slot] = co;
+        s_cd[slot] = rgb_depth[id];
+      }
+    }
+    __syncthreads();
+    if (__all_sync(0xffffffffu, P0.done && P1.done)) continue;
+
+    const int n = min(FWD2_BATCH, to_do);
+    for (int j = 0; j < n; ++j) {
+      if (P0.done && P1.done) break;
+      contributor++;
+      const float4 a4 = s_a[j];
+      const float4 con_o = s_co[j];
+      const float4 cd = s_cd[j];
+      if (!P0.done) fwd_fragment(P0, a4, con_o, cd, contributor);
+      if (!P1.done) fwd_fragment(P1, a4, con_o, cd, contributor);
+    }
+  }
+
+  const size_t plane = (size_t)H * W;
+  if (in0) {
+    const uint32_t pix = (uint32_t)W * by + bx;
+    n_contrib[pix] = P0.last;
+    out_color[pix] = P0.C0 + P0.T * bg_color[0];
+    out_color[plane + pix] = P0.C1 + P0.T * bg_color[1];
+    out_color[2 * plane + pix] = P0.C2 + P0.T * bg_color[2];
+    out_alpha[pix] = P0.weight;
+    out_depth[pix] = P0.D;
+  }
+  if (in1) {
+    const uint32_t pix = (uint32_t)W * (by + 4) + bx;
+    n_contrib[pix] = P1.last;
+    out_color[pix] = P1.C0 + P1.T * bg_color[0];
+    out_color[plane + pix] = P1.C1 + P1.T * bg_color[1];
+    out_color[2 * plane + pix] = P1.C2 + P1.T * bg_color[2];
+    out_alpha[pix] = P1.weight;
+    out_depth[pix] = P1.D;
+  }
+}
+
 int launch_blend_forward(const EgsForwardArgs& a, const GeomPtrs& g, const uint32_t* point_list,
                          const ImagePtrs& im, cudaStream_t stream) {
   const dim3 grid(tiles_x(a.width), tiles_y(a.height), 1);
   StageTimer timer(stream, ST_BLEND_FWD);
-  blend_forward_kernel<<<grid, TILE_PIXELS, 0, stream>>>(
-      im.ranges, point_list, a.width, a.height, (int)grid.x, g.means2D, g.conic_opacity,
-      g.rgb_depth, a.background, a.out_color, a.out_depth, a.out_alpha, im.n_contrib);
+  // EGS_FWD=v1 selects the one-pixel-per-thread kernel (A/B runs); results are bit-identical
+  const char* sel = getenv("EGS_FWD");
+  if (sel && strcmp(sel, "v1") == 0) {
+    blend_forward_kernel<<<grid, TILE_PIXELS, 0, stream>>>(
+        im.ranges, point_list, a.width, a.height, (int)grid.x, g.means2D, g.conic_opacity,
+        g.rgb_depth, a.background, a.out_color, a.out_depth, a.out_alpha, im.n_contrib);
+  } else {
+    blend_forward2_kernel<<<grid, FWD2_THREADS, 0, stream>>>(
+        im.ranges, point_list, a.width, a.height, (int)grid.x, g.means2D, g.conic_opacity,
+        g.rgb_depth, a.background, a.out_color, a.out_depth, a.out_alpha, im.n_contrib);
+  }
   EGS_AFTER_LAUNCH(stream, a.debug);
   return EGS_OK;
 }
