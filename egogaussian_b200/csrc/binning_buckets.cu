@@ -41,41 +41,59 @@ constexpr int BK_RADIX = 1 << BK_BITS;             // 512
 constexpr int BK_CAP = 12288;                      // words per bucket held in shared memory (2 buffers)
 
 // ---------------------------------------------------------------------------------------------
-// duplicate + bucket histogram
+// duplicate, then bucket histogram
 // ---------------------------------------------------------------------------------------------
+// One packed word (tile | depth bits | index) per instance, in Gaussian-index order
+// (duplicateWithKeys, rasterizer_impl.cu:70-111).
 __global__ void __launch_bounds__(256)
-duplicate_bucket_kernel(int P, const float2* __restrict__ means2D, const float* __restrict__ depths,
-                        const uint32_t* __restrict__ offsets, const int* __restrict__ radii,
-                        uint64_t* __restrict__ words, int grid_x, int grid_y, int idx_bits,
-                        int bucket_shift /* tile id >> bucket_shift = bucket */,
-                        uint32_t* __restrict__ bucket_hist) {
+duplicate_words_kernel(int P, const float2* __restrict__ means2D, const float* __restrict__ depths,
+                       const uint32_t* __restrict__ offsets, const int* __restrict__ radii,
+                       uint64_t* __restrict__ words, int grid_x, int grid_y, int idx_bits) {
+  const int idx = blockIdx.x * blockDim.x + threadIdx.x;
+  if (idx >= P) return;
+  const int r = radii[idx];
+  if (r <= 0) return;
+  uint32_t off = (idx == 0) ? 0u : offsets[idx - 1];
+  uint2 lo, hi;
+  tile_rect(means2D[idx], r, grid_x, grid_y, lo, hi);
+  const uint64_t low = ((uint64_t)__float_as_uint(depths[idx]) << idx_bits) | (uint32_t)idx;
+  const int tile_shift = 32 + idx_bits;
+  for (uint32_t y = lo.y; y < hi.y; ++y)
+    for (uint32_t x = lo.x; x < hi.x; ++x)
+      words[off++] = ((uint64_t)(y * (uint32_t)grid_x + x) << tile_shift) | low;
+}
+
+// Bucket histogram of the word list. A thread takes 8 consecutive words -- the instances of one
+// Gaussian are consecutive and mostly fall into one or two buckets -- and adds run lengths, so the
+// shared-memory atomics are a fraction of the word count.
+constexpr int BH_ITEMS = 8;
+__global__ void __launch_bounds__(256)
+bucket_histogram_kernel(const uint64_t* __restrict__ words, int n, int shift, uint32_t* __restrict__ bucket_hist) {
   __shared__ uint32_t s_hist[MSD_BINS];
   for (int i = threadIdx.x; i < MSD_BINS; i += blockDim.x) s_hist[i] = 0;
   __syncthreads();
-  // grid-stride: a fixed, small grid keeps the number of global histogram flushes (up to 1024
-  // reductions per CTA) far below the number of instances
-  for (int idx = blockIdx.x * blockDim.x + threadIdx.x; idx < P; idx += gridDim.x * blockDim.x) {
-    const int r = radii[idx];
-    if (r > 0) {
-      uint32_t off = (idx == 0) ? 0u : offsets[idx - 1];
-      uint2 lo, hi;
-      tile_rect(means2D[idx], r, grid_x, grid_y, lo, hi);
-      const uint64_t low = ((uint64_t)__float_as_uint(depths[idx]) << idx_bits) | (uint32_t)idx;
-      const int tile_shift = 32 + idx_bits;
-      for (uint32_t y = lo.y; y < hi.y; ++y) {
-        // a row of the rectangle is a run of consecutive tile ids: count it per bucket in one go
-        uint32_t x = lo.x;
-        while (x < hi.x) {
-          const uint32_t t0 = y * (uint32_t)grid_x + x;
-          const uint32_t bucket = t0 >> bucket_shift;
-          const uint32_t run_end = min(hi.x, x + (((bucket + 1u) << bucket_shift) - t0));
-          for (uint32_t xx = x; xx < run_end; ++xx)
-            words[off++] = ((uint64_t)(y * (uint32_t)grid_x + xx) << tile_shift) | low;
-          atomicAdd(&s_hist[bucket], run_end - x);
-          x = run_end;
-        }
+  const size_t stride = (size_t)gridDim.x * blockDim.x * BH_ITEMS;
+  for (size_t base = ((size_t)blockIdx.x * blockDim.x + threadIdx.x) * BH_ITEMS; base < (size_t)n; base += stride) {
+    uint32_t prev = 0xffffffffu, cnt = 0;
+    if (base + BH_ITEMS <= (size_t)n) {
+      const ulonglong2* p = reinterpret_cast<const ulonglong2*>(words + base);
+#pragma unroll
+      for (int k = 0; k < BH_ITEMS / 2; ++k) {
+        const ulonglong2 v = p[k];
+        const uint32_t b0 = (uint32_t)(v.x >> shift), b1 = (uint32_t)(v.y >> shift);
+        if (b0 != prev) { if (cnt) atomicAdd(&s_hist[prev], cnt); prev = b0; cnt = 0; }
+        ++cnt;
+        if (b1 != prev) { atomicAdd(&s_hist[prev], cnt); prev = b1; cnt = 0; }
+        ++cnt;
+      }
+    } else {
+      for (size_t i = base; i < (size_t)n; ++i) {
+        const uint32_t b0 = (uint32_t)(words[i] >> shift);
+        if (b0 != prev) { if (cnt) atomicAdd(&s_hist[prev], cnt); prev = b0; cnt = 0; }
+        ++cnt;
       }
     }
+    if (cnt) atomicAdd(&s_hist[prev], cnt);
   }
   __syncthreads();
   for (int i = threadIdx.x; i < MSD_BINS; i += blockDim.x) {
@@ -469,10 +487,12 @@ int launch_binning_buckets(const GeomPtrs& g, const BinningPtrs& b, const ImageP
   {
     StageTimer timer(stream, ST_DUPLICATE);
     EGS_CUDA_TRY(cudaMemsetAsync(b.hist, 0, b.zero_bytes, stream));
-    int dup_blocks = (P + 255) / 256;
-    if (dup_blocks > 148 * 8) dup_blocks = 148 * 8;
-    duplicate_bucket_kernel<<<dup_blocks, 256, 0, stream>>>(P, g.means2D, g.depths, g.point_offsets, radii,
-                                                            b.keys[1], gx, gy, ib, bucket_shift, hist);
+    duplicate_words_kernel<<<(P + 255) / 256, 256, 0, stream>>>(P, g.means2D, g.depths, g.point_offsets, radii,
+                                                                b.keys[1], gx, gy, ib);
+    EGS_AFTER_LAUNCH(stream, debug);
+    int hist_blocks = (R + 256 * BH_ITEMS - 1) / (256 * BH_ITEMS);
+    if (hist_blocks > 148 * 4) hist_blocks = 148 * 4;
+    bucket_histogram_kernel<<<hist_blocks, 256, 0, stream>>>(b.keys[1], R, ib + 32 + bucket_shift, hist);
     EGS_AFTER_LAUNCH(stream, debug);
     bucket_scan_kernel<<<1, MSD_BINS, 0, stream>>>(hist, start);
     EGS_AFTER_LAUNCH(stream, debug);

@@ -229,9 +229,11 @@ int launch_blend_forward(const EgsForwardArgs& a, const GeomPtrs& g, const uint3
                          const ImagePtrs& im, cudaStream_t stream) {
   const dim3 grid(tiles_x(a.width), tiles_y(a.height), 1);
   StageTimer timer(stream, ST_BLEND_FWD);
-  // EGS_FWD=v1 selects the one-pixel-per-thread kernel (A/B runs); results are bit-identical
+  // Default: one pixel per thread. EGS_FWD=v2 selects the two-pixels-per-thread kernel; results are
+  // bit-identical, and on B200 at 1M Gaussians v2 measured 5 % slower (0.364 vs 0.348 ms): the
+  // forward loop is already at its instruction floor and v2 only adds divergence per warp.
   const char* sel = getenv("EGS_FWD");
-  if (sel && strcmp(sel, "v1") == 0) {
+  if (!(sel && strcmp(sel, "v2") == 0)) {
     blend_forward_kernel<<<grid, TILE_PIXELS, 0, stream>>>(
         im.ranges, point_list, a.width, a.height, (int)grid.x, g.means2D, g.conic_opacity,
         g.rgb_depth, a.background, a.out_color, a.out_depth, a.out_alpha, im.n_contrib);
