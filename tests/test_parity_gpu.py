@@ -302,6 +302,24 @@ def test_three_binning_paths_agree(built, cuda_device, monkeypatch):
             assert int(torch.bincount(tiles >> shift).max()) > 12288
 
 
+def test_kernel_variants_agree(built, cuda_device, monkeypatch):
+    """The alternative blend kernels kept for A/B timing compute the same thing: the two forward
+    kernels are bit-identical (the log-domain pre-filter of v2 is conservative), the two backward
+    kernels agree within the gradient tolerance (v2 uses ex2.approx / rcp.approx)."""
+    kw, ups = case_inputs(CASES[0], cuda_device)
+    monkeypatch.delenv("EGS_FWD", raising=False)
+    monkeypatch.delenv("EGS_BWD", raising=False)
+    f1, g2 = run_cuda(kw, ups)
+    monkeypatch.setenv("EGS_FWD", "v2")
+    monkeypatch.setenv("EGS_BWD", "v1")
+    f2, g1 = run_cuda(kw, ups)
+    for k in ("color", "depth", "alpha"):
+        assert torch.equal(getattr(f1, k), getattr(f2, k)), k
+    assert torch.equal(f1.image_view()["n_contrib"], f2.image_view()["n_contrib"])
+    for k in ("means2D", "means3D", "opacity", "sh", "scales", "rotations"):
+        assert grad_rel_err(g2[k], g1[k]) <= GRAD_RTOL, k
+
+
 def test_adam_and_se3(built, cuda_device):
     from egogaussian_b200 import scenes
     from egogaussian_b200.diff_gaussian_rasterization import _C
