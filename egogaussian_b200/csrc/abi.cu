@@ -170,20 +170,23 @@ extern "C" int egs_forward(const EgsForwardArgs* args, void* stream_v, int* num_
     return EGS_ERR_ALLOC;
   }
   const BinningPtrs b(bin_mem, (size_t)R);
-  // Three binning paths with identical results:
-  //   buckets  packed words, one global partition on the top tile bits + per-bucket CTA sort
-  //   packed   packed words, five global LSD passes (R too large for the bucket sorter)
-  //   pairs    (u64 key, u32 value) LSD sort (tile | depth | index does not fit 64 bits)
-  // EGS_SORT=pairs|packed forces a path (tests, A/B timing).
+  // Binning paths, all with identical results:
+  //   buckets  packed words, one global partition on the top tile bits + one CTA per bucket
+  //   packed   packed words, five global onesweep passes (R too large for the bucket sorter)
+  //   pairs    keys + value array through the same onesweep kernel (tile | depth | index does not
+  //            fit one 64-bit word, e.g. more than 1M Gaussians at 1280x720)
+  //   pairs8   the first, plain 8-bit pair sort of binning.cu, kept as an independent cross-check
+  // EGS_SORT=packed|pairs|pairs8 forces a path (tests, A/B timing).
   const char* force = getenv("EGS_SORT");
-  const bool want_pairs = force && strcmp(force, "pairs") == 0;
-  const bool want_packed = force && strcmp(force, "packed") == 0;
-  if (!packed_path_fits(a.P, a.width, a.height) || want_pairs) {
+  const bool fits = packed_path_fits(a.P, a.width, a.height);
+  if (force && strcmp(force, "pairs8") == 0) {
     if (int rc = launch_binning(g, b, im, a.radii, a.P, R, a.width, a.height, stream, a.debug)) return rc;
-  } else if (bucket_path_ok(a.P, R, a.width, a.height) && !want_packed) {
+  } else if (!fits || (force && strcmp(force, "pairs") == 0)) {
+    if (int rc = launch_binning_packed(g, b, im, a.radii, a.P, R, a.width, a.height, true, stream, a.debug)) return rc;
+  } else if (bucket_path_ok(a.P, R, a.width, a.height) && !(force && strcmp(force, "packed") == 0)) {
     if (int rc = launch_binning_buckets(g, b, im, a.radii, a.P, R, a.width, a.height, stream, a.debug)) return rc;
   } else {
-    if (int rc = launch_binning_packed(g, b, im, a.radii, a.P, R, a.width, a.height, stream, a.debug)) return rc;
+    if (int rc = launch_binning_packed(g, b, im, a.radii, a.P, R, a.width, a.height, false, stream, a.debug)) return rc;
   }
 
   const uint32_t* point_list = b.vals[0];

@@ -19,6 +19,8 @@
 // Scenes whose indices do not fit (P > 2^(32 - bit)) take the pair-sorting path in binning.cu.
 #include "common.cuh"
 
+#include <stddef.h>
+
 namespace egs {
 
 constexpr int PK_BITS = 9;
@@ -106,6 +108,7 @@ struct PackedSmem {
   uint32_t digit_global[PK_RADIX];
   uint32_t warp_sums[PK_WARPS];
   uint32_t tile;
+  uint32_t exch_v[PK_TILE];                 // 16 KB, pair mode only (kept last: not allocated otherwise)
 };
 
 // status words carry flag and value together, so relaxed device-scope accesses are enough
@@ -118,9 +121,13 @@ __device__ __forceinline__ void st_status(uint32_t* p, uint32_t v) {
   asm volatile("st.relaxed.gpu.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
 }
 
-template <bool LAST>
+// PAIRS = false: `in` holds packed words (key and index in one u64); the LAST pass unpacks.
+// PAIRS = true : `in` holds bare keys and a u32 value array travels with them (scenes whose
+//                indices do not fit beside the key); every pass moves both arrays.
+template <bool LAST, bool PAIRS>
 __global__ void __launch_bounds__(PK_THREADS)
-packed_onesweep_kernel(const uint64_t* __restrict__ in, uint64_t* __restrict__ out,
+packed_onesweep_kernel(const uint64_t* __restrict__ in, const uint32_t* __restrict__ vals_in,
+                       uint64_t* __restrict__ out,
                        uint32_t* __restrict__ vals_out, int n, int shift, uint32_t digit_mask,
                        int idx_bits, const uint32_t* __restrict__ digit_base,
                        uint32_t* __restrict__ ticket, uint32_t* __restrict__ status_raw) {
@@ -138,11 +145,13 @@ packed_onesweep_kernel(const uint64_t* __restrict__ in, uint64_t* __restrict__ o
   const size_t warp_base = block_base + (size_t)warp * (32 * PK_ITEMS);
 
   uint64_t word[PK_ITEMS];
+  uint32_t val[PAIRS ? PK_ITEMS : 1];
   uint32_t rank[PK_ITEMS];
 #pragma unroll
   for (int i = 0; i < PK_ITEMS; ++i) {
     const size_t g = warp_base + (size_t)i * 32 + lane;
     word[i] = g < (size_t)n ? in[g] : ~0ull;
+    if (PAIRS) val[i] = g < (size_t)n ? vals_in[g] : 0u;
   }
   // 1. block histogram (unordered shared-memory atomics) and EARLY publication of the aggregate,
   //    so that successors' look-backs find it while this block is still ranking
@@ -216,7 +225,9 @@ packed_onesweep_kernel(const uint64_t* __restrict__ in, uint64_t* __restrict__ o
     const size_t g = warp_base + (size_t)i * 32 + lane;
     if (g < (size_t)n) {
       const uint32_t d = (uint32_t)(word[i] >> shift) & digit_mask;
-      S.exch[S.digit_local[d] + S.warp_hist[warp][d] + rank[i]] = word[i];
+      const uint32_t pos = S.digit_local[d] + S.warp_hist[warp][d] + rank[i];
+      S.exch[pos] = word[i];
+      if (PAIRS) S.exch_v[pos] = val[i];
     }
   }
   __syncthreads();
@@ -230,7 +241,10 @@ packed_onesweep_kernel(const uint64_t* __restrict__ in, uint64_t* __restrict__ o
       const uint64_t w = S.exch[k];
       const uint32_t d = (uint32_t)(w >> shift) & digit_mask;
       const uint32_t dst = S.digit_global[d] + k;
-      if (LAST) {
+      if (PAIRS) {
+        out[dst] = w;
+        vals_out[dst] = S.exch_v[k];
+      } else if (LAST) {
         out[dst] = w >> idx_bits;                 // (tile << 32) | depth bits
         vals_out[dst] = (uint32_t)(w & idx_mask); // Gaussian index
       } else {
@@ -253,21 +267,76 @@ bool packed_path_fits(int P, int W, int H) {
   return ib + 32 + tile_id_bits((uint32_t)(tiles_x(W) * tiles_y(H))) <= 64;
 }
 
+// (u64 key, u32 value) generation for the pair mode, same order as duplicateWithKeys
+__global__ void __launch_bounds__(256)
+duplicate_pairs_kernel(int P, const float2* __restrict__ means2D, const float* __restrict__ depths,
+                       const uint32_t* __restrict__ offsets, const int* __restrict__ radii,
+                       uint64_t* __restrict__ keys, uint32_t* __restrict__ vals, int grid_x, int grid_y) {
+  const int idx = blockIdx.x * blockDim.x + threadIdx.x;
+  if (idx >= P) return;
+  const int r = radii[idx];
+  if (r <= 0) return;
+  uint32_t off = (idx == 0) ? 0u : offsets[idx - 1];
+  uint2 lo, hi;
+  tile_rect(means2D[idx], r, grid_x, grid_y, lo, hi);
+  const uint64_t depth_bits = (uint64_t)__float_as_uint(depths[idx]);
+  for (uint32_t y = lo.y; y < hi.y; ++y)
+    for (uint32_t x = lo.x; x < hi.x; ++x) {
+      keys[off] = ((uint64_t)(y * (uint32_t)grid_x + x) << 32) | depth_bits;
+      vals[off] = (uint32_t)idx;
+      ++off;
+    }
+}
+
+template <bool PAIRS>
+static int run_onesweep_passes(const BinningPtrs& b, int R, int passes, int begin_bit, int end_bit, int ib,
+                               int src, cudaStream_t stream, bool debug) {
+  const int blocks = (int)b.sort_blocks;
+  const size_t smem = PAIRS ? sizeof(PackedSmem) : offsetof(PackedSmem, exch_v);
+  EGS_CUDA_TRY(cudaFuncSetAttribute(packed_onesweep_kernel<false, PAIRS>,
+                                    cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  EGS_CUDA_TRY(cudaFuncSetAttribute(packed_onesweep_kernel<true, PAIRS>,
+                                    cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  for (int p = 0; p < passes; ++p) {
+    const int shift = begin_bit + p * PK_BITS;
+    const int width = (end_bit - shift) < PK_BITS ? (end_bit - shift) : PK_BITS;
+    const int dst = src ^ 1;
+    uint32_t* status = b.status + (size_t)p * b.sort_blocks * PK_RADIX;
+    if (p + 1 < passes) {
+      packed_onesweep_kernel<false, PAIRS><<<blocks, PK_THREADS, smem, stream>>>(
+          b.keys[src], b.vals[src], b.keys[dst], PAIRS ? b.vals[dst] : nullptr, R, shift, (1u << width) - 1u, ib,
+          b.hist + p * PK_RADIX, b.ticket + p, status);
+    } else {
+      packed_onesweep_kernel<true, PAIRS><<<blocks, PK_THREADS, smem, stream>>>(
+          b.keys[src], b.vals[src], b.keys[dst], b.vals[dst], R, shift, (1u << width) - 1u, ib,
+          b.hist + p * PK_RADIX, b.ticket + p, status);
+    }
+    EGS_AFTER_LAUNCH(stream, debug);
+    src = dst;
+  }
+  return EGS_OK;
+}
+
+// pairs = false: packed words (index inside the word); pairs = true: keys + a value array
 int launch_binning_packed(const GeomPtrs& g, const BinningPtrs& b, const ImagePtrs& im, const int* radii,
-                          int P, int R, int W, int H, cudaStream_t stream, bool debug) {
+                          int P, int R, int W, int H, bool pairs, cudaStream_t stream, bool debug) {
   const int gx = tiles_x(W), gy = tiles_y(H);
   EGS_CUDA_TRY(cudaMemsetAsync(im.ranges, 0, (size_t)gx * gy * sizeof(uint2), stream));
   if (R == 0) return EGS_OK;
-  const int ib = tile_id_bits((uint32_t)(P > 1 ? P - 1 : 1));
+  const int ib = pairs ? 0 : tile_id_bits((uint32_t)(P > 1 ? P - 1 : 1));
   const int key_bits = 32 + tile_id_bits((uint32_t)(gx * gy));
   const int begin_bit = ib, end_bit = ib + key_bits;
   const int passes = (key_bits + PK_BITS - 1) / PK_BITS;
-  // ping-pong so that the last pass reads keys[1] and leaves the sorted keys in keys[0]
-  int src = (passes & 1) ? 1 : 0;
+  // ping-pong so that the last pass reads buffer 1 and leaves the sorted lists in buffer 0
+  const int src = (passes & 1) ? 1 : 0;
   {
     StageTimer timer(stream, ST_DUPLICATE);
-    duplicate_packed_kernel<<<(P + 255) / 256, 256, 0, stream>>>(P, g.means2D, g.depths, g.point_offsets,
-                                                                 radii, b.keys[src], gx, gy, ib);
+    if (pairs)
+      duplicate_pairs_kernel<<<(P + 255) / 256, 256, 0, stream>>>(P, g.means2D, g.depths, g.point_offsets, radii,
+                                                                  b.keys[src], b.vals[src], gx, gy);
+    else
+      duplicate_packed_kernel<<<(P + 255) / 256, 256, 0, stream>>>(P, g.means2D, g.depths, g.point_offsets,
+                                                                   radii, b.keys[src], gx, gy, ib);
     EGS_AFTER_LAUNCH(stream, debug);
   }
   {
@@ -284,29 +353,9 @@ int launch_binning_packed(const GeomPtrs& g, const BinningPtrs& b, const ImagePt
   }
   {
     StageTimer timer(stream, ST_SORT_PASSES);
-    const int blocks = (int)b.sort_blocks;
-    const size_t smem = sizeof(PackedSmem);
-    EGS_CUDA_TRY(cudaFuncSetAttribute(packed_onesweep_kernel<false>,
-                                      cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    EGS_CUDA_TRY(cudaFuncSetAttribute(packed_onesweep_kernel<true>,
-                                      cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    for (int p = 0; p < passes; ++p) {
-      const int shift = begin_bit + p * PK_BITS;
-      const int width = (end_bit - shift) < PK_BITS ? (end_bit - shift) : PK_BITS;
-      const int dst = src ^ 1;
-      uint32_t* status = b.status + (size_t)p * b.sort_blocks * PK_RADIX;
-      if (p + 1 < passes) {
-        packed_onesweep_kernel<false><<<blocks, PK_THREADS, smem, stream>>>(
-            b.keys[src], b.keys[dst], nullptr, R, shift, (1u << width) - 1u, ib, b.hist + p * PK_RADIX,
-            b.ticket + p, status);
-      } else {
-        packed_onesweep_kernel<true><<<blocks, PK_THREADS, smem, stream>>>(
-            b.keys[src], b.keys[dst], b.vals[0], R, shift, (1u << width) - 1u, ib, b.hist + p * PK_RADIX,
-            b.ticket + p, status);
-      }
-      EGS_AFTER_LAUNCH(stream, debug);
-      src = dst;
-    }
+    const int rc = pairs ? run_onesweep_passes<true>(b, R, passes, begin_bit, end_bit, ib, src, stream, debug)
+                         : run_onesweep_passes<false>(b, R, passes, begin_bit, end_bit, ib, src, stream, debug);
+    if (rc) return rc;
   }
   return launch_tile_ranges(R, b.keys[0], im, stream, debug);
 }

@@ -220,7 +220,7 @@ int launch_scan_tiles(const GeomPtrs& g, int P, cudaStream_t stream, bool debug)
 // packed-word fast path (binning_packed.cu) and the shared range kernel
 bool packed_path_fits(int P, int W, int H);
 int launch_binning_packed(const GeomPtrs& g, const BinningPtrs& b, const ImagePtrs& im, const int* radii,
-                          int P, int R, int W, int H, cudaStream_t stream, bool debug);
+                          int P, int R, int W, int H, bool pairs, cudaStream_t stream, bool debug);
 // MSD-bucket path (binning_buckets.cu): one global partition pass + one CTA per bucket
 bool bucket_path_ok(int P, int R, int W, int H);
 int launch_binning_buckets(const GeomPtrs& g, const BinningPtrs& b, const ImagePtrs& im, const int* radii,

@@ -285,7 +285,7 @@ def test_three_binning_paths_agree(built, cuda_device, monkeypatch):
         av = a.binning_view()
         keys = av["keys"]
         assert bool((keys[1:] >= keys[:-1]).all())
-        for forced in ("packed", "pairs"):
+        for forced in ("packed", "pairs", "pairs8"):
             monkeypatch.setenv("EGS_SORT", forced)
             b = cabi.forward(**kw)
             assert a.num_rendered == b.num_rendered
