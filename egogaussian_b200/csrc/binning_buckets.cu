@@ -486,7 +486,10 @@ int launch_binning_buckets(const GeomPtrs& g, const BinningPtrs& b, const ImageP
   uint32_t* start = b.hist + MSD_BINS;     // [MSD_BINS + 1]
   {
     StageTimer timer(stream, ST_DUPLICATE);
-    EGS_CUDA_TRY(cudaMemsetAsync(b.hist, 0, b.zero_bytes, stream));
+    // histogram, ticket and the status words of the single partition pass (not the whole area the
+    // five-pass paths need)
+    const size_t zero = reinterpret_cast<char*>(b.status + b.sort_blocks * MSD_BINS) - reinterpret_cast<char*>(b.hist);
+    EGS_CUDA_TRY(cudaMemsetAsync(b.hist, 0, zero, stream));
     duplicate_words_kernel<<<(P + 255) / 256, 256, 0, stream>>>(P, g.means2D, g.depths, g.point_offsets, radii,
                                                                 b.keys[1], gx, gy, ib);
     EGS_AFTER_LAUNCH(stream, debug);

@@ -1,0 +1,43 @@
+"""Per-launch DRAM traffic of each stage from an `ncu --set full` report -> profiles/traffic.json.
+
+  python tools/ncu_traffic.py gpurun_out/prof.ncu-rep [profiles/traffic.json]
+
+bench.py reads the JSON to fill `roofline.traffic` (dram__bytes_read.sum + dram__bytes_write.sum
+per launch of the dominant kernel). Runs here, without a GPU.
+"""
+import csv
+import io
+import json
+import subprocess
+import sys
+from collections import defaultdict
+
+STAGE_OF = {
+    "preprocess_forward_kernel": "preprocess_fwd", "scan_tiles_kernel": "scan",
+    "duplicate_words_kernel": "duplicate_keys", "bucket_histogram_kernel": "duplicate_keys",
+    "duplicate_packed_kernel": "duplicate_keys", "msd_partition_kernel": "sort_histogram",
+    "bucket_sort_kernel": "sort_passes", "packed_onesweep_kernel": "sort_passes",
+    "blend_forward_kernel": "blend_fwd", "blend_forward2_kernel": "blend_fwd",
+    "blend_backward_kernel": "blend_bwd", "blend_backward2_kernel": "blend_bwd",
+    "preprocess_backward_kernel": "preprocess_bwd", "adam_multi_kernel": "adam",
+}
+
+rep = sys.argv[1]
+dst = sys.argv[2] if len(sys.argv) > 2 else "profiles/traffic.json"
+out = subprocess.run(["ncu", "-i", rep, "--page", "raw", "--csv"], capture_output=True, text=True).stdout
+rows = list(csv.reader(io.StringIO(out)))
+hdr, units = rows[0], rows[1]
+kn, rd, wr = hdr.index("Kernel Name"), hdr.index("dram__bytes_read.sum"), hdr.index("dram__bytes_write.sum")
+scale = {"byte": 1.0, "Kbyte": 1e3, "Mbyte": 1e6, "Gbyte": 1e9}
+acc = defaultdict(list)
+for r in rows[2:]:
+    name = r[kn].split("(")[0].split("<")[0].replace("void ", "").replace("egs::", "").strip()
+    stage = STAGE_OF.get(name)
+    if stage is None:
+        continue
+    acc[(stage, name)].append(float(r[rd]) * scale[units[rd]] + float(r[wr]) * scale[units[wr]])
+result = {"source": rep, "unit": "bytes per launch (dram__bytes_read.sum + dram__bytes_write.sum)", "stages": {}}
+for (stage, name), v in sorted(acc.items()):
+    result["stages"].setdefault(stage, {})[name] = {"launches_captured": len(v), "bytes_per_launch": sum(v) / len(v)}
+json.dump(result, open(dst, "w"), indent=1)
+print(json.dumps(result, indent=1))
