@@ -364,6 +364,7 @@ blend_backward2_kernel(const uint2* __restrict__ ranges, const uint32_t* __restr
   // store (shared-memory float atomicAdd is a compare-and-swap loop on this architecture)
   __shared__ float s_acc[(BWD2_THREADS / 32) * BWD2_BATCH * ACC_PITCH];
   __shared__ uint32_t s_hit[BWD2_BATCH];   // bit w: warp w stored totals for this entry in this batch
+  __shared__ unsigned char s_reach[BWD2_BATCH];   // bit w: the entry can reach warp w's 8x8 pixels
   __shared__ uint32_t s_max_contrib;
 
   const unsigned tid = threadIdx.x;
@@ -411,6 +412,8 @@ blend_backward2_kernel(const uint2* __restrict__ ranges, const uint32_t* __restr
       s_id[tid] = id;
       // alpha >= 1/255  <=>  power >= -log(255 o); o <= 0 can never contribute
       s_a[tid] = make_float4(xy.x, xy.y, co.w > 0.f ? -__logf(255.f * co.w) : 1.f, co.w);
+      s_reach[tid] = (unsigned char)footprint_mask<8, 8>(xy, co, (float)(blockIdx.x * TILE_X),
+                                                         (float)(blockIdx.y * TILE_Y));
       s_b[tid] = make_float4(co.x, co.y, co.z, cd.w);
       s_c[tid] = cd;
     }
@@ -421,6 +424,7 @@ blend_backward2_kernel(const uint2* __restrict__ ranges, const uint32_t* __restr
     for (int j = 0; j < n; ++j) {
       const uint32_t jpos = (uint32_t)(walk - 1 - (r * BWD2_BATCH + j));
       if (jpos >= warp_last) continue;   // warp-uniform
+      if (!((s_reach[j] >> warp) & 1u)) continue;   // the entry cannot touch this warp's 8x8 block
       const float4 a4 = s_a[j];
       const float4 b4 = s_b[j];
       const float dx0 = a4.x - P0.px, dy0 = a4.y - P0.py;

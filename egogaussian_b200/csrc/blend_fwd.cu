@@ -30,6 +30,7 @@ blend_forward_kernel(const uint2* __restrict__ ranges, const uint32_t* __restric
   __shared__ float2 s_xy[BLEND_BATCH];
   __shared__ float4 s_co[BLEND_BATCH];
   __shared__ float4 s_cd[BLEND_BATCH];
+  __shared__ unsigned char s_mask[BLEND_BATCH];   // bit w: the entry can reach warp w's 8x4 pixels
 
   const unsigned tid = threadIdx.x;
   const unsigned warp = tid >> 5, lane = tid & 31;
@@ -49,7 +50,8 @@ blend_forward_kernel(const uint2* __restrict__ ranges, const uint32_t* __restric
 
   bool done = !inside;
   float T = 1.0f;
-  uint32_t contributor = 0, last_contributor = 0;
+  uint32_t last_contributor = 0;
+  const float tile_x0 = (float)(blockIdx.x * TILE_X), tile_y0 = (float)(blockIdx.y * TILE_Y);
   float C0 = 0.f, C1 = 0.f, C2 = 0.f, weight = 0.f, D = 0.f;
 
   for (int r = 0; r < rounds; ++r, to_do -= BLEND_BATCH) {
@@ -57,16 +59,20 @@ blend_forward_kernel(const uint2* __restrict__ ranges, const uint32_t* __restric
     const int progress = r * BLEND_BATCH + (int)tid;
     if (progress < total) {
       const uint32_t id = point_list[range.x + progress];
-      s_xy[tid] = means2D[id];
-      s_co[tid] = conic_opacity[id];
+      const float2 xy = means2D[id];
+      const float4 co = conic_opacity[id];
+      s_xy[tid] = xy;
+      s_co[tid] = co;
       s_cd[tid] = rgb_depth[id];
+      s_mask[tid] = (unsigned char)footprint_mask<8, 4>(xy, co, tile_x0, tile_y0);
     }
     __syncthreads();
     if (__all_sync(0xffffffffu, done)) continue;  // warp-uniform: nothing left for these 32 pixels
 
     const int n = min(BLEND_BATCH, to_do);
     for (int j = 0; !done && j < n; ++j) {
-      contributor++;
+      // one byte decides for the whole warp whether this entry can touch its 8x4 pixels at all
+      if (!((s_mask[j] >> warp) & 1u)) continue;
       const float2 xy = s_xy[j];
       const float2 d = make_float2(xy.x - pixf.x, xy.y - pixf.y);
       const float4 con_o = s_co[j];
@@ -86,7 +92,7 @@ blend_forward_kernel(const uint2* __restrict__ ranges, const uint32_t* __restric
       weight += alpha * T;
       D += cd.w * alpha * T;
       T = test_T;
-      last_contributor = contributor;
+      last_contributor = (uint32_t)(r * BLEND_BATCH + j + 1);   // 1-based position in the tile's list
     }
   }
 

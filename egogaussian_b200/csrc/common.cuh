@@ -328,6 +328,47 @@ __device__ __forceinline__ void tile_rect(const float2 p, int r, int gx, int gy,
 
 __device__ __forceinline__ unsigned lane_id() { return threadIdx.x & 31; }
 
+// Which BW x BH pixel blocks of a 16x16 tile can a Gaussian contribute to? Bit (by * NBX + bx) of
+// the result is set when the block may contain a pixel with alpha = o * exp(power) >= 1/255, where
+// power = -0.5 (A dx^2 + C dy^2) - B dx dy. That region is the ellipse A dx^2 + 2B dx dy + C dy^2
+// <= 2 log(255 o), whose bounding box has half-extents sqrt(k C / det), sqrt(k A / det). The test
+// is conservative, so skipping an unmarked block never changes a result: the per-pixel test
+// evaluates `power` in fp32 with an absolute error of at most ~2e-7 * k * AC/det near the boundary
+// (each of its three terms is bounded by k * AC/det there), so with AC/det <= 100 and k <= ~11 a
+// margin of 1e-3 on the log covers it five times over; the extents get another 1e-3 px. Anything
+// unusual (non-positive or non-finite opacity, degenerate or very elongated conic, non-finite
+// centre) marks every block and leaves the decision to the exact per-pixel test. The tile kernels use one warp per block, so a warp skips a whole list entry with
+// one shared-memory byte instead of evaluating 32 or 64 pixels.
+template <int BW, int BH>
+__device__ __forceinline__ unsigned footprint_mask(const float2 xy, const float4 conic_o, float tile_x0,
+                                                   float tile_y0) {
+  constexpr int NBX = TILE_X / BW, NBY = TILE_Y / BH;
+  constexpr unsigned ALL = (1u << (NBX * NBY)) - 1u;
+  const float A = conic_o.x, B = conic_o.y, C = conic_o.z, o = conic_o.w;
+  const float det = A * C - B * B;
+  const float k = 2.f * (__logf(255.f * o) + 1e-3f);
+  const bool regular = o > 0.f && det > 0.f && A > 0.f && C > 0.f && det * 100.f >= A * C && isfinite(k) &&
+                       isfinite(det) && isfinite(xy.x) && isfinite(xy.y);
+  if (!regular) return ALL;
+  if (k <= 0.f) return 0u;   // o < 1/255: alpha can never reach the threshold
+  const float ex = sqrtf(k * C / det) * 1.0001f + 1e-3f;
+  const float ey = sqrtf(k * A / det) * 1.0001f + 1e-3f;
+  if (!(isfinite(ex) && isfinite(ey))) return ALL;
+  const float lo_x = xy.x - ex - tile_x0, hi_x = xy.x + ex - tile_x0;   // tile-local pixel range
+  const float lo_y = xy.y - ey - tile_y0, hi_y = xy.y + ey - tile_y0;
+  unsigned mask = 0u;
+#pragma unroll
+  for (int by = 0; by < NBY; ++by) {
+    const bool ytest = lo_y <= (float)(by * BH + BH - 1) && hi_y >= (float)(by * BH);
+#pragma unroll
+    for (int bx = 0; bx < NBX; ++bx) {
+      const bool xtest = lo_x <= (float)(bx * BW + BW - 1) && hi_x >= (float)(bx * BW);
+      if (ytest && xtest) mask |= 1u << (by * NBX + bx);
+    }
+  }
+  return mask;
+}
+
 // Lanes of the warp that are valid and hold the same BITS-bit digit as this lane. One ballot per
 // digit bit (fixed cost, independent ballots pipeline) instead of the match.any instruction, whose
 // cost grows with the number of distinct values in the warp.
