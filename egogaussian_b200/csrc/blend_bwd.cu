@@ -256,14 +256,18 @@ blend_backward_kernel(const uint2* __restrict__ ranges, const uint32_t* __restri
 //   * whether a fragment contributes is decided without the exponential:
 //       alpha = o * exp(power) >= 1/255   <=>   power >= -log(255 * o) =: thr (staged per entry),
 //     so exp, the divide and everything after run only on warps where some lane contributes;
-//     (pre-selection only, with a margin: the exact forward test is repeated on the selected ones);
 //   * backward is tolerance-checked (1e-4 of the tensor maximum), not bit-checked, so the
-//     reciprocal of (1 - alpha) uses the hardware approximation (rcp.approx, one MUFU).
+//     exponential and the reciprocal use the fast hardware approximations (ex2.approx, rcp.approx).
 constexpr int BWD2_THREADS = 128;
 constexpr int BWD2_BATCH = 128;
 
-// single-instruction hardware reciprocal (MUFU.RCP, flush-to-zero): the __fdividef intrinsic wraps
-// it in denormal-range fix-ups that cost more than the operation
+// single-instruction hardware approximations (MUFU.EX2 / MUFU.RCP, flush-to-zero): the __expf and
+// __fdividef intrinsics wrap them in denormal-range fix-ups that cost more than the operation
+__device__ __forceinline__ float ex2_approx(float x) {
+  float y;
+  asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
+  return y;
+}
 __device__ __forceinline__ float rcp_approx(float x) {
   float y;
   asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
@@ -306,13 +310,8 @@ __device__ __forceinline__ void fragment_backward(PixelState& s, float dx, float
                                                   const float4 a4, const float4 b4, const float4 c4,
                                                   float ddelx_dx, float ddely_dy, float (&q)[10]) {
   const float opac = a4.w;
-  // The caller's log-domain test only pre-selects (with a margin); whether the fragment took part
-  // in the forward blend is decided here exactly as forward decided it -- same `power` bits, same
-  // expf, same comparison -- because a fragment wrongly added or dropped shifts T for the rest of
-  // the pixel's walk by 0.4 %.
-  const float G = expf(power);
+  const float G = ex2_approx(power * 1.4426950408889634f);
   const float alpha = fminf(0.99f, opac * G);
-  if (alpha < 1.0f / 255.0f) return;
   const float rcp = rcp_approx(1.f - alpha);
   s.T = s.T * rcp;
   const float w = alpha * s.T;
@@ -412,10 +411,7 @@ blend_backward2_kernel(const uint2* __restrict__ ranges, const uint32_t* __restr
       const float4 cd = rgb_depth[id];
       s_id[tid] = id;
       // alpha >= 1/255  <=>  power >= -log(255 o); o <= 0 can never contribute
-      // pre-selection threshold with a 1e-3 margin below -log(255 o); NaN opacity compares false
-      // everywhere and is left to the exact test like in forward
-      s_a[tid] = make_float4(xy.x, xy.y, co.w > 0.f ? -__logf(255.f * co.w) - 1e-3f : (co.w == co.w ? 1.f : -1e30f),
-                             co.w);
+      s_a[tid] = make_float4(xy.x, xy.y, co.w > 0.f ? -__logf(255.f * co.w) : 1.f, co.w);
       s_reach[tid] = (unsigned char)footprint_mask<8, 8>(xy, co, (float)(blockIdx.x * TILE_X),
                                                          (float)(blockIdx.y * TILE_Y));
       s_b[tid] = make_float4(co.x, co.y, co.z, cd.w);
