@@ -131,6 +131,9 @@ constexpr int SORT_TILE = SORT_THREADS * SORT_ITEMS;
 constexpr int SORT_MAX_PASSES = 8;
 // status / histogram words per sort block: 8 passes x 256 digits (pair sort) or 6 x 512 (packed sort)
 constexpr int SORT_STATUS_WORDS = 3072;
+// histogram area shared by the paths: digit histograms of all passes (<= 3072 words), or bucket
+// histogram + bucket starts + largest-first order (1024 + 1025 + 1024 words)
+constexpr int SORT_HIST_WORDS = 4096;
 
 inline int sort_passes(int W, int H) {
   int bits = 32 + tile_id_bits((uint32_t)(tiles_x(W) * tiles_y(H)));
@@ -149,7 +152,7 @@ struct BinningLayout {
     vals[0] = take(R * 4);
     vals[1] = take(R * 4);
     // everything from `hist` to the end is zeroed with one memset per forward
-    hist = take(SORT_STATUS_WORDS * 4);
+    hist = take(SORT_HIST_WORDS * 4);
     ticket = take(SORT_MAX_PASSES * 4);
     status = take(sort_blocks * SORT_STATUS_WORDS * 4);
     total = o + 256;
