@@ -52,6 +52,7 @@ def parse():
     ap.add_argument("--geom", default="scale_rot", choices=["scale_rot", "cov"])
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
     ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--no-hint", action="store_true", help="A/B: exact-size forward (host waits for the count mid-way)")
     return ap.parse_args()
 
 
@@ -223,7 +224,10 @@ def run_ours(a, rank, world, local_rank):
     state = {}
 
     def step():
-        fwd = cabi.forward(**kw)
+        # like a training loop (and like the torch binding does by itself): guess this iteration's
+        # instance count from the previous one so the forward never stalls the GPU on the host
+        fwd = cabi.forward(num_rendered_hint=0 if a.no_hint else state.get("hint", 0), **kw)
+        state["hint"] = int(fwd.num_rendered * 1.25) + 8192
         out = flat.as_backward_out()
         if a.geom != "scale_rot":
             out = {"means3D": out["means3D"], "sh": out["sh"], "opacity": out["opacity"], "means2D": out["means2D"],

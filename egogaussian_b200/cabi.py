@@ -35,6 +35,7 @@ class EgsForwardArgs(C.Structure):
         ("geom_alloc", ALLOC_FN), ("geom_ctx", C.c_void_p),
         ("binning_alloc", ALLOC_FN), ("binning_ctx", C.c_void_p),
         ("image_alloc", ALLOC_FN), ("image_ctx", C.c_void_p),
+        ("num_rendered_hint", C.c_int),
     ]
 
 
@@ -54,6 +55,7 @@ class EgsBackwardArgs(C.Structure):
         ("dL_dmeans2D", c_float_p), ("dL_dcolors", c_float_p), ("dL_dopacity", c_float_p),
         ("dL_dmeans3D", c_float_p), ("dL_dcov3D", c_float_p), ("dL_dsh", c_float_p),
         ("dL_dscales", c_float_p), ("dL_drotations", c_float_p), ("debug", C.c_int),
+        ("binning_bytes", C.c_size_t),
     ]
 
 
@@ -78,7 +80,7 @@ class EgsImageView(C.Structure):
 
 # every symbol include/egs_rasterizer.h declares (the CPU test suite checks they all resolve)
 EXPORTED_SYMBOLS = [
-    "egs_geom_bytes", "egs_binning_bytes", "egs_image_bytes", "egs_forward",
+    "egs_geom_bytes", "egs_binning_bytes", "egs_binning_capacity", "egs_image_bytes", "egs_forward",
     "egs_backward_scratch_bytes", "egs_backward", "egs_mark_visible", "egs_adam_step",
     "egs_se3_apply", "egs_adam_se3_step", "egs_geom_view", "egs_binning_view", "egs_image_view",
     "egs_launch_count", "egs_last_error", "egs_abi_version",
@@ -99,6 +101,8 @@ def load() -> C.CDLL:
     lib.egs_geom_bytes.argtypes = [C.c_int]
     lib.egs_binning_bytes.restype = C.c_size_t
     lib.egs_binning_bytes.argtypes = [C.c_int, C.c_int, C.c_int]
+    lib.egs_binning_capacity.restype = C.c_int
+    lib.egs_binning_capacity.argtypes = [C.c_size_t]
     lib.egs_image_bytes.restype = C.c_size_t
     lib.egs_image_bytes.argtypes = [C.c_int, C.c_int]
     lib.egs_backward_scratch_bytes.restype = C.c_size_t
@@ -207,7 +211,8 @@ class ForwardResult:
             e = torch.empty((0,), dtype=torch.int64, device=self.geom.device)
             return {"keys": e, "values": e.to(torch.int32)}
         v = EgsBinningView()
-        _check(lib.egs_binning_view(self.binning.data_ptr(), R, self.W, self.H, C.byref(v)), "egs_binning_view")
+        cap = lib.egs_binning_capacity(int(self.binning.numel()))   # the blob may be laid out for a guessed capacity
+        _check(lib.egs_binning_view(self.binning.data_ptr(), cap, self.W, self.H, C.byref(v)), "egs_binning_view")
         d = self.binning.device
         return {"keys": _view(v.keys_sorted, (R,), torch.int64, d),
                 "values": _view(v.values_sorted, (R,), torch.int32, d)}
@@ -232,8 +237,10 @@ def _stream_handle(stream=None) -> int:
 def forward(*, means3D, opacities, bg, viewmatrix, projmatrix, campos, tanfovx, tanfovy,
             image_height, image_width, sh_degree=0, shs=None, colors_precomp=None, scales=None,
             rotations=None, cov3D_precomp=None, scale_modifier=1.0, prefiltered=False, debug=False,
-            stream=None, out=None) -> ForwardResult:
-    """egs_forward on torch-owned device memory. `out` may carry preallocated output tensors."""
+            stream=None, out=None, num_rendered_hint=0) -> ForwardResult:
+    """egs_forward on torch-owned device memory. `out` may carry preallocated output tensors;
+    `num_rendered_hint` > 0 lets the library enqueue everything before the instance count is read
+    back (results never depend on it, see the header)."""
     import torch
     lib = load()
     dev = means3D.device
@@ -276,6 +283,7 @@ def forward(*, means3D, opacities, bg, viewmatrix, projmatrix, campos, tanfovx, 
     a.out_color, a.out_depth, a.out_alpha = res.color.data_ptr(), res.depth.data_ptr(), res.alpha.data_ptr()
     a.radii = res.radii.data_ptr() if P else None
     a.geom_alloc, a.binning_alloc, a.image_alloc = cb["geom"], cb["binning"], cb["image"]
+    a.num_rendered_hint = int(num_rendered_hint)
     n = C.c_int(0)
     with torch.cuda.device(dev):
         _check(lib.egs_forward(C.byref(a), _stream_handle(stream), C.byref(n)), "egs_forward")
@@ -322,6 +330,7 @@ def backward(fwd: ForwardResult, *, means3D, bg, viewmatrix, projmatrix, campos,
     a.radii, a.out_alpha = fwd.radii.data_ptr(), fwd.alpha.data_ptr()
     a.geom_buffer = fwd.geom.data_ptr()
     a.binning_buffer = fwd.binning.data_ptr() if fwd.binning is not None and fwd.num_rendered else None
+    a.binning_bytes = int(fwd.binning.numel()) if fwd.binning is not None else 0
     a.image_buffer = fwd.image.data_ptr()
     a.dL_dout_color, a.dL_dout_depth, a.dL_dout_alpha = _ptr(dL_dcolor), _ptr(dL_ddepth), _ptr(dL_dalpha)
     a.scratch = scratch.data_ptr()
@@ -372,6 +381,7 @@ def backward_static_scratch(fwd: ForwardResult, *, means3D, bg, viewmatrix, proj
     a.out_alpha = fwd.alpha.data_ptr()
     a.geom_buffer = fwd.geom.data_ptr() if fwd.geom is not None else None
     a.binning_buffer = fwd.binning.data_ptr() if fwd.binning is not None and fwd.num_rendered else None
+    a.binning_bytes = int(fwd.binning.numel()) if fwd.binning is not None else 0
     a.image_buffer = fwd.image.data_ptr() if fwd.image is not None else None
     a.dL_dout_color, a.dL_dout_depth, a.dL_dout_alpha = _ptr(dL_dcolor), _ptr(dL_ddepth), _ptr(dL_dalpha)
     a.scratch = None   # ignored by this entry point

@@ -78,6 +78,26 @@ static const char* kStageNames[ST_COUNT] = {"preprocess_fwd", "scan", "duplicate
                                             "sort_passes", "tile_ranges", "blend_fwd", "bwd_zero",
                                             "blend_bwd", "preprocess_bwd", "adam", "se3"};
 
+// Pinned read-back slot of the instance count, one per host thread, created on first use and kept
+// for the life of the process.
+struct HostCountSlot {
+  uint32_t* host = nullptr;
+  cudaEvent_t arrived = nullptr;
+};
+static HostCountSlot* host_count_slot() {
+  static thread_local HostCountSlot slot;
+  if (!slot.host) {
+    void* p = nullptr;
+    if (cudaHostAlloc(&p, 64, cudaHostAllocDefault) != cudaSuccess) return nullptr;
+    if (cudaEventCreateWithFlags(&slot.arrived, cudaEventDisableTiming) != cudaSuccess) {
+      cudaFreeHost(p);
+      return nullptr;
+    }
+    slot.host = static_cast<uint32_t*>(p);
+  }
+  return &slot;
+}
+
 static int check_pairs(const char* who, const void* shs, const void* colors, const void* scales,
                        const void* rotations, const void* cov) {
   if ((shs == nullptr) == (colors == nullptr)) {
@@ -103,6 +123,16 @@ extern "C" size_t egs_binning_bytes(int R, int W, int H) {
   return BinningLayout((size_t)(R < 0 ? 0 : R)).total;
 }
 extern "C" size_t egs_image_bytes(int W, int H) { return ImageLayout(W, H).total; }
+// inverse of egs_binning_bytes on capacities (multiples of SORT_TILE): the size is strictly
+// increasing in the number of sort blocks, so a binary search recovers it
+extern "C" int egs_binning_capacity(size_t bytes) {
+  size_t lo = 0, hi = (size_t)1 << 18;   // blocks; 2^18 * 4096 = 2^30 instances
+  while (lo < hi) {
+    const size_t mid = (lo + hi) / 2;
+    if (BinningLayout(mid * SORT_TILE).total < bytes) lo = mid + 1; else hi = mid;
+  }
+  return (int)(lo * SORT_TILE);
+}
 extern "C" size_t egs_backward_scratch_bytes(int P) { return BackwardScratch::bytes((size_t)(P < 0 ? 0 : P)); }
 
 extern "C" int egs_forward(const EgsForwardArgs* args, void* stream_v, int* num_rendered) {
@@ -153,18 +183,57 @@ extern "C" int egs_forward(const EgsForwardArgs* args, void* stream_v, int* num_
   if (int rc = launch_preprocess_forward(a, g, stream)) return rc;
   if (int rc = launch_scan_tiles(g, a.P, stream, a.debug)) return rc;
 
-  // the one device->host read per forward (the reference's is rasterizer_impl.cu:281-282)
-  uint32_t R_host = 0;
-  EGS_CUDA_TRY(cudaMemcpyAsync(&R_host, g.point_offsets + (a.P - 1), sizeof(uint32_t),
-                               cudaMemcpyDeviceToHost, stream));
-  EGS_CUDA_TRY(cudaStreamSynchronize(stream));
+  // The one device->host read per forward (the reference's is rasterizer_impl.cu:281-282): the
+  // instance count lands in a pinned slot and an event marks its arrival.
+  HostCountSlot* slot = host_count_slot();
+  if (!slot) {
+    set_error("egs_forward: cannot allocate the pinned read-back slot");
+    return EGS_ERR_CUDA;
+  }
+  const uint32_t* n_dev = g.point_offsets + (a.P - 1);
+  EGS_CUDA_TRY(cudaMemcpyAsync(slot->host, n_dev, sizeof(uint32_t), cudaMemcpyDeviceToHost, stream));
+  EGS_CUDA_TRY(cudaEventRecord(slot->arrived, stream));
+
+  const char* force = getenv("EGS_SORT");
+  const bool fits = packed_path_fits(a.P, a.width, a.height);
+  const bool forced = force && force[0] != 0;
+
+  // Speculative run: with a caller-provided guess the binning workspace is sized from the guess and
+  // binning + blend are enqueued before the count is known; the kernels read the count on the
+  // device and skip themselves if it does not fit. Only the bucket path takes part.
+  int capacity = 0;
+  void* bin_mem = nullptr;
+  bool enqueued = false;
+  if (a.num_rendered_hint > 0 && fits && !forced && !a.debug &&
+      bucket_path_ok(a.P, a.num_rendered_hint, a.width, a.height)) {
+    capacity = a.num_rendered_hint;
+    bin_mem = a.binning_alloc(a.binning_ctx, egs_binning_bytes(capacity, a.width, a.height));
+    if (!bin_mem) {
+      set_error("egs_forward: binning workspace callback returned NULL");
+      return EGS_ERR_ALLOC;
+    }
+    const BinningPtrs b(bin_mem, (size_t)capacity);
+    const InstanceCount count{n_dev, (uint32_t)capacity};
+    if (int rc = launch_binning_buckets(g, b, im, a.radii, a.P, capacity, count, a.width, a.height, stream, false))
+      return rc;
+    if (int rc = launch_blend_forward(a, g, b.vals[0], im, stream)) return rc;
+    enqueued = true;
+  }
+
+  // wait for the count only (it arrived right after the scan; the GPU keeps working on what was
+  // enqueued above)
+  EGS_CUDA_TRY(cudaEventSynchronize(slot->arrived));
+  const uint32_t R_host = *slot->host;
   if (R_host >= (1u << 30)) {
     set_error("egs_forward: num_rendered %u exceeds the supported 2^30", R_host);
     return EGS_ERR_TOO_LARGE;
   }
   const int R = (int)R_host;
+  *num_rendered = R;
+  if (enqueued && R <= capacity) return EGS_OK;
 
-  void* bin_mem = a.binning_alloc(a.binning_ctx, egs_binning_bytes(R, a.width, a.height));
+  // exact run (no guess, guess too small, forced path, or a path that does not speculate)
+  bin_mem = a.binning_alloc(a.binning_ctx, egs_binning_bytes(R, a.width, a.height));
   if (!bin_mem) {
     set_error("egs_forward: binning workspace callback returned NULL");
     return EGS_ERR_ALLOC;
@@ -177,22 +246,18 @@ extern "C" int egs_forward(const EgsForwardArgs* args, void* stream_v, int* num_
   //            fit one 64-bit word, e.g. more than 1M Gaussians at 1280x720)
   //   pairs8   the first, plain 8-bit pair sort of binning.cu, kept as an independent cross-check
   // EGS_SORT=packed|pairs|pairs8 forces a path (tests, A/B timing).
-  const char* force = getenv("EGS_SORT");
-  const bool fits = packed_path_fits(a.P, a.width, a.height);
   if (force && strcmp(force, "pairs8") == 0) {
     if (int rc = launch_binning(g, b, im, a.radii, a.P, R, a.width, a.height, stream, a.debug)) return rc;
   } else if (!fits || (force && strcmp(force, "pairs") == 0)) {
     if (int rc = launch_binning_packed(g, b, im, a.radii, a.P, R, a.width, a.height, true, stream, a.debug)) return rc;
   } else if (bucket_path_ok(a.P, R, a.width, a.height) && !(force && strcmp(force, "packed") == 0)) {
-    if (int rc = launch_binning_buckets(g, b, im, a.radii, a.P, R, a.width, a.height, stream, a.debug)) return rc;
+    const InstanceCount count{n_dev, (uint32_t)R};
+    if (int rc = launch_binning_buckets(g, b, im, a.radii, a.P, R, count, a.width, a.height, stream, a.debug))
+      return rc;
   } else {
     if (int rc = launch_binning_packed(g, b, im, a.radii, a.P, R, a.width, a.height, false, stream, a.debug)) return rc;
   }
-
-  const uint32_t* point_list = b.vals[0];
-  if (int rc = launch_blend_forward(a, g, point_list, im, stream)) return rc;
-  *num_rendered = R;
-  return EGS_OK;
+  return launch_blend_forward(a, g, b.vals[0], im, stream);
 }
 
 extern "C" int egs_backward(const EgsBackwardArgs* args, void* stream_v) {
@@ -230,7 +295,8 @@ extern "C" int egs_backward(const EgsBackwardArgs* args, void* stream_v) {
     EGS_CUDA_TRY(cudaMemsetAsync(s.acc, 0, (size_t)a.P * 48, stream));
   }
   if (a.num_rendered > 0) {
-    const BinningPtrs b(const_cast<void*>(a.binning_buffer), (size_t)a.num_rendered);
+    const size_t layout_for = a.binning_bytes ? (size_t)egs_binning_capacity(a.binning_bytes) : (size_t)a.num_rendered;
+    const BinningPtrs b(const_cast<void*>(a.binning_buffer), layout_for);
     const uint32_t* point_list = b.vals[0];
     if (int rc = launch_blend_backward(a, g, point_list, im, s, stream)) return rc;
   }

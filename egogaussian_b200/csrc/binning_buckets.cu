@@ -51,9 +51,12 @@ constexpr int BK_CAP = 12288;                      // words per bucket held in s
 __global__ void __launch_bounds__(256)
 duplicate_words_kernel(int P, const float2* __restrict__ means2D, const float* __restrict__ depths,
                        const uint32_t* __restrict__ offsets, const int* __restrict__ radii,
-                       uint64_t* __restrict__ words, int grid_x, int grid_y, int idx_bits) {
+                       uint64_t* __restrict__ words, int grid_x, int grid_y, int idx_bits,
+                       InstanceCount count) {
   const int idx = blockIdx.x * blockDim.x + threadIdx.x;
   if (idx >= P) return;
+  uint32_t n;
+  if (!count.get(n)) return;   // more instances than the buffer holds: write nothing
   const int r = radii[idx];
   if (r <= 0) return;
   uint32_t off = (idx == 0) ? 0u : offsets[idx - 1];
@@ -71,7 +74,10 @@ duplicate_words_kernel(int P, const float2* __restrict__ means2D, const float* _
 // shared-memory atomics are a fraction of the word count.
 constexpr int BH_ITEMS = 8;
 __global__ void __launch_bounds__(256)
-bucket_histogram_kernel(const uint64_t* __restrict__ words, int n, int shift, uint32_t* __restrict__ bucket_hist) {
+bucket_histogram_kernel(const uint64_t* __restrict__ words, InstanceCount count, int shift,
+                        uint32_t* __restrict__ bucket_hist) {
+  uint32_t n;
+  if (!count.get(n)) return;
   __shared__ uint32_t s_hist[MSD_BINS];
   for (int i = threadIdx.x; i < MSD_BINS; i += blockDim.x) s_hist[i] = 0;
   __syncthreads();
@@ -175,11 +181,13 @@ __device__ __forceinline__ void st_relaxed_u32(uint32_t* p, uint32_t v) {
 }
 
 __global__ void __launch_bounds__(MSD_THREADS)
-msd_partition_kernel(const uint64_t* __restrict__ in, uint64_t* __restrict__ out, int n, int shift,
-                     const uint32_t* __restrict__ bucket_start, uint32_t* __restrict__ ticket,
+msd_partition_kernel(const uint64_t* __restrict__ in, uint64_t* __restrict__ out, InstanceCount count,
+                     int shift, const uint32_t* __restrict__ bucket_start, uint32_t* __restrict__ ticket,
                      uint32_t* __restrict__ status_raw) {
   extern __shared__ __align__(16) unsigned char smem_raw[];
   MsdSmem& S = *reinterpret_cast<MsdSmem*>(smem_raw);
+  uint32_t n;
+  if (!count.get(n)) return;   // the guessed capacity was too small: forward re-runs this stage
   const unsigned tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   if (tid == 0) S.tile = atomicAdd(ticket, 1u);
 #pragma unroll
@@ -188,6 +196,9 @@ msd_partition_kernel(const uint64_t* __restrict__ in, uint64_t* __restrict__ out
   const uint32_t tile = S.tile;
   const unsigned lt_mask = (1u << lane) - 1u;
   const size_t block_base = (size_t)tile * MSD_TILE;
+  // the grid is sized for the capacity; CTAs whose tile lies beyond the real count have nothing to
+  // do and nobody looks back at them (look-backs only walk towards tile 0)
+  if (block_base >= (size_t)n) return;
   const size_t warp_base = block_base + (size_t)warp * (32 * MSD_ITEMS);
 
   uint64_t word[MSD_ITEMS];
@@ -498,11 +509,15 @@ bool bucket_path_ok(int P, int R, int W, int H) {
   return (long long)R <= (long long)MSD_BINS * BK_CAP * 8 / 10;
 }
 
+// `capacity` sizes the grids and the workspace `b`; the real number of instances is read on the
+// device through `count` (it may still be in flight when this is enqueued). capacity == 0 means
+// the count is known to be 0.
 int launch_binning_buckets(const GeomPtrs& g, const BinningPtrs& b, const ImagePtrs& im, const int* radii,
-                           int P, int R, int W, int H, cudaStream_t stream, bool debug) {
+                           int P, int capacity, InstanceCount count, int W, int H, cudaStream_t stream,
+                           bool debug) {
   const int gx = tiles_x(W), gy = tiles_y(H);
   const int n_tiles = gx * gy;
-  if (R == 0) {
+  if (capacity == 0) {
     EGS_CUDA_TRY(cudaMemsetAsync(im.ranges, 0, (size_t)n_tiles * sizeof(uint2), stream));
     return EGS_OK;
   }
@@ -522,11 +537,11 @@ int launch_binning_buckets(const GeomPtrs& g, const BinningPtrs& b, const ImageP
     const size_t zero = reinterpret_cast<char*>(b.status + b.sort_blocks * MSD_BINS) - reinterpret_cast<char*>(b.hist);
     EGS_CUDA_TRY(cudaMemsetAsync(b.hist, 0, zero, stream));
     duplicate_words_kernel<<<(P + 255) / 256, 256, 0, stream>>>(P, g.means2D, g.depths, g.point_offsets, radii,
-                                                                b.keys[1], gx, gy, ib);
+                                                                b.keys[1], gx, gy, ib, count);
     EGS_AFTER_LAUNCH(stream, debug);
-    int hist_blocks = (R + 256 * BH_ITEMS - 1) / (256 * BH_ITEMS);
+    int hist_blocks = (capacity + 256 * BH_ITEMS - 1) / (256 * BH_ITEMS);
     if (hist_blocks > 148 * 4) hist_blocks = 148 * 4;
-    bucket_histogram_kernel<<<hist_blocks, 256, 0, stream>>>(b.keys[1], R, ib + 32 + bucket_shift, hist);
+    bucket_histogram_kernel<<<hist_blocks, 256, 0, stream>>>(b.keys[1], count, ib + 32 + bucket_shift, hist);
     EGS_AFTER_LAUNCH(stream, debug);
     bucket_scan_kernel<<<1, MSD_BINS, 0, stream>>>(hist, start, order);
     EGS_AFTER_LAUNCH(stream, debug);
@@ -536,7 +551,7 @@ int launch_binning_buckets(const GeomPtrs& g, const BinningPtrs& b, const ImageP
     EGS_CUDA_TRY(cudaFuncSetAttribute(msd_partition_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                       (int)sizeof(MsdSmem)));
     msd_partition_kernel<<<(int)b.sort_blocks, MSD_THREADS, sizeof(MsdSmem), stream>>>(
-        b.keys[1], b.keys[0], R, ib + 32 + bucket_shift, start, b.ticket, b.status);
+        b.keys[1], b.keys[0], count, ib + 32 + bucket_shift, start, b.ticket, b.status);
     EGS_AFTER_LAUNCH(stream, debug);
   }
   {

@@ -143,10 +143,13 @@ inline int sort_passes(int W, int H) {
 struct BinningLayout {
   size_t keys[2], vals[2], hist, status, ticket, total;
   size_t sort_blocks;
-  explicit BinningLayout(size_t R) {
+  // `instances` is num_rendered or a capacity >= num_rendered; the layout only depends on it
+  // rounded up to a multiple of SORT_TILE, and `total` is strictly increasing in that capacity
+  explicit BinningLayout(size_t instances) {
     size_t o = 0;
     auto take = [&](size_t bytes) { size_t r = o; o = align_up(o + bytes); return r; };
-    sort_blocks = (R + SORT_TILE - 1) / SORT_TILE;
+    sort_blocks = (instances + SORT_TILE - 1) / SORT_TILE;
+    const size_t R = sort_blocks * SORT_TILE;
     keys[0] = take(R * 8);
     keys[1] = take(R * 8);
     vals[0] = take(R * 4);
@@ -226,8 +229,22 @@ int launch_binning_packed(const GeomPtrs& g, const BinningPtrs& b, const ImagePt
                           int P, int R, int W, int H, bool pairs, cudaStream_t stream, bool debug);
 // MSD-bucket path (binning_buckets.cu): one global partition pass + one CTA per bucket
 bool bucket_path_ok(int P, int R, int W, int H);
+// The number of instances as the device sees it: `n_dev` points at the last element of the
+// tiles_touched scan, `cap` is what the workspace was sized for. Kernels enqueued before the host
+// knows the count read it here and skip themselves when it does not fit.
+struct InstanceCount {
+  const uint32_t* n_dev;
+  uint32_t cap;
+#ifdef __CUDACC__
+  __device__ __forceinline__ bool get(uint32_t& n) const {
+    n = *n_dev;
+    return n <= cap;
+  }
+#endif
+};
 int launch_binning_buckets(const GeomPtrs& g, const BinningPtrs& b, const ImagePtrs& im, const int* radii,
-                           int P, int R, int W, int H, cudaStream_t stream, bool debug);
+                           int P, int capacity, InstanceCount count, int W, int H, cudaStream_t stream,
+                           bool debug);
 int launch_tile_ranges(int R, const uint64_t* sorted_keys, const ImagePtrs& im, cudaStream_t stream,
                        bool debug);
 int launch_binning(const GeomPtrs& g, const BinningPtrs& b, const ImagePtrs& im, const int* radii,

@@ -41,6 +41,23 @@ struct BlobCtx {
   torch::Device dev;
 };
 
+// Recent num_rendered per problem size (a handful of entries per host thread is plenty: a trainer
+// renders one or two resolutions).
+struct CountGuess {
+  int P = -1, W = 0, H = 0;
+  double recent_max = 0;   // decays slowly so that a past outlier does not inflate the workspace for ever
+};
+CountGuess& guess_for(int P, int W, int H) {
+  static thread_local CountGuess table[4];
+  static thread_local int next = 0;
+  for (auto& g : table)
+    if (g.P == P && g.W == W && g.H == H) return g;
+  CountGuess& g = table[next];
+  next = (next + 1) % 4;
+  g = CountGuess{P, W, H, 0};
+  return g;
+}
+
 void* blob_alloc(void* ctx, size_t bytes) {
   auto* c = static_cast<BlobCtx*>(ctx);
   c->blob = torch::empty({(int64_t)bytes}, torch::TensorOptions().dtype(torch::kUInt8).device(c->dev));
@@ -107,9 +124,14 @@ rasterize_gaussians(const torch::Tensor& background, const torch::Tensor& means3
   a.geom_alloc = blob_alloc;    a.geom_ctx = &geom;
   a.binning_alloc = blob_alloc; a.binning_ctx = &binning;
   a.image_alloc = blob_alloc;   a.image_ctx = &image;
+  // guess of num_rendered from recent calls with the same problem size: lets egs_forward enqueue
+  // everything before the count is read back (it re-runs by itself when the guess is too small)
+  CountGuess& guess = guess_for(P, W, H);
+  a.num_rendered_hint = guess.recent_max > 0 ? (int)(guess.recent_max * 1.25) + 8192 : 0;
 
   int rendered = 0;
   check(egs_forward(&a, at::cuda::getCurrentCUDAStream().stream(), &rendered), "egs_forward");
+  guess.recent_max = std::max<double>(rendered, guess.recent_max * (63.0 / 64.0));
   return std::make_tuple(rendered, out_color, out_depth, out_alpha, radii, geom.blob, binning.blob,
                          image.blob);
 }
@@ -198,6 +220,7 @@ rasterize_gaussians_backward(const torch::Tensor& background, const torch::Tenso
     a.dL_dscales = has_sr ? dL_dscales.data_ptr<float>() : nullptr;
     a.dL_drotations = has_sr ? dL_drotations.data_ptr<float>() : nullptr;
     a.debug = debug;
+    a.binning_bytes = (size_t)binningBuffer.numel();   // the blob may be laid out for a guessed capacity
     check(egs_backward(&a, at::cuda::getCurrentCUDAStream().stream()), "egs_backward");
   }
   return std::make_tuple(dL_dmeans2D, dL_dcolors, dL_dopacity, dL_dmeans3D, dL_dcov3D, dL_dsh,

@@ -84,12 +84,24 @@ typedef struct EgsForwardArgs {
   EgsAllocFn geom_alloc;   void* geom_ctx;    /* size = egs_geom_bytes(P) */
   EgsAllocFn binning_alloc; void* binning_ctx; /* size = egs_binning_bytes(num_rendered) */
   EgsAllocFn image_alloc;  void* image_ctx;   /* size = egs_image_bytes(width,height) */
+  /* Optional: the caller's guess of num_rendered (0 = none), e.g. 1.2 x the value of the previous
+   * iteration. With a guess the binning workspace is requested for that many instances BEFORE the
+   * count is known and every kernel is enqueued without waiting for it; the one device->host
+   * read is then waited for after the last launch (it completes early in the forward), so the
+   * GPU never idles on the host and the call returns about one blend earlier. If the real count
+   * exceeds the guess, the enqueued work has skipped itself, binning_alloc is called a second
+   * time with the exact size and binning + blend are enqueued again: results never depend on the
+   * guess. */
+  int num_rendered_hint;
 } EgsForwardArgs;
 
 /* Sizes of the three workspaces; pure functions of their arguments so that backward can
- * re-derive the internal layout (rasterizer_impl.h:67-73 `required<T>`). */
+ * re-derive the internal layout (rasterizer_impl.h:67-73 `required<T>`). The binning workspace is
+ * laid out for a capacity = num_rendered rounded up to a multiple of 4096, and its size is
+ * strictly increasing in that capacity, so egs_binning_capacity() recovers it from the size. */
 size_t egs_geom_bytes(int P);
 size_t egs_binning_bytes(int num_rendered, int width, int height);
+int egs_binning_capacity(size_t binning_bytes);
 size_t egs_image_bytes(int width, int height);
 
 /* Forward render. On success *num_rendered is the number of (Gaussian, tile) instances.
@@ -132,6 +144,9 @@ typedef struct EgsBackwardArgs {
   float* dL_dscales;           /* [P,3]  written only when scales != NULL, else may be NULL */
   float* dL_drotations;        /* [P,4]  written only when rotations != NULL, else may be NULL */
   int debug;
+  /* Size in bytes of the binning blob forward was given (0 = egs_binning_bytes(num_rendered)):
+   * when forward ran with a num_rendered_hint the blob is laid out for the hinted capacity. */
+  size_t binning_bytes;
 } EgsBackwardArgs;
 
 size_t egs_backward_scratch_bytes(int P);
@@ -225,6 +240,7 @@ typedef struct EgsImageView {
   const uint32_t* ranges;        /* [tiles,2] */
 } EgsImageView;
 int egs_geom_view(const void* geom_buffer, int P, EgsGeomView* out);
+/* `num_rendered` here only selects the layout: pass egs_binning_capacity(size of the blob). */
 int egs_binning_view(const void* binning_buffer, int num_rendered, int width, int height,
                      EgsBinningView* out);
 int egs_image_view(const void* image_buffer, int width, int height, EgsImageView* out);

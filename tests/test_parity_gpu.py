@@ -302,6 +302,35 @@ def test_three_binning_paths_agree(built, cuda_device, monkeypatch):
             assert int(torch.bincount(tiles >> shift).max()) > 12288
 
 
+def test_num_rendered_hint_never_changes_results(built, cuda_device):
+    """EgsForwardArgs.num_rendered_hint only moves the host wait: a generous guess, a tight one, one
+    that is too small (the enqueued work skips itself and the exact path re-runs after a second
+    binning_alloc) and no guess at all give identical buffers, images and gradients."""
+    from egogaussian_b200 import cabi
+    kw, ups = case_inputs(CASES[0], cuda_device)
+    base, gbase = run_cuda(kw, ups)
+    R = base.num_rendered
+    assert R > 4096
+    bkw = {k: v for k, v in kw.items() if k not in ("opacities", "image_height", "image_width")}
+    for hint in (R, R + 1, 2 * R + 12345, R - 1, R // 3, 1):
+        f = cabi.forward(num_rendered_hint=hint, **kw)
+        assert f.num_rendered == R, hint
+        if hint >= R:   # the guessed workspace was kept
+            assert f.binning.numel() == cabi.load().egs_binning_bytes(hint, f.W, f.H), hint
+        else:
+            assert f.binning.numel() == base.binning.numel(), hint
+        for k in ("color", "depth", "alpha", "radii"):
+            assert torch.equal(getattr(f, k), getattr(base, k)), (hint, k)
+        fv, bv = f.binning_view(), base.binning_view()
+        assert torch.equal(fv["keys"], bv["keys"]) and torch.equal(fv["values"], bv["values"]), hint
+        fi, bi = f.image_view(), base.image_view()
+        assert torch.equal(fi["ranges"], bi["ranges"]) and torch.equal(fi["n_contrib"], bi["n_contrib"]), hint
+        g = cabi.backward(f, dL_dcolor=ups["dL_dcolor"], dL_ddepth=ups["dL_ddepth"],
+                          dL_dalpha=ups["dL_dalpha"], **bkw)
+        for k in ("means2D", "means3D", "opacity", "sh", "scales", "rotations"):
+            assert grad_rel_err(g[k], gbase[k]) <= GRAD_RTOL, (hint, k)
+
+
 def test_kernel_variants_agree(built, cuda_device, monkeypatch):
     """The alternative blend kernels kept for A/B timing compute the same thing: the two forward
     kernels are bit-identical (the log-domain pre-filter of v2 is conservative), the two backward
