@@ -25,6 +25,7 @@ from __future__ import annotations
 
 import argparse
 import json
+import math
 import os
 import subprocess
 import sys
@@ -191,6 +192,82 @@ def timed_region(step, steps, warmup, dist_on, device):
     return sec
 
 
+class _TrainerModel:
+    """Raw optimiser parameters of the bench scene, named like the reference's GaussianModel
+    attributes (scene/gaussian_model.py:326-338): what a training iteration really starts from."""
+
+    def __init__(self, a, device):
+        import torch
+        from egogaussian_b200 import scenes
+        sc = scenes.make_scene(a.P, a.width, a.height, sh_degree=a.sh_degree, seed=3001, view=None)
+        op = sc.opacities.reshape(-1, 1).clamp(1e-5, 1 - 1e-5)
+        raw = {"_xyz": sc.means3D, "_features_dc": sc.shs[:, :1], "_features_rest": sc.shs[:, 1:],
+               "_opacity": torch.log(op / (1 - op)), "_scaling": torch.log(sc.scales), "_rotation": sc.rotations}
+        for k, v in raw.items():
+            setattr(self, k, v.to(device).contiguous().requires_grad_(True))
+        self._is_object = torch.zeros(a.P, 1, dtype=torch.int32, device=device)
+        self.active_sh_degree = self.max_sh_degree = a.sh_degree
+        self.names = list(raw)
+        self.lrs = [1.6e-4, 2.5e-3, 2.5e-3 / 20, 0.05, 5e-3, 1e-3]   # arguments/__init__.py defaults
+        cam = sc.camera
+        self.image_width, self.image_height = a.width, a.height
+        self.FoVx, self.FoVy = 2 * math.atan(cam.tanfovx), 2 * math.atan(cam.tanfovy)
+        self.world_view_transform = cam.viewmatrix.to(device)
+        self.full_proj_transform = cam.projmatrix.to(device)
+        self.camera_center = cam.campos.to(device)
+        self.bg, self.tanfovx, self.tanfovy = sc.bg.to(device), cam.tanfovx, cam.tanfovy
+
+    def params(self):
+        return [getattr(self, k) for k in self.names]
+
+
+class _Pipe:
+    compute_cov3D_python = True    # forced by the reference's trainers (train.py:49)
+    convert_SHs_python = False
+
+
+def eager_glue(pc, scaling_modifier=1.0):
+    """What the reference's Python evaluates before every rasterizer call, as the same sequence of
+    eager torch ops (get_opacity / get_features / get_covariance: scene/gaussian_model.py:29-33,
+    126-153,167-168; zero-filled matrices written entry by entry: utils/general_utils.py:110-158).
+    Used only to time the untouched glue beside the fused kernels."""
+    import torch
+    opacity = torch.sigmoid(pc._opacity)
+    shs = torch.cat((pc._features_dc, pc._features_rest), dim=1)
+    s = scaling_modifier * torch.exp(pc._scaling)
+    r = pc._rotation
+    q = r / torch.sqrt(r[:, 0] * r[:, 0] + r[:, 1] * r[:, 1] + r[:, 2] * r[:, 2] + r[:, 3] * r[:, 3])[:, None]
+    w, x, y, z = q[:, 0], q[:, 1], q[:, 2], q[:, 3]
+    R = torch.zeros((q.size(0), 3, 3), device=q.device)
+    entries = ((0, 0, 1 - 2 * (y * y + z * z)), (0, 1, 2 * (x * y - w * z)), (0, 2, 2 * (x * z + w * y)),
+               (1, 0, 2 * (x * y + w * z)), (1, 1, 1 - 2 * (x * x + z * z)), (1, 2, 2 * (y * z - w * x)),
+               (2, 0, 2 * (x * z - w * y)), (2, 1, 2 * (y * z + w * x)), (2, 2, 1 - 2 * (x * x + y * y)))
+    for i, j, v in entries:
+        R[:, i, j] = v
+    S = torch.zeros((s.shape[0], 3, 3), dtype=torch.float, device=s.device)
+    for j in range(3):
+        S[:, j, j] = s[:, j]
+    L = R @ S
+    sym = L @ L.transpose(1, 2)
+    cov = torch.zeros((sym.shape[0], 6), dtype=torch.float, device=sym.device)
+    for k, (i, j) in enumerate(((0, 0), (0, 1), (0, 2), (1, 1), (1, 2), (2, 2))):
+        cov[:, k] = sym[:, i, j]
+    return cov, opacity, shs
+
+
+def trainer_iteration_rate(a, device, weights, render_fn, optimizer_step, dist_on):
+    """iterations/s of: raw parameters -> glue -> rasterizer -> loss -> backward -> Adam."""
+    wc, wd, wa = (w.to(device).contiguous() for w in weights)
+
+    def it():
+        color, depth, alpha = render_fn()
+        loss = (color * wc).sum() + (depth * wd).sum() + (alpha * wa).sum()
+        loss.backward()
+        optimizer_step()
+
+    return a.steps / timed_region(it, a.steps, 3, dist_on, device)
+
+
 def cpu_baseline(cpu_kw, weights):
     """One fwd+bwd iteration of the same workload on the host cores with the CPU oracle."""
     from oracle import cpu_oracle as orc
@@ -346,6 +423,49 @@ def run_ours(a, rank, world, local_rank):
     except Exception as exc:  # informational only
         extra["train_step_error"] = str(exc)[:200]
 
+    # ---- trainer mode: the iteration starts from the RAW parameters ----------
+    # raw -> activations + covariance -> rasterizer -> loss -> backward -> Adam over the six groups,
+    # once with the fused model kernels behind gaussian_renderer.render(), once with the reference's
+    # eager torch glue in front of the same rasterizer. `--impl reference` reports the same
+    # iteration with the reference rasterizer and torch.optim.Adam.
+    if world == 1 and not a.no_e2e:
+        try:
+            from egogaussian_b200.gaussian_renderer import render
+            del leaves, dv
+            pc = _TrainerModel(a, device)
+            params = pc.params()
+            ms_ = [torch.zeros_like(p) for p in params]
+            vs_ = [torch.zeros_like(p) for p in params]
+            stepc = [0]
+
+            def fused_adam():
+                stepc[0] += 1
+                with torch.no_grad():
+                    _C.adam_step(params, [p.grad for p in params], ms_, vs_, pc.lrs, [stepc[0]] * len(params),
+                                 0.9, 0.999, 1e-15)
+                for p in params:
+                    p.grad = None
+
+            def render_fused():
+                pkg = render(pc, pc, _Pipe(), pc.bg)
+                return pkg["render"], pkg["depth"], pkg["alpha"]
+
+            def render_eager_glue():
+                cov, opacity, shs = eager_glue(pc)
+                rs = GaussianRasterizationSettings(a.height, a.width, pc.tanfovx, pc.tanfovy, pc.bg, 1.0,
+                                                   pc.world_view_transform, pc.full_proj_transform, a.sh_degree,
+                                                   pc.camera_center, False, False)
+                color, _, depth, alpha = GaussianRasterizer(rs)(
+                    means3D=pc._xyz, means2D=torch.zeros_like(pc._xyz, requires_grad=True), opacities=opacity,
+                    shs=shs, cov3D_precomp=cov)
+                return color, depth, alpha
+
+            extra["trainer_iters_per_s"] = trainer_iteration_rate(a, device, weights, render_fused, fused_adam, False)
+            extra["trainer_iters_per_s_eager_glue"] = trainer_iteration_rate(a, device, weights, render_eager_glue,
+                                                                             fused_adam, False)
+        except Exception as exc:  # informational only
+            extra["trainer_error"] = str(exc)[:300]
+
     if rank != 0:
         return None
     line = {
@@ -433,7 +553,34 @@ def run_reference(a, rank, world, local_rank):
             t.grad = None
 
     sec2 = timed_region(e2e_step, a.steps, a.warmup, False, device)
-    return {"impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": 1, "steps": a.steps,
+
+    # trainer mode, the reference's way: eager torch glue + its rasterizer + torch.optim.Adam
+    # configured as scene/gaussian_model.py:189-198 (one group per tensor, lr per group, eps 1e-15)
+    extra = {}
+    try:
+        del leaves, dv
+        pc = _TrainerModel(a, device)
+        opt = torch.optim.Adam([{"params": [p], "lr": lr} for p, lr in zip(pc.params(), pc.lrs)], lr=0.0, eps=1e-15)
+        rs = dict(bg=pc.bg, scale_modifier=1.0, viewmatrix=pc.world_view_transform, projmatrix=pc.full_proj_transform,
+                  tanfovx=pc.tanfovx, tanfovy=pc.tanfovy, image_height=a.height, image_width=a.width,
+                  sh_degree=a.sh_degree, campos=pc.camera_center)
+
+        def render_reference():
+            cov, opacity, shs = eager_glue(pc)
+            color, _, depth, alpha = rast(rs, means3D=pc._xyz, means2D=torch.zeros_like(pc._xyz, requires_grad=True),
+                                          opacities=opacity, shs=shs, scales=None, rotations=None, cov3D_precomp=cov)
+            return color, depth, alpha
+
+        def adam():
+            opt.step()
+            opt.zero_grad(set_to_none=True)
+
+        extra["trainer_iters_per_s"] = trainer_iteration_rate(a, device, weights, render_reference, adam, False)
+    except Exception as exc:  # informational only
+        extra["trainer_error"] = str(exc)[:300]
+
+    return {"impl": "reference", "extra": extra,
+            "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": 1, "steps": a.steps,
             "warmup": a.warmup, "ms_per_step": sec / a.steps * 1e3, "higher_is_better": True, "scaling": "weak",
             "vs_baseline": None, "dtype": "f32", "data": "synthetic",
             "config": {"workload": "configs[2]: 1M-Gaussian SH3 scene, 1280x720, unmodified reference CUDA "

@@ -64,6 +64,14 @@ class EgsAdamGroup(C.Structure):
                 ("exp_avg_sq", c_float_p), ("n", C.c_longlong), ("lr", C.c_double), ("step", C.c_int)]
 
 
+class EgsModelArgs(C.Structure):
+    _fields_ = [("P", C.c_int), ("sh_coeffs", C.c_int),
+                ("scaling_raw", c_float_p), ("rotation_raw", c_float_p), ("opacity_raw", c_float_p),
+                ("features_dc", c_float_p), ("features_rest", c_float_p), ("scale_modifier", C.c_float),
+                ("is_object", C.c_void_p), ("which_object", C.c_int),
+                ("accum_R", c_float_p), ("train_R", c_float_p), ("row0_copies", C.c_int)]
+
+
 class EgsGeomView(C.Structure):
     _fields_ = [("depths", C.c_void_p), ("means2D", C.c_void_p), ("conic_opacity", C.c_void_p),
                 ("rgb_depth", C.c_void_p), ("clamped", C.c_void_p), ("tiles_touched", C.c_void_p),
@@ -82,7 +90,7 @@ class EgsImageView(C.Structure):
 EXPORTED_SYMBOLS = [
     "egs_geom_bytes", "egs_binning_bytes", "egs_binning_capacity", "egs_image_bytes", "egs_forward",
     "egs_backward_scratch_bytes", "egs_backward", "egs_mark_visible", "egs_adam_step",
-    "egs_se3_apply", "egs_adam_se3_step", "egs_geom_view", "egs_binning_view", "egs_image_view",
+    "egs_se3_apply", "egs_adam_se3_step", "egs_model_forward", "egs_model_backward", "egs_geom_view", "egs_binning_view", "egs_image_view",
     "egs_launch_count", "egs_last_error", "egs_abi_version",
     "egs_profile_enable", "egs_profile_read", "egs_profile_stage_name",
 ]
@@ -122,6 +130,10 @@ def load() -> C.CDLL:
     lib.egs_adam_se3_step.argtypes = [C.c_int, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p,
                                       C.c_int, C.c_void_p, C.c_double, C.c_int, C.c_double, C.c_double,
                                       C.c_double, C.c_void_p]
+    lib.egs_model_forward.restype = C.c_int
+    lib.egs_model_forward.argtypes = [C.POINTER(EgsModelArgs), C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]
+    lib.egs_model_backward.restype = C.c_int
+    lib.egs_model_backward.argtypes = [C.POINTER(EgsModelArgs)] + [C.c_void_p] * 10
     lib.egs_geom_view.restype = C.c_int
     lib.egs_geom_view.argtypes = [C.c_void_p, C.c_int, C.POINTER(EgsGeomView)]
     lib.egs_binning_view.restype = C.c_int
@@ -405,6 +417,69 @@ def mark_visible(means3D, viewmatrix, projmatrix, stream=None):
         with torch.cuda.device(means3D.device):
             _check(lib.egs_mark_visible(P, _ptr(means3D), _ptr(viewmatrix), _ptr(projmatrix), out.data_ptr(),
                                         _stream_handle(stream)), "egs_mark_visible")
+    return out
+
+
+def _model_args(*, scaling_raw=None, rotation_raw=None, opacity_raw=None, features_dc=None, features_rest=None,
+                scale_modifier=1.0, is_object=None, which_object=None, accum_R=None, train_R=None,
+                row0_copies=0) -> EgsModelArgs:
+    m = EgsModelArgs()
+    first = next(t for t in (scaling_raw, opacity_raw, features_dc) if t is not None)
+    m.P = int(first.shape[0])
+    m.sh_coeffs = 0 if features_dc is None else 1 + (0 if features_rest is None else int(features_rest.shape[1]))
+    m.scaling_raw, m.rotation_raw, m.opacity_raw = _ptr(scaling_raw), _ptr(rotation_raw), _ptr(opacity_raw)
+    m.features_dc, m.features_rest = _ptr(features_dc), _ptr(features_rest)
+    m.scale_modifier = float(scale_modifier)
+    # which_object=None selects every Gaussian (gaussian_model.py:50-51): no mask at all
+    m.is_object = _ptr(is_object) if which_object is not None else None
+    m.which_object = int(which_object) if which_object is not None else 0
+    m.accum_R, m.train_R = _ptr(accum_R), _ptr(train_R)
+    m.row0_copies = int(row0_copies)
+    return m
+
+
+def model_forward(*, want=("cov3D", "opacity", "shs"), stream=None, **model):
+    """egs_model_forward: raw GaussianModel parameters -> {cov3D [P,6], opacity [P,1], shs [P,M,3]}."""
+    import torch
+    lib = load()
+    m = _model_args(**model)
+    dev = next(t for t in model.values() if hasattr(t, "device")).device
+    out = {}
+    if "cov3D" in want:
+        out["cov3D"] = torch.empty((m.P, 6), dtype=torch.float32, device=dev)
+    if "opacity" in want:
+        out["opacity"] = torch.empty((m.P, 1), dtype=torch.float32, device=dev)
+    if "shs" in want:
+        out["shs"] = torch.empty((m.P, m.sh_coeffs, 3), dtype=torch.float32, device=dev)
+    with torch.cuda.device(dev):
+        _check(lib.egs_model_forward(C.byref(m), _ptr(out.get("cov3D")), _ptr(out.get("opacity")),
+                                     _ptr(out.get("shs")), _stream_handle(stream)), "egs_model_forward")
+    return out
+
+
+def model_backward(*, dL_dcov3D=None, dL_dopacity=None, dL_dshs=None, stream=None, **model):
+    """egs_model_backward: gradients w.r.t. the raw parameters (and train_R when it is given)."""
+    import torch
+    lib = load()
+    m = _model_args(**model)
+    dev = next(t for t in model.values() if hasattr(t, "device")).device
+    out = {}
+    if dL_dcov3D is not None:
+        out["scaling_raw"] = torch.empty((m.P, 3), dtype=torch.float32, device=dev)
+        out["rotation_raw"] = torch.empty((m.P, 4), dtype=torch.float32, device=dev)
+        if model.get("train_R") is not None:
+            out["train_R"] = torch.empty((3, 3), dtype=torch.float32, device=dev)
+    if dL_dopacity is not None:
+        out["opacity_raw"] = torch.empty((m.P, 1), dtype=torch.float32, device=dev)
+    if dL_dshs is not None:
+        out["features_dc"] = torch.empty((m.P, 1, 3), dtype=torch.float32, device=dev)
+        out["features_rest"] = torch.empty((m.P, m.sh_coeffs - 1, 3), dtype=torch.float32, device=dev)
+    with torch.cuda.device(dev):
+        _check(lib.egs_model_backward(C.byref(m), _ptr(dL_dcov3D), _ptr(dL_dopacity), _ptr(dL_dshs),
+                                      _ptr(out.get("scaling_raw")), _ptr(out.get("rotation_raw")),
+                                      _ptr(out.get("opacity_raw")), _ptr(out.get("features_dc")),
+                                      _ptr(out.get("features_rest")), _ptr(out.get("train_R")),
+                                      _stream_handle(stream)), "egs_model_backward")
     return out
 
 

@@ -1,0 +1,262 @@
+// model.cu -- the GaussianModel activations between the optimiser's raw parameters and the
+// rasterizer inputs, forward and backward, as three small HBM-bound kernels (SURVEY.md 8a rows
+// A-21/A-22): covariance + opacity per Gaussian, and the dc/rest feature concatenation.
+//
+// Replaces, per iteration, in the reference (compute_cov3D_python is forced on, train.py:49):
+//   get_scaling / get_opacity / get_features          scene/gaussian_model.py:126-153
+//   get_covariance / get_rotated_covariance           scene/gaussian_model.py:29-63,167-171
+//   build_rotation / build_scaling_rotation / strip_symmetric   utils/general_utils.py:110-158
+// i.e. ~25 torch kernels and their autograd graph, by one launch each way (plus the concat).
+#include "common.cuh"
+#include "model_math.cuh"
+
+namespace egs {
+
+constexpr int MODEL_THREADS = 256;
+
+struct ModelKernelArgs {
+  int P;
+  const float* scaling_raw;
+  const float* rotation_raw;
+  const float* opacity_raw;
+  float mod;
+  const int* is_object;
+  int which;
+  const float* accum_R;
+  const float* train_R;
+  int row0_copies;
+};
+
+// Selection of build_covariance_from_scaling_rotation_w_rot (gaussian_model.py:46-63). The mask
+// tensor is [P,1], so `nonzero(mask).squeeze()` holds (row, 0) PAIRS and indexing L with it touches
+// row 0 once per selected row as well: row 0 is rotated whenever any row is. `row0_copies` (> 0
+// when that happens) is how many index entries name row 0; the host counts it (cabi / binding).
+__device__ __forceinline__ bool row_selected(const ModelKernelArgs& a, int i) {
+  if (a.accum_R == nullptr && a.train_R == nullptr) return false;
+  if (i == 0 && a.row0_copies > 0) return true;
+  return a.is_object == nullptr || a.is_object[i] == a.which;
+}
+
+__global__ void __launch_bounds__(MODEL_THREADS)
+model_forward_kernel(ModelKernelArgs a, float* __restrict__ cov3D, float* __restrict__ opacity) {
+  __shared__ float s_rot[18];
+  if (threadIdx.x < 9) s_rot[threadIdx.x] = a.accum_R ? a.accum_R[threadIdx.x] : 0.f;
+  else if (threadIdx.x < 18) s_rot[threadIdx.x] = a.train_R ? a.train_R[threadIdx.x - 9] : 0.f;
+  __syncthreads();
+  const int i = blockIdx.x * MODEL_THREADS + threadIdx.x;
+  if (i >= a.P) return;
+  if (opacity != nullptr) opacity[i] = sigmoid_fwd(a.opacity_raw[i]);
+  if (cov3D == nullptr) return;
+  const float s_raw[3] = {a.scaling_raw[3 * i], a.scaling_raw[3 * i + 1], a.scaling_raw[3 * i + 2]};
+  const float4 q_raw = reinterpret_cast<const float4*>(a.rotation_raw)[i];
+  RawFrame f;
+  raw_frame(s_raw, q_raw, a.mod, f);
+  M33 L = frame_factor(f);
+  if (row_selected(a, i)) {
+    const M33 A = m33_load(s_rot), T = m33_load(s_rot + 9);
+    L = rotate_factor(L, a.accum_R ? &A : nullptr, a.train_R ? &T : nullptr, nullptr);
+  }
+  float c[6];
+  factor_to_cov6(L, c);
+  float2* out = reinterpret_cast<float2*>(cov3D + 6 * (size_t)i);
+  out[0] = make_float2(c[0], c[1]);
+  out[1] = make_float2(c[2], c[3]);
+  out[2] = make_float2(c[4], c[5]);
+}
+
+__global__ void __launch_bounds__(MODEL_THREADS)
+model_backward_kernel(ModelKernelArgs a, const float* __restrict__ dL_dcov3D,
+                      const float* __restrict__ dL_dopacity, float* __restrict__ d_scaling_raw,
+                      float* __restrict__ d_rotation_raw, float* __restrict__ d_opacity_raw,
+                      float* __restrict__ d_train_R) {
+  __shared__ float s_rot[18];
+  __shared__ float s_dT[MODEL_THREADS / 32][9];
+  if (threadIdx.x < 9) s_rot[threadIdx.x] = a.accum_R ? a.accum_R[threadIdx.x] : 0.f;
+  else if (threadIdx.x < 18) s_rot[threadIdx.x] = a.train_R ? a.train_R[threadIdx.x - 9] : 0.f;
+  __syncthreads();
+  const int i = blockIdx.x * MODEL_THREADS + threadIdx.x;
+  const bool live = i < a.P;
+  float dT[9];
+#pragma unroll
+  for (int k = 0; k < 9; ++k) dT[k] = 0.f;
+
+  if (live && d_opacity_raw != nullptr) {
+    const float y = sigmoid_fwd(a.opacity_raw[i]);
+    d_opacity_raw[i] = sigmoid_bwd(y, dL_dopacity[i]);
+  }
+  if (live && dL_dcov3D != nullptr) {
+    const float s_raw[3] = {a.scaling_raw[3 * i], a.scaling_raw[3 * i + 1], a.scaling_raw[3 * i + 2]};
+    const float4 q_raw = reinterpret_cast<const float4*>(a.rotation_raw)[i];
+    RawFrame f;
+    raw_frame(s_raw, q_raw, a.mod, f);
+    const M33 L0 = frame_factor(f);
+    const float2* g2 = reinterpret_cast<const float2*>(dL_dcov3D + 6 * (size_t)i);
+    const float2 g01 = g2[0], g23 = g2[1], g45 = g2[2];
+    const float d6[6] = {g01.x, g01.y, g23.x, g23.y, g45.x, g45.y};
+    M33 dL0;
+    if (row_selected(a, i)) {
+      const M33 A = m33_load(s_rot), T = m33_load(s_rot + 9);
+      M33 mid;
+      const M33 Lf = rotate_factor(L0, a.accum_R ? &A : nullptr, a.train_R ? &T : nullptr, &mid);
+      M33 g = cov6_backward_to_factor(d6, Lf);
+      // every index entry that names this row receives the row's full gradient (index_put with
+      // duplicate indices): row 0 counts `row0_copies` times, any other selected row once
+      const float copies = (i == 0 && a.row0_copies > 0) ? (float)a.row0_copies : 1.f;
+#pragma unroll
+      for (int r = 0; r < 3; ++r)
+#pragma unroll
+        for (int c = 0; c < 3; ++c) g.m[r][c] *= copies;
+      if (a.train_R) {
+        const M33 gT = m33_mult(g, mid);   // dT = g mid^T
+#pragma unroll
+        for (int k = 0; k < 9; ++k) dT[k] = gT.m[k / 3][k % 3];
+        g = m33_tmul(T, g);
+      }
+      if (a.accum_R) g = m33_tmul(A, g);
+      dL0 = g;
+    } else {
+      dL0 = cov6_backward_to_factor(d6, L0);
+    }
+    float ds[3], dq[4];
+    frame_backward(f, dL0, a.mod, ds, dq);
+    d_scaling_raw[3 * i] = ds[0];
+    d_scaling_raw[3 * i + 1] = ds[1];
+    d_scaling_raw[3 * i + 2] = ds[2];
+    reinterpret_cast<float4*>(d_rotation_raw)[i] = make_float4(dq[0], dq[1], dq[2], dq[3]);
+  }
+
+  if (d_train_R != nullptr && a.train_R != nullptr) {   // block-reduce the 3x3 pose gradient
+    const unsigned lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+#pragma unroll
+    for (int k = 0; k < 9; ++k) {
+      float v = dT[k];
+#pragma unroll
+      for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+      if (lane == 0) s_dT[warp][k] = v;
+    }
+    __syncthreads();
+    if (threadIdx.x < 9) {
+      float v = 0.f;
+#pragma unroll
+      for (int w = 0; w < MODEL_THREADS / 32; ++w) v += s_dT[w][threadIdx.x];
+      if (v != 0.f) atomicAdd(d_train_R + threadIdx.x, v);
+    }
+  }
+}
+
+// get_features: cat(_features_dc [P,1,3], _features_rest [P,M-1,3]) along dim 1, and its backward
+// (the split). One CTA moves FEAT_ROWS whole rows; both sides are contiguous runs, so the scalar
+// accesses coalesce.
+constexpr int FEAT_ROWS = 64;
+
+template <bool SPLIT>
+__global__ void __launch_bounds__(MODEL_THREADS)
+features_kernel(int P, int M, float* __restrict__ dc, float* __restrict__ rest, float* __restrict__ full) {
+  const int row0 = blockIdx.x * FEAT_ROWS;
+  const int rows = min(FEAT_ROWS, P - row0);
+  const int width = 3 * M, wrest = width - 3;
+  float* f = full + (size_t)row0 * width;
+  float* d = dc + (size_t)row0 * 3;
+  float* r = rest + (size_t)row0 * wrest;
+  for (int t = threadIdx.x; t < rows * width; t += MODEL_THREADS) {
+    const int gi = t / width, k = t - gi * width;
+    float* part = k < 3 ? d + gi * 3 + k : r + gi * wrest + (k - 3);
+    if (SPLIT) *part = f[t];
+    else f[t] = *part;
+  }
+}
+
+static int check_model(const EgsModelArgs* m, const char* who) {
+  if (m == nullptr || m->P < 0) {
+    set_error("%s: NULL args or negative P", who);
+    return EGS_ERR_INVALID_ARGUMENT;
+  }
+  if (m->row0_copies < 0) {
+    set_error("%s: row0_copies must be >= 0", who);
+    return EGS_ERR_INVALID_ARGUMENT;
+  }
+  return EGS_OK;
+}
+
+static ModelKernelArgs kernel_args(const EgsModelArgs* m) {
+  ModelKernelArgs k;
+  k.P = m->P;
+  k.scaling_raw = m->scaling_raw;
+  k.rotation_raw = m->rotation_raw;
+  k.opacity_raw = m->opacity_raw;
+  k.mod = m->scale_modifier;
+  k.is_object = m->is_object;
+  k.which = m->which_object;
+  k.accum_R = m->accum_R;
+  k.train_R = m->train_R;
+  k.row0_copies = (m->accum_R || m->train_R) ? m->row0_copies : 0;
+  return k;
+}
+
+static bool aligned_to(const void* p, uintptr_t a) { return (reinterpret_cast<uintptr_t>(p) & (a - 1)) == 0; }
+
+}  // namespace egs
+
+extern "C" int egs_model_forward(const EgsModelArgs* m, float* cov3D, float* opacity, float* shs, void* stream) {
+  using namespace egs;
+  if (int rc = check_model(m, "egs_model_forward")) return rc;
+  const int P = m->P, M = m->sh_coeffs;
+  if (P == 0) return EGS_OK;
+  if ((cov3D && (!m->scaling_raw || !m->rotation_raw)) || (opacity && !m->opacity_raw) ||
+      (shs && (M < 1 || !m->features_dc || (M > 1 && !m->features_rest)))) {
+    set_error("egs_model_forward: a requested output lacks its raw input (or sh_coeffs < 1)");
+    return EGS_ERR_INVALID_ARGUMENT;
+  }
+  if (cov3D && (!aligned_to(m->rotation_raw, 16) || !aligned_to(cov3D, 8))) {
+    set_error("egs_model_forward: rotation_raw must be 16-byte and cov3D 8-byte aligned");
+    return EGS_ERR_INVALID_ARGUMENT;
+  }
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  StageTimer timer(st, ST_MODEL_FWD);
+  if (cov3D || opacity) {
+    model_forward_kernel<<<(P + MODEL_THREADS - 1) / MODEL_THREADS, MODEL_THREADS, 0, st>>>(
+        kernel_args(m), cov3D, opacity);
+    EGS_AFTER_LAUNCH(st, false);
+  }
+  if (shs) {
+    features_kernel<false><<<(P + FEAT_ROWS - 1) / FEAT_ROWS, MODEL_THREADS, 0, st>>>(
+        P, M, const_cast<float*>(m->features_dc), const_cast<float*>(m->features_rest), shs);
+    EGS_AFTER_LAUNCH(st, false);
+  }
+  return EGS_OK;
+}
+
+extern "C" int egs_model_backward(const EgsModelArgs* m, const float* dL_dcov3D, const float* dL_dopacity,
+                                  const float* dL_dshs, float* d_scaling_raw, float* d_rotation_raw,
+                                  float* d_opacity_raw, float* d_features_dc, float* d_features_rest,
+                                  float* d_train_R, void* stream) {
+  using namespace egs;
+  if (int rc = check_model(m, "egs_model_backward")) return rc;
+  const int P = m->P, M = m->sh_coeffs;
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  if (d_train_R) EGS_CUDA_TRY(cudaMemsetAsync(d_train_R, 0, 9 * sizeof(float), st));
+  if (P == 0) return EGS_OK;
+  if ((dL_dcov3D && (!m->scaling_raw || !m->rotation_raw || !d_scaling_raw || !d_rotation_raw)) ||
+      (dL_dopacity && (!m->opacity_raw || !d_opacity_raw)) ||
+      (dL_dshs && (M < 1 || !d_features_dc || (M > 1 && !d_features_rest)))) {
+    set_error("egs_model_backward: an upstream gradient lacks its raw input or its output");
+    return EGS_ERR_INVALID_ARGUMENT;
+  }
+  if (dL_dcov3D && (!aligned_to(m->rotation_raw, 16) || !aligned_to(d_rotation_raw, 16) || !aligned_to(dL_dcov3D, 8))) {
+    set_error("egs_model_backward: rotation tensors must be 16-byte and dL_dcov3D 8-byte aligned");
+    return EGS_ERR_INVALID_ARGUMENT;
+  }
+  StageTimer timer(st, ST_MODEL_BWD);
+  if (dL_dcov3D || dL_dopacity) {
+    model_backward_kernel<<<(P + MODEL_THREADS - 1) / MODEL_THREADS, MODEL_THREADS, 0, st>>>(
+        kernel_args(m), dL_dcov3D, dL_dopacity, d_scaling_raw, d_rotation_raw,
+        dL_dopacity ? d_opacity_raw : nullptr, dL_dcov3D ? d_train_R : nullptr);
+    EGS_AFTER_LAUNCH(st, false);
+  }
+  if (dL_dshs) {
+    features_kernel<true><<<(P + FEAT_ROWS - 1) / FEAT_ROWS, MODEL_THREADS, 0, st>>>(
+        P, M, d_features_dc, d_features_rest, const_cast<float*>(dL_dshs));
+    EGS_AFTER_LAUNCH(st, false);
+  }
+  return EGS_OK;
+}

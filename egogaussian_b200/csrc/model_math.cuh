@@ -1,0 +1,181 @@
+// model_math.cuh -- per-Gaussian arithmetic of the GaussianModel activations that sit between the
+// optimiser's raw parameters and the rasterizer inputs:
+//
+//   get_scaling  = exp(_scaling)                                scene/gaussian_model.py:126-128
+//   get_opacity  = sigmoid(_opacity)                            scene/gaussian_model.py:151-153
+//   build_rotation(_rotation): q = r / |r|, R(q)                utils/general_utils.py:124-146
+//   build_scaling_rotation: L = R diag(mod * s)                 utils/general_utils.py:148-158
+//   build_covariance_from_scaling_rotation[_w_rot]:
+//        L' = [train_R] accum_R L on the selected rows, Sigma = L' L'^T, 6 upper entries
+//                                                               scene/gaussian_model.py:29-63
+//
+// Shared by the standalone activation kernels (model.cu) and the raw-parameter mode of the
+// preprocess kernels, so both produce bit-identical covariances.
+//
+// The reference evaluates these with separate torch kernels, i.e. every product and sum is rounded
+// on its own. The quaternion -> R part is written with explicit round-to-nearest intrinsics so
+// that nvcc does not contract it into FMAs and R, L match torch bit for bit; the 3-term dot
+// products behind `@` (cuBLAS bmm, summation order unspecified) are plain FMA chains and are
+// tolerance-checked (tests/test_model_gpu.py).
+#pragma once
+#include <cuda_runtime.h>
+
+namespace egs {
+
+struct M33 {
+  float m[3][3];   // row-major m[row][col], like the torch tensors it stands for
+};
+
+__device__ __forceinline__ M33 m33_load(const float* __restrict__ p) {
+  M33 r;
+#pragma unroll
+  for (int i = 0; i < 3; ++i)
+#pragma unroll
+    for (int j = 0; j < 3; ++j) r.m[i][j] = p[3 * i + j];
+  return r;
+}
+
+// C = A B
+__device__ __forceinline__ M33 m33_mul(const M33& A, const M33& B) {
+  M33 C;
+#pragma unroll
+  for (int i = 0; i < 3; ++i)
+#pragma unroll
+    for (int j = 0; j < 3; ++j)
+      C.m[i][j] = fmaf(A.m[i][2], B.m[2][j], fmaf(A.m[i][1], B.m[1][j], A.m[i][0] * B.m[0][j]));
+  return C;
+}
+
+// C = A^T B
+__device__ __forceinline__ M33 m33_tmul(const M33& A, const M33& B) {
+  M33 C;
+#pragma unroll
+  for (int i = 0; i < 3; ++i)
+#pragma unroll
+    for (int j = 0; j < 3; ++j)
+      C.m[i][j] = fmaf(A.m[2][i], B.m[2][j], fmaf(A.m[1][i], B.m[1][j], A.m[0][i] * B.m[0][j]));
+  return C;
+}
+
+// C = A B^T
+__device__ __forceinline__ M33 m33_mult(const M33& A, const M33& B) {
+  M33 C;
+#pragma unroll
+  for (int i = 0; i < 3; ++i)
+#pragma unroll
+    for (int j = 0; j < 3; ++j)
+      C.m[i][j] = fmaf(A.m[i][2], B.m[j][2], fmaf(A.m[i][1], B.m[j][1], A.m[i][0] * B.m[j][0]));
+  return C;
+}
+
+// What the forward of one Gaussian leaves behind for its backward.
+struct RawFrame {
+  float s[3];      // exp(_scaling)
+  float sm[3];     // scale_modifier * s
+  float q[4];      // normalised quaternion (r, x, y, z)
+  float norm;      // |raw quaternion|
+  M33 R;           // rotation of the normalised quaternion
+};
+
+// general_utils.py:124-146, one rounding per torch op.
+__device__ __forceinline__ void raw_frame(const float s_raw[3], const float4 q_raw, float mod, RawFrame& f) {
+#pragma unroll
+  for (int j = 0; j < 3; ++j) {
+    f.s[j] = expf(s_raw[j]);
+    f.sm[j] = __fmul_rn(mod, f.s[j]);
+  }
+  float n2 = __fadd_rn(__fmul_rn(q_raw.x, q_raw.x), __fmul_rn(q_raw.y, q_raw.y));
+  n2 = __fadd_rn(n2, __fmul_rn(q_raw.z, q_raw.z));
+  n2 = __fadd_rn(n2, __fmul_rn(q_raw.w, q_raw.w));
+  f.norm = __fsqrt_rn(n2);
+  const float r = __fdiv_rn(q_raw.x, f.norm), x = __fdiv_rn(q_raw.y, f.norm);
+  const float y = __fdiv_rn(q_raw.z, f.norm), z = __fdiv_rn(q_raw.w, f.norm);
+  f.q[0] = r; f.q[1] = x; f.q[2] = y; f.q[3] = z;
+  const float xx = __fmul_rn(x, x), yy = __fmul_rn(y, y), zz = __fmul_rn(z, z);
+  const float xy = __fmul_rn(x, y), xz = __fmul_rn(x, z), yz = __fmul_rn(y, z);
+  const float rx = __fmul_rn(r, x), ry = __fmul_rn(r, y), rz = __fmul_rn(r, z);
+  f.R.m[0][0] = __fsub_rn(1.f, __fmul_rn(2.f, __fadd_rn(yy, zz)));
+  f.R.m[0][1] = __fmul_rn(2.f, __fsub_rn(xy, rz));
+  f.R.m[0][2] = __fmul_rn(2.f, __fadd_rn(xz, ry));
+  f.R.m[1][0] = __fmul_rn(2.f, __fadd_rn(xy, rz));
+  f.R.m[1][1] = __fsub_rn(1.f, __fmul_rn(2.f, __fadd_rn(xx, zz)));
+  f.R.m[1][2] = __fmul_rn(2.f, __fsub_rn(yz, rx));
+  f.R.m[2][0] = __fmul_rn(2.f, __fsub_rn(xz, ry));
+  f.R.m[2][1] = __fmul_rn(2.f, __fadd_rn(yz, rx));
+  f.R.m[2][2] = __fsub_rn(1.f, __fmul_rn(2.f, __fadd_rn(xx, yy)));
+}
+
+// L = R diag(sm): the bmm against a diagonal matrix adds exact zeros, so one product per entry.
+__device__ __forceinline__ M33 frame_factor(const RawFrame& f) {
+  M33 L;
+#pragma unroll
+  for (int i = 0; i < 3; ++i)
+#pragma unroll
+    for (int j = 0; j < 3; ++j) L.m[i][j] = __fmul_rn(f.R.m[i][j], f.sm[j]);
+  return L;
+}
+
+// strip_symmetric(L L^T): [xx, xy, xz, yy, yz, zz]   (general_utils.py:110-122)
+__device__ __forceinline__ void factor_to_cov6(const M33& L, float c[6]) {
+  auto dot = [&](int a, int b) {
+    return fmaf(L.m[a][2], L.m[b][2], fmaf(L.m[a][1], L.m[b][1], L.m[a][0] * L.m[b][0]));
+  };
+  c[0] = dot(0, 0); c[1] = dot(0, 1); c[2] = dot(0, 2);
+  c[3] = dot(1, 1); c[4] = dot(1, 2); c[5] = dot(2, 2);
+}
+
+// The selected rows' factor goes through accum_R and then, during pose training, through
+// ObjectMove.rot_L (geometry_utils.py:26-28): L' = train_R (accum_R L).
+__device__ __forceinline__ M33 rotate_factor(const M33& L0, const M33* accum_R, const M33* train_R, M33* mid) {
+  M33 L = L0;
+  if (accum_R) L = m33_mul(*accum_R, L);
+  if (mid) *mid = L;
+  if (train_R) L = m33_mul(*train_R, L);
+  return L;
+}
+
+// Gradient of the six stored covariance entries w.r.t. the final factor: only the upper triangle of
+// Sigma is read, so dSigma is upper-triangular and dL = (dSigma + dSigma^T) L.
+__device__ __forceinline__ M33 cov6_backward_to_factor(const float d[6], const M33& L) {
+  M33 G;
+  G.m[0][0] = 2.f * d[0]; G.m[0][1] = d[1];       G.m[0][2] = d[2];
+  G.m[1][0] = d[1];       G.m[1][1] = 2.f * d[3]; G.m[1][2] = d[4];
+  G.m[2][0] = d[2];       G.m[2][1] = d[4];       G.m[2][2] = 2.f * d[5];
+  return m33_mul(G, L);
+}
+
+// dL0 (gradient of L = R diag(sm)) -> raw scaling and raw quaternion gradients.
+__device__ __forceinline__ void frame_backward(const RawFrame& f, const M33& dL0, float mod,
+                                               float ds_raw[3], float dq_raw[4]) {
+  M33 dR;
+#pragma unroll
+  for (int j = 0; j < 3; ++j) {
+    float dsm = 0.f;
+#pragma unroll
+    for (int i = 0; i < 3; ++i) {
+      dsm = fmaf(dL0.m[i][j], f.R.m[i][j], dsm);
+      dR.m[i][j] = dL0.m[i][j] * f.sm[j];
+    }
+    ds_raw[j] = dsm * mod * f.s[j];   // through mod * exp(raw)
+  }
+  const float r = f.q[0], x = f.q[1], y = f.q[2], z = f.q[3];
+  float dq[4];
+  dq[0] = 2.f * (-z * dR.m[0][1] + y * dR.m[0][2] + z * dR.m[1][0] - x * dR.m[1][2] - y * dR.m[2][0] + x * dR.m[2][1]);
+  dq[1] = 2.f * (y * dR.m[0][1] + z * dR.m[0][2] + y * dR.m[1][0] - 2.f * x * dR.m[1][1] - r * dR.m[1][2] +
+                 z * dR.m[2][0] + r * dR.m[2][1] - 2.f * x * dR.m[2][2]);
+  dq[2] = 2.f * (-2.f * y * dR.m[0][0] + x * dR.m[0][1] + r * dR.m[0][2] + x * dR.m[1][0] + z * dR.m[1][2] -
+                 r * dR.m[2][0] + z * dR.m[2][1] - 2.f * y * dR.m[2][2]);
+  dq[3] = 2.f * (-2.f * z * dR.m[0][0] - r * dR.m[0][1] + x * dR.m[0][2] + r * dR.m[1][0] - 2.f * z * dR.m[1][1] +
+                 y * dR.m[1][2] + x * dR.m[2][0] + y * dR.m[2][1]);
+  // q = raw / |raw|
+  const float qdq = f.q[0] * dq[0] + f.q[1] * dq[1] + f.q[2] * dq[2] + f.q[3] * dq[3];
+  const float inv = 1.f / f.norm;
+#pragma unroll
+  for (int k = 0; k < 4; ++k) dq_raw[k] = (dq[k] - f.q[k] * qdq) * inv;
+}
+
+// torch.sigmoid and its autograd formula grad * (1 - y) * y
+__device__ __forceinline__ float sigmoid_fwd(float x) { return 1.f / (1.f + expf(-x)); }
+__device__ __forceinline__ float sigmoid_bwd(float y, float g) { return g * (1.f - y) * y; }
+
+}  // namespace egs

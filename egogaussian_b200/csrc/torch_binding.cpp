@@ -320,9 +320,106 @@ void adam_se3_step(torch::Tensor xyz, const torch::Tensor& grad, torch::Tensor e
         "egs_adam_se3_step");
 }
 
+// ---- GaussianModel activations (egs_model_forward / egs_model_backward) --------------------------
+// Tensors that are absent are passed as empty tensors, like the rasterizer's optional inputs.
+struct ModelHold {
+  torch::Tensor s, q, o, dc, rest, obj, A, T;
+  EgsModelArgs args{};
+};
+
+void fill_model(ModelHold& h, const torch::Device& dev, const torch::Tensor& scaling_raw,
+                const torch::Tensor& rotation_raw, const torch::Tensor& opacity_raw,
+                const torch::Tensor& features_dc, const torch::Tensor& features_rest, double scale_modifier,
+                const torch::Tensor& is_object, int64_t which_object, const torch::Tensor& accum_R,
+                const torch::Tensor& train_R, int64_t row0_copies, int64_t P) {
+  EgsModelArgs& m = h.args;
+  m.P = (int)P;
+  m.scaling_raw = opt_ptr(scaling_raw, h.s, dev, "scaling_raw");
+  m.rotation_raw = opt_ptr(rotation_raw, h.q, dev, "rotation_raw");
+  m.opacity_raw = opt_ptr(opacity_raw, h.o, dev, "opacity_raw");
+  m.features_dc = opt_ptr(features_dc, h.dc, dev, "features_dc");
+  m.features_rest = opt_ptr(features_rest, h.rest, dev, "features_rest");
+  m.sh_coeffs = m.features_dc ? 1 + (features_rest.numel() ? (int)features_rest.size(1) : 0) : 0;
+  m.scale_modifier = (float)scale_modifier;
+  m.is_object = nullptr;
+  if (is_object.defined() && is_object.numel() != 0) {
+    TORCH_CHECK(is_object.device() == dev && is_object.scalar_type() == torch::kInt32 && is_object.numel() == P,
+                "is_object must be int32 [P] or [P,1] on ", dev);
+    h.obj = is_object.contiguous();
+    m.is_object = h.obj.data_ptr<int>();
+  }
+  m.which_object = (int)which_object;
+  m.accum_R = opt_ptr(accum_R, h.A, dev, "accum_R");
+  m.train_R = opt_ptr(train_R, h.T, dev, "train_R");
+  TORCH_CHECK((!m.accum_R || accum_R.numel() == 9) && (!m.train_R || train_R.numel() == 9), "rotations must be 3x3");
+  m.row0_copies = (int)row0_copies;
+}
+
+std::tuple<torch::Tensor, torch::Tensor, torch::Tensor> model_forward(
+    const torch::Tensor& scaling_raw, const torch::Tensor& rotation_raw, const torch::Tensor& opacity_raw,
+    const torch::Tensor& features_dc, const torch::Tensor& features_rest, double scale_modifier,
+    const torch::Tensor& is_object, int64_t which_object, const torch::Tensor& accum_R,
+    const torch::Tensor& train_R, int64_t row0_copies) {
+  const torch::Tensor& first = scaling_raw.numel() ? scaling_raw : (opacity_raw.numel() ? opacity_raw : features_dc);
+  TORCH_CHECK(first.defined() && first.is_cuda(), "model_forward: parameters must be CUDA tensors");
+  const torch::Device dev = first.device();
+  c10::cuda::CUDAGuard guard(dev);
+  const int64_t P = first.size(0);
+  ModelHold h;
+  fill_model(h, dev, scaling_raw, rotation_raw, opacity_raw, features_dc, features_rest, scale_modifier, is_object,
+             which_object, accum_R, train_R, row0_copies, P);
+  auto opt = torch::TensorOptions().dtype(torch::kFloat32).device(dev);
+  torch::Tensor cov = h.args.scaling_raw ? torch::empty({P, 6}, opt) : torch::empty({0}, opt);
+  torch::Tensor opacity = h.args.opacity_raw ? torch::empty({P, 1}, opt) : torch::empty({0}, opt);
+  torch::Tensor shs = h.args.features_dc ? torch::empty({P, (int64_t)h.args.sh_coeffs, 3}, opt) : torch::empty({0}, opt);
+  check(egs_model_forward(&h.args, cov.numel() ? cov.data_ptr<float>() : nullptr,
+                          opacity.numel() ? opacity.data_ptr<float>() : nullptr,
+                          shs.numel() ? shs.data_ptr<float>() : nullptr,
+                          at::cuda::getCurrentCUDAStream().stream()),
+        "egs_model_forward");
+  return std::make_tuple(cov, opacity, shs);
+}
+
+// returns (d_scaling_raw, d_rotation_raw, d_opacity_raw, d_features_dc, d_features_rest, d_train_R);
+// entries whose upstream gradient is absent come back as empty tensors
+std::vector<torch::Tensor> model_backward(
+    const torch::Tensor& scaling_raw, const torch::Tensor& rotation_raw, const torch::Tensor& opacity_raw,
+    int64_t sh_coeffs, double scale_modifier, const torch::Tensor& is_object, int64_t which_object,
+    const torch::Tensor& accum_R, const torch::Tensor& train_R, int64_t row0_copies,
+    const torch::Tensor& dL_dcov3D, const torch::Tensor& dL_dopacity, const torch::Tensor& dL_dshs) {
+  const torch::Tensor& first = dL_dcov3D.numel() ? dL_dcov3D : (dL_dopacity.numel() ? dL_dopacity : dL_dshs);
+  TORCH_CHECK(first.defined() && first.is_cuda(), "model_backward: gradients must be CUDA tensors");
+  const torch::Device dev = first.device();
+  c10::cuda::CUDAGuard guard(dev);
+  const int64_t P = first.size(0);
+  ModelHold h;
+  fill_model(h, dev, scaling_raw, rotation_raw, opacity_raw, torch::Tensor(), torch::Tensor(), scale_modifier,
+             is_object, which_object, accum_R, train_R, row0_copies, P);
+  h.args.sh_coeffs = (int)sh_coeffs;
+  torch::Tensor kc, ko, ks;
+  const float* gc = opt_ptr(dL_dcov3D, kc, dev, "dL_dcov3D");
+  const float* go = opt_ptr(dL_dopacity, ko, dev, "dL_dopacity");
+  const float* gs = opt_ptr(dL_dshs, ks, dev, "dL_dshs");
+  auto opt = torch::TensorOptions().dtype(torch::kFloat32).device(dev);
+  auto none = [&]() { return torch::empty({0}, opt); };
+  torch::Tensor ds = gc ? torch::empty({P, 3}, opt) : none();
+  torch::Tensor dq = gc ? torch::empty({P, 4}, opt) : none();
+  torch::Tensor dT = (gc && h.args.train_R) ? torch::empty({3, 3}, opt) : none();
+  torch::Tensor dop = go ? torch::empty({P, 1}, opt) : none();
+  torch::Tensor ddc = gs ? torch::empty({P, 1, 3}, opt) : none();
+  torch::Tensor drest = gs ? torch::empty({P, sh_coeffs - 1, 3}, opt) : none();
+  auto p = [](torch::Tensor& t) { return t.numel() ? t.data_ptr<float>() : nullptr; };
+  check(egs_model_backward(&h.args, gc, go, gs, p(ds), p(dq), p(dop), p(ddc), p(drest), p(dT),
+                           at::cuda::getCurrentCUDAStream().stream()),
+        "egs_model_backward");
+  return {ds, dq, dop, ddc, drest, dT};
+}
+
 }  // namespace
 
 PYBIND11_MODULE(TORCH_EXTENSION_NAME, m) {
+  m.def("model_forward", &model_forward);
+  m.def("model_backward", &model_backward);
   m.def("rasterize_gaussians", &rasterize_gaussians);
   m.def("rasterize_gaussians_backward", &rasterize_gaussians_backward);
   m.def("mark_visible", &mark_visible);

@@ -12,6 +12,10 @@
  *   egs_adam_step      <- torch.optim.Adam.step as configured in scene/gaussian_model.py:180-202
  *   egs_se3_apply      <- GaussianModel.apply_trans_rot_new        scene/gaussian_model.py:939-986
  *   egs_adam_se3_step  <- reverse_trans_rot_new + Adam.step        scene/gaussian_model.py:1037-1060
+ *   egs_model_forward / egs_model_backward
+ *                      <- get_scaling/get_opacity/get_features     scene/gaussian_model.py:126-153
+ *                         get_covariance/get_rotated_covariance    scene/gaussian_model.py:29-63,167-171
+ *                         build_rotation/build_scaling_rotation    utils/general_utils.py:110-158
  *
  * Conventions
  *   - plain C, no torch types, no exceptions; every pointer named `d_*` or documented as
@@ -217,6 +221,56 @@ int egs_se3_apply(int P, const float* xyz, const int* is_object, int which_objec
 int egs_adam_se3_step(int P, float* xyz, const float* grad_moved, float* exp_avg, float* exp_avg_sq,
                       const int* is_object, int which_object, const float* Rt, double lr, int step,
                       double beta1, double beta2, double eps, void* stream);
+
+/* ---- GaussianModel activations --------------------- */
+
+/* The optimiser's raw parameters and what render() derives from them every iteration
+ * (gaussian_renderer/__init__.py:57-86 with compute_cov3D_python forced on, train.py:49):
+ *   opacity = sigmoid(opacity_raw)                       get_opacity
+ *   shs     = cat(features_dc, features_rest) on dim 1   get_features
+ *   cov3D   = strip_symmetric(L' L'^T), L = R(q/|q|) diag(scale_modifier * exp(scaling_raw)),
+ *             L' = train_R * (accum_R * L) on the selected rows, L' = L elsewhere
+ *                                                        get_covariance / get_rotated_covariance
+ * Selected rows: accum_R == NULL and train_R == NULL -> none (plain get_covariance);
+ * otherwise is_object == NULL -> all (which_object=None), else rows with is_object[i] ==
+ * which_object. accum_R NULL with train_R set means accum_R = identity (gaussian_model.py:55).
+ *
+ * row0_copies reproduces an indexing quirk of gaussian_model.py:49-59: the mask is a [P,1] tensor,
+ * so nonzero(mask).squeeze() is a list of (row, 0) pairs, and indexing L with it reads and
+ * overwrites row 0 once per selected row too. Whenever at least one row is selected, row 0 is
+ * rotated as well, and in backward it receives its gradient once per index entry naming it.
+ * Pass row0_copies = n_selected + (row 0 selected ? 1 : 0) when n_selected > 0, else 0; pass 0
+ * always to get the "intended" per-row behaviour instead. */
+typedef struct EgsModelArgs {
+  int P;
+  int sh_coeffs;               /* M of the concatenated feature tensor (1 + rest) */
+  const float* scaling_raw;    /* device [P,3]   GaussianModel._scaling (log scale) */
+  const float* rotation_raw;   /* device [P,4]   _rotation, un-normalised (w,x,y,z); 16-B aligned */
+  const float* opacity_raw;    /* device [P,1]   _opacity logits */
+  const float* features_dc;    /* device [P,1,3] */
+  const float* features_rest;  /* device [P,M-1,3] (NULL when M == 1) */
+  float scale_modifier;
+  const int* is_object;        /* device [P] int32 (the reference's [P,1] tensor) or NULL */
+  int which_object;
+  const float* accum_R;        /* device [9] row-major 3x3, or NULL */
+  const float* train_R;        /* device [9] row-major rot6d_to_matrix(obj_rotation_6d)
+                                  (during_training, geometry_utils.py:26-28), or NULL */
+  int row0_copies;
+} EgsModelArgs;
+
+/* Each output is optional (NULL = not wanted): cov3D [P,6], opacity [P,1], shs [P,M,3]. Only the
+ * raw inputs an output needs have to be set. One launch for cov3D+opacity, one for shs. */
+int egs_model_forward(const EgsModelArgs* model, float* cov3D, float* opacity, float* shs, void* stream);
+
+/* Backward of the above. Each upstream gradient is optional and selects its outputs:
+ * dL_dcov3D -> d_scaling_raw [P,3], d_rotation_raw [P,4] (and d_train_R, device [9], overwritten
+ * with dL/d train_R when both it and model->train_R are set); dL_dopacity -> d_opacity_raw [P,1];
+ * dL_dshs [P,M,3] -> d_features_dc [P,1,3], d_features_rest [P,M-1,3]. Every element of a
+ * selected output is written. */
+int egs_model_backward(const EgsModelArgs* model, const float* dL_dcov3D, const float* dL_dopacity,
+                       const float* dL_dshs, float* d_scaling_raw, float* d_rotation_raw,
+                       float* d_opacity_raw, float* d_features_dc, float* d_features_rest,
+                       float* d_train_R, void* stream);
 
 /* ---- introspection (tests / bench) ----------------------------------------------------- */
 

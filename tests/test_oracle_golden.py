@@ -70,3 +70,50 @@ def test_oracle_backward_from_own_forward_stays_close():
     for k in ("means2D", "means3D", "opacity"):
         b = gold["g_" + k].astype(np.float64)
         assert np.abs(g[k].reshape(b.shape) - b).max() <= 1e-2 * np.abs(b).max()
+
+
+# ---- activation / covariance glue (oracle/model_ref.py) against the reference's own Python ----------
+from golden.make_model_golden import MODEL_CASES, model_inputs  # noqa: E402
+
+
+def run_model_restatement(case, device="cpu"):
+    """oracle/model_ref.py on the seeded inputs of `case`: outputs and autograd gradients."""
+    import torch
+    from oracle import model_ref as mr
+    x = {k: v.to(device) for k, v in model_inputs(case).items()}
+    leaves = {k: x[k].clone().requires_grad_(True)
+              for k in ("scaling_raw", "rotation_raw", "opacity_raw", "features_dc", "features_rest")}
+    rot6d = x["rot6d"].clone().requires_grad_(True)
+    if case["rot_cov"]:
+        cov = mr.rotated_covariance(leaves["scaling_raw"], leaves["rotation_raw"], case["mod"], x["is_object"],
+                                    case["which"], x["accum_R"] if case["accum"] else None,
+                                    mr.rot6d_to_matrix(rot6d) if case["train"] else None)
+    else:
+        cov = mr.covariance(leaves["scaling_raw"], leaves["rotation_raw"], case["mod"])
+    _, opacity, shs = mr.activations(leaves["scaling_raw"], leaves["opacity_raw"], leaves["features_dc"],
+                                     leaves["features_rest"])
+    ((cov * x["g_cov"]).sum() + (opacity * x["g_opacity"]).sum() + (shs * x["g_shs"]).sum()).backward()
+    out = {"cov3D": cov, "opacity": opacity, "shs": shs}
+    out.update({"d_" + k: v.grad for k, v in leaves.items()})
+    out["d_rot6d"] = rot6d.grad if rot6d.grad is not None else torch.zeros(3, 2)
+    return {k: v.detach().cpu().numpy() for k, v in out.items()}
+
+
+def assert_model_close(got, gold, what, value_rtol=1e-6, grad_rtol=1e-4):
+    """Values within `value_rtol`, gradients within `grad_rtol`, both relative to the tensor maximum
+    (the path's stated gradient tolerance; fp32 sums in another order)."""
+    for k in gold.files:
+        a, b = got[k].astype(np.float64), gold[k].astype(np.float64)
+        assert a.shape == b.shape, (what, k)
+        if a.size == 0:   # features_rest at M == 1
+            continue
+        tol =grad_rtol if k.startswith("d_") else value_rtol
+        assert np.abs(a - b).max() <= tol * max(np.abs(b).max(), 1e-30), (what, k, np.abs(a - b).max())
+
+
+@pytest.mark.parametrize("case", MODEL_CASES, ids=[c["name"] for c in MODEL_CASES])
+def test_model_restatement_matches_reference(case):
+    gold = np.load(GOLDEN / f"{case['name']}.npz")
+    assert_model_close(run_model_restatement(case), gold, case["name"])
+    if case["name"] == "model_object_train":   # the row-0 gradient multiplicity is really there
+        assert np.abs(gold["d_scaling_raw"][0]).max() > 5 * np.abs(gold["d_scaling_raw"][1:]).max()
