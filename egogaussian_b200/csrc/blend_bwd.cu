@@ -364,7 +364,9 @@ blend_backward2_kernel(const uint2* __restrict__ ranges, const uint32_t* __restr
   // store (shared-memory float atomicAdd is a compare-and-swap loop on this architecture)
   __shared__ float s_acc[(BWD2_THREADS / 32) * BWD2_BATCH * ACC_PITCH];
   __shared__ uint32_t s_hit[BWD2_BATCH];   // bit w: warp w stored totals for this entry in this batch
-  __shared__ unsigned char s_reach[BWD2_BATCH];   // bit w: the entry can reach warp w's 8x8 pixels
+  // [pixel warp][32-entry chunk]: entries of the batch that can reach the warp's 8x8 pixels. A warp
+  // pops set bits in list order and never issues an instruction for the other entries.
+  __shared__ uint32_t s_bits[BWD2_THREADS / 32][BWD2_BATCH / 32];
   __shared__ uint32_t s_max_contrib;
 
   const unsigned tid = threadIdx.x;
@@ -400,10 +402,15 @@ blend_backward2_kernel(const uint2* __restrict__ ranges, const uint32_t* __restr
   const int my_slot = my_quantity >= 0 ? record_slot_of_quantity(my_quantity) : 0;
   const bool i_add = my_quantity >= 0 && (lane & 1) == 0;
 
+  // shared-window addresses formed once (see lds_f4 in common.cuh)
+  const uint32_t a_a = smem_addr(s_a), a_b = smem_addr(s_b), a_c = smem_addr(s_c);
+  const uint32_t a_bits = smem_addr(&s_bits[warp][0]);
+
   const int rounds = (walk + BWD2_BATCH - 1) / BWD2_BATCH;
   for (int r = 0; r < rounds; ++r) {
     __syncthreads();
     const int pos = walk - 1 - (r * BWD2_BATCH + (int)tid);
+    unsigned reach = 0u;
     if (pos >= 0) {
       const uint32_t id = point_list[range.x + pos];
       const float2 xy = means2D[id];
@@ -412,21 +419,36 @@ blend_backward2_kernel(const uint2* __restrict__ ranges, const uint32_t* __restr
       s_id[tid] = id;
       // alpha >= 1/255  <=>  power >= -log(255 o); o <= 0 can never contribute
       s_a[tid] = make_float4(xy.x, xy.y, co.w > 0.f ? -__logf(255.f * co.w) : 1.f, co.w);
-      s_reach[tid] = (unsigned char)footprint_mask<8, 8>(xy, co, (float)(blockIdx.x * TILE_X),
-                                                         (float)(blockIdx.y * TILE_Y));
+      reach = footprint_mask<8, 8>(xy, co, (float)(blockIdx.x * TILE_X), (float)(blockIdx.y * TILE_Y));
       s_b[tid] = make_float4(co.x, co.y, co.z, cd.w);
       s_c[tid] = cd;
     }
     s_hit[tid] = 0u;
+    {
+      uint32_t mine = 0u;   // lane w ends up with pixel warp w's word for this staging warp's chunk
+#pragma unroll
+      for (unsigned w = 0; w < BWD2_THREADS / 32; ++w) {
+        const uint32_t word = __ballot_sync(0xffffffffu, (reach >> w) & 1u);
+        if (lane == w) mine = word;
+      }
+      if (lane < BWD2_THREADS / 32) s_bits[lane][warp] = mine;
+    }
     __syncthreads();
 
     const int n = min(BWD2_BATCH, walk - r * BWD2_BATCH);
-    for (int j = 0; j < n; ++j) {
+    // entries j < jmin lie behind the last contributor of every pixel of this warp
+    const int jmin = walk - r * BWD2_BATCH - (int)warp_last;
+    for (int c = 0; c < BWD2_BATCH / 32; ++c) {
+     uint32_t bits = lds_u32(a_bits + 4u * c);
+     const int lo = jmin - 32 * c;
+     if (lo >= 32) continue;
+     if (lo > 0) bits &= 0xffffffffu << lo;
+     while (bits != 0u) {   // warp-uniform: every lane holds the same word
+      const int j = c * 32 + __ffs((int)bits) - 1;
+      bits &= bits - 1u;
       const uint32_t jpos = (uint32_t)(walk - 1 - (r * BWD2_BATCH + j));
-      if (jpos >= warp_last) continue;   // warp-uniform
-      if (!((s_reach[j] >> warp) & 1u)) continue;   // the entry cannot touch this warp's 8x8 block
-      const float4 a4 = s_a[j];
-      const float4 b4 = s_b[j];
+      const float4 a4 = lds_f4(a_a + 16u * j);
+      const float4 b4 = lds_f4(a_b + 16u * j);
       const float dx0 = a4.x - P0.px, dy0 = a4.y - P0.py;
       const float dx1 = a4.x - P1.px, dy1 = a4.y - P1.py;
       const float power0 = -0.5f * (b4.x * dx0 * dx0 + b4.z * dy0 * dy0) - b4.y * dx0 * dy0;
@@ -438,12 +460,13 @@ blend_backward2_kernel(const uint2* __restrict__ ranges, const uint32_t* __restr
       float q[10];
 #pragma unroll
       for (int k = 0; k < 10; ++k) q[k] = 0.f;
-      const float4 c4 = s_c[j];
+      const float4 c4 = lds_f4(a_c + 16u * j);
       if (act0) fragment_backward(P0, dx0, dy0, power0, a4, b4, c4, ddelx_dx, ddely_dy, q);
       if (act1) fragment_backward(P1, dx1, dy1, power1, a4, b4, c4, ddelx_dx, ddely_dy, q);
       const float total = warp_packed_reduce10(q, lane);
       if (i_add) s_acc[(warp * BWD2_BATCH + j) * ACC_PITCH + my_slot] = total;
       if (lane == 0) atomicOr(&s_hit[j], 1u << warp);
+     }
     }
     __syncthreads();
 

@@ -108,6 +108,113 @@ blend_forward_kernel(const uint2* __restrict__ ranges, const uint32_t* __restric
 }
 
 // ---------------------------------------------------------------------------------------------
+// v3 (default): the same blend, driven by per-warp bit lists instead of a per-entry mask test
+// ---------------------------------------------------------------------------------------------
+// The staging warps turn the footprint masks of their 32 entries into one 32-bit word per pixel
+// warp (eight ballots), so a pixel warp walks only the entries that can reach its 8x4 block: it
+// pops set bits in list order and never issues an instruction for the others (in the kernel above
+// a skipped entry still costs ~13 instructions, and more than half of all entries are skipped).
+// Shared memory is addressed through window addresses formed once (see lds_f4). The arithmetic of
+// a blended fragment is unchanged, so the images stay bit-identical.
+__global__ void __launch_bounds__(TILE_PIXELS)
+blend_forward3_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__ point_list,
+                      int W, int H, int grid_x, const float2* __restrict__ means2D,
+                      const float4* __restrict__ conic_opacity, const float4* __restrict__ rgb_depth,
+                      const float* __restrict__ bg_color, float* __restrict__ out_color,
+                      float* __restrict__ out_depth, float* __restrict__ out_alpha,
+                      uint32_t* __restrict__ n_contrib) {
+  __shared__ float2 s_xy[BLEND_BATCH];
+  __shared__ float4 s_co[BLEND_BATCH];
+  __shared__ float4 s_cd[BLEND_BATCH];
+  __shared__ uint32_t s_bits[8][BLEND_BATCH / 32];   // [pixel warp][32-entry chunk]
+
+  const unsigned tid = threadIdx.x;
+  const unsigned warp = tid >> 5, lane = tid & 31;
+  const unsigned lx = (warp & 1) * 8 + (lane & 7);
+  const unsigned ly = (warp >> 1) * 4 + (lane >> 3);
+  const unsigned px = blockIdx.x * TILE_X + lx;
+  const unsigned py = blockIdx.y * TILE_Y + ly;
+  const bool inside = px < (unsigned)W && py < (unsigned)H;
+  const uint32_t pix_id = (uint32_t)W * py + px;
+  const float2 pixf = make_float2((float)px, (float)py);
+
+  const uint2 range = ranges[blockIdx.y * grid_x + blockIdx.x];
+  const int total = (int)(range.y - range.x);
+  const int rounds = (total + BLEND_BATCH - 1) / BLEND_BATCH;
+
+  bool done = !inside;
+  float T = 1.0f;
+  uint32_t last_contributor = 0;
+  const float tile_x0 = (float)(blockIdx.x * TILE_X), tile_y0 = (float)(blockIdx.y * TILE_Y);
+  float C0 = 0.f, C1 = 0.f, C2 = 0.f, weight = 0.f, D = 0.f;
+  const uint32_t a_xy = smem_addr(s_xy), a_co = smem_addr(s_co), a_cd = smem_addr(s_cd);
+  const uint32_t a_bits = smem_addr(&s_bits[warp][0]);
+
+  for (int r = 0; r < rounds; ++r) {
+    if (__syncthreads_count(done) == TILE_PIXELS) break;
+    const int progress = r * BLEND_BATCH + (int)tid;
+    unsigned mask = 0u;
+    if (progress < total) {
+      const uint32_t id = point_list[range.x + progress];
+      const float2 xy = means2D[id];
+      const float4 co = conic_opacity[id];
+      s_xy[tid] = xy;
+      s_co[tid] = co;
+      s_cd[tid] = rgb_depth[id];
+      mask = footprint_mask<8, 4>(xy, co, tile_x0, tile_y0);
+    }
+    uint32_t mine = 0u;   // lane w ends up with the word of pixel warp w for this chunk
+#pragma unroll
+    for (unsigned w = 0; w < 8; ++w) {
+      const uint32_t word = __ballot_sync(0xffffffffu, (mask >> w) & 1u);
+      if (lane == w) mine = word;
+    }
+    if (lane < 8) s_bits[lane][warp] = mine;
+    __syncthreads();
+    if (__all_sync(0xffffffffu, done)) continue;  // warp-uniform: nothing left for these 32 pixels
+
+    const uint32_t first = (uint32_t)(r * BLEND_BATCH) + 1u;
+    for (uint32_t c = 0; c < BLEND_BATCH / 32 && !done; ++c) {
+      uint32_t bits = lds_u32(a_bits + 4u * c);
+      while (bits != 0u && !done) {
+        const uint32_t j = c * 32u + (uint32_t)__ffs((int)bits) - 1u;
+        bits &= bits - 1u;
+        const float2 xy = lds_f2(a_xy + 8u * j);
+        const float4 con_o = lds_f4(a_co + 16u * j);
+        const float2 d = make_float2(xy.x - pixf.x, xy.y - pixf.y);
+        const float power = -0.5f * (con_o.x * d.x * d.x + con_o.z * d.y * d.y) - con_o.y * d.x * d.y;
+        if (power > 0.0f) continue;
+        const float alpha = min(0.99f, con_o.w * expf(power));
+        if (alpha < 1.0f / 255.0f) continue;
+        const float test_T = T * (1 - alpha);
+        if (test_T < 0.0001f) {
+          done = true;
+          continue;
+        }
+        const float4 cd = lds_f4(a_cd + 16u * j);
+        C0 += cd.x * alpha * T;
+        C1 += cd.y * alpha * T;
+        C2 += cd.z * alpha * T;
+        weight += alpha * T;
+        D += cd.w * alpha * T;
+        T = test_T;
+        last_contributor = first + j;   // 1-based position in the tile's list
+      }
+    }
+  }
+
+  if (inside) {
+    const size_t plane = (size_t)H * W;
+    n_contrib[pix_id] = last_contributor;
+    out_color[pix_id] = C0 + T * bg_color[0];
+    out_color[plane + pix_id] = C1 + T * bg_color[1];
+    out_color[2 * plane + pix_id] = C2 + T * bg_color[2];
+    out_alpha[pix_id] = weight;
+    out_depth[pix_id] = D;
+  }
+}
+
+// ---------------------------------------------------------------------------------------------
 // v2: two pixels per thread + a conservative log-domain pre-filter
 // ---------------------------------------------------------------------------------------------
 // Bit-identical results to the kernel above (and so to the reference): every fragment that is
@@ -239,7 +346,11 @@ int launch_blend_forward(const EgsForwardArgs& a, const GeomPtrs& g, const uint3
   // bit-identical, and on B200 at 1M Gaussians v2 measured 5 % slower (0.364 vs 0.348 ms): the
   // forward loop is already at its instruction floor and v2 only adds divergence per warp.
   const char* sel = getenv("EGS_FWD");
-  if (!(sel && strcmp(sel, "v2") == 0)) {
+  if (!sel || strcmp(sel, "v3") == 0) {
+    blend_forward3_kernel<<<grid, TILE_PIXELS, 0, stream>>>(
+        im.ranges, point_list, a.width, a.height, (int)grid.x, g.means2D, g.conic_opacity,
+        g.rgb_depth, a.background, a.out_color, a.out_depth, a.out_alpha, im.n_contrib);
+  } else if (strcmp(sel, "v2") != 0) {
     blend_forward_kernel<<<grid, TILE_PIXELS, 0, stream>>>(
         im.ranges, point_list, a.width, a.height, (int)grid.x, g.means2D, g.conic_opacity,
         g.rgb_depth, a.background, a.out_color, a.out_depth, a.out_alpha, im.n_contrib);

@@ -389,6 +389,29 @@ __device__ __forceinline__ unsigned footprint_mask(const float2 xy, const float4
   return mask;
 }
 
+// Shared-memory loads through a 32-bit shared-window address that is formed once outside the hot
+// loop. Indexing a __shared__ array inside the tile loops makes nvcc re-derive the window base
+// (S2R SR_CgaCtaId + LEA, ~4 instructions per access on sm_100) on every iteration.
+__device__ __forceinline__ uint32_t smem_addr(const void* p) {
+  return (uint32_t)__cvta_generic_to_shared(p);
+}
+__device__ __forceinline__ float2 lds_f2(uint32_t addr) {
+  float2 v;
+  asm volatile("ld.shared.v2.f32 {%0, %1}, [%2];" : "=f"(v.x), "=f"(v.y) : "r"(addr) : "memory");
+  return v;
+}
+__device__ __forceinline__ float4 lds_f4(uint32_t addr) {
+  float4 v;
+  asm volatile("ld.shared.v4.f32 {%0, %1, %2, %3}, [%4];"
+               : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "r"(addr) : "memory");
+  return v;
+}
+__device__ __forceinline__ uint32_t lds_u32(uint32_t addr) {
+  uint32_t v;
+  asm volatile("ld.shared.u32 %0, [%1];" : "=r"(v) : "r"(addr) : "memory");
+  return v;
+}
+
 // Lanes of the warp that are valid and hold the same BITS-bit digit as this lane. One ballot per
 // digit bit (fixed cost, independent ballots pipeline) instead of the match.any instruction, whose
 // cost grows with the number of distinct values in the warp.
