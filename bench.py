@@ -255,13 +255,24 @@ def eager_glue(pc, scaling_modifier=1.0):
     return cov, opacity, shs
 
 
-def trainer_iteration_rate(a, device, weights, render_fn, optimizer_step, dist_on):
-    """iterations/s of: raw parameters -> glue -> rasterizer -> loss -> backward -> Adam."""
+def trainer_targets(a, device):
+    """A ground-truth frame and a hand/object mask for the trainers' image loss (seeded noise: the
+    loss kernels do not care what the picture shows)."""
+    import torch
+    gen = torch.Generator().manual_seed(3003)
+    gt = torch.rand(3, a.height, a.width, generator=gen).to(device)
+    mask = (torch.rand(a.height, a.width, generator=gen) < 0.15).to(torch.int32).to(device)
+    return gt, mask
+
+
+def trainer_iteration_rate(a, device, weights, render_fn, optimizer_step, dist_on, loss_fn=None):
+    """iterations/s of: raw parameters -> glue -> rasterizer -> loss -> backward -> Adam. Without
+    `loss_fn` the loss is the weighted sum the rasterizer metric uses."""
     wc, wd, wa = (w.to(device).contiguous() for w in weights)
 
     def it():
         color, depth, alpha = render_fn()
-        loss = (color * wc).sum() + (depth * wd).sum() + (alpha * wa).sum()
+        loss = loss_fn(color) if loss_fn else (color * wc).sum() + (depth * wd).sum() + (alpha * wa).sum()
         loss.backward()
         optimizer_step()
 
@@ -461,6 +472,13 @@ def run_ours(a, rank, world, local_rank):
                 return color, depth, alpha
 
             extra["trainer_iters_per_s"] = trainer_iteration_rate(a, device, weights, render_fused, fused_adam, False)
+            # the same with the trainers' real loss, (1 - l) L1 + l (1 - SSIM) and the gradient mask
+            # (trainers/train_static_bg.py:98-102), from the fused loss kernels
+            from egogaussian_b200 import loss_utils
+            gt_img, int_mask = trainer_targets(a, device)
+            extra["trainer_ssim_iters_per_s"] = trainer_iteration_rate(
+                a, device, weights, render_fused, fused_adam, False,
+                loss_fn=lambda color: loss_utils.image_loss(color, gt_img, 0.2, grad_mask=int_mask)[0])
             extra["trainer_iters_per_s_eager_glue"] = trainer_iteration_rate(a, device, weights, render_eager_glue,
                                                                              fused_adam, False)
         except Exception as exc:  # informational only
@@ -576,6 +594,11 @@ def run_reference(a, rank, world, local_rank):
             opt.zero_grad(set_to_none=True)
 
         extra["trainer_iters_per_s"] = trainer_iteration_rate(a, device, weights, render_reference, adam, False)
+        from oracle import loss_ref   # the reference's torch loss, restated (utils/loss_utils.py)
+        gt_img, int_mask = trainer_targets(a, device)
+        extra["trainer_ssim_iters_per_s"] = trainer_iteration_rate(
+            a, device, weights, render_reference, adam, False,
+            loss_fn=lambda color: loss_ref.image_loss(color, gt_img, 0.2, int_mask)[0])
     except Exception as exc:  # informational only
         extra["trainer_error"] = str(exc)[:300]
 

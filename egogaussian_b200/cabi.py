@@ -72,6 +72,12 @@ class EgsModelArgs(C.Structure):
                 ("accum_R", c_float_p), ("train_R", c_float_p), ("row0_copies", C.c_int)]
 
 
+class EgsLossArgs(C.Structure):
+    _fields_ = [("channels", C.c_int), ("height", C.c_int), ("width", C.c_int),
+                ("image", c_float_p), ("target", c_float_p), ("grad_mask", C.c_void_p),
+                ("lambda_dssim", C.c_float)]
+
+
 class EgsGeomView(C.Structure):
     _fields_ = [("depths", C.c_void_p), ("means2D", C.c_void_p), ("conic_opacity", C.c_void_p),
                 ("rgb_depth", C.c_void_p), ("clamped", C.c_void_p), ("tiles_touched", C.c_void_p),
@@ -90,7 +96,8 @@ class EgsImageView(C.Structure):
 EXPORTED_SYMBOLS = [
     "egs_geom_bytes", "egs_binning_bytes", "egs_binning_capacity", "egs_image_bytes", "egs_forward",
     "egs_backward_scratch_bytes", "egs_backward", "egs_mark_visible", "egs_adam_step",
-    "egs_se3_apply", "egs_adam_se3_step", "egs_model_forward", "egs_model_backward", "egs_geom_view", "egs_binning_view", "egs_image_view",
+    "egs_se3_apply", "egs_adam_se3_step", "egs_model_forward", "egs_model_backward",
+    "egs_image_loss_workspace_bytes", "egs_image_loss", "egs_geom_view", "egs_binning_view", "egs_image_view",
     "egs_launch_count", "egs_last_error", "egs_abi_version",
     "egs_profile_enable", "egs_profile_read", "egs_profile_stage_name",
 ]
@@ -134,6 +141,10 @@ def load() -> C.CDLL:
     lib.egs_model_forward.argtypes = [C.POINTER(EgsModelArgs), C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]
     lib.egs_model_backward.restype = C.c_int
     lib.egs_model_backward.argtypes = [C.POINTER(EgsModelArgs)] + [C.c_void_p] * 10
+    lib.egs_image_loss_workspace_bytes.restype = C.c_size_t
+    lib.egs_image_loss_workspace_bytes.argtypes = [C.c_int, C.c_int, C.c_int]
+    lib.egs_image_loss.restype = C.c_int
+    lib.egs_image_loss.argtypes = [C.POINTER(EgsLossArgs), C.c_void_p, C.c_void_p, C.c_void_p, C.c_size_t, C.c_void_p]
     lib.egs_geom_view.restype = C.c_int
     lib.egs_geom_view.argtypes = [C.c_void_p, C.c_int, C.POINTER(EgsGeomView)]
     lib.egs_binning_view.restype = C.c_int
@@ -481,6 +492,25 @@ def model_backward(*, dL_dcov3D=None, dL_dopacity=None, dL_dshs=None, stream=Non
                                       _ptr(out.get("features_rest")), _ptr(out.get("train_R")),
                                       _stream_handle(stream)), "egs_model_backward")
     return out
+
+
+def image_loss(image, target, lambda_dssim, grad_mask=None, want_grad=True, stream=None):
+    """egs_image_loss: returns (terms [3] = L1 mean, SSIM mean, loss; dL/dimage or None)."""
+    import torch
+    lib = load()
+    a = EgsLossArgs()
+    a.channels, a.height, a.width = (int(v) for v in image.shape)
+    a.image, a.target = _ptr(image), _ptr(target)
+    a.grad_mask = _ptr(grad_mask)
+    a.lambda_dssim = float(lambda_dssim)
+    nbytes = lib.egs_image_loss_workspace_bytes(a.channels, a.height, a.width)
+    ws = torch.empty((nbytes,), dtype=torch.uint8, device=image.device)
+    terms = torch.empty((3,), dtype=torch.float32, device=image.device)
+    grad = torch.empty_like(image) if want_grad else None
+    with torch.cuda.device(image.device):
+        _check(lib.egs_image_loss(C.byref(a), terms.data_ptr(), _ptr(grad), ws.data_ptr(), nbytes,
+                                  _stream_handle(stream)), "egs_image_loss")
+    return terms, grad
 
 
 def launch_count() -> int:

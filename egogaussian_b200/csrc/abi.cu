@@ -77,7 +77,7 @@ void profile_end(cudaStream_t stream, void* token) {
 static const char* kStageNames[ST_COUNT] = {"preprocess_fwd", "scan", "duplicate_keys", "sort_histogram",
                                             "sort_passes", "tile_ranges", "blend_fwd", "bwd_zero",
                                             "blend_bwd", "preprocess_bwd", "adam", "se3",
-                                            "model_fwd", "model_bwd"};
+                                            "model_fwd", "model_bwd", "image_loss"};
 
 // Pinned read-back slot of the instance count, one per host thread, created on first use and kept
 // for the life of the process.

@@ -47,7 +47,7 @@ inline size_t align_up(size_t x, size_t a = 256) { return (x + a - 1) / a * a; }
 // Stage ids of the built-in event timing (egs_profile_* in the header).
 enum Stage {
   ST_PREPROCESS = 0, ST_SCAN, ST_DUPLICATE, ST_SORT_HIST, ST_SORT_PASSES, ST_RANGES, ST_BLEND_FWD,
-  ST_BWD_ZERO, ST_BLEND_BWD, ST_PREPROCESS_BWD, ST_ADAM, ST_SE3, ST_MODEL_FWD, ST_MODEL_BWD, ST_COUNT
+  ST_BWD_ZERO, ST_BLEND_BWD, ST_PREPROCESS_BWD, ST_ADAM, ST_SE3, ST_MODEL_FWD, ST_MODEL_BWD, ST_LOSS, ST_COUNT
 };
 static_assert(ST_COUNT <= EGS_PROFILE_STAGES, "grow EGS_PROFILE_STAGES");
 bool profiling_enabled();

@@ -415,9 +415,46 @@ std::vector<torch::Tensor> model_backward(
   return {ds, dq, dop, ddc, drest, dT};
 }
 
+// ---- image loss (egs_image_loss) ---------------------------------------------------------------------
+// returns (terms [3] = L1 mean, SSIM mean, loss; d loss / d image, empty when want_grad is false)
+std::tuple<torch::Tensor, torch::Tensor> image_loss(const torch::Tensor& image, const torch::Tensor& target,
+                                                    const torch::Tensor& grad_mask, double lambda_dssim,
+                                                    bool want_grad) {
+  TORCH_CHECK(image.is_cuda() && image.dim() == 3 && image.scalar_type() == torch::kFloat32,
+              "image_loss: image must be a float32 CUDA tensor [C,H,W]");
+  TORCH_CHECK(target.sizes() == image.sizes(), "image_loss: image and target must have the same shape");
+  const torch::Device dev = image.device();
+  c10::cuda::CUDAGuard guard(dev);
+  torch::Tensor ki, kt, km;
+  EgsLossArgs a{};
+  a.channels = (int)image.size(0);
+  a.height = (int)image.size(1);
+  a.width = (int)image.size(2);
+  a.image = req_ptr(image, ki, dev, "image");
+  a.target = req_ptr(target, kt, dev, "target");
+  a.grad_mask = nullptr;
+  if (grad_mask.defined() && grad_mask.numel() != 0) {
+    TORCH_CHECK(grad_mask.device() == dev && grad_mask.numel() == image.size(1) * image.size(2),
+                "image_loss: grad_mask must hold H*W elements on ", dev);
+    km = grad_mask.to(torch::kInt32).contiguous();
+    a.grad_mask = km.data_ptr<int>();
+  }
+  a.lambda_dssim = (float)lambda_dssim;
+  const size_t bytes = egs_image_loss_workspace_bytes(a.channels, a.height, a.width);
+  auto f32 = torch::TensorOptions().dtype(torch::kFloat32).device(dev);
+  torch::Tensor ws = torch::empty({(int64_t)bytes}, f32.dtype(torch::kByte));
+  torch::Tensor terms = torch::empty({3}, f32);
+  torch::Tensor grad = want_grad ? torch::empty_like(ki) : torch::empty({0}, f32);
+  check(egs_image_loss(&a, terms.data_ptr<float>(), want_grad ? grad.data_ptr<float>() : nullptr, ws.data_ptr(),
+                       bytes, at::cuda::getCurrentCUDAStream().stream()),
+        "egs_image_loss");
+  return std::make_tuple(terms, grad);
+}
+
 }  // namespace
 
 PYBIND11_MODULE(TORCH_EXTENSION_NAME, m) {
+  m.def("image_loss", &image_loss);
   m.def("model_forward", &model_forward);
   m.def("model_backward", &model_backward);
   m.def("rasterize_gaussians", &rasterize_gaussians);

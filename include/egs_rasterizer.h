@@ -16,6 +16,7 @@
  *                      <- get_scaling/get_opacity/get_features     scene/gaussian_model.py:126-153
  *                         get_covariance/get_rotated_covariance    scene/gaussian_model.py:29-63,167-171
  *                         build_rotation/build_scaling_rotation    utils/general_utils.py:110-158
+ *   egs_image_loss     <- l1_loss + ssim (+ gradient mask hook)    utils/loss_utils.py:57-106
  *
  * Conventions
  *   - plain C, no torch types, no exceptions; every pointer named `d_*` or documented as
@@ -271,6 +272,31 @@ int egs_model_backward(const EgsModelArgs* model, const float* dL_dcov3D, const 
                        const float* dL_dshs, float* d_scaling_raw, float* d_rotation_raw,
                        float* d_opacity_raw, float* d_features_dc, float* d_features_rest,
                        float* d_train_R, void* stream);
+
+/* ---- image loss of the trainers ------------------------------------ */
+
+/* loss = (1 - lambda_dssim) * mean|image - target| + lambda_dssim * (1 - SSIM(image, target))
+ * with the reference's SSIM: 11x11 Gaussian window, sigma 1.5, zero padding, per channel, mean over
+ * all elements (utils/loss_utils.py:57-106; call sites trainers/train_static_bg.py:100-102,
+ * fine_all.py:99-100, fine_obj.py:142-143, coarse_obj_pose.py:252-253). Both terms are symmetric
+ * in their two arguments, so the argument order of a call site does not matter; the gradient is
+ * taken w.r.t. `image`. */
+typedef struct EgsLossArgs {
+  int channels, height, width;
+  const float* image;      /* device [C,H,W]  the rendered image */
+  const float* target;     /* device [C,H,W]  ground truth */
+  const int* grad_mask;    /* device [H,W] int32 or NULL: the gradient is multiplied by (1 - mask),
+                              the register_hook of trainers/train_static_bg.py:98 */
+  float lambda_dssim;
+} EgsLossArgs;
+
+size_t egs_image_loss_workspace_bytes(int channels, int height, int width);
+
+/* out_terms: device [3] = {L1 mean, SSIM mean, loss}. dL_dimage: device [C,H,W] = d loss / d image
+ * (every element written), or NULL for the value only. Deterministic (fixed summation order).
+ * workspace: device, 256-byte aligned, >= egs_image_loss_workspace_bytes(). */
+int egs_image_loss(const EgsLossArgs* args, float* out_terms, float* dL_dimage, void* workspace,
+                   size_t workspace_bytes, void* stream);
 
 /* ---- introspection (tests / bench) ----------------------------------------------------- */
 

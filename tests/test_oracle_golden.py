@@ -117,3 +117,33 @@ def test_model_restatement_matches_reference(case):
     assert_model_close(run_model_restatement(case), gold, case["name"])
     if case["name"] == "model_object_train":   # the row-0 gradient multiplicity is really there
         assert np.abs(gold["d_scaling_raw"][0]).max() > 5 * np.abs(gold["d_scaling_raw"][1:]).max()
+
+
+# ---- image loss (oracle/loss_ref.py) against the reference's own utils/loss_utils.py ------------------
+from golden.make_loss_golden import LOSS_CASES, loss_inputs  # noqa: E402
+
+
+def run_loss_restatement(case, device="cpu"):
+    from oracle import loss_ref
+    x = {k: v.to(device) for k, v in loss_inputs(case).items()}
+    leaf = x["render"].clone().requires_grad_(True)
+    loss, l1, s = loss_ref.image_loss(leaf, x["gt"], case["lam"], x["mask"] if case["mask"] else None)
+    loss.backward()
+    return {"l1": l1.detach().cpu().numpy(), "ssim": s.detach().cpu().numpy(), "loss": loss.detach().cpu().numpy(),
+            "d_render": leaf.grad.cpu().numpy()}
+
+
+def assert_loss_close(got, gold, what, value_rtol=2e-6, grad_rtol=1e-4):
+    """Scalars within 2e-6 relative (fp32 means over up to 1e6 elements, summed in another order);
+    the gradient image within 1e-4 of its maximum, the path's gradient tolerance."""
+    for k in ("l1", "ssim", "loss"):
+        assert abs(float(got[k]) - float(gold[k])) <= value_rtol * max(abs(float(gold[k])), 1e-3), (what, k)
+    a, b = got["d_render"].astype(np.float64), gold["d_render"].astype(np.float64)
+    assert a.shape == b.shape
+    assert np.abs(a - b).max() <= grad_rtol * np.abs(b).max(), (what, np.abs(a - b).max(), np.abs(b).max())
+
+
+@pytest.mark.parametrize("case", LOSS_CASES, ids=[c["name"] for c in LOSS_CASES])
+def test_loss_restatement_matches_reference(case):
+    gold = np.load(GOLDEN / f"{case['name']}.npz")
+    assert_loss_close(run_loss_restatement(case), gold, case["name"])
