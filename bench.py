@@ -476,9 +476,26 @@ def run_ours(a, rank, world, local_rank):
             # (trainers/train_static_bg.py:98-102), from the fused loss kernels
             from egogaussian_b200 import loss_utils
             gt_img, int_mask = trainer_targets(a, device)
+            cabi.profile_enable(True)
+            cabi.profile_read()
             extra["trainer_ssim_iters_per_s"] = trainer_iteration_rate(
                 a, device, weights, render_fused, fused_adam, False,
                 loss_fn=lambda color: loss_utils.image_loss(color, gt_img, 0.2, grad_mask=int_mask)[0])
+            tprof = cabi.profile_read()
+            cabi.profile_enable(False)
+            # algorithmic bytes of the added stages: raw parameters in, activated
+            # tensors out and the reverse; 8 image-sized reads/writes each way for the loss; 28 B per
+            # optimised float for Adam
+            floats = sum(p.numel() for p in params)
+            talg = {"model_fwd": P * (12 + 16 + 4 + 12 * M) + P * (24 + 4 + 12 * M),
+                    "model_bwd": P * (12 + 16 + 4 + 24 + 4 + 12 * M) + P * (12 + 16 + 4 + 12 * M),
+                    "image_loss": (2 + 3 + 3 + 2 + 1) * 3 * N * 4 + 4 * N, "adam": 28 * floats}
+            iters = a.steps + 3   # timed + warm-up iterations between the two reads
+            extra["trainer_kernels"] = {
+                k: {"ms_per_step": round(tprof[k][0] / iters, 4), "alg_MB": round(talg[k] / 1e6, 2),
+                    "GBps": round(talg[k] / (tprof[k][0] / iters) / 1e6, 1),
+                    "frac_hbm": round(talg[k] / (tprof[k][0] / iters) / 1e6 / peak, 4)}
+                for k in talg if k in tprof and tprof[k][1] > 0}
             extra["trainer_iters_per_s_eager_glue"] = trainer_iteration_rate(a, device, weights, render_eager_glue,
                                                                              fused_adam, False)
         except Exception as exc:  # informational only

@@ -97,7 +97,7 @@ EXPORTED_SYMBOLS = [
     "egs_geom_bytes", "egs_binning_bytes", "egs_binning_capacity", "egs_image_bytes", "egs_forward",
     "egs_backward_scratch_bytes", "egs_backward", "egs_mark_visible", "egs_adam_step",
     "egs_se3_apply", "egs_adam_se3_step", "egs_model_forward", "egs_model_backward",
-    "egs_image_loss_workspace_bytes", "egs_image_loss", "egs_geom_view", "egs_binning_view", "egs_image_view",
+    "egs_image_loss_workspace_bytes", "egs_image_loss", "egs_densify_stats", "egs_geom_view", "egs_binning_view", "egs_image_view",
     "egs_launch_count", "egs_last_error", "egs_abi_version",
     "egs_profile_enable", "egs_profile_read", "egs_profile_stage_name",
 ]
@@ -145,6 +145,8 @@ def load() -> C.CDLL:
     lib.egs_image_loss_workspace_bytes.argtypes = [C.c_int, C.c_int, C.c_int]
     lib.egs_image_loss.restype = C.c_int
     lib.egs_image_loss.argtypes = [C.POINTER(EgsLossArgs), C.c_void_p, C.c_void_p, C.c_void_p, C.c_size_t, C.c_void_p]
+    lib.egs_densify_stats.restype = C.c_int
+    lib.egs_densify_stats.argtypes = [C.c_int] + [C.c_void_p] * 6
     lib.egs_geom_view.restype = C.c_int
     lib.egs_geom_view.argtypes = [C.c_void_p, C.c_int, C.POINTER(EgsGeomView)]
     lib.egs_binning_view.restype = C.c_int
@@ -511,6 +513,15 @@ def image_loss(image, target, lambda_dssim, grad_mask=None, want_grad=True, stre
         _check(lib.egs_image_loss(C.byref(a), terms.data_ptr(), _ptr(grad), ws.data_ptr(), nbytes,
                                   _stream_handle(stream)), "egs_image_loss")
     return terms, grad
+
+
+def densify_stats(radii, dL_dmeans2D, max_radii2D, xyz_gradient_accum, denom, stream=None) -> None:
+    """egs_densify_stats: in-place update of the three bookkeeping tensors."""
+    import torch
+    with torch.cuda.device(radii.device):
+        _check(load().egs_densify_stats(int(radii.shape[0]), _ptr(radii), _ptr(dL_dmeans2D), _ptr(max_radii2D),
+                                        _ptr(xyz_gradient_accum), _ptr(denom), _stream_handle(stream)),
+               "egs_densify_stats")
 
 
 def launch_count() -> int:

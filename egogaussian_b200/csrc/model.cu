@@ -166,6 +166,24 @@ features_kernel(int P, int M, float* __restrict__ dc, float* __restrict__ rest, 
   }
 }
 
+// Per-iteration densification bookkeeping (scene/gaussian_model.py:735-740 and
+// trainers/train_static_bg.py:128), for the rows with radii > 0:
+//   max_radii2D = max(max_radii2D, radii); xyz_gradient_accum += |dL/dmean2D.xy|; denom += 1.
+// The reference does this with boolean-mask indexing, i.e. several nonzero() host syncs per
+// iteration; here it is one pass without any.
+__global__ void __launch_bounds__(MODEL_THREADS)
+densify_stats_kernel(int P, const int* __restrict__ radii, const float* __restrict__ dL_dmeans2D,
+                     float* __restrict__ max_radii2D, float* __restrict__ grad_accum, float* __restrict__ denom) {
+  const int i = blockIdx.x * MODEL_THREADS + threadIdx.x;
+  if (i >= P) return;
+  const int r = radii[i];
+  if (r <= 0) return;
+  max_radii2D[i] = fmaxf(max_radii2D[i], (float)r);
+  const float gx = dL_dmeans2D[3 * i], gy = dL_dmeans2D[3 * i + 1];
+  grad_accum[i] += sqrtf(gx * gx + gy * gy);
+  denom[i] += 1.f;
+}
+
 static int check_model(const EgsModelArgs* m, const char* who) {
   if (m == nullptr || m->P < 0) {
     set_error("%s: NULL args or negative P", who);
@@ -258,5 +276,20 @@ extern "C" int egs_model_backward(const EgsModelArgs* m, const float* dL_dcov3D,
         P, M, d_features_dc, d_features_rest, const_cast<float*>(dL_dshs));
     EGS_AFTER_LAUNCH(st, false);
   }
+  return EGS_OK;
+}
+
+extern "C" int egs_densify_stats(int P, const int* radii, const float* dL_dmeans2D, float* max_radii2D,
+                                 float* xyz_gradient_accum, float* denom, void* stream) {
+  using namespace egs;
+  if (P < 0 || (P > 0 && (!radii || !dL_dmeans2D || !max_radii2D || !xyz_gradient_accum || !denom))) {
+    set_error("egs_densify_stats: NULL argument or negative P");
+    return EGS_ERR_INVALID_ARGUMENT;
+  }
+  if (P == 0) return EGS_OK;
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  densify_stats_kernel<<<(P + MODEL_THREADS - 1) / MODEL_THREADS, MODEL_THREADS, 0, st>>>(
+      P, radii, dL_dmeans2D, max_radii2D, xyz_gradient_accum, denom);
+  EGS_AFTER_LAUNCH(st, false);
   return EGS_OK;
 }

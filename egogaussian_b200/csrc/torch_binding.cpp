@@ -451,9 +451,28 @@ std::tuple<torch::Tensor, torch::Tensor> image_loss(const torch::Tensor& image, 
   return std::make_tuple(terms, grad);
 }
 
+void densify_stats(const torch::Tensor& radii, const torch::Tensor& dL_dmeans2D, torch::Tensor max_radii2D,
+                   torch::Tensor xyz_gradient_accum, torch::Tensor denom) {
+  TORCH_CHECK(radii.is_cuda() && radii.scalar_type() == torch::kInt32 && radii.is_contiguous(),
+              "densify_stats: radii must be contiguous int32 CUDA");
+  const int64_t P = radii.numel();
+  for (const torch::Tensor* t : {&dL_dmeans2D, (const torch::Tensor*)&max_radii2D,
+                                 (const torch::Tensor*)&xyz_gradient_accum, (const torch::Tensor*)&denom})
+    TORCH_CHECK(t->device() == radii.device() && t->scalar_type() == torch::kFloat32 && t->is_contiguous(),
+                "densify_stats: tensors must be contiguous float32 on the device of radii");
+  TORCH_CHECK(dL_dmeans2D.numel() == 3 * P && max_radii2D.numel() == P && xyz_gradient_accum.numel() == P &&
+                  denom.numel() == P, "densify_stats: shape mismatch");
+  c10::cuda::CUDAGuard guard(radii.device());
+  check(egs_densify_stats((int)P, radii.data_ptr<int>(), dL_dmeans2D.data_ptr<float>(), max_radii2D.data_ptr<float>(),
+                          xyz_gradient_accum.data_ptr<float>(), denom.data_ptr<float>(),
+                          at::cuda::getCurrentCUDAStream().stream()),
+        "egs_densify_stats");
+}
+
 }  // namespace
 
 PYBIND11_MODULE(TORCH_EXTENSION_NAME, m) {
+  m.def("densify_stats", &densify_stats);
   m.def("image_loss", &image_loss);
   m.def("model_forward", &model_forward);
   m.def("model_backward", &model_backward);

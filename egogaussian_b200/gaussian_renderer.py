@@ -201,6 +201,16 @@ def render(viewpoint_camera, pc, pipe, bg_color: torch.Tensor, scaling_modifier:
             "alpha": rendered_alpha}
 
 
+def add_densification_stats(pc, viewspace_point_tensor: torch.Tensor, radii: torch.Tensor) -> None:
+    """The trainers' per-iteration bookkeeping in one launch and without a host sync
+    (trainers/train_static_bg.py:128-129; GaussianModel.add_densification_stats,
+    scene/gaussian_model.py:735-740): for the rows with ``radii > 0`` updates ``pc.max_radii2D``,
+    ``pc.xyz_gradient_accum`` and ``pc.denom`` in place. ``radii`` is the rasterizer's output;
+    the visibility filter is derived from it, as the reference does (``radii > 0``)."""
+    with torch.no_grad():
+        _C.densify_stats(radii, viewspace_point_tensor.grad, pc.max_radii2D, pc.xyz_gradient_accum, pc.denom)
+
+
 def _activations_only(pc, dc, rest):
     """opacity and features without the covariance (compute_cov3D_python=False)."""
     return _ModelActivations.apply(_EMPTY, _EMPTY, pc._opacity, dc, rest, 1.0, _EMPTY, -1, _EMPTY, _EMPTY, 0)

@@ -273,6 +273,17 @@ int egs_model_backward(const EgsModelArgs* model, const float* dL_dcov3D, const 
                        float* d_opacity_raw, float* d_features_dc, float* d_features_rest,
                        float* d_train_R, void* stream);
 
+/* Per-iteration densification bookkeeping (the per-iteration half:
+ * GaussianModel.add_densification_stats, scene/gaussian_model.py:735-740, and the max_radii2D
+ * line of trainers/train_static_bg.py:128). For rows with radii[i] > 0:
+ *   max_radii2D[i] = max(max_radii2D[i], radii[i]);
+ *   xyz_gradient_accum[i] += sqrt(g.x^2 + g.y^2) with g = dL_dmeans2D[i] (viewspace_points.grad);
+ *   denom[i] += 1.
+ * All arrays are device, length P ([P,3] for dL_dmeans2D); no host sync (the reference's boolean
+ * mask indexing costs several per iteration). */
+int egs_densify_stats(int P, const int* radii, const float* dL_dmeans2D, float* max_radii2D,
+                      float* xyz_gradient_accum, float* denom, void* stream);
+
 /* ---- image loss of the trainers ------------------------------------ */
 
 /* loss = (1 - lambda_dssim) * mean|image - target| + lambda_dssim * (1 - SSIM(image, target))

@@ -124,8 +124,35 @@ def run_reference(case: dict, GaussianModel, ObjectMove) -> dict:
     return {k: v.detach().numpy() for k, v in out.items()}
 
 
+def stats_inputs() -> dict:
+    gen = torch.Generator().manual_seed(4999)
+    P = 5000
+    radii = torch.randint(0, 40, (P,), generator=gen, dtype=torch.int32)
+    radii[torch.rand(P, generator=gen) < 0.3] = 0
+    return {"radii": radii, "grad": torch.randn(P, 3, generator=gen) * 1e-3,
+            "max_radii2D": torch.rand(P, generator=gen) * 30, "accum": torch.rand(P, 1, generator=gen),
+            "denom": torch.randint(0, 50, (P, 1), generator=gen).float()}
+
+
+def run_reference_stats(GaussianModel) -> dict:
+    """Two iterations of the per-iteration densification bookkeeping:
+    GaussianModel.add_densification_stats (scene/gaussian_model.py:735-740) plus the trainer's
+    max_radii2D line (trainers/train_static_bg.py:128, restated here: it is not in a function)."""
+    x = stats_inputs()
+    pc = GaussianModel(3)
+    pc.max_radii2D, pc.xyz_gradient_accum, pc.denom = x["max_radii2D"].clone(), x["accum"].clone(), x["denom"].clone()
+    for it in range(2):
+        vp = torch.zeros(x["grad"].shape)
+        vp.grad = x["grad"] * (it + 1)
+        vis = x["radii"] > 0
+        pc.max_radii2D[vis] = torch.max(pc.max_radii2D[vis], x["radii"][vis])
+        pc.add_densification_stats(vp, vis)
+    return {"max_radii2D": pc.max_radii2D.numpy(), "accum": pc.xyz_gradient_accum.numpy(), "denom": pc.denom.numpy()}
+
+
 def main():
     GaussianModel, ObjectMove = _import_reference()
+    np.savez_compressed(OUT / "model_stats.npz", **run_reference_stats(GaussianModel))
     for case in MODEL_CASES:
         res = run_reference(case, GaussianModel, ObjectMove)
         np.savez_compressed(OUT / f"{case['name']}.npz", **res)

@@ -66,6 +66,22 @@ def test_model_kernels_against_live_restatement(case, built, cuda_device):
     assert np.array_equal(ours["shs"], ref["shs"]) and np.array_equal(ours["d_features_rest"], ref["d_features_rest"])
 
 
+def test_densify_stats_against_reference_golden(built, cuda_device):
+    """Two iterations of max_radii2D / xyz_gradient_accum / denom bookkeeping against the
+    reference's own GaussianModel.add_densification_stats (golden model_stats.npz): counters and
+    maxima exactly, the accumulated norms within 1e-6 relative."""
+    from egogaussian_b200 import cabi
+    from golden.make_model_golden import stats_inputs
+    x = {k: v.to(cuda_device) for k, v in stats_inputs().items()}
+    gold = np.load(GOLDEN / "model_stats.npz")
+    mx, acc, den = x["max_radii2D"].clone(), x["accum"].clone(), x["denom"].clone()
+    for it in range(2):
+        cabi.densify_stats(x["radii"], (x["grad"] * (it + 1)).contiguous(), mx, acc, den)
+    assert np.array_equal(mx.cpu().numpy(), gold["max_radii2D"])
+    assert np.array_equal(den.cpu().numpy(), gold["denom"])
+    np.testing.assert_allclose(acc.cpu().numpy(), gold["accum"], rtol=1e-6, atol=0)
+
+
 class _Camera:
     def __init__(self, cam, W, H):
         self.image_width, self.image_height = W, H
