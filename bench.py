@@ -489,13 +489,18 @@ def run_ours(a, rank, world, local_rank):
             floats = sum(p.numel() for p in params)
             talg = {"model_fwd": P * (12 + 16 + 4 + 12 * M) + P * (24 + 4 + 12 * M),
                     "model_bwd": P * (12 + 16 + 4 + 24 + 4 + 12 * M) + P * (12 + 16 + 4 + 12 * M),
-                    "image_loss": (2 + 3 + 3 + 2 + 1) * 3 * N * 4 + 4 * N, "adam": 28 * floats}
+                    "image_loss": (2 + 3 + 3 + 2 + 1) * 3 * N * 4 + 4 * N, "adam": 28 * floats,
+                    # raw-parameter mode of the per-Gaussian kernels (render(fused=True)): raw scale,
+                    # quaternion, opacity logit and the split SH rows in; no cov3D / opacity / SH tensors
+                    "preprocess_fwd": 20 * P + V * (28 + 4 + 12 * M + 4 + 8 + 16 + 16 + 1),
+                    "preprocess_bwd": P * (12 + 4 + 12 * M + 1 + 28 + 4 + 48) + P * (12 + 12 + 4 + 28 + 12 * M)}
             iters = a.steps + 3   # timed + warm-up iterations between the two reads
             extra["trainer_kernels"] = {
                 k: {"ms_per_step": round(tprof[k][0] / iters, 4), "alg_MB": round(talg[k] / 1e6, 2),
                     "GBps": round(talg[k] / (tprof[k][0] / iters) / 1e6, 1),
                     "frac_hbm": round(talg[k] / (tprof[k][0] / iters) / 1e6 / peak, 4)}
                 for k in talg if k in tprof and tprof[k][1] > 0}
+            extra["trainer_stage_ms"] = {k: round(v[0] / iters, 4) for k, v in tprof.items() if v[1] > 0}
             extra["trainer_iters_per_s_eager_glue"] = trainer_iteration_rate(a, device, weights, render_eager_glue,
                                                                              fused_adam, False)
         except Exception as exc:  # informational only

@@ -72,6 +72,11 @@ class EgsModelArgs(C.Structure):
                 ("accum_R", c_float_p), ("train_R", c_float_p), ("row0_copies", C.c_int)]
 
 
+class EgsModelGrads(C.Structure):
+    _fields_ = [("d_scaling_raw", c_float_p), ("d_rotation_raw", c_float_p), ("d_opacity_raw", c_float_p),
+                ("d_features_dc", c_float_p), ("d_features_rest", c_float_p), ("d_train_R", c_float_p)]
+
+
 class EgsLossArgs(C.Structure):
     _fields_ = [("channels", C.c_int), ("height", C.c_int), ("width", C.c_int),
                 ("image", c_float_p), ("target", c_float_p), ("grad_mask", C.c_void_p),
@@ -97,6 +102,7 @@ EXPORTED_SYMBOLS = [
     "egs_geom_bytes", "egs_binning_bytes", "egs_binning_capacity", "egs_image_bytes", "egs_forward",
     "egs_backward_scratch_bytes", "egs_backward", "egs_mark_visible", "egs_adam_step",
     "egs_se3_apply", "egs_adam_se3_step", "egs_model_forward", "egs_model_backward",
+    "egs_forward_raw", "egs_backward_raw",
     "egs_image_loss_workspace_bytes", "egs_image_loss", "egs_densify_stats", "egs_geom_view", "egs_binning_view", "egs_image_view",
     "egs_launch_count", "egs_last_error", "egs_abi_version",
     "egs_profile_enable", "egs_profile_read", "egs_profile_stage_name",
@@ -141,6 +147,11 @@ def load() -> C.CDLL:
     lib.egs_model_forward.argtypes = [C.POINTER(EgsModelArgs), C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]
     lib.egs_model_backward.restype = C.c_int
     lib.egs_model_backward.argtypes = [C.POINTER(EgsModelArgs)] + [C.c_void_p] * 10
+    lib.egs_forward_raw.restype = C.c_int
+    lib.egs_forward_raw.argtypes = [C.POINTER(EgsForwardArgs), C.POINTER(EgsModelArgs), C.c_void_p, C.POINTER(C.c_int)]
+    lib.egs_backward_raw.restype = C.c_int
+    lib.egs_backward_raw.argtypes = [C.POINTER(EgsBackwardArgs), C.POINTER(EgsModelArgs), C.POINTER(EgsModelGrads),
+                                     C.c_void_p]
     lib.egs_image_loss_workspace_bytes.restype = C.c_size_t
     lib.egs_image_loss_workspace_bytes.argtypes = [C.c_int, C.c_int, C.c_int]
     lib.egs_image_loss.restype = C.c_int

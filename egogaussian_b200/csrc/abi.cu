@@ -136,20 +136,44 @@ extern "C" int egs_binning_capacity(size_t bytes) {
 }
 extern "C" size_t egs_backward_scratch_bytes(int P) { return BackwardScratch::bytes((size_t)(P < 0 ? 0 : P)); }
 
-extern "C" int egs_forward(const EgsForwardArgs* args, void* stream_v, int* num_rendered) {
+// Raw-parameter mode: the five derived inputs must be absent and their raw sources present.
+static int check_raw_model(const char* who, const EgsModelArgs* m, int P, int sh_degree, const void* shs,
+                           const void* colors, const void* opacities, const void* scales, const void* rotations,
+                           const void* cov) {
+  if (shs || opacities || scales || rotations || cov) {
+    set_error("%s: opacities / shs / scales / rotations / cov3D_precomp must be NULL (they come from the model)", who);
+    return EGS_ERR_INVALID_ARGUMENT;
+  }
+  if (m->P != P || !m->scaling_raw || !m->rotation_raw || !m->opacity_raw || m->row0_copies < 0 ||
+      (reinterpret_cast<uintptr_t>(m->rotation_raw) & 15u) != 0) {
+    set_error("%s: model needs P == args->P, scaling_raw, rotation_raw (16-byte aligned) and opacity_raw", who);
+    return EGS_ERR_INVALID_ARGUMENT;
+  }
+  if (!colors) {
+    if (!m->features_dc || m->sh_coeffs < 1 || m->sh_coeffs > 16 || (m->sh_coeffs > 1 && !m->features_rest) ||
+        m->sh_coeffs < (sh_degree + 1) * (sh_degree + 1)) {
+      set_error("%s: model features missing or sh_coeffs %d unusable for degree %d", who, m->sh_coeffs, sh_degree);
+      return EGS_ERR_INVALID_ARGUMENT;
+    }
+  }
+  return EGS_OK;
+}
+
+static int forward_impl(const char* who, const EgsForwardArgs* args, const EgsModelArgs* model, void* stream_v,
+                        int* num_rendered) {
   if (!args || !num_rendered) {
-    set_error("egs_forward: NULL args");
+    set_error("%s: NULL args", who);
     return EGS_ERR_INVALID_ARGUMENT;
   }
   const EgsForwardArgs& a = *args;
   cudaStream_t stream = static_cast<cudaStream_t>(stream_v);
   *num_rendered = 0;
   if (a.P < 0 || a.width <= 0 || a.height <= 0 || a.sh_degree < 0 || a.sh_degree > 3) {
-    set_error("egs_forward: bad P / image size / sh_degree");
+    set_error("%s: bad P / image size / sh_degree", who);
     return EGS_ERR_INVALID_ARGUMENT;
   }
   if (!a.out_color || !a.out_depth || !a.out_alpha || !a.background) {
-    set_error("egs_forward: NULL output or background");
+    set_error("%s: NULL output or background", who);
     return EGS_ERR_INVALID_ARGUMENT;
   }
   const size_t N = (size_t)a.width * a.height;
@@ -160,35 +184,40 @@ extern "C" int egs_forward(const EgsForwardArgs* args, void* stream_v, int* num_
     EGS_CUDA_TRY(cudaMemsetAsync(a.out_alpha, 0, N * sizeof(float), stream));
     return EGS_OK;
   }
-  if (int rc = check_pairs("egs_forward", a.shs, a.colors_precomp, a.scales, a.rotations, a.cov3D_precomp))
+  if (model != nullptr) {
+    if (int rc = check_raw_model(who, model, a.P, a.sh_degree, a.shs, a.colors_precomp, a.opacities, a.scales,
+                                 a.rotations, a.cov3D_precomp))
+      return rc;
+  } else if (int rc = check_pairs(who, a.shs, a.colors_precomp, a.scales, a.rotations, a.cov3D_precomp)) {
     return rc;
-  if (!a.means3D || !a.opacities || !a.viewmatrix || !a.projmatrix || !a.campos || !a.radii ||
+  }
+  if (!a.means3D || (!a.opacities && !model) || !a.viewmatrix || !a.projmatrix || !a.campos || !a.radii ||
       !a.geom_alloc || !a.binning_alloc || !a.image_alloc) {
-    set_error("egs_forward: NULL required input");
+    set_error("%s: NULL required input", who);
     return EGS_ERR_INVALID_ARGUMENT;
   }
   if (a.shs && a.sh_coeffs < (a.sh_degree + 1) * (a.sh_degree + 1)) {
-    set_error("egs_forward: sh_coeffs %d too small for degree %d", a.sh_coeffs, a.sh_degree);
+    set_error("%s: sh_coeffs %d too small for degree %d", who, a.sh_coeffs, a.sh_degree);
     return EGS_ERR_INVALID_ARGUMENT;
   }
 
   void* geom_mem = a.geom_alloc(a.geom_ctx, egs_geom_bytes(a.P));
   void* img_mem = a.image_alloc(a.image_ctx, egs_image_bytes(a.width, a.height));
   if (!geom_mem || !img_mem) {
-    set_error("egs_forward: workspace callback returned NULL");
+    set_error("%s: workspace callback returned NULL", who);
     return EGS_ERR_ALLOC;
   }
   const GeomPtrs g(geom_mem, (size_t)a.P);
   const ImagePtrs im(img_mem, a.width, a.height);
 
-  if (int rc = launch_preprocess_forward(a, g, stream)) return rc;
+  if (int rc = launch_preprocess_forward(a, model, g, stream)) return rc;
   if (int rc = launch_scan_tiles(g, a.P, stream, a.debug)) return rc;
 
   // The one device->host read per forward (the reference's is rasterizer_impl.cu:281-282): the
   // instance count lands in a pinned slot and an event marks its arrival.
   HostCountSlot* slot = host_count_slot();
   if (!slot) {
-    set_error("egs_forward: cannot allocate the pinned read-back slot");
+    set_error("%s: cannot allocate the pinned read-back slot", who);
     return EGS_ERR_CUDA;
   }
   const uint32_t* n_dev = g.point_offsets + (a.P - 1);
@@ -210,7 +239,7 @@ extern "C" int egs_forward(const EgsForwardArgs* args, void* stream_v, int* num_
     capacity = a.num_rendered_hint;
     bin_mem = a.binning_alloc(a.binning_ctx, egs_binning_bytes(capacity, a.width, a.height));
     if (!bin_mem) {
-      set_error("egs_forward: binning workspace callback returned NULL");
+      set_error("%s: binning workspace callback returned NULL", who);
       return EGS_ERR_ALLOC;
     }
     const BinningPtrs b(bin_mem, (size_t)capacity);
@@ -226,7 +255,7 @@ extern "C" int egs_forward(const EgsForwardArgs* args, void* stream_v, int* num_
   EGS_CUDA_TRY(cudaEventSynchronize(slot->arrived));
   const uint32_t R_host = *slot->host;
   if (R_host >= (1u << 30)) {
-    set_error("egs_forward: num_rendered %u exceeds the supported 2^30", R_host);
+    set_error("%s: num_rendered %u exceeds the supported 2^30", who, R_host);
     return EGS_ERR_TOO_LARGE;
   }
   const int R = (int)R_host;
@@ -236,7 +265,7 @@ extern "C" int egs_forward(const EgsForwardArgs* args, void* stream_v, int* num_
   // exact run (no guess, guess too small, forced path, or a path that does not speculate)
   bin_mem = a.binning_alloc(a.binning_ctx, egs_binning_bytes(R, a.width, a.height));
   if (!bin_mem) {
-    set_error("egs_forward: binning workspace callback returned NULL");
+    set_error("%s: binning workspace callback returned NULL", who);
     return EGS_ERR_ALLOC;
   }
   const BinningPtrs b(bin_mem, (size_t)R);
@@ -261,30 +290,55 @@ extern "C" int egs_forward(const EgsForwardArgs* args, void* stream_v, int* num_
   return launch_blend_forward(a, g, b.vals[0], im, stream);
 }
 
-extern "C" int egs_backward(const EgsBackwardArgs* args, void* stream_v) {
+extern "C" int egs_forward(const EgsForwardArgs* args, void* stream, int* num_rendered) {
+  return forward_impl("egs_forward", args, nullptr, stream, num_rendered);
+}
+
+extern "C" int egs_forward_raw(const EgsForwardArgs* args, const EgsModelArgs* model, void* stream,
+                               int* num_rendered) {
+  if (!model) {
+    set_error("egs_forward_raw: NULL model");
+    return EGS_ERR_INVALID_ARGUMENT;
+  }
+  return forward_impl("egs_forward_raw", args, model, stream, num_rendered);
+}
+
+static int backward_impl(const char* who, const EgsBackwardArgs* args, const EgsModelArgs* model,
+                         const EgsModelGrads* grads, void* stream_v) {
   if (!args) {
-    set_error("egs_backward: NULL args");
+    set_error("%s: NULL args", who);
     return EGS_ERR_INVALID_ARGUMENT;
   }
   const EgsBackwardArgs& a = *args;
   cudaStream_t stream = static_cast<cudaStream_t>(stream_v);
   if (a.P < 0 || a.width <= 0 || a.height <= 0 || a.num_rendered < 0) {
-    set_error("egs_backward: bad sizes");
+    set_error("%s: bad sizes", who);
     return EGS_ERR_INVALID_ARGUMENT;
   }
   if (a.P == 0) return EGS_OK;
-  if (int rc = check_pairs("egs_backward", a.shs, a.colors_precomp, a.scales, a.rotations, a.cov3D_precomp))
+  if (model != nullptr) {
+    if (int rc = check_raw_model(who, model, a.P, a.sh_degree, a.shs, a.colors_precomp, nullptr, a.scales,
+                                 a.rotations, a.cov3D_precomp))
+      return rc;
+    if (!grads || !grads->d_scaling_raw || !grads->d_rotation_raw || !grads->d_opacity_raw ||
+        (reinterpret_cast<uintptr_t>(grads->d_rotation_raw) & 15u) != 0 ||
+        (!a.colors_precomp && (!grads->d_features_dc || (model->sh_coeffs > 1 && !grads->d_features_rest)))) {
+      set_error("%s: missing raw-parameter gradient output (d_rotation_raw must be 16-byte aligned)", who);
+      return EGS_ERR_INVALID_ARGUMENT;
+    }
+  } else if (int rc = check_pairs(who, a.shs, a.colors_precomp, a.scales, a.rotations, a.cov3D_precomp)) {
     return rc;
+  }
   if (!a.means3D || !a.radii || !a.out_alpha || !a.geom_buffer || !a.image_buffer ||
       (a.num_rendered > 0 && !a.binning_buffer) || !a.dL_dout_color || !a.dL_dout_depth ||
-      !a.dL_dout_alpha || !a.scratch || !a.dL_dmeans2D || !a.dL_dopacity || !a.dL_dmeans3D ||
+      !a.dL_dout_alpha || !a.scratch || !a.dL_dmeans2D || (!a.dL_dopacity && !model) || !a.dL_dmeans3D ||
       !a.background || !a.viewmatrix || !a.projmatrix || !a.campos) {
-    set_error("egs_backward: NULL required argument");
+    set_error("%s: NULL required argument", who);
     return EGS_ERR_INVALID_ARGUMENT;
   }
   if ((a.colors_precomp && !a.dL_dcolors) || (a.cov3D_precomp && !a.dL_dcov3D) || (a.shs && !a.dL_dsh) ||
       (a.scales && (!a.dL_dscales || !a.dL_drotations))) {
-    set_error("egs_backward: missing gradient output for a provided input");
+    set_error("%s: missing gradient output for a provided input", who);
     return EGS_ERR_INVALID_ARGUMENT;
   }
   const GeomPtrs g(const_cast<void*>(a.geom_buffer), (size_t)a.P);
@@ -301,7 +355,20 @@ extern "C" int egs_backward(const EgsBackwardArgs* args, void* stream_v) {
     const uint32_t* point_list = b.vals[0];
     if (int rc = launch_blend_backward(a, g, point_list, im, s, stream)) return rc;
   }
-  return launch_preprocess_backward(a, g, s, stream);
+  return launch_preprocess_backward(a, model, grads, g, s, stream);
+}
+
+extern "C" int egs_backward(const EgsBackwardArgs* args, void* stream) {
+  return backward_impl("egs_backward", args, nullptr, nullptr, stream);
+}
+
+extern "C" int egs_backward_raw(const EgsBackwardArgs* args, const EgsModelArgs* model, const EgsModelGrads* grads,
+                                void* stream) {
+  if (!model) {
+    set_error("egs_backward_raw: NULL model");
+    return EGS_ERR_INVALID_ARGUMENT;
+  }
+  return backward_impl("egs_backward_raw", args, model, grads, stream);
 }
 
 // ---- backward with the scratch inside the library image --------------------------------------

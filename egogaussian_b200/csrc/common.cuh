@@ -221,7 +221,10 @@ struct BackwardScratch {
 // ---------------------------------------------------------------------------------------------
 // stage entry points (each enqueues kernels on `stream`; return EgsStatus)
 // ---------------------------------------------------------------------------------------------
-int launch_preprocess_forward(const EgsForwardArgs& a, const GeomPtrs& g, cudaStream_t stream);
+// `model` non-NULL selects the raw-parameter mode (egs_forward_raw / egs_backward_raw): opacity,
+// covariance and SH rows are derived from the optimiser's raw tensors inside the kernel.
+int launch_preprocess_forward(const EgsForwardArgs& a, const EgsModelArgs* model, const GeomPtrs& g,
+                              cudaStream_t stream);
 int launch_scan_tiles(const GeomPtrs& g, int P, cudaStream_t stream, bool debug);
 // packed-word fast path (binning_packed.cu) and the shared range kernel
 bool packed_path_fits(int P, int W, int H);
@@ -253,8 +256,8 @@ int launch_blend_forward(const EgsForwardArgs& a, const GeomPtrs& g, const uint3
                          const ImagePtrs& im, cudaStream_t stream);
 int launch_blend_backward(const EgsBackwardArgs& a, const GeomPtrs& g, const uint32_t* point_list,
                           const ImagePtrs& im, const BackwardScratch& s, cudaStream_t stream);
-int launch_preprocess_backward(const EgsBackwardArgs& a, const GeomPtrs& g,
-                               const BackwardScratch& s, cudaStream_t stream);
+int launch_preprocess_backward(const EgsBackwardArgs& a, const EgsModelArgs* model, const EgsModelGrads* grads,
+                               const GeomPtrs& g, const BackwardScratch& s, cudaStream_t stream);
 int launch_mark_visible(int P, const float* means3D, const float* view, const float* proj,
                         unsigned char* present, cudaStream_t stream);
 

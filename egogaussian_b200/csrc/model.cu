@@ -14,50 +14,19 @@ namespace egs {
 
 constexpr int MODEL_THREADS = 256;
 
-struct ModelKernelArgs {
-  int P;
-  const float* scaling_raw;
-  const float* rotation_raw;
-  const float* opacity_raw;
-  float mod;
-  const int* is_object;
-  int which;
-  const float* accum_R;
-  const float* train_R;
-  int row0_copies;
-};
-
-// Selection of build_covariance_from_scaling_rotation_w_rot (gaussian_model.py:46-63). The mask
-// tensor is [P,1], so `nonzero(mask).squeeze()` holds (row, 0) PAIRS and indexing L with it touches
-// row 0 once per selected row as well: row 0 is rotated whenever any row is. `row0_copies` (> 0
-// when that happens) is how many index entries name row 0; the host counts it (cabi / binding).
-__device__ __forceinline__ bool row_selected(const ModelKernelArgs& a, int i) {
-  if (a.accum_R == nullptr && a.train_R == nullptr) return false;
-  if (i == 0 && a.row0_copies > 0) return true;
-  return a.is_object == nullptr || a.is_object[i] == a.which;
-}
+using ModelKernelArgs = RawModel;   // model_math.cuh: shared with the raw mode of the preprocess kernels
 
 __global__ void __launch_bounds__(MODEL_THREADS)
 model_forward_kernel(ModelKernelArgs a, float* __restrict__ cov3D, float* __restrict__ opacity) {
   __shared__ float s_rot[18];
-  if (threadIdx.x < 9) s_rot[threadIdx.x] = a.accum_R ? a.accum_R[threadIdx.x] : 0.f;
-  else if (threadIdx.x < 18) s_rot[threadIdx.x] = a.train_R ? a.train_R[threadIdx.x - 9] : 0.f;
+  stage_rotations(a, s_rot);
   __syncthreads();
   const int i = blockIdx.x * MODEL_THREADS + threadIdx.x;
   if (i >= a.P) return;
   if (opacity != nullptr) opacity[i] = sigmoid_fwd(a.opacity_raw[i]);
   if (cov3D == nullptr) return;
-  const float s_raw[3] = {a.scaling_raw[3 * i], a.scaling_raw[3 * i + 1], a.scaling_raw[3 * i + 2]};
-  const float4 q_raw = reinterpret_cast<const float4*>(a.rotation_raw)[i];
-  RawFrame f;
-  raw_frame(s_raw, q_raw, a.mod, f);
-  M33 L = frame_factor(f);
-  if (row_selected(a, i)) {
-    const M33 A = m33_load(s_rot), T = m33_load(s_rot + 9);
-    L = rotate_factor(L, a.accum_R ? &A : nullptr, a.train_R ? &T : nullptr, nullptr);
-  }
   float c[6];
-  factor_to_cov6(L, c);
+  raw_covariance(a, i, s_rot, c);
   float2* out = reinterpret_cast<float2*>(cov3D + 6 * (size_t)i);
   out[0] = make_float2(c[0], c[1]);
   out[1] = make_float2(c[2], c[3]);
@@ -71,8 +40,7 @@ model_backward_kernel(ModelKernelArgs a, const float* __restrict__ dL_dcov3D,
                       float* __restrict__ d_train_R) {
   __shared__ float s_rot[18];
   __shared__ float s_dT[MODEL_THREADS / 32][9];
-  if (threadIdx.x < 9) s_rot[threadIdx.x] = a.accum_R ? a.accum_R[threadIdx.x] : 0.f;
-  else if (threadIdx.x < 18) s_rot[threadIdx.x] = a.train_R ? a.train_R[threadIdx.x - 9] : 0.f;
+  stage_rotations(a, s_rot);
   __syncthreads();
   const int i = blockIdx.x * MODEL_THREADS + threadIdx.x;
   const bool live = i < a.P;
@@ -85,63 +53,19 @@ model_backward_kernel(ModelKernelArgs a, const float* __restrict__ dL_dcov3D,
     d_opacity_raw[i] = sigmoid_bwd(y, dL_dopacity[i]);
   }
   if (live && dL_dcov3D != nullptr) {
-    const float s_raw[3] = {a.scaling_raw[3 * i], a.scaling_raw[3 * i + 1], a.scaling_raw[3 * i + 2]};
-    const float4 q_raw = reinterpret_cast<const float4*>(a.rotation_raw)[i];
-    RawFrame f;
-    raw_frame(s_raw, q_raw, a.mod, f);
-    const M33 L0 = frame_factor(f);
     const float2* g2 = reinterpret_cast<const float2*>(dL_dcov3D + 6 * (size_t)i);
     const float2 g01 = g2[0], g23 = g2[1], g45 = g2[2];
     const float d6[6] = {g01.x, g01.y, g23.x, g23.y, g45.x, g45.y};
-    M33 dL0;
-    if (row_selected(a, i)) {
-      const M33 A = m33_load(s_rot), T = m33_load(s_rot + 9);
-      M33 mid;
-      const M33 Lf = rotate_factor(L0, a.accum_R ? &A : nullptr, a.train_R ? &T : nullptr, &mid);
-      M33 g = cov6_backward_to_factor(d6, Lf);
-      // every index entry that names this row receives the row's full gradient (index_put with
-      // duplicate indices): row 0 counts `row0_copies` times, any other selected row once
-      const float copies = (i == 0 && a.row0_copies > 0) ? (float)a.row0_copies : 1.f;
-#pragma unroll
-      for (int r = 0; r < 3; ++r)
-#pragma unroll
-        for (int c = 0; c < 3; ++c) g.m[r][c] *= copies;
-      if (a.train_R) {
-        const M33 gT = m33_mult(g, mid);   // dT = g mid^T
-#pragma unroll
-        for (int k = 0; k < 9; ++k) dT[k] = gT.m[k / 3][k % 3];
-        g = m33_tmul(T, g);
-      }
-      if (a.accum_R) g = m33_tmul(A, g);
-      dL0 = g;
-    } else {
-      dL0 = cov6_backward_to_factor(d6, L0);
-    }
     float ds[3], dq[4];
-    frame_backward(f, dL0, a.mod, ds, dq);
+    raw_covariance_backward(a, i, s_rot, d6, ds, dq, dT);
     d_scaling_raw[3 * i] = ds[0];
     d_scaling_raw[3 * i + 1] = ds[1];
     d_scaling_raw[3 * i + 2] = ds[2];
     reinterpret_cast<float4*>(d_rotation_raw)[i] = make_float4(dq[0], dq[1], dq[2], dq[3]);
   }
 
-  if (d_train_R != nullptr && a.train_R != nullptr) {   // block-reduce the 3x3 pose gradient
-    const unsigned lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-#pragma unroll
-    for (int k = 0; k < 9; ++k) {
-      float v = dT[k];
-#pragma unroll
-      for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
-      if (lane == 0) s_dT[warp][k] = v;
-    }
-    __syncthreads();
-    if (threadIdx.x < 9) {
-      float v = 0.f;
-#pragma unroll
-      for (int w = 0; w < MODEL_THREADS / 32; ++w) v += s_dT[w][threadIdx.x];
-      if (v != 0.f) atomicAdd(d_train_R + threadIdx.x, v);
-    }
-  }
+  // block-reduce the 3x3 pose gradient (every thread takes part)
+  if (d_train_R != nullptr && a.train_R != nullptr) reduce_pose_gradient(dT, s_dT, d_train_R);
 }
 
 // get_features: cat(_features_dc [P,1,3], _features_rest [P,M-1,3]) along dim 1, and its backward
@@ -196,20 +120,7 @@ static int check_model(const EgsModelArgs* m, const char* who) {
   return EGS_OK;
 }
 
-static ModelKernelArgs kernel_args(const EgsModelArgs* m) {
-  ModelKernelArgs k;
-  k.P = m->P;
-  k.scaling_raw = m->scaling_raw;
-  k.rotation_raw = m->rotation_raw;
-  k.opacity_raw = m->opacity_raw;
-  k.mod = m->scale_modifier;
-  k.is_object = m->is_object;
-  k.which = m->which_object;
-  k.accum_R = m->accum_R;
-  k.train_R = m->train_R;
-  k.row0_copies = (m->accum_R || m->train_R) ? m->row0_copies : 0;
-  return k;
-}
+static ModelKernelArgs kernel_args(const EgsModelArgs* m) { return raw_model_from(m); }
 
 static bool aligned_to(const void* p, uintptr_t a) { return (reinterpret_cast<uintptr_t>(p) & (a - 1)) == 0; }
 

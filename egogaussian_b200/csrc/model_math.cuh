@@ -19,6 +19,7 @@
 // tolerance-checked (tests/test_model_gpu.py).
 #pragma once
 #include <cuda_runtime.h>
+#include "../../include/egs_rasterizer.h"
 
 namespace egs {
 
@@ -172,6 +173,161 @@ __device__ __forceinline__ void frame_backward(const RawFrame& f, const M33& dL0
   const float inv = 1.f / f.norm;
 #pragma unroll
   for (int k = 0; k < 4; ++k) dq_raw[k] = (dq[k] - f.q[k] * qdq) * inv;
+}
+
+// Device view of EgsModelArgs, passed to kernels by value.
+struct RawModel {
+  int P;
+  const float* scaling_raw;
+  const float* rotation_raw;
+  const float* opacity_raw;
+  const float* features_dc;
+  const float* features_rest;
+  float mod;
+  const int* is_object;
+  int which;
+  const float* accum_R;
+  const float* train_R;
+  int row0_copies;
+};
+
+inline RawModel raw_model_from(const EgsModelArgs* m) {
+  RawModel k;
+  k.P = m->P;
+  k.scaling_raw = m->scaling_raw;
+  k.rotation_raw = m->rotation_raw;
+  k.opacity_raw = m->opacity_raw;
+  k.features_dc = m->features_dc;
+  k.features_rest = m->features_rest;
+  k.mod = m->scale_modifier;
+  k.is_object = m->is_object;
+  k.which = m->which_object;
+  k.accum_R = m->accum_R;
+  k.train_R = m->train_R;
+  k.row0_copies = (m->accum_R || m->train_R) ? m->row0_copies : 0;
+  return k;
+}
+
+// Selection of build_covariance_from_scaling_rotation_w_rot (gaussian_model.py:46-63). The mask
+// tensor is [P,1], so `nonzero(mask).squeeze()` holds (row, 0) PAIRS and indexing L with it touches
+// row 0 once per selected row as well: row 0 is rotated whenever any row is. `row0_copies` (> 0
+// when that happens) is how many index entries name row 0; the host counts it (cabi / binding).
+__device__ __forceinline__ bool row_selected(const RawModel& a, int i) {
+  if (a.accum_R == nullptr && a.train_R == nullptr) return false;
+  if (i == 0 && a.row0_copies > 0) return true;
+  return a.is_object == nullptr || a.is_object[i] == a.which;
+}
+
+// The two optional 3x3 rotations, staged once per CTA: s_rot[0..9) = accum_R, [9..18) = train_R.
+__device__ __forceinline__ void stage_rotations(const RawModel& a, float* s_rot) {
+  if (threadIdx.x < 9) s_rot[threadIdx.x] = a.accum_R ? a.accum_R[threadIdx.x] : 0.f;
+  else if (threadIdx.x < 18) s_rot[threadIdx.x] = a.train_R ? a.train_R[threadIdx.x - 9] : 0.f;
+}
+
+// Forward of one row: frame, final factor, six covariance entries.
+__device__ __forceinline__ void raw_covariance(const RawModel& a, int i, const float* s_rot, float cov6[6]) {
+  const float s_raw[3] = {a.scaling_raw[3 * i], a.scaling_raw[3 * i + 1], a.scaling_raw[3 * i + 2]};
+  const float4 q_raw = reinterpret_cast<const float4*>(a.rotation_raw)[i];
+  RawFrame f;
+  raw_frame(s_raw, q_raw, a.mod, f);
+  M33 L = frame_factor(f);
+  if (row_selected(a, i)) {
+    const M33 A = m33_load(s_rot), T = m33_load(s_rot + 9);
+    L = rotate_factor(L, a.accum_R ? &A : nullptr, a.train_R ? &T : nullptr, nullptr);
+  }
+  factor_to_cov6(L, cov6);
+}
+
+// Backward of one row: d6 = dL/d(six covariance entries) -> raw scaling / quaternion gradients and
+// this row's contribution dT[9] to dL/d train_R (zero when the row is not rotated by train_R).
+__device__ __forceinline__ void raw_covariance_backward(const RawModel& a, int i, const float* s_rot,
+                                                        const float d6[6], float ds[3], float dq[4], float dT[9]) {
+  const float s_raw[3] = {a.scaling_raw[3 * i], a.scaling_raw[3 * i + 1], a.scaling_raw[3 * i + 2]};
+  const float4 q_raw = reinterpret_cast<const float4*>(a.rotation_raw)[i];
+  RawFrame f;
+  raw_frame(s_raw, q_raw, a.mod, f);
+  const M33 L0 = frame_factor(f);
+  M33 dL0;
+  if (row_selected(a, i)) {
+    const M33 A = m33_load(s_rot), T = m33_load(s_rot + 9);
+    M33 mid;
+    const M33 Lf = rotate_factor(L0, a.accum_R ? &A : nullptr, a.train_R ? &T : nullptr, &mid);
+    M33 g = cov6_backward_to_factor(d6, Lf);
+    // every index entry that names this row receives the row's full gradient (index_put with
+    // duplicate indices): row 0 counts `row0_copies` times, any other selected row once
+    const float copies = (i == 0 && a.row0_copies > 0) ? (float)a.row0_copies : 1.f;
+#pragma unroll
+    for (int r = 0; r < 3; ++r)
+#pragma unroll
+      for (int c = 0; c < 3; ++c) g.m[r][c] *= copies;
+    if (a.train_R) {
+      const M33 gT = m33_mult(g, mid);   // dT = g mid^T
+#pragma unroll
+      for (int k = 0; k < 9; ++k) dT[k] = gT.m[k / 3][k % 3];
+      g = m33_tmul(T, g);
+    }
+    if (a.accum_R) g = m33_tmul(A, g);
+    dL0 = g;
+  } else {
+    dL0 = cov6_backward_to_factor(d6, L0);
+  }
+  frame_backward(f, dL0, a.mod, ds, dq);
+}
+
+// Sum dT over the CTA and add it to d_train_R (device [9]) with nine atomics. Every thread of the
+// CTA must call this. `s_part` is [blockDim.x / 32][9] floats of shared memory.
+__device__ __forceinline__ void reduce_pose_gradient(const float dT[9], float (*s_part)[9], float* d_train_R) {
+  const unsigned lane = threadIdx.x & 31, warp = threadIdx.x >> 5, warps = blockDim.x >> 5;
+#pragma unroll
+  for (int k = 0; k < 9; ++k) {
+    float v = dT[k];
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+    if (lane == 0) s_part[warp][k] = v;
+  }
+  __syncthreads();
+  if (threadIdx.x < 9) {
+    float v = 0.f;
+    for (unsigned w = 0; w < warps; ++w) v += s_part[w][threadIdx.x];
+    if (v != 0.f) atomicAdd(d_train_R + threadIdx.x, v);
+  }
+}
+
+// Warp-wide copy between one contiguous global run of `count` floats, holding rows of `width`
+// floats back to back, and a pitched shared-memory tile: element e of the run is
+// tile[(e / width) * pitch + col0 + e % width]. Used to stage the split features_dc / features_rest
+// rows (width 3 and 3M - 3) next to each other in one SH row per Gaussian, and to write the
+// gradient rows back. float4 global accesses when the run is 16-byte aligned, all loads of an
+// unrolled group issued before their stores (a one-load-per-iteration loop exposes the full DRAM
+// latency 45 times per warp); e / width by reciprocal multiplication, exact for e < 2^20 / width.
+template <bool TO_TILE>
+__device__ __forceinline__ void warp_rows_copy(float* tile, int pitch, int col0, int width, float* run, int count,
+                                               unsigned lane) {
+  const uint32_t inv = ((1u << 20) + (uint32_t)width - 1u) / (uint32_t)width;
+  auto slot = [&](int e) -> float& {
+    const int r = (int)(((uint32_t)e * inv) >> 20);
+    return tile[r * pitch + col0 + (e - r * width)];
+  };
+  int done = 0;
+  if ((reinterpret_cast<uintptr_t>(run) & 15u) == 0) {
+    const int nvec = count >> 2;
+    float4* run4 = reinterpret_cast<float4*>(run);
+#pragma unroll 4
+    for (int f = (int)lane; f < nvec; f += 32) {
+      if (TO_TILE) {
+        const float4 v = __ldg(run4 + f);
+        slot(4 * f) = v.x; slot(4 * f + 1) = v.y; slot(4 * f + 2) = v.z; slot(4 * f + 3) = v.w;
+      } else {
+        run4[f] = make_float4(slot(4 * f), slot(4 * f + 1), slot(4 * f + 2), slot(4 * f + 3));
+      }
+    }
+    done = nvec << 2;
+  }
+#pragma unroll 4
+  for (int e = done + (int)lane; e < count; e += 32) {
+    if (TO_TILE) slot(e) = __ldg(run + e);
+    else run[e] = slot(e);
+  }
 }
 
 // torch.sigmoid and its autograd formula grad * (1 - y) * y

@@ -7,6 +7,7 @@
 // (column-major products summed left to right, double-precision ndc->pixel) and the file is
 // compiled with nvcc's default -fmad=true and no fast-math, like the reference.
 #include "common.cuh"
+#include "model_math.cuh"
 
 namespace egs {
 
@@ -112,9 +113,15 @@ constexpr int PF_THREADS = 128;
 constexpr int PF_SH_ROW = 48;
 constexpr int PF_SH_PITCH = 49;
 
-template <bool STAGED>
+// SH_MODE: 0 = every thread reads its own row from global memory, 1 = rows staged with float4
+// loads from one contiguous [P,16,3] tensor, 2 = rows staged from the split features_dc /
+// features_rest tensors of the raw-parameter mode (any M; get_features' concat never materialises).
+// `raw` carries the optimiser's raw tensors: when raw.scaling_raw / raw.opacity_raw are set the
+// covariance and the opacity are derived here (model_math.cuh) instead of being read.
+// RAW is a template parameter so that the ordinary instantiations carry none of that code.
+template <int SH_MODE, bool RAW>
 __global__ void __launch_bounds__(PF_THREADS)
-preprocess_forward_kernel(int P, int D, int M, const float* __restrict__ means3D,
+preprocess_forward_kernel(RawModel raw, int P, int D, int M, const float* __restrict__ means3D,
                           const float* __restrict__ scales, float scale_modifier,
                           const float* __restrict__ rotations, const float* __restrict__ opacities,
                           const float* __restrict__ shs, const float* __restrict__ cov3D_precomp,
@@ -133,12 +140,29 @@ preprocess_forward_kernel(int P, int D, int M, const float* __restrict__ means3D
     s_proj[threadIdx.x] = projmatrix[threadIdx.x];
   }
   if (threadIdx.x < 3) s_cam[threadIdx.x] = campos[threadIdx.x];
-  __shared__ float s_sh[STAGED ? (PF_THREADS / 32) * 32 * PF_SH_PITCH : 1];
+  __shared__ float s_sh[SH_MODE != 0 ? (PF_THREADS / 32) * 32 * PF_SH_PITCH : 1];
+  __shared__ float s_rot[RAW ? 18 : 1];
+  if (RAW) stage_rotations(raw, s_rot);
   __syncthreads();
 
   const int idx = blockIdx.x * blockDim.x + threadIdx.x;
   const float* sh_row = nullptr;
-  if (STAGED) {
+  if (SH_MODE == 2) {
+    const unsigned lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int first = blockIdx.x * blockDim.x + warp * 32;
+    const int rows = min(32, P - first);
+    float* tile = s_sh + warp * 32 * PF_SH_PITCH;
+    if (rows > 0) {
+      const int wrest = 3 * M - 3;
+      warp_rows_copy<true>(tile, PF_SH_PITCH, 0, 3, const_cast<float*>(raw.features_dc) + (size_t)first * 3,
+                           rows * 3, lane);
+      if (wrest > 0)
+        warp_rows_copy<true>(tile, PF_SH_PITCH, 3, wrest,
+                             const_cast<float*>(raw.features_rest) + (size_t)first * wrest, rows * wrest, lane);
+    }
+    __syncwarp();
+    sh_row = tile + lane * PF_SH_PITCH;
+  } else if (SH_MODE == 1) {
     const unsigned lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const int first = blockIdx.x * blockDim.x + warp * 32;
     const int rows = min(32, P - first);
@@ -173,7 +197,9 @@ preprocess_forward_kernel(int P, int D, int M, const float* __restrict__ means3D
     const float3 p_proj = make_float3(p_hom.x * p_w, p_hom.y * p_w, p_hom.z * p_w);
 
     float cov6[6];
-    if (cov3D_precomp != nullptr) {
+    if (RAW) {
+      raw_covariance(raw, idx, s_rot, cov6);
+    } else if (cov3D_precomp != nullptr) {
 #pragma unroll
       for (int k = 0; k < 6; ++k) cov6[k] = cov3D_precomp[6 * idx + k];
     } else {
@@ -209,7 +235,8 @@ preprocess_forward_kernel(int P, int D, int M, const float* __restrict__ means3D
         }
         depths[idx] = p_view.z;
         means2D[idx] = point_image;
-        conic_opacity[idx] = make_float4(conic.x, conic.y, conic.z, opacities[idx]);
+        const float opacity = RAW ? sigmoid_fwd(raw.opacity_raw[idx]) : opacities[idx];
+        conic_opacity[idx] = make_float4(conic.x, conic.y, conic.z, opacity);
         rgb_depth[idx] = make_float4(rgb.x, rgb.y, rgb.z, p_view.z);
         radius_out = (int)my_radius;
         tiles_out = n_tiles;
@@ -230,23 +257,32 @@ mark_visible_kernel(int P, const float* __restrict__ means3D, const float* __res
   present[idx] = pv.z > 0.2f ? 1 : 0;
 }
 
-int launch_preprocess_forward(const EgsForwardArgs& a, const GeomPtrs& g, cudaStream_t stream) {
+int launch_preprocess_forward(const EgsForwardArgs& a, const EgsModelArgs* model, const GeomPtrs& g,
+                              cudaStream_t stream) {
   const int P = a.P;
   const float focal_y = a.height / (2.0f * a.tan_fovy);
   const float focal_x = a.width / (2.0f * a.tan_fovx);
   const int blocks = (P + PF_THREADS - 1) / PF_THREADS;
   StageTimer timer(stream, ST_PREPROCESS);
   const bool staged = a.shs != nullptr && a.sh_coeffs == 16 && (reinterpret_cast<uintptr_t>(a.shs) & 15u) == 0;
+  RawModel raw{};
+  if (model != nullptr) raw = raw_model_from(model);
+  const bool split = model != nullptr && a.colors_precomp == nullptr;
+  const int sh_coeffs = split ? model->sh_coeffs : a.sh_coeffs;
 #define EGS_PF_ARGS                                                                                     \
-  P, a.sh_degree, a.sh_coeffs, a.means3D, a.scales, a.scale_modifier, a.rotations, a.opacities, a.shs,  \
+  raw, P, a.sh_degree, sh_coeffs, a.means3D, a.scales, a.scale_modifier, a.rotations, a.opacities, a.shs,  \
       a.cov3D_precomp, a.colors_precomp, a.viewmatrix, a.projmatrix, a.campos, a.width, a.height,       \
       a.tan_fovx, a.tan_fovy, focal_x, focal_y, tiles_x(a.width), tiles_y(a.height), a.radii,           \
       g.means2D, g.depths, g.conic_opacity, g.rgb_depth, g.clamped, g.tiles_touched, a.prefiltered,     \
       nullptr
-  if (staged)
-    preprocess_forward_kernel<true><<<blocks, PF_THREADS, 0, stream>>>(EGS_PF_ARGS);
+  if (split)
+    preprocess_forward_kernel<2, true><<<blocks, PF_THREADS, 0, stream>>>(EGS_PF_ARGS);
+  else if (model != nullptr)
+    preprocess_forward_kernel<0, true><<<blocks, PF_THREADS, 0, stream>>>(EGS_PF_ARGS);
+  else if (staged)
+    preprocess_forward_kernel<1, false><<<blocks, PF_THREADS, 0, stream>>>(EGS_PF_ARGS);
   else
-    preprocess_forward_kernel<false><<<blocks, PF_THREADS, 0, stream>>>(EGS_PF_ARGS);
+    preprocess_forward_kernel<0, false><<<blocks, PF_THREADS, 0, stream>>>(EGS_PF_ARGS);
 #undef EGS_PF_ARGS
   EGS_AFTER_LAUNCH(stream, a.debug);
   return EGS_OK;

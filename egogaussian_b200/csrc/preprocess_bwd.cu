@@ -11,6 +11,7 @@
 // Gaussians, so none of the outputs needs a prior memset (the reference zero-fills ten tensors,
 // 304 B per Gaussian at SH degree 3, rasterize_points.cu:158-167).
 #include "common.cuh"
+#include "model_math.cuh"
 
 namespace egs {
 
@@ -175,6 +176,7 @@ __device__ __forceinline__ void cov3d_recompute(const float3 s, float mod, const
 // Everything one Gaussian needs. `sh_in` / `sh_out` are this Gaussian's rows of SH coefficients
 // and of their gradients; they may be the same shared-memory row (staged mode) because every
 // coefficient is read before its gradient is written.
+template <bool RAW>
 __device__ __forceinline__ void
 gaussian_backward(int idx, int D, int M, const float* __restrict__ means3D, const int* __restrict__ radii,
                   const float* sh_in, float* sh_out, bool has_sh,
@@ -185,7 +187,10 @@ gaussian_backward(int idx, int D, int M, const float* __restrict__ means3D, cons
                   float tan_fovy, const float4* __restrict__ acc, float* __restrict__ dL_dmeans2D,
                   float* __restrict__ dL_dcolors, float* __restrict__ dL_dopacity,
                   float* __restrict__ dL_dmeans3D, float* __restrict__ dL_dcov3D,
-                  float* __restrict__ dL_dscales, float* __restrict__ dL_drot) {
+                  float* __restrict__ dL_dscales, float* __restrict__ dL_drot,
+                  // raw-parameter mode (egs_backward_raw): gradients go to the raw tensors
+                  const RawModel& raw, const float* s_rot, const EgsModelGrads& rg, float* dT) {
+  constexpr bool raw_geom = RAW;
   if (!(radii[idx] > 0)) {
     // culled: every gradient is zero
 #pragma unroll
@@ -193,19 +198,24 @@ gaussian_backward(int idx, int D, int M, const float* __restrict__ means3D, cons
       dL_dmeans2D[3 * idx + k] = 0.f;
       dL_dmeans3D[3 * idx + k] = 0.f;
     }
-    dL_dopacity[idx] = 0.f;
+    if (RAW) rg.d_opacity_raw[idx] = 0.f;
+    else dL_dopacity[idx] = 0.f;
     if (colors_precomp != nullptr) {
 #pragma unroll
       for (int k = 0; k < 3; ++k) dL_dcolors[3 * idx + k] = 0.f;
     }
-    if (cov3D_precomp != nullptr) {
+    if (raw_geom) {
+#pragma unroll
+      for (int k = 0; k < 3; ++k) rg.d_scaling_raw[3 * idx + k] = 0.f;
+      reinterpret_cast<float4*>(rg.d_rotation_raw)[idx] = make_float4(0.f, 0.f, 0.f, 0.f);
+    } else if (cov3D_precomp != nullptr) {
 #pragma unroll
       for (int k = 0; k < 6; ++k) dL_dcov3D[6 * idx + k] = 0.f;
     }
     if (has_sh) {
       for (int k = 0; k < 3 * M; ++k) sh_out[k] = 0.f;
     }
-    if (scales != nullptr) {
+    if (scales != nullptr && !raw_geom) {
 #pragma unroll
       for (int k = 0; k < 3; ++k) dL_dscales[3 * idx + k] = 0.f;
       reinterpret_cast<float4*>(dL_drot)[idx] = make_float4(0.f, 0.f, 0.f, 0.f);
@@ -219,7 +229,8 @@ gaussian_backward(int idx, int D, int M, const float* __restrict__ means3D, cons
   dL_dmeans2D[3 * idx + 0] = a0.x;
   dL_dmeans2D[3 * idx + 1] = a0.y;
   dL_dmeans2D[3 * idx + 2] = 0.f;
-  dL_dopacity[idx] = a0.z;
+  if (RAW) rg.d_opacity_raw[idx] = sigmoid_bwd(sigmoid_fwd(raw.opacity_raw[idx]), a0.z);
+  else dL_dopacity[idx] = a0.z;
   const float dL_ddepth = a0.w;
 
   const float3 mean = make_float3(means3D[3 * idx], means3D[3 * idx + 1], means3D[3 * idx + 2]);
@@ -228,7 +239,9 @@ gaussian_backward(int idx, int D, int M, const float* __restrict__ means3D, cons
   float cov6[6];
   float3 scl = make_float3(0.f, 0.f, 0.f);
   float4 rot = make_float4(0.f, 0.f, 0.f, 0.f);
-  if (cov3D_precomp != nullptr) {
+  if (raw_geom) {
+    raw_covariance(raw, idx, s_rot, cov6);
+  } else if (cov3D_precomp != nullptr) {
 #pragma unroll
     for (int k = 0; k < 6; ++k) cov6[k] = cov3D_precomp[6 * idx + k];
   } else {
@@ -342,7 +355,14 @@ gaussian_backward(int idx, int D, int M, const float* __restrict__ means3D, cons
   dL_dmeans3D[3 * idx + 2] = dmean.z;
 
   // ---- covariance parametrisation -------------------------------------------------------------
-  if (cov3D_precomp != nullptr) {
+  if (raw_geom) {
+    float ds[3], dq[4];
+    raw_covariance_backward(raw, idx, s_rot, dcov, ds, dq, dT);
+    rg.d_scaling_raw[3 * idx + 0] = ds[0];
+    rg.d_scaling_raw[3 * idx + 1] = ds[1];
+    rg.d_scaling_raw[3 * idx + 2] = ds[2];
+    reinterpret_cast<float4*>(rg.d_rotation_raw)[idx] = make_float4(dq[0], dq[1], dq[2], dq[3]);
+  } else if (cov3D_precomp != nullptr) {
 #pragma unroll
     for (int k = 0; k < 6; ++k) dL_dcov3D[6 * idx + k] = dcov[k];
   } else {
@@ -366,9 +386,12 @@ constexpr int PB_WARPS = PB_THREADS / 32;
 constexpr int SH_ROW = 48;        // 16 coefficients x RGB
 constexpr int SH_PITCH = 49;      // odd pitch: a lane walking its own row is conflict-free
 
-template <bool STAGED>
-__global__ void __launch_bounds__(PB_THREADS)
-preprocess_backward_kernel(int P, int D, int M, const float* __restrict__ means3D,
+// SH_MODE as in the forward kernel: 0 = rows straight from global memory, 1 = staged float4 rows of
+// one contiguous [P,16,3] tensor, 2 = rows staged from / written back to the split features_dc /
+// features_rest tensors of the raw-parameter mode.
+template <int SH_MODE, bool RAW>
+__global__ void __launch_bounds__(PB_THREADS, 6)
+preprocess_backward_kernel(RawModel raw, EgsModelGrads rg, int P, int D, int M, const float* __restrict__ means3D,
                            const int* __restrict__ radii, const float* __restrict__ shs,
                            const unsigned char* __restrict__ clamped,
                            const float* __restrict__ scales, const float* __restrict__ rotations,
@@ -382,59 +405,86 @@ preprocess_backward_kernel(int P, int D, int M, const float* __restrict__ means3
                            float* __restrict__ dL_dcov3D, float* __restrict__ dL_dsh,
                            float* __restrict__ dL_dscales, float* __restrict__ dL_drot) {
   __shared__ float view[16], proj[16], s_cam[3];
-  __shared__ float s_sh[STAGED ? PB_WARPS * 32 * SH_PITCH : 1];
+  __shared__ float s_sh[SH_MODE != 0 ? PB_WARPS * 32 * SH_PITCH : 1];
+  __shared__ float s_rot[RAW ? 18 : 1];
+  __shared__ float s_dT[RAW ? PB_WARPS : 1][9];
   if (threadIdx.x < 16) {
     view[threadIdx.x] = viewmatrix[threadIdx.x];
     proj[threadIdx.x] = projmatrix[threadIdx.x];
   }
   if (threadIdx.x < 3) s_cam[threadIdx.x] = campos[threadIdx.x];
+  if (RAW) stage_rotations(raw, s_rot);
   __syncthreads();
   const int idx = blockIdx.x * blockDim.x + threadIdx.x;
   const unsigned lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-  const bool has_sh = shs != nullptr;
+  float dT[RAW ? 9 : 1];
+#pragma unroll
+  for (int k = 0; k < (RAW ? 9 : 1); ++k) dT[k] = 0.f;
 
-  if (STAGED) {
-    // rows [first, first + rows) of this warp, as one contiguous run of rows * 48 floats
+#define EGS_GB_TAIL                                                                                          \
+  clamped, scales, rotations, cov3D_precomp, colors_precomp, scale_modifier, view, proj, s_cam, h_x, h_y,     \
+      tan_fovx, tan_fovy, acc, dL_dmeans2D, dL_dcolors, dL_dopacity, dL_dmeans3D, dL_dcov3D, dL_dscales,      \
+      dL_drot, raw, s_rot, rg, dT
+
+  if (SH_MODE != 0) {
+    // rows [first, first + rows) of this warp
     const int first = blockIdx.x * blockDim.x + warp * 32;
     const int rows = min(32, P - first);
     float* tile = s_sh + warp * 32 * SH_PITCH;
+    const int wrest = 3 * M - 3;
     if (rows > 0) {
-      const float4* src = reinterpret_cast<const float4*>(shs + (size_t)first * SH_ROW);
-      for (int f = lane; f < rows * (SH_ROW / 4); f += 32) {
-        const float4 v = __ldg(src + f);
-        const int row = f / (SH_ROW / 4), k = (f % (SH_ROW / 4)) * 4;
-        float* d = tile + row * SH_PITCH + k;
-        d[0] = v.x; d[1] = v.y; d[2] = v.z; d[3] = v.w;
+      if (SH_MODE == 1) {   // one contiguous run of rows * 48 floats
+        const float4* src = reinterpret_cast<const float4*>(shs + (size_t)first * SH_ROW);
+        for (int f = lane; f < rows * (SH_ROW / 4); f += 32) {
+          const float4 v = __ldg(src + f);
+          const int row = f / (SH_ROW / 4), k = (f % (SH_ROW / 4)) * 4;
+          float* d = tile + row * SH_PITCH + k;
+          d[0] = v.x; d[1] = v.y; d[2] = v.z; d[3] = v.w;
+        }
+      } else {              // two contiguous runs: rows * 3 and rows * (3M - 3) floats
+        warp_rows_copy<true>(tile, SH_PITCH, 0, 3, const_cast<float*>(raw.features_dc) + (size_t)first * 3,
+                             rows * 3, lane);
+        if (wrest > 0)
+          warp_rows_copy<true>(tile, SH_PITCH, 3, wrest,
+                               const_cast<float*>(raw.features_rest) + (size_t)first * wrest, rows * wrest, lane);
       }
     }
     __syncwarp();
     if (idx < P) {
       float* row = tile + lane * SH_PITCH;
-      gaussian_backward(idx, D, M, means3D, radii, row, row, true, clamped, scales, rotations, cov3D_precomp,
-                        colors_precomp, scale_modifier, view, proj, s_cam, h_x, h_y, tan_fovx, tan_fovy, acc,
-                        dL_dmeans2D, dL_dcolors, dL_dopacity, dL_dmeans3D, dL_dcov3D, dL_dscales, dL_drot);
+      gaussian_backward<RAW>(idx, D, M, means3D, radii, row, row, true, EGS_GB_TAIL);
     }
     __syncwarp();
     if (rows > 0) {
-      float4* dst = reinterpret_cast<float4*>(dL_dsh + (size_t)first * SH_ROW);
-      for (int f = lane; f < rows * (SH_ROW / 4); f += 32) {
-        const int row = f / (SH_ROW / 4), k = (f % (SH_ROW / 4)) * 4;
-        const float* srow = tile + row * SH_PITCH + k;
-        dst[f] = make_float4(srow[0], srow[1], srow[2], srow[3]);
+      if (SH_MODE == 1) {
+        float4* dst = reinterpret_cast<float4*>(dL_dsh + (size_t)first * SH_ROW);
+        for (int f = lane; f < rows * (SH_ROW / 4); f += 32) {
+          const int row = f / (SH_ROW / 4), k = (f % (SH_ROW / 4)) * 4;
+          const float* srow = tile + row * SH_PITCH + k;
+          dst[f] = make_float4(srow[0], srow[1], srow[2], srow[3]);
+        }
+      } else {
+        warp_rows_copy<false>(tile, SH_PITCH, 0, 3, rg.d_features_dc + (size_t)first * 3, rows * 3, lane);
+        if (wrest > 0)
+          warp_rows_copy<false>(tile, SH_PITCH, 3, wrest, rg.d_features_rest + (size_t)first * wrest, rows * wrest,
+                                lane);
       }
     }
-  } else {
-    if (idx >= P) return;
+  } else if (idx < P) {
+    const bool has_sh = shs != nullptr;
     const size_t off = (size_t)idx * M * 3;
-    gaussian_backward(idx, D, M, means3D, radii, has_sh ? shs + off : nullptr, has_sh ? dL_dsh + off : nullptr,
-                      has_sh, clamped, scales, rotations, cov3D_precomp, colors_precomp, scale_modifier, view,
-                      proj, s_cam, h_x, h_y, tan_fovx, tan_fovy, acc, dL_dmeans2D, dL_dcolors, dL_dopacity,
-                      dL_dmeans3D, dL_dcov3D, dL_dscales, dL_drot);
+    gaussian_backward<RAW>(idx, D, M, means3D, radii, has_sh ? shs + off : nullptr, has_sh ? dL_dsh + off : nullptr,
+                      has_sh, EGS_GB_TAIL);
+  }
+#undef EGS_GB_TAIL
+  // dL/d train_R: every thread of the CTA takes part (no early return above)
+  if (RAW) {
+    if (raw.train_R != nullptr && rg.d_train_R != nullptr) reduce_pose_gradient(dT, s_dT, rg.d_train_R);
   }
 }
 
-int launch_preprocess_backward(const EgsBackwardArgs& a, const GeomPtrs& g,
-                               const BackwardScratch& s, cudaStream_t stream) {
+int launch_preprocess_backward(const EgsBackwardArgs& a, const EgsModelArgs* model, const EgsModelGrads* grads,
+                               const GeomPtrs& g, const BackwardScratch& s, cudaStream_t stream) {
   const float focal_y = a.height / (2.0f * a.tan_fovy);
   const float focal_x = a.width / (2.0f * a.tan_fovx);
   StageTimer timer(stream, ST_PREPROCESS_BWD);
@@ -442,15 +492,29 @@ int launch_preprocess_backward(const EgsBackwardArgs& a, const GeomPtrs& g,
   const bool staged = a.shs != nullptr && a.sh_coeffs == 16 &&
                       (reinterpret_cast<uintptr_t>(a.shs) & 15u) == 0 &&
                       (reinterpret_cast<uintptr_t>(a.dL_dsh) & 15u) == 0;
+  RawModel raw{};
+  EgsModelGrads rg{};
+  if (model != nullptr) {
+    raw = raw_model_from(model);
+    rg = *grads;
+    if (rg.d_train_R != nullptr && raw.train_R != nullptr)
+      EGS_CUDA_TRY(cudaMemsetAsync(rg.d_train_R, 0, 9 * sizeof(float), stream));
+  }
+  const bool split = model != nullptr && a.colors_precomp == nullptr;
+  const int sh_coeffs = split ? model->sh_coeffs : a.sh_coeffs;
 #define EGS_PB_ARGS                                                                                   \
-  a.P, a.sh_degree, a.sh_coeffs, a.means3D, a.radii, a.shs, g.clamped, a.scales, a.rotations,         \
+  raw, rg, a.P, a.sh_degree, sh_coeffs, a.means3D, a.radii, a.shs, g.clamped, a.scales, a.rotations,         \
       a.cov3D_precomp, a.colors_precomp, a.scale_modifier, a.viewmatrix, a.projmatrix, a.campos,      \
       focal_x, focal_y, a.tan_fovx, a.tan_fovy, s.acc, a.dL_dmeans2D, a.dL_dcolors, a.dL_dopacity,    \
       a.dL_dmeans3D, a.dL_dcov3D, a.dL_dsh, a.dL_dscales, a.dL_drotations
-  if (staged)
-    preprocess_backward_kernel<true><<<blocks, PB_THREADS, 0, stream>>>(EGS_PB_ARGS);
+  if (split)
+    preprocess_backward_kernel<2, true><<<blocks, PB_THREADS, 0, stream>>>(EGS_PB_ARGS);
+  else if (model != nullptr)
+    preprocess_backward_kernel<0, true><<<blocks, PB_THREADS, 0, stream>>>(EGS_PB_ARGS);
+  else if (staged)
+    preprocess_backward_kernel<1, false><<<blocks, PB_THREADS, 0, stream>>>(EGS_PB_ARGS);
   else
-    preprocess_backward_kernel<false><<<blocks, PB_THREADS, 0, stream>>>(EGS_PB_ARGS);
+    preprocess_backward_kernel<0, false><<<blocks, PB_THREADS, 0, stream>>>(EGS_PB_ARGS);
 #undef EGS_PB_ARGS
   EGS_AFTER_LAUNCH(stream, a.debug);
   return EGS_OK;

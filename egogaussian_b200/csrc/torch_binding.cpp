@@ -415,6 +415,144 @@ std::vector<torch::Tensor> model_backward(
   return {ds, dq, dop, ddc, drest, dT};
 }
 
+// ---- rasterizer on raw parameters (egs_forward_raw / egs_backward_raw) -------------------------------
+// returns (num_rendered, color, depth, alpha, radii, geomBuffer, binningBuffer, imgBuffer)
+std::tuple<int, torch::Tensor, torch::Tensor, torch::Tensor, torch::Tensor, torch::Tensor, torch::Tensor,
+           torch::Tensor>
+rasterize_gaussians_raw(const torch::Tensor& background, const torch::Tensor& means3D, const torch::Tensor& colors,
+                        const torch::Tensor& scaling_raw, const torch::Tensor& rotation_raw,
+                        const torch::Tensor& opacity_raw, const torch::Tensor& features_dc,
+                        const torch::Tensor& features_rest, double scale_modifier, const torch::Tensor& is_object,
+                        int64_t which_object, const torch::Tensor& accum_R, const torch::Tensor& train_R,
+                        int64_t row0_copies, const torch::Tensor& viewmatrix, const torch::Tensor& projmatrix,
+                        double tan_fovx, double tan_fovy, int64_t image_height, int64_t image_width, int64_t degree,
+                        const torch::Tensor& campos, bool prefiltered, bool debug) {
+  TORCH_CHECK(means3D.is_cuda() && means3D.ndimension() == 2 && means3D.size(1) == 3,
+              "means3D must be a CUDA tensor (num_points, 3); there is no CPU path");
+  const torch::Device dev = means3D.device();
+  c10::cuda::CUDAGuard guard(dev);
+  const int P = (int)means3D.size(0);
+  const int H = (int)image_height, W = (int)image_width;
+  auto fopt = means3D.options().dtype(torch::kFloat32);
+  torch::Tensor out_color = torch::empty({EGS_NUM_CHANNELS, H, W}, fopt);
+  torch::Tensor out_depth = torch::empty({1, H, W}, fopt);
+  torch::Tensor out_alpha = torch::empty({1, H, W}, fopt);
+  torch::Tensor radii = torch::empty({P}, means3D.options().dtype(torch::kInt32));
+  BlobCtx geom{torch::empty({0}, torch::TensorOptions().dtype(torch::kUInt8).device(dev)), dev};
+  BlobCtx binning = geom, image = geom;
+
+  const bool has_colors = colors.defined() && colors.numel() != 0;
+  ModelHold h;
+  fill_model(h, dev, scaling_raw, rotation_raw, opacity_raw, has_colors ? torch::Tensor() : features_dc,
+             has_colors ? torch::Tensor() : features_rest, scale_modifier, is_object, which_object, accum_R, train_R,
+             row0_copies, P);
+  torch::Tensor k[6];
+  EgsForwardArgs a{};
+  a.P = P;
+  a.sh_degree = (int)degree;
+  a.sh_coeffs = h.args.sh_coeffs;
+  a.width = W;
+  a.height = H;
+  a.background = req_ptr(background, k[0], dev, "background");
+  a.means3D = P ? req_ptr(means3D, k[1], dev, "means3D") : nullptr;
+  a.colors_precomp = opt_ptr(colors, k[2], dev, "colors_precomp");
+  a.scale_modifier = (float)scale_modifier;
+  a.viewmatrix = req_ptr(viewmatrix, k[3], dev, "viewmatrix");
+  a.projmatrix = req_ptr(projmatrix, k[4], dev, "projmatrix");
+  a.campos = req_ptr(campos, k[5], dev, "campos");
+  a.tan_fovx = (float)tan_fovx;
+  a.tan_fovy = (float)tan_fovy;
+  a.prefiltered = prefiltered;
+  a.debug = debug;
+  a.out_color = out_color.data_ptr<float>();
+  a.out_depth = out_depth.data_ptr<float>();
+  a.out_alpha = out_alpha.data_ptr<float>();
+  a.radii = radii.data_ptr<int>();
+  a.geom_alloc = blob_alloc;    a.geom_ctx = &geom;
+  a.binning_alloc = blob_alloc; a.binning_ctx = &binning;
+  a.image_alloc = blob_alloc;   a.image_ctx = &image;
+  CountGuess& guess = guess_for(P, W, H);
+  a.num_rendered_hint = guess.recent_max > 0 ? (int)(guess.recent_max * 1.25) + 8192 : 0;
+  int rendered = 0;
+  check(egs_forward_raw(&a, &h.args, at::cuda::getCurrentCUDAStream().stream(), &rendered), "egs_forward_raw");
+  guess.recent_max = std::max<double>(rendered, guess.recent_max * (63.0 / 64.0));
+  return std::make_tuple(rendered, out_color, out_depth, out_alpha, radii, geom.blob, binning.blob, image.blob);
+}
+
+// returns (dL_dmeans2D, dL_dmeans3D, dL_dcolors, d_scaling_raw, d_rotation_raw, d_opacity_raw,
+//          d_features_dc, d_features_rest, d_train_R); absent ones are empty tensors
+std::vector<torch::Tensor> rasterize_gaussians_raw_backward(
+    const torch::Tensor& background, const torch::Tensor& means3D, const torch::Tensor& radii,
+    const torch::Tensor& colors, const torch::Tensor& scaling_raw, const torch::Tensor& rotation_raw,
+    const torch::Tensor& opacity_raw, const torch::Tensor& features_dc, const torch::Tensor& features_rest,
+    double scale_modifier, const torch::Tensor& is_object, int64_t which_object, const torch::Tensor& accum_R,
+    const torch::Tensor& train_R, int64_t row0_copies, const torch::Tensor& viewmatrix,
+    const torch::Tensor& projmatrix, double tan_fovx, double tan_fovy, const torch::Tensor& dL_dout_color,
+    const torch::Tensor& dL_dout_depth, const torch::Tensor& dL_dout_alpha, int64_t degree,
+    const torch::Tensor& campos, const torch::Tensor& geomBuffer, int64_t R, const torch::Tensor& binningBuffer,
+    const torch::Tensor& imageBuffer, const torch::Tensor& alphas, bool want_train_R, bool debug) {
+  TORCH_CHECK(means3D.is_cuda(), "means3D must be a CUDA tensor (there is no CPU path)");
+  const torch::Device dev = means3D.device();
+  c10::cuda::CUDAGuard guard(dev);
+  const int P = (int)means3D.size(0);
+  const int H = (int)dL_dout_color.size(1), W = (int)dL_dout_color.size(2);
+  auto fopt = means3D.options().dtype(torch::kFloat32);
+  const bool has_colors = colors.defined() && colors.numel() != 0;
+  ModelHold h;
+  fill_model(h, dev, scaling_raw, rotation_raw, opacity_raw, has_colors ? torch::Tensor() : features_dc,
+             has_colors ? torch::Tensor() : features_rest, scale_modifier, is_object, which_object, accum_R, train_R,
+             row0_copies, P);
+  const int M = h.args.sh_coeffs;
+  auto none = [&]() { return torch::empty({0}, fopt); };
+  torch::Tensor dL_dmeans3D = torch::empty({P, 3}, fopt), dL_dmeans2D = torch::empty({P, 3}, fopt);
+  torch::Tensor dL_dcolors = has_colors ? torch::empty({P, EGS_NUM_CHANNELS}, fopt) : none();
+  torch::Tensor ds = torch::empty({P, 3}, fopt), dq = torch::empty({P, 4}, fopt), dop = torch::empty({P, 1}, fopt);
+  torch::Tensor ddc = (!has_colors && M > 0) ? torch::empty({P, 1, 3}, fopt) : none();
+  torch::Tensor drest = (!has_colors && M > 1) ? torch::empty({P, (int64_t)M - 1, 3}, fopt) : none();
+  torch::Tensor dT = (want_train_R && h.args.train_R) ? torch::zeros({3, 3}, fopt) : none();
+  if (P != 0) {
+    torch::Tensor scratch = torch::empty({(int64_t)egs_backward_scratch_bytes(P)},
+                                         torch::TensorOptions().dtype(torch::kUInt8).device(dev));
+    torch::Tensor k[12];
+    EgsBackwardArgs a{};
+    a.P = P;
+    a.sh_degree = (int)degree;
+    a.sh_coeffs = M;
+    a.num_rendered = (int)R;
+    a.width = W;
+    a.height = H;
+    a.background = req_ptr(background, k[0], dev, "background");
+    a.means3D = req_ptr(means3D, k[1], dev, "means3D");
+    a.colors_precomp = opt_ptr(colors, k[2], dev, "colors_precomp");
+    a.scale_modifier = (float)scale_modifier;
+    a.viewmatrix = req_ptr(viewmatrix, k[3], dev, "viewmatrix");
+    a.projmatrix = req_ptr(projmatrix, k[4], dev, "projmatrix");
+    a.campos = req_ptr(campos, k[5], dev, "campos");
+    a.tan_fovx = (float)tan_fovx;
+    a.tan_fovy = (float)tan_fovy;
+    TORCH_CHECK(radii.scalar_type() == torch::kInt32 && radii.device() == dev, "radii must be int32 on ", dev);
+    k[6] = radii.contiguous();
+    a.radii = k[6].data_ptr<int>();
+    a.out_alpha = req_ptr(alphas, k[7], dev, "alphas");
+    a.geom_buffer = geomBuffer.data_ptr();
+    a.binning_buffer = binningBuffer.numel() ? binningBuffer.data_ptr() : nullptr;
+    a.image_buffer = imageBuffer.data_ptr();
+    a.dL_dout_color = req_ptr(dL_dout_color, k[8], dev, "dL_dout_color");
+    a.dL_dout_depth = req_ptr(dL_dout_depth, k[9], dev, "dL_dout_depth");
+    a.dL_dout_alpha = req_ptr(dL_dout_alpha, k[10], dev, "dL_dout_alpha");
+    a.scratch = scratch.data_ptr();
+    a.dL_dmeans2D = dL_dmeans2D.data_ptr<float>();
+    a.dL_dmeans3D = dL_dmeans3D.data_ptr<float>();
+    a.dL_dcolors = has_colors ? dL_dcolors.data_ptr<float>() : nullptr;
+    a.debug = debug;
+    a.binning_bytes = (size_t)binningBuffer.numel();
+    auto p = [](torch::Tensor& t) { return t.numel() ? t.data_ptr<float>() : nullptr; };
+    EgsModelGrads g{p(ds), p(dq), p(dop), p(ddc), p(drest), p(dT)};
+    check(egs_backward_raw(&a, &h.args, &g, at::cuda::getCurrentCUDAStream().stream()), "egs_backward_raw");
+  }
+  return {dL_dmeans2D, dL_dmeans3D, dL_dcolors, ds, dq, dop, ddc, drest, dT};
+}
+
 // ---- image loss (egs_image_loss) ---------------------------------------------------------------------
 // returns (terms [3] = L1 mean, SSIM mean, loss; d loss / d image, empty when want_grad is false)
 std::tuple<torch::Tensor, torch::Tensor> image_loss(const torch::Tensor& image, const torch::Tensor& target,
@@ -474,6 +612,8 @@ void densify_stats(const torch::Tensor& radii, const torch::Tensor& dL_dmeans2D,
 PYBIND11_MODULE(TORCH_EXTENSION_NAME, m) {
   m.def("densify_stats", &densify_stats);
   m.def("image_loss", &image_loss);
+  m.def("rasterize_gaussians_raw", &rasterize_gaussians_raw);
+  m.def("rasterize_gaussians_raw_backward", &rasterize_gaussians_raw_backward);
   m.def("model_forward", &model_forward);
   m.def("model_backward", &model_backward);
   m.def("rasterize_gaussians", &rasterize_gaussians);

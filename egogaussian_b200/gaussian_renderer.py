@@ -26,7 +26,7 @@ import torch
 
 from .diff_gaussian_rasterization import GaussianRasterizationSettings, GaussianRasterizer, _C
 
-__all__ = ["render", "model_activations", "get_covariance", "get_rotated_covariance", "rot6d_to_matrix",
+__all__ = ["render", "rasterize_raw", "model_activations", "get_covariance", "get_rotated_covariance", "rot6d_to_matrix",
            "row0_copies"]
 
 _EMPTY = torch.empty(0)
@@ -104,8 +104,15 @@ def model_activations(scaling_raw, rotation_raw, opacity_raw, features_dc, featu
     ``rotate`` selects get_rotated_covariance semantics: rows with ``is_object == which_object``
     (all rows when ``which_object`` is None) use ``train_R @ (accum_R @ L)``. ``quirk`` keeps the
     reference's treatment of row 0 (see ``row0_copies``)."""
-    P = scaling_raw.shape[0]
-    dev = scaling_raw.device
+    mask, which, accum_R, train_R, copies = _selection(scaling_raw.shape[0], scaling_raw.device, is_object,
+                                                       which_object, accum_R, train_R, rotate, quirk)
+    return _ModelActivations.apply(scaling_raw, rotation_raw, opacity_raw, features_dc, features_rest,
+                                   float(scale_modifier), mask, which, accum_R, train_R, copies)
+
+
+def _selection(P, dev, is_object, which_object, accum_R, train_R, rotate, quirk):
+    """Arguments of the object-rotation part as the extension wants them:
+    (mask int32 or empty, which, accum_R or empty, train_R or empty, row0_copies)."""
     copies = 0
     mask = _EMPTY
     if rotate:
@@ -124,9 +131,62 @@ def model_activations(scaling_raw, rotation_raw, opacity_raw, features_dc, featu
     def dev_or_empty(t):
         return _EMPTY if t is None else t.to(device=dev, dtype=torch.float32)
 
-    return _ModelActivations.apply(scaling_raw, rotation_raw, opacity_raw, features_dc, features_rest,
-                                   float(scale_modifier), mask, -1 if which_object is None else int(which_object),
-                                   dev_or_empty(accum_R), dev_or_empty(train_R), copies)
+    return mask, -1 if which_object is None else int(which_object), dev_or_empty(accum_R), dev_or_empty(train_R), copies
+
+
+class _RasterizeRaw(torch.autograd.Function):
+    """Rasterizer on the raw parameters (egs_forward_raw / egs_backward_raw): activations, covariance
+    and the dc/rest split live inside the per-Gaussian kernels, nothing intermediate reaches HBM."""
+
+    @staticmethod
+    def forward(ctx, means3D, means2D, colors, scaling_raw, rotation_raw, opacity_raw, features_dc, features_rest,
+                mask, which, accum_R, train_R, copies, rs):
+        out = _C.rasterize_gaussians_raw(rs.bg, means3D, colors, scaling_raw, rotation_raw, opacity_raw, features_dc,
+                                         features_rest, rs.scale_modifier, mask, which, accum_R, train_R, copies,
+                                         rs.viewmatrix, rs.projmatrix, rs.tanfovx, rs.tanfovy, rs.image_height,
+                                         rs.image_width, rs.sh_degree, rs.campos, rs.prefiltered, rs.debug)
+        num_rendered, color, depth, alpha, radii, geom, binning, img = out
+        ctx.rs, ctx.meta = rs, (num_rendered, which, copies)
+        ctx.save_for_backward(means3D, colors, scaling_raw, rotation_raw, opacity_raw, features_dc, features_rest,
+                              mask, accum_R, train_R, radii, geom, binning, img, alpha)
+        ctx.mark_non_differentiable(radii)
+        return color, radii, depth, alpha
+
+    @staticmethod
+    def backward(ctx, g_color, _g_radii, g_depth, g_alpha):
+        (means3D, colors, scaling_raw, rotation_raw, opacity_raw, features_dc, features_rest, mask, accum_R, train_R,
+         radii, geom, binning, img, alpha) = ctx.saved_tensors
+        rs = ctx.rs
+        num_rendered, which, copies = ctx.meta
+        need = ctx.needs_input_grad
+        g = _C.rasterize_gaussians_raw_backward(
+            rs.bg, means3D, radii, colors, scaling_raw, rotation_raw, opacity_raw, features_dc, features_rest,
+            rs.scale_modifier, mask, which, accum_R, train_R, copies, rs.viewmatrix, rs.projmatrix, rs.tanfovx,
+            rs.tanfovy, g_color, g_depth, g_alpha, rs.sh_degree, rs.campos, geom, num_rendered, binning, img, alpha,
+            bool(need[11]), rs.debug)
+        d_means2D, d_means3D, d_colors, ds, dq, dop, ddc, drest, dT = g
+
+        def out(t, i):
+            return t if (need[i] and t.numel()) else None
+
+        return (out(d_means3D, 0), out(d_means2D, 1), out(d_colors, 2), out(ds, 3), out(dq, 4), out(dop, 5),
+                out(ddc, 6), out(drest, 7), None, None, None, out(dT, 11), None, None)
+
+
+def rasterize_raw(raster_settings, means3D, means2D, scaling_raw, rotation_raw, opacity_raw, features_dc=None,
+                  features_rest=None, colors_precomp=None, is_object=None, which_object=None, accum_R=None,
+                  train_R=None, rotate=False, quirk=True):
+    """(color, radii, depth, alpha) straight from the raw GaussianModel parameters; the covariance
+    semantics are those of ``model_activations`` (get_covariance / get_rotated_covariance)."""
+    if (features_dc is None) == (colors_precomp is None):
+        raise Exception('Please provide excatly one of either SHs or precomputed colors!')
+    mask, which, accum_R, train_R, copies = _selection(means3D.shape[0], means3D.device, is_object, which_object,
+                                                       accum_R, train_R, rotate, quirk)
+    e = _EMPTY
+    return _RasterizeRaw.apply(means3D, means2D, e if colors_precomp is None else colors_precomp, scaling_raw,
+                               rotation_raw, opacity_raw, e if features_dc is None else features_dc,
+                               e if features_rest is None else features_rest, mask, which, accum_R, train_R, copies,
+                               raster_settings)
 
 
 def get_covariance(pc, scaling_modifier: float = 1.0) -> torch.Tensor:
@@ -144,8 +204,12 @@ def get_rotated_covariance(pc, accum_R, which_object, during_training, scaling_m
 
 def render(viewpoint_camera, pc, pipe, bg_color: torch.Tensor, scaling_modifier: float = 1.0,
            override_color=None, rot_cov: bool = False, accum_R=None, which_object=None,
-           during_training: bool = False):
-    """Render one view (gaussian_renderer/__init__.py:18-107). ``bg_color`` must be on the GPU."""
+           during_training: bool = False, fused: bool = True):
+    """Render one view (gaussian_renderer/__init__.py:18-107). ``bg_color`` must be on the GPU.
+
+    With ``pipe.compute_cov3D_python`` (forced on by the reference's trainers) the activations and
+    the covariance build run inside the rasterizer's per-Gaussian kernels (``fused=True``, default)
+    or as their own kernel pair in front of it (``fused=False``); both render identically."""
     xyz = pc._xyz
     screenspace_points = torch.zeros_like(xyz, requires_grad=True)
     raster_settings = GaussianRasterizationSettings(
@@ -171,6 +235,21 @@ def render(viewpoint_camera, pc, pipe, bg_color: torch.Tensor, scaling_modifier:
     rest = pc._features_rest if want_shs else _EMPTY
 
     scales = rotations = cov3D_precomp = None
+    if pipe.compute_cov3D_python and fused:
+        train_R = None
+        if rot_cov and during_training:
+            train_R = rot6d_to_matrix(pc.trainable_object_move.obj_rotation_6d)
+        rendered_image, radii, rendered_depth, rendered_alpha = rasterize_raw(
+            raster_settings, xyz, screenspace_points, pc._scaling, pc._rotation, pc._opacity,
+            features_dc=dc if want_shs else None, features_rest=rest if want_shs else None,
+            colors_precomp=override_color, is_object=pc._is_object, which_object=which_object, accum_R=accum_R,
+            train_R=train_R, rotate=rot_cov)
+        return {"render": rendered_image,
+                "viewspace_points": screenspace_points,
+                "visibility_filter": radii > 0,
+                "radii": radii,
+                "depth": rendered_depth,
+                "alpha": rendered_alpha}
     if pipe.compute_cov3D_python:
         train_R = None
         if rot_cov and during_training:

@@ -273,6 +273,35 @@ int egs_model_backward(const EgsModelArgs* model, const float* dL_dcov3D, const 
                        float* d_opacity_raw, float* d_features_dc, float* d_features_rest,
                        float* d_train_R, void* stream);
 
+/* The same activations fused INTO the rasterizer (SURVEY.md 8f rank 1 as stated: "fuse activations
+ * + covariance build + SH concat into preprocess"): the per-Gaussian forward kernel reads the raw
+ * parameters directly and the per-Gaussian backward kernel writes the raw-parameter gradients, so
+ * cov3D, the activated opacity and the concatenated SH tensor (and their gradients) never touch
+ * HBM. Arithmetic is shared with egs_model_forward/backward (csrc/model_math.cuh), so
+ * egs_forward_raw(args, model) renders bit-identically to egs_model_forward + egs_forward with
+ * cov3D_precomp / opacities / shs set to its outputs.
+ *
+ * egs_forward_raw: args->opacities, shs, scales, rotations and cov3D_precomp must be NULL (they come
+ * from `model`); args->sh_coeffs is ignored (model->sh_coeffs is used); args->colors_precomp may be
+ * set (override_color), in which case the feature tensors are not read. Everything else as
+ * egs_forward. */
+int egs_forward_raw(const EgsForwardArgs* args, const EgsModelArgs* model, void* stream, int* num_rendered);
+
+typedef struct EgsModelGrads {   /* device, caller-allocated, every element written */
+  float* d_scaling_raw;    /* [P,3] */
+  float* d_rotation_raw;   /* [P,4], 16-byte aligned */
+  float* d_opacity_raw;    /* [P,1] */
+  float* d_features_dc;    /* [P,1,3]   (NULL when colors_precomp was used) */
+  float* d_features_rest;  /* [P,M-1,3] (NULL when M == 1 or colors_precomp was used) */
+  float* d_train_R;        /* device [9], overwritten; NULL unless model->train_R is set and wanted */
+} EgsModelGrads;
+
+/* egs_backward_raw: the inputs of egs_backward (same NULL rules as egs_forward_raw); of its outputs
+ * only dL_dmeans2D, dL_dmeans3D and (with colors_precomp) dL_dcolors are used, the rest is ignored
+ * and the raw-parameter gradients go to `grads`. */
+int egs_backward_raw(const EgsBackwardArgs* args, const EgsModelArgs* model, const EgsModelGrads* grads,
+                     void* stream);
+
 /* Per-iteration densification bookkeeping (the per-iteration half:
  * GaussianModel.add_densification_stats, scene/gaussian_model.py:735-740, and the max_radii2D
  * line of trainers/train_static_bg.py:128). For rows with radii[i] > 0:

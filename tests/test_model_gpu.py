@@ -122,6 +122,58 @@ class _Model:
                 "rot6d": self.trainable_object_move.obj_rotation_6d}
 
 
+@pytest.mark.parametrize("mode", ["static", "object_train", "override_color", "sh0"])
+def test_fused_raw_rasterizer_equals_two_stage(mode, built, cuda_device):
+    """egs_forward_raw / egs_backward_raw (activations inside the per-Gaussian kernels) against
+    egs_model_forward -> egs_forward -> egs_backward -> egs_model_backward: the two share their
+    arithmetic (csrc/model_math.cuh), so images and radii are bit-identical; gradients agree to the
+    run-to-run noise of the tile kernel's float atomics (2e-5 of the tensor maximum)."""
+    from egogaussian_b200 import scenes
+    from egogaussian_b200.gaussian_renderer import render
+    dev = cuda_device
+    W, H, P = 320, 192, 20_000
+    deg = 0 if mode == "sh0" else 2
+    sc = scenes.make_scene(P, W, H, sh_degree=deg, seed=93).to(dev)
+    cam = _Camera(sc.camera, W, H)
+    gen = torch.Generator().manual_seed(94)
+    w = [torch.randn(s, generator=gen).to(dev) for s in ((3, H, W), (1, H, W), (1, H, W))]
+    kw = {}
+    if mode == "object_train":
+        kw = dict(rot_cov=True, accum_R=torch.linalg.qr(torch.randn(3, 3, generator=gen))[0].contiguous(),
+                  which_object=1, during_training=True)
+    color_leaf = {}
+    results = []
+    for fused in (True, False):
+        pc = _Model(sc, dev, (deg + 1) ** 2)
+        if mode == "override_color":
+            color_leaf[fused] = torch.rand(P, 3, generator=torch.Generator().manual_seed(95)).to(dev).requires_grad_(True)
+            kw["override_color"] = color_leaf[fused]
+        pkg = render(cam, pc, _Pipe(), sc.bg, scaling_modifier=0.9, fused=fused, **kw)
+        ((pkg["render"] * w[0]).sum() + (pkg["depth"] * w[1]).sum() + (pkg["alpha"] * w[2]).sum()).backward()
+        results.append((pkg, pc))
+    (a, pa), (b, pb) = results
+    for k in ("render", "depth", "alpha", "radii"):
+        assert torch.equal(a[k], b[k]), k
+
+    def close(x, y):   # the tile kernel's float atomics land in a different order on every run
+        return (x - y).abs().max().item() <= 2e-5 * y.abs().max().item()
+    assert close(a["viewspace_points"].grad, b["viewspace_points"].grad)
+    la, lb = pa.leaves(), pb.leaves()
+    for k in la:
+        ga, gb = la[k].grad, lb[k].grad
+        if k == "rot6d":
+            if mode == "object_train":
+                assert (ga - gb).abs().max().item() <= 1e-5 * gb.abs().max().item()
+            else:
+                assert ga is None and gb is None
+        elif (mode == "override_color" and k in ("f_dc", "f_rest")) or (mode == "sh0" and k == "f_rest"):
+            assert ga is None and gb is None
+        else:
+            assert close(ga, gb), k
+    if mode == "override_color":
+        assert close(color_leaf[True].grad, color_leaf[False].grad)
+
+
 @pytest.mark.parametrize("mode", ["static", "object_train"])
 def test_render_mirror_equals_torch_glue(mode, built, cuda_device):
     """render() on raw parameters == the reference's glue (restated in torch, oracle/model_ref.py)
