@@ -26,6 +26,7 @@ def main():
     ap.add_argument("--sh-degree", type=int, default=3)
     ap.add_argument("--geom", default="scale_rot")
     ap.add_argument("--adam", action="store_true")
+    ap.add_argument("--trainer", action="store_true", help="also run two whole training iterations from raw parameters")
     a = ap.parse_args()
     import torch
     import bench
@@ -43,6 +44,27 @@ def main():
         m = [torch.zeros_like(p) for p in params]
         v = [torch.zeros_like(p) for p in params]
         _C.adam_step(params, [g[n] for n in names], m, v, [1e-3] * len(names), [1] * len(names), 0.9, 0.999, 1e-15)
+    if a.trainer:
+        # one whole training iteration from the raw parameters: render() in raw-parameter mode, the
+        # fused image loss, backward, densification bookkeeping, fused Adam
+        from egogaussian_b200 import gaussian_renderer as gr, loss_utils
+        from egogaussian_b200.diff_gaussian_rasterization import _C
+        pc = bench._TrainerModel(a, dev)
+        pc.max_radii2D = torch.zeros(a.P, device=dev)
+        pc.xyz_gradient_accum = torch.zeros(a.P, 1, device=dev)
+        pc.denom = torch.zeros(a.P, 1, device=dev)
+        gt_img, int_mask = bench.trainer_targets(a, dev)
+        params = pc.params()
+        m = [torch.zeros_like(p) for p in params]
+        v = [torch.zeros_like(p) for p in params]
+        for it in range(2):
+            pkg = gr.render(pc, pc, bench._Pipe(), pc.bg)
+            loss_utils.image_loss(pkg["render"], gt_img, 0.2, grad_mask=int_mask)[0].backward()
+            gr.add_densification_stats(pc, pkg["viewspace_points"], pkg["radii"])
+            with torch.no_grad():
+                _C.adam_step(params, [p.grad for p in params], m, v, pc.lrs, [it + 1] * len(params), 0.9, 0.999, 1e-15)
+            for p in params:
+                p.grad = None
     torch.cuda.synchronize()
     print("profile_step ok: R =", fwd.num_rendered)
 
