@@ -30,9 +30,10 @@ namespace egs {
 
 constexpr int MSD_BITS_MAX = 10;
 constexpr int MSD_BINS = 1 << MSD_BITS_MAX;        // 1024
-constexpr int MSD_THREADS = 1024;                  // one thread per bin
+constexpr int MSD_THREADS = 256;
 constexpr int MSD_WARPS = MSD_THREADS / 32;
-constexpr int MSD_ITEMS = 4;
+constexpr int MSD_DPT = MSD_BINS / MSD_THREADS;    // digits owned by one thread (4)
+constexpr int MSD_ITEMS = 16;
 constexpr int MSD_TILE = MSD_THREADS * MSD_ITEMS;  // 4096 words per CTA (same as SORT_TILE)
 static_assert(MSD_TILE == SORT_TILE, "status sizing");
 static_assert(MSD_BINS <= SORT_STATUS_WORDS, "status sizing");
@@ -163,9 +164,9 @@ constexpr uint32_t MSD_FLAG_PREFIX = 1u << 31;
 constexpr uint32_t MSD_VALUE_MASK = (1u << 30) - 1u;
 
 struct MsdSmem {
-  uint16_t warp_hist[MSD_WARPS][MSD_BINS];   // 64 KB (a warp holds at most 128 items)
+  uint16_t warp_hist[MSD_WARPS][MSD_BINS];   // 16 KB (a warp holds at most 512 items)
   uint64_t exch[MSD_TILE];                   // 32 KB
-  uint32_t digit_local[MSD_BINS];
+  uint16_t digit_local[MSD_BINS];            // first slot of each digit in exch (< MSD_TILE)
   uint32_t digit_global[MSD_BINS];
   uint32_t warp_sums[MSD_WARPS];
   uint32_t tile;
@@ -180,7 +181,11 @@ __device__ __forceinline__ void st_relaxed_u32(uint32_t* p, uint32_t v) {
   asm volatile("st.relaxed.gpu.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
 }
 
-__global__ void __launch_bounds__(MSD_THREADS)
+// 256 threads x 16 words: the fixed per-CTA work (clearing and scanning the per-warp counters,
+// the look-back) is shared by 16 words per thread instead of 4 (the first version ran 1024 threads
+// x 4 words and spent more instructions on that bookkeeping than on the words). A thread owns
+// four adjacent digits and walks their four look-back chains together.
+__global__ void __launch_bounds__(MSD_THREADS, 3)
 msd_partition_kernel(const uint64_t* __restrict__ in, uint64_t* __restrict__ out, InstanceCount count,
                      int shift, const uint32_t* __restrict__ bucket_start, uint32_t* __restrict__ ticket,
                      uint32_t* __restrict__ status_raw) {
@@ -190,8 +195,12 @@ msd_partition_kernel(const uint64_t* __restrict__ in, uint64_t* __restrict__ out
   if (!count.get(n)) return;   // the guessed capacity was too small: forward re-runs this stage
   const unsigned tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   if (tid == 0) S.tile = atomicAdd(ticket, 1u);
+  {
+    uint4* z = reinterpret_cast<uint4*>(&S.warp_hist[0][0]);
+    constexpr int VEC = (int)(sizeof(S.warp_hist) / sizeof(uint4));
 #pragma unroll
-  for (int w = 0; w < MSD_WARPS; ++w) S.warp_hist[w][tid] = 0;
+    for (int i = 0; i < VEC / MSD_THREADS; ++i) z[i * MSD_THREADS + tid] = make_uint4(0u, 0u, 0u, 0u);
+  }
   __syncthreads();
   const uint32_t tile = S.tile;
   const unsigned lt_mask = (1u << lane) - 1u;
@@ -202,7 +211,7 @@ msd_partition_kernel(const uint64_t* __restrict__ in, uint64_t* __restrict__ out
   const size_t warp_base = block_base + (size_t)warp * (32 * MSD_ITEMS);
 
   uint64_t word[MSD_ITEMS];
-  uint32_t rank[MSD_ITEMS];
+  uint16_t rank[MSD_ITEMS];
 #pragma unroll
   for (int i = 0; i < MSD_ITEMS; ++i) {
     const size_t g = warp_base + (size_t)i * 32 + lane;
@@ -218,22 +227,32 @@ msd_partition_kernel(const uint64_t* __restrict__ in, uint64_t* __restrict__ out
     __syncwarp();
     if (ok && (peers & lt_mask) == 0u) S.warp_hist[warp][d] = (uint16_t)(before + __popc(peers));
     __syncwarp();
-    rank[i] = before + __popc(peers & lt_mask);
+    rank[i] = (uint16_t)(before + __popc(peers & lt_mask));
   }
   __syncthreads();
   {
-    const uint32_t d = tid;
-    uint32_t run = 0;
-#pragma unroll 8
-    for (int w = 0; w < MSD_WARPS; ++w) {
-      const uint32_t c = S.warp_hist[w][d];
-      S.warp_hist[w][d] = (uint16_t)run;
-      run += c;
+    // digits d0 .. d0 + 3 of this thread: per-warp counts -> exclusive warp offsets, block counts
+    const uint32_t d0 = tid * MSD_DPT;
+    uint32_t block_count[MSD_DPT];
+    uint32_t mine = 0;
+#pragma unroll
+    for (int k = 0; k < MSD_DPT; ++k) {
+      uint32_t run = 0;
+#pragma unroll
+      for (int w = 0; w < MSD_WARPS; ++w) {
+        const uint32_t c = S.warp_hist[w][d0 + k];
+        S.warp_hist[w][d0 + k] = (uint16_t)run;
+        run += c;
+      }
+      block_count[k] = run;
+      mine += run;
     }
-    const uint32_t block_count = run;
-    uint32_t* st = status_raw + (size_t)tile * MSD_BINS + d;
-    if (tile != 0) st_relaxed_u32(st, MSD_FLAG_AGG | block_count);
-    uint32_t incl = block_count;
+    uint32_t* st = status_raw + (size_t)tile * MSD_BINS + d0;
+    if (tile != 0) {
+#pragma unroll
+      for (int k = 0; k < MSD_DPT; ++k) st_relaxed_u32(st + k, MSD_FLAG_AGG | block_count[k]);
+    }
+    uint32_t incl = mine;
 #pragma unroll
     for (int s = 1; s < 32; s <<= 1) {
       const uint32_t t = __shfl_up_sync(0xffffffffu, incl, s);
@@ -241,23 +260,42 @@ msd_partition_kernel(const uint64_t* __restrict__ in, uint64_t* __restrict__ out
     }
     if (lane == 31) S.warp_sums[warp] = incl;
     __syncthreads();
-    uint32_t woff = 0;
-    for (unsigned w = 0; w < warp; ++w) woff += S.warp_sums[w];
-    const uint32_t local_start = woff + incl - block_count;
-    S.digit_local[d] = local_start;
-    uint32_t excl = 0;
+    uint32_t start = incl - mine;   // first slot of digit d0 in the CTA's exchange buffer
+    for (unsigned w = 0; w < warp; ++w) start += S.warp_sums[w];
+    uint32_t local_start[MSD_DPT];
+#pragma unroll
+    for (int k = 0; k < MSD_DPT; ++k) {
+      local_start[k] = start;
+      S.digit_local[d0 + k] = (uint16_t)start;
+      start += block_count[k];
+    }
+    uint32_t excl[MSD_DPT];
+#pragma unroll
+    for (int k = 0; k < MSD_DPT; ++k) excl[k] = 0;
     if (tile != 0) {
-      const uint32_t* prev = st - MSD_BINS;
-      for (;;) {
-        uint32_t s;
-        do { s = ld_relaxed_u32(prev); } while ((s & (MSD_FLAG_AGG | MSD_FLAG_PREFIX)) == 0u);
-        excl += s & MSD_VALUE_MASK;
-        if (s & MSD_FLAG_PREFIX) break;
-        prev -= MSD_BINS;
+      const uint32_t* prev[MSD_DPT];
+      unsigned open = (1u << MSD_DPT) - 1u;
+#pragma unroll
+      for (int k = 0; k < MSD_DPT; ++k) prev[k] = st + k - MSD_BINS;
+      while (open) {
+        uint32_t s[MSD_DPT];
+#pragma unroll
+        for (int k = 0; k < MSD_DPT; ++k) s[k] = (open >> k) & 1u ? ld_relaxed_u32(prev[k]) : 0u;
+#pragma unroll
+        for (int k = 0; k < MSD_DPT; ++k) {
+          if (((open >> k) & 1u) && (s[k] & (MSD_FLAG_AGG | MSD_FLAG_PREFIX)) != 0u) {
+            excl[k] += s[k] & MSD_VALUE_MASK;
+            if (s[k] & MSD_FLAG_PREFIX) open &= ~(1u << k);
+            else prev[k] -= MSD_BINS;
+          }
+        }
       }
     }
-    st_relaxed_u32(st, MSD_FLAG_PREFIX | (excl + block_count));
-    S.digit_global[d] = bucket_start[d] + excl - local_start;
+#pragma unroll
+    for (int k = 0; k < MSD_DPT; ++k) {
+      st_relaxed_u32(st + k, MSD_FLAG_PREFIX | (excl[k] + block_count[k]));
+      S.digit_global[d0 + k] = bucket_start[d0 + k] + excl[k] - local_start[k];
+    }
   }
   __syncthreads();
 #pragma unroll
