@@ -337,8 +337,12 @@ static_assert(sizeof(uint32_t) * BK_WARPS * BK_RADIX <= sizeof(uint64_t) * BK_CA
 constexpr int BK_ROUNDS = ((BK_CAP + BK_WARPS - 1) / BK_WARPS + 31) / 32;   // 12
 
 template <bool HWMATCH>   // true: match.any instruction; false: one ballot per digit bit
-__device__ __forceinline__ void bucket_pass_smem(BucketSmem& S, const uint64_t* A, uint64_t* B, uint32_t n,
+__device__ __forceinline__ void bucket_pass_smem(BucketSmem& S, int cur /* source buffer 0 | 1 */, uint32_t n,
                                                  int shift, uint32_t mask) {
+  // indexed through S so that the compiler knows both buffers are shared memory (LDS / STS instead
+  // of generic loads and stores through a pointer that may also name an overflow bucket)
+  const uint64_t* A = S.buf[cur];
+  uint64_t* B = S.buf[cur ^ 1];
   const unsigned tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   const unsigned lt_mask = (1u << lane) - 1u;
   uint16_t* hist = &S.warp_hist[0][0];
@@ -508,7 +512,7 @@ bucket_sort_kernel(uint64_t* __restrict__ words /* partitioned; receives the sor
     const int shift = idx_bits + p * BK_BITS;
     const int width = min(BK_BITS, rem_bits - p * BK_BITS);
     if (in_smem)
-      bucket_pass_smem<HWMATCH>(S, A, B, n, shift, (1u << width) - 1u);
+      bucket_pass_smem<HWMATCH>(S, p & 1, n, shift, (1u << width) - 1u);
     else
       bucket_pass<uint32_t>(S, reinterpret_cast<uint32_t*>(&S.buf[0][0]), A, B, n, shift, (1u << width) - 1u);
     uint64_t* t = A;
