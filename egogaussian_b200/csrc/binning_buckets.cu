@@ -48,65 +48,73 @@ constexpr int BK_CAP = 12288;                      // words per bucket held in s
 // duplicate, then bucket histogram
 // ---------------------------------------------------------------------------------------------
 // One packed word (tile | depth bits | index) per instance, in Gaussian-index order
-// (duplicateWithKeys, rasterizer_impl.cu:70-111).
-__global__ void __launch_bounds__(256)
+// (duplicateWithKeys, rasterizer_impl.cu:70-111), and the bucket histogram of those words.
+//
+// Warp-cooperative: a warp takes 32 consecutive Gaussians. Their instances form one contiguous run
+// of the output (the offsets are a prefix sum), and the lanes share that run evenly: lane l writes
+// output slots base + 32 c + l. A slot finds its Gaussian by a 5-step binary search over the 32
+// start offsets (shuffles) and its tile from the slot's position inside that Gaussian's rectangle.
+// Compared with one thread looping over its own rectangle this removes the divergence between
+// small and large rectangles, makes every store coalesced, and lets the warp count a bucket once
+// per 32 slots (match.any) for the histogram, which therefore needs no pass of its own.
+constexpr int DUP_THREADS = 256;
+__global__ void __launch_bounds__(DUP_THREADS)
 duplicate_words_kernel(int P, const float2* __restrict__ means2D, const float* __restrict__ depths,
                        const uint32_t* __restrict__ offsets, const int* __restrict__ radii,
                        uint64_t* __restrict__ words, int grid_x, int grid_y, int idx_bits,
-                       InstanceCount count) {
-  const int idx = blockIdx.x * blockDim.x + threadIdx.x;
-  if (idx >= P) return;
+                       InstanceCount count, int bucket_shift, uint32_t* __restrict__ bucket_hist) {
   uint32_t n;
   if (!count.get(n)) return;   // more instances than the buffer holds: write nothing
-  const int r = radii[idx];
-  if (r <= 0) return;
-  uint32_t off = (idx == 0) ? 0u : offsets[idx - 1];
-  uint2 lo, hi;
-  tile_rect(means2D[idx], r, grid_x, grid_y, lo, hi);
-  const uint64_t low = ((uint64_t)__float_as_uint(depths[idx]) << idx_bits) | (uint32_t)idx;
-  const int tile_shift = 32 + idx_bits;
-  for (uint32_t y = lo.y; y < hi.y; ++y)
-    for (uint32_t x = lo.x; x < hi.x; ++x)
-      words[off++] = ((uint64_t)(y * (uint32_t)grid_x + x) << tile_shift) | low;
-}
-
-// Bucket histogram of the word list. A thread takes 8 consecutive words -- the instances of one
-// Gaussian are consecutive and mostly fall into one or two buckets -- and adds run lengths, so the
-// shared-memory atomics are a fraction of the word count.
-constexpr int BH_ITEMS = 8;
-__global__ void __launch_bounds__(256)
-bucket_histogram_kernel(const uint64_t* __restrict__ words, InstanceCount count, int shift,
-                        uint32_t* __restrict__ bucket_hist) {
-  uint32_t n;
-  if (!count.get(n)) return;
   __shared__ uint32_t s_hist[MSD_BINS];
-  for (int i = threadIdx.x; i < MSD_BINS; i += blockDim.x) s_hist[i] = 0;
+  for (int i = threadIdx.x; i < MSD_BINS; i += DUP_THREADS) s_hist[i] = 0;
   __syncthreads();
-  const size_t stride = (size_t)gridDim.x * blockDim.x * BH_ITEMS;
-  for (size_t base = ((size_t)blockIdx.x * blockDim.x + threadIdx.x) * BH_ITEMS; base < (size_t)n; base += stride) {
-    uint32_t prev = 0xffffffffu, cnt = 0;
-    if (base + BH_ITEMS <= (size_t)n) {
-      const ulonglong2* p = reinterpret_cast<const ulonglong2*>(words + base);
-#pragma unroll
-      for (int k = 0; k < BH_ITEMS / 2; ++k) {
-        const ulonglong2 v = p[k];
-        const uint32_t b0 = (uint32_t)(v.x >> shift), b1 = (uint32_t)(v.y >> shift);
-        if (b0 != prev) { if (cnt) atomicAdd(&s_hist[prev], cnt); prev = b0; cnt = 0; }
-        ++cnt;
-        if (b1 != prev) { atomicAdd(&s_hist[prev], cnt); prev = b1; cnt = 0; }
-        ++cnt;
-      }
-    } else {
-      for (size_t i = base; i < (size_t)n; ++i) {
-        const uint32_t b0 = (uint32_t)(words[i] >> shift);
-        if (b0 != prev) { if (cnt) atomicAdd(&s_hist[prev], cnt); prev = b0; cnt = 0; }
-        ++cnt;
-      }
+  const unsigned lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const int groups = (P + 31) / 32;
+  const int tile_shift = 32 + idx_bits;
+  for (int group = blockIdx.x * (DUP_THREADS / 32) + warp; group < groups; group += gridDim.x * (DUP_THREADS / 32)) {
+    const int idx = group * 32 + (int)lane;
+    const bool valid = idx < P;
+    const int r = valid ? radii[idx] : 0;
+    const uint32_t end = offsets[valid ? idx : P - 1];
+    uint32_t lox = 0, loy = 0, w = 1, cnt = 0, dbits = 0;
+    if (r > 0) {
+      uint2 lo, hi;
+      tile_rect(means2D[idx], r, grid_x, grid_y, lo, hi);
+      lox = lo.x;
+      loy = lo.y;
+      w = max(hi.x - lo.x, 1u);   // never 0: slots outside the run still divide by it
+      cnt = (hi.x - lo.x) * (hi.y - lo.y);
+      dbits = __float_as_uint(depths[idx]);
     }
-    if (cnt) atomicAdd(&s_hist[prev], cnt);
+    const uint32_t start = end - cnt;   // culled and out-of-range lanes: empty run at their neighbour's end
+    const uint32_t run_base = __shfl_sync(0xffffffffu, start, 0);
+    const uint32_t run_end = __shfl_sync(0xffffffffu, end, 31);
+    for (uint32_t o = run_base + lane; o - lane < run_end; o += 32) {   // warp-uniform trip count
+      // owner = the last lane whose run starts at or before slot o (empty runs sort before it)
+      int L = 0;
+#pragma unroll
+      for (int step = 16; step > 0; step >>= 1) {
+        const uint32_t s_mid = __shfl_sync(0xffffffffu, start, L + step);
+        if (s_mid <= o) L += step;
+      }
+      const uint32_t o_start = __shfl_sync(0xffffffffu, start, L);
+      const uint32_t o_lox = __shfl_sync(0xffffffffu, lox, L);
+      const uint32_t o_loy = __shfl_sync(0xffffffffu, loy, L);
+      const uint32_t o_w = __shfl_sync(0xffffffffu, w, L);
+      const uint32_t o_d = __shfl_sync(0xffffffffu, dbits, L);
+      const bool live = o < run_end;
+      const uint32_t local = o - o_start;
+      const uint32_t dy = local / o_w;
+      const uint32_t tile = (o_loy + dy) * (uint32_t)grid_x + o_lox + (local - dy * o_w);
+      if (live)
+        words[o] = ((uint64_t)tile << tile_shift) | ((uint64_t)o_d << idx_bits) | (uint32_t)(group * 32 + L);
+      const uint32_t bucket = tile >> bucket_shift;
+      const uint32_t peers = __match_any_sync(0xffffffffu, live ? bucket : 0xffffffffu);
+      if (live && (peers & ((1u << lane) - 1u)) == 0u) atomicAdd(&s_hist[bucket], (uint32_t)__popc(peers));
+    }
   }
   __syncthreads();
-  for (int i = threadIdx.x; i < MSD_BINS; i += blockDim.x) {
+  for (int i = threadIdx.x; i < MSD_BINS; i += DUP_THREADS) {
     const uint32_t c = s_hist[i];
     if (c) atomicAdd(&bucket_hist[i], c);
   }
@@ -578,12 +586,10 @@ int launch_binning_buckets(const GeomPtrs& g, const BinningPtrs& b, const ImageP
     // five-pass paths need)
     const size_t zero = reinterpret_cast<char*>(b.status + b.sort_blocks * MSD_BINS) - reinterpret_cast<char*>(b.hist);
     EGS_CUDA_TRY(cudaMemsetAsync(b.hist, 0, zero, stream));
-    duplicate_words_kernel<<<(P + 255) / 256, 256, 0, stream>>>(P, g.means2D, g.depths, g.point_offsets, radii,
-                                                                b.keys[1], gx, gy, ib, count);
-    EGS_AFTER_LAUNCH(stream, debug);
-    int hist_blocks = (capacity + 256 * BH_ITEMS - 1) / (256 * BH_ITEMS);
-    if (hist_blocks > 148 * 4) hist_blocks = 148 * 4;
-    bucket_histogram_kernel<<<hist_blocks, 256, 0, stream>>>(b.keys[1], count, ib + 32 + bucket_shift, hist);
+    // 4 CTAs per SM, each warp strides over groups of 32 Gaussians; the bucket histogram comes out
+    // of the same kernel
+    duplicate_words_kernel<<<148 * 4, DUP_THREADS, 0, stream>>>(P, g.means2D, g.depths, g.point_offsets, radii,
+                                                             b.keys[1], gx, gy, ib, count, bucket_shift, hist);
     EGS_AFTER_LAUNCH(stream, debug);
     bucket_scan_kernel<<<1, MSD_BINS, 0, stream>>>(hist, start, order);
     EGS_AFTER_LAUNCH(stream, debug);
