@@ -403,8 +403,11 @@ blend_backward2_kernel(const uint2* __restrict__ ranges, const uint32_t* __restr
   const bool i_add = my_quantity >= 0 && (lane & 1) == 0;
 
   // shared-window addresses formed once (see lds_f4 in common.cuh)
-  const uint32_t a_a = smem_addr(s_a), a_b = smem_addr(s_b), a_c = smem_addr(s_c);
-  const uint32_t a_bits = smem_addr(&s_bits[warp][0]);
+  uint32_t a_a = smem_addr(s_a), a_b = smem_addr(s_b), a_c = smem_addr(s_c);
+  uint32_t a_bits = smem_addr(&s_bits[warp][0]);
+  uint32_t a_acc = smem_addr(&s_acc[warp * BWD2_BATCH * ACC_PITCH + my_slot]);   // this lane's slot, entry 0
+  // opaque to the optimiser, or it re-derives the window addresses inside the loop
+  asm volatile("" : "+r"(a_a), "+r"(a_b), "+r"(a_c), "+r"(a_bits), "+r"(a_acc));
 
   const int rounds = (walk + BWD2_BATCH - 1) / BWD2_BATCH;
   for (int r = 0; r < rounds; ++r) {
@@ -464,7 +467,7 @@ blend_backward2_kernel(const uint2* __restrict__ ranges, const uint32_t* __restr
       if (act0) fragment_backward(P0, dx0, dy0, power0, a4, b4, c4, ddelx_dx, ddely_dy, q);
       if (act1) fragment_backward(P1, dx1, dy1, power1, a4, b4, c4, ddelx_dx, ddely_dy, q);
       const float total = warp_packed_reduce10(q, lane);
-      if (i_add) s_acc[(warp * BWD2_BATCH + j) * ACC_PITCH + my_slot] = total;
+      if (i_add) sts_f32(a_acc + (uint32_t)(j * ACC_PITCH * 4), total);
       if (lane == 0) atomicOr(&s_hit[j], 1u << warp);
      }
     }

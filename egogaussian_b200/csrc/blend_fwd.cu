@@ -147,8 +147,11 @@ blend_forward3_kernel(const uint2* __restrict__ ranges, const uint32_t* __restri
   uint32_t last_contributor = 0;
   const float tile_x0 = (float)(blockIdx.x * TILE_X), tile_y0 = (float)(blockIdx.y * TILE_Y);
   float C0 = 0.f, C1 = 0.f, C2 = 0.f, weight = 0.f, D = 0.f;
-  const uint32_t a_xy = smem_addr(s_xy), a_co = smem_addr(s_co), a_cd = smem_addr(s_cd);
-  const uint32_t a_bits = smem_addr(&s_bits[warp][0]);
+  uint32_t a_xy = smem_addr(s_xy), a_co = smem_addr(s_co), a_cd = smem_addr(s_cd);
+  uint32_t a_bits = smem_addr(&s_bits[warp][0]);
+  // opaque to the optimiser, or it re-derives the window addresses inside the loop instead of
+  // keeping four registers
+  asm volatile("" : "+r"(a_xy), "+r"(a_co), "+r"(a_cd), "+r"(a_bits));
 
   for (int r = 0; r < rounds; ++r) {
     if (__syncthreads_count(done) == TILE_PIXELS) break;
@@ -176,7 +179,7 @@ blend_forward3_kernel(const uint2* __restrict__ ranges, const uint32_t* __restri
     const uint32_t first = (uint32_t)(r * BLEND_BATCH) + 1u;
     for (uint32_t c = 0; c < BLEND_BATCH / 32 && !done; ++c) {
       uint32_t bits = lds_u32(a_bits + 4u * c);
-      while (bits != 0u && !done) {
+      while (bits != 0u) {   // a pixel that saturates clears its own copy of the word
         const uint32_t j = c * 32u + (uint32_t)__ffs((int)bits) - 1u;
         bits &= bits - 1u;
         const float2 xy = lds_f2(a_xy + 8u * j);
@@ -189,6 +192,7 @@ blend_forward3_kernel(const uint2* __restrict__ ranges, const uint32_t* __restri
         const float test_T = T * (1 - alpha);
         if (test_T < 0.0001f) {
           done = true;
+          bits = 0u;
           continue;
         }
         const float4 cd = lds_f4(a_cd + 16u * j);
