@@ -379,6 +379,16 @@ __device__ __forceinline__ unsigned footprint_mask(const float2 xy, const float4
   if (!(isfinite(ex) && isfinite(ey))) return ALL;
   const float lo_x = xy.x - ex - tile_x0, hi_x = xy.x + ex - tile_x0;   // tile-local pixel range
   const float lo_y = xy.y - ey - tile_y0, hi_y = xy.y + ey - tile_y0;
+  // Blocks that pass the bounding-box test are then tested against the ellipse itself: the smallest
+  // q(d) = A dx^2 + 2 B dx dy + C dy^2 over the block's rectangle of pixel centres (0 when the centre
+  // lies inside, otherwise attained on one of the four edges, where q is a 1-D parabola) must not
+  // exceed k. Rotated, elongated footprints fill their bounding box poorly, so this removes
+  // another share of the (entry, block) pairs. The continuous minimum is <= the minimum over the
+  // pixels and the comparison carries a 1 % + 0.05 margin (fp32 cancellation in q stays below
+  // 1e-6 x the 3 terms <= 300 k), so the test remains conservative.
+  const float cx = xy.x - tile_x0, cy = xy.y - tile_y0;   // centre in tile-local pixel coordinates
+  const float inv_A = 1.f / A, inv_C = 1.f / C;
+  const float k_lim = k * 1.01f + 0.05f;
   unsigned mask = 0u;
 #pragma unroll
   for (int by = 0; by < NBY; ++by) {
@@ -386,7 +396,24 @@ __device__ __forceinline__ unsigned footprint_mask(const float2 xy, const float4
 #pragma unroll
     for (int bx = 0; bx < NBX; ++bx) {
       const bool xtest = lo_x <= (float)(bx * BW + BW - 1) && hi_x >= (float)(bx * BW);
-      if (ytest && xtest) mask |= 1u << (by * NBX + bx);
+      if (ytest && xtest) {
+        const float x0 = (float)(bx * BW) - cx, x1 = (float)(bx * BW + BW - 1) - cx;
+        const float y0 = (float)(by * BH) - cy, y1 = (float)(by * BH + BH - 1) - cy;
+        bool hit = x0 <= 0.f && x1 >= 0.f && y0 <= 0.f && y1 >= 0.f;
+        if (!hit) {
+          auto on_vertical = [&](float xe) {   // min over y in [y0, y1] at x = xe
+            const float ys = fminf(fmaxf(-B * xe * inv_C, y0), y1);
+            return (A * xe + 2.f * B * ys) * xe + C * ys * ys;
+          };
+          auto on_horizontal = [&](float ye) {
+            const float xs = fminf(fmaxf(-B * ye * inv_A, x0), x1);
+            return (C * ye + 2.f * B * xs) * ye + A * xs * xs;
+          };
+          const float q = fminf(fminf(on_vertical(x0), on_vertical(x1)), fminf(on_horizontal(y0), on_horizontal(y1)));
+          hit = !(q > k_lim);   // NaN counts as a hit
+        }
+        if (hit) mask |= 1u << (by * NBX + bx);
+      }
     }
   }
   return mask;
