@@ -304,9 +304,10 @@ template <bool TO_TILE>
 __device__ __forceinline__ void warp_rows_copy(float* tile, int pitch, int col0, int width, float* run, int count,
                                                unsigned lane) {
   const uint32_t inv = ((1u << 20) + (uint32_t)width - 1u) / (uint32_t)width;
-  auto slot = [&](int e) -> float& {
+  auto offset_of = [&](int e, int& k) -> int {   // tile offset of element e; k = its column in the row
     const int r = (int)(((uint32_t)e * inv) >> 20);
-    return tile[r * pitch + col0 + (e - r * width)];
+    k = e - r * width;
+    return r * pitch + col0 + k;
   };
   int done = 0;
   if ((reinterpret_cast<uintptr_t>(run) & 15u) == 0) {
@@ -314,19 +315,28 @@ __device__ __forceinline__ void warp_rows_copy(float* tile, int pitch, int col0,
     float4* run4 = reinterpret_cast<float4*>(run);
 #pragma unroll 4
     for (int f = (int)lane; f < nvec; f += 32) {
+      // one division for the first component, the other three step along (and across) the rows
+      int k;
+      int o0 = offset_of(4 * f, k), o1, o2, o3;
+      const int wrap = pitch - width;   // extra tile offset when a component starts the next row
+      ++k; o1 = o0 + 1; if (k >= width) { k -= width; o1 += wrap; }
+      ++k; o2 = o1 + 1; if (k >= width) { k -= width; o2 += wrap; }
+      ++k; o3 = o2 + 1; if (k >= width) { k -= width; o3 += wrap; }
       if (TO_TILE) {
         const float4 v = __ldg(run4 + f);
-        slot(4 * f) = v.x; slot(4 * f + 1) = v.y; slot(4 * f + 2) = v.z; slot(4 * f + 3) = v.w;
+        tile[o0] = v.x; tile[o1] = v.y; tile[o2] = v.z; tile[o3] = v.w;
       } else {
-        run4[f] = make_float4(slot(4 * f), slot(4 * f + 1), slot(4 * f + 2), slot(4 * f + 3));
+        run4[f] = make_float4(tile[o0], tile[o1], tile[o2], tile[o3]);
       }
     }
     done = nvec << 2;
   }
 #pragma unroll 4
   for (int e = done + (int)lane; e < count; e += 32) {
-    if (TO_TILE) slot(e) = __ldg(run + e);
-    else run[e] = slot(e);
+    int k;
+    const int o = offset_of(e, k);
+    if (TO_TILE) tile[o] = __ldg(run + e);
+    else run[e] = tile[o];
   }
 }
 
