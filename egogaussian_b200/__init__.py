@@ -3,8 +3,9 @@
 Layout (only what the hot path needs):
   csrc/                         CUDA kernels (sm_100a), the C-ABI and the torch binding
   diff_gaussian_rasterization/  host-side mirror of the reference's Python interface
+  gaussian_renderer.py          render() mirror; activations / covariance and the raw-parameter rasterizer
+  loss_utils.py                 l1_loss / ssim / image_loss mirrors on the fused loss kernels
   cabi.py                       ctypes view of include/egs_rasterizer.h (tests, bench)
-  optim.py                      fused Adam (+ rigid SE(3)) step on top of the C-ABI
   parallel.py                   view-data-parallel gradient all-reduce (torch.distributed / NCCL)
   scenes.py                     seeded synthetic scenes and cameras
   build.py                      in-tree sm_100a build
