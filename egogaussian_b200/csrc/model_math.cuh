@@ -224,10 +224,17 @@ __device__ __forceinline__ void stage_rotations(const RawModel& a, float* s_rot)
   else if (threadIdx.x < 18) s_rot[threadIdx.x] = a.train_R ? a.train_R[threadIdx.x - 9] : 0.f;
 }
 
-// Forward of one row: frame, final factor, six covariance entries.
+// Forward of one row: frame, final factor, six covariance entries. The second form takes the raw
+// scale and quaternion from registers (callers that issue their loads early).
+__device__ __forceinline__ void raw_covariance_from(const RawModel& a, int i, const float s_raw[3], const float4 q_raw,
+                                                    const float* s_rot, float cov6[6]);
 __device__ __forceinline__ void raw_covariance(const RawModel& a, int i, const float* s_rot, float cov6[6]) {
   const float s_raw[3] = {a.scaling_raw[3 * i], a.scaling_raw[3 * i + 1], a.scaling_raw[3 * i + 2]};
   const float4 q_raw = reinterpret_cast<const float4*>(a.rotation_raw)[i];
+  raw_covariance_from(a, i, s_raw, q_raw, s_rot, cov6);
+}
+__device__ __forceinline__ void raw_covariance_from(const RawModel& a, int i, const float s_raw[3], const float4 q_raw,
+                                                    const float* s_rot, float cov6[6]) {
   RawFrame f;
   raw_frame(s_raw, q_raw, a.mod, f);
   M33 L = frame_factor(f);
@@ -313,20 +320,30 @@ __device__ __forceinline__ void warp_rows_copy(float* tile, int pitch, int col0,
   if ((reinterpret_cast<uintptr_t>(run) & 15u) == 0) {
     const int nvec = count >> 2;
     float4* run4 = reinterpret_cast<float4*>(run);
-#pragma unroll 4
-    for (int f = (int)lane; f < nvec; f += 32) {
-      // one division for the first component, the other three step along (and across) the rows
-      int k;
-      int o0 = offset_of(4 * f, k), o1, o2, o3;
-      const int wrap = pitch - width;   // extra tile offset when a component starts the next row
-      ++k; o1 = o0 + 1; if (k >= width) { k -= width; o1 += wrap; }
-      ++k; o2 = o1 + 1; if (k >= width) { k -= width; o2 += wrap; }
-      ++k; o3 = o2 + 1; if (k >= width) { k -= width; o3 += wrap; }
+    constexpr int GROUP = 4;   // float4 loads issued back to back before any of them is used
+    for (int f0 = (int)lane; f0 < nvec; f0 += 32 * GROUP) {
+      float4 v[GROUP];
       if (TO_TILE) {
-        const float4 v = __ldg(run4 + f);
-        tile[o0] = v.x; tile[o1] = v.y; tile[o2] = v.z; tile[o3] = v.w;
-      } else {
-        run4[f] = make_float4(tile[o0], tile[o1], tile[o2], tile[o3]);
+#pragma unroll
+        for (int j = 0; j < GROUP; ++j)
+          if (f0 + 32 * j < nvec) v[j] = __ldg(run4 + f0 + 32 * j);
+      }
+#pragma unroll
+      for (int j = 0; j < GROUP; ++j) {
+        const int f = f0 + 32 * j;
+        if (f >= nvec) break;
+        // one division for the first component, the other three step along (and across) the rows
+        int k;
+        int o0 = offset_of(4 * f, k), o1, o2, o3;
+        const int wrap = pitch - width;   // extra tile offset when a component starts the next row
+        ++k; o1 = o0 + 1; if (k >= width) { k -= width; o1 += wrap; }
+        ++k; o2 = o1 + 1; if (k >= width) { k -= width; o2 += wrap; }
+        ++k; o3 = o2 + 1; if (k >= width) { k -= width; o3 += wrap; }
+        if (TO_TILE) {
+          tile[o0] = v[j].x; tile[o1] = v[j].y; tile[o2] = v[j].z; tile[o3] = v[j].w;
+        } else {
+          run4[f] = make_float4(tile[o0], tile[o1], tile[o2], tile[o3]);
+        }
       }
     }
     done = nvec << 2;
@@ -337,6 +354,29 @@ __device__ __forceinline__ void warp_rows_copy(float* tile, int pitch, int col0,
     const int o = offset_of(e, k);
     if (TO_TILE) tile[o] = __ldg(run + e);
     else run[e] = tile[o];
+  }
+}
+
+// Stage the contiguous SH rows of a warp's Gaussians ([rows][48] floats, 16-byte aligned) into a
+// pitched shared tile. The loads go out in groups of six per lane before any is consumed: a loop
+// that loads and stores one float4 per trip exposes the full DRAM latency twelve times per warp,
+// and that latency chain, not bandwidth, was what bounded both preprocess kernels.
+__device__ __forceinline__ void stage_rows48(float* tile, int pitch, const float4* __restrict__ src, int rows,
+                                             unsigned lane) {
+  constexpr int PER_ROW = 12, GROUP = 6;
+  const int nvec = rows * PER_ROW;
+  for (int f0 = (int)lane; f0 < nvec; f0 += 32 * GROUP) {
+    float4 v[GROUP];
+#pragma unroll
+    for (int j = 0; j < GROUP; ++j)
+      if (f0 + 32 * j < nvec) v[j] = __ldg(src + f0 + 32 * j);
+#pragma unroll
+    for (int j = 0; j < GROUP; ++j) {
+      const int f = f0 + 32 * j;
+      if (f >= nvec) break;
+      float* d = tile + (f / PER_ROW) * pitch + (f % PER_ROW) * 4;
+      d[0] = v[j].x; d[1] = v[j].y; d[2] = v[j].z; d[3] = v[j].w;
+    }
   }
 }
 

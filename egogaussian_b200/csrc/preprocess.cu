@@ -147,6 +147,26 @@ preprocess_forward_kernel(RawModel raw, int P, int D, int M, const float* __rest
 
   const int idx = blockIdx.x * blockDim.x + threadIdx.x;
   const float* sh_row = nullptr;
+
+  // Issue this Gaussian's own loads before the SH rows are staged, so that they are in flight
+  // together with the 6 KB the warp is about to pull in (ncu: the kernel waits on memory, not on
+  // issue slots). g[] holds raw scale + quaternion, scale + quaternion, or the six covariance entries.
+  float3 p_orig = make_float3(0.f, 0.f, 0.f);
+  float g[7] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+  float opacity_in = 0.f;
+  if (idx < P) {
+    p_orig = make_float3(means3D[3 * idx], means3D[3 * idx + 1], means3D[3 * idx + 2]);
+    if (RAW || cov3D_precomp == nullptr) {
+      const float* sc = RAW ? raw.scaling_raw : scales;
+      const float4 q = reinterpret_cast<const float4*>(RAW ? raw.rotation_raw : rotations)[idx];
+      g[0] = sc[3 * idx]; g[1] = sc[3 * idx + 1]; g[2] = sc[3 * idx + 2];
+      g[3] = q.x; g[4] = q.y; g[5] = q.z; g[6] = q.w;
+    } else {
+#pragma unroll
+      for (int k = 0; k < 6; ++k) g[k] = cov3D_precomp[6 * idx + k];
+    }
+    opacity_in = RAW ? raw.opacity_raw[idx] : opacities[idx];
+  }
   if (SH_MODE == 2) {
     const unsigned lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const int first = blockIdx.x * blockDim.x + warp * 32;
@@ -168,12 +188,7 @@ preprocess_forward_kernel(RawModel raw, int P, int D, int M, const float* __rest
     const int rows = min(32, P - first);
     float* tile = s_sh + warp * 32 * PF_SH_PITCH;
     if (rows > 0) {
-      const float4* src = reinterpret_cast<const float4*>(shs + (size_t)first * PF_SH_ROW);
-      for (int f = lane; f < rows * (PF_SH_ROW / 4); f += 32) {
-        const float4 v = __ldg(src + f);
-        float* d = tile + (f / (PF_SH_ROW / 4)) * PF_SH_PITCH + (f % (PF_SH_ROW / 4)) * 4;
-        d[0] = v.x; d[1] = v.y; d[2] = v.z; d[3] = v.w;
-      }
+      stage_rows48(tile, PF_SH_PITCH, reinterpret_cast<const float4*>(shs + (size_t)first * PF_SH_ROW), rows, lane);
     }
     __syncwarp();
     sh_row = tile + lane * PF_SH_PITCH;
@@ -185,7 +200,6 @@ preprocess_forward_kernel(RawModel raw, int P, int D, int M, const float* __rest
   int radius_out = 0;
   uint32_t tiles_out = 0;
 
-  const float3 p_orig = make_float3(means3D[3 * idx], means3D[3 * idx + 1], means3D[3 * idx + 2]);
   const float3 p_view = xform_point_4x3(p_orig, s_view);
 
   // near culling: z_view <= 0.2 (auxiliary.h:150); the x/y frustum test is disabled there too
@@ -198,14 +212,12 @@ preprocess_forward_kernel(RawModel raw, int P, int D, int M, const float* __rest
 
     float cov6[6];
     if (RAW) {
-      raw_covariance(raw, idx, s_rot, cov6);
+      raw_covariance_from(raw, idx, g, make_float4(g[3], g[4], g[5], g[6]), s_rot, cov6);
     } else if (cov3D_precomp != nullptr) {
 #pragma unroll
-      for (int k = 0; k < 6; ++k) cov6[k] = cov3D_precomp[6 * idx + k];
+      for (int k = 0; k < 6; ++k) cov6[k] = g[k];
     } else {
-      const float3 s = make_float3(scales[3 * idx], scales[3 * idx + 1], scales[3 * idx + 2]);
-      const float4 q = reinterpret_cast<const float4*>(rotations)[idx];
-      cov3d_from_scale_rot(s, scale_modifier, q, cov6);
+      cov3d_from_scale_rot(make_float3(g[0], g[1], g[2]), scale_modifier, make_float4(g[3], g[4], g[5], g[6]), cov6);
     }
 
     const float3 cov = cov2d_ewa(p_orig, focal_x, focal_y, tan_fovx, tan_fovy, cov6, s_view);
@@ -235,7 +247,7 @@ preprocess_forward_kernel(RawModel raw, int P, int D, int M, const float* __rest
         }
         depths[idx] = p_view.z;
         means2D[idx] = point_image;
-        const float opacity = RAW ? sigmoid_fwd(raw.opacity_raw[idx]) : opacities[idx];
+        const float opacity = RAW ? sigmoid_fwd(opacity_in) : opacity_in;
         conic_opacity[idx] = make_float4(conic.x, conic.y, conic.z, opacity);
         rgb_depth[idx] = make_float4(rgb.x, rgb.y, rgb.z, p_view.z);
         radius_out = (int)my_radius;

@@ -434,13 +434,7 @@ preprocess_backward_kernel(RawModel raw, EgsModelGrads rg, int P, int D, int M, 
     const int wrest = 3 * M - 3;
     if (rows > 0) {
       if (SH_MODE == 1) {   // one contiguous run of rows * 48 floats
-        const float4* src = reinterpret_cast<const float4*>(shs + (size_t)first * SH_ROW);
-        for (int f = lane; f < rows * (SH_ROW / 4); f += 32) {
-          const float4 v = __ldg(src + f);
-          const int row = f / (SH_ROW / 4), k = (f % (SH_ROW / 4)) * 4;
-          float* d = tile + row * SH_PITCH + k;
-          d[0] = v.x; d[1] = v.y; d[2] = v.z; d[3] = v.w;
-        }
+        stage_rows48(tile, SH_PITCH, reinterpret_cast<const float4*>(shs + (size_t)first * SH_ROW), rows, lane);
       } else {              // two contiguous runs: rows * 3 and rows * (3M - 3) floats
         warp_rows_copy<true>(tile, SH_PITCH, 0, 3, const_cast<float*>(raw.features_dc) + (size_t)first * 3,
                              rows * 3, lane);
