@@ -380,6 +380,27 @@ __device__ __forceinline__ void stage_rows48(float* tile, int pitch, const float
   }
 }
 
+// The same staging with asynchronous copies (cp.async, 4 bytes each, global -> shared without a
+// register in between): a lane queues all of its elements at once, so the whole run of a warp is in
+// flight together and the queue depth does not cost registers; the odd pitch keeps the later
+// row-wise reads conflict-free (16-byte copies would need 16-byte aligned rows). Call
+// stage_rows_wait() before the tile is read.
+__device__ __forceinline__ void stage_rows_async(float* tile, int pitch, int col0, int width, const float* run,
+                                                 int count, unsigned lane) {
+  const uint32_t inv = ((1u << 20) + (uint32_t)width - 1u) / (uint32_t)width;
+  const uint32_t base = (uint32_t)__cvta_generic_to_shared(tile);
+#pragma unroll 4
+  for (int e = (int)lane; e < count; e += 32) {
+    const int r = (int)(((uint32_t)e * inv) >> 20);
+    const uint32_t dst = base + 4u * (uint32_t)(r * pitch + col0 + (e - r * width));
+    asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"(dst), "l"(run + e) : "memory");
+  }
+}
+__device__ __forceinline__ void stage_rows_wait() {
+  asm volatile("cp.async.commit_group;\ncp.async.wait_group 0;" ::: "memory");
+  __syncwarp();
+}
+
 // torch.sigmoid and its autograd formula grad * (1 - y) * y
 __device__ __forceinline__ float sigmoid_fwd(float x) { return 1.f / (1.f + expf(-x)); }
 __device__ __forceinline__ float sigmoid_bwd(float y, float g) { return g * (1.f - y) * y; }

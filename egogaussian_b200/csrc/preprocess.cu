@@ -174,13 +174,11 @@ preprocess_forward_kernel(RawModel raw, int P, int D, int M, const float* __rest
     float* tile = s_sh + warp * 32 * PF_SH_PITCH;
     if (rows > 0) {
       const int wrest = 3 * M - 3;
-      warp_rows_copy<true>(tile, PF_SH_PITCH, 0, 3, const_cast<float*>(raw.features_dc) + (size_t)first * 3,
-                           rows * 3, lane);
+      stage_rows_async(tile, PF_SH_PITCH, 0, 3, raw.features_dc + (size_t)first * 3, rows * 3, lane);
       if (wrest > 0)
-        warp_rows_copy<true>(tile, PF_SH_PITCH, 3, wrest,
-                             const_cast<float*>(raw.features_rest) + (size_t)first * wrest, rows * wrest, lane);
+        stage_rows_async(tile, PF_SH_PITCH, 3, wrest, raw.features_rest + (size_t)first * wrest, rows * wrest, lane);
     }
-    __syncwarp();
+    stage_rows_wait();
     sh_row = tile + lane * PF_SH_PITCH;
   } else if (SH_MODE == 1) {
     const unsigned lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
@@ -188,9 +186,9 @@ preprocess_forward_kernel(RawModel raw, int P, int D, int M, const float* __rest
     const int rows = min(32, P - first);
     float* tile = s_sh + warp * 32 * PF_SH_PITCH;
     if (rows > 0) {
-      stage_rows48(tile, PF_SH_PITCH, reinterpret_cast<const float4*>(shs + (size_t)first * PF_SH_ROW), rows, lane);
+      stage_rows_async(tile, PF_SH_PITCH, 0, PF_SH_ROW, shs + (size_t)first * PF_SH_ROW, rows * PF_SH_ROW, lane);
     }
-    __syncwarp();
+    stage_rows_wait();
     sh_row = tile + lane * PF_SH_PITCH;
   } else if (shs != nullptr && idx < P) {
     sh_row = shs + (size_t)idx * M * 3;

@@ -434,16 +434,14 @@ preprocess_backward_kernel(RawModel raw, EgsModelGrads rg, int P, int D, int M, 
     const int wrest = 3 * M - 3;
     if (rows > 0) {
       if (SH_MODE == 1) {   // one contiguous run of rows * 48 floats
-        stage_rows48(tile, SH_PITCH, reinterpret_cast<const float4*>(shs + (size_t)first * SH_ROW), rows, lane);
+        stage_rows_async(tile, SH_PITCH, 0, SH_ROW, shs + (size_t)first * SH_ROW, rows * SH_ROW, lane);
       } else {              // two contiguous runs: rows * 3 and rows * (3M - 3) floats
-        warp_rows_copy<true>(tile, SH_PITCH, 0, 3, const_cast<float*>(raw.features_dc) + (size_t)first * 3,
-                             rows * 3, lane);
+        stage_rows_async(tile, SH_PITCH, 0, 3, raw.features_dc + (size_t)first * 3, rows * 3, lane);
         if (wrest > 0)
-          warp_rows_copy<true>(tile, SH_PITCH, 3, wrest,
-                               const_cast<float*>(raw.features_rest) + (size_t)first * wrest, rows * wrest, lane);
+          stage_rows_async(tile, SH_PITCH, 3, wrest, raw.features_rest + (size_t)first * wrest, rows * wrest, lane);
       }
     }
-    __syncwarp();
+    stage_rows_wait();
     if (idx < P) {
       float* row = tile + lane * SH_PITCH;
       gaussian_backward<RAW>(idx, D, M, means3D, radii, row, row, true, EGS_GB_TAIL);
