@@ -357,30 +357,7 @@ __device__ __forceinline__ void warp_rows_copy(float* tile, int pitch, int col0,
   }
 }
 
-// Stage the contiguous SH rows of a warp's Gaussians ([rows][48] floats, 16-byte aligned) into a
-// pitched shared tile. The loads go out in groups of six per lane before any is consumed: a loop
-// that loads and stores one float4 per trip exposes the full DRAM latency twelve times per warp,
-// and that latency chain, not bandwidth, was what bounded both preprocess kernels.
-__device__ __forceinline__ void stage_rows48(float* tile, int pitch, const float4* __restrict__ src, int rows,
-                                             unsigned lane) {
-  constexpr int PER_ROW = 12, GROUP = 6;
-  const int nvec = rows * PER_ROW;
-  for (int f0 = (int)lane; f0 < nvec; f0 += 32 * GROUP) {
-    float4 v[GROUP];
-#pragma unroll
-    for (int j = 0; j < GROUP; ++j)
-      if (f0 + 32 * j < nvec) v[j] = __ldg(src + f0 + 32 * j);
-#pragma unroll
-    for (int j = 0; j < GROUP; ++j) {
-      const int f = f0 + 32 * j;
-      if (f >= nvec) break;
-      float* d = tile + (f / PER_ROW) * pitch + (f % PER_ROW) * 4;
-      d[0] = v[j].x; d[1] = v[j].y; d[2] = v[j].z; d[3] = v[j].w;
-    }
-  }
-}
-
-// The same staging with asynchronous copies (cp.async, 4 bytes each, global -> shared without a
+// Staging of such rows with asynchronous copies (cp.async, 4 bytes each, global -> shared without a
 // register in between): a lane queues all of its elements at once, so the whole run of a warp is in
 // flight together and the queue depth does not cost registers; the odd pitch keeps the later
 // row-wise reads conflict-free (16-byte copies would need 16-byte aligned rows). Call
