@@ -8,7 +8,8 @@
 //     (16 B) in shared memory, so the inner loop never touches global memory (the reference
 //     gathers colour and depth from global per blended fragment);
 //   * each warp covers an 8x4 pixel block instead of 16x2, which makes whole-warp skips and
-//     whole-warp termination more likely; a warp whose 32 pixels are done skips the inner loop;
+//     whole-warp termination more likely; a warp whose 32 pixels are done skips the inner loop,
+//     and a warp only visits the list entries whose footprint can reach its block at all;
 //   * the per-pixel arithmetic keeps the reference's expression shapes, because the alpha and
 //     transmittance thresholds make the image sensitive to the last bit of `power`.
 #include "common.cuh"
@@ -20,102 +21,13 @@ namespace egs {
 
 constexpr int BLEND_BATCH = 256;
 
-__global__ void __launch_bounds__(TILE_PIXELS)
-blend_forward_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__ point_list,
-                     int W, int H, int grid_x, const float2* __restrict__ means2D,
-                     const float4* __restrict__ conic_opacity, const float4* __restrict__ rgb_depth,
-                     const float* __restrict__ bg_color, float* __restrict__ out_color,
-                     float* __restrict__ out_depth, float* __restrict__ out_alpha,
-                     uint32_t* __restrict__ n_contrib) {
-  __shared__ float2 s_xy[BLEND_BATCH];
-  __shared__ float4 s_co[BLEND_BATCH];
-  __shared__ float4 s_cd[BLEND_BATCH];
-  __shared__ unsigned char s_mask[BLEND_BATCH];   // bit w: the entry can reach warp w's 8x4 pixels
-
-  const unsigned tid = threadIdx.x;
-  const unsigned warp = tid >> 5, lane = tid & 31;
-  // 8 warps as a 2 (x) by 4 (y) arrangement of 8x4-pixel blocks
-  const unsigned lx = (warp & 1) * 8 + (lane & 7);
-  const unsigned ly = (warp >> 1) * 4 + (lane >> 3);
-  const unsigned px = blockIdx.x * TILE_X + lx;
-  const unsigned py = blockIdx.y * TILE_Y + ly;
-  const bool inside = px < (unsigned)W && py < (unsigned)H;
-  const uint32_t pix_id = (uint32_t)W * py + px;
-  const float2 pixf = make_float2((float)px, (float)py);
-
-  const uint2 range = ranges[blockIdx.y * grid_x + blockIdx.x];
-  const int total = (int)(range.y - range.x);
-  const int rounds = (total + BLEND_BATCH - 1) / BLEND_BATCH;
-  int to_do = total;
-
-  bool done = !inside;
-  float T = 1.0f;
-  uint32_t last_contributor = 0;
-  const float tile_x0 = (float)(blockIdx.x * TILE_X), tile_y0 = (float)(blockIdx.y * TILE_Y);
-  float C0 = 0.f, C1 = 0.f, C2 = 0.f, weight = 0.f, D = 0.f;
-
-  for (int r = 0; r < rounds; ++r, to_do -= BLEND_BATCH) {
-    if (__syncthreads_count(done) == TILE_PIXELS) break;
-    const int progress = r * BLEND_BATCH + (int)tid;
-    if (progress < total) {
-      const uint32_t id = point_list[range.x + progress];
-      const float2 xy = means2D[id];
-      const float4 co = conic_opacity[id];
-      s_xy[tid] = xy;
-      s_co[tid] = co;
-      s_cd[tid] = rgb_depth[id];
-      s_mask[tid] = (unsigned char)footprint_mask<8, 4>(xy, co, tile_x0, tile_y0);
-    }
-    __syncthreads();
-    if (__all_sync(0xffffffffu, done)) continue;  // warp-uniform: nothing left for these 32 pixels
-
-    const int n = min(BLEND_BATCH, to_do);
-    for (int j = 0; !done && j < n; ++j) {
-      // one byte decides for the whole warp whether this entry can touch its 8x4 pixels at all
-      if (!((s_mask[j] >> warp) & 1u)) continue;
-      const float2 xy = s_xy[j];
-      const float2 d = make_float2(xy.x - pixf.x, xy.y - pixf.y);
-      const float4 con_o = s_co[j];
-      const float power = -0.5f * (con_o.x * d.x * d.x + con_o.z * d.y * d.y) - con_o.y * d.x * d.y;
-      if (power > 0.0f) continue;
-      const float alpha = min(0.99f, con_o.w * expf(power));
-      if (alpha < 1.0f / 255.0f) continue;
-      const float test_T = T * (1 - alpha);
-      if (test_T < 0.0001f) {
-        done = true;
-        continue;
-      }
-      const float4 cd = s_cd[j];
-      C0 += cd.x * alpha * T;
-      C1 += cd.y * alpha * T;
-      C2 += cd.z * alpha * T;
-      weight += alpha * T;
-      D += cd.w * alpha * T;
-      T = test_T;
-      last_contributor = (uint32_t)(r * BLEND_BATCH + j + 1);   // 1-based position in the tile's list
-    }
-  }
-
-  if (inside) {
-    const size_t plane = (size_t)H * W;
-    n_contrib[pix_id] = last_contributor;
-    out_color[pix_id] = C0 + T * bg_color[0];
-    out_color[plane + pix_id] = C1 + T * bg_color[1];
-    out_color[2 * plane + pix_id] = C2 + T * bg_color[2];
-    out_alpha[pix_id] = weight;
-    out_depth[pix_id] = D;
-  }
-}
-
-// ---------------------------------------------------------------------------------------------
-// v3 (default): the same blend, driven by per-warp bit lists instead of a per-entry mask test
-// ---------------------------------------------------------------------------------------------
-// The staging warps turn the footprint masks of their 32 entries into one 32-bit word per pixel
-// warp (eight ballots), so a pixel warp walks only the entries that can reach its 8x4 block: it
-// pops set bits in list order and never issues an instruction for the others (in the kernel above
-// a skipped entry still costs ~13 instructions, and more than half of all entries are skipped).
-// Shared memory is addressed through window addresses formed once (see lds_f4). The arithmetic of
-// a blended fragment is unchanged, so the images stay bit-identical.
+// The staging warps turn the footprint masks of their 32 entries (common.cuh: footprint_mask) into
+// one 32-bit word per pixel warp (eight ballots), so a pixel warp walks only the entries that can
+// reach its 8x4 block: it pops set bits in list order and never issues an instruction for the
+// others (in the first version, which tested one mask byte per entry, a skipped entry still cost
+// ~13 instructions, and more than half of all entries are skipped: 0.318 -> 0.245 ms). Shared
+// memory is addressed through window addresses formed once (see lds_f4). The arithmetic of a
+// blended fragment keeps the reference's expression shapes, so the images are bit-identical.
 __global__ void __launch_bounds__(TILE_PIXELS)
 blend_forward3_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__ point_list,
                       int W, int H, int grid_x, const float2* __restrict__ means2D,
@@ -346,16 +258,12 @@ int launch_blend_forward(const EgsForwardArgs& a, const GeomPtrs& g, const uint3
                          const ImagePtrs& im, cudaStream_t stream) {
   const dim3 grid(tiles_x(a.width), tiles_y(a.height), 1);
   StageTimer timer(stream, ST_BLEND_FWD);
-  // Default: one pixel per thread. EGS_FWD=v2 selects the two-pixels-per-thread kernel; results are
-  // bit-identical, and on B200 at 1M Gaussians v2 measured 5 % slower (0.364 vs 0.348 ms): the
-  // forward loop is already at its instruction floor and v2 only adds divergence per warp.
+  // Default: one pixel per thread, per-warp bit lists. EGS_FWD=v2 selects the older
+  // two-pixels-per-thread kernel without bit lists, kept as an independent implementation for
+  // tests/test_parity_gpu.py::test_kernel_variants_agree (bit-identical results, slower).
   const char* sel = getenv("EGS_FWD");
-  if (!sel || strcmp(sel, "v3") == 0) {
+  if (!(sel && strcmp(sel, "v2") == 0)) {
     blend_forward3_kernel<<<grid, TILE_PIXELS, 0, stream>>>(
-        im.ranges, point_list, a.width, a.height, (int)grid.x, g.means2D, g.conic_opacity,
-        g.rgb_depth, a.background, a.out_color, a.out_depth, a.out_alpha, im.n_contrib);
-  } else if (strcmp(sel, "v2") != 0) {
-    blend_forward_kernel<<<grid, TILE_PIXELS, 0, stream>>>(
         im.ranges, point_list, a.width, a.height, (int)grid.x, g.means2D, g.conic_opacity,
         g.rgb_depth, a.background, a.out_color, a.out_depth, a.out_alpha, im.n_contrib);
   } else {
