@@ -17,7 +17,7 @@ STAGE_OF = {
     "duplicate_words_kernel": "duplicate_keys", "bucket_histogram_kernel": "duplicate_keys",
     "duplicate_packed_kernel": "duplicate_keys", "msd_partition_kernel": "sort_histogram",
     "bucket_sort_kernel": "sort_passes", "packed_onesweep_kernel": "sort_passes",
-    "blend_forward_kernel": "blend_fwd", "blend_forward2_kernel": "blend_fwd",
+    "blend_forward3_kernel": "blend_fwd", "blend_forward2_kernel": "blend_fwd",
     "blend_backward_kernel": "blend_bwd", "blend_backward2_kernel": "blend_bwd",
     "preprocess_backward_kernel": "preprocess_bwd", "adam_multi_kernel": "adam",
 }
@@ -29,15 +29,23 @@ rows = list(csv.reader(io.StringIO(out)))
 hdr, units = rows[0], rows[1]
 kn, rd, wr = hdr.index("Kernel Name"), hdr.index("dram__bytes_read.sum"), hdr.index("dram__bytes_write.sum")
 scale = {"byte": 1.0, "Kbyte": 1e3, "Mbyte": 1e6, "Gbyte": 1e9}
+issue = hdr.index("smsp__issue_active.avg.pct_of_peak_sustained_active")
+active = hdr.index("sm__warps_active.avg.pct_of_peak_sustained_active")
 acc = defaultdict(list)
+util = defaultdict(list)
 for r in rows[2:]:
     name = r[kn].split("(")[0].split("<")[0].replace("void ", "").replace("egs::", "").strip()
     stage = STAGE_OF.get(name)
     if stage is None:
         continue
     acc[(stage, name)].append(float(r[rd]) * scale[units[rd]] + float(r[wr]) * scale[units[wr]])
+    util[(stage, name)].append((float(r[issue]), float(r[active])))
 result = {"source": rep, "unit": "bytes per launch (dram__bytes_read.sum + dram__bytes_write.sum)", "stages": {}}
 for (stage, name), v in sorted(acc.items()):
-    result["stages"].setdefault(stage, {})[name] = {"launches_captured": len(v), "bytes_per_launch": sum(v) / len(v)}
+    u = util[(stage, name)]
+    result["stages"].setdefault(stage, {})[name] = {
+        "launches_captured": len(v), "bytes_per_launch": sum(v) / len(v),
+        "issue_active_pct": round(sum(x[0] for x in u) / len(u), 1),     # smsp__issue_active, % of peak
+        "warps_active_pct": round(sum(x[1] for x in u) / len(u), 1)}     # achieved occupancy
 json.dump(result, open(dst, "w"), indent=1)
 print(json.dumps(result, indent=1))
