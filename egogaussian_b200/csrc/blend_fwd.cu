@@ -28,7 +28,7 @@ constexpr int BLEND_BATCH = 256;
 // ~13 instructions, and more than half of all entries are skipped: 0.318 -> 0.245 ms). Shared
 // memory is addressed through window addresses formed once (see lds_f4). The arithmetic of a
 // blended fragment keeps the reference's expression shapes, so the images are bit-identical.
-__global__ void __launch_bounds__(TILE_PIXELS)
+__global__ void __launch_bounds__(TILE_PIXELS, 6)
 blend_forward3_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__ point_list,
                       int W, int H, int grid_x, const float2* __restrict__ means2D,
                       const float4* __restrict__ conic_opacity, const float4* __restrict__ rgb_depth,
