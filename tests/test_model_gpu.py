@@ -122,7 +122,7 @@ class _Model:
                 "rot6d": self.trainable_object_move.obj_rotation_6d}
 
 
-@pytest.mark.parametrize("mode", ["static", "object_train", "override_color", "sh0"])
+@pytest.mark.parametrize("mode", ["static", "object_train", "override_color", "sh0", "full_size"])
 def test_fused_raw_rasterizer_equals_two_stage(mode, built, cuda_device):
     """egs_forward_raw / egs_backward_raw (activations inside the per-Gaussian kernels) against
     egs_model_forward -> egs_forward -> egs_backward -> egs_model_backward: the two share their
@@ -133,6 +133,8 @@ def test_fused_raw_rasterizer_equals_two_stage(mode, built, cuda_device):
     dev = cuda_device
     W, H, P = 320, 192, 20_011   # not a multiple of 32: the last warp stages a ragged run of SH rows
     deg = 0 if mode == "sh0" else (1 if mode == "override_color" else 2)
+    if mode == "full_size":      # BASELINE configs[2]: 1M Gaussians, SH3, 1280x720
+        W, H, P, deg = 1280, 720, 1_000_000, 3
     sc = scenes.make_scene(P, W, H, sh_degree=deg, seed=93).to(dev)
     cam = _Camera(sc.camera, W, H)
     gen = torch.Generator().manual_seed(94)
@@ -155,8 +157,12 @@ def test_fused_raw_rasterizer_equals_two_stage(mode, built, cuda_device):
     for k in ("render", "depth", "alpha", "radii"):
         assert torch.equal(a[k], b[k]), k
 
-    def close(x, y):   # the tile kernel's float atomics land in a different order on every run
-        return (x - y).abs().max().item() <= 2e-5 * y.abs().max().item()
+    # the tile kernel's float atomics land in a different order on every run; that noise grows with
+    # the number of fragments per Gaussian, so the 1M case gets the path's 1e-4 gradient tolerance
+    rtol = 1e-4 if mode == "full_size" else 2e-5
+
+    def close(x, y):
+        return (x - y).abs().max().item() <= rtol * y.abs().max().item()
     assert close(a["viewspace_points"].grad, b["viewspace_points"].grad)
     la, lb = pa.leaves(), pb.leaves()
     for k in la:
