@@ -4,6 +4,7 @@ Layout (only what the hot path needs):
   csrc/                         CUDA kernels (sm_100a), the C-ABI and the torch binding
   diff_gaussian_rasterization/  host-side mirror of the reference's Python interface
   gaussian_renderer.py          render() mirror; activations / covariance and the raw-parameter rasterizer
+  render_helper.py              get_render_label mirror (the trainers' per-iteration label render)
   loss_utils.py                 l1_loss / ssim / image_loss mirrors on the fused loss kernels
   cabi.py                       ctypes view of include/egs_rasterizer.h (tests, bench)
   parallel.py                   view-data-parallel gradient all-reduce (torch.distributed / NCCL)

@@ -180,6 +180,41 @@ def test_fused_raw_rasterizer_equals_two_stage(mode, built, cuda_device):
         assert close(color_leaf[True].grad, color_leaf[False].grad)
 
 
+def test_label_render_against_reference_rasterizer(built, cuda_device):
+    """get_render_label (gaussian_renderer/render_helper.py:58-66 mirror) against the same recipe fed
+    to the unmodified reference rasterizer: label image within 1e-5, gradient into the label within
+    1e-4 of its maximum, nothing else receives a gradient."""
+    from egogaussian_b200 import render_helper, scenes
+    from oracle import ref_dgr
+    if not ref_dgr.available():
+        pytest.skip("oracle/_ref not built")
+    dev = cuda_device
+    W, H, P = 320, 192, 12_345
+    sc = scenes.make_scene(P, W, H, sh_degree=0, seed=97).to(dev)
+    cam = _Camera(sc.camera, W, H)
+    gen = torch.Generator().manual_seed(98)
+    w = torch.randn(3, H, W, generator=gen).to(dev)
+    pc = _Model(sc, dev, 1)
+    pc._label = torch.rand(P, 1, generator=gen).to(dev).requires_grad_(True)
+    img = render_helper.get_render_label(cam, pc, sc.bg)
+    (img * w).sum().backward()
+    assert pc._xyz.grad is None and pc._scaling.grad is None and pc._opacity.grad is None
+
+    label_ref = pc._label.detach().clone().requires_grad_(True)
+    colors = torch.zeros(P, 3, device=dev)
+    colors = colors + label_ref            # the label in every channel, differentiable
+    rs = dict(bg=sc.bg, scale_modifier=1.0, viewmatrix=cam.world_view_transform, projmatrix=cam.full_proj_transform,
+              tanfovx=float(sc.camera.tanfovx), tanfovy=float(sc.camera.tanfovy), image_height=H, image_width=W,
+              sh_degree=0, campos=cam.camera_center)
+    ref_img, _, _, _ = ref_dgr.make_autograd_rasterizer()(
+        rs, means3D=pc._xyz.detach(), means2D=torch.zeros_like(pc._xyz), opacities=torch.sigmoid(pc._opacity).detach(),
+        colors_precomp=colors, scales=torch.exp(pc._scaling).detach(),
+        rotations=torch.nn.functional.normalize(pc._rotation).detach())
+    (ref_img * w).sum().backward()
+    assert (img - ref_img).abs().max().item() <= 1e-5
+    assert (pc._label.grad - label_ref.grad).abs().max().item() <= 1e-4 * label_ref.grad.abs().max().item()
+
+
 @pytest.mark.parametrize("mode", ["static", "object_train"])
 def test_render_mirror_equals_torch_glue(mode, built, cuda_device):
     """render() on raw parameters == the reference's glue (restated in torch, oracle/model_ref.py)
