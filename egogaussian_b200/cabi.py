@@ -55,7 +55,7 @@ class EgsBackwardArgs(C.Structure):
         ("dL_dmeans2D", c_float_p), ("dL_dcolors", c_float_p), ("dL_dopacity", c_float_p),
         ("dL_dmeans3D", c_float_p), ("dL_dcov3D", c_float_p), ("dL_dsh", c_float_p),
         ("dL_dscales", c_float_p), ("dL_drotations", c_float_p), ("debug", C.c_int),
-        ("binning_bytes", C.c_size_t),
+        ("binning_bytes", C.c_size_t), ("colors_only", C.c_int),
     ]
 
 

@@ -331,13 +331,19 @@ static int backward_impl(const char* who, const EgsBackwardArgs* args, const Egs
   }
   if (!a.means3D || !a.radii || !a.out_alpha || !a.geom_buffer || !a.image_buffer ||
       (a.num_rendered > 0 && !a.binning_buffer) || !a.dL_dout_color || !a.dL_dout_depth ||
-      !a.dL_dout_alpha || !a.scratch || !a.dL_dmeans2D || (!a.dL_dopacity && !model) || !a.dL_dmeans3D ||
+      !a.dL_dout_alpha || !a.scratch ||
+      (!a.colors_only && (!a.dL_dmeans2D || (!a.dL_dopacity && !model) || !a.dL_dmeans3D)) ||
       !a.background || !a.viewmatrix || !a.projmatrix || !a.campos) {
     set_error("%s: NULL required argument", who);
     return EGS_ERR_INVALID_ARGUMENT;
   }
-  if ((a.colors_precomp && !a.dL_dcolors) || (a.cov3D_precomp && !a.dL_dcov3D) || (a.shs && !a.dL_dsh) ||
-      (a.scales && (!a.dL_dscales || !a.dL_drotations))) {
+  if (a.colors_only && (!a.colors_precomp || model != nullptr)) {
+    set_error("%s: colors_only needs colors_precomp (and is not a raw-parameter mode)", who);
+    return EGS_ERR_INVALID_ARGUMENT;
+  }
+  if ((a.colors_precomp && !a.dL_dcolors) ||
+      (!a.colors_only && ((a.cov3D_precomp && !a.dL_dcov3D) || (a.shs && !a.dL_dsh) ||
+                          (a.scales && (!a.dL_dscales || !a.dL_drotations))))) {
     set_error("%s: missing gradient output for a provided input", who);
     return EGS_ERR_INVALID_ARGUMENT;
   }

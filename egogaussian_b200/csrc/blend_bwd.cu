@@ -305,7 +305,10 @@ __device__ __forceinline__ void pixel_init(PixelState& s, bool inside, uint32_t 
   s.bg_dot = bg[0] * s.dL_dpixel[0] + bg[1] * s.dL_dpixel[1] + bg[2] * s.dL_dpixel[2];
 }
 
-// one contributing fragment: advances the pixel's recurrences and adds its ten partial sums to q
+// one contributing fragment: advances the pixel's recurrences and adds its ten partial sums to q.
+// COLORS_ONLY (EgsBackwardArgs.colors_only): just the transmittance recurrence and the three colour
+// sums; nothing that feeds the geometry or opacity gradients is evaluated.
+template <bool COLORS_ONLY>
 __device__ __forceinline__ void fragment_backward(PixelState& s, float dx, float dy, float power,
                                                   const float4 a4, const float4 b4, const float4 c4,
                                                   float ddelx_dx, float ddely_dy, float (&q)[10]) {
@@ -315,6 +318,11 @@ __device__ __forceinline__ void fragment_backward(PixelState& s, float dx, float
   const float rcp = rcp_approx(1.f - alpha);
   s.T = s.T * rcp;
   const float w = alpha * s.T;
+  if (COLORS_ONLY) {
+#pragma unroll
+    for (int ch = 0; ch < 3; ++ch) q[7 + ch] += w * s.dL_dpixel[ch];
+    return;
+  }
   float dL_dopa = 0.0f;
   const float c[3] = {c4.x, c4.y, c4.z};
 #pragma unroll
@@ -348,6 +356,7 @@ __device__ __forceinline__ void fragment_backward(PixelState& s, float dx, float
   q[2] += G * dL_dopa;
 }
 
+template <bool COLORS_ONLY>
 __global__ void __launch_bounds__(BWD2_THREADS)
 blend_backward2_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__ point_list,
                        int W, int H, int grid_x, const float* __restrict__ bg_color,
@@ -464,8 +473,8 @@ blend_backward2_kernel(const uint2* __restrict__ ranges, const uint32_t* __restr
 #pragma unroll
       for (int k = 0; k < 10; ++k) q[k] = 0.f;
       const float4 c4 = lds_f4(a_c + 16u * j);
-      if (act0) fragment_backward(P0, dx0, dy0, power0, a4, b4, c4, ddelx_dx, ddely_dy, q);
-      if (act1) fragment_backward(P1, dx1, dy1, power1, a4, b4, c4, ddelx_dx, ddely_dy, q);
+      if (act0) fragment_backward<COLORS_ONLY>(P0, dx0, dy0, power0, a4, b4, c4, ddelx_dx, ddely_dy, q);
+      if (act1) fragment_backward<COLORS_ONLY>(P1, dx1, dy1, power1, a4, b4, c4, ddelx_dx, ddely_dy, q);
       const float total = warp_packed_reduce10(q, lane);
       if (i_add) sts_f32(a_acc + (uint32_t)(j * ACC_PITCH * 4), total);
       if (lane == 0) atomicOr(&s_hit[j], 1u << warp);
@@ -508,8 +517,13 @@ int launch_blend_backward(const EgsBackwardArgs& a, const GeomPtrs& g, const uin
         im.ranges, point_list, a.width, a.height, (int)grid.x, a.background, g.means2D,
         g.conic_opacity, g.rgb_depth, a.out_alpha, im.n_contrib, a.dL_dout_color, a.dL_dout_depth,
         a.dL_dout_alpha, s.acc);
+  } else if (a.colors_only) {
+    blend_backward2_kernel<true><<<grid, BWD2_THREADS, 0, stream>>>(
+        im.ranges, point_list, a.width, a.height, (int)grid.x, a.background, g.means2D,
+        g.conic_opacity, g.rgb_depth, a.out_alpha, im.n_contrib, a.dL_dout_color, a.dL_dout_depth,
+        a.dL_dout_alpha, s.acc);
   } else {
-    blend_backward2_kernel<<<grid, BWD2_THREADS, 0, stream>>>(
+    blend_backward2_kernel<false><<<grid, BWD2_THREADS, 0, stream>>>(
         im.ranges, point_list, a.width, a.height, (int)grid.x, a.background, g.means2D,
         g.conic_opacity, g.rgb_depth, a.out_alpha, im.n_contrib, a.dL_dout_color, a.dL_dout_depth,
         a.dL_dout_alpha, s.acc);

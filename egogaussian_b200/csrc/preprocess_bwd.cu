@@ -189,8 +189,16 @@ gaussian_backward(int idx, int D, int M, const float* __restrict__ means3D, cons
                   float* __restrict__ dL_dmeans3D, float* __restrict__ dL_dcov3D,
                   float* __restrict__ dL_dscales, float* __restrict__ dL_drot,
                   // raw-parameter mode (egs_backward_raw): gradients go to the raw tensors
-                  const RawModel& raw, const float* s_rot, const EgsModelGrads& rg, float* dT) {
+                  const RawModel& raw, const float* s_rot, const EgsModelGrads& rg, float* dT, bool colors_only) {
   constexpr bool raw_geom = RAW;
+  if (colors_only) {   // EgsBackwardArgs.colors_only: unpack the colour accumulators, nothing else
+    const bool seen = radii[idx] > 0;
+    const float4 a2 = seen ? acc[3 * (size_t)idx + 2] : make_float4(0.f, 0.f, 0.f, 0.f);
+    dL_dcolors[3 * idx + 0] = a2.x;
+    dL_dcolors[3 * idx + 1] = a2.y;
+    dL_dcolors[3 * idx + 2] = a2.z;
+    return;
+  }
   if (!(radii[idx] > 0)) {
     // culled: every gradient is zero
 #pragma unroll
@@ -403,7 +411,7 @@ preprocess_backward_kernel(RawModel raw, EgsModelGrads rg, int P, int D, int M, 
                            float* __restrict__ dL_dmeans2D, float* __restrict__ dL_dcolors,
                            float* __restrict__ dL_dopacity, float* __restrict__ dL_dmeans3D,
                            float* __restrict__ dL_dcov3D, float* __restrict__ dL_dsh,
-                           float* __restrict__ dL_dscales, float* __restrict__ dL_drot) {
+                           float* __restrict__ dL_dscales, float* __restrict__ dL_drot, bool colors_only) {
   __shared__ float view[16], proj[16], s_cam[3];
   __shared__ float s_sh[SH_MODE != 0 ? PB_WARPS * 32 * SH_PITCH : 1];
   __shared__ float s_rot[RAW ? 18 : 1];
@@ -424,7 +432,7 @@ preprocess_backward_kernel(RawModel raw, EgsModelGrads rg, int P, int D, int M, 
 #define EGS_GB_TAIL                                                                                          \
   clamped, scales, rotations, cov3D_precomp, colors_precomp, scale_modifier, view, proj, s_cam, h_x, h_y,     \
       tan_fovx, tan_fovy, acc, dL_dmeans2D, dL_dcolors, dL_dopacity, dL_dmeans3D, dL_dcov3D, dL_dscales,      \
-      dL_drot, raw, s_rot, rg, dT
+      dL_drot, raw, s_rot, rg, dT, colors_only
 
   if (SH_MODE != 0) {
     // rows [first, first + rows) of this warp
@@ -498,7 +506,7 @@ int launch_preprocess_backward(const EgsBackwardArgs& a, const EgsModelArgs* mod
   raw, rg, a.P, a.sh_degree, sh_coeffs, a.means3D, a.radii, a.shs, g.clamped, a.scales, a.rotations,         \
       a.cov3D_precomp, a.colors_precomp, a.scale_modifier, a.viewmatrix, a.projmatrix, a.campos,      \
       focal_x, focal_y, a.tan_fovx, a.tan_fovy, s.acc, a.dL_dmeans2D, a.dL_dcolors, a.dL_dopacity,    \
-      a.dL_dmeans3D, a.dL_dcov3D, a.dL_dsh, a.dL_dscales, a.dL_drotations
+      a.dL_dmeans3D, a.dL_dcov3D, a.dL_dsh, a.dL_dscales, a.dL_drotations, a.colors_only != 0
   if (split)
     preprocess_backward_kernel<2, true><<<blocks, PB_THREADS, 0, stream>>>(EGS_PB_ARGS);
   else if (model != nullptr)

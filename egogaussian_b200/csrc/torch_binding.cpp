@@ -138,7 +138,7 @@ rasterize_gaussians(const torch::Tensor& background, const torch::Tensor& means3
 
 std::tuple<torch::Tensor, torch::Tensor, torch::Tensor, torch::Tensor, torch::Tensor, torch::Tensor,
            torch::Tensor, torch::Tensor>
-rasterize_gaussians_backward(const torch::Tensor& background, const torch::Tensor& means3D,
+rasterize_backward_impl(bool colors_only, const torch::Tensor& background, const torch::Tensor& means3D,
                              const torch::Tensor& radii, const torch::Tensor& colors,
                              const torch::Tensor& scales, const torch::Tensor& rotations,
                              const float scale_modifier, const torch::Tensor& cov3D_precomp,
@@ -166,14 +166,16 @@ rasterize_gaussians_backward(const torch::Tensor& background, const torch::Tenso
 
   // outputs are fully written by the kernels: empty, not zeros (the reference zero-fills ten
   // tensors, rasterize_points.cu:158-167). Gradients of absent inputs are zero-size tensors.
-  torch::Tensor dL_dmeans3D = torch::empty({P, 3}, fopt);
-  torch::Tensor dL_dmeans2D = torch::empty({P, 3}, fopt);
-  torch::Tensor dL_dopacity = torch::empty({P, 1}, fopt);
+  TORCH_CHECK(!colors_only || has_colors, "colors-only backward needs colors_precomp");
+  const int64_t Pg = colors_only ? 0 : P;   // colors-only: no other gradient is produced
+  torch::Tensor dL_dmeans3D = torch::empty({Pg, 3}, fopt);
+  torch::Tensor dL_dmeans2D = torch::empty({Pg, 3}, fopt);
+  torch::Tensor dL_dopacity = torch::empty({Pg, 1}, fopt);
   torch::Tensor dL_dcolors = torch::empty({has_colors ? P : 0, EGS_NUM_CHANNELS}, fopt);
-  torch::Tensor dL_dcov3D = torch::empty({has_cov ? P : 0, 6}, fopt);
-  torch::Tensor dL_dsh = torch::empty({has_sh ? P : 0, M, 3}, fopt);
-  torch::Tensor dL_dscales = torch::empty({has_sr ? P : 0, 3}, fopt);
-  torch::Tensor dL_drotations = torch::empty({has_sr ? P : 0, 4}, fopt);
+  torch::Tensor dL_dcov3D = torch::empty({has_cov ? Pg : 0, 6}, fopt);
+  torch::Tensor dL_dsh = torch::empty({has_sh ? Pg : 0, M, 3}, fopt);
+  torch::Tensor dL_dscales = torch::empty({has_sr ? Pg : 0, 3}, fopt);
+  torch::Tensor dL_drotations = torch::empty({has_sr ? Pg : 0, 4}, fopt);
 
   if (P != 0) {
     torch::Tensor scratch = torch::empty({(int64_t)egs_backward_scratch_bytes(P)},
@@ -211,21 +213,41 @@ rasterize_gaussians_backward(const torch::Tensor& background, const torch::Tenso
     a.dL_dout_depth = req_ptr(dL_dout_depth, k[13], dev, "dL_dout_depth");
     a.dL_dout_alpha = req_ptr(dL_dout_alpha, k[14], dev, "dL_dout_alpha");
     a.scratch = scratch.data_ptr();
-    a.dL_dmeans2D = dL_dmeans2D.data_ptr<float>();
-    a.dL_dcolors = has_colors ? dL_dcolors.data_ptr<float>() : nullptr;
-    a.dL_dopacity = dL_dopacity.data_ptr<float>();
-    a.dL_dmeans3D = dL_dmeans3D.data_ptr<float>();
-    a.dL_dcov3D = has_cov ? dL_dcov3D.data_ptr<float>() : nullptr;
-    a.dL_dsh = has_sh ? dL_dsh.data_ptr<float>() : nullptr;
-    a.dL_dscales = has_sr ? dL_dscales.data_ptr<float>() : nullptr;
-    a.dL_drotations = has_sr ? dL_drotations.data_ptr<float>() : nullptr;
+    auto out = [](torch::Tensor& t) { return t.numel() ? t.data_ptr<float>() : nullptr; };
+    a.dL_dmeans2D = out(dL_dmeans2D);
+    a.dL_dcolors = out(dL_dcolors);
+    a.dL_dopacity = out(dL_dopacity);
+    a.dL_dmeans3D = out(dL_dmeans3D);
+    a.dL_dcov3D = out(dL_dcov3D);
+    a.dL_dsh = out(dL_dsh);
+    a.dL_dscales = out(dL_dscales);
+    a.dL_drotations = out(dL_drotations);
     a.debug = debug;
+    a.colors_only = colors_only ? 1 : 0;
     a.binning_bytes = (size_t)binningBuffer.numel();   // the blob may be laid out for a guessed capacity
     check(egs_backward(&a, at::cuda::getCurrentCUDAStream().stream()), "egs_backward");
   }
   return std::make_tuple(dL_dmeans2D, dL_dcolors, dL_dopacity, dL_dmeans3D, dL_dcov3D, dL_dsh,
                          dL_dscales, dL_drotations);
 }
+
+// the reference's signature (rasterize_points.h:41-65), and the same with only dL_dcolors produced
+#define EGS_BWD_PARAMS                                                                                      \
+  const torch::Tensor &background, const torch::Tensor &means3D, const torch::Tensor &radii,                \
+      const torch::Tensor &colors, const torch::Tensor &scales, const torch::Tensor &rotations,             \
+      const float scale_modifier, const torch::Tensor &cov3D_precomp, const torch::Tensor &viewmatrix,      \
+      const torch::Tensor &projmatrix, const float tan_fovx, const float tan_fovy,                          \
+      const torch::Tensor &dL_dout_color, const torch::Tensor &dL_dout_depth,                               \
+      const torch::Tensor &dL_dout_alpha, const torch::Tensor &sh, const int degree,                        \
+      const torch::Tensor &campos, const torch::Tensor &geomBuffer, const int R,                            \
+      const torch::Tensor &binningBuffer, const torch::Tensor &imageBuffer, const torch::Tensor &alphas,    \
+      const bool debug
+#define EGS_BWD_ARGS                                                                                        \
+  background, means3D, radii, colors, scales, rotations, scale_modifier, cov3D_precomp, viewmatrix,         \
+      projmatrix, tan_fovx, tan_fovy, dL_dout_color, dL_dout_depth, dL_dout_alpha, sh, degree, campos,      \
+      geomBuffer, R, binningBuffer, imageBuffer, alphas, debug
+auto rasterize_gaussians_backward(EGS_BWD_PARAMS) { return rasterize_backward_impl(false, EGS_BWD_ARGS); }
+auto rasterize_gaussians_backward_colors(EGS_BWD_PARAMS) { return rasterize_backward_impl(true, EGS_BWD_ARGS); }
 
 torch::Tensor mark_visible(torch::Tensor& means3D, torch::Tensor& viewmatrix, torch::Tensor& projmatrix) {
   TORCH_CHECK(means3D.is_cuda(), "means3D must be a CUDA tensor (there is no CPU path)");
@@ -618,6 +640,7 @@ PYBIND11_MODULE(TORCH_EXTENSION_NAME, m) {
   m.def("model_backward", &model_backward);
   m.def("rasterize_gaussians", &rasterize_gaussians);
   m.def("rasterize_gaussians_backward", &rasterize_gaussians_backward);
+  m.def("rasterize_gaussians_backward_colors", &rasterize_gaussians_backward_colors);
   m.def("mark_visible", &mark_visible);
   m.def("adam_step", &adam_step);
   m.def("se3_apply", &se3_apply);

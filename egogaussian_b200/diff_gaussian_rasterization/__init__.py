@@ -99,9 +99,15 @@ class _RasterizeGaussians(torch.autograd.Function):
                 cov3Ds_precomp, rs.viewmatrix, rs.projmatrix, rs.tanfovx, rs.tanfovy, grad_color,
                 grad_depth, grad_alpha, sh, rs.sh_degree, rs.campos, geom_blob, ctx.num_rendered,
                 binning_blob, image_blob, alpha, rs.debug)
+        # Only the precomputed colours want a gradient (the trainers' label render,
+        # gaussian_renderer/render_helper.py:40-66): both backward kernels skip everything else.
+        need = ctx.needs_input_grad
+        colors_only = colors_precomp.numel() != 0 and need[3] and not any(need[i] for i in (0, 1, 2, 4, 5, 6, 7))
+        fn = _C.rasterize_gaussians_backward_colors if colors_only else _C.rasterize_gaussians_backward
         (g_means2D, g_colors, g_opacities, g_means3D, g_cov3D, g_sh, g_scales, g_rotations) = \
-            _call_with_snapshot(_C.rasterize_gaussians_backward, args, rs.debug, "snapshot_bw.dump",
-                                "backward")
+            _call_with_snapshot(fn, args, rs.debug, "snapshot_bw.dump", "backward")
+        if colors_only:
+            return (None, None, None, g_colors, None, None, None, None, None)
 
         def present(g, inp):  # absent inputs were empty tensors and get no gradient
             return g if inp.numel() != 0 else None

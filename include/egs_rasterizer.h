@@ -152,6 +152,11 @@ typedef struct EgsBackwardArgs {
   /* Size in bytes of the binning blob forward was given (0 = egs_binning_bytes(num_rendered)):
    * when forward ran with a num_rendered_hint the blob is laid out for the hinted capacity. */
   size_t binning_bytes;
+  /* Non-zero: only dL_dcolors is wanted (requires colors_precomp). Everything that feeds the other
+   * gradients is skipped in both backward kernels and no other output is written (they may be
+   * NULL). This is the backward of the trainers' per-iteration label render
+   * (gaussian_renderer/render_helper.py:40-66: geometry detached, the label as colour). */
+  int colors_only;
 } EgsBackwardArgs;
 
 size_t egs_backward_scratch_bytes(int P);

@@ -215,6 +215,34 @@ def test_label_render_against_reference_rasterizer(built, cuda_device):
     assert (pc._label.grad - label_ref.grad).abs().max().item() <= 1e-4 * label_ref.grad.abs().max().item()
 
 
+def test_colors_only_backward_equals_full_backward(built, cuda_device):
+    """EgsBackwardArgs.colors_only (taken when only colors_precomp wants a gradient) gives the colour
+    gradient of the full backward, to the run-to-run noise of the float atomics."""
+    from egogaussian_b200 import scenes
+    from egogaussian_b200.diff_gaussian_rasterization import GaussianRasterizationSettings, GaussianRasterizer
+    dev = cuda_device
+    W, H, P = 400, 240, 30_000
+    sc = scenes.make_scene(P, W, H, sh_degree=0, seed=99).to(dev)
+    cam = sc.camera
+    rs = GaussianRasterizationSettings(H, W, float(cam.tanfovx), float(cam.tanfovy), sc.bg, 1.0, cam.viewmatrix,
+                                       cam.projmatrix, 0, cam.campos, False, False)
+    gen = torch.Generator().manual_seed(100)
+    w = [torch.randn(s, generator=gen).to(dev) for s in ((3, H, W), (1, H, W), (1, H, W))]
+    base = torch.rand(P, 3, generator=gen).to(dev)
+    grads = []
+    for full in (False, True):
+        colors = base.clone().requires_grad_(True)
+        means = sc.means3D.clone().requires_grad_(full)
+        color, radii, depth, alpha = GaussianRasterizer(rs)(
+            means3D=means, means2D=torch.zeros_like(means), opacities=sc.opacities, colors_precomp=colors,
+            scales=sc.scales, rotations=sc.rotations)
+        ((color * w[0]).sum() + (depth * w[1]).sum() + (alpha * w[2]).sum()).backward()
+        assert (means.grad is not None) == full
+        grads.append(colors.grad)
+    assert (grads[0] - grads[1]).abs().max().item() <= 2e-5 * grads[1].abs().max().item()
+    assert grads[0].abs().max().item() > 0
+
+
 @pytest.mark.parametrize("mode", ["static", "object_train"])
 def test_render_mirror_equals_torch_glue(mode, built, cuda_device):
     """render() on raw parameters == the reference's glue (restated in torch, oracle/model_ref.py)
