@@ -77,6 +77,10 @@ class EgsModelGrads(C.Structure):
                 ("d_features_dc", c_float_p), ("d_features_rest", c_float_p), ("d_train_R", c_float_p)]
 
 
+class EgsRowTensor(C.Structure):
+    _fields_ = [("src", C.c_void_p), ("dst", C.c_void_p), ("row_bytes", C.c_int)]
+
+
 class EgsLossArgs(C.Structure):
     _fields_ = [("channels", C.c_int), ("height", C.c_int), ("width", C.c_int),
                 ("image", c_float_p), ("target", c_float_p), ("grad_mask", C.c_void_p),
@@ -103,7 +107,8 @@ EXPORTED_SYMBOLS = [
     "egs_backward_scratch_bytes", "egs_backward", "egs_mark_visible", "egs_adam_step",
     "egs_se3_apply", "egs_adam_se3_step", "egs_model_forward", "egs_model_backward",
     "egs_forward_raw", "egs_backward_raw",
-    "egs_image_loss_workspace_bytes", "egs_image_loss", "egs_densify_stats", "egs_geom_view", "egs_binning_view", "egs_image_view",
+    "egs_image_loss_workspace_bytes", "egs_image_loss", "egs_densify_stats",
+    "egs_compact_scratch_bytes", "egs_compact_plan", "egs_compact_rows", "egs_geom_view", "egs_binning_view", "egs_image_view",
     "egs_launch_count", "egs_last_error", "egs_abi_version",
     "egs_profile_enable", "egs_profile_read", "egs_profile_stage_name",
 ]
@@ -156,6 +161,12 @@ def load() -> C.CDLL:
     lib.egs_image_loss_workspace_bytes.argtypes = [C.c_int, C.c_int, C.c_int]
     lib.egs_image_loss.restype = C.c_int
     lib.egs_image_loss.argtypes = [C.POINTER(EgsLossArgs), C.c_void_p, C.c_void_p, C.c_void_p, C.c_size_t, C.c_void_p]
+    lib.egs_compact_scratch_bytes.restype = C.c_size_t
+    lib.egs_compact_scratch_bytes.argtypes = [C.c_int]
+    lib.egs_compact_plan.restype = C.c_int
+    lib.egs_compact_plan.argtypes = [C.c_int, C.c_void_p, C.c_void_p, C.c_size_t, C.POINTER(C.c_int), C.c_void_p]
+    lib.egs_compact_rows.restype = C.c_int
+    lib.egs_compact_rows.argtypes = [C.c_int, C.c_void_p, C.POINTER(EgsRowTensor), C.c_int, C.c_void_p]
     lib.egs_densify_stats.restype = C.c_int
     lib.egs_densify_stats.argtypes = [C.c_int] + [C.c_void_p] * 6
     lib.egs_geom_view.restype = C.c_int
@@ -524,6 +535,35 @@ def image_loss(image, target, lambda_dssim, grad_mask=None, want_grad=True, stre
         _check(lib.egs_image_loss(C.byref(a), terms.data_ptr(), _ptr(grad), ws.data_ptr(), nbytes,
                                   _stream_handle(stream)), "egs_image_loss")
     return terms, grad
+
+
+def compact_rows(keep, tensors, stream=None):
+    """egs_compact_plan + egs_compact_rows: `[t[keep] for t in tensors]` for contiguous tensors whose
+    first dimension is len(keep) and whose rows are a multiple of 4 bytes; one scan, one gather."""
+    import torch
+    lib = load()
+    P = int(keep.shape[0])
+    keep_u8 = keep.to(torch.uint8).contiguous() if keep.dtype != torch.uint8 else keep.contiguous()
+    dev = keep.device
+    nbytes = lib.egs_compact_scratch_bytes(P)
+    scratch = torch.empty((nbytes,), dtype=torch.uint8, device=dev)
+    count = C.c_int()
+    with torch.cuda.device(dev):
+        _check(lib.egs_compact_plan(P, _ptr(keep_u8), scratch.data_ptr(), nbytes, C.byref(count),
+                                    _stream_handle(stream)), "egs_compact_plan")
+        n = count.value
+        outs = [torch.empty((n,) + tuple(t.shape[1:]), dtype=t.dtype, device=dev) for t in tensors]
+        for first in range(0, len(tensors), 32):
+            chunk = list(zip(tensors[first:first + 32], outs[first:first + 32]))
+            arr = (EgsRowTensor * len(chunk))()
+            for k, (t, o) in enumerate(chunk):
+                assert t.is_contiguous() and t.shape[0] == P
+                row_bytes = t.element_size() * (t.numel() // max(P, 1))
+                arr[k].src, arr[k].dst, arr[k].row_bytes = t.data_ptr(), o.data_ptr() if n else None, row_bytes
+            if n and P:
+                _check(lib.egs_compact_rows(P, scratch.data_ptr(), arr, len(chunk), _stream_handle(stream)),
+                       "egs_compact_rows")
+    return outs
 
 
 def densify_stats(radii, dL_dmeans2D, max_radii2D, xyz_gradient_accum, denom, stream=None) -> None:

@@ -17,6 +17,9 @@
  *                         get_covariance/get_rotated_covariance    scene/gaussian_model.py:29-63,167-171
  *                         build_rotation/build_scaling_rotation    utils/general_utils.py:110-158
  *   egs_image_loss     <- l1_loss + ssim (+ gradient mask hook)    utils/loss_utils.py:57-106
+ *   egs_densify_stats  <- add_densification_stats + max_radii2D    scene/gaussian_model.py:735-740
+ *   egs_compact_plan / egs_compact_rows
+ *                      <- prune_points / _prune_optimizer          scene/gaussian_model.py:506-557
  *
  * Conventions
  *   - plain C, no torch types, no exceptions; every pointer named `d_*` or documented as
@@ -317,6 +320,24 @@ int egs_backward_raw(const EgsBackwardArgs* args, const EgsModelArgs* model, con
  * mask indexing costs several per iteration). */
 int egs_densify_stats(int P, const int* radii, const float* dL_dmeans2D, float* max_radii2D,
                       float* xyz_gradient_accum, float* denom, void* stream);
+
+/* Stable row compaction of up to EGS_COMPACT_MAX_TENSORS tensors at once (the
+ * periodic half: GaussianModel.prune_points / _prune_optimizer, scene/gaussian_model.py:506-557,
+ * i.e. `tensor[mask]` on every parameter, both Adam moments and the bookkeeping tensors).
+ * egs_compact_plan scans keep[P] (device, one byte per row, non-zero = keep) into `scratch`
+ * (device, egs_compact_scratch_bytes(P)) and returns the number of kept rows in *count (host; the
+ * one synchronisation, needed to size the outputs). egs_compact_rows then copies, for every kept
+ * row in order, row i of each src to row k of its dst (k = kept rows before i): one launch for all
+ * tensors. row_bytes must be a multiple of 4; src and dst must not overlap. */
+#define EGS_COMPACT_MAX_TENSORS 32
+typedef struct EgsRowTensor {
+  const void* src;   /* device [P, row_bytes] */
+  void* dst;         /* device [count, row_bytes] */
+  int row_bytes;
+} EgsRowTensor;
+size_t egs_compact_scratch_bytes(int P);
+int egs_compact_plan(int P, const unsigned char* keep, void* scratch, size_t scratch_bytes, int* count, void* stream);
+int egs_compact_rows(int P, const void* scratch, const EgsRowTensor* tensors, int n_tensors, void* stream);
 
 /* ---- image loss of the trainers ------------------------------------ */
 
