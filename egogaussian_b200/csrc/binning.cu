@@ -74,22 +74,31 @@ scan_tiles_kernel(const uint32_t* __restrict__ in, uint32_t* __restrict__ out, i
     }
     if (lane < SCAN_THREADS / 32) s_warp_sums[lane] = wi - w;  // exclusive warp offsets
     const uint32_t block_total = __shfl_sync(0xffffffffu, wi, SCAN_THREADS / 32 - 1);
-    if (lane == 0) {
-      uint32_t excl = 0;
-      if (tile == 0) {
-        st[0] = SCAN_FLAG_PREFIX | block_total;
-      } else {
-        st[tile] = SCAN_FLAG_AGG | block_total;
-        for (int t = (int)tile - 1;; --t) {
-          unsigned long long s;
+    // decoupled look-back, 32 predecessors per step: lane l reads tile (t0 - l); the sum runs up to
+    // the nearest tile that already holds an inclusive prefix (one lane walking back tile by tile
+    // paid an L2 round trip per predecessor: 14 us for 245 tiles)
+    uint32_t excl = 0;
+    if (tile == 0) {
+      if (lane == 0) st[0] = SCAN_FLAG_PREFIX | block_total;
+    } else {
+      if (lane == 0) st[tile] = SCAN_FLAG_AGG | block_total;
+      for (int t0 = (int)tile - 1;; t0 -= 32) {
+        const int t = t0 - (int)lane;
+        unsigned long long s = SCAN_FLAG_PREFIX;   // before tile 0: an empty prefix
+        if (t >= 0) {
           do { s = st[t]; } while ((s & (SCAN_FLAG_AGG | SCAN_FLAG_PREFIX)) == 0);
-          excl += (uint32_t)(s & SCAN_VALUE_MASK);
-          if (s & SCAN_FLAG_PREFIX) break;
         }
-        st[tile] = SCAN_FLAG_PREFIX | (unsigned long long)(excl + block_total);
+        const unsigned prefixes = __ballot_sync(0xffffffffu, (s & SCAN_FLAG_PREFIX) != 0);
+        const int first = prefixes ? __ffs((int)prefixes) - 1 : 32;
+        uint32_t val = (int)lane <= first ? (uint32_t)(s & SCAN_VALUE_MASK) : 0u;
+#pragma unroll
+        for (int d = 16; d > 0; d >>= 1) val += __shfl_xor_sync(0xffffffffu, val, d);
+        excl += val;
+        if (prefixes) break;
       }
-      s_block_prefix = excl;
+      if (lane == 0) st[tile] = SCAN_FLAG_PREFIX | (unsigned long long)(excl + block_total);
     }
+    if (lane == 0) s_block_prefix = excl;
   }
   __syncthreads();
   const uint32_t off = s_block_prefix + s_warp_sums[warp] + (incl - run);
