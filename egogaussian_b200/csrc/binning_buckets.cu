@@ -167,6 +167,18 @@ __device__ __forceinline__ uint32_t ld_relaxed_u32(const uint32_t* p) {
   asm volatile("ld.relaxed.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
   return v;
 }
+// four adjacent status words in one request (each word is read atomically; the vector as a whole
+// need not be)
+__device__ __forceinline__ uint4 ld_relaxed_v4(const uint32_t* p) {
+  uint4 v;
+  asm volatile("ld.relaxed.gpu.global.v4.u32 {%0, %1, %2, %3}, [%4];"
+               : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "l"(p) : "memory");
+  return v;
+}
+__device__ __forceinline__ void st_relaxed_v4(uint32_t* p, uint4 v) {
+  asm volatile("st.relaxed.gpu.global.v4.u32 [%0], {%1, %2, %3, %4};" ::"l"(p), "r"(v.x), "r"(v.y), "r"(v.z), "r"(v.w)
+               : "memory");
+}
 __device__ __forceinline__ void st_relaxed_u32(uint32_t* p, uint32_t v) {
   asm volatile("st.relaxed.gpu.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
 }
@@ -238,10 +250,10 @@ msd_partition_kernel(const uint64_t* __restrict__ in, uint64_t* __restrict__ out
       mine += run;
     }
     uint32_t* st = status_raw + (size_t)tile * MSD_BINS + d0;
-    if (tile != 0) {
-#pragma unroll
-      for (int k = 0; k < MSD_DPT; ++k) st_relaxed_u32(st + k, MSD_FLAG_AGG | block_count[k]);
-    }
+    static_assert(MSD_DPT == 4, "a thread's digits are one 16-byte status vector");
+    if (tile != 0)
+      st_relaxed_v4(st, make_uint4(MSD_FLAG_AGG | block_count[0], MSD_FLAG_AGG | block_count[1],
+                                   MSD_FLAG_AGG | block_count[2], MSD_FLAG_AGG | block_count[3]));
     uint32_t incl = mine;
 #pragma unroll
     for (int s = 1; s < 32; s <<= 1) {
@@ -263,29 +275,32 @@ msd_partition_kernel(const uint64_t* __restrict__ in, uint64_t* __restrict__ out
 #pragma unroll
     for (int k = 0; k < MSD_DPT; ++k) excl[k] = 0;
     if (tile != 0) {
-      const uint32_t* prev[MSD_DPT];
+      // A predecessor publishes its four words together (first all aggregates, later all prefixes),
+      // so the four chains move in step: one 16-byte read per predecessor tile. A word that is still
+      // empty means that tile has not ranked yet: read it again.
+      const uint32_t* prev = st - MSD_BINS;
       unsigned open = (1u << MSD_DPT) - 1u;
-#pragma unroll
-      for (int k = 0; k < MSD_DPT; ++k) prev[k] = st + k - MSD_BINS;
       while (open) {
-        uint32_t s[MSD_DPT];
+        const uint4 v = ld_relaxed_v4(prev);
+        const uint32_t s[MSD_DPT] = {v.x, v.y, v.z, v.w};
+        bool all_seen = true;
 #pragma unroll
-        for (int k = 0; k < MSD_DPT; ++k) s[k] = (open >> k) & 1u ? ld_relaxed_u32(prev[k]) : 0u;
+        for (int k = 0; k < MSD_DPT; ++k) all_seen = all_seen && (s[k] & (MSD_FLAG_AGG | MSD_FLAG_PREFIX)) != 0u;
+        if (!all_seen) continue;
 #pragma unroll
         for (int k = 0; k < MSD_DPT; ++k) {
-          if (((open >> k) & 1u) && (s[k] & (MSD_FLAG_AGG | MSD_FLAG_PREFIX)) != 0u) {
+          if ((open >> k) & 1u) {
             excl[k] += s[k] & MSD_VALUE_MASK;
             if (s[k] & MSD_FLAG_PREFIX) open &= ~(1u << k);
-            else prev[k] -= MSD_BINS;
           }
         }
+        prev -= MSD_BINS;
       }
     }
+    st_relaxed_v4(st, make_uint4(MSD_FLAG_PREFIX | (excl[0] + block_count[0]), MSD_FLAG_PREFIX | (excl[1] + block_count[1]),
+                                 MSD_FLAG_PREFIX | (excl[2] + block_count[2]), MSD_FLAG_PREFIX | (excl[3] + block_count[3])));
 #pragma unroll
-    for (int k = 0; k < MSD_DPT; ++k) {
-      st_relaxed_u32(st + k, MSD_FLAG_PREFIX | (excl[k] + block_count[k]));
-      S.digit_global[d0 + k] = bucket_start[d0 + k] + excl[k] - local_start[k];
-    }
+    for (int k = 0; k < MSD_DPT; ++k) S.digit_global[d0 + k] = bucket_start[d0 + k] + excl[k] - local_start[k];
   }
   __syncthreads();
 #pragma unroll
