@@ -18,6 +18,7 @@
  *                         build_rotation/build_scaling_rotation    utils/general_utils.py:110-158
  *   egs_image_loss     <- l1_loss + ssim (+ gradient mask hook)    utils/loss_utils.py:57-106
  *   egs_densify_stats  <- add_densification_stats + max_radii2D    scene/gaussian_model.py:735-740
+ *   egs_knn_mean_dist2 <- distCUDA2                                submodules/simple-knn/spatial.cu:15-27
  *   egs_compact_plan / egs_compact_rows
  *                      <- prune_points / _prune_optimizer          scene/gaussian_model.py:506-557
  *
@@ -338,6 +339,12 @@ typedef struct EgsRowTensor {
 size_t egs_compact_scratch_bytes(int P);
 int egs_compact_plan(int P, const unsigned char* keep, void* scratch, size_t scratch_bytes, int* count, void* stream);
 int egs_compact_rows(int P, const void* scratch, const EgsRowTensor* tensors, int n_tensors, void* stream);
+
+/* Mean squared distance of every point to its three nearest neighbours, the point itself excluded
+ * (distCUDA2 of submodules/simple-knn, used once at initialisation to set the
+ * scales, scene/gaussian_model.py:301,312). points: device [P,3]; mean_dist2: device [P]. With fewer
+ * than four points the missing neighbours count as FLT_MAX, like the reference. */
+int egs_knn_mean_dist2(int P, const float* points, float* mean_dist2, void* stream);
 
 /* ---- image loss of the trainers ------------------------------------ */
 

@@ -24,13 +24,31 @@ REF = Path("/root/reference/submodules/diff-gaussian-rasterization")
 SOURCES = ["cuda_rasterizer/rasterizer_impl.cu", "cuda_rasterizer/forward.cu", "cuda_rasterizer/backward.cu",
            "rasterize_points.cu", "ext.cpp"]
 MODULE = "ref_dgr_C"
+# the reference's second native submodule (init-time KNN, scene/gaussian_model.py:301): three files
+KNN_REF = Path("/root/reference/submodules/simple-knn")
+KNN_SOURCES = ["simple_knn.cu", "spatial.cu", "ext.cpp"]
+KNN_MODULE = "ref_knn_C"
 
 
 def available() -> bool:
     return (OUT / f"{MODULE}.so").exists()
 
 
+def knn_available() -> bool:
+    return (OUT / f"{KNN_MODULE}.so").exists()
+
+
 def build(force: bool = False) -> Path | None:
+    build_knn(force)
+    return _build(MODULE, REF, SOURCES, [str(REF / "third_party/glm"), str(REF)], force)
+
+
+def build_knn(force: bool = False) -> Path | None:
+    """`oracle/_ref/ref_knn_C.so` exporting the reference's distCUDA2 (simple-knn/ext.cpp)."""
+    return _build(KNN_MODULE, KNN_REF, KNN_SOURCES, [str(KNN_REF)], force)
+
+
+def _build(MODULE: str, REF: Path, SOURCES: list, extra_inc: list, force: bool) -> Path | None:
     target = OUT / f"{MODULE}.so"
     if target.exists() and not force:
         return target
@@ -39,7 +57,7 @@ def build(force: bool = False) -> Path | None:
     import torch
     from torch.utils import cpp_extension as ce
     OUT.mkdir(parents=True, exist_ok=True)
-    inc = list(ce.include_paths("cuda")) + [sysconfig.get_paths()["include"], str(REF / "third_party/glm"), str(REF)]
+    inc = list(ce.include_paths("cuda")) + [sysconfig.get_paths()["include"], *extra_inc]
     common = ["-std=c++17", "-O3", "-gencode", "arch=compute_100,code=sm_100", "-Xcompiler", "-fPIC",
               f"-DTORCH_EXTENSION_NAME={MODULE}", "-DTORCH_API_INCLUDE_EXTENSION_H",
               f"-D_GLIBCXX_USE_CXX11_ABI={int(torch._C._GLIBCXX_USE_CXX11_ABI)}",
@@ -48,7 +66,7 @@ def build(force: bool = False) -> Path | None:
     objs = []
 
     def compile_one(rel):
-        obj = OUT / (Path(rel).name + ".o")
+        obj = OUT / (MODULE + "_" + Path(rel).name + ".o")
         cmd = ["nvcc", *common, "-x", "cu", "-c", str(REF / rel), "-o", str(obj)]
         r = subprocess.run(cmd, capture_output=True, text=True)
         if r.returncode != 0:

@@ -147,3 +147,24 @@ def assert_loss_close(got, gold, what, value_rtol=2e-6, grad_rtol=1e-4):
 def test_loss_restatement_matches_reference(case):
     gold = np.load(GOLDEN / f"{case['name']}.npz")
     assert_loss_close(run_loss_restatement(case), gold, case["name"])
+
+
+# ---- KNN statistic (oracle/knn_ref.py) against the reference's own simple-knn module -----------------
+from golden.make_knn_golden import KNN_CASES, knn_points  # noqa: E402
+
+
+def assert_knn_close(got, gold, what):
+    """1e-6 relative: the squared distances are three products and two sums in fp32 (the GPU fuses
+    them into FMAs, numpy does not); infinities (fewer than four points) must match exactly."""
+    got, gold = np.asarray(got, np.float64), np.asarray(gold, np.float64)
+    assert got.shape == gold.shape, what
+    fin = np.isfinite(gold)
+    assert np.array_equal(np.isfinite(got), fin), what
+    np.testing.assert_allclose(got[fin], gold[fin], rtol=1e-6, atol=0, err_msg=what)
+
+
+@pytest.mark.parametrize("name", KNN_CASES)
+def test_knn_restatement_matches_reference(name):
+    from oracle import knn_ref
+    gold = np.load(GOLDEN / f"{name}.npz")["mean_dist2"]
+    assert_knn_close(knn_ref.mean_dist2(knn_points(name)), gold, name)
