@@ -108,7 +108,7 @@ EXPORTED_SYMBOLS = [
     "egs_se3_apply", "egs_adam_se3_step", "egs_model_forward", "egs_model_backward",
     "egs_forward_raw", "egs_backward_raw",
     "egs_image_loss_workspace_bytes", "egs_image_loss", "egs_densify_stats",
-    "egs_compact_scratch_bytes", "egs_compact_plan", "egs_compact_rows", "egs_knn_mean_dist2", "egs_geom_view", "egs_binning_view", "egs_image_view",
+    "egs_compact_scratch_bytes", "egs_compact_plan", "egs_compact_rows", "egs_knn_workspace_bytes", "egs_knn_mean_dist2", "egs_geom_view", "egs_binning_view", "egs_image_view",
     "egs_launch_count", "egs_last_error", "egs_abi_version",
     "egs_profile_enable", "egs_profile_read", "egs_profile_stage_name",
 ]
@@ -168,7 +168,9 @@ def load() -> C.CDLL:
     lib.egs_compact_rows.restype = C.c_int
     lib.egs_compact_rows.argtypes = [C.c_int, C.c_void_p, C.POINTER(EgsRowTensor), C.c_int, C.c_void_p]
     lib.egs_knn_mean_dist2.restype = C.c_int
-    lib.egs_knn_mean_dist2.argtypes = [C.c_int, C.c_void_p, C.c_void_p, C.c_void_p]
+    lib.egs_knn_mean_dist2.argtypes = [C.c_int, C.c_void_p, C.c_void_p, C.c_void_p, C.c_size_t, C.c_void_p]
+    lib.egs_knn_workspace_bytes.restype = C.c_size_t
+    lib.egs_knn_workspace_bytes.argtypes = [C.c_int]
     lib.egs_densify_stats.restype = C.c_int
     lib.egs_densify_stats.argtypes = [C.c_int] + [C.c_void_p] * 6
     lib.egs_geom_view.restype = C.c_int
@@ -568,16 +570,20 @@ def compact_rows(keep, tensors, stream=None):
     return outs
 
 
-def knn_mean_dist2(points, stream=None):
-    """egs_knn_mean_dist2: [P] mean squared distance to the three nearest neighbours (distCUDA2)."""
+def knn_mean_dist2(points, stream=None, exhaustive=False):
+    """egs_knn_mean_dist2: [P] mean squared distance to the three nearest neighbours (distCUDA2).
+    `exhaustive` withholds the workspace, which forces the all-pairs sweep at any size."""
     import torch
     P = int(points.shape[0])
     pts = points.contiguous().float()
     out = torch.empty((P,), dtype=torch.float32, device=points.device)
     if P:
+        lib = load()
+        nbytes = 0 if exhaustive else int(lib.egs_knn_workspace_bytes(P))
         with torch.cuda.device(points.device):
-            _check(load().egs_knn_mean_dist2(P, _ptr(pts), out.data_ptr(), _stream_handle(stream)),
-                   "egs_knn_mean_dist2")
+            ws = torch.empty((nbytes,), dtype=torch.uint8, device=points.device) if nbytes else None
+            _check(lib.egs_knn_mean_dist2(P, _ptr(pts), out.data_ptr(), ws.data_ptr() if nbytes else None, nbytes,
+                                          _stream_handle(stream)), "egs_knn_mean_dist2")
     return out
 
 

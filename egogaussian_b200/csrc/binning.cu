@@ -124,6 +124,15 @@ int launch_scan_tiles(const GeomPtrs& g, int P, cudaStream_t stream, bool debug)
   return EGS_OK;
 }
 
+// the same scan for any u32 array (the cell counts of knn.cu); `status` holds n / SCAN_TILE + 2 words
+int launch_inclusive_scan(const uint32_t* in, uint32_t* out, int n, unsigned long long* status, cudaStream_t stream) {
+  const int blocks = (n + SCAN_TILE - 1) / SCAN_TILE;
+  EGS_CUDA_TRY(cudaMemsetAsync(status, 0, (size_t)(blocks + 1) * 8, stream));
+  scan_tiles_kernel<<<blocks, SCAN_THREADS, 0, stream>>>(in, out, n, status);
+  EGS_AFTER_LAUNCH(stream, false);
+  return EGS_OK;
+}
+
 // ---------------------------------------------------------------------------------------------
 // key duplication: one (tile << 32 | depth bits, gaussian) pair per covered tile, rows first
 // ---------------------------------------------------------------------------------------------

@@ -226,6 +226,7 @@ struct BackwardScratch {
 int launch_preprocess_forward(const EgsForwardArgs& a, const EgsModelArgs* model, const GeomPtrs& g,
                               cudaStream_t stream);
 int launch_scan_tiles(const GeomPtrs& g, int P, cudaStream_t stream, bool debug);
+int launch_inclusive_scan(const uint32_t* in, uint32_t* out, int n, unsigned long long* status, cudaStream_t stream);
 // packed-word fast path (binning_packed.cu) and the shared range kernel
 bool packed_path_fits(int P, int W, int H);
 int launch_binning_packed(const GeomPtrs& g, const BinningPtrs& b, const ImagePtrs& im, const int* radii,

@@ -343,8 +343,14 @@ int egs_compact_rows(int P, const void* scratch, const EgsRowTensor* tensors, in
 /* Mean squared distance of every point to its three nearest neighbours, the point itself excluded
  * (distCUDA2 of submodules/simple-knn, used once at initialisation to set the
  * scales, scene/gaussian_model.py:301,312). points: device [P,3]; mean_dist2: device [P]. With fewer
- * than four points the missing neighbours count as FLT_MAX, like the reference. */
-int egs_knn_mean_dist2(int P, const float* points, float* mean_dist2, void* stream);
+ * than four points the missing neighbours count as FLT_MAX, like the reference.
+ * workspace: egs_knn_workspace_bytes(P) bytes of device memory, 256-byte aligned (0 bytes for small
+ * clouds, which are swept exhaustively). With it, large clouds are searched through a uniform grid
+ * built on the device; with workspace == NULL the exhaustive sweep runs at any size (same result,
+ * quadratic time). */
+size_t egs_knn_workspace_bytes(int P);
+int egs_knn_mean_dist2(int P, const float* points, float* mean_dist2, void* workspace, size_t workspace_bytes,
+                       void* stream);
 
 /* ---- image loss of the trainers ------------------------------------ */
 
