@@ -87,6 +87,27 @@ class EgsLossArgs(C.Structure):
                 ("lambda_dssim", C.c_float)]
 
 
+EGS_MAX_PEERS = 8
+EGS_EXCHANGE_SIGNAL_WORDS = 64
+EGS_EXCHANGE_MAX_SEGMENTS = 8
+
+
+class EgsPeerGroup(C.Structure):
+    _fields_ = [("world", C.c_int), ("rank", C.c_int), ("grads", C.c_void_p * EGS_MAX_PEERS),
+                ("signals", C.c_void_p * EGS_MAX_PEERS)]
+
+
+class EgsExchangeSegment(C.Structure):
+    _fields_ = [("begin", C.c_longlong), ("end", C.c_longlong), ("lr_a", C.c_double), ("lr_b", C.c_double),
+                ("period", C.c_int), ("split", C.c_int)]
+
+
+class EgsExchangeAdamArgs(C.Structure):
+    _fields_ = [("params", C.c_void_p * EGS_MAX_PEERS), ("exp_avg", C.c_void_p), ("exp_avg_sq", C.c_void_p),
+                ("segments", C.POINTER(EgsExchangeSegment)), ("n_segments", C.c_int), ("step", C.c_int),
+                ("beta1", C.c_double), ("beta2", C.c_double), ("eps", C.c_double)]
+
+
 class EgsGeomView(C.Structure):
     _fields_ = [("depths", C.c_void_p), ("means2D", C.c_void_p), ("conic_opacity", C.c_void_p),
                 ("rgb_depth", C.c_void_p), ("clamped", C.c_void_p), ("tiles_touched", C.c_void_p),
@@ -108,7 +129,8 @@ EXPORTED_SYMBOLS = [
     "egs_se3_apply", "egs_adam_se3_step", "egs_model_forward", "egs_model_backward",
     "egs_forward_raw", "egs_backward_raw",
     "egs_image_loss_workspace_bytes", "egs_image_loss", "egs_densify_stats",
-    "egs_compact_scratch_bytes", "egs_compact_plan", "egs_compact_rows", "egs_knn_workspace_bytes", "egs_knn_mean_dist2", "egs_geom_view", "egs_binning_view", "egs_image_view",
+    "egs_compact_scratch_bytes", "egs_compact_plan", "egs_compact_rows", "egs_knn_workspace_bytes", "egs_knn_mean_dist2",
+    "egs_exchange_sum", "egs_exchange_shard_floats", "egs_exchange_adam_step", "egs_geom_view", "egs_binning_view", "egs_image_view",
     "egs_launch_count", "egs_last_error", "egs_abi_version",
     "egs_profile_enable", "egs_profile_read", "egs_profile_stage_name",
 ]
@@ -169,6 +191,13 @@ def load() -> C.CDLL:
     lib.egs_compact_rows.argtypes = [C.c_int, C.c_void_p, C.POINTER(EgsRowTensor), C.c_int, C.c_void_p]
     lib.egs_knn_mean_dist2.restype = C.c_int
     lib.egs_knn_mean_dist2.argtypes = [C.c_int, C.c_void_p, C.c_void_p, C.c_void_p, C.c_size_t, C.c_void_p]
+    lib.egs_exchange_sum.restype = C.c_int
+    lib.egs_exchange_sum.argtypes = [C.POINTER(EgsPeerGroup), C.c_longlong, C.c_float, C.c_uint32, C.c_int, C.c_void_p]
+    lib.egs_exchange_shard_floats.restype = C.c_longlong
+    lib.egs_exchange_shard_floats.argtypes = [C.c_longlong, C.c_int]
+    lib.egs_exchange_adam_step.restype = C.c_int
+    lib.egs_exchange_adam_step.argtypes = [C.POINTER(EgsPeerGroup), C.POINTER(EgsExchangeAdamArgs), C.c_longlong,
+                                           C.c_float, C.c_uint32, C.c_int, C.c_void_p]
     lib.egs_knn_workspace_bytes.restype = C.c_size_t
     lib.egs_knn_workspace_bytes.argtypes = [C.c_int]
     lib.egs_densify_stats.restype = C.c_int
@@ -585,6 +614,41 @@ def knn_mean_dist2(points, stream=None, exhaustive=False):
             _check(lib.egs_knn_mean_dist2(P, _ptr(pts), out.data_ptr(), ws.data_ptr() if nbytes else None, nbytes,
                                           _stream_handle(stream)), "egs_knn_mean_dist2")
     return out
+
+
+def peer_group(world: int, rank: int, grad_ptrs, signal_ptrs) -> EgsPeerGroup:
+    """EgsPeerGroup from the per-rank device addresses (ints) of the gradient buffers and signal words."""
+    g = EgsPeerGroup()
+    g.world, g.rank = world, rank
+    for q in range(world):
+        g.grads[q] = int(grad_ptrs[q])
+        g.signals[q] = int(signal_ptrs[q])
+    return g
+
+
+def exchange_sum(group: EgsPeerGroup, n_floats: int, epoch: int, scale: float = 1.0, max_ctas: int = 0,
+                 stream=None) -> None:
+    """egs_exchange_sum: every rank's flat gradient buffer <- scale * the sum over ranks."""
+    _check(load().egs_exchange_sum(C.byref(group), n_floats, scale, epoch, max_ctas, _stream_handle(stream)),
+           "egs_exchange_sum")
+
+
+def exchange_adam_step(group: EgsPeerGroup, param_ptrs, exp_avg, exp_avg_sq, segments, n_floats: int, epoch: int,
+                       step: int, betas=(0.9, 0.999), eps: float = 1e-15, scale: float = 1.0, max_ctas: int = 0,
+                       stream=None) -> None:
+    """egs_exchange_adam_step. `segments`: [(begin, end, lr_a, lr_b, period, split)] in floats;
+    exp_avg / exp_avg_sq: this rank's moment shards (egs_exchange_shard_floats floats each)."""
+    a = EgsExchangeAdamArgs()
+    for q in range(group.world):
+        a.params[q] = int(param_ptrs[q])
+    a.exp_avg, a.exp_avg_sq = exp_avg.data_ptr(), exp_avg_sq.data_ptr()
+    segs = (EgsExchangeSegment * max(len(segments), 1))()
+    for k, (b, e, la, lb, per, sp) in enumerate(segments):
+        segs[k] = EgsExchangeSegment(b, e, la, lb, per, sp)
+    a.segments, a.n_segments, a.step = segs, len(segments), step
+    a.beta1, a.beta2, a.eps = betas[0], betas[1], eps
+    _check(load().egs_exchange_adam_step(C.byref(group), C.byref(a), n_floats, scale, epoch, max_ctas,
+                                         _stream_handle(stream)), "egs_exchange_adam_step")
 
 
 def densify_stats(radii, dL_dmeans2D, max_radii2D, xyz_gradient_accum, denom, stream=None) -> None:

@@ -1,0 +1,283 @@
+// exchange.cu -- the gradient exchange of view-data-parallel training as ONE kernel per rank over
+// peer-mapped memory (NVLink 5 / NVSwitch), with or without the Adam update inside it.
+//
+// Every rank holds the full Gaussian set and back-propagates another view; the flat gradient
+// buffers of all ranks are mapped into every rank's address space. Rank r owns slice r:
+//
+//   barrier in   every rank has finished its backward (a flag per peer, release/acquire at system scope)
+//   reduce       load slice r of all `world` buffers with 16-byte peer loads, add in rank order
+//   [update]     egs_exchange_adam_step: Adam on slice r of the parameters, moments sharded by rank
+//   broadcast    store the sums (or the new parameters) into slice r of every rank's buffer
+//   barrier out  every rank's stores have landed before anyone's next kernel starts
+//
+// so each link carries (world - 1) / world of the buffer once in each direction and nothing is staged
+// or copied: the same volume as a ring all-reduce, at full NVSwitch bandwidth from the first byte,
+// one launch, and with the update fused the optimiser's 28 B/float pass shrinks to the rank's own slice.
+// Sums are formed in rank order by exactly one rank per element, so all ranks see the same bits.
+#include "common.cuh"
+#include "adam_math.cuh"
+
+#include <math.h>
+
+namespace egs {
+
+constexpr int EX_THREADS = 512;
+constexpr int EX_SLOT_IN = 0;                                   // [0, 8): "rank q entered exchange e"
+constexpr int EX_SLOT_OUT = EGS_MAX_PEERS;                      // [8, 16): "rank q finished exchange e"
+constexpr int EX_SLOT_COUNT = 2 * EGS_MAX_PEERS;                // CTAs of this rank that finished
+constexpr int EX_SLOT_ERROR = EGS_EXCHANGE_SIGNAL_WORDS - 1;    // set when a peer never showed up
+constexpr unsigned long long EX_TIMEOUT_NS = 20ull * 1000 * 1000 * 1000;
+
+struct ExSegmentDev {
+  long long begin4, end4;   // in 4-float chunks
+  float neg_step_a, neg_step_b;
+  int period, split;
+};
+
+struct ExLaunch {
+  int world, rank;
+  float* grads[EGS_MAX_PEERS];
+  float* params[EGS_MAX_PEERS];
+  uint32_t* signals[EGS_MAX_PEERS];
+  long long lo4, hi4;   // this rank's slice, in 4-float chunks
+  float scale;
+  uint32_t epoch;
+  // Adam
+  float* exp_avg;
+  float* exp_avg_sq;
+  ExSegmentDev seg[EGS_EXCHANGE_MAX_SEGMENTS];
+  int n_segments;
+  float one_minus_b1, b2, one_minus_b2, eps, bc2_sqrt;
+};
+
+__device__ __forceinline__ uint32_t ld_acquire_sys(const uint32_t* p) {
+  uint32_t v;
+  asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+  return v;
+}
+__device__ __forceinline__ void st_release_sys(uint32_t* p, uint32_t v) {
+  asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
+}
+// peer data changes between launches under the same addresses: keep it out of the L1
+__device__ __forceinline__ float4 ld_peer_f4(const float* p) {
+  float4 v;
+  asm volatile("ld.relaxed.sys.global.v4.f32 {%0, %1, %2, %3}, [%4];"
+               : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w)
+               : "l"(p)
+               : "memory");
+  return v;
+}
+__device__ __forceinline__ void st_peer_f4(float* p, float4 v) {
+  asm volatile("st.relaxed.sys.global.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(p), "f"(v.x), "f"(v.y), "f"(v.z), "f"(v.w)
+               : "memory");
+}
+__device__ __forceinline__ unsigned long long global_ns() {
+  unsigned long long t;
+  asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t));
+  return t;
+}
+
+// threads [0, world) each wait for one peer's flag to reach `epoch`
+__device__ __forceinline__ void wait_peer_flags(const ExLaunch& L, int slot) {
+  if ((int)threadIdx.x < L.world) {
+    const uint32_t* flag = L.signals[L.rank] + slot + threadIdx.x;
+    const unsigned long long t0 = global_ns();
+    while ((int)(ld_acquire_sys(flag) - L.epoch) < 0) {
+      if (global_ns() - t0 > EX_TIMEOUT_NS) {
+        L.signals[L.rank][EX_SLOT_ERROR] = 1u;
+        break;
+      }
+    }
+  }
+  __syncthreads();
+}
+
+__device__ __forceinline__ float4 sum_over_ranks(const ExLaunch& L, long long c) {
+  float4 part[EGS_MAX_PEERS];
+#pragma unroll
+  for (int q = 0; q < EGS_MAX_PEERS; ++q)
+    if (q < L.world) part[q] = ld_peer_f4(L.grads[q] + 4 * c);
+  float4 acc = part[0];
+#pragma unroll
+  for (int q = 1; q < EGS_MAX_PEERS; ++q)
+    if (q < L.world) {
+      acc.x += part[q].x; acc.y += part[q].y; acc.z += part[q].z; acc.w += part[q].w;
+    }
+  acc.x *= L.scale; acc.y *= L.scale; acc.z *= L.scale; acc.w *= L.scale;
+  return acc;
+}
+
+__device__ __forceinline__ void store_to_all(float* const* bufs, int world, long long c, float4 v) {
+#pragma unroll
+  for (int q = 0; q < EGS_MAX_PEERS; ++q)
+    if (q < world) st_peer_f4(bufs[q] + 4 * c, v);
+}
+
+template <bool ADAM>
+__global__ void __launch_bounds__(EX_THREADS, 2) exchange_kernel(const __grid_constant__ ExLaunch L) {
+  __shared__ bool s_last;
+  // ---- barrier in: my backward is complete (this kernel follows it in stream order) ----
+  if (blockIdx.x == 0 && (int)threadIdx.x < L.world)
+    st_release_sys(L.signals[threadIdx.x] + EX_SLOT_IN + L.rank, L.epoch);
+  wait_peer_flags(L, EX_SLOT_IN);
+
+  const long long stride = (long long)gridDim.x * EX_THREADS;
+  for (long long c = L.lo4 + (long long)blockIdx.x * EX_THREADS + threadIdx.x; c < L.hi4; c += stride) {
+    const float4 g = sum_over_ranks(L, c);
+    if (ADAM) {
+      int si = -1;
+#pragma unroll 1
+      for (int k = 0; k < L.n_segments; ++k)
+        if (c >= L.seg[k].begin4 && c < L.seg[k].end4) si = k;
+      if (si >= 0) {
+        const ExSegmentDev& S = L.seg[si];
+        float ns[4] = {S.neg_step_a, S.neg_step_a, S.neg_step_a, S.neg_step_a};
+        if (S.period > 0) {
+          const int r0 = (int)(((c - S.begin4) * 4) % S.period);
+#pragma unroll
+          for (int k = 0; k < 4; ++k) {
+            int r = r0 + k;
+            if (r >= S.period) r -= S.period;
+            ns[k] = r < S.split ? S.neg_step_a : S.neg_step_b;
+          }
+        }
+        const long long k4 = (c - L.lo4) * 4;
+        float4 p = *reinterpret_cast<const float4*>(L.params[L.rank] + 4 * c);
+        float4 m = *reinterpret_cast<const float4*>(L.exp_avg + k4);
+        float4 v = *reinterpret_cast<const float4*>(L.exp_avg_sq + k4);
+        adam_elem(p.x, g.x, m.x, v.x, L.one_minus_b1, L.b2, L.one_minus_b2, L.eps, ns[0], L.bc2_sqrt);
+        adam_elem(p.y, g.y, m.y, v.y, L.one_minus_b1, L.b2, L.one_minus_b2, L.eps, ns[1], L.bc2_sqrt);
+        adam_elem(p.z, g.z, m.z, v.z, L.one_minus_b1, L.b2, L.one_minus_b2, L.eps, ns[2], L.bc2_sqrt);
+        adam_elem(p.w, g.w, m.w, v.w, L.one_minus_b1, L.b2, L.one_minus_b2, L.eps, ns[3], L.bc2_sqrt);
+        *reinterpret_cast<float4*>(L.exp_avg + k4) = m;
+        *reinterpret_cast<float4*>(L.exp_avg_sq + k4) = v;
+        store_to_all(L.params, L.world, c, p);
+        continue;
+      }
+    }
+    store_to_all(L.grads, L.world, c, g);
+  }
+
+  // ---- barrier out: all my stores are visible everywhere, then all peers' stores are visible here ----
+  __threadfence_system();
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    uint32_t* count = L.signals[L.rank] + EX_SLOT_COUNT;
+    const uint32_t done = atomicAdd(count, 1u);
+    __threadfence_system();
+    s_last = done == gridDim.x - 1;
+    if (s_last) *count = 0u;   // every other CTA of this launch is past it
+  }
+  __syncthreads();
+  if (!s_last) return;
+  if ((int)threadIdx.x < L.world) st_release_sys(L.signals[threadIdx.x] + EX_SLOT_OUT + L.rank, L.epoch);
+  wait_peer_flags(L, EX_SLOT_OUT);
+}
+
+static int fill_group(const char* who, const EgsPeerGroup* g, long long n, ExLaunch& L) {
+  if (!g || g->world < 1 || g->world > EGS_MAX_PEERS || g->rank < 0 || g->rank >= g->world || n < 0 || (n & 3)) {
+    set_error("%s: world must be in [1, %d], rank in [0, world), n_floats a non-negative multiple of 4", who,
+              EGS_MAX_PEERS);
+    return EGS_ERR_INVALID_ARGUMENT;
+  }
+  for (int q = 0; q < g->world; ++q) {
+    if ((n > 0 && !g->grads[q]) || !g->signals[q] || (reinterpret_cast<uintptr_t>(g->grads[q]) & 15u)) {
+      set_error("%s: gradient buffer or signal words of rank %d missing or not 16-byte aligned", who, q);
+      return EGS_ERR_INVALID_ARGUMENT;
+    }
+    L.grads[q] = g->grads[q];
+    L.signals[q] = g->signals[q];
+  }
+  L.world = g->world;
+  L.rank = g->rank;
+  const long long n4 = n / 4, per = (n4 + g->world - 1) / g->world;
+  L.lo4 = per * g->rank < n4 ? per * g->rank : n4;
+  L.hi4 = L.lo4 + per < n4 ? L.lo4 + per : n4;
+  return EGS_OK;
+}
+
+static unsigned exchange_grid(const ExLaunch& L, int max_ctas) {
+  long long ctas = (L.hi4 - L.lo4 + EX_THREADS - 1) / EX_THREADS;
+  const long long cap = max_ctas > 0 ? max_ctas : 148 * 2;
+  if (ctas > cap) ctas = cap;
+  return (unsigned)(ctas < 1 ? 1 : ctas);   // an empty slice still takes part in the barriers
+}
+
+}  // namespace egs
+
+extern "C" long long egs_exchange_shard_floats(long long n_floats, int world) {
+  if (world < 1 || n_floats < 0) return 0;
+  const long long n4 = (n_floats + 3) / 4;
+  return (n4 + world - 1) / world * 4;
+}
+
+extern "C" int egs_exchange_sum(const EgsPeerGroup* group, long long n_floats, float scale, uint32_t epoch,
+                                int max_ctas, void* stream) {
+  using namespace egs;
+  ExLaunch L = {};
+  if (int rc = fill_group("egs_exchange_sum", group, n_floats, L)) return rc;
+  L.scale = scale;
+  L.epoch = epoch;
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  exchange_kernel<false><<<exchange_grid(L, max_ctas), EX_THREADS, 0, st>>>(L);
+  EGS_AFTER_LAUNCH(st, false);
+  return EGS_OK;
+}
+
+extern "C" int egs_exchange_adam_step(const EgsPeerGroup* group, const EgsExchangeAdamArgs* adam, long long n_floats,
+                                      float scale, uint32_t epoch, int max_ctas, void* stream) {
+  using namespace egs;
+  static const char* who = "egs_exchange_adam_step";
+  ExLaunch L = {};
+  if (int rc = fill_group(who, group, n_floats, L)) return rc;
+  if (!adam || (n_floats > 0 && (!adam->exp_avg || !adam->exp_avg_sq)) || adam->step < 1 || adam->n_segments < 0 ||
+      adam->n_segments > EGS_EXCHANGE_MAX_SEGMENTS || (adam->n_segments > 0 && !adam->segments)) {
+    set_error("%s: moments missing, step < 1 or more than %d segments", who, EGS_EXCHANGE_MAX_SEGMENTS);
+    return EGS_ERR_INVALID_ARGUMENT;
+  }
+  for (int q = 0; q < L.world; ++q) {
+    if ((n_floats > 0 && !adam->params[q]) || (reinterpret_cast<uintptr_t>(adam->params[q]) & 15u)) {
+      set_error("%s: parameter buffer of rank %d missing or not 16-byte aligned", who, q);
+      return EGS_ERR_INVALID_ARGUMENT;
+    }
+    L.params[q] = adam->params[q];
+  }
+  if ((reinterpret_cast<uintptr_t>(adam->exp_avg) | reinterpret_cast<uintptr_t>(adam->exp_avg_sq)) & 15u) {
+    set_error("%s: moments must be 16-byte aligned", who);
+    return EGS_ERR_INVALID_ARGUMENT;
+  }
+  // scalar prologue in double like torch's python-side bias corrections (see optim.cu)
+  const double bc1 = 1.0 - pow(adam->beta1, (double)adam->step);
+  const double bc2 = 1.0 - pow(adam->beta2, (double)adam->step);
+  long long prev_end = 0;
+  for (int k = 0; k < adam->n_segments; ++k) {
+    const EgsExchangeSegment& s = adam->segments[k];
+    if (s.begin < prev_end || s.end < s.begin || s.end > n_floats || (s.begin & 3) || (s.end & 3) || s.period < 0 ||
+        (s.period > 0 && (s.split < 0 || s.split > s.period))) {
+      set_error("%s: segment %d is not an ascending 4-float-aligned range inside the buffer", who, k);
+      return EGS_ERR_INVALID_ARGUMENT;
+    }
+    prev_end = s.end;
+    ExSegmentDev& d = L.seg[k];
+    d.begin4 = s.begin / 4;
+    d.end4 = s.end / 4;
+    d.neg_step_a = (float)(-(s.lr_a / bc1));
+    d.neg_step_b = (float)(-(s.lr_b / bc1));
+    d.period = s.period;
+    d.split = s.split;
+  }
+  L.n_segments = adam->n_segments;
+  L.exp_avg = adam->exp_avg;
+  L.exp_avg_sq = adam->exp_avg_sq;
+  L.one_minus_b1 = (float)(1.0 - adam->beta1);
+  L.b2 = (float)adam->beta2;
+  L.one_minus_b2 = (float)(1.0 - adam->beta2);
+  L.eps = (float)adam->eps;
+  L.bc2_sqrt = (float)sqrt(bc2);
+  L.scale = scale;
+  L.epoch = epoch;
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  exchange_kernel<true><<<exchange_grid(L, max_ctas), EX_THREADS, 0, st>>>(L);
+  EGS_AFTER_LAUNCH(st, false);
+  return EGS_OK;
+}

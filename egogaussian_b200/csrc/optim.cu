@@ -13,6 +13,7 @@
 // then un-moves them after backward (:1037-1060). The fused step keeps parameters canonical and
 // pulls the gradient back instead: g = R^T g' (SURVEY.md 8a A-24).
 #include "common.cuh"
+#include "adam_math.cuh"
 #include <math.h>
 
 namespace egs {
@@ -36,15 +37,6 @@ struct AdamLaunch {
   long long total_chunks;
   float one_minus_b1, b2, one_minus_b2, eps;
 };
-
-__device__ __forceinline__ void adam_elem(float& p, float g, float& m, float& v, float omb1,
-                                          float b2, float omb2, float eps, float neg_step,
-                                          float bc2_sqrt) {
-  m = m + (g - m) * omb1;
-  v = v * b2 + omb2 * g * g;
-  const float denom = sqrtf(v) / bc2_sqrt + eps;
-  p = p + neg_step * (m / denom);
-}
 
 __global__ void __launch_bounds__(256) adam_multi_kernel(const AdamLaunch L) {
   for (long long c = (long long)blockIdx.x * blockDim.x + threadIdx.x; c < L.total_chunks;

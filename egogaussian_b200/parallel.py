@@ -21,7 +21,8 @@ class FlatGrads:
     densification statistic's input, gaussian_model.py:735-740) rides along at the end.
     """
 
-    def __init__(self, P: int, M: int, device, with_means2D: bool = True):
+    def __init__(self, P: int, M: int, device, with_means2D: bool = True, allocate=None):
+        """`allocate(n_floats)` supplies the flat buffer (PeerExchange.allocate for peer-mapped memory)."""
         self.layout: List[Tuple[str, Tuple[int, ...]]] = [
             ("means3D", (P, 3)), ("sh", (P, M, 3)), ("opacity", (P, 1)), ("scales", (P, 3)), ("rotations", (P, 4))]
         if with_means2D:
@@ -32,7 +33,9 @@ class FlatGrads:
         for n in sizes:
             self.offsets.append(off)
             off += (n + 3) // 4 * 4
-        self.flat = torch.zeros(off, dtype=torch.float32, device=device)
+        self.flat = torch.zeros(off, dtype=torch.float32, device=device) if allocate is None else allocate(off)
+        assert self.flat.numel() == off and self.flat.dtype == torch.float32
+        self.sizes = sizes
         self.views: Dict[str, torch.Tensor] = {
             name: self.flat[o:o + n].view(shape) for (name, shape), o, n in zip(self.layout, self.offsets, sizes)}
 
@@ -43,6 +46,21 @@ class FlatGrads:
 
     def nbytes(self) -> int:
         return self.flat.numel() * 4
+
+    def adam_segments(self, lrs: Dict[str, float]):
+        """The parameter groups of the reference's optimiser (scene/gaussian_model.py:189-197) as
+        segments of this layout for PeerExchange.adam_step: (begin, end, lr_a, lr_b, period, split) in
+        floats. `lrs` has xyz, f_dc, f_rest, opacity, scaling, rotation. The SH rows hold features_dc
+        (first 3 floats) and features_rest, which differ in learning rate only."""
+        names = {"means3D": "xyz", "opacity": "opacity", "scales": "scaling", "rotations": "rotation"}
+        out = []
+        for (name, shape), o, n in zip(self.layout, self.offsets, self.sizes):
+            end = o + (n + 3) // 4 * 4
+            if name == "sh":
+                out.append((o, end, lrs["f_dc"], lrs["f_rest"], 3 * shape[1], 3))
+            elif name in names:
+                out.append((o, end, lrs[names[name]], 0.0, 0, 0))
+        return out
 
 
 def allreduce_gradients(flat: torch.Tensor, average: bool = False, group=None) -> torch.Tensor:
@@ -59,3 +77,77 @@ def allreduce_gradients(flat: torch.Tensor, average: bool = False, group=None) -
 def views_for_rank(n_views: int, rank: int, world: int) -> Sequence[int]:
     """GPU r of n renders views {r, r+n, ...} of the batch (SURVEY.md 8e partitioning)."""
     return list(range(rank, n_views, world))
+
+
+class PeerExchange:
+    """The gradient exchange over peer-mapped memory: one kernel per rank instead of a library
+    all-reduce (csrc/exchange.cu; include/egs_rasterizer.h egs_exchange_sum / egs_exchange_adam_step).
+
+    torch.distributed's symmetric memory is the plumbing: it allocates the flat buffers, exchanges the
+    handles and maps every rank's buffer into this process. GPUs of one NVLink domain only; raises
+    when the buffers cannot be mapped (the caller then stays on `allreduce_gradients`)."""
+
+    def __init__(self, device, group=None):
+        import torch.distributed as dist
+        import torch.distributed._symmetric_memory as symm
+        from . import cabi
+        self._symm, self._cabi, self._dist = symm, cabi, dist
+        self.device = torch.device(device)
+        self.group = group if group is not None else dist.group.WORLD
+        self.world, self.rank = dist.get_world_size(self.group), dist.get_rank(self.group)
+        if self.world > cabi.EGS_MAX_PEERS:
+            raise ValueError(f"PeerExchange spans one node: at most {cabi.EGS_MAX_PEERS} ranks")
+        self._handles = []
+        self.epoch = 0
+        self.signals = self.allocate(cabi.EGS_EXCHANGE_SIGNAL_WORDS)   # float zeros == u32 zeros
+        self._signal_ptrs = self.peer_pointers(self.signals)
+        self._groups = {}
+
+    def allocate(self, n_floats: int) -> torch.Tensor:
+        """A zeroed fp32 buffer that every rank of the group can address (collective call)."""
+        t = self._symm.empty(int(n_floats), dtype=torch.float32, device=self.device)
+        t.zero_()
+        hdl = self._symm.rendezvous(t, self.group)
+        self._handles.append((t, hdl))
+        torch.cuda.synchronize(self.device)
+        self._dist.barrier(self.group)
+        return t
+
+    def peer_pointers(self, t: torch.Tensor):
+        for buf, hdl in self._handles:
+            if buf.data_ptr() == t.data_ptr():
+                return [int(p) for p in hdl.buffer_ptrs]
+        raise ValueError("tensor was not allocated by this PeerExchange")
+
+    def _group_for(self, grads: torch.Tensor):
+        key = grads.data_ptr()
+        if key not in self._groups:
+            self._groups[key] = self._cabi.peer_group(self.world, self.rank, self.peer_pointers(grads),
+                                                      self._signal_ptrs)
+        return self._groups[key]
+
+    def sum(self, grads: torch.Tensor, average: bool = False, max_ctas: int = 0) -> torch.Tensor:
+        """In place on all ranks: grads <- sum (or mean) over ranks. Stream-ordered, no host sync."""
+        self.epoch += 1
+        self._cabi.exchange_sum(self._group_for(grads), grads.numel(), self.epoch,
+                                scale=1.0 / self.world if average else 1.0, max_ctas=max_ctas)
+        return grads
+
+    def moment_shards(self, n_floats: int):
+        """This rank's zeroed Adam moments for a flat buffer of n_floats (1/world of it)."""
+        n = int(self._cabi.load().egs_exchange_shard_floats(n_floats, self.world))
+        return (torch.zeros(n, dtype=torch.float32, device=self.device),
+                torch.zeros(n, dtype=torch.float32, device=self.device))
+
+    def adam_step(self, grads: torch.Tensor, params: torch.Tensor, exp_avg, exp_avg_sq, segments, step: int,
+                  betas=(0.9, 0.999), eps: float = 1e-15, average: bool = False, max_ctas: int = 0) -> None:
+        """Sum the gradients, update this rank's slice of `params` and publish it to all ranks."""
+        self.epoch += 1
+        self._cabi.exchange_adam_step(self._group_for(grads), self.peer_pointers(params), exp_avg, exp_avg_sq,
+                                      segments, grads.numel(), self.epoch, step, betas=betas, eps=eps,
+                                      scale=1.0 / self.world if average else 1.0, max_ctas=max_ctas)
+
+    def failed(self) -> bool:
+        """True when a kernel gave up waiting for a peer (synchronises)."""
+        torch.cuda.synchronize(self.device)
+        return bool(self.signals.view(torch.int32)[self._cabi.EGS_EXCHANGE_SIGNAL_WORDS - 1].item())

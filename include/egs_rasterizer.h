@@ -12,6 +12,8 @@
  *   egs_adam_step      <- torch.optim.Adam.step as configured in scene/gaussian_model.py:180-202
  *   egs_se3_apply      <- GaussianModel.apply_trans_rot_new        scene/gaussian_model.py:939-986
  *   egs_adam_se3_step  <- reverse_trans_rot_new + Adam.step        scene/gaussian_model.py:1037-1060
+ *   egs_exchange_sum / egs_exchange_adam_step <- the gradient sum of view-data-parallel training
+ *                         (no reference counterpart; loss.backward() + optimizer.step(), train.py:124,177)
  *   egs_model_forward / egs_model_backward
  *                      <- get_scaling/get_opacity/get_features     scene/gaussian_model.py:126-153
  *                         get_covariance/get_rotated_covariance    scene/gaussian_model.py:29-63,167-171
@@ -231,6 +233,63 @@ int egs_se3_apply(int P, const float* xyz, const int* is_object, int which_objec
 int egs_adam_se3_step(int P, float* xyz, const float* grad_moved, float* exp_avg, float* exp_avg_sq,
                       const int* is_object, int which_object, const float* Rt, double lr, int step,
                       double beta1, double beta2, double eps, void* stream);
+
+/* ---- gradient exchange of view-data-parallel training --------------------- */
+
+/* Every rank renders another camera view of the same scene; the one exchange of the path is the
+ * sum of the parameter gradients (the reference has no multi-GPU mode: this replaces what a
+ * DistributedDataParallel wrapper around train.py's loss.backward(), train.py:124, would do with
+ * NCCL). All ranks keep their gradients in ONE flat fp32 buffer of the same layout, mapped into every
+ * peer's address space (CUDA IPC / symmetric memory over NVLink), and one kernel per rank does the
+ * whole exchange: rank r sums slice r of all the buffers in rank order and writes the sums back into
+ * every buffer, between two flag barriers that live in the signal words. No host synchronisation, no
+ * staging copies; every rank ends with bit-identical sums. */
+#define EGS_MAX_PEERS 8
+#define EGS_EXCHANGE_SIGNAL_WORDS 64
+typedef struct EgsPeerGroup {
+  int world, rank;
+  float* grads[EGS_MAX_PEERS];      /* flat gradient buffer of every rank, as mapped on THIS rank; 16-byte aligned */
+  uint32_t* signals[EGS_MAX_PEERS]; /* EGS_EXCHANGE_SIGNAL_WORDS u32 of every rank, zero before the first call */
+} EgsPeerGroup;
+
+/* grads[p][0..n) <- scale * sum over q of grads[q][0..n), on all ranks p. n_floats % 4 == 0.
+ * `epoch` is the number of this exchange: the same on all ranks, 1 at the first call and one higher at
+ * every call on the same signal words (both entry points count). `max_ctas` bounds the grid (0: two per
+ * SM); all kernels of one exchange must be able to run at the same time. A peer that does not show up
+ * within 20 s makes the kernel give up and set signals[rank][EGS_EXCHANGE_SIGNAL_WORDS - 1] to 1. */
+int egs_exchange_sum(const EgsPeerGroup* group, long long n_floats, float scale, uint32_t epoch, int max_ctas,
+                     void* stream);
+
+/* One parameter group inside the flat layout: floats [begin, end), both multiples of 4. Elements whose
+ * offset from `begin`, modulo `period`, is below `split` use lr_a, the others lr_b (features_dc and
+ * features_rest share the rows of the SH gradient but not the learning rate,
+ * scene/gaussian_model.py:191-192); period == 0: lr_a throughout. */
+typedef struct EgsExchangeSegment {
+  long long begin, end;
+  double lr_a, lr_b;
+  int period, split;
+} EgsExchangeSegment;
+#define EGS_EXCHANGE_MAX_SEGMENTS 8
+
+typedef struct EgsExchangeAdamArgs {
+  float* params[EGS_MAX_PEERS];  /* flat parameter buffer of every rank, same layout as the gradients */
+  float* exp_avg;                /* THIS rank's shard of the moments: egs_exchange_shard_floats() floats each, */
+  float* exp_avg_sq;             /* element k belongs to flat element rank * shard + k */
+  const EgsExchangeSegment* segments;   /* host array, ascending, disjoint */
+  int n_segments;
+  int step;                      /* Adam step number of this update (>= 1) */
+  double beta1, beta2, eps;
+} EgsExchangeAdamArgs;
+long long egs_exchange_shard_floats(long long n_floats, int world);
+
+/* The exchange with the optimiser inside it: rank r sums slice r of the gradients as above, applies
+ * the Adam update of egs_adam_step to slice r of the parameters with its shard of the moments, and
+ * writes the new parameters into every rank's parameter buffer (reduce-scatter, update, all-gather in
+ * one kernel; the moments exist once per node instead of once per rank). Floats outside every
+ * segment (the screen-space gradient that rides along for the densification statistic) are summed
+ * and written back like egs_exchange_sum does; gradients inside segments are left as they were. */
+int egs_exchange_adam_step(const EgsPeerGroup* group, const EgsExchangeAdamArgs* adam, long long n_floats,
+                           float scale, uint32_t epoch, int max_ctas, void* stream);
 
 /* ---- GaussianModel activations --------------------- */
 

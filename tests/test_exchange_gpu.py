@@ -1,0 +1,144 @@
+"""GPU tests of the peer-memory gradient exchange (egs_exchange_sum / egs_exchange_adam_step,
+SURVEY.md 8e). On one GPU the ranks are emulated: every "rank" owns a buffer and a stream on the same
+device, and the kernels of one exchange run side by side (small grids), meeting in the same flag
+barriers a real NVLink group uses. With two or more GPUs the real thing runs under torchrun
+(tests/exchange_worker.py) against NCCL's all-reduce and the single-GPU Adam kernel."""
+import os
+import subprocess
+import sys
+from pathlib import Path
+
+import pytest
+import torch
+
+pytestmark = pytest.mark.gpu
+ROOT = Path(__file__).resolve().parent.parent
+
+
+class EmulatedGroup:
+    def __init__(self, world, n, device, seed=0):
+        from egogaussian_b200 import cabi
+        self.cabi, self.world, self.n = cabi, world, n
+        gen = torch.Generator().manual_seed(seed)
+        self.grads = [torch.randn(n, generator=gen).to(device) for _ in range(world)]
+        self.signals = [torch.zeros(cabi.EGS_EXCHANGE_SIGNAL_WORDS, dtype=torch.int32, device=device)
+                        for _ in range(world)]
+        self.streams = [torch.cuda.Stream(device) for _ in range(world)]
+        self.groups = [cabi.peer_group(world, r, [g.data_ptr() for g in self.grads],
+                                       [s.data_ptr() for s in self.signals]) for r in range(world)]
+        self.epoch = 0
+        torch.cuda.synchronize(device)
+
+    def each_rank(self, fn):
+        self.epoch += 1
+        for r in range(self.world):
+            with torch.cuda.stream(self.streams[r]):
+                fn(r, self.groups[r], self.epoch)
+        torch.cuda.synchronize()
+        assert all(int(s[-1].item()) == 0 for s in self.signals), "a rank gave up waiting for its peers"
+
+
+def rank_order_sum(tensors, scale=1.0):
+    acc = tensors[0].clone()
+    for t in tensors[1:]:
+        acc += t
+    return acc * scale if scale != 1.0 else acc
+
+
+@pytest.mark.parametrize("world,n", [(1, 4096), (2, 1 << 20), (3, 1000 * 4), (4, 4), (8, 1 << 18), (5, 0)])
+def test_exchange_sum_emulated(world, n, built, cuda_device):
+    g = EmulatedGroup(world, n, cuda_device, seed=world)
+    for it in range(3):   # epochs advance; the counters reset themselves
+        expect = rank_order_sum(g.grads, 0.5 if it == 1 else 1.0)
+        g.each_rank(lambda r, grp, e: g.cabi.exchange_sum(grp, n, e, scale=0.5 if it == 1 else 1.0, max_ctas=4))
+        for r in range(world):
+            assert torch.equal(g.grads[r], expect), (world, n, it, r)   # same bits on every rank
+        for t in g.grads:   # new gradients for the next round
+            t.add_(torch.randn_like(t))
+        torch.cuda.synchronize()
+
+
+def test_exchange_adam_step_emulated_matches_sum_then_adam(built, cuda_device):
+    """Reduce-scatter + Adam + all-gather in one kernel == rank-order sum, then egs_adam_step on
+    every group (two learning rates inside the SH rows), bit for bit; moments sharded by rank."""
+    from egogaussian_b200 import cabi
+    from egogaussian_b200.diff_gaussian_rasterization import _C
+    from egogaussian_b200.parallel import FlatGrads
+    world, P, M = 3, 2501, 16
+    lrs = {"xyz": 1.6e-4, "f_dc": 2.5e-3, "f_rest": 1.25e-4, "opacity": 0.05, "scaling": 5e-3, "rotation": 1e-3}
+    layout = FlatGrads(P, M, cuda_device)
+    n = layout.flat.numel()
+    segs = layout.adam_segments(lrs)
+    g = EmulatedGroup(world, n, cuda_device, seed=9)
+    gen = torch.Generator().manual_seed(3)
+    start = torch.randn(n, generator=gen).to(cuda_device)
+    params = [start.clone() for _ in range(world)]
+    shard = int(cabi.load().egs_exchange_shard_floats(n, world))
+    moments = [(torch.zeros(shard, device=cuda_device), torch.zeros(shard, device=cuda_device)) for _ in range(world)]
+
+    # expected: dense Adam on the summed gradient, one run per learning rate, selected per element
+    exp_p, exp_m, exp_v = start.clone(), torch.zeros_like(start), torch.zeros_like(start)
+    lr_of = torch.zeros(n, device=cuda_device, dtype=torch.float64)
+    for (b, e, la, lb, per, sp) in segs:
+        lr_of[b:e] = la
+        if per:
+            idx = (torch.arange(e - b, device=cuda_device) % per) >= sp
+            lr_of[b:e][idx] = lb
+    covered = lr_of > 0
+    for step in (1, 2, 3):
+        summed = rank_order_sum(g.grads)
+        new_p = exp_p.clone()
+        new_m = new_v = None
+        for lr in sorted(set(lr_of[covered].tolist())):
+            p, m, v = exp_p.clone(), exp_m.clone(), exp_v.clone()
+            _C.adam_step([p], [summed], [m], [v], [lr], [step], 0.9, 0.999, 1e-15)
+            pick = lr_of == lr
+            new_p[pick] = p[pick]
+            new_m, new_v = m, v   # the moments do not depend on the learning rate
+        exp_p = new_p
+        exp_m = torch.where(covered, new_m, exp_m)
+        exp_v = torch.where(covered, new_v, exp_v)
+
+        before = [t.clone() for t in g.grads]
+        g.each_rank(lambda r, grp, e: cabi.exchange_adam_step(
+            grp, [p.data_ptr() for p in params], moments[r][0], moments[r][1], segs, n, e, step, max_ctas=4))
+        tail = ~covered   # means2D rides along: summed on all ranks, no update
+        for r in range(world):
+            assert torch.equal(params[r], exp_p), (step, r, (params[r] != exp_p).sum().item())
+            assert torch.equal(g.grads[r][tail], summed[tail])
+            assert torch.equal(g.grads[r][covered], before[r][covered])
+            lo, hi = r * shard, min(n, (r + 1) * shard)
+            if hi > lo:
+                assert torch.equal(moments[r][0][:hi - lo], exp_m[lo:hi])
+                assert torch.equal(moments[r][1][:hi - lo], exp_v[lo:hi])
+        for t in g.grads:
+            t.copy_(torch.randn(n, generator=gen).to(cuda_device))
+        torch.cuda.synchronize()
+
+
+def test_exchange_rejects_bad_arguments(built, cuda_device):
+    from egogaussian_b200 import cabi
+    g = EmulatedGroup(2, 64, cuda_device)
+    with pytest.raises(cabi.EgsError):
+        cabi.exchange_sum(g.groups[0], 62, 1)            # not a multiple of 4
+    bad = cabi.peer_group(2, 0, [t.data_ptr() for t in g.grads], [t.data_ptr() for t in g.signals])
+    bad.world = 9
+    with pytest.raises(cabi.EgsError):
+        cabi.exchange_sum(bad, 64, 1)
+    m = torch.zeros(32, device=cuda_device)
+    with pytest.raises(cabi.EgsError):                   # overlapping segments
+        cabi.exchange_adam_step(g.groups[0], [t.data_ptr() for t in g.grads], m, m.clone(),
+                                [(0, 32, 1e-3, 0, 0, 0), (16, 64, 1e-3, 0, 0, 0)], 64, 1, 1)
+
+
+@pytest.mark.timeout(600)
+def test_exchange_across_gpus_under_torchrun(built):
+    """Two real ranks over NVLink peer memory (skipped on a one-GPU box)."""
+    if torch.cuda.device_count() < 2:
+        pytest.skip("needs two GPUs")
+    env = dict(os.environ, PYTHONPATH=str(ROOT))
+    cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node", "2",
+           "--master-addr", "127.0.0.1", "--master-port", "29731", str(ROOT / "tests" / "exchange_worker.py")]
+    out = subprocess.run(cmd, env=env, capture_output=True, text=True, timeout=500)
+    assert out.returncode == 0, out.stdout[-3000:] + out.stderr[-3000:]
+    assert "exchange worker ok" in out.stdout
