@@ -53,6 +53,7 @@ def parse():
     ap.add_argument("--geom", default="scale_rot", choices=["scale_rot", "cov"])
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
     ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--nccl", action="store_true", help="A/B at N>1: NCCL all-reduce instead of the peer-memory exchange kernel")
     ap.add_argument("--no-hint", action="store_true", help="A/B: exact-size forward (host waits for the count mid-way)")
     return ap.parse_args()
 
@@ -296,6 +297,9 @@ def cpu_baseline(cpu_kw, weights):
 
 
 # --------------------------------------------------------------------------------------------
+LEAF_TO_FLAT = {"means3D": "means3D", "opacities": "opacity", "shs": "sh", "scales": "scales", "rotations": "rotations"}
+
+
 def run_ours(a, rank, world, local_rank):
     import torch
     import torch.distributed as dist
@@ -307,11 +311,23 @@ def run_ours(a, rank, world, local_rank):
     kw, ups, host, cpu_kw, weights = build_inputs(a, rank if dist_on else None, device)
     P, M = a.P, (a.sh_degree + 1) ** 2
     bkw = {k: v for k, v in kw.items() if k not in ("opacities", "image_height", "image_width")}
-    flat = parallel.FlatGrads(P, M, device)
+    # the gradient exchange of view-DP: one kernel per rank over peer-mapped memory (csrc/exchange.cu);
+    # NCCL's all-reduce only if the buffers cannot be mapped on this box (or with --nccl)
+    ex, exchange = None, "none"
+    if dist_on and not a.nccl:
+        try:
+            ex = parallel.PeerExchange(device, multicast=world > 2)
+        except Exception as exc:
+            exchange = "nccl all_reduce (peer mapping failed: %s)" % str(exc)[:120]
+    elif dist_on:
+        exchange = "nccl all_reduce"
+    flat = parallel.FlatGrads(P, M, device, allocate=ex.allocate if ex else None)
+    if ex:
+        exchange = "egs_exchange_sum, " + ("switch multicast" if ex.multicast_pointer(flat.flat) else "peer loads/stores")
     scratch = torch.empty((cabi.load().egs_backward_scratch_bytes(P),), dtype=torch.uint8, device=device)
     state = {}
 
-    def step():
+    def step(exchange_grads=True):
         # like a training loop (and like the torch binding does by itself): guess this iteration's
         # instance count from the previous one so the forward never stalls the GPU on the host
         fwd = cabi.forward(num_rendered_hint=0 if a.no_hint else state.get("hint", 0), **kw)
@@ -321,8 +337,11 @@ def run_ours(a, rank, world, local_rank):
             out = {"means3D": out["means3D"], "sh": out["sh"], "opacity": out["opacity"], "means2D": out["means2D"],
                    "cov3D": state.setdefault("cov", torch.empty((P, 6), device=device))}
         cabi.backward(fwd, out=out, scratch=scratch, **bkw, **ups)
-        if dist_on:
-            parallel.allreduce_gradients(flat.flat)
+        if dist_on and exchange_grads:
+            if ex:
+                ex.sum(flat.flat)
+            else:
+                parallel.allreduce_gradients(flat.flat)
         state["fwd"] = fwd
 
     clocks = ClockSampler(local_rank) if rank == 0 else None
@@ -402,7 +421,11 @@ def run_ours(a, rank, world, local_rank):
             torch.cuda.current_stream().wait_event(copied)
             loss = (color * dv["wc"]).sum() + (depth * dv["wd"]).sum() + (alpha * dv["wa"]).sum()
             loss.backward()
-            if dist_on:
+            if dist_on and ex and all(k in LEAF_TO_FLAT for k in leaves):   # gather the autograd gradients into the peer-mapped flat buffer, one exchange
+                for k, t in leaves.items():
+                    flat.views[LEAF_TO_FLAT[k]].copy_(t.grad.view_as(flat.views[LEAF_TO_FLAT[k]]))
+                ex.sum(flat.flat)
+            elif dist_on:
                 for t in leaves.values():
                     dist.all_reduce(t.grad)
             loss_host.copy_(loss.detach(), non_blocking=True)
@@ -431,9 +454,27 @@ def run_ours(a, rank, world, local_rank):
             stepc[0] += 1
             _C.adam_step(params, grads, ms_, vs_, lrs, [stepc[0]] * len(params), 0.9, 0.999, 1e-15)
 
+        if ex:   # exchange and update in one kernel: Adam on the rank's slice, moments sharded by rank
+            del params, ms_, vs_
+            params_flat = ex.allocate(flat.flat.numel())
+            params_flat.normal_()
+            m_shard, v_shard = ex.moment_shards(flat.flat.numel())
+            segs = flat.adam_segments({"xyz": 1.6e-4, "f_dc": 2.5e-3, "f_rest": 2.5e-3 / 20, "opacity": 0.05,
+                                       "scaling": 5e-3, "rotation": 1e-3})
+            torch.cuda.synchronize()
+            dist.barrier()
+
+            def train_step():   # noqa: F811
+                step(exchange_grads=False)
+                stepc[0] += 1
+                ex.adam_step(flat.flat, params_flat, m_shard, v_shard, segs, stepc[0])
+            extra["train_step_exchange"] = "egs_exchange_adam_step"
+
         sec3 = timed_region(train_step, a.steps, 3, dist_on, device)
         extra["train_step_iters_per_s"] = world * a.steps / sec3
-        extra["adam_floats"] = int(sum(p.numel() for p in params))
+        extra["adam_floats"] = int(sum(flat.sizes[:5 if a.geom == "scale_rot" else 3]))
+        if ex and ex.failed():
+            raise RuntimeError("a rank gave up waiting for its peers inside the exchange kernel")
     except Exception as exc:  # informational only
         extra["train_step_error"] = str(exc)[:200]
 
@@ -519,7 +560,7 @@ def run_ours(a, rank, world, local_rank):
                                "(rank r renders view r of the configs[3] 8-view batch when N>1)",
                    "P": P, "sh_degree": a.sh_degree, "width": a.width, "height": a.height, "geometry": a.geom,
                    "num_rendered": R, "visible": V, "fragments": frag,
-                   "parallelism": "view-dp%d" % world if dist_on else "single",
+                   "parallelism": "view-dp%d" % world if dist_on else "single", "exchange": exchange,
                    "l2": "working set (>300 MB of Gaussian data + sort buffers per step) exceeds the 126 MB L2; no flush"},
         "e2e": e2e, "gpu_launches": int(launches), "roofline": roofline, "kernels": kernels, "clocks": clk,
         "mfragments_per_s": {"fwd": frag / (kernels["blend_fwd"]["ms_per_step"] * 1e3),

@@ -94,7 +94,7 @@ EGS_EXCHANGE_MAX_SEGMENTS = 8
 
 class EgsPeerGroup(C.Structure):
     _fields_ = [("world", C.c_int), ("rank", C.c_int), ("grads", C.c_void_p * EGS_MAX_PEERS),
-                ("signals", C.c_void_p * EGS_MAX_PEERS)]
+                ("signals", C.c_void_p * EGS_MAX_PEERS), ("grads_multicast", C.c_void_p)]
 
 
 class EgsExchangeSegment(C.Structure):
@@ -103,7 +103,8 @@ class EgsExchangeSegment(C.Structure):
 
 
 class EgsExchangeAdamArgs(C.Structure):
-    _fields_ = [("params", C.c_void_p * EGS_MAX_PEERS), ("exp_avg", C.c_void_p), ("exp_avg_sq", C.c_void_p),
+    _fields_ = [("params", C.c_void_p * EGS_MAX_PEERS), ("params_multicast", C.c_void_p),
+                ("exp_avg", C.c_void_p), ("exp_avg_sq", C.c_void_p),
                 ("segments", C.POINTER(EgsExchangeSegment)), ("n_segments", C.c_int), ("step", C.c_int),
                 ("beta1", C.c_double), ("beta2", C.c_double), ("eps", C.c_double)]
 
@@ -616,10 +617,11 @@ def knn_mean_dist2(points, stream=None, exhaustive=False):
     return out
 
 
-def peer_group(world: int, rank: int, grad_ptrs, signal_ptrs) -> EgsPeerGroup:
+def peer_group(world: int, rank: int, grad_ptrs, signal_ptrs, grads_multicast: int = 0) -> EgsPeerGroup:
     """EgsPeerGroup from the per-rank device addresses (ints) of the gradient buffers and signal words."""
     g = EgsPeerGroup()
     g.world, g.rank = world, rank
+    g.grads_multicast = int(grads_multicast) or None
     for q in range(world):
         g.grads[q] = int(grad_ptrs[q])
         g.signals[q] = int(signal_ptrs[q])
@@ -635,12 +637,13 @@ def exchange_sum(group: EgsPeerGroup, n_floats: int, epoch: int, scale: float = 
 
 def exchange_adam_step(group: EgsPeerGroup, param_ptrs, exp_avg, exp_avg_sq, segments, n_floats: int, epoch: int,
                        step: int, betas=(0.9, 0.999), eps: float = 1e-15, scale: float = 1.0, max_ctas: int = 0,
-                       stream=None) -> None:
+                       stream=None, params_multicast: int = 0) -> None:
     """egs_exchange_adam_step. `segments`: [(begin, end, lr_a, lr_b, period, split)] in floats;
     exp_avg / exp_avg_sq: this rank's moment shards (egs_exchange_shard_floats floats each)."""
     a = EgsExchangeAdamArgs()
     for q in range(group.world):
         a.params[q] = int(param_ptrs[q])
+    a.params_multicast = int(params_multicast) or None
     a.exp_avg, a.exp_avg_sq = exp_avg.data_ptr(), exp_avg_sq.data_ptr()
     segs = (EgsExchangeSegment * max(len(segments), 1))()
     for k, (b, e, la, lb, per, sp) in enumerate(segments):

@@ -39,6 +39,8 @@ struct ExLaunch {
   float* grads[EGS_MAX_PEERS];
   float* params[EGS_MAX_PEERS];
   uint32_t* signals[EGS_MAX_PEERS];
+  float* grads_mc;    // multicast mappings of the same buffers, or NULL
+  float* params_mc;
   long long lo4, hi4;   // this rank's slice, in 4-float chunks
   float scale;
   uint32_t epoch;
@@ -92,73 +94,16 @@ __device__ __forceinline__ void wait_peer_flags(const ExLaunch& L, int slot) {
   __syncthreads();
 }
 
-__device__ __forceinline__ float4 sum_over_ranks(const ExLaunch& L, long long c) {
-  float4 part[EGS_MAX_PEERS];
-#pragma unroll
-  for (int q = 0; q < EGS_MAX_PEERS; ++q)
-    if (q < L.world) part[q] = ld_peer_f4(L.grads[q] + 4 * c);
-  float4 acc = part[0];
-#pragma unroll
-  for (int q = 1; q < EGS_MAX_PEERS; ++q)
-    if (q < L.world) {
-      acc.x += part[q].x; acc.y += part[q].y; acc.z += part[q].z; acc.w += part[q].w;
-    }
-  acc.x *= L.scale; acc.y *= L.scale; acc.z *= L.scale; acc.w *= L.scale;
-  return acc;
-}
-
-__device__ __forceinline__ void store_to_all(float* const* bufs, int world, long long c, float4 v) {
-#pragma unroll
-  for (int q = 0; q < EGS_MAX_PEERS; ++q)
-    if (q < world) st_peer_f4(bufs[q] + 4 * c, v);
-}
-
-template <bool ADAM>
-__global__ void __launch_bounds__(EX_THREADS, 2) exchange_kernel(const __grid_constant__ ExLaunch L) {
-  __shared__ bool s_last;
-  // ---- barrier in: my backward is complete (this kernel follows it in stream order) ----
+// my backward is complete (this kernel follows it in stream order); wait until every peer's is
+__device__ __forceinline__ void barrier_in(const ExLaunch& L) {
   if (blockIdx.x == 0 && (int)threadIdx.x < L.world)
     st_release_sys(L.signals[threadIdx.x] + EX_SLOT_IN + L.rank, L.epoch);
   wait_peer_flags(L, EX_SLOT_IN);
+}
 
-  const long long stride = (long long)gridDim.x * EX_THREADS;
-  for (long long c = L.lo4 + (long long)blockIdx.x * EX_THREADS + threadIdx.x; c < L.hi4; c += stride) {
-    const float4 g = sum_over_ranks(L, c);
-    if (ADAM) {
-      int si = -1;
-#pragma unroll 1
-      for (int k = 0; k < L.n_segments; ++k)
-        if (c >= L.seg[k].begin4 && c < L.seg[k].end4) si = k;
-      if (si >= 0) {
-        const ExSegmentDev& S = L.seg[si];
-        float ns[4] = {S.neg_step_a, S.neg_step_a, S.neg_step_a, S.neg_step_a};
-        if (S.period > 0) {
-          const int r0 = (int)(((c - S.begin4) * 4) % S.period);
-#pragma unroll
-          for (int k = 0; k < 4; ++k) {
-            int r = r0 + k;
-            if (r >= S.period) r -= S.period;
-            ns[k] = r < S.split ? S.neg_step_a : S.neg_step_b;
-          }
-        }
-        const long long k4 = (c - L.lo4) * 4;
-        float4 p = *reinterpret_cast<const float4*>(L.params[L.rank] + 4 * c);
-        float4 m = *reinterpret_cast<const float4*>(L.exp_avg + k4);
-        float4 v = *reinterpret_cast<const float4*>(L.exp_avg_sq + k4);
-        adam_elem(p.x, g.x, m.x, v.x, L.one_minus_b1, L.b2, L.one_minus_b2, L.eps, ns[0], L.bc2_sqrt);
-        adam_elem(p.y, g.y, m.y, v.y, L.one_minus_b1, L.b2, L.one_minus_b2, L.eps, ns[1], L.bc2_sqrt);
-        adam_elem(p.z, g.z, m.z, v.z, L.one_minus_b1, L.b2, L.one_minus_b2, L.eps, ns[2], L.bc2_sqrt);
-        adam_elem(p.w, g.w, m.w, v.w, L.one_minus_b1, L.b2, L.one_minus_b2, L.eps, ns[3], L.bc2_sqrt);
-        *reinterpret_cast<float4*>(L.exp_avg + k4) = m;
-        *reinterpret_cast<float4*>(L.exp_avg_sq + k4) = v;
-        store_to_all(L.params, L.world, c, p);
-        continue;
-      }
-    }
-    store_to_all(L.grads, L.world, c, g);
-  }
-
-  // ---- barrier out: all my stores are visible everywhere, then all peers' stores are visible here ----
+// all my stores are visible everywhere, then all peers' stores are visible here; the last CTA of the
+// grid speaks for the rank
+__device__ __forceinline__ void barrier_out(const ExLaunch& L, bool& s_last) {
   __threadfence_system();
   __syncthreads();
   if (threadIdx.x == 0) {
@@ -172,6 +117,129 @@ __global__ void __launch_bounds__(EX_THREADS, 2) exchange_kernel(const __grid_co
   if (!s_last) return;
   if ((int)threadIdx.x < L.world) st_release_sys(L.signals[threadIdx.x] + EX_SLOT_OUT + L.rank, L.epoch);
   wait_peer_flags(L, EX_SLOT_OUT);
+}
+
+// multicast addresses (NVLink SHARP): one load returns the sum over all ranks, formed in the switch;
+// one store lands in every rank's buffer
+__device__ __forceinline__ float4 ld_reduce_mc_f4(const float* p) {
+  float4 v;
+  asm volatile("multimem.ld_reduce.relaxed.sys.global.add.v4.f32 {%0, %1, %2, %3}, [%4];"
+               : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w)
+               : "l"(p)
+               : "memory");
+  return v;
+}
+__device__ __forceinline__ void st_mc_f4(float* p, float4 v) {
+  asm volatile("multimem.st.relaxed.sys.global.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(p), "f"(v.x), "f"(v.y),
+               "f"(v.z), "f"(v.w)
+               : "memory");
+}
+
+__device__ __forceinline__ void store_to_all(float* const* bufs, int world, long long c, float4 v) {
+#pragma unroll
+  for (int q = 0; q < EGS_MAX_PEERS; ++q)
+    if (q < world) st_peer_f4(bufs[q] + 4 * c, v);
+}
+
+// Adam on chunk c of this rank's slice; returns the new parameters
+__device__ __forceinline__ float4 adam_chunk(const ExLaunch& L, const ExSegmentDev& S, long long c, const float4 g) {
+  float ns0 = S.neg_step_a, ns1 = S.neg_step_a, ns2 = S.neg_step_a, ns3 = S.neg_step_a;
+  if (S.period > 0) {
+    const int r0 = (int)(((c - S.begin4) * 4) % S.period);
+    auto pick = [&](int r) { return (r >= S.period ? r - S.period : r) < S.split ? S.neg_step_a : S.neg_step_b; };
+    ns0 = pick(r0); ns1 = pick(r0 + 1); ns2 = pick(r0 + 2); ns3 = pick(r0 + 3);
+  }
+  const long long k4 = (c - L.lo4) * 4;
+  float4 p = *reinterpret_cast<const float4*>(L.params[L.rank] + 4 * c);
+  float4 m = *reinterpret_cast<const float4*>(L.exp_avg + k4);
+  float4 v = *reinterpret_cast<const float4*>(L.exp_avg_sq + k4);
+  adam_elem(p.x, g.x, m.x, v.x, L.one_minus_b1, L.b2, L.one_minus_b2, L.eps, ns0, L.bc2_sqrt);
+  adam_elem(p.y, g.y, m.y, v.y, L.one_minus_b1, L.b2, L.one_minus_b2, L.eps, ns1, L.bc2_sqrt);
+  adam_elem(p.z, g.z, m.z, v.z, L.one_minus_b1, L.b2, L.one_minus_b2, L.eps, ns2, L.bc2_sqrt);
+  adam_elem(p.w, g.w, m.w, v.w, L.one_minus_b1, L.b2, L.one_minus_b2, L.eps, ns3, L.bc2_sqrt);
+  *reinterpret_cast<float4*>(L.exp_avg + k4) = m;
+  *reinterpret_cast<float4*>(L.exp_avg_sq + k4) = v;
+  return p;
+}
+
+__device__ __forceinline__ int segment_of(const ExLaunch& L, long long c) {
+  int si = -1;
+#pragma unroll 1
+  for (int k = 0; k < L.n_segments; ++k)
+    if (c >= L.seg[k].begin4 && c < L.seg[k].end4) si = k;
+  return si;
+}
+
+// WMAX: the smallest of 2, 4, 8 that holds `world`; a thread keeps 8 peer loads of 16 bytes in flight
+// (8 / WMAX chunks from every rank), which is what it takes to fill an NVLink with 1024 threads per SM
+template <bool ADAM, int WMAX>
+__global__ void __launch_bounds__(EX_THREADS, 2) exchange_kernel(const __grid_constant__ ExLaunch L) {
+  constexpr int U = 8 / WMAX;
+  __shared__ bool s_last;
+  barrier_in(L);
+
+  const long long stride = (long long)gridDim.x * EX_THREADS * U;
+  for (long long c0 = L.lo4 + (long long)blockIdx.x * EX_THREADS * U + threadIdx.x; c0 < L.hi4; c0 += stride) {
+    float4 part[U][WMAX];
+#pragma unroll
+    for (int u = 0; u < U; ++u)
+#pragma unroll
+      for (int q = 0; q < WMAX; ++q)
+        if (q < L.world && c0 + u * EX_THREADS < L.hi4) part[u][q] = ld_peer_f4(L.grads[q] + 4 * (c0 + u * EX_THREADS));
+#pragma unroll
+    for (int u = 0; u < U; ++u) {
+      const long long c = c0 + u * EX_THREADS;
+      if (c >= L.hi4) break;
+      float4 g = part[u][0];   // rank order, whoever adds
+#pragma unroll
+      for (int q = 1; q < WMAX; ++q)
+        if (q < L.world) {
+          g.x += part[u][q].x; g.y += part[u][q].y; g.z += part[u][q].z; g.w += part[u][q].w;
+        }
+      g.x *= L.scale; g.y *= L.scale; g.z *= L.scale; g.w *= L.scale;
+      if (ADAM) {
+        const int si = segment_of(L, c);
+        if (si >= 0) {
+          store_to_all(L.params, L.world, c, adam_chunk(L, L.seg[si], c, g));
+          continue;
+        }
+      }
+      store_to_all(L.grads, L.world, c, g);
+    }
+  }
+
+  barrier_out(L, s_last);
+}
+
+// The same exchange through the switch: (world - 1) / world of the buffer crosses each link once per
+// direction instead of twice. Four reductions of 16 bytes in flight per thread.
+template <bool ADAM>
+__global__ void __launch_bounds__(EX_THREADS, 2) exchange_mc_kernel(const __grid_constant__ ExLaunch L) {
+  constexpr int U = 4;
+  __shared__ bool s_last;
+  barrier_in(L);
+  const long long stride = (long long)gridDim.x * EX_THREADS * U;
+  for (long long c0 = L.lo4 + (long long)blockIdx.x * EX_THREADS * U + threadIdx.x; c0 < L.hi4; c0 += stride) {
+    float4 g[U];
+#pragma unroll
+    for (int u = 0; u < U; ++u)
+      if (c0 + u * EX_THREADS < L.hi4) g[u] = ld_reduce_mc_f4(L.grads_mc + 4 * (c0 + u * EX_THREADS));
+#pragma unroll
+    for (int u = 0; u < U; ++u) {
+      const long long c = c0 + u * EX_THREADS;
+      if (c >= L.hi4) break;
+      g[u].x *= L.scale; g[u].y *= L.scale; g[u].z *= L.scale; g[u].w *= L.scale;
+      if (ADAM) {
+        const int si = segment_of(L, c);
+        if (si >= 0) {
+          st_mc_f4(L.params_mc + 4 * c, adam_chunk(L, L.seg[si], c, g[u]));
+          continue;
+        }
+      }
+      st_mc_f4(L.grads_mc + 4 * c, g[u]);
+    }
+  }
+  barrier_out(L, s_last);
 }
 
 static int fill_group(const char* who, const EgsPeerGroup* g, long long n, ExLaunch& L) {
@@ -188,6 +256,11 @@ static int fill_group(const char* who, const EgsPeerGroup* g, long long n, ExLau
     L.grads[q] = g->grads[q];
     L.signals[q] = g->signals[q];
   }
+  if (reinterpret_cast<uintptr_t>(g->grads_multicast) & 15u) {
+    set_error("%s: multicast address not 16-byte aligned", who);
+    return EGS_ERR_INVALID_ARGUMENT;
+  }
+  L.grads_mc = g->grads_multicast;
   L.world = g->world;
   L.rank = g->rank;
   const long long n4 = n / 4, per = (n4 + g->world - 1) / g->world;
@@ -197,7 +270,7 @@ static int fill_group(const char* who, const EgsPeerGroup* g, long long n, ExLau
 }
 
 static unsigned exchange_grid(const ExLaunch& L, int max_ctas) {
-  long long ctas = (L.hi4 - L.lo4 + EX_THREADS - 1) / EX_THREADS;
+  long long ctas = (L.hi4 - L.lo4 + EX_THREADS - 1) / EX_THREADS;   // (more than the unrolled loop needs: harmless)
   const long long cap = max_ctas > 0 ? max_ctas : 148 * 2;
   if (ctas > cap) ctas = cap;
   return (unsigned)(ctas < 1 ? 1 : ctas);   // an empty slice still takes part in the barriers
@@ -219,7 +292,11 @@ extern "C" int egs_exchange_sum(const EgsPeerGroup* group, long long n_floats, f
   L.scale = scale;
   L.epoch = epoch;
   cudaStream_t st = static_cast<cudaStream_t>(stream);
-  exchange_kernel<false><<<exchange_grid(L, max_ctas), EX_THREADS, 0, st>>>(L);
+  const unsigned grid = exchange_grid(L, max_ctas);
+  if (L.grads_mc) exchange_mc_kernel<false><<<grid, EX_THREADS, 0, st>>>(L);
+  else if (L.world <= 2) exchange_kernel<false, 2><<<grid, EX_THREADS, 0, st>>>(L);
+  else if (L.world <= 4) exchange_kernel<false, 4><<<grid, EX_THREADS, 0, st>>>(L);
+  else exchange_kernel<false, 8><<<grid, EX_THREADS, 0, st>>>(L);
   EGS_AFTER_LAUNCH(st, false);
   return EGS_OK;
 }
@@ -277,7 +354,14 @@ extern "C" int egs_exchange_adam_step(const EgsPeerGroup* group, const EgsExchan
   L.scale = scale;
   L.epoch = epoch;
   cudaStream_t st = static_cast<cudaStream_t>(stream);
-  exchange_kernel<true><<<exchange_grid(L, max_ctas), EX_THREADS, 0, st>>>(L);
+  // through the switch only when both buffers have a multicast mapping
+  L.params_mc = adam->params_multicast;
+  if (!L.params_mc || (reinterpret_cast<uintptr_t>(L.params_mc) & 15u)) L.grads_mc = L.params_mc = nullptr;
+  const unsigned grid = exchange_grid(L, max_ctas);
+  if (L.grads_mc) exchange_mc_kernel<true><<<grid, EX_THREADS, 0, st>>>(L);
+  else if (L.world <= 2) exchange_kernel<true, 2><<<grid, EX_THREADS, 0, st>>>(L);
+  else if (L.world <= 4) exchange_kernel<true, 4><<<grid, EX_THREADS, 0, st>>>(L);
+  else exchange_kernel<true, 8><<<grid, EX_THREADS, 0, st>>>(L);
   EGS_AFTER_LAUNCH(st, false);
   return EGS_OK;
 }

@@ -87,7 +87,9 @@ class PeerExchange:
     handles and maps every rank's buffer into this process. GPUs of one NVLink domain only; raises
     when the buffers cannot be mapped (the caller then stays on `allreduce_gradients`)."""
 
-    def __init__(self, device, group=None):
+    def __init__(self, device, group=None, multicast: bool = True):
+        """`multicast`: form the sums inside the NVLink switch when the buffers have a multicast
+        mapping (NVLS); otherwise, or when False, peer loads and stores."""
         import torch.distributed as dist
         import torch.distributed._symmetric_memory as symm
         from . import cabi
@@ -98,6 +100,7 @@ class PeerExchange:
         if self.world > cabi.EGS_MAX_PEERS:
             raise ValueError(f"PeerExchange spans one node: at most {cabi.EGS_MAX_PEERS} ranks")
         self._handles = []
+        self.use_multicast = multicast
         self.epoch = 0
         self.signals = self.allocate(cabi.EGS_EXCHANGE_SIGNAL_WORDS)   # float zeros == u32 zeros
         self._signal_ptrs = self.peer_pointers(self.signals)
@@ -113,17 +116,30 @@ class PeerExchange:
         self._dist.barrier(self.group)
         return t
 
-    def peer_pointers(self, t: torch.Tensor):
+    def _handle_of(self, t: torch.Tensor):
         for buf, hdl in self._handles:
             if buf.data_ptr() == t.data_ptr():
-                return [int(p) for p in hdl.buffer_ptrs]
+                return hdl
         raise ValueError("tensor was not allocated by this PeerExchange")
+
+    def peer_pointers(self, t: torch.Tensor):
+        hdl = self._handle_of(t)
+        off = t.data_ptr() - int(hdl.buffer_ptrs[self.rank])   # the tensor may sit inside a larger block
+        return [int(p) + off for p in hdl.buffer_ptrs]
+
+    def multicast_pointer(self, t: torch.Tensor) -> int:
+        """Address of the switch's multicast mapping of `t`, 0 when there is none."""
+        hdl = self._handle_of(t)
+        if not self.use_multicast or self.world < 2 or not getattr(hdl, "has_multicast_support", lambda *a: False):
+            return 0
+        base = int(getattr(hdl, "multicast_ptr", 0) or 0)
+        return base + (t.data_ptr() - int(hdl.buffer_ptrs[self.rank])) if base else 0
 
     def _group_for(self, grads: torch.Tensor):
         key = grads.data_ptr()
         if key not in self._groups:
             self._groups[key] = self._cabi.peer_group(self.world, self.rank, self.peer_pointers(grads),
-                                                      self._signal_ptrs)
+                                                      self._signal_ptrs, self.multicast_pointer(grads))
         return self._groups[key]
 
     def sum(self, grads: torch.Tensor, average: bool = False, max_ctas: int = 0) -> torch.Tensor:
@@ -145,7 +161,8 @@ class PeerExchange:
         self.epoch += 1
         self._cabi.exchange_adam_step(self._group_for(grads), self.peer_pointers(params), exp_avg, exp_avg_sq,
                                       segments, grads.numel(), self.epoch, step, betas=betas, eps=eps,
-                                      scale=1.0 / self.world if average else 1.0, max_ctas=max_ctas)
+                                      scale=1.0 / self.world if average else 1.0, max_ctas=max_ctas,
+                                      params_multicast=self.multicast_pointer(params))
 
     def failed(self) -> bool:
         """True when a kernel gave up waiting for a peer (synchronises)."""

@@ -250,6 +250,10 @@ typedef struct EgsPeerGroup {
   int world, rank;
   float* grads[EGS_MAX_PEERS];      /* flat gradient buffer of every rank, as mapped on THIS rank; 16-byte aligned */
   uint32_t* signals[EGS_MAX_PEERS]; /* EGS_EXCHANGE_SIGNAL_WORDS u32 of every rank, zero before the first call */
+  float* grads_multicast;           /* NVLink-switch multicast mapping of the same gradient buffers, or NULL:
+                                       with it the sums are formed inside the switch (multimem.ld_reduce) and
+                                       stored to all ranks by one store; the order of the additions is then
+                                       the switch's, still one result for all ranks */
 } EgsPeerGroup;
 
 /* grads[p][0..n) <- scale * sum over q of grads[q][0..n), on all ranks p. n_floats % 4 == 0.
@@ -273,6 +277,7 @@ typedef struct EgsExchangeSegment {
 
 typedef struct EgsExchangeAdamArgs {
   float* params[EGS_MAX_PEERS];  /* flat parameter buffer of every rank, same layout as the gradients */
+  float* params_multicast;       /* multicast mapping of the parameter buffers, or NULL (then peer stores) */
   float* exp_avg;                /* THIS rank's shard of the moments: egs_exchange_shard_floats() floats each, */
   float* exp_avg_sq;             /* element k belongs to flat element rank * shard + k */
   const EgsExchangeSegment* segments;   /* host array, ascending, disjoint */

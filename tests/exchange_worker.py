@@ -17,10 +17,26 @@ def main():
     device = torch.device("cuda", int(os.environ.get("LOCAL_RANK", rank)))
     torch.cuda.set_device(device)
     dist.init_process_group("nccl", device_id=device)
-    ex = PeerExchange(device)
+    for multicast in (False, True):
+        run(rank, world, device, multicast)
+    if rank == 0:
+        print("exchange worker ok", flush=True)
+    dist.barrier()
+    dist.destroy_process_group()
+
+
+def run(rank, world, device, multicast):
+    from egogaussian_b200.diff_gaussian_rasterization import _C
+    from egogaussian_b200.parallel import FlatGrads, PeerExchange
+    ex = PeerExchange(device, multicast=multicast)
     P, M = int(os.environ.get("EGS_EXCHANGE_P", "200000")), 16
     layout = FlatGrads(P, M, device, allocate=ex.allocate)
     n = layout.flat.numel()
+    through_switch = ex.multicast_pointer(layout.flat) != 0
+    if multicast and not through_switch:
+        if rank == 0:
+            print("no multicast mapping on this box: switch path not exercised", flush=True)
+        return
     gen = torch.Generator().manual_seed(100 + rank)
 
     # ---- sum against NCCL (two ranks: a + b in either order; more: within rounding) ----
@@ -93,11 +109,8 @@ def main():
     assert not ex.failed()
     if rank == 0:
         mb = n * 4 / 1e6
-        print(f"exchange timing world={world} buffer={mb:.1f} MB: nccl all_reduce {t_nccl:.3f} ms, "
-              f"peer sum {t_peer:.3f} ms, peer sum+adam {t_fused:.3f} ms", flush=True)
-        print("exchange worker ok", flush=True)
-    dist.barrier()
-    dist.destroy_process_group()
+        print(f"exchange timing world={world} buffer={mb:.1f} MB {'switch multicast' if through_switch else 'peer loads/stores'}: "
+              f"nccl all_reduce {t_nccl:.3f} ms, sum {t_peer:.3f} ms, sum+adam {t_fused:.3f} ms", flush=True)
 
 
 if __name__ == "__main__":
