@@ -316,7 +316,7 @@ def run_ours(a, rank, world, local_rank):
     ex, exchange = None, "none"
     if dist_on and not a.nccl:
         try:
-            ex = parallel.PeerExchange(device, multicast=world > 2)
+            ex = parallel.PeerExchange(device)
         except Exception as exc:
             exchange = "nccl all_reduce (peer mapping failed: %s)" % str(exc)[:120]
     elif dist_on:
