@@ -109,6 +109,11 @@ class EgsExchangeAdamArgs(C.Structure):
                 ("beta1", C.c_double), ("beta2", C.c_double), ("eps", C.c_double)]
 
 
+class EgsPlyColumns(C.Structure):   # also EgsPlyColumnsOut: same layout, without the consts
+    _fields_ = [(n, C.c_void_p) for n in ("xyz", "features_dc", "features_rest", "opacity", "scaling", "rotation",
+                                          "label", "generation", "is_object")]
+
+
 class EgsGeomView(C.Structure):
     _fields_ = [("depths", C.c_void_p), ("means2D", C.c_void_p), ("conic_opacity", C.c_void_p),
                 ("rgb_depth", C.c_void_p), ("clamped", C.c_void_p), ("tiles_touched", C.c_void_p),
@@ -130,7 +135,7 @@ EXPORTED_SYMBOLS = [
     "egs_se3_apply", "egs_adam_se3_step", "egs_model_forward", "egs_model_backward",
     "egs_forward_raw", "egs_backward_raw",
     "egs_image_loss_workspace_bytes", "egs_image_loss", "egs_densify_stats",
-    "egs_compact_scratch_bytes", "egs_compact_plan", "egs_compact_rows", "egs_knn_workspace_bytes", "egs_knn_mean_dist2",
+    "egs_compact_scratch_bytes", "egs_compact_plan", "egs_compact_rows", "egs_knn_workspace_bytes", "egs_knn_mean_dist2", "egs_ply_record_floats", "egs_ply_pack", "egs_ply_unpack",
     "egs_exchange_sum", "egs_exchange_shard_floats", "egs_exchange_adam_step", "egs_geom_view", "egs_binning_view", "egs_image_view",
     "egs_launch_count", "egs_last_error", "egs_abi_version",
     "egs_profile_enable", "egs_profile_read", "egs_profile_stage_name",
@@ -199,6 +204,13 @@ def load() -> C.CDLL:
     lib.egs_exchange_adam_step.restype = C.c_int
     lib.egs_exchange_adam_step.argtypes = [C.POINTER(EgsPeerGroup), C.POINTER(EgsExchangeAdamArgs), C.c_longlong,
                                            C.c_float, C.c_uint32, C.c_int, C.c_void_p]
+    lib.egs_ply_record_floats.restype = C.c_int
+    lib.egs_ply_record_floats.argtypes = [C.c_int, C.c_int]
+    lib.egs_ply_pack.restype = C.c_int
+    lib.egs_ply_pack.argtypes = [C.c_int, C.c_int, C.POINTER(EgsPlyColumns), C.c_int, C.c_void_p, C.c_void_p]
+    lib.egs_ply_unpack.restype = C.c_int
+    lib.egs_ply_unpack.argtypes = [C.c_int, C.c_int, C.c_void_p, C.c_int, C.POINTER(C.c_int), C.POINTER(EgsPlyColumns),
+                                   C.c_float, C.c_int, C.c_void_p]
     lib.egs_knn_workspace_bytes.restype = C.c_size_t
     lib.egs_knn_workspace_bytes.argtypes = [C.c_int]
     lib.egs_densify_stats.restype = C.c_int

@@ -14,6 +14,7 @@
  *   egs_adam_se3_step  <- reverse_trans_rot_new + Adam.step        scene/gaussian_model.py:1037-1060
  *   egs_exchange_sum / egs_exchange_adam_step <- the gradient sum of view-data-parallel training
  *                         (no reference counterpart; loss.backward() + optimizer.step(), train.py:124,177)
+ *   egs_ply_pack / egs_ply_unpack <- GaussianModel.save_ply / load_ply  scene/gaussian_model.py:375-481
  *   egs_model_forward / egs_model_backward
  *                      <- get_scaling/get_opacity/get_features     scene/gaussian_model.py:126-153
  *                         get_covariance/get_rotated_covariance    scene/gaussian_model.py:29-63,167-171
@@ -415,6 +416,34 @@ int egs_compact_rows(int P, const void* scratch, const EgsRowTensor* tensors, in
 size_t egs_knn_workspace_bytes(int P);
 int egs_knn_mean_dist2(int P, const float* points, float* mean_dist2, void* workspace, size_t workspace_bytes,
                        void* stream);
+
+/* ---- checkpoint records (save_ply / load_ply, scene/gaussian_model.py:340-481) ---- */
+
+/* One record of 4-byte floats per Gaussian, in the reference's property order:
+ *   x y z  nx ny nz (zeros)  f_dc_0..2  f_rest_0..  opacity  scale_0..2  rot_0..3  [label generation is_object]
+ * f_rest_j with j = c * (sh_coeffs - 1) + k is features_rest[p][k][c] (gaussian_model.py:381). All device
+ * pointers; features_dc [P,1,3], features_rest [P,sh_coeffs-1,3], label [P,1] float, generation and
+ * is_object [P,1] int32 (stored as floats in the file, like the reference does). */
+typedef struct EgsPlyColumns {
+  const float *xyz, *features_dc, *features_rest, *opacity, *scaling, *rotation, *label;
+  const int *generation, *is_object;
+} EgsPlyColumns;
+typedef struct EgsPlyColumnsOut {
+  float *xyz, *features_dc, *features_rest, *opacity, *scaling, *rotation, *label;
+  int *generation, *is_object;
+} EgsPlyColumnsOut;
+#define EGS_PLY_MAX_COLUMNS 128
+
+/* 14 + 3 * sh_coeffs (+ 3 with the extras): 62 / 65 at SH degree 3. */
+int egs_ply_record_floats(int sh_coeffs, int with_extras);
+/* rows: device [P, egs_ply_record_floats()] <- the columns (what save_ply writes after the header). */
+int egs_ply_pack(int P, int sh_coeffs, const EgsPlyColumns* cols, int with_extras, float* rows, void* stream);
+/* The columns <- rows: device [P, record_floats] as read from a file whose properties may come in any
+ * order: column_of (host, egs_ply_record_floats(sh_coeffs, 1) ints) gives, for every canonical column, its
+ * position in the file's record, or -1 when the file lacks it (normals and the three extras only; a
+ * missing label becomes label_default, generation 0, is_object is_object_default: load_ply :444-461). */
+int egs_ply_unpack(int P, int sh_coeffs, const float* rows, int record_floats, const int* column_of,
+                   const EgsPlyColumnsOut* cols, float label_default, int is_object_default, void* stream);
 
 /* ---- image loss of the trainers ------------------------------------ */
 
