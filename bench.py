@@ -165,6 +165,49 @@ def build_inputs(a, view, device):
     return kw, ups, host, cpu_kw, (wc, wd, wa)
 
 
+class HostLoop:
+    """Per-step host<->device traffic of the e2e region, two steps in flight, the way a training loop
+    feeds frames and logs its loss: step k's inputs are copied from pinned memory into buffer k % 2
+    (images on a side stream, camera on the main one), its loss is copied back asynchronously, and the
+    host reads the loss of step k - 1 once step k is enqueued. Every step still pays its own copies
+    and its own read; the host just does not idle the GPU between steps. Used by both arms."""
+
+    def __init__(self, host, device):
+        import torch
+        self.torch, self.host = torch, host
+        self.dv = [{k: torch.empty_like(v, device=device) for k, v in host.items()} for _ in range(2)]
+        self.loss_host = [torch.empty((), dtype=torch.float32).pin_memory() for _ in range(2)]
+        self.done = [torch.cuda.Event() for _ in range(2)]
+        self.copied = [torch.cuda.Event() for _ in range(2)]
+        self.copy_stream = torch.cuda.Stream(device=device)
+        self.k, self.last_loss = 0, None
+
+    def begin(self):
+        """Enqueue this step's host->device copies; returns (device buffers, event of the image copies).
+        Buffer k % 2 is free: step k - 2 finished before its loss was read at the end of step k - 1."""
+        b = self.k % 2
+        dv = self.dv[b]
+        with self.torch.cuda.stream(self.copy_stream):
+            for k in ("wc", "wd", "wa"):
+                dv[k].copy_(self.host[k], non_blocking=True)
+            self.copied[b].record()
+        for k in ("viewmatrix", "projmatrix", "campos"):
+            dv[k].copy_(self.host[k], non_blocking=True)
+        return dv, self.copied[b]
+
+    def end(self, loss):
+        b = self.k % 2
+        self.loss_host[b].copy_(loss.detach(), non_blocking=True)
+        self.done[b].record()
+        if self.k > 0:
+            self.done[1 - b].synchronize()                  # the previous step's result is on the host
+            self.last_loss = float(self.loss_host[1 - b])
+        self.k += 1
+
+    def bytes_in(self):
+        return sum(v.numel() * 4 for v in self.host.values())
+
+
 def timed_region(step, steps, warmup, dist_on, device):
     """W untimed steps, then exactly K steps between barrier+synchronize pairs; CUDA events on the
     launching (current) stream; returns seconds, max over ranks."""
@@ -396,22 +439,14 @@ def run_ours(a, rank, world, local_rank):
     if not a.no_e2e:
         leaves = {k: kw[k].clone().requires_grad_(True) for k in ("means3D", "opacities", "shs", "scales", "rotations",
                                                                   "cov3D_precomp") if k in kw}
-        dv = {k: torch.empty_like(v, device=device) for k, v in host.items()}
-        h2d = sum(v.numel() * 4 for v in host.values())
-        loss_host = torch.empty((), dtype=torch.float32).pin_memory()
-
-        copy_stream, copied = torch.cuda.Stream(device=device), torch.cuda.Event()
+        loop = HostLoop(host, device)
+        h2d = loop.bytes_in()
 
         def e2e_step():
             # the big host inputs (the upstream-gradient images, standing in for the ground-truth
-            # frame) are not needed before the loss: prefetch them on a side stream while the
+            # frame) are not needed before the loss: they are prefetched on a side stream while the
             # forward runs; the camera matrices are needed at once and go on the main stream
-            with torch.cuda.stream(copy_stream):
-                for k in ("wc", "wd", "wa"):
-                    dv[k].copy_(host[k], non_blocking=True)
-                copied.record()
-            for k in ("viewmatrix", "projmatrix", "campos"):
-                dv[k].copy_(host[k], non_blocking=True)
+            dv, copied = loop.begin()
             rs = GaussianRasterizationSettings(a.height, a.width, kw["tanfovx"], kw["tanfovy"], kw["bg"], 1.0,
                                                dv["viewmatrix"], dv["projmatrix"], a.sh_degree, dv["campos"], False, False)
             means2D = torch.zeros_like(leaves["means3D"], requires_grad=True)
@@ -428,14 +463,15 @@ def run_ours(a, rank, world, local_rank):
             elif dist_on:
                 for t in leaves.values():
                     dist.all_reduce(t.grad)
-            loss_host.copy_(loss.detach(), non_blocking=True)
-            torch.cuda.current_stream().synchronize()   # the step's result is on the host
+            loop.end(loss)                                  # loss k -> pinned memory; loss k - 1 read on the host
             for t in leaves.values():
                 t.grad = None
 
         sec2 = timed_region(e2e_step, a.steps, a.warmup, dist_on, device)
         e2e = {"value": world * a.steps / sec2, "unit": UNIT, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": 4,
-               "ms_per_step": sec2 / a.steps * 1e3}
+               "ms_per_step": sec2 / a.steps * 1e3, "last_loss": loop.last_loss,
+               "host_loop": "two steps in flight: every step copies its inputs from pinned memory and its loss back; "
+                            "the host reads loss k-1 after enqueueing step k (same loop in the reference arm)"}
 
     # ---- full training step (adds the fused Adam over all parameter groups), informational ----
     extra = {}
@@ -486,7 +522,7 @@ def run_ours(a, rank, world, local_rank):
     if world == 1 and not a.no_e2e:
         try:
             from egogaussian_b200.gaussian_renderer import render
-            del leaves, dv
+            del leaves, loop
             pc = _TrainerModel(a, device)
             params = pc.params()
             ms_ = [torch.zeros_like(p) for p in params]
@@ -607,20 +643,12 @@ def run_reference(a, rank, world, local_rank):
     rast = ref_dgr.make_autograd_rasterizer()
     leaves = {k: kw[k].clone().requires_grad_(True) for k in ("means3D", "opacities", "shs", "scales", "rotations",
                                                               "cov3D_precomp") if k in kw}
-    dv = {k: torch.empty_like(v, device=device) for k, v in host.items()}
-    h2d = sum(v.numel() * 4 for v in host.values())
-    loss_host = torch.empty((), dtype=torch.float32).pin_memory()
-
-    copy_stream, copied = torch.cuda.Stream(device=device), torch.cuda.Event()
+    loop = HostLoop(host, device)
+    h2d = loop.bytes_in()
 
     def e2e_step():
-        # same host-input schedule as our arm: images prefetched on a side stream, camera first
-        with torch.cuda.stream(copy_stream):
-            for k in ("wc", "wd", "wa"):
-                dv[k].copy_(host[k], non_blocking=True)
-            copied.record()
-        for k in ("viewmatrix", "projmatrix", "campos"):
-            dv[k].copy_(host[k], non_blocking=True)
+        # same host loop as our arm: images prefetched on a side stream, camera first, loss read one step late
+        dv, copied = loop.begin()
         rs = dict(bg=kw["bg"], scale_modifier=1.0, viewmatrix=dv["viewmatrix"], projmatrix=dv["projmatrix"],
                   tanfovx=kw["tanfovx"], tanfovy=kw["tanfovy"], image_height=a.height, image_width=a.width,
                   sh_degree=a.sh_degree, campos=dv["campos"])
@@ -631,8 +659,7 @@ def run_reference(a, rank, world, local_rank):
         torch.cuda.current_stream().wait_event(copied)
         loss = (color * dv["wc"]).sum() + (depth * dv["wd"]).sum() + (alpha * dv["wa"]).sum()
         loss.backward()
-        loss_host.copy_(loss.detach(), non_blocking=True)
-        torch.cuda.current_stream().synchronize()
+        loop.end(loss)
         for t in leaves.values():
             t.grad = None
 
@@ -642,7 +669,7 @@ def run_reference(a, rank, world, local_rank):
     # configured as scene/gaussian_model.py:189-198 (one group per tensor, lr per group, eps 1e-15)
     extra = {}
     try:
-        del leaves, dv
+        del leaves, loop
         pc = _TrainerModel(a, device)
         opt = torch.optim.Adam([{"params": [p], "lr": lr} for p, lr in zip(pc.params(), pc.lrs)], lr=0.0, eps=1e-15)
         rs = dict(bg=pc.bg, scale_modifier=1.0, viewmatrix=pc.world_view_transform, projmatrix=pc.full_proj_transform,
