@@ -2,9 +2,12 @@
 
 The path shards across camera views: every rank holds the full Gaussian parameter set, renders
 and back-propagates a different view, and the only exchange is the sum of parameter gradients.
-Gradients are written by egs_backward straight into views of ONE flat fp32 buffer, so the
-exchange is a single all-reduce (NCCL over NVLink/NVSwitch on GPUs, gloo in the CPU tests); the
-replicated fused Adam step then keeps all ranks bit-identical without a broadcast.
+Gradients are written by egs_backward straight into views of ONE flat fp32 buffer (FlatGrads). On
+the GPUs of one NVLink domain that buffer is peer-mapped and the exchange is one kernel per rank
+(PeerExchange: egs_exchange_sum, or egs_exchange_adam_step with the optimiser inside it); a single
+library all-reduce (allreduce_gradients: NCCL, gloo in the CPU tests) followed by the replicated fused
+Adam step remains for groups that cannot map each other's memory. Either way all ranks stay
+bit-identical without a parameter broadcast.
 """
 from __future__ import annotations
 

@@ -66,3 +66,32 @@ def test_flat_layout_and_partition():
     before = fg.flat.clone()
     parallel.allreduce_gradients(fg.flat)
     assert torch.equal(before, fg.flat)
+
+
+def test_adam_segments_cover_the_parameter_groups_of_the_flat_layout():
+    """FlatGrads.adam_segments: the reference's optimiser groups (scene/gaussian_model.py:189-197) as
+    4-float-aligned, ascending, disjoint ranges of the flat buffer; means2D stays outside."""
+    P, M = 257, 16
+    fg = parallel.FlatGrads(P, M, "cpu")
+    lrs = {"xyz": 1.6e-4, "f_dc": 2.5e-3, "f_rest": 1.25e-4, "opacity": 0.05, "scaling": 5e-3, "rotation": 1e-3}
+    segs = fg.adam_segments(lrs)
+    assert [s[2] for s in segs] == [1.6e-4, 2.5e-3, 0.05, 5e-3, 1e-3]
+    prev = 0
+    for (b, e, la, lb, per, sp), off in zip(segs, fg.offsets):
+        assert b == off and b >= prev and b % 4 == 0 and e % 4 == 0 and e > b
+        prev = e
+    sh = segs[1]
+    assert sh[3] == 1.25e-4 and sh[4] == 3 * M and sh[5] == 3          # first 3 floats of a row: features_dc
+    assert segs[-1][1] <= fg.offsets[-1]                                # means2D rides behind the last group
+    assert fg.flat.numel() - fg.offsets[-1] >= 3 * P
+
+
+def test_exchange_shards_tile_the_buffer():
+    from egogaussian_b200 import cabi
+    lib = cabi.load()
+    for n, world in [(0, 1), (4, 8), (1000, 3), (62_000_000, 8), (59_000_004, 5)]:
+        shard = lib.egs_exchange_shard_floats(n, world)
+        assert shard % 4 == 0 and shard * world >= n and (shard - 4) * world < n or n == 0
+    assert lib.egs_exchange_shard_floats(16, 0) == 0
+    g = cabi.peer_group(2, 1, [16, 32], [64, 128], grads_multicast=0)
+    assert g.world == 2 and g.rank == 1 and g.grads[1] == 32 and g.signals[0] == 64 and not g.grads_multicast
