@@ -126,15 +126,19 @@ def algorithmic_bytes(P, V, R, N, Tn, M, D, geom, passes):
         # MSD-bucket path (binning_buckets.cu): duplicate + one global partition pass (stage
         # "sort_histogram") + one CTA per bucket that reads 8 B and writes index + key (stage
         # "sort_passes"); tile ranges come out of the bucket kernel
-        binning = {"duplicate_keys": 20 * P + 8 * R, "sort_histogram": 16 * R, "sort_passes": 8 * R + 12 * R + 8 * Tn}
+        binning = {"duplicate_keys": 24 * P + 8 * R, "sort_histogram": 16 * R, "sort_passes": 8 * R + 12 * R + 8 * Tn}
     else:
         binning = {"duplicate_keys": 20 * P + (8 if packed else 12) * R, "sort_histogram": 8 * R,
                    "sort_passes": (R * 16 * (pk_passes - 1) + R * 20) if packed else R * 24 * passes,
                    "tile_ranges": 8 * R + 16 * Tn}
+    if packed and P >= 4096:
+        # front-to-back presort of the Gaussians: build the (depth key | index) words, three stable
+        # partition passes over them, the last one writing the bare indices
+        binning["depth_order"] = (8 + 8) * P + 2 * 16 * P + 12 * P
     return {
         **binning,
         "preprocess_fwd": 20 * P + V * (g + 4 + c + 4 + 8 + 16 + 12 + 3 + cov_store),
-        "scan": 8 * P,
+        "scan": (12 if packed and P >= 4096 else 8) * P,
         "blend_fwd": 44 * R + 24 * N + 8 * Tn,
         "bwd_zero": 48 * P,
         "blend_bwd": 44 * R + 28 * N + 8 * Tn + 40 * R,

@@ -77,7 +77,7 @@ void profile_end(cudaStream_t stream, void* token) {
 static const char* kStageNames[ST_COUNT] = {"preprocess_fwd", "scan", "duplicate_keys", "sort_histogram",
                                             "sort_passes", "tile_ranges", "blend_fwd", "bwd_zero",
                                             "blend_bwd", "preprocess_bwd", "adam", "se3",
-                                            "model_fwd", "model_bwd", "image_loss"};
+                                            "model_fwd", "model_bwd", "image_loss", "depth_order"};
 
 // Pinned read-back slot of the instance count, one per host thread, created on first use and kept
 // for the life of the process.
@@ -211,7 +211,19 @@ static int forward_impl(const char* who, const EgsForwardArgs* args, const EgsMo
   const ImagePtrs im(img_mem, a.width, a.height);
 
   if (int rc = launch_preprocess_forward(a, model, g, stream)) return rc;
-  if (int rc = launch_scan_tiles(g, a.P, stream, a.debug)) return rc;
+
+  const char* force = getenv("EGS_SORT");
+  const bool fits = packed_path_fits(a.P, a.width, a.height);
+  const bool forced = force && force[0] != 0;
+  // Front-to-back presort of the Gaussians (binning.cu): the instances are then emitted in depth
+  // order and the instance sorters only order the tile bits. Pays off from a few thousand
+  // Gaussians on; EGS_PRESORT=0 turns it off (A/B, cross-check), the forced paths never use it.
+  static const bool presort_on = !(getenv("EGS_PRESORT") && getenv("EGS_PRESORT")[0] == '0');
+  const bool presort = presort_on && fits && !forced && a.P >= 4096;
+  const uint32_t* order = presort ? g.sort_vals[0] : nullptr;
+  if (presort)
+    if (int rc = launch_depth_order(g, a.P, a.radii, stream, a.debug)) return rc;
+  if (int rc = launch_scan_tiles(g, a.P, order, stream, a.debug)) return rc;
 
   // The one device->host read per forward (the reference's is rasterizer_impl.cu:281-282): the
   // instance count lands in a pinned slot and an event marks its arrival.
@@ -223,10 +235,6 @@ static int forward_impl(const char* who, const EgsForwardArgs* args, const EgsMo
   const uint32_t* n_dev = g.point_offsets + (a.P - 1);
   EGS_CUDA_TRY(cudaMemcpyAsync(slot->host, n_dev, sizeof(uint32_t), cudaMemcpyDeviceToHost, stream));
   EGS_CUDA_TRY(cudaEventRecord(slot->arrived, stream));
-
-  const char* force = getenv("EGS_SORT");
-  const bool fits = packed_path_fits(a.P, a.width, a.height);
-  const bool forced = force && force[0] != 0;
 
   // Speculative run: with a caller-provided guess the binning workspace is sized from the guess and
   // binning + blend are enqueued before the count is known; the kernels read the count on the
@@ -244,7 +252,7 @@ static int forward_impl(const char* who, const EgsForwardArgs* args, const EgsMo
     }
     const BinningPtrs b(bin_mem, (size_t)capacity);
     const InstanceCount count{n_dev, (uint32_t)capacity};
-    if (int rc = launch_binning_buckets(g, b, im, a.radii, a.P, capacity, count, a.width, a.height, stream, false))
+    if (int rc = launch_binning_buckets(g, b, im, a.radii, order, a.P, capacity, count, a.width, a.height, stream, false))
       return rc;
     if (int rc = launch_blend_forward(a, g, b.vals[0], im, stream)) return rc;
     enqueued = true;
@@ -279,13 +287,13 @@ static int forward_impl(const char* who, const EgsForwardArgs* args, const EgsMo
   if (force && strcmp(force, "pairs8") == 0) {
     if (int rc = launch_binning(g, b, im, a.radii, a.P, R, a.width, a.height, stream, a.debug)) return rc;
   } else if (!fits || (force && strcmp(force, "pairs") == 0)) {
-    if (int rc = launch_binning_packed(g, b, im, a.radii, a.P, R, a.width, a.height, true, stream, a.debug)) return rc;
+    if (int rc = launch_binning_packed(g, b, im, a.radii, order, a.P, R, a.width, a.height, true, stream, a.debug)) return rc;
   } else if (bucket_path_ok(a.P, R, a.width, a.height) && !(force && strcmp(force, "packed") == 0)) {
     const InstanceCount count{n_dev, (uint32_t)R};
-    if (int rc = launch_binning_buckets(g, b, im, a.radii, a.P, R, count, a.width, a.height, stream, a.debug))
+    if (int rc = launch_binning_buckets(g, b, im, a.radii, order, a.P, R, count, a.width, a.height, stream, a.debug))
       return rc;
   } else {
-    if (int rc = launch_binning_packed(g, b, im, a.radii, a.P, R, a.width, a.height, false, stream, a.debug)) return rc;
+    if (int rc = launch_binning_packed(g, b, im, a.radii, order, a.P, R, a.width, a.height, false, stream, a.debug)) return rc;
   }
   return launch_blend_forward(a, g, b.vals[0], im, stream);
 }

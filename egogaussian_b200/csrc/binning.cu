@@ -26,9 +26,11 @@ constexpr unsigned long long SCAN_FLAG_AGG = 1ull << 62;
 constexpr unsigned long long SCAN_FLAG_PREFIX = 1ull << 63;
 constexpr unsigned long long SCAN_VALUE_MASK = (1ull << 62) - 1;
 
+// GATHER: element i of the scanned sequence is in[perm[i]]
+template <bool GATHER>
 __global__ void __launch_bounds__(SCAN_THREADS)
-scan_tiles_kernel(const uint32_t* __restrict__ in, uint32_t* __restrict__ out, int n,
-                  unsigned long long* __restrict__ status) {
+scan_tiles_kernel(const uint32_t* __restrict__ in, const uint32_t* __restrict__ perm, uint32_t* __restrict__ out,
+                  int n, unsigned long long* __restrict__ status) {
   __shared__ uint32_t s_tile;
   __shared__ uint32_t s_warp_sums[SCAN_THREADS / 32];
   __shared__ uint32_t s_block_prefix;
@@ -39,7 +41,12 @@ scan_tiles_kernel(const uint32_t* __restrict__ in, uint32_t* __restrict__ out, i
 
   const size_t base = (size_t)tile * SCAN_TILE + (size_t)threadIdx.x * SCAN_ITEMS;
   uint32_t v[SCAN_ITEMS];
-  if (base + SCAN_ITEMS <= (size_t)n) {
+  if (GATHER) {
+#pragma unroll
+    for (int k = 0; k < SCAN_ITEMS; ++k) v[k] = (base + k < (size_t)n) ? perm[base + k] : 0u;
+#pragma unroll
+    for (int k = 0; k < SCAN_ITEMS; ++k) v[k] = (base + k < (size_t)n) ? in[v[k]] : 0u;
+  } else if (base + SCAN_ITEMS <= (size_t)n) {
     const uint4* p = reinterpret_cast<const uint4*>(in + base);
 #pragma unroll
     for (int k = 0; k < SCAN_ITEMS / 4; ++k) {
@@ -114,12 +121,16 @@ scan_tiles_kernel(const uint32_t* __restrict__ in, uint32_t* __restrict__ out, i
   }
 }
 
-int launch_scan_tiles(const GeomPtrs& g, int P, cudaStream_t stream, bool debug) {
+int launch_scan_tiles(const GeomPtrs& g, int P, const uint32_t* order, cudaStream_t stream, bool debug) {
   const int blocks = (P + SCAN_TILE - 1) / SCAN_TILE;
   StageTimer timer(stream, ST_SCAN);
   EGS_CUDA_TRY(cudaMemsetAsync(g.scan_status, 0, (size_t)(blocks + 1) * 8, stream));
-  scan_tiles_kernel<<<blocks, SCAN_THREADS, 0, stream>>>(g.tiles_touched, g.point_offsets, P,
-                                                          g.scan_status);
+  if (order)
+    scan_tiles_kernel<true><<<blocks, SCAN_THREADS, 0, stream>>>(g.tiles_touched, order, g.point_offsets, P,
+                                                                 g.scan_status);
+  else
+    scan_tiles_kernel<false><<<blocks, SCAN_THREADS, 0, stream>>>(g.tiles_touched, nullptr, g.point_offsets, P,
+                                                                  g.scan_status);
   EGS_AFTER_LAUNCH(stream, debug);
   return EGS_OK;
 }
@@ -128,7 +139,7 @@ int launch_scan_tiles(const GeomPtrs& g, int P, cudaStream_t stream, bool debug)
 int launch_inclusive_scan(const uint32_t* in, uint32_t* out, int n, unsigned long long* status, cudaStream_t stream) {
   const int blocks = (n + SCAN_TILE - 1) / SCAN_TILE;
   EGS_CUDA_TRY(cudaMemsetAsync(status, 0, (size_t)(blocks + 1) * 8, stream));
-  scan_tiles_kernel<<<blocks, SCAN_THREADS, 0, stream>>>(in, out, n, status);
+  scan_tiles_kernel<false><<<blocks, SCAN_THREADS, 0, stream>>>(in, nullptr, out, n, status);
   EGS_AFTER_LAUNCH(stream, false);
   return EGS_OK;
 }

@@ -57,10 +57,16 @@ constexpr int BK_CAP = 12288;                      // words per bucket held in s
 // Compared with one thread looping over its own rectangle this removes the divergence between
 // small and large rectangles, makes every store coalesced, and lets the warp count a bucket once
 // per 32 slots (match.any) for the histogram, which therefore needs no pass of its own.
+// words of GeomPtrs::sort_aux (depth presort): three digit histograms, their exclusive scans, tickets,
+// meta (2: P for the partition kernel, 3: veto flag), then three status areas
+constexpr int DO_HIST = 0, DO_START = 3 * 1024, DO_TICKET = 6 * 1024, DO_META = DO_TICKET + 8,
+              DO_STATUS = DO_META + 8;
+static_assert(DO_STATUS == DEPTH_ORDER_AUX_WORDS, "aux layout");
 constexpr int DUP_THREADS = 256;
 __global__ void __launch_bounds__(DUP_THREADS)
 duplicate_words_kernel(int P, const float2* __restrict__ means2D, const float* __restrict__ depths,
                        const uint32_t* __restrict__ offsets, const int* __restrict__ radii,
+                       const uint32_t* __restrict__ order /* NULL: slot j of the scan is Gaussian j */,
                        uint64_t* __restrict__ words, int grid_x, int grid_y, int idx_bits,
                        InstanceCount count, int bucket_shift, uint32_t* __restrict__ bucket_hist) {
   uint32_t n;
@@ -72,10 +78,11 @@ duplicate_words_kernel(int P, const float2* __restrict__ means2D, const float* _
   const int groups = (P + 31) / 32;
   const int tile_shift = 32 + idx_bits;
   for (int group = blockIdx.x * (DUP_THREADS / 32) + warp; group < groups; group += gridDim.x * (DUP_THREADS / 32)) {
-    const int idx = group * 32 + (int)lane;
-    const bool valid = idx < P;
+    const int slot = group * 32 + (int)lane;
+    const bool valid = slot < P;
+    const int idx = !valid ? 0 : order ? (int)order[slot] : slot;
     const int r = valid ? radii[idx] : 0;
-    const uint32_t end = offsets[valid ? idx : P - 1];
+    const uint32_t end = offsets[valid ? slot : P - 1];
     uint32_t lox = 0, loy = 0, w = 1, cnt = 0, dbits = 0;
     if (r > 0) {
       uint2 lo, hi;
@@ -102,12 +109,13 @@ duplicate_words_kernel(int P, const float2* __restrict__ means2D, const float* _
       const uint32_t o_loy = __shfl_sync(0xffffffffu, loy, L);
       const uint32_t o_w = __shfl_sync(0xffffffffu, w, L);
       const uint32_t o_d = __shfl_sync(0xffffffffu, dbits, L);
+      const uint32_t o_idx = __shfl_sync(0xffffffffu, (uint32_t)idx, L);
       const bool live = o < run_end;
       const uint32_t local = o - o_start;
       const uint32_t dy = local / o_w;
       const uint32_t tile = (o_loy + dy) * (uint32_t)grid_x + o_lox + (local - dy * o_w);
       if (live)
-        words[o] = ((uint64_t)tile << tile_shift) | ((uint64_t)o_d << idx_bits) | (uint32_t)(group * 32 + L);
+        words[o] = ((uint64_t)tile << tile_shift) | ((uint64_t)o_d << idx_bits) | o_idx;
       const uint32_t bucket = tile >> bucket_shift;
       const uint32_t peers = __match_any_sync(0xffffffffu, live ? bucket : 0xffffffffu);
       if (live && (peers & ((1u << lane) - 1u)) == 0u) atomicAdd(&s_hist[bucket], (uint32_t)__popc(peers));
@@ -187,10 +195,15 @@ __device__ __forceinline__ void st_relaxed_u32(uint32_t* p, uint32_t v) {
 // the look-back) is shared by 16 words per thread instead of 4 (the first version ran 1024 threads
 // x 4 words and spent more instructions on that bookkeeping than on the words). A thread owns
 // four adjacent digits and walks their four look-back chains together.
+// The digit is (word >> shift) & mask: the top bits of the word for the bucket partition (mask all
+// ones), any 10-bit field for the stable LSD passes of the depth presort. EMIT_IDX: the pass writes
+// only the low index bits of every word, as 32-bit values (last pass of the presort).
+template <bool EMIT_IDX>
 __global__ void __launch_bounds__(MSD_THREADS, 3)
 msd_partition_kernel(const uint64_t* __restrict__ in, uint64_t* __restrict__ out, InstanceCount count,
-                     int shift, const uint32_t* __restrict__ bucket_start, uint32_t* __restrict__ ticket,
-                     uint32_t* __restrict__ status_raw) {
+                     int shift, uint32_t mask, const uint32_t* __restrict__ bucket_start,
+                     uint32_t* __restrict__ ticket, uint32_t* __restrict__ status_raw,
+                     uint32_t* __restrict__ out_idx, uint32_t idx_mask) {
   extern __shared__ __align__(16) unsigned char smem_raw[];
   MsdSmem& S = *reinterpret_cast<MsdSmem*>(smem_raw);
   uint32_t n;
@@ -223,7 +236,7 @@ msd_partition_kernel(const uint64_t* __restrict__ in, uint64_t* __restrict__ out
   for (int i = 0; i < MSD_ITEMS; ++i) {
     const size_t g = warp_base + (size_t)i * 32 + lane;
     const bool ok = g < (size_t)n;
-    const uint32_t d = (uint32_t)(word[i] >> shift);
+    const uint32_t d = (uint32_t)(word[i] >> shift) & mask;
     const uint32_t peers = __match_any_sync(0xffffffffu, ok ? d : (0x10000u + lane));
     const uint32_t before = ok ? S.warp_hist[warp][d] : 0u;
     __syncwarp();
@@ -307,7 +320,7 @@ msd_partition_kernel(const uint64_t* __restrict__ in, uint64_t* __restrict__ out
   for (int i = 0; i < MSD_ITEMS; ++i) {
     const size_t g = warp_base + (size_t)i * 32 + lane;
     if (g < (size_t)n) {
-      const uint32_t d = (uint32_t)(word[i] >> shift);
+      const uint32_t d = (uint32_t)(word[i] >> shift) & mask;
       S.exch[S.digit_local[d] + S.warp_hist[warp][d] + rank[i]] = word[i];
     }
   }
@@ -318,7 +331,11 @@ msd_partition_kernel(const uint64_t* __restrict__ in, uint64_t* __restrict__ out
     const uint32_t k = m * MSD_THREADS + tid;
     if (k < valid) {
       const uint64_t w = S.exch[k];
-      out[S.digit_global[(uint32_t)(w >> shift)] + k] = w;
+      const uint32_t dst = S.digit_global[(uint32_t)(w >> shift) & mask] + k;
+      if (EMIT_IDX)
+        out_idx[dst] = (uint32_t)w & idx_mask;
+      else
+        out[dst] = w;
     }
   }
 }
@@ -485,7 +502,9 @@ bucket_sort_kernel(uint64_t* __restrict__ words /* partitioned; receives the sor
                    uint64_t* __restrict__ scratch /* other ping-pong buffer (overflow buckets) */,
                    const uint32_t* __restrict__ bucket_start, const uint32_t* __restrict__ order,
                    uint32_t* __restrict__ point_list, uint2* __restrict__ ranges, int n_tiles, int idx_bits, int bucket_shift,
-                   int rem_bits /* key bits below the bucket digit */) {
+                   int rem_bits /* key bits below the bucket digit */,
+                   int first_bit /* key bits below this one are in order already (32: presorted by depth) */,
+                   const uint32_t* __restrict__ presort_veto /* NULL, or a flag: nonzero = sort all the bits after all */) {
   extern __shared__ __align__(16) unsigned char smem_raw[];
   BucketSmem& S = *reinterpret_cast<BucketSmem*>(smem_raw);
   const uint32_t bucket = order[blockIdx.x];   // largest bucket first
@@ -498,6 +517,7 @@ bucket_sort_kernel(uint64_t* __restrict__ words /* partitioned; receives the sor
   const uint32_t tile_hi = min((uint32_t)n_tiles, (bucket + 1u) << bucket_shift);
   for (uint32_t t = tile_lo + tid; t < tile_hi; t += BK_THREADS) ranges[t] = make_uint2(0u, 0u);
   if (n == 0) return;
+  if (presort_veto && *presort_veto) first_bit = 0;
 
   const bool in_smem = n <= (uint32_t)BK_CAP;
   uint64_t* A;
@@ -512,10 +532,10 @@ bucket_sort_kernel(uint64_t* __restrict__ words /* partitioned; receives the sor
   }
   __syncthreads();
 
-  const int passes = (rem_bits + BK_BITS - 1) / BK_BITS;
+  const int passes = (rem_bits - first_bit + BK_BITS - 1) / BK_BITS;
   for (int p = 0; p < passes; ++p) {
-    const int shift = idx_bits + p * BK_BITS;
-    const int width = min(BK_BITS, rem_bits - p * BK_BITS);
+    const int shift = idx_bits + first_bit + p * BK_BITS;
+    const int width = min(BK_BITS, rem_bits - first_bit - p * BK_BITS);
     if (in_smem)
       bucket_pass_smem<HWMATCH>(S, p & 1, n, shift, (1u << width) - 1u);
     else
@@ -550,6 +570,104 @@ bucket_sort_kernel(uint64_t* __restrict__ words /* partitioned; receives the sor
 // ---------------------------------------------------------------------------------------------
 // host side
 // ---------------------------------------------------------------------------------------------
+// ---------------------------------------------------------------------------------------------
+// front-to-back order of the Gaussians
+// ---------------------------------------------------------------------------------------------
+// The per-tile lists are ordered by (tile, depth bits, index). Sorting the ~1M Gaussians by depth once
+// and emitting the ~10M instances in that order leaves the instance sorter only the tile bits to do
+// (its passes are stable): one pass per bucket instead of four. A visible Gaussian lies beyond the
+// near plane (depth > 0.2, preprocess), so depth bits - bits(0.2f) fits 30 bits for every depth below
+// 6.8e37: three stable 10-bit passes of the partition kernel above, the last one writing the bare
+// indices. Culled Gaussians get the largest key and end up behind the visible ones (they emit nothing).
+// A frame with a depth beyond that raises the veto flag instead, and the bucket sorter then orders all
+// the bits itself as if there had been no presort: the order is then merely some permutation, which is
+// all the scan and the duplication need.
+constexpr uint32_t DEPTH_KEY_BASE = 0x3E4CCCCDu;   // bits of 0.2f
+constexpr uint32_t DEPTH_KEY_MAX = (1u << 30) - 1u;
+
+__global__ void __launch_bounds__(256)
+depth_words_kernel(int P, const float* __restrict__ depths, const int* __restrict__ radii, int idx_bits,
+                   uint64_t* __restrict__ words, uint32_t* __restrict__ hist /* [3][MSD_BINS] */,
+                   uint32_t* __restrict__ meta) {
+  __shared__ uint32_t s_hist[3 * MSD_BINS];
+  for (int i = threadIdx.x; i < 3 * MSD_BINS; i += 256) s_hist[i] = 0;
+  __syncthreads();
+  bool veto = false;
+  for (int i = blockIdx.x * 256 + threadIdx.x; i < P; i += gridDim.x * 256) {
+    uint32_t key = DEPTH_KEY_MAX;
+    if (radii[i] > 0) {
+      const uint32_t b = __float_as_uint(depths[i]);
+      key = b - DEPTH_KEY_BASE;
+      if (b < DEPTH_KEY_BASE || key >= DEPTH_KEY_MAX) {
+        veto = true;
+        key &= DEPTH_KEY_MAX;
+      }
+    }
+    words[i] = ((uint64_t)key << idx_bits) | (uint32_t)i;
+    atomicAdd(&s_hist[key & (MSD_BINS - 1)], 1u);
+    atomicAdd(&s_hist[MSD_BINS + ((key >> 10) & (MSD_BINS - 1))], 1u);
+    atomicAdd(&s_hist[2 * MSD_BINS + (key >> 20)], 1u);
+  }
+  if (veto) meta[3] = 1u;
+  if (blockIdx.x == 0 && threadIdx.x == 0) meta[2] = (uint32_t)P;
+  __syncthreads();
+  for (int i = threadIdx.x; i < 3 * MSD_BINS; i += 256) {
+    const uint32_t c = s_hist[i];
+    if (c) atomicAdd(&hist[i], c);
+  }
+}
+
+// exclusive scan of the three digit histograms, one block each
+__global__ void __launch_bounds__(MSD_BINS)
+depth_scan_kernel(const uint32_t* __restrict__ hist, uint32_t* __restrict__ start) {
+  __shared__ uint32_t s_w[MSD_BINS / 32];
+  const uint32_t v = hist[blockIdx.x * MSD_BINS + threadIdx.x];
+  const unsigned lane = lane_id(), warp = threadIdx.x >> 5;
+  uint32_t incl = v;
+#pragma unroll
+  for (int d = 1; d < 32; d <<= 1) {
+    const uint32_t t = __shfl_up_sync(0xffffffffu, incl, d);
+    if (lane >= d) incl += t;
+  }
+  if (lane == 31) s_w[warp] = incl;
+  __syncthreads();
+  uint32_t woff = 0;
+  for (unsigned w = 0; w < warp; ++w) woff += s_w[w];
+  start[blockIdx.x * MSD_BINS + threadIdx.x] = woff + incl - v;
+}
+
+int launch_depth_order(const GeomPtrs& g, int P, const int* radii, cudaStream_t stream, bool debug) {
+  StageTimer timer(stream, ST_DEPTH_ORDER);
+  uint32_t* aux = g.sort_aux;
+  const int ib = tile_id_bits((uint32_t)(P > 1 ? P - 1 : 1));
+  EGS_CUDA_TRY(cudaMemsetAsync(aux, 0, g.sort_aux_bytes, stream));
+  const int blocks = P < 148 * 4 * 256 ? (P + 255) / 256 : 148 * 4;
+  depth_words_kernel<<<blocks, 256, 0, stream>>>(P, g.depths, radii, ib, g.sort_keys[0], aux + DO_HIST, aux + DO_META);
+  EGS_AFTER_LAUNCH(stream, debug);
+  depth_scan_kernel<<<3, MSD_BINS, 0, stream>>>(aux + DO_HIST, aux + DO_START);
+  EGS_AFTER_LAUNCH(stream, debug);
+  EGS_CUDA_TRY(cudaFuncSetAttribute(msd_partition_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                    (int)sizeof(MsdSmem)));
+  EGS_CUDA_TRY(cudaFuncSetAttribute(msd_partition_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                    (int)sizeof(MsdSmem)));
+  const InstanceCount count{aux + DO_META + 2, (uint32_t)P};
+  const int grid = (int)g.sort_blocks;
+  const size_t status_stride = g.sort_blocks * MSD_BINS;
+  msd_partition_kernel<false><<<grid, MSD_THREADS, sizeof(MsdSmem), stream>>>(
+      g.sort_keys[0], g.sort_keys[1], count, ib, MSD_BINS - 1, aux + DO_START, aux + DO_TICKET, aux + DO_STATUS,
+      nullptr, 0u);
+  EGS_AFTER_LAUNCH(stream, debug);
+  msd_partition_kernel<false><<<grid, MSD_THREADS, sizeof(MsdSmem), stream>>>(
+      g.sort_keys[1], g.sort_keys[0], count, ib + 10, MSD_BINS - 1, aux + DO_START + MSD_BINS, aux + DO_TICKET + 1,
+      aux + DO_STATUS + status_stride, nullptr, 0u);
+  EGS_AFTER_LAUNCH(stream, debug);
+  msd_partition_kernel<true><<<grid, MSD_THREADS, sizeof(MsdSmem), stream>>>(
+      g.sort_keys[0], nullptr, count, ib + 20, MSD_BINS - 1, aux + DO_START + 2 * MSD_BINS, aux + DO_TICKET + 2,
+      aux + DO_STATUS + 2 * status_stride, g.sort_vals[0], (uint32_t)((1ull << ib) - 1ull));
+  EGS_AFTER_LAUNCH(stream, debug);
+  return EGS_OK;
+}
+
 bool bucket_path_ok(int P, int R, int W, int H) {
   if (!packed_path_fits(P, W, H)) return false;
   // most buckets must fit in shared memory; otherwise the pure LSD path is the better choice
@@ -560,8 +678,8 @@ bool bucket_path_ok(int P, int R, int W, int H) {
 // device through `count` (it may still be in flight when this is enqueued). capacity == 0 means
 // the count is known to be 0.
 int launch_binning_buckets(const GeomPtrs& g, const BinningPtrs& b, const ImagePtrs& im, const int* radii,
-                           int P, int capacity, InstanceCount count, int W, int H, cudaStream_t stream,
-                           bool debug) {
+                           const uint32_t* gauss_order, int P, int capacity, InstanceCount count, int W, int H,
+                           cudaStream_t stream, bool debug) {
   const int gx = tiles_x(W), gy = tiles_y(H);
   const int n_tiles = gx * gy;
   if (capacity == 0) {
@@ -586,34 +704,39 @@ int launch_binning_buckets(const GeomPtrs& g, const BinningPtrs& b, const ImageP
     // 4 CTAs per SM, each warp strides over groups of 32 Gaussians; the bucket histogram comes out
     // of the same kernel
     duplicate_words_kernel<<<148 * 4, DUP_THREADS, 0, stream>>>(P, g.means2D, g.depths, g.point_offsets, radii,
-                                                             b.keys[1], gx, gy, ib, count, bucket_shift, hist);
+                                                             gauss_order, b.keys[1], gx, gy, ib, count, bucket_shift,
+                                                             hist);
     EGS_AFTER_LAUNCH(stream, debug);
     bucket_scan_kernel<<<1, MSD_BINS, 0, stream>>>(hist, start, order);
     EGS_AFTER_LAUNCH(stream, debug);
   }
   {
     StageTimer timer(stream, ST_SORT_HIST);   // reported as the global partition pass
-    EGS_CUDA_TRY(cudaFuncSetAttribute(msd_partition_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+    EGS_CUDA_TRY(cudaFuncSetAttribute(msd_partition_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                       (int)sizeof(MsdSmem)));
-    msd_partition_kernel<<<(int)b.sort_blocks, MSD_THREADS, sizeof(MsdSmem), stream>>>(
-        b.keys[1], b.keys[0], count, ib + 32 + bucket_shift, start, b.ticket, b.status);
+    msd_partition_kernel<false><<<(int)b.sort_blocks, MSD_THREADS, sizeof(MsdSmem), stream>>>(
+        b.keys[1], b.keys[0], count, ib + 32 + bucket_shift, 0xffffffffu, start, b.ticket, b.status, nullptr, 0u);
     EGS_AFTER_LAUNCH(stream, debug);
   }
   {
     StageTimer timer(stream, ST_SORT_PASSES);   // reported as the per-bucket sort
     // The sorter is issue-bound: the match.any instruction measured 12 % faster than one ballot per
     // digit bit (0.269 vs 0.305 ms at C3). EGS_MATCH=ballot keeps the ballot form for A/B runs.
+    // emitted front to back, the stable partition left every bucket ordered by depth: only the tile
+    // bits below the bucket digit remain (one pass instead of four)
+    const int first_bit = gauss_order ? 32 : 0;
+    const uint32_t* presort_veto = gauss_order ? g.sort_aux + DO_META + 3 : nullptr;
     const char* m = getenv("EGS_MATCH");
     if (!(m && strcmp(m, "ballot") == 0)) {
       EGS_CUDA_TRY(cudaFuncSetAttribute(bucket_sort_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                         (int)sizeof(BucketSmem)));
       bucket_sort_kernel<true><<<MSD_BINS, BK_THREADS, sizeof(BucketSmem), stream>>>(
-          b.keys[0], b.keys[1], start, order, b.vals[0], im.ranges, n_tiles, ib, bucket_shift, rem_bits);
+          b.keys[0], b.keys[1], start, order, b.vals[0], im.ranges, n_tiles, ib, bucket_shift, rem_bits, first_bit, presort_veto);
     } else {
       EGS_CUDA_TRY(cudaFuncSetAttribute(bucket_sort_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                         (int)sizeof(BucketSmem)));
       bucket_sort_kernel<false><<<MSD_BINS, BK_THREADS, sizeof(BucketSmem), stream>>>(
-          b.keys[0], b.keys[1], start, order, b.vals[0], im.ranges, n_tiles, ib, bucket_shift, rem_bits);
+          b.keys[0], b.keys[1], start, order, b.vals[0], im.ranges, n_tiles, ib, bucket_shift, rem_bits, first_bit, presort_veto);
     }
     EGS_AFTER_LAUNCH(stream, debug);
   }

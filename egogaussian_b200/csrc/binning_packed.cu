@@ -36,12 +36,14 @@ static_assert(PK_MAX_PASSES * PK_RADIX <= SORT_STATUS_WORDS, "status array too s
 __global__ void __launch_bounds__(256)
 duplicate_packed_kernel(int P, const float2* __restrict__ means2D, const float* __restrict__ depths,
                         const uint32_t* __restrict__ offsets, const int* __restrict__ radii,
+                        const uint32_t* __restrict__ order /* NULL: slot j of the scan is Gaussian j */,
                         uint64_t* __restrict__ words, int grid_x, int grid_y, int idx_bits) {
-  const int idx = blockIdx.x * blockDim.x + threadIdx.x;
-  if (idx >= P) return;
+  const int slot = blockIdx.x * blockDim.x + threadIdx.x;
+  if (slot >= P) return;
+  const int idx = order ? (int)order[slot] : slot;
   const int r = radii[idx];
   if (r <= 0) return;
-  uint32_t off = (idx == 0) ? 0u : offsets[idx - 1];
+  uint32_t off = (slot == 0) ? 0u : offsets[slot - 1];
   uint2 lo, hi;
   tile_rect(means2D[idx], r, grid_x, grid_y, lo, hi);
   const uint64_t low = ((uint64_t)__float_as_uint(depths[idx]) << idx_bits) | (uint32_t)idx;
@@ -271,12 +273,14 @@ bool packed_path_fits(int P, int W, int H) {
 __global__ void __launch_bounds__(256)
 duplicate_pairs_kernel(int P, const float2* __restrict__ means2D, const float* __restrict__ depths,
                        const uint32_t* __restrict__ offsets, const int* __restrict__ radii,
-                       uint64_t* __restrict__ keys, uint32_t* __restrict__ vals, int grid_x, int grid_y) {
-  const int idx = blockIdx.x * blockDim.x + threadIdx.x;
-  if (idx >= P) return;
+                       const uint32_t* __restrict__ order, uint64_t* __restrict__ keys, uint32_t* __restrict__ vals,
+                       int grid_x, int grid_y) {
+  const int slot = blockIdx.x * blockDim.x + threadIdx.x;
+  if (slot >= P) return;
+  const int idx = order ? (int)order[slot] : slot;
   const int r = radii[idx];
   if (r <= 0) return;
-  uint32_t off = (idx == 0) ? 0u : offsets[idx - 1];
+  uint32_t off = (slot == 0) ? 0u : offsets[slot - 1];
   uint2 lo, hi;
   tile_rect(means2D[idx], r, grid_x, grid_y, lo, hi);
   const uint64_t depth_bits = (uint64_t)__float_as_uint(depths[idx]);
@@ -319,7 +323,8 @@ static int run_onesweep_passes(const BinningPtrs& b, int R, int passes, int begi
 
 // pairs = false: packed words (index inside the word); pairs = true: keys + a value array
 int launch_binning_packed(const GeomPtrs& g, const BinningPtrs& b, const ImagePtrs& im, const int* radii,
-                          int P, int R, int W, int H, bool pairs, cudaStream_t stream, bool debug) {
+                          const uint32_t* order, int P, int R, int W, int H, bool pairs, cudaStream_t stream,
+                          bool debug) {
   const int gx = tiles_x(W), gy = tiles_y(H);
   EGS_CUDA_TRY(cudaMemsetAsync(im.ranges, 0, (size_t)gx * gy * sizeof(uint2), stream));
   if (R == 0) return EGS_OK;
@@ -333,10 +338,10 @@ int launch_binning_packed(const GeomPtrs& g, const BinningPtrs& b, const ImagePt
     StageTimer timer(stream, ST_DUPLICATE);
     if (pairs)
       duplicate_pairs_kernel<<<(P + 255) / 256, 256, 0, stream>>>(P, g.means2D, g.depths, g.point_offsets, radii,
-                                                                  b.keys[src], b.vals[src], gx, gy);
+                                                                  order, b.keys[src], b.vals[src], gx, gy);
     else
       duplicate_packed_kernel<<<(P + 255) / 256, 256, 0, stream>>>(P, g.means2D, g.depths, g.point_offsets,
-                                                                   radii, b.keys[src], gx, gy, ib);
+                                                                   radii, order, b.keys[src], gx, gy, ib);
     EGS_AFTER_LAUNCH(stream, debug);
   }
   {

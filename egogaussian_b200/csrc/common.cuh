@@ -47,7 +47,8 @@ inline size_t align_up(size_t x, size_t a = 256) { return (x + a - 1) / a * a; }
 // Stage ids of the built-in event timing (egs_profile_* in the header).
 enum Stage {
   ST_PREPROCESS = 0, ST_SCAN, ST_DUPLICATE, ST_SORT_HIST, ST_SORT_PASSES, ST_RANGES, ST_BLEND_FWD,
-  ST_BWD_ZERO, ST_BLEND_BWD, ST_PREPROCESS_BWD, ST_ADAM, ST_SE3, ST_MODEL_FWD, ST_MODEL_BWD, ST_LOSS, ST_COUNT
+  ST_BWD_ZERO, ST_BLEND_BWD, ST_PREPROCESS_BWD, ST_ADAM, ST_SE3, ST_MODEL_FWD, ST_MODEL_BWD, ST_LOSS,
+  ST_DEPTH_ORDER, ST_COUNT
 };
 static_assert(ST_COUNT <= EGS_PROFILE_STAGES, "grow EGS_PROFILE_STAGES");
 bool profiling_enabled();
@@ -69,10 +70,17 @@ struct StageTimer {
 // workspace carving (pure functions of the sizes, so backward can re-derive the pointers)
 // ---------------------------------------------------------------------------------------------
 constexpr int SCAN_TILE = 4096;   // elements per block of the tiles_touched scan
+// presort aux, in u32 words: hist[3][1024] start[3][1024] ticket[8] meta[8], then status[3][blocks][1024]
+constexpr int DEPTH_ORDER_AUX_WORDS = 6 * 1024 + 8 + 8;
+constexpr int SORT_RADIX_BITS = 8;
+constexpr int SORT_RADIX = 1 << SORT_RADIX_BITS;
+constexpr int SORT_THREADS = 256;
+constexpr int SORT_ITEMS = 16;
+constexpr int SORT_TILE = SORT_THREADS * SORT_ITEMS;
 
 struct GeomLayout {
   size_t depths, means2D, conic_opacity, rgb_depth, clamped, tiles_touched, point_offsets,
-      scan_status, total;
+      scan_status, sort_keys[2], sort_vals[2], sort_aux, sort_blocks, sort_aux_bytes, total;
   explicit GeomLayout(size_t P) {
     size_t o = 0;
     auto take = [&](size_t bytes) { size_t r = o; o = align_up(o + bytes); return r; };
@@ -84,6 +92,16 @@ struct GeomLayout {
     tiles_touched = take(P * 4);
     point_offsets = take(P * 4);
     scan_status = take(((P + SCAN_TILE - 1) / SCAN_TILE + 1) * 8 + 256);
+    // front-to-back order of the Gaussians (binning presort, binning_buckets.cu): packed words
+    // (30-bit depth key | index) in two buffers, the resulting order, and aux = digit histograms,
+    // their scans, tickets, flags and the status words of three partition passes
+    sort_keys[0] = take(P * 8);
+    sort_keys[1] = take(P * 8);
+    sort_vals[0] = take(P * 4);
+    sort_vals[1] = 0;
+    sort_blocks = (P + SORT_TILE - 1) / SORT_TILE;
+    sort_aux_bytes = (DEPTH_ORDER_AUX_WORDS + 3 * sort_blocks * 1024) * 4;
+    sort_aux = take(sort_aux_bytes);
     total = o + 256;
   }
 };
@@ -97,6 +115,10 @@ struct GeomPtrs {
   uint32_t* tiles_touched;
   uint32_t* point_offsets;
   unsigned long long* scan_status;  // [0] ticket, [1..] per-block status words
+  uint64_t* sort_keys[2];           // depth-order presort; the order ends in sort_vals[0]
+  uint32_t* sort_vals[2];
+  uint32_t* sort_aux;
+  size_t sort_blocks, sort_aux_bytes;
   GeomPtrs(void* base, size_t P) {
     GeomLayout L(P);
     char* b = static_cast<char*>(base);
@@ -108,6 +130,12 @@ struct GeomPtrs {
     tiles_touched = reinterpret_cast<uint32_t*>(b + L.tiles_touched);
     point_offsets = reinterpret_cast<uint32_t*>(b + L.point_offsets);
     scan_status = reinterpret_cast<unsigned long long*>(b + L.scan_status);
+    for (int k = 0; k < 2; ++k) sort_keys[k] = reinterpret_cast<uint64_t*>(b + L.sort_keys[k]);
+    sort_vals[0] = reinterpret_cast<uint32_t*>(b + L.sort_vals[0]);
+    sort_vals[1] = nullptr;
+    sort_aux = reinterpret_cast<uint32_t*>(b + L.sort_aux);
+    sort_blocks = L.sort_blocks;
+    sort_aux_bytes = L.sort_aux_bytes;
   }
 };
 
@@ -123,11 +151,6 @@ inline int tile_id_bits(uint32_t n_tiles) {
   return b;
 }
 
-constexpr int SORT_RADIX_BITS = 8;
-constexpr int SORT_RADIX = 1 << SORT_RADIX_BITS;
-constexpr int SORT_THREADS = 256;
-constexpr int SORT_ITEMS = 16;
-constexpr int SORT_TILE = SORT_THREADS * SORT_ITEMS;
 constexpr int SORT_MAX_PASSES = 8;
 // status / histogram words per sort block: 8 passes x 256 digits (pair sort) or 6 x 512 (packed sort)
 constexpr int SORT_STATUS_WORDS = 3072;
@@ -225,12 +248,18 @@ struct BackwardScratch {
 // covariance and SH rows are derived from the optimiser's raw tensors inside the kernel.
 int launch_preprocess_forward(const EgsForwardArgs& a, const EgsModelArgs* model, const GeomPtrs& g,
                               cudaStream_t stream);
-int launch_scan_tiles(const GeomPtrs& g, int P, cudaStream_t stream, bool debug);
+// order != NULL: the scan runs over tiles_touched[order[i]] (front-to-back order of the Gaussians)
+int launch_scan_tiles(const GeomPtrs& g, int P, const uint32_t* order, cudaStream_t stream, bool debug);
+// g.sort_vals[0] <- Gaussian indices by ascending depth bits, ties by index; culled ones last
+int launch_depth_order(const GeomPtrs& g, int P, const int* radii, cudaStream_t stream, bool debug);
 int launch_inclusive_scan(const uint32_t* in, uint32_t* out, int n, unsigned long long* status, cudaStream_t stream);
 // packed-word fast path (binning_packed.cu) and the shared range kernel
 bool packed_path_fits(int P, int W, int H);
+// `order` (all binning launchers): NULL, or the front-to-back order the scan ran over; instances are
+// then emitted in that order, which is what the sorters' stability turns into less work
 int launch_binning_packed(const GeomPtrs& g, const BinningPtrs& b, const ImagePtrs& im, const int* radii,
-                          int P, int R, int W, int H, bool pairs, cudaStream_t stream, bool debug);
+                          const uint32_t* order, int P, int R, int W, int H, bool pairs, cudaStream_t stream,
+                          bool debug);
 // MSD-bucket path (binning_buckets.cu): one global partition pass + one CTA per bucket
 bool bucket_path_ok(int P, int R, int W, int H);
 // The number of instances as the device sees it: `n_dev` points at the last element of the
@@ -247,8 +276,8 @@ struct InstanceCount {
 #endif
 };
 int launch_binning_buckets(const GeomPtrs& g, const BinningPtrs& b, const ImagePtrs& im, const int* radii,
-                           int P, int capacity, InstanceCount count, int W, int H, cudaStream_t stream,
-                           bool debug);
+                           const uint32_t* order, int P, int capacity, InstanceCount count, int W, int H,
+                           cudaStream_t stream, bool debug);
 int launch_tile_ranges(int R, const uint64_t* sorted_keys, const ImagePtrs& im, cudaStream_t stream,
                        bool debug);
 int launch_binning(const GeomPtrs& g, const BinningPtrs& b, const ImagePtrs& im, const int* radii,
