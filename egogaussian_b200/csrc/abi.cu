@@ -219,7 +219,9 @@ static int forward_impl(const char* who, const EgsForwardArgs* args, const EgsMo
   // order and the instance sorters only order the tile bits. Pays off from a few thousand
   // Gaussians on; EGS_PRESORT=0 turns it off (A/B, cross-check), the forced paths never use it.
   static const bool presort_on = !(getenv("EGS_PRESORT") && getenv("EGS_PRESORT")[0] == '0');
-  const bool presort = presort_on && fits && !forced && a.P >= 4096;
+  // (EGS_SORT=packed_presorted: the five-pass packed path fed in presorted order, which is what a
+  // frame with too many instances for the bucket sorter gets; a test hook like the other EGS_SORT values)
+  const bool presort = presort_on && fits && a.P >= 4096 && (!forced || strcmp(force, "packed_presorted") == 0);
   const uint32_t* order = presort ? g.sort_vals[0] : nullptr;
   if (presort)
     if (int rc = launch_depth_order(g, a.P, a.radii, stream, a.debug)) return rc;
@@ -288,7 +290,7 @@ static int forward_impl(const char* who, const EgsForwardArgs* args, const EgsMo
     if (int rc = launch_binning(g, b, im, a.radii, a.P, R, a.width, a.height, stream, a.debug)) return rc;
   } else if (!fits || (force && strcmp(force, "pairs") == 0)) {
     if (int rc = launch_binning_packed(g, b, im, a.radii, order, a.P, R, a.width, a.height, true, stream, a.debug)) return rc;
-  } else if (bucket_path_ok(a.P, R, a.width, a.height) && !(force && strcmp(force, "packed") == 0)) {
+  } else if (bucket_path_ok(a.P, R, a.width, a.height) && !(force && strncmp(force, "packed", 6) == 0)) {
     const InstanceCount count{n_dev, (uint32_t)R};
     if (int rc = launch_binning_buckets(g, b, im, a.radii, order, a.P, R, count, a.width, a.height, stream, a.debug))
       return rc;

@@ -588,7 +588,7 @@ constexpr uint32_t DEPTH_KEY_MAX = (1u << 30) - 1u;
 __global__ void __launch_bounds__(256)
 depth_words_kernel(int P, const float* __restrict__ depths, const int* __restrict__ radii, int idx_bits,
                    uint64_t* __restrict__ words, uint32_t* __restrict__ hist /* [3][MSD_BINS] */,
-                   uint32_t* __restrict__ meta) {
+                   uint32_t* __restrict__ meta, bool scramble /* test: keys unrelated to depth + veto */) {
   __shared__ uint32_t s_hist[3 * MSD_BINS];
   for (int i = threadIdx.x; i < 3 * MSD_BINS; i += 256) s_hist[i] = 0;
   __syncthreads();
@@ -598,7 +598,8 @@ depth_words_kernel(int P, const float* __restrict__ depths, const int* __restric
     if (radii[i] > 0) {
       const uint32_t b = __float_as_uint(depths[i]);
       key = b - DEPTH_KEY_BASE;
-      if (b < DEPTH_KEY_BASE || key >= DEPTH_KEY_MAX) {
+      if (scramble) key *= 2654435761u;   // a bijection of the 30-bit keys: equal depths still tie, as in a real veto
+      if (scramble || b < DEPTH_KEY_BASE || key >= DEPTH_KEY_MAX) {
         veto = true;
         key &= DEPTH_KEY_MAX;
       }
@@ -642,7 +643,11 @@ int launch_depth_order(const GeomPtrs& g, int P, const int* radii, cudaStream_t 
   const int ib = tile_id_bits((uint32_t)(P > 1 ? P - 1 : 1));
   EGS_CUDA_TRY(cudaMemsetAsync(aux, 0, g.sort_aux_bytes, stream));
   const int blocks = P < 148 * 4 * 256 ? (P + 255) / 256 : 148 * 4;
-  depth_words_kernel<<<blocks, 256, 0, stream>>>(P, g.depths, radii, ib, g.sort_keys[0], aux + DO_HIST, aux + DO_META);
+  // EGS_PRESORT_DEBUG=scramble exercises the veto: an order unrelated to depth, full sort downstream
+  const char* dbg = getenv("EGS_PRESORT_DEBUG");
+  const bool scramble = dbg && strcmp(dbg, "scramble") == 0;
+  depth_words_kernel<<<blocks, 256, 0, stream>>>(P, g.depths, radii, ib, g.sort_keys[0], aux + DO_HIST, aux + DO_META,
+                                                 scramble);
   EGS_AFTER_LAUNCH(stream, debug);
   depth_scan_kernel<<<3, MSD_BINS, 0, stream>>>(aux + DO_HIST, aux + DO_START);
   EGS_AFTER_LAUNCH(stream, debug);

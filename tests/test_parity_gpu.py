@@ -285,7 +285,7 @@ def test_three_binning_paths_agree(built, cuda_device, monkeypatch):
         av = a.binning_view()
         keys = av["keys"]
         assert bool((keys[1:] >= keys[:-1]).all())
-        for forced in ("packed", "pairs", "pairs8"):
+        for forced in ("packed", "pairs", "pairs8", "packed_presorted"):
             monkeypatch.setenv("EGS_SORT", forced)
             b = cabi.forward(**kw)
             assert a.num_rendered == b.num_rendered
@@ -293,6 +293,15 @@ def test_three_binning_paths_agree(built, cuda_device, monkeypatch):
             assert torch.equal(av["keys"], bv["keys"]) and torch.equal(av["values"], bv["values"]), forced
             assert torch.equal(a.image_view()["ranges"], b.image_view()["ranges"]), forced
             assert torch.equal(a.color, b.color) and torch.equal(a.radii, b.radii), forced
+        monkeypatch.delenv("EGS_SORT")
+        # the presort's veto (a depth beyond its 30-bit key range): instances emitted in an order
+        # unrelated to depth, every bucket sorted on all its bits after all
+        monkeypatch.setenv("EGS_PRESORT_DEBUG", "scramble")
+        c = cabi.forward(**kw)
+        monkeypatch.delenv("EGS_PRESORT_DEBUG")
+        cv = c.binning_view()
+        assert torch.equal(av["keys"], cv["keys"]) and torch.equal(av["values"], cv["values"]), "veto"
+        assert torch.equal(a.image_view()["ranges"], c.image_view()["ranges"]) and torch.equal(a.color, c.color)
         gv = a.geom_view()
         # the scan runs over the Gaussians front to back (presort) or in index order: same total
         assert int(gv["point_offsets"][-1]) == int(gv["tiles_touched"].to(torch.int64).sum())
