@@ -471,3 +471,26 @@ def test_adam_and_se3(built, cuda_device):
     m1, v1 = torch.zeros_like(p), torch.zeros_like(p)
     _C.adam_se3_step(p, g_moved, m1, v1, is_obj, 1, Rt, 1.6e-4, 1, 0.9, 0.999, 1e-15)
     assert torch.allclose(p, p_ref.detach(), rtol=1e-6, atol=4e-6 * 1.6e-4)
+
+
+def test_forward_lists_are_identical_across_calls(built, cuda_device):
+    """The sorted instance list is a pure function of the inputs: exact-size and guessed-size calls,
+    repeated, give the same count, keys and values (look-back orders, atomics and the depth presort
+    must never leak into the result)."""
+    from egogaussian_b200 import cabi, scenes
+    for P, W, H in ((200_000, 640, 360), (1_000_000, 1280, 720)):
+        sc = scenes.make_scene(P, W, H, sh_degree=0, seed=11).to(cuda_device)
+        cam = sc.camera
+        kw = dict(means3D=sc.means3D, opacities=sc.opacities, bg=sc.bg, viewmatrix=cam.viewmatrix,
+                  projmatrix=cam.projmatrix, campos=cam.campos, tanfovx=cam.tanfovx, tanfovy=cam.tanfovy,
+                  image_height=H, image_width=W, sh_degree=0, shs=sc.shs, scales=sc.scales, rotations=sc.rotations)
+        first = None
+        for i in range(12):
+            f = cabi.forward(**kw) if i % 2 == 0 else cabi.forward(num_rendered_hint=int(first[0] * 1.2), **kw)
+            bv = f.binning_view()
+            sig = (f.num_rendered, bv["keys"].clone(), bv["values"].clone())
+            if first is None:
+                first = sig
+            else:
+                assert sig[0] == first[0], (P, i)
+                assert torch.equal(sig[1], first[1]) and torch.equal(sig[2], first[2]), (P, i)
