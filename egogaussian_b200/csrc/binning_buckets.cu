@@ -63,12 +63,25 @@ constexpr int DO_HIST = 0, DO_START = 3 * 1024, DO_TICKET = 6 * 1024, DO_META = 
               DO_STATUS = DO_META + 8;
 static_assert(DO_STATUS == DEPTH_ORDER_AUX_WORDS, "aux layout");
 constexpr int DUP_THREADS = 256;
+// A Gaussian covering more tiles than this is left to duplicate_big_kernel (front-to-back order only):
+// the nearest Gaussians are the largest on screen, they all sit in the first groups of that order, and
+// a warp that owns 32 of them would emit over a hundred thousand words alone (measured: the kernel
+// went from 0.08 to 0.18 ms on two of the eight bench views).
+constexpr uint32_t DUP_BIG = 512;
+
+__device__ __forceinline__ void count_bucket(uint32_t* s_hist, bool live, uint32_t bucket, unsigned lane) {
+  const uint32_t peers = __match_any_sync(0xffffffffu, live ? bucket : 0xffffffffu);
+  if (live && (peers & ((1u << lane) - 1u)) == 0u) atomicAdd(&s_hist[bucket], (uint32_t)__popc(peers));
+}
+
 __global__ void __launch_bounds__(DUP_THREADS)
 duplicate_words_kernel(int P, const float2* __restrict__ means2D, const float* __restrict__ depths,
                        const uint32_t* __restrict__ offsets, const int* __restrict__ radii,
                        const uint32_t* __restrict__ order /* NULL: slot j of the scan is Gaussian j */,
                        uint64_t* __restrict__ words, int grid_x, int grid_y, int idx_bits,
-                       InstanceCount count, int bucket_shift, uint32_t* __restrict__ bucket_hist) {
+                       InstanceCount count, int bucket_shift, uint32_t* __restrict__ bucket_hist,
+                       uint32_t* __restrict__ big_list /* with order: scan slots left to duplicate_big_kernel */,
+                       uint32_t* __restrict__ big_count) {
   uint32_t n;
   if (!count.get(n)) return;   // more instances than the buffer holds: write nothing
   __shared__ uint32_t s_hist[MSD_BINS];
@@ -82,7 +95,6 @@ duplicate_words_kernel(int P, const float2* __restrict__ means2D, const float* _
     const bool valid = slot < P;
     const int idx = !valid ? 0 : order ? (int)order[slot] : slot;
     const int r = valid ? radii[idx] : 0;
-    const uint32_t end = offsets[valid ? slot : P - 1];
     uint32_t lox = 0, loy = 0, w = 1, cnt = 0, dbits = 0;
     if (r > 0) {
       uint2 lo, hi;
@@ -93,32 +105,83 @@ duplicate_words_kernel(int P, const float2* __restrict__ means2D, const float* _
       cnt = (hi.x - lo.x) * (hi.y - lo.y);
       dbits = __float_as_uint(depths[idx]);
     }
-    const uint32_t start = end - cnt;   // culled and out-of-range lanes: empty run at their neighbour's end
-    const uint32_t run_base = __shfl_sync(0xffffffffu, start, 0);
-    const uint32_t run_end = __shfl_sync(0xffffffffu, end, 31);
-    for (uint32_t o = run_base + lane; o - lane < run_end; o += 32) {   // warp-uniform trip count
-      // owner = the last lane whose run starts at or before slot o (empty runs sort before it)
+    // first output slot of this Gaussian; the warp's own runs, big ones taken out, are numbered
+    // contiguously (`mine`) and shared evenly between the lanes
+    const uint32_t start = (valid ? offsets[slot] : 0u) - cnt;
+    if (big_list != nullptr && cnt > DUP_BIG) {
+      big_list[atomicAdd(big_count, 1u)] = (uint32_t)slot;
+      cnt = 0;
+    }
+    uint32_t incl = cnt;
+#pragma unroll
+    for (int d = 1; d < 32; d <<= 1) {
+      const uint32_t t = __shfl_up_sync(0xffffffffu, incl, d);
+      if (lane >= d) incl += t;
+    }
+    const uint32_t mine = incl - cnt;
+    const uint32_t total = __shfl_sync(0xffffffffu, incl, 31);
+    for (uint32_t o = lane; o - lane < total; o += 32) {   // warp-uniform trip count
+      // owner = the last lane whose run starts at or before o (empty runs sort before it)
       int L = 0;
 #pragma unroll
       for (int step = 16; step > 0; step >>= 1) {
-        const uint32_t s_mid = __shfl_sync(0xffffffffu, start, L + step);
+        const uint32_t s_mid = __shfl_sync(0xffffffffu, mine, L + step);
         if (s_mid <= o) L += step;
       }
+      const uint32_t o_mine = __shfl_sync(0xffffffffu, mine, L);
       const uint32_t o_start = __shfl_sync(0xffffffffu, start, L);
       const uint32_t o_lox = __shfl_sync(0xffffffffu, lox, L);
       const uint32_t o_loy = __shfl_sync(0xffffffffu, loy, L);
       const uint32_t o_w = __shfl_sync(0xffffffffu, w, L);
       const uint32_t o_d = __shfl_sync(0xffffffffu, dbits, L);
       const uint32_t o_idx = __shfl_sync(0xffffffffu, (uint32_t)idx, L);
-      const bool live = o < run_end;
-      const uint32_t local = o - o_start;
+      const bool live = o < total;
+      const uint32_t local = o - o_mine;
       const uint32_t dy = local / o_w;
       const uint32_t tile = (o_loy + dy) * (uint32_t)grid_x + o_lox + (local - dy * o_w);
       if (live)
-        words[o] = ((uint64_t)tile << tile_shift) | ((uint64_t)o_d << idx_bits) | o_idx;
-      const uint32_t bucket = tile >> bucket_shift;
-      const uint32_t peers = __match_any_sync(0xffffffffu, live ? bucket : 0xffffffffu);
-      if (live && (peers & ((1u << lane) - 1u)) == 0u) atomicAdd(&s_hist[bucket], (uint32_t)__popc(peers));
+        words[o_start + local] = ((uint64_t)tile << tile_shift) | ((uint64_t)o_d << idx_bits) | o_idx;
+      count_bucket(s_hist, live, tile >> bucket_shift, lane);
+    }
+  }
+  __syncthreads();
+  for (int i = threadIdx.x; i < MSD_BINS; i += DUP_THREADS) {
+    const uint32_t c = s_hist[i];
+    if (c) atomicAdd(&bucket_hist[i], c);
+  }
+}
+
+// The Gaussians duplicate_words_kernel set aside: one CTA per Gaussian at a time, its words shared
+// between the 256 threads.
+__global__ void __launch_bounds__(DUP_THREADS)
+duplicate_big_kernel(const float2* __restrict__ means2D, const float* __restrict__ depths,
+                     const uint32_t* __restrict__ offsets, const int* __restrict__ radii,
+                     const uint32_t* __restrict__ order, uint64_t* __restrict__ words, int grid_x, int grid_y,
+                     int idx_bits, InstanceCount count, int bucket_shift, uint32_t* __restrict__ bucket_hist,
+                     const uint32_t* __restrict__ big_list, const uint32_t* __restrict__ big_count) {
+  uint32_t n;
+  if (!count.get(n)) return;
+  const uint32_t n_big = *big_count;
+  if (blockIdx.x >= n_big) return;
+  __shared__ uint32_t s_hist[MSD_BINS];
+  for (int i = threadIdx.x; i < MSD_BINS; i += DUP_THREADS) s_hist[i] = 0;
+  __syncthreads();
+  const unsigned lane = threadIdx.x & 31;
+  const int tile_shift = 32 + idx_bits;
+  for (uint32_t b = blockIdx.x; b < n_big; b += gridDim.x) {
+    const uint32_t slot = big_list[b];
+    const uint32_t idx = order[slot];
+    uint2 lo, hi;
+    tile_rect(means2D[idx], radii[idx], grid_x, grid_y, lo, hi);
+    const uint32_t w = hi.x - lo.x, cnt = w * (hi.y - lo.y);
+    const uint32_t start = offsets[slot] - cnt;
+    const uint64_t low = ((uint64_t)__float_as_uint(depths[idx]) << idx_bits) | idx;
+    for (uint32_t t = threadIdx.x; t - threadIdx.x < cnt; t += DUP_THREADS) {   // CTA-uniform trip count
+      const bool live = t < cnt;
+      const uint32_t dy = t / w;
+      const uint32_t tile = (lo.y + dy) * (uint32_t)grid_x + lo.x + (t - dy * w);
+      if (live) words[start + t] = ((uint64_t)tile << tile_shift) | low;
+      count_bucket(s_hist, live, tile >> bucket_shift, lane);
     }
   }
   __syncthreads();
@@ -708,10 +771,20 @@ int launch_binning_buckets(const GeomPtrs& g, const BinningPtrs& b, const ImageP
     EGS_CUDA_TRY(cudaMemsetAsync(b.hist, 0, zero, stream));
     // 4 CTAs per SM, each warp strides over groups of 32 Gaussians; the bucket histogram comes out
     // of the same kernel
+    // with the presort: sort_keys[1] is free again and holds the list of set-aside Gaussians, counted
+    // in meta[4] (zeroed with the rest of the aux words when the presort started)
+    uint32_t* big_list = gauss_order ? reinterpret_cast<uint32_t*>(g.sort_keys[1]) : nullptr;
+    uint32_t* big_count = gauss_order ? g.sort_aux + DO_META + 4 : nullptr;
     duplicate_words_kernel<<<148 * 4, DUP_THREADS, 0, stream>>>(P, g.means2D, g.depths, g.point_offsets, radii,
                                                              gauss_order, b.keys[1], gx, gy, ib, count, bucket_shift,
-                                                             hist);
+                                                             hist, big_list, big_count);
     EGS_AFTER_LAUNCH(stream, debug);
+    if (gauss_order) {
+      duplicate_big_kernel<<<148 * 4, DUP_THREADS, 0, stream>>>(g.means2D, g.depths, g.point_offsets, radii, gauss_order,
+                                                             b.keys[1], gx, gy, ib, count, bucket_shift, hist, big_list,
+                                                             big_count);
+      EGS_AFTER_LAUNCH(stream, debug);
+    }
     bucket_scan_kernel<<<1, MSD_BINS, 0, stream>>>(hist, start, order);
     EGS_AFTER_LAUNCH(stream, debug);
   }
