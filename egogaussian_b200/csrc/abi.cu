@@ -215,13 +215,19 @@ static int forward_impl(const char* who, const EgsForwardArgs* args, const EgsMo
   const char* force = getenv("EGS_SORT");
   const bool fits = packed_path_fits(a.P, a.width, a.height);
   const bool forced = force && force[0] != 0;
-  // Front-to-back presort of the Gaussians (binning.cu): the instances are then emitted in depth
-  // order and the instance sorters only order the tile bits. Pays off from a few thousand
-  // Gaussians on; EGS_PRESORT=0 turns it off (A/B, cross-check), the forced paths never use it.
-  static const bool presort_on = !(getenv("EGS_PRESORT") && getenv("EGS_PRESORT")[0] == '0');
-  // (EGS_SORT=packed_presorted: the five-pass packed path fed in presorted order, which is what a
-  // frame with too many instances for the bucket sorter gets; a test hook like the other EGS_SORT values)
-  const bool presort = presort_on && fits && a.P >= 4096 && (!forced || strcmp(force, "packed_presorted") == 0);
+  // Front-to-back presort of the Gaussians (binning_buckets.cu): the instances are then emitted in
+  // depth order and the bucket sorter only orders the tile bits. Sorting the Gaussians costs ~0.06 ms
+  // plus 0.04 ms per million and saves ~0.02 ms per million INSTANCES, so it is used from 3M expected
+  // instances on (the caller's guess; without one, from 300k Gaussians on). EGS_PRESORT=0 / 1 forces
+  // it off / on (A/B, tests); the forced sort paths never use it, except the test hook
+  // EGS_SORT=packed_presorted: the five-pass packed path fed in presorted order, which is what a
+  // frame with too many instances for the bucket sorter gets.
+  const char* ps = getenv("EGS_PRESORT");
+  const bool presort_wanted = ps && ps[0] == '0'   ? false
+                              : ps && ps[0] == '1' ? a.P >= 64
+                              : a.num_rendered_hint > 0 ? a.num_rendered_hint >= 3000000
+                                                        : a.P >= 300000;
+  const bool presort = presort_wanted && fits && (!forced || strcmp(force, "packed_presorted") == 0);
   const uint32_t* order = presort ? g.sort_vals[0] : nullptr;
   if (presort)
     if (int rc = launch_depth_order(g, a.P, a.radii, stream, a.debug)) return rc;

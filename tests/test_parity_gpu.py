@@ -280,6 +280,7 @@ def test_three_binning_paths_agree(built, cuda_device, monkeypatch):
                   projmatrix=cam.projmatrix, campos=cam.campos, tanfovx=cam.tanfovx, tanfovy=cam.tanfovy,
                   image_height=H, image_width=W, sh_degree=1, shs=sc.shs, cov3D_precomp=sc.cov3D())
         monkeypatch.delenv("EGS_SORT", raising=False)
+        monkeypatch.setenv("EGS_PRESORT", "1")   # these scenes are below the size where it is used by itself
         a = cabi.forward(**kw)
         assert a.num_rendered > 0
         av = a.binning_view()
