@@ -194,7 +194,7 @@ duplicate_big_kernel(const float2* __restrict__ means2D, const float* __restrict
 // exclusive scan of the bucket histogram; start[MSD_BINS] = total
 __global__ void __launch_bounds__(MSD_BINS)
 bucket_scan_kernel(const uint32_t* __restrict__ hist, uint32_t* __restrict__ start,
-                   uint32_t* __restrict__ order) {
+                   uint32_t* __restrict__ order, uint32_t* __restrict__ work_count, uint32_t listed) {
   __shared__ uint32_t s_w[MSD_BINS / 32];
   const uint32_t v = hist[threadIdx.x];
   const unsigned lane = lane_id(), warp = threadIdx.x >> 5;
@@ -214,7 +214,10 @@ bucket_scan_kernel(const uint32_t* __restrict__ hist, uint32_t* __restrict__ sta
   // order[k] = bucket handled by CTA k of the sorter. Largest-first scheduling (a bitonic sort of
   // the counts here) was measured: no gain at ~7 waves of similar buckets, and the sort itself cost
   // 6 us on the critical path, so the order is the identity.
+  // With the presort, bucket_split_kernel takes the buckets that fit it and lists the others here
+  // (`listed` = 0: the list starts empty).
   order[threadIdx.x] = threadIdx.x;
+  if (threadIdx.x == 0) *work_count = listed;
 }
 
 // ---------------------------------------------------------------------------------------------
@@ -560,17 +563,10 @@ __device__ __forceinline__ void bucket_pass(BucketSmem& S, CNT* hist, const uint
 }
 
 template <bool HWMATCH>
-__global__ void __launch_bounds__(BK_THREADS)
-bucket_sort_kernel(uint64_t* __restrict__ words /* partitioned; receives the sorted keys in place */,
-                   uint64_t* __restrict__ scratch /* other ping-pong buffer (overflow buckets) */,
-                   const uint32_t* __restrict__ bucket_start, const uint32_t* __restrict__ order,
-                   uint32_t* __restrict__ point_list, uint2* __restrict__ ranges, int n_tiles, int idx_bits, int bucket_shift,
-                   int rem_bits /* key bits below the bucket digit */,
-                   int first_bit /* key bits below this one are in order already (32: presorted by depth) */,
-                   const uint32_t* __restrict__ presort_veto /* NULL, or a flag: nonzero = sort all the bits after all */) {
-  extern __shared__ __align__(16) unsigned char smem_raw[];
-  BucketSmem& S = *reinterpret_cast<BucketSmem*>(smem_raw);
-  const uint32_t bucket = order[blockIdx.x];   // largest bucket first
+__device__ __forceinline__ void sort_one_bucket(BucketSmem& S, const uint32_t bucket, uint64_t* __restrict__ words,
+                                                uint64_t* __restrict__ scratch, const uint32_t* __restrict__ bucket_start,
+                                                uint32_t* __restrict__ point_list, uint2* __restrict__ ranges, int n_tiles,
+                                                int idx_bits, int bucket_shift, int rem_bits, int first_bit) {
   const uint32_t seg = bucket_start[bucket];
   const uint32_t n = bucket_start[bucket + 1] - seg;
   const unsigned tid = threadIdx.x;
@@ -580,7 +576,6 @@ bucket_sort_kernel(uint64_t* __restrict__ words /* partitioned; receives the sor
   const uint32_t tile_hi = min((uint32_t)n_tiles, (bucket + 1u) << bucket_shift);
   for (uint32_t t = tile_lo + tid; t < tile_hi; t += BK_THREADS) ranges[t] = make_uint2(0u, 0u);
   if (n == 0) return;
-  if (presort_veto && *presort_veto) first_bit = 0;
 
   const bool in_smem = n <= (uint32_t)BK_CAP;
   uint64_t* A;
@@ -630,9 +625,140 @@ bucket_sort_kernel(uint64_t* __restrict__ words /* partitioned; receives the sor
   for (uint32_t i = tid; i < n; i += BK_THREADS) words[seg + i] = A[i] >> idx_bits;
 }
 
+// CTA k takes the buckets order[k], order[k + gridDim.x], ... of the first *work_count entries: all 1024
+// buckets with one CTA each, or the few that bucket_split_kernel left over.
+template <bool HWMATCH>
+__global__ void __launch_bounds__(BK_THREADS)
+bucket_sort_kernel(uint64_t* __restrict__ words /* partitioned; receives the sorted keys in place */,
+                   uint64_t* __restrict__ scratch /* other ping-pong buffer (overflow buckets) */,
+                   const uint32_t* __restrict__ bucket_start, const uint32_t* __restrict__ order,
+                   const uint32_t* __restrict__ work_count, uint32_t* __restrict__ point_list,
+                   uint2* __restrict__ ranges, int n_tiles, int idx_bits, int bucket_shift,
+                   int rem_bits /* key bits below the bucket digit */,
+                   int first_bit /* key bits below this one are in order already (32: presorted by depth) */,
+                   const uint32_t* __restrict__ presort_veto /* NULL, or a flag: nonzero = sort all the bits after all */) {
+  extern __shared__ __align__(16) unsigned char smem_raw[];
+  BucketSmem& S = *reinterpret_cast<BucketSmem*>(smem_raw);
+  if (presort_veto && *presort_veto) first_bit = 0;
+  const uint32_t count = *work_count;
+  for (uint32_t k = blockIdx.x; k < count; k += gridDim.x) {
+    sort_one_bucket<HWMATCH>(S, order[k], words, scratch, bucket_start, point_list, ranges, n_tiles, idx_bits,
+                             bucket_shift, rem_bits, first_bit);
+    __syncthreads();   // shared buffers are free for the next bucket
+  }
+}
+
 // ---------------------------------------------------------------------------------------------
 // host side
 // ---------------------------------------------------------------------------------------------
+// ---------------------------------------------------------------------------------------------
+// presorted buckets: a stable split on the tile bits, words in registers
+// ---------------------------------------------------------------------------------------------
+// After the depth presort a bucket only has to be split by the BITS tile bits below the bucket digit.
+// That needs no staging in shared memory: a thread keeps its (at most 24) words in registers, a warp
+// counts the 2^BITS bins with one ballot each while ranking, the per-warp counts are scanned in a few
+// hundred bytes of shared memory, and index list, keys and tile ranges go straight to global memory.
+// Two CTAs fit an SM, where bucket_sort_kernel's two 96 KB buffers allow one (0.089 -> see DESIGN.md).
+// Buckets beyond BK_CAP words, wider splits and vetoed frames stay with bucket_sort_kernel.
+constexpr int BS_THREADS = 512;
+constexpr int BS_WARPS = BS_THREADS / 32;
+constexpr int BS_ROUNDS = BK_CAP / BS_THREADS;   // 24
+constexpr int BS_MAX_BITS = 3;
+static_assert(BS_ROUNDS * BS_THREADS == BK_CAP, "capacity");
+
+template <int BITS>
+__global__ void __launch_bounds__(BS_THREADS, 2)
+bucket_split_kernel(uint64_t* __restrict__ words /* partitioned; receives the sorted keys in place */,
+                    const uint32_t* __restrict__ bucket_start, uint32_t* __restrict__ point_list,
+                    uint2* __restrict__ ranges, int n_tiles, int idx_bits, const uint32_t* __restrict__ presort_veto,
+                    uint32_t* __restrict__ leftover /* buckets for bucket_sort_kernel */, uint32_t* __restrict__ leftover_count) {
+  constexpr int BINS = 1 << BITS;
+  __shared__ uint32_t s_warp[BS_WARPS][BINS];   // per-warp counts, then exclusive offsets inside the bin
+  __shared__ uint32_t s_bin[BINS + 1];          // first slot of every bin
+  const uint32_t bucket = blockIdx.x;
+  const uint32_t seg = bucket_start[bucket];
+  const uint32_t n = bucket_start[bucket + 1] - seg;
+  const unsigned tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  if (*presort_veto || n > (uint32_t)BK_CAP) {
+    if (tid == 0) leftover[atomicAdd(leftover_count, 1u)] = bucket;
+    return;
+  }
+  const unsigned lt_mask = (1u << lane) - 1u;
+  const uint32_t chunk = ((n + BS_WARPS - 1) / BS_WARPS + 31u) & ~31u;   // per warp, multiple of 32
+  const uint32_t begin = warp * chunk;
+  const uint32_t end = min(n, begin + chunk);
+  const int tile_shift = idx_bits + 32;
+
+  uint64_t w[BS_ROUNDS];
+#pragma unroll
+  for (int r = 0; r < BS_ROUNDS; ++r) {
+    const uint32_t i = begin + r * 32 + lane;
+    w[r] = i < end ? words[seg + i] : ~0ull;
+  }
+  uint32_t cnt[BINS];
+#pragma unroll
+  for (int b = 0; b < BINS; ++b) cnt[b] = 0;
+  uint16_t rank[BS_ROUNDS];
+#pragma unroll
+  for (int r = 0; r < BS_ROUNDS; ++r) {
+    rank[r] = 0;
+    if (begin + r * 32 < end) {   // warp-uniform
+      const bool ok = begin + r * 32 + lane < end;
+      const uint32_t d = (uint32_t)(w[r] >> tile_shift) & (BINS - 1);
+#pragma unroll
+      for (int b = 0; b < BINS; ++b) {
+        const uint32_t m = __ballot_sync(0xffffffffu, ok && d == (uint32_t)b);
+        if (d == (uint32_t)b) rank[r] = (uint16_t)(cnt[b] + __popc(m & lt_mask));
+        cnt[b] += __popc(m);
+      }
+    }
+  }
+#pragma unroll
+  for (int b = 0; b < BINS; ++b)
+    if (lane == (unsigned)b) s_warp[warp][b] = cnt[b];
+  __syncthreads();   // also: every word of the bucket is in a register before anything is overwritten
+  if (tid < BINS) {
+    uint32_t run = 0;
+#pragma unroll
+    for (int q = 0; q < BS_WARPS; ++q) {
+      const uint32_t c = s_warp[q][tid];
+      s_warp[q][tid] = run;
+      run += c;
+    }
+    s_bin[tid + 1] = run;   // bin totals for now
+  }
+  __syncthreads();
+  if (tid == 0) {
+    uint32_t run = 0;
+    s_bin[0] = 0;
+#pragma unroll
+    for (int b = 0; b < BINS; ++b) {
+      run += s_bin[b + 1];
+      s_bin[b + 1] = run;
+    }
+  }
+  __syncthreads();
+  const uint64_t idx_mask = (1ull << idx_bits) - 1ull;
+#pragma unroll
+  for (int r = 0; r < BS_ROUNDS; ++r) {
+    const uint32_t i = begin + r * 32 + lane;
+    if (i < end) {
+      const uint32_t d = (uint32_t)(w[r] >> tile_shift) & (BINS - 1);
+      const uint32_t dst = seg + s_bin[d] + s_warp[warp][d] + rank[r];
+      point_list[dst] = (uint32_t)(w[r] & idx_mask);
+      words[dst] = w[r] >> idx_bits;
+    }
+  }
+  // bin b is tile (bucket << BITS) | b; empty tiles read (0, 0) like the reference's zero fill
+  if (tid < BINS) {
+    const uint32_t tile = (bucket << BITS) | tid;
+    if (tile < (uint32_t)n_tiles) {
+      const uint32_t lo = s_bin[tid], hi = s_bin[tid + 1];
+      ranges[tile] = hi > lo ? make_uint2(seg + lo, seg + hi) : make_uint2(0u, 0u);
+    }
+  }
+}
+
 // ---------------------------------------------------------------------------------------------
 // front-to-back order of the Gaussians
 // ---------------------------------------------------------------------------------------------
@@ -762,7 +888,11 @@ int launch_binning_buckets(const GeomPtrs& g, const BinningPtrs& b, const ImageP
   uint32_t* hist = b.hist;                 // [MSD_BINS]
   uint32_t* start = b.hist + MSD_BINS;     // [MSD_BINS + 1]
   uint32_t* order = b.hist + 2 * MSD_BINS + 8;   // [MSD_BINS]
-  static_assert(3 * MSD_BINS + 8 <= SORT_HIST_WORDS, "histogram area too small");
+  uint32_t* work_count = order + MSD_BINS;       // buckets listed in `order` for bucket_sort_kernel
+  static_assert(3 * MSD_BINS + 8 + 1 <= SORT_HIST_WORDS, "histogram area too small");
+  // presorted frames: the buckets that fit go through the register-resident split (EGS_SPLIT=0: A/B)
+  const char* sp = getenv("EGS_SPLIT");
+  const bool split_ran = gauss_order != nullptr && bucket_shift <= BS_MAX_BITS && !(sp && sp[0] == '0');
   {
     StageTimer timer(stream, ST_DUPLICATE);
     // histogram, ticket and the status words of the single partition pass (not the whole area the
@@ -785,7 +915,7 @@ int launch_binning_buckets(const GeomPtrs& g, const BinningPtrs& b, const ImageP
                                                              big_count);
       EGS_AFTER_LAUNCH(stream, debug);
     }
-    bucket_scan_kernel<<<1, MSD_BINS, 0, stream>>>(hist, start, order);
+    bucket_scan_kernel<<<1, MSD_BINS, 0, stream>>>(hist, start, order, work_count, split_ran ? 0u : (uint32_t)MSD_BINS);
     EGS_AFTER_LAUNCH(stream, debug);
   }
   {
@@ -804,17 +934,30 @@ int launch_binning_buckets(const GeomPtrs& g, const BinningPtrs& b, const ImageP
     // bits below the bucket digit remain (one pass instead of four)
     const int first_bit = gauss_order ? 32 : 0;
     const uint32_t* presort_veto = gauss_order ? g.sort_aux + DO_META + 3 : nullptr;
+    if (split_ran) {
+      switch (bucket_shift) {
+        case 0: bucket_split_kernel<0><<<MSD_BINS, BS_THREADS, 0, stream>>>(b.keys[0], start, b.vals[0], im.ranges, n_tiles, ib, presort_veto, order, work_count); break;
+        case 1: bucket_split_kernel<1><<<MSD_BINS, BS_THREADS, 0, stream>>>(b.keys[0], start, b.vals[0], im.ranges, n_tiles, ib, presort_veto, order, work_count); break;
+        case 2: bucket_split_kernel<2><<<MSD_BINS, BS_THREADS, 0, stream>>>(b.keys[0], start, b.vals[0], im.ranges, n_tiles, ib, presort_veto, order, work_count); break;
+        default: bucket_split_kernel<3><<<MSD_BINS, BS_THREADS, 0, stream>>>(b.keys[0], start, b.vals[0], im.ranges, n_tiles, ib, presort_veto, order, work_count); break;
+      }
+      EGS_AFTER_LAUNCH(stream, debug);
+    }
+    // after the split only its leftovers are listed: one CTA per SM walks the list
+    const int sort_grid = split_ran ? 148 : MSD_BINS;
     const char* m = getenv("EGS_MATCH");
     if (!(m && strcmp(m, "ballot") == 0)) {
       EGS_CUDA_TRY(cudaFuncSetAttribute(bucket_sort_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                         (int)sizeof(BucketSmem)));
-      bucket_sort_kernel<true><<<MSD_BINS, BK_THREADS, sizeof(BucketSmem), stream>>>(
-          b.keys[0], b.keys[1], start, order, b.vals[0], im.ranges, n_tiles, ib, bucket_shift, rem_bits, first_bit, presort_veto);
+      bucket_sort_kernel<true><<<sort_grid, BK_THREADS, sizeof(BucketSmem), stream>>>(
+          b.keys[0], b.keys[1], start, order, work_count, b.vals[0], im.ranges, n_tiles, ib, bucket_shift, rem_bits,
+          first_bit, presort_veto);
     } else {
       EGS_CUDA_TRY(cudaFuncSetAttribute(bucket_sort_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                         (int)sizeof(BucketSmem)));
-      bucket_sort_kernel<false><<<MSD_BINS, BK_THREADS, sizeof(BucketSmem), stream>>>(
-          b.keys[0], b.keys[1], start, order, b.vals[0], im.ranges, n_tiles, ib, bucket_shift, rem_bits, first_bit, presort_veto);
+      bucket_sort_kernel<false><<<sort_grid, BK_THREADS, sizeof(BucketSmem), stream>>>(
+          b.keys[0], b.keys[1], start, order, work_count, b.vals[0], im.ranges, n_tiles, ib, bucket_shift, rem_bits,
+          first_bit, presort_veto);
     }
     EGS_AFTER_LAUNCH(stream, debug);
   }
