@@ -221,6 +221,12 @@ def load() -> C.CDLL:
     lib.egs_binning_view.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_int, C.POINTER(EgsBinningView)]
     lib.egs_image_view.restype = C.c_int
     lib.egs_image_view.argtypes = [C.c_void_p, C.c_int, C.c_int, C.POINTER(EgsImageView)]
+    lib.egs_binning_keys.restype = C.c_int
+    lib.egs_binning_keys.argtypes = [C.c_void_p, C.c_int, C.c_void_p, C.c_int, C.c_void_p, C.c_int, C.c_int, C.c_void_p]
+    lib.egs_debug_option.restype = C.c_int
+    lib.egs_debug_option.argtypes = [C.c_char_p, C.c_char_p]
+    lib.egs_exchange_set_timeout_ms.restype = C.c_int
+    lib.egs_exchange_set_timeout_ms.argtypes = [C.c_ulonglong]
     lib.egs_launch_count.restype = C.c_ulonglong
     lib.egs_profile_enable.restype = C.c_int
     lib.egs_profile_enable.argtypes = [C.c_int]
@@ -236,6 +242,15 @@ def load() -> C.CDLL:
 
 class EgsError(RuntimeError):
     pass
+
+
+def debug_option(name: str, value: Optional[str] = None) -> None:
+    """egs_debug_option: force a binning path / kernel variant for tests and A/B timing (None = default)."""
+    _check(load().egs_debug_option(name.encode(), None if value is None else str(value).encode()), "egs_debug_option")
+
+
+def exchange_set_timeout_ms(ms: int) -> None:
+    _check(load().egs_exchange_set_timeout_ms(int(ms)), "egs_exchange_set_timeout_ms")
 
 
 def _check(rc: int, what: str) -> None:
@@ -305,6 +320,10 @@ class ForwardResult:
             return {"keys": e, "values": e.to(torch.int32)}
         v = EgsBinningView()
         cap = lib.egs_binning_capacity(int(self.binning.numel()))   # the blob may be laid out for a guessed capacity
+        # forward does not write the sorted keys (nothing on the path reads them): rebuild them
+        with torch.cuda.device(self.binning.device):
+            _check(lib.egs_binning_keys(self.geom.data_ptr(), self.P, self.binning.data_ptr(), cap,
+                                        self.image.data_ptr(), self.W, self.H, _stream_handle()), "egs_binning_keys")
         _check(lib.egs_binning_view(self.binning.data_ptr(), cap, self.W, self.H, C.byref(v)), "egs_binning_view")
         d = self.binning.device
         return {"keys": _view(v.keys_sorted, (R,), torch.int64, d),

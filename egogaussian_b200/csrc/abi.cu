@@ -32,6 +32,7 @@ void count_launch(unsigned n) { g_launches.fetch_add(n, std::memory_order_relaxe
 // ---- stage timing ---------------------------------------------------------------------------
 struct ProfRecord {
   int stage;
+  int device;   // events belong to the device they were created on
   cudaEvent_t a, b;
   unsigned long long launches_before;
   unsigned long long launches;
@@ -45,15 +46,24 @@ bool profiling_enabled() { return g_prof_on.load(std::memory_order_relaxed); }
 
 void profile_begin(cudaStream_t stream, int stage, void** token) {
   ProfRecord* r = nullptr;
+  int dev = 0;
+  if (cudaGetDevice(&dev) != cudaSuccess) {
+    *token = nullptr;
+    return;
+  }
   {
     std::lock_guard<std::mutex> lk(g_prof_mu);
-    if (!g_prof_free.empty()) {
-      r = g_prof_free.back();
-      g_prof_free.pop_back();
+    for (size_t i = g_prof_free.size(); i-- > 0;) {   // a pooled pair is reused only on its own device
+      if (g_prof_free[i]->device == dev) {
+        r = g_prof_free[i];
+        g_prof_free.erase(g_prof_free.begin() + (long)i);
+        break;
+      }
     }
   }
   if (!r) {
     r = new ProfRecord();
+    r->device = dev;
     if (cudaEventCreate(&r->a) != cudaSuccess || cudaEventCreate(&r->b) != cudaSuccess) {
       delete r;
       *token = nullptr;
@@ -79,14 +89,20 @@ static const char* kStageNames[ST_COUNT] = {"preprocess_fwd", "scan", "duplicate
                                             "blend_bwd", "preprocess_bwd", "adam", "se3",
                                             "model_fwd", "model_bwd", "image_loss", "depth_order"};
 
-// Pinned read-back slot of the instance count, one per host thread, created on first use and kept
-// for the life of the process.
+// Pinned read-back slot of a forward call (word 0: instance count, 1: presort veto, 2: prefilter
+// fault), one per host thread AND device: the event that marks the arrival belongs to the device it
+// was created on, so a thread that renders on cuda:0 and later on cuda:1 needs one of each. Created
+// on first use with that device current and kept for the life of the process.
+constexpr int kMaxDevices = 64;
 struct HostCountSlot {
   uint32_t* host = nullptr;
   cudaEvent_t arrived = nullptr;
 };
 static HostCountSlot* host_count_slot() {
-  static thread_local HostCountSlot slot;
+  static thread_local HostCountSlot slots[kMaxDevices];
+  int dev = -1;
+  if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= kMaxDevices) return nullptr;
+  HostCountSlot& slot = slots[dev];
   if (!slot.host) {
     void* p = nullptr;
     if (cudaHostAlloc(&p, 64, cudaHostAllocDefault) != cudaSuccess) return nullptr;
@@ -97,6 +113,17 @@ static HostCountSlot* host_count_slot() {
     slot.host = static_cast<uint32_t*>(p);
   }
   return &slot;
+}
+
+// ---- test / A-B switches (egs_debug_option) ---------------------------------------------------
+static std::atomic<int> g_dbg_sort{SORT_AUTO}, g_dbg_presort{-1}, g_dbg_scramble{0}, g_dbg_fwd_v2{0};
+DebugOptions debug_options() {
+  DebugOptions o;
+  o.sort = g_dbg_sort.load(std::memory_order_relaxed);
+  o.presort = g_dbg_presort.load(std::memory_order_relaxed);
+  o.presort_scramble = g_dbg_scramble.load(std::memory_order_relaxed);
+  o.fwd_v2 = g_dbg_fwd_v2.load(std::memory_order_relaxed);
+  return o;
 }
 
 static int check_pairs(const char* who, const void* shs, const void* colors, const void* scales,
@@ -212,46 +239,53 @@ static int forward_impl(const char* who, const EgsForwardArgs* args, const EgsMo
 
   if (int rc = launch_preprocess_forward(a, model, g, stream)) return rc;
 
-  const char* force = getenv("EGS_SORT");
-  const bool fits = packed_path_fits(a.P, a.width, a.height);
-  const bool forced = force && force[0] != 0;
+  const DebugOptions dbg = debug_options();
+  const bool fits = packed_path_fits(a.P, a.width, a.height);   // tile | depth | index in one 64-bit word
+  const bool forced = dbg.sort != SORT_AUTO;
   // Front-to-back presort of the Gaussians (binning_buckets.cu): the instances are then emitted in
-  // depth order and the bucket sorter only orders the tile bits. Sorting the Gaussians costs ~0.06 ms
-  // plus 0.04 ms per million and saves ~0.02 ms per million INSTANCES, so it is used from 3M expected
-  // instances on (the caller's guess; without one, from 300k Gaussians on). EGS_PRESORT=0 / 1 forces
-  // it off / on (A/B, tests); the forced sort paths never use it, except the test hook
-  // EGS_SORT=packed_presorted: the five-pass packed path fed in presorted order, which is what a
-  // frame with too many instances for the bucket sorter gets.
-  const char* ps = getenv("EGS_PRESORT");
-  const bool presort_wanted = ps && ps[0] == '0'   ? false
-                              : ps && ps[0] == '1' ? a.P >= 64
+  // depth order, carry no depth bits and a bucket only needs a stable split on a few tile bits.
+  // Sorting the Gaussians costs ~0.06 ms plus 0.04 ms per million and saves ~0.02 ms per million
+  // INSTANCES, so it is used from 3M expected instances on (the caller's guess; without one, from 300k
+  // Gaussians on), and whenever the full word does not fit (more than 2^(32 - tile bits) Gaussians).
+  // egs_debug_option("presort", "0" / "1") forces it off / on (A/B, tests); the forced sort paths
+  // never use it.
+  const bool presort_wanted = dbg.presort == 0   ? false
+                              : dbg.presort == 1 ? a.P >= 64
+                              : !fits            ? a.P >= 64
                               : a.num_rendered_hint > 0 ? a.num_rendered_hint >= 3000000
                                                         : a.P >= 300000;
-  const bool presort = presort_wanted && fits && (!forced || strcmp(force, "packed_presorted") == 0);
+  const bool presort = presort_wanted && !forced && presorted_path_ok(a.P, a.width, a.height);
   const uint32_t* order = presort ? g.sort_vals[0] : nullptr;
   if (presort)
     if (int rc = launch_depth_order(g, a.P, a.radii, stream, a.debug)) return rc;
   if (int rc = launch_scan_tiles(g, a.P, order, stream, a.debug)) return rc;
 
   // The one device->host read per forward (the reference's is rasterizer_impl.cu:281-282): the
-  // instance count lands in a pinned slot and an event marks its arrival.
+  // instance count (and, next to it, the presort's veto and the prefilter fault) lands in a pinned
+  // slot and an event marks its arrival.
   HostCountSlot* slot = host_count_slot();
   if (!slot) {
     set_error("%s: cannot allocate the pinned read-back slot", who);
     return EGS_ERR_CUDA;
   }
   const uint32_t* n_dev = g.point_offsets + (a.P - 1);
+  const uint32_t* veto_dev = presort ? presort_veto_flag(g) : nullptr;
+  slot->host[1] = slot->host[2] = 0u;
   EGS_CUDA_TRY(cudaMemcpyAsync(slot->host, n_dev, sizeof(uint32_t), cudaMemcpyDeviceToHost, stream));
+  if (veto_dev)
+    EGS_CUDA_TRY(cudaMemcpyAsync(slot->host + 1, veto_dev, sizeof(uint32_t), cudaMemcpyDeviceToHost, stream));
+  if (a.prefiltered)
+    EGS_CUDA_TRY(cudaMemcpyAsync(slot->host + 2, g.prefilter_fault, sizeof(uint32_t), cudaMemcpyDeviceToHost, stream));
   EGS_CUDA_TRY(cudaEventRecord(slot->arrived, stream));
 
   // Speculative run: with a caller-provided guess the binning workspace is sized from the guess and
-  // binning + blend are enqueued before the count is known; the kernels read the count on the
-  // device and skip themselves if it does not fit. Only the bucket path takes part.
+  // binning + blend are enqueued before the count is known; the kernels read the count (and the veto)
+  // on the device and skip themselves if it does not fit. Only the bucket path takes part.
   int capacity = 0;
   void* bin_mem = nullptr;
   bool enqueued = false;
-  if (a.num_rendered_hint > 0 && fits && !forced && !a.debug &&
-      bucket_path_ok(a.P, a.num_rendered_hint, a.width, a.height)) {
+  if (a.num_rendered_hint > 0 && !forced && !a.debug &&
+      (presort || bucket_path_ok(a.P, a.num_rendered_hint, a.width, a.height))) {
     capacity = a.num_rendered_hint;
     bin_mem = a.binning_alloc(a.binning_ctx, egs_binning_bytes(capacity, a.width, a.height));
     if (!bin_mem) {
@@ -259,8 +293,9 @@ static int forward_impl(const char* who, const EgsForwardArgs* args, const EgsMo
       return EGS_ERR_ALLOC;
     }
     const BinningPtrs b(bin_mem, (size_t)capacity);
-    const InstanceCount count{n_dev, (uint32_t)capacity};
-    if (int rc = launch_binning_buckets(g, b, im, a.radii, order, a.P, capacity, count, a.width, a.height, stream, false))
+    const InstanceCount count{n_dev, (uint32_t)capacity, veto_dev};
+    if (int rc = launch_binning_buckets(g, b, im, a.radii, order, presort, a.P, capacity, count, a.width, a.height, stream,
+                                        false))
       return rc;
     if (int rc = launch_blend_forward(a, g, b.vals[0], im, stream)) return rc;
     enqueued = true;
@@ -269,16 +304,22 @@ static int forward_impl(const char* who, const EgsForwardArgs* args, const EgsMo
   // wait for the count only (it arrived right after the scan; the GPU keeps working on what was
   // enqueued above)
   EGS_CUDA_TRY(cudaEventSynchronize(slot->arrived));
-  const uint32_t R_host = *slot->host;
+  const uint32_t R_host = slot->host[0];
+  const bool vetoed = presort && slot->host[1] != 0u;
+  if (a.prefiltered && slot->host[2] != 0u) {
+    // the reference prints this and traps the kernel (auxiliary.h:154-161); here it is an error code
+    set_error("%s: Point is filtered although prefiltered is set. This shouldn't happen!", who);
+    return EGS_ERR_PREFILTERED;
+  }
   if (R_host >= (1u << 30)) {
     set_error("%s: num_rendered %u exceeds the supported 2^30", who, R_host);
     return EGS_ERR_TOO_LARGE;
   }
   const int R = (int)R_host;
   *num_rendered = R;
-  if (enqueued && R <= capacity) return EGS_OK;
+  if (enqueued && R <= capacity && !vetoed) return EGS_OK;
 
-  // exact run (no guess, guess too small, forced path, or a path that does not speculate)
+  // exact run (no guess, guess too small, presort vetoed, forced path, or a path that does not speculate)
   bin_mem = a.binning_alloc(a.binning_ctx, egs_binning_bytes(R, a.width, a.height));
   if (!bin_mem) {
     set_error("%s: binning workspace callback returned NULL", who);
@@ -286,19 +327,23 @@ static int forward_impl(const char* who, const EgsForwardArgs* args, const EgsMo
   }
   const BinningPtrs b(bin_mem, (size_t)R);
   // Binning paths, all with identical results:
-  //   buckets  packed words, one global partition on the top tile bits + one CTA per bucket
-  //   packed   packed words, five global onesweep passes (R too large for the bucket sorter)
-  //   pairs    keys + value array through the same onesweep kernel (tile | depth | index does not
-  //            fit one 64-bit word, e.g. more than 1M Gaussians at 1280x720)
+  //   buckets, presorted   tile | index words, one global partition + a register-resident split per bucket
+  //   buckets, full words  tile | depth | index words, one global partition + one CTA sort per bucket
+  //   packed   full words, five global onesweep passes (R too large for the bucket sorter)
+  //   pairs    keys + value array through the same onesweep kernel (the full word does not fit 64 bits
+  //            and the presort is off or gave up)
   //   pairs8   the first, plain 8-bit pair sort of binning.cu, kept as an independent cross-check
-  // EGS_SORT=packed|pairs|pairs8 forces a path (tests, A/B timing).
-  if (force && strcmp(force, "pairs8") == 0) {
+  // `order` stays what the scan ran over in every case (any permutation serves the unsorted paths).
+  const InstanceCount count{n_dev, (uint32_t)R, nullptr};
+  if (dbg.sort == SORT_PAIRS8) {
     if (int rc = launch_binning(g, b, im, a.radii, a.P, R, a.width, a.height, stream, a.debug)) return rc;
-  } else if (!fits || (force && strcmp(force, "pairs") == 0)) {
+  } else if (presort && !vetoed) {
+    if (int rc = launch_binning_buckets(g, b, im, a.radii, order, true, a.P, R, count, a.width, a.height, stream, a.debug))
+      return rc;
+  } else if (!fits || dbg.sort == SORT_PAIRS) {
     if (int rc = launch_binning_packed(g, b, im, a.radii, order, a.P, R, a.width, a.height, true, stream, a.debug)) return rc;
-  } else if (bucket_path_ok(a.P, R, a.width, a.height) && !(force && strncmp(force, "packed", 6) == 0)) {
-    const InstanceCount count{n_dev, (uint32_t)R};
-    if (int rc = launch_binning_buckets(g, b, im, a.radii, order, a.P, R, count, a.width, a.height, stream, a.debug))
+  } else if (bucket_path_ok(a.P, R, a.width, a.height) && dbg.sort != SORT_PACKED) {
+    if (int rc = launch_binning_buckets(g, b, im, a.radii, order, false, a.P, R, count, a.width, a.height, stream, a.debug))
       return rc;
   } else {
     if (int rc = launch_binning_packed(g, b, im, a.radii, order, a.P, R, a.width, a.height, false, stream, a.debug)) return rc;
@@ -400,7 +445,6 @@ extern "C" int egs_backward_raw(const EgsBackwardArgs* args, const EgsModelArgs*
 static __device__ __align__(256) float4 g_static_backward_records[(size_t)EGS_STATIC_SCRATCH_MAX_GAUSSIANS * 3];
 
 namespace {
-constexpr int kMaxDevices = 64;
 std::mutex g_static_scratch_mu;
 void* g_static_scratch_addr[kMaxDevices] = {};   // per device, filled on that device's first call
 }  // namespace
@@ -468,6 +512,50 @@ extern "C" int egs_binning_view(const void* binning_buffer, int R, int W, int H,
   (void)W; (void)H;
   out->keys_sorted = b.keys[0];
   out->values_sorted = b.vals[0];
+  return EGS_OK;
+}
+
+extern "C" int egs_binning_keys(const void* geom_buffer, int P, void* binning_buffer, int R, const void* image_buffer,
+                                int W, int H, void* stream) {
+  if (!geom_buffer || !binning_buffer || !image_buffer || P < 0 || R < 0 || W <= 0 || H <= 0) {
+    set_error("egs_binning_keys: NULL blob or bad size");
+    return EGS_ERR_INVALID_ARGUMENT;
+  }
+  if (P == 0 || R == 0) return EGS_OK;
+  const GeomPtrs g(const_cast<void*>(geom_buffer), (size_t)P);
+  const BinningPtrs b(binning_buffer, (size_t)R);
+  const ImagePtrs im(const_cast<void*>(image_buffer), W, H);
+  return launch_binning_keys(g, im, b.vals[0], b.keys[0], W, H, static_cast<cudaStream_t>(stream));
+}
+
+extern "C" int egs_debug_option(const char* name, const char* value) {
+  if (!name) {
+    set_error("egs_debug_option: NULL name");
+    return EGS_ERR_INVALID_ARGUMENT;
+  }
+  const bool unset = value == nullptr || value[0] == 0;
+  if (strcmp(name, "sort") == 0) {
+    int v = SORT_AUTO;
+    if (!unset) {
+      if (strcmp(value, "packed") == 0) v = SORT_PACKED;
+      else if (strcmp(value, "pairs") == 0) v = SORT_PAIRS;
+      else if (strcmp(value, "pairs8") == 0) v = SORT_PAIRS8;
+      else {
+        set_error("egs_debug_option: sort = packed | pairs | pairs8, got '%s'", value);
+        return EGS_ERR_INVALID_ARGUMENT;
+      }
+    }
+    g_dbg_sort.store(v, std::memory_order_relaxed);
+  } else if (strcmp(name, "presort") == 0) {
+    g_dbg_presort.store(unset ? -1 : (value[0] == '0' ? 0 : 1), std::memory_order_relaxed);
+  } else if (strcmp(name, "presort_scramble") == 0) {
+    g_dbg_scramble.store(unset || value[0] == '0' ? 0 : 1, std::memory_order_relaxed);
+  } else if (strcmp(name, "blend_forward") == 0) {
+    g_dbg_fwd_v2.store(!unset && strcmp(value, "v2") == 0 ? 1 : 0, std::memory_order_relaxed);
+  } else {
+    set_error("egs_debug_option: unknown option '%s'", name);
+    return EGS_ERR_INVALID_ARGUMENT;
+  }
   return EGS_OK;
 }
 

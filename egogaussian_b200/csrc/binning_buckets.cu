@@ -1,30 +1,32 @@
 // binning_buckets.cu -- MSD-bucket binning: one global partition pass on the top tile bits, then
-// every bucket is sorted to completion by ONE CTA in shared memory.
+// every bucket is finished by ONE CTA.
 //
 // Same result as duplicateWithKeys + cub::DeviceRadixSort::SortPairs + identifyTileRanges of the
 // reference (DGR/cuda_rasterizer/rasterizer_impl.cu:70-138, 290-319): the unique ordering by
 // (tile, depth bits, Gaussian index) -- see binning_packed.cu for why that is what a stable sort
 // of the reference's key list produces.
 //
-// Why: at the sizes of this path (R ~ 1e7 packed words, 73 MB -- L2-resident) an LSD radix sort
-// is not bandwidth-bound but serialised by its passes: every onesweep pass chains ~2200 CTAs
-// through a decoupled look-back (ncu: 23-30 % of samples spin there) and all five passes go
-// through global memory. Here only the FIRST digit (the top <= 10 bits of the tile id) is a
-// global pass. It cuts the list into <= 1024 contiguous buckets of a few adjacent tiles each;
-// a bucket (~9k words at 1M Gaussians, 1280x720) fits in shared memory, so the remaining 34-35
-// key bits are sorted by one CTA with four 9-bit LSD passes that never leave the SM and need no
-// cross-CTA protocol. The CTA then holds its tiles completely sorted, so it also emits the
-// per-tile ranges (identifyTileRanges disappears) and the unpacked index list.
-// Global traffic per instance: 8 (duplicate) + 16 (partition) + 8 + 12 (bucket sort in/out)
-// = 44 B instead of ~100 B for five global passes.
+// Why: at the sizes of this path (R ~ 1e7 instances -- L2-resident) an LSD radix sort is not
+// bandwidth-bound but serialised by its passes: every onesweep pass chains a few thousand CTAs
+// through a decoupled look-back and all passes go through global memory. Here only the FIRST digit
+// (the top <= 10 bits of the tile id) is a global pass. It cuts the list into <= 1024 contiguous
+// buckets of a few adjacent tiles each, and one CTA finishes a bucket.
 //
-// Buckets longer than the shared-memory capacity are sorted by the same CTA through global
-// memory (correct, slower); the host picks the pure LSD path instead when R is so large that
-// most buckets would overflow.
+// Two forms of the instance word:
+//   presorted   the Gaussians were put in front-to-back order first (launch_depth_order), the
+//               instances are emitted in that order and every pass is stable, so a word is just
+//               tile | index -- 32 bits when they fit (1M Gaussians at 1280x720: 12 + 20), else 64
+//               -- and a bucket only needs a stable split on the <= 7 tile bits below the bucket
+//               digit (bucket_split_kernel, words in registers). No limit on the number of
+//               Gaussians: the depth never has to share the word with the index.
+//   full        tile | depth bits | index in 64 bits (when they fit); bucket_sort_kernel orders the
+//               remaining 32 + few bits of a bucket with 9-bit LSD passes in shared memory. Used for
+//               small frames, where sorting the Gaussians first costs more than it saves, and when
+//               the presort gave up (a depth outside its 30-bit key range).
+// Either way the CTA that finishes a bucket also writes its tiles' ranges (identifyTileRanges
+// disappears) and the bare index list. The sorted 64-bit keys themselves are not written: no kernel
+// reads them (launch_binning_keys rebuilds them for the parity tests).
 #include "common.cuh"
-
-#include <stdlib.h>
-#include <string.h>
 
 namespace egs {
 
@@ -33,9 +35,13 @@ constexpr int MSD_BINS = 1 << MSD_BITS_MAX;        // 1024
 constexpr int MSD_THREADS = 256;
 constexpr int MSD_WARPS = MSD_THREADS / 32;
 constexpr int MSD_DPT = MSD_BINS / MSD_THREADS;    // digits owned by one thread (4)
-constexpr int MSD_ITEMS = 16;
-constexpr int MSD_TILE = MSD_THREADS * MSD_ITEMS;  // 4096 words per CTA (same as SORT_TILE)
-static_assert(MSD_TILE == SORT_TILE, "status sizing");
+// words per thread of the partition kernel: 32 KB of exchange buffer per CTA either way
+template <typename WORD>
+struct MsdCfg {
+  static constexpr int ITEMS = sizeof(WORD) == 8 ? 16 : 32;
+  static constexpr int TILE = MSD_THREADS * ITEMS;   // 4096 64-bit or 8192 32-bit words per CTA
+};
+static_assert(MsdCfg<uint64_t>::TILE == SORT_TILE, "status sizing");
 static_assert(MSD_BINS <= SORT_STATUS_WORDS, "status sizing");
 
 constexpr int BK_THREADS = 1024;
@@ -74,14 +80,23 @@ __device__ __forceinline__ void count_bucket(uint32_t* s_hist, bool live, uint32
   if (live && (peers & ((1u << lane) - 1u)) == 0u) atomicAdd(&s_hist[bucket], (uint32_t)__popc(peers));
 }
 
+// DEPTH: tile | depth bits | index (64-bit words only); otherwise tile | index
+template <typename WORD, bool DEPTH>
+__device__ __forceinline__ WORD make_word(uint32_t tile, uint32_t dbits, uint32_t idx, int idx_bits) {
+  if (DEPTH) return (WORD)(((uint64_t)tile << (32 + idx_bits)) | ((uint64_t)dbits << idx_bits) | idx);
+  return (WORD)(((WORD)tile << idx_bits) | (WORD)idx);
+}
+
+template <typename WORD, bool DEPTH>
 __global__ void __launch_bounds__(DUP_THREADS)
 duplicate_words_kernel(int P, const float2* __restrict__ means2D, const float* __restrict__ depths,
                        const uint32_t* __restrict__ offsets, const int* __restrict__ radii,
                        const uint32_t* __restrict__ order /* NULL: slot j of the scan is Gaussian j */,
-                       uint64_t* __restrict__ words, int grid_x, int grid_y, int idx_bits,
+                       WORD* __restrict__ words, int grid_x, int grid_y, int idx_bits,
                        InstanceCount count, int bucket_shift, uint32_t* __restrict__ bucket_hist,
                        uint32_t* __restrict__ big_list /* with order: scan slots left to duplicate_big_kernel */,
                        uint32_t* __restrict__ big_count) {
+  static_assert(!DEPTH || sizeof(WORD) == 8, "depth bits need the 64-bit word");
   uint32_t n;
   if (!count.get(n)) return;   // more instances than the buffer holds: write nothing
   __shared__ uint32_t s_hist[MSD_BINS];
@@ -89,7 +104,6 @@ duplicate_words_kernel(int P, const float2* __restrict__ means2D, const float* _
   __syncthreads();
   const unsigned lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   const int groups = (P + 31) / 32;
-  const int tile_shift = 32 + idx_bits;
   for (int group = blockIdx.x * (DUP_THREADS / 32) + warp; group < groups; group += gridDim.x * (DUP_THREADS / 32)) {
     const int slot = group * 32 + (int)lane;
     const bool valid = slot < P;
@@ -103,7 +117,7 @@ duplicate_words_kernel(int P, const float2* __restrict__ means2D, const float* _
       loy = lo.y;
       w = max(hi.x - lo.x, 1u);   // never 0: slots outside the run still divide by it
       cnt = (hi.x - lo.x) * (hi.y - lo.y);
-      dbits = __float_as_uint(depths[idx]);
+      if (DEPTH) dbits = __float_as_uint(depths[idx]);
     }
     // first output slot of this Gaussian; the warp's own runs, big ones taken out, are numbered
     // contiguously (`mine`) and shared evenly between the lanes
@@ -133,14 +147,13 @@ duplicate_words_kernel(int P, const float2* __restrict__ means2D, const float* _
       const uint32_t o_lox = __shfl_sync(0xffffffffu, lox, L);
       const uint32_t o_loy = __shfl_sync(0xffffffffu, loy, L);
       const uint32_t o_w = __shfl_sync(0xffffffffu, w, L);
-      const uint32_t o_d = __shfl_sync(0xffffffffu, dbits, L);
+      const uint32_t o_d = DEPTH ? __shfl_sync(0xffffffffu, dbits, L) : 0u;
       const uint32_t o_idx = __shfl_sync(0xffffffffu, (uint32_t)idx, L);
       const bool live = o < total;
       const uint32_t local = o - o_mine;
       const uint32_t dy = local / o_w;
       const uint32_t tile = (o_loy + dy) * (uint32_t)grid_x + o_lox + (local - dy * o_w);
-      if (live)
-        words[o_start + local] = ((uint64_t)tile << tile_shift) | ((uint64_t)o_d << idx_bits) | o_idx;
+      if (live) words[o_start + local] = make_word<WORD, DEPTH>(tile, o_d, o_idx, idx_bits);
       count_bucket(s_hist, live, tile >> bucket_shift, lane);
     }
   }
@@ -153,10 +166,11 @@ duplicate_words_kernel(int P, const float2* __restrict__ means2D, const float* _
 
 // The Gaussians duplicate_words_kernel set aside: one CTA per Gaussian at a time, its words shared
 // between the 256 threads.
+template <typename WORD, bool DEPTH>
 __global__ void __launch_bounds__(DUP_THREADS)
 duplicate_big_kernel(const float2* __restrict__ means2D, const float* __restrict__ depths,
                      const uint32_t* __restrict__ offsets, const int* __restrict__ radii,
-                     const uint32_t* __restrict__ order, uint64_t* __restrict__ words, int grid_x, int grid_y,
+                     const uint32_t* __restrict__ order, WORD* __restrict__ words, int grid_x, int grid_y,
                      int idx_bits, InstanceCount count, int bucket_shift, uint32_t* __restrict__ bucket_hist,
                      const uint32_t* __restrict__ big_list, const uint32_t* __restrict__ big_count) {
   uint32_t n;
@@ -167,7 +181,6 @@ duplicate_big_kernel(const float2* __restrict__ means2D, const float* __restrict
   for (int i = threadIdx.x; i < MSD_BINS; i += DUP_THREADS) s_hist[i] = 0;
   __syncthreads();
   const unsigned lane = threadIdx.x & 31;
-  const int tile_shift = 32 + idx_bits;
   for (uint32_t b = blockIdx.x; b < n_big; b += gridDim.x) {
     const uint32_t slot = big_list[b];
     const uint32_t idx = order[slot];
@@ -175,12 +188,12 @@ duplicate_big_kernel(const float2* __restrict__ means2D, const float* __restrict
     tile_rect(means2D[idx], radii[idx], grid_x, grid_y, lo, hi);
     const uint32_t w = hi.x - lo.x, cnt = w * (hi.y - lo.y);
     const uint32_t start = offsets[slot] - cnt;
-    const uint64_t low = ((uint64_t)__float_as_uint(depths[idx]) << idx_bits) | idx;
+    const uint32_t dbits = DEPTH ? __float_as_uint(depths[idx]) : 0u;
     for (uint32_t t = threadIdx.x; t - threadIdx.x < cnt; t += DUP_THREADS) {   // CTA-uniform trip count
       const bool live = t < cnt;
       const uint32_t dy = t / w;
       const uint32_t tile = (lo.y + dy) * (uint32_t)grid_x + lo.x + (t - dy * w);
-      if (live) words[start + t] = ((uint64_t)tile << tile_shift) | low;
+      if (live) words[start + t] = make_word<WORD, DEPTH>(tile, dbits, idx, idx_bits);
       count_bucket(s_hist, live, tile >> bucket_shift, lane);
     }
   }
@@ -193,8 +206,7 @@ duplicate_big_kernel(const float2* __restrict__ means2D, const float* __restrict
 
 // exclusive scan of the bucket histogram; start[MSD_BINS] = total
 __global__ void __launch_bounds__(MSD_BINS)
-bucket_scan_kernel(const uint32_t* __restrict__ hist, uint32_t* __restrict__ start,
-                   uint32_t* __restrict__ order, uint32_t* __restrict__ work_count, uint32_t listed) {
+bucket_scan_kernel(const uint32_t* __restrict__ hist, uint32_t* __restrict__ start) {
   __shared__ uint32_t s_w[MSD_BINS / 32];
   const uint32_t v = hist[threadIdx.x];
   const unsigned lane = lane_id(), warp = threadIdx.x >> 5;
@@ -210,14 +222,6 @@ bucket_scan_kernel(const uint32_t* __restrict__ hist, uint32_t* __restrict__ sta
   for (unsigned w = 0; w < warp; ++w) woff += s_w[w];
   start[threadIdx.x] = woff + incl - v;
   if (threadIdx.x == MSD_BINS - 1) start[MSD_BINS] = woff + incl;
-
-  // order[k] = bucket handled by CTA k of the sorter. Largest-first scheduling (a bitonic sort of
-  // the counts here) was measured: no gain at ~7 waves of similar buckets, and the sort itself cost
-  // 6 us on the critical path, so the order is the identity.
-  // With the presort, bucket_split_kernel takes the buckets that fit it and lists the others here
-  // (`listed` = 0: the list starts empty).
-  order[threadIdx.x] = threadIdx.x;
-  if (threadIdx.x == 0) *work_count = listed;
 }
 
 // ---------------------------------------------------------------------------------------------
@@ -227,20 +231,16 @@ constexpr uint32_t MSD_FLAG_AGG = 1u << 30;
 constexpr uint32_t MSD_FLAG_PREFIX = 1u << 31;
 constexpr uint32_t MSD_VALUE_MASK = (1u << 30) - 1u;
 
+template <typename WORD>
 struct MsdSmem {
-  uint16_t warp_hist[MSD_WARPS][MSD_BINS];   // 16 KB (a warp holds at most 512 items)
-  uint64_t exch[MSD_TILE];                   // 32 KB
-  uint16_t digit_local[MSD_BINS];            // first slot of each digit in exch (< MSD_TILE)
+  uint16_t warp_hist[MSD_WARPS][MSD_BINS];   // 16 KB (a warp holds at most 1024 items)
+  WORD exch[MsdCfg<WORD>::TILE];             // 32 KB
+  uint16_t digit_local[MSD_BINS];            // first slot of each digit in exch (< TILE)
   uint32_t digit_global[MSD_BINS];
   uint32_t warp_sums[MSD_WARPS];
   uint32_t tile;
 };
 
-__device__ __forceinline__ uint32_t ld_relaxed_u32(const uint32_t* p) {
-  uint32_t v;
-  asm volatile("ld.relaxed.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
-  return v;
-}
 // four adjacent status words in one request (each word is read atomically; the vector as a whole
 // need not be)
 __device__ __forceinline__ uint4 ld_relaxed_v4(const uint32_t* p) {
@@ -253,25 +253,25 @@ __device__ __forceinline__ void st_relaxed_v4(uint32_t* p, uint4 v) {
   asm volatile("st.relaxed.gpu.global.v4.u32 [%0], {%1, %2, %3, %4};" ::"l"(p), "r"(v.x), "r"(v.y), "r"(v.z), "r"(v.w)
                : "memory");
 }
-__device__ __forceinline__ void st_relaxed_u32(uint32_t* p, uint32_t v) {
-  asm volatile("st.relaxed.gpu.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
-}
 
-// 256 threads x 16 words: the fixed per-CTA work (clearing and scanning the per-warp counters,
-// the look-back) is shared by 16 words per thread instead of 4 (the first version ran 1024 threads
-// x 4 words and spent more instructions on that bookkeeping than on the words). A thread owns
-// four adjacent digits and walks their four look-back chains together.
+// 256 threads x 16 (64-bit) or 32 (32-bit) words: the fixed per-CTA work (clearing and scanning the
+// per-warp counters, the look-back) is shared by many words per thread (the first version ran 1024
+// threads x 4 words and spent more instructions on that bookkeeping than on the words), and the
+// 32-bit form halves both the bytes and the length of the look-back chain. A thread owns four
+// adjacent digits and walks their four look-back chains together.
 // The digit is (word >> shift) & mask: the top bits of the word for the bucket partition (mask all
 // ones), any 10-bit field for the stable LSD passes of the depth presort. EMIT_IDX: the pass writes
 // only the low index bits of every word, as 32-bit values (last pass of the presort).
-template <bool EMIT_IDX>
+template <typename WORD, bool EMIT_IDX>
 __global__ void __launch_bounds__(MSD_THREADS, 3)
-msd_partition_kernel(const uint64_t* __restrict__ in, uint64_t* __restrict__ out, InstanceCount count,
+msd_partition_kernel(const WORD* __restrict__ in, WORD* __restrict__ out, InstanceCount count,
                      int shift, uint32_t mask, const uint32_t* __restrict__ bucket_start,
                      uint32_t* __restrict__ ticket, uint32_t* __restrict__ status_raw,
                      uint32_t* __restrict__ out_idx, uint32_t idx_mask) {
+  constexpr int ITEMS = MsdCfg<WORD>::ITEMS;
+  constexpr int TILE = MsdCfg<WORD>::TILE;
   extern __shared__ __align__(16) unsigned char smem_raw[];
-  MsdSmem& S = *reinterpret_cast<MsdSmem*>(smem_raw);
+  MsdSmem<WORD>& S = *reinterpret_cast<MsdSmem<WORD>*>(smem_raw);
   uint32_t n;
   if (!count.get(n)) return;   // the guessed capacity was too small: forward re-runs this stage
   const unsigned tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
@@ -285,21 +285,21 @@ msd_partition_kernel(const uint64_t* __restrict__ in, uint64_t* __restrict__ out
   __syncthreads();
   const uint32_t tile = S.tile;
   const unsigned lt_mask = (1u << lane) - 1u;
-  const size_t block_base = (size_t)tile * MSD_TILE;
+  const size_t block_base = (size_t)tile * TILE;
   // the grid is sized for the capacity; CTAs whose tile lies beyond the real count have nothing to
   // do and nobody looks back at them (look-backs only walk towards tile 0)
   if (block_base >= (size_t)n) return;
-  const size_t warp_base = block_base + (size_t)warp * (32 * MSD_ITEMS);
+  const size_t warp_base = block_base + (size_t)warp * (32 * ITEMS);
 
-  uint64_t word[MSD_ITEMS];
-  uint16_t rank[MSD_ITEMS];
+  WORD word[ITEMS];
+  uint32_t rank2[ITEMS / 2];   // two 16-bit ranks per register
 #pragma unroll
-  for (int i = 0; i < MSD_ITEMS; ++i) {
+  for (int i = 0; i < ITEMS; ++i) {
     const size_t g = warp_base + (size_t)i * 32 + lane;
-    word[i] = g < (size_t)n ? in[g] : ~0ull;
+    word[i] = g < (size_t)n ? in[g] : ~(WORD)0;
   }
 #pragma unroll
-  for (int i = 0; i < MSD_ITEMS; ++i) {
+  for (int i = 0; i < ITEMS; ++i) {
     const size_t g = warp_base + (size_t)i * 32 + lane;
     const bool ok = g < (size_t)n;
     const uint32_t d = (uint32_t)(word[i] >> shift) & mask;
@@ -308,7 +308,8 @@ msd_partition_kernel(const uint64_t* __restrict__ in, uint64_t* __restrict__ out
     __syncwarp();
     if (ok && (peers & lt_mask) == 0u) S.warp_hist[warp][d] = (uint16_t)(before + __popc(peers));
     __syncwarp();
-    rank[i] = (uint16_t)(before + __popc(peers & lt_mask));
+    const uint32_t rk = before + __popc(peers & lt_mask);
+    if (i & 1) rank2[i / 2] |= rk << 16; else rank2[i / 2] = rk;
   }
   __syncthreads();
   {
@@ -383,20 +384,21 @@ msd_partition_kernel(const uint64_t* __restrict__ in, uint64_t* __restrict__ out
   }
   __syncthreads();
 #pragma unroll
-  for (int i = 0; i < MSD_ITEMS; ++i) {
+  for (int i = 0; i < ITEMS; ++i) {
     const size_t g = warp_base + (size_t)i * 32 + lane;
     if (g < (size_t)n) {
       const uint32_t d = (uint32_t)(word[i] >> shift) & mask;
-      S.exch[S.digit_local[d] + S.warp_hist[warp][d] + rank[i]] = word[i];
+      const uint32_t rk = (i & 1) ? rank2[i / 2] >> 16 : rank2[i / 2] & 0xffffu;
+      S.exch[S.digit_local[d] + S.warp_hist[warp][d] + rk] = word[i];
     }
   }
   __syncthreads();
-  const uint32_t valid = (uint32_t)min((size_t)MSD_TILE, (size_t)n - block_base);
+  const uint32_t valid = (uint32_t)min((size_t)TILE, (size_t)n - block_base);
 #pragma unroll
-  for (int m = 0; m < MSD_ITEMS; ++m) {
+  for (int m = 0; m < ITEMS; ++m) {
     const uint32_t k = m * MSD_THREADS + tid;
     if (k < valid) {
-      const uint64_t w = S.exch[k];
+      const WORD w = S.exch[k];
       const uint32_t dst = S.digit_global[(uint32_t)(w >> shift) & mask] + k;
       if (EMIT_IDX)
         out_idx[dst] = (uint32_t)w & idx_mask;
@@ -424,7 +426,6 @@ static_assert(sizeof(uint32_t) * BK_WARPS * BK_RADIX <= sizeof(uint64_t) * BK_CA
 // scanned, then the item is placed at digit start + warp offset + rank.
 constexpr int BK_ROUNDS = ((BK_CAP + BK_WARPS - 1) / BK_WARPS + 31) / 32;   // 12
 
-template <bool HWMATCH>   // true: match.any instruction; false: one ballot per digit bit
 __device__ __forceinline__ void bucket_pass_smem(BucketSmem& S, int cur /* source buffer 0 | 1 */, uint32_t n,
                                                  int shift, uint32_t mask) {
   // indexed through S so that the compiler knows both buffers are shared memory (LDS / STS instead
@@ -450,8 +451,8 @@ __device__ __forceinline__ void bucket_pass_smem(BucketSmem& S, int cur /* sourc
       const uint32_t i = row + lane;
       const bool ok = i < end;
       const uint32_t d = ok ? (uint32_t)(A[i] >> shift) & mask : 0u;
-      const uint32_t peers = HWMATCH ? __match_any_sync(0xffffffffu, ok ? d : (0x10000u + lane))
-                                     : match_digit<BK_BITS>(d, ok);
+      // the sorter is issue-bound: match.any measured 12 % faster than one ballot per digit bit
+      const uint32_t peers = __match_any_sync(0xffffffffu, ok ? d : (0x10000u + lane));
       const uint32_t before = ok ? hist[warp * BK_RADIX + d] : 0u;
       __syncwarp();
       if (ok && (peers & lt_mask) == 0u) hist[warp * BK_RADIX + d] = (uint16_t)(before + __popc(peers));
@@ -562,11 +563,10 @@ __device__ __forceinline__ void bucket_pass(BucketSmem& S, CNT* hist, const uint
   __syncthreads();
 }
 
-template <bool HWMATCH>
 __device__ __forceinline__ void sort_one_bucket(BucketSmem& S, const uint32_t bucket, uint64_t* __restrict__ words,
                                                 uint64_t* __restrict__ scratch, const uint32_t* __restrict__ bucket_start,
                                                 uint32_t* __restrict__ point_list, uint2* __restrict__ ranges, int n_tiles,
-                                                int idx_bits, int bucket_shift, int rem_bits, int first_bit) {
+                                                int idx_bits, int bucket_shift, int rem_bits) {
   const uint32_t seg = bucket_start[bucket];
   const uint32_t n = bucket_start[bucket + 1] - seg;
   const unsigned tid = threadIdx.x;
@@ -590,12 +590,12 @@ __device__ __forceinline__ void sort_one_bucket(BucketSmem& S, const uint32_t bu
   }
   __syncthreads();
 
-  const int passes = (rem_bits - first_bit + BK_BITS - 1) / BK_BITS;
+  const int passes = (rem_bits + BK_BITS - 1) / BK_BITS;
   for (int p = 0; p < passes; ++p) {
-    const int shift = idx_bits + first_bit + p * BK_BITS;
-    const int width = min(BK_BITS, rem_bits - first_bit - p * BK_BITS);
+    const int shift = idx_bits + p * BK_BITS;
+    const int width = min(BK_BITS, rem_bits - p * BK_BITS);
     if (in_smem)
-      bucket_pass_smem<HWMATCH>(S, p & 1, n, shift, (1u << width) - 1u);
+      bucket_pass_smem(S, p & 1, n, shift, (1u << width) - 1u);
     else
       bucket_pass<uint32_t>(S, reinterpret_cast<uint32_t*>(&S.buf[0][0]), A, B, n, shift, (1u << width) - 1u);
     uint64_t* t = A;
@@ -621,133 +621,190 @@ __device__ __forceinline__ void sort_one_bucket(BucketSmem& S, const uint32_t bu
     }
     if (i == n - 1) ranges[tile].y = seg + n;
   }
-  __syncthreads();   // every A[i - 1] has been read before the in-place overwrite below
-  for (uint32_t i = tid; i < n; i += BK_THREADS) words[seg + i] = A[i] >> idx_bits;
 }
 
-// CTA k takes the buckets order[k], order[k + gridDim.x], ... of the first *work_count entries: all 1024
-// buckets with one CTA each, or the few that bucket_split_kernel left over.
-template <bool HWMATCH>
+// Full words (tile | depth bits | index): CTA b sorts bucket b on every key bit below the bucket digit.
 __global__ void __launch_bounds__(BK_THREADS)
-bucket_sort_kernel(uint64_t* __restrict__ words /* partitioned; receives the sorted keys in place */,
+bucket_sort_kernel(uint64_t* __restrict__ words /* partitioned */,
                    uint64_t* __restrict__ scratch /* other ping-pong buffer (overflow buckets) */,
-                   const uint32_t* __restrict__ bucket_start, const uint32_t* __restrict__ order,
-                   const uint32_t* __restrict__ work_count, uint32_t* __restrict__ point_list,
+                   const uint32_t* __restrict__ bucket_start, uint32_t* __restrict__ point_list,
                    uint2* __restrict__ ranges, int n_tiles, int idx_bits, int bucket_shift,
-                   int rem_bits /* key bits below the bucket digit */,
-                   int first_bit /* key bits below this one are in order already (32: presorted by depth) */,
-                   const uint32_t* __restrict__ presort_veto /* NULL, or a flag: nonzero = sort all the bits after all */) {
+                   int rem_bits /* key bits below the bucket digit */) {
   extern __shared__ __align__(16) unsigned char smem_raw[];
   BucketSmem& S = *reinterpret_cast<BucketSmem*>(smem_raw);
-  if (presort_veto && *presort_veto) first_bit = 0;
-  const uint32_t count = *work_count;
-  for (uint32_t k = blockIdx.x; k < count; k += gridDim.x) {
-    sort_one_bucket<HWMATCH>(S, order[k], words, scratch, bucket_start, point_list, ranges, n_tiles, idx_bits,
-                             bucket_shift, rem_bits, first_bit);
-    __syncthreads();   // shared buffers are free for the next bucket
-  }
+  // (a frame whose instances did not fit, or whose presort gave up, has an all-zero bucket histogram:
+  // every bucket is empty and the tile ranges come out (0, 0), so the blend that was enqueued behind
+  // this kernel draws the background and forward re-runs the stage)
+  sort_one_bucket(S, blockIdx.x, words, scratch, bucket_start, point_list, ranges, n_tiles, idx_bits, bucket_shift,
+                  rem_bits);
 }
 
-// ---------------------------------------------------------------------------------------------
-// host side
-// ---------------------------------------------------------------------------------------------
 // ---------------------------------------------------------------------------------------------
 // presorted buckets: a stable split on the tile bits, words in registers
 // ---------------------------------------------------------------------------------------------
 // After the depth presort a bucket only has to be split by the BITS tile bits below the bucket digit.
 // That needs no staging in shared memory: a thread keeps its (at most 24) words in registers, a warp
-// counts the 2^BITS bins with one ballot each while ranking, the per-warp counts are scanned in a few
-// hundred bytes of shared memory, and index list, keys and tile ranges go straight to global memory.
-// Two CTAs fit an SM, where bucket_sort_kernel's two 96 KB buffers allow one (0.090 -> 0.061 ms at C3).
-// Buckets beyond BK_CAP words, wider splits and vetoed frames stay with bucket_sort_kernel.
+// ranks them (one ballot per bin for up to 8 bins, match.any with per-warp counters beyond that), the
+// per-warp counts are scanned in a few hundred bytes of shared memory, and index list and tile ranges
+// go straight to global memory. Two CTAs fit an SM, where bucket_sort_kernel's two 96 KB buffers
+// allow one (0.090 -> 0.061 ms at C3).
+// A bucket longer than one chunk (SplitCfg) is taken in chunks: a counting sweep first gives the bin sizes,
+// then every chunk is ranked as above on top of the running bin offsets. So there is no limit on the
+// bucket size (R = 25M instances at 6M Gaussians make every bucket exceed one chunk).
 constexpr int BS_THREADS = 512;
 constexpr int BS_WARPS = BS_THREADS / 32;
-constexpr int BS_ROUNDS = BK_CAP / BS_THREADS;   // 24
-constexpr int BS_MAX_BITS = 3;
-static_assert(BS_ROUNDS * BS_THREADS == BK_CAP, "capacity");
+// words a thread holds per chunk: 24 32-bit or 16 64-bit ones (64 registers per thread at two CTAs per SM)
+template <typename WORD>
+struct SplitCfg {
+  static constexpr int ROUNDS = sizeof(WORD) == 8 ? 16 : 24;
+  static constexpr int CHUNK = BS_THREADS * ROUNDS;   // 12288 or 8192
+};
+constexpr int BS_MAX_BITS = 7;                      // up to 2^17 tiles (8192 x 4096 pixels)
 
-template <int BITS>
+template <typename WORD, int BITS>
 __global__ void __launch_bounds__(BS_THREADS, 2)
-bucket_split_kernel(uint64_t* __restrict__ words /* partitioned; receives the sorted keys in place */,
-                    const uint32_t* __restrict__ bucket_start, uint32_t* __restrict__ point_list,
-                    uint2* __restrict__ ranges, int n_tiles, int idx_bits, const uint32_t* __restrict__ presort_veto,
-                    uint32_t* __restrict__ leftover /* buckets for bucket_sort_kernel */, uint32_t* __restrict__ leftover_count) {
+bucket_split_kernel(const WORD* __restrict__ words /* partitioned */, const uint32_t* __restrict__ bucket_start,
+                    uint32_t* __restrict__ point_list, uint2* __restrict__ ranges, int n_tiles, int idx_bits) {
   constexpr int BINS = 1 << BITS;
+  constexpr bool BALLOT = BITS <= 3;
+  constexpr int BS_ROUNDS = SplitCfg<WORD>::ROUNDS;
+  constexpr int BS_CHUNK = SplitCfg<WORD>::CHUNK;
   __shared__ uint32_t s_warp[BS_WARPS][BINS];   // per-warp counts, then exclusive offsets inside the bin
-  __shared__ uint32_t s_bin[BINS + 1];          // first slot of every bin
+  __shared__ uint32_t s_bin[BINS + 1];          // first slot of every bin in the bucket
+  __shared__ uint32_t s_tot[BINS];              // size of every bin
+  __shared__ uint32_t s_run[BINS];              // words of earlier chunks in every bin
+  // (skipped frames arrive here with an all-zero bucket histogram: see bucket_sort_kernel)
   const uint32_t bucket = blockIdx.x;
   const uint32_t seg = bucket_start[bucket];
   const uint32_t n = bucket_start[bucket + 1] - seg;
   const unsigned tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-  if (*presort_veto || n > (uint32_t)BK_CAP) {
-    if (tid == 0) leftover[atomicAdd(leftover_count, 1u)] = bucket;
-    return;
-  }
   const unsigned lt_mask = (1u << lane) - 1u;
-  const uint32_t chunk = ((n + BS_WARPS - 1) / BS_WARPS + 31u) & ~31u;   // per warp, multiple of 32
-  const uint32_t begin = warp * chunk;
-  const uint32_t end = min(n, begin + chunk);
-  const int tile_shift = idx_bits + 32;
-
-  uint64_t w[BS_ROUNDS];
-#pragma unroll
-  for (int r = 0; r < BS_ROUNDS; ++r) {
-    const uint32_t i = begin + r * 32 + lane;
-    w[r] = i < end ? words[seg + i] : ~0ull;
+  const uint32_t idx_mask = (uint32_t)((1ull << idx_bits) - 1ull);
+  for (int i = tid; i < BINS; i += BS_THREADS) {
+    s_tot[i] = 0u;
+    s_run[i] = 0u;
   }
-  uint32_t cnt[BINS];
+  __syncthreads();
+  const uint32_t chunks = (n + BS_CHUNK - 1) / BS_CHUNK;
+  if (chunks > 1) {   // counting sweep (CTA-uniform)
+    uint32_t c = 0;
+    for (uint32_t base = warp * 32; base < n; base += BS_THREADS) {   // warp-uniform trip count
+      const uint32_t i = base + lane;
+      const bool ok = i < n;
+      const uint32_t d = ok ? (uint32_t)(words[seg + i] >> idx_bits) & (BINS - 1) : 0u;
+      if (BALLOT) {
 #pragma unroll
-  for (int b = 0; b < BINS; ++b) cnt[b] = 0;
-  uint16_t rank[BS_ROUNDS];
-#pragma unroll
-  for (int r = 0; r < BS_ROUNDS; ++r) {
-    rank[r] = 0;
-    if (begin + r * 32 < end) {   // warp-uniform
-      const bool ok = begin + r * 32 + lane < end;
-      const uint32_t d = (uint32_t)(w[r] >> tile_shift) & (BINS - 1);
-#pragma unroll
-      for (int b = 0; b < BINS; ++b) {
-        const uint32_t m = __ballot_sync(0xffffffffu, ok && d == (uint32_t)b);
-        if (d == (uint32_t)b) rank[r] = (uint16_t)(cnt[b] + __popc(m & lt_mask));
-        cnt[b] += __popc(m);
+        for (int b = 0; b < BINS; ++b) {
+          const uint32_t m = __ballot_sync(0xffffffffu, ok && d == (uint32_t)b);
+          if (lane == (unsigned)b) c += __popc(m);
+        }
+      } else if (ok) {
+        atomicAdd(&s_tot[d], 1u);
       }
     }
+    if (BALLOT && lane < BINS && c) atomicAdd(&s_tot[lane], c);
+    __syncthreads();
   }
-#pragma unroll
-  for (int b = 0; b < BINS; ++b)
-    if (lane == (unsigned)b) s_warp[warp][b] = cnt[b];
-  __syncthreads();   // also: every word of the bucket is in a register before anything is overwritten
-  if (tid < BINS) {
-    uint32_t run = 0;
-#pragma unroll
-    for (int q = 0; q < BS_WARPS; ++q) {
-      const uint32_t c = s_warp[q][tid];
-      s_warp[q][tid] = run;
-      run += c;
+  if (chunks != 1) {   // bin starts known up front (no words at all: all zero)
+    if (tid == 0) {
+      uint32_t run = 0;
+      for (int b = 0; b < BINS; ++b) {
+        s_bin[b] = run;
+        run += s_tot[b];
+      }
+      s_bin[BINS] = run;
     }
-    s_bin[tid + 1] = run;   // bin totals for now
+    __syncthreads();
   }
-  __syncthreads();
-  if (tid == 0) {
-    uint32_t run = 0;
-    s_bin[0] = 0;
+
+  for (uint32_t ch = 0; ch < chunks; ++ch) {
+    const uint32_t c0 = ch * BS_CHUNK;
+    const uint32_t nc = min((uint32_t)BS_CHUNK, n - c0);
+    const uint32_t per_warp = ((nc + BS_WARPS - 1) / BS_WARPS + 31u) & ~31u;   // multiple of 32, <= 32 * ROUNDS
+    const uint32_t begin = warp * per_warp;
+    const uint32_t end = min(nc, begin + per_warp);
+    const WORD* src = words + seg + c0;
+
+    WORD w[BS_ROUNDS];
 #pragma unroll
-    for (int b = 0; b < BINS; ++b) {
-      run += s_bin[b + 1];
-      s_bin[b + 1] = run;
+    for (int r = 0; r < BS_ROUNDS; ++r) {
+      const uint32_t i = begin + r * 32 + lane;
+      w[r] = i < end ? src[i] : ~(WORD)0;
     }
-  }
-  __syncthreads();
-  const uint64_t idx_mask = (1ull << idx_bits) - 1ull;
+    uint32_t rank2[BS_ROUNDS / 2];   // two 16-bit ranks per register
+    uint32_t cnt[BALLOT ? BINS : 1];
+    if (BALLOT) {
 #pragma unroll
-  for (int r = 0; r < BS_ROUNDS; ++r) {
-    const uint32_t i = begin + r * 32 + lane;
-    if (i < end) {
-      const uint32_t d = (uint32_t)(w[r] >> tile_shift) & (BINS - 1);
-      const uint32_t dst = seg + s_bin[d] + s_warp[warp][d] + rank[r];
-      point_list[dst] = (uint32_t)(w[r] & idx_mask);
-      words[dst] = w[r] >> idx_bits;
+      for (int b = 0; b < BINS; ++b) cnt[b] = 0;
+    } else {
+      for (int b = lane; b < BINS; b += 32) s_warp[warp][b] = 0u;
+      __syncwarp();
     }
+#pragma unroll
+    for (int r = 0; r < BS_ROUNDS; ++r) {
+      uint32_t rk = 0;
+      if (begin + r * 32 < end) {   // warp-uniform
+        const bool ok = begin + r * 32 + lane < end;
+        const uint32_t d = (uint32_t)(w[r] >> idx_bits) & (BINS - 1);
+        if (BALLOT) {
+#pragma unroll
+          for (int b = 0; b < BINS; ++b) {
+            const uint32_t m = __ballot_sync(0xffffffffu, ok && d == (uint32_t)b);
+            if (d == (uint32_t)b) rk = cnt[b] + __popc(m & lt_mask);
+            cnt[b] += __popc(m);
+          }
+        } else {
+          const uint32_t peers = __match_any_sync(0xffffffffu, ok ? d : (0x10000u + lane));
+          const uint32_t before = ok ? s_warp[warp][d] : 0u;
+          __syncwarp();
+          if (ok && (peers & lt_mask) == 0u) s_warp[warp][d] = before + __popc(peers);
+          __syncwarp();
+          rk = before + __popc(peers & lt_mask);
+        }
+      }
+      if (r & 1) rank2[r / 2] |= rk << 16; else rank2[r / 2] = rk;
+    }
+    if (BALLOT) {
+#pragma unroll
+      for (int b = 0; b < BINS; ++b)
+        if (lane == (unsigned)b) s_warp[warp][b] = cnt[b];
+    }
+    __syncthreads();   // also: the previous chunk's scatter is over before s_run moves
+    uint32_t chunk_total = 0;
+    if (tid < BINS) {
+      uint32_t run = 0;
+#pragma unroll
+      for (int q = 0; q < BS_WARPS; ++q) {
+        const uint32_t c = s_warp[q][tid];
+        s_warp[q][tid] = run;
+        run += c;
+      }
+      chunk_total = run;
+      if (chunks == 1) s_tot[tid] = run;
+    }
+    __syncthreads();
+    if (chunks == 1) {
+      if (tid == 0) {
+        uint32_t run = 0;
+        for (int b = 0; b < BINS; ++b) {
+          s_bin[b] = run;
+          run += s_tot[b];
+        }
+        s_bin[BINS] = run;
+      }
+      __syncthreads();
+    }
+#pragma unroll
+    for (int r = 0; r < BS_ROUNDS; ++r) {
+      const uint32_t i = begin + r * 32 + lane;
+      if (i < end) {
+        const uint32_t d = (uint32_t)(w[r] >> idx_bits) & (BINS - 1);
+        const uint32_t rk = (r & 1) ? rank2[r / 2] >> 16 : rank2[r / 2] & 0xffffu;
+        point_list[seg + s_bin[d] + s_run[d] + s_warp[warp][d] + rk] = (uint32_t)w[r] & idx_mask;
+      }
+    }
+    __syncthreads();
+    if (tid < BINS) s_run[tid] += chunk_total;
   }
   // bin b is tile (bucket << BITS) | b; empty tiles read (0, 0) like the reference's zero fill
   if (tid < BINS) {
@@ -756,6 +813,18 @@ bucket_split_kernel(uint64_t* __restrict__ words /* partitioned; receives the so
       const uint32_t lo = s_bin[tid], hi = s_bin[tid + 1];
       ranges[tile] = hi > lo ? make_uint2(seg + lo, seg + hi) : make_uint2(0u, 0u);
     }
+  }
+}
+
+// keys[i] = tile << 32 | depth bits of the Gaussian at position i of the sorted list: what the
+// reference's sorted key array holds (rasterizer_impl.cu:301-309). Nothing on the path reads it.
+__global__ void __launch_bounds__(256)
+binning_keys_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__ point_list,
+                    const float* __restrict__ depths, uint64_t* __restrict__ keys, int n_tiles) {
+  for (int t = blockIdx.x; t < n_tiles; t += gridDim.x) {
+    const uint2 r = ranges[t];
+    for (uint32_t i = r.x + threadIdx.x; i < r.y; i += 256)
+      keys[i] = ((uint64_t)t << 32) | __float_as_uint(depths[point_list[i]]);
   }
 }
 
@@ -826,54 +895,115 @@ depth_scan_kernel(const uint32_t* __restrict__ hist, uint32_t* __restrict__ star
   start[blockIdx.x * MSD_BINS + threadIdx.x] = woff + incl - v;
 }
 
+const uint32_t* presort_veto_flag(const GeomPtrs& g) { return g.sort_aux + DO_META + 3; }
+
 int launch_depth_order(const GeomPtrs& g, int P, const int* radii, cudaStream_t stream, bool debug) {
   StageTimer timer(stream, ST_DEPTH_ORDER);
   uint32_t* aux = g.sort_aux;
   const int ib = tile_id_bits((uint32_t)(P > 1 ? P - 1 : 1));
   EGS_CUDA_TRY(cudaMemsetAsync(aux, 0, g.sort_aux_bytes, stream));
   const int blocks = P < 148 * 4 * 256 ? (P + 255) / 256 : 148 * 4;
-  // EGS_PRESORT_DEBUG=scramble exercises the veto: an order unrelated to depth, full sort downstream
-  const char* dbg = getenv("EGS_PRESORT_DEBUG");
-  const bool scramble = dbg && strcmp(dbg, "scramble") == 0;
+  // test hook (egs_debug_option "presort_scramble"): an order unrelated to depth + the veto raised
+  const bool scramble = debug_options().presort_scramble != 0;
   depth_words_kernel<<<blocks, 256, 0, stream>>>(P, g.depths, radii, ib, g.sort_keys[0], aux + DO_HIST, aux + DO_META,
                                                  scramble);
   EGS_AFTER_LAUNCH(stream, debug);
   depth_scan_kernel<<<3, MSD_BINS, 0, stream>>>(aux + DO_HIST, aux + DO_START);
   EGS_AFTER_LAUNCH(stream, debug);
-  EGS_CUDA_TRY(cudaFuncSetAttribute(msd_partition_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                    (int)sizeof(MsdSmem)));
-  EGS_CUDA_TRY(cudaFuncSetAttribute(msd_partition_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                    (int)sizeof(MsdSmem)));
-  const InstanceCount count{aux + DO_META + 2, (uint32_t)P};
+  constexpr int SMEM = (int)sizeof(MsdSmem<uint64_t>);
+  EGS_CUDA_TRY(cudaFuncSetAttribute(msd_partition_kernel<uint64_t, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM));
+  EGS_CUDA_TRY(cudaFuncSetAttribute(msd_partition_kernel<uint64_t, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM));
+  const InstanceCount count{aux + DO_META + 2, (uint32_t)P, nullptr};
   const int grid = (int)g.sort_blocks;
   const size_t status_stride = g.sort_blocks * MSD_BINS;
-  msd_partition_kernel<false><<<grid, MSD_THREADS, sizeof(MsdSmem), stream>>>(
+  msd_partition_kernel<uint64_t, false><<<grid, MSD_THREADS, SMEM, stream>>>(
       g.sort_keys[0], g.sort_keys[1], count, ib, MSD_BINS - 1, aux + DO_START, aux + DO_TICKET, aux + DO_STATUS,
       nullptr, 0u);
   EGS_AFTER_LAUNCH(stream, debug);
-  msd_partition_kernel<false><<<grid, MSD_THREADS, sizeof(MsdSmem), stream>>>(
+  msd_partition_kernel<uint64_t, false><<<grid, MSD_THREADS, SMEM, stream>>>(
       g.sort_keys[1], g.sort_keys[0], count, ib + 10, MSD_BINS - 1, aux + DO_START + MSD_BINS, aux + DO_TICKET + 1,
       aux + DO_STATUS + status_stride, nullptr, 0u);
   EGS_AFTER_LAUNCH(stream, debug);
-  msd_partition_kernel<true><<<grid, MSD_THREADS, sizeof(MsdSmem), stream>>>(
+  msd_partition_kernel<uint64_t, true><<<grid, MSD_THREADS, SMEM, stream>>>(
       g.sort_keys[0], nullptr, count, ib + 20, MSD_BINS - 1, aux + DO_START + 2 * MSD_BINS, aux + DO_TICKET + 2,
       aux + DO_STATUS + 2 * status_stride, g.sort_vals[0], (uint32_t)((1ull << ib) - 1ull));
   EGS_AFTER_LAUNCH(stream, debug);
   return EGS_OK;
 }
 
+// full words: tile | depth | index must fit 64 bits and most buckets the sorter's shared memory;
+// otherwise the pure LSD paths are the better choice
 bool bucket_path_ok(int P, int R, int W, int H) {
   if (!packed_path_fits(P, W, H)) return false;
-  // most buckets must fit in shared memory; otherwise the pure LSD path is the better choice
   return (long long)R <= (long long)MSD_BINS * BK_CAP * 8 / 10;
+}
+
+// presorted words (tile | index, 32 or 64 bits): any P; the split handles up to BS_MAX_BITS tile bits
+// below the 10-bit bucket digit
+bool presorted_path_ok(int P, int W, int H) {
+  const int tb = tile_id_bits((uint32_t)(tiles_x(W) * tiles_y(H)));
+  return P >= 1 && tb - MSD_BITS_MAX <= BS_MAX_BITS;
+}
+
+template <typename WORD, bool DEPTH>
+static int launch_duplicate(const GeomPtrs& g, WORD* words, const int* radii, const uint32_t* gauss_order, int P, int gx,
+                            int gy, int ib, InstanceCount count, int bucket_shift, uint32_t* hist, cudaStream_t stream,
+                            bool debug) {
+  // 4 CTAs per SM, each warp strides over groups of 32 Gaussians; the bucket histogram comes out of the
+  // same kernel. With the presort, sort_keys[1] is free again and holds the list of set-aside
+  // Gaussians, counted in meta[4] (zeroed with the rest of the aux words when the presort started).
+  uint32_t* big_list = gauss_order ? reinterpret_cast<uint32_t*>(g.sort_keys[1]) : nullptr;
+  uint32_t* big_count = gauss_order ? g.sort_aux + DO_META + 4 : nullptr;
+  duplicate_words_kernel<WORD, DEPTH><<<148 * 4, DUP_THREADS, 0, stream>>>(
+      P, g.means2D, g.depths, g.point_offsets, radii, gauss_order, words, gx, gy, ib, count, bucket_shift, hist, big_list,
+      big_count);
+  EGS_AFTER_LAUNCH(stream, debug);
+  if (gauss_order) {
+    duplicate_big_kernel<WORD, DEPTH><<<148 * 4, DUP_THREADS, 0, stream>>>(
+        g.means2D, g.depths, g.point_offsets, radii, gauss_order, words, gx, gy, ib, count, bucket_shift, hist, big_list,
+        big_count);
+    EGS_AFTER_LAUNCH(stream, debug);
+  }
+  return EGS_OK;
+}
+
+template <typename WORD>
+static int launch_partition(const WORD* in, WORD* out, int capacity, InstanceCount count, int shift, const uint32_t* start,
+                            uint32_t* ticket, uint32_t* status, cudaStream_t stream, bool debug) {
+  constexpr int SMEM = (int)sizeof(MsdSmem<WORD>);
+  EGS_CUDA_TRY(cudaFuncSetAttribute(msd_partition_kernel<WORD, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM));
+  const int grid = (capacity + MsdCfg<WORD>::TILE - 1) / MsdCfg<WORD>::TILE;
+  msd_partition_kernel<WORD, false><<<grid, MSD_THREADS, SMEM, stream>>>(in, out, count, shift, 0xffffffffu, start, ticket,
+                                                                        status, nullptr, 0u);
+  EGS_AFTER_LAUNCH(stream, debug);
+  return EGS_OK;
+}
+
+template <typename WORD>
+static int launch_split(const WORD* words, const uint32_t* start, uint32_t* point_list, uint2* ranges, int n_tiles, int ib,
+                        int bits, cudaStream_t stream, bool debug) {
+#define EGS_SPLIT_CASE(B)                                                                                         \
+  case B:                                                                                                         \
+    bucket_split_kernel<WORD, B><<<MSD_BINS, BS_THREADS, 0, stream>>>(words, start, point_list, ranges, n_tiles, ib); \
+    break;
+  switch (bits) {
+    EGS_SPLIT_CASE(0) EGS_SPLIT_CASE(1) EGS_SPLIT_CASE(2) EGS_SPLIT_CASE(3) EGS_SPLIT_CASE(4) EGS_SPLIT_CASE(5)
+    EGS_SPLIT_CASE(6) EGS_SPLIT_CASE(7)
+    default:
+      set_error("binning: %d tile bits below the bucket digit (image too large for the presorted path)", bits);
+      return EGS_ERR_TOO_LARGE;
+  }
+#undef EGS_SPLIT_CASE
+  EGS_AFTER_LAUNCH(stream, debug);
+  return EGS_OK;
 }
 
 // `capacity` sizes the grids and the workspace `b`; the real number of instances is read on the
 // device through `count` (it may still be in flight when this is enqueued). capacity == 0 means
 // the count is known to be 0.
 int launch_binning_buckets(const GeomPtrs& g, const BinningPtrs& b, const ImagePtrs& im, const int* radii,
-                           const uint32_t* gauss_order, int P, int capacity, InstanceCount count, int W, int H,
-                           cudaStream_t stream, bool debug) {
+                           const uint32_t* gauss_order, bool presorted, int P, int capacity, InstanceCount count, int W,
+                           int H, cudaStream_t stream, bool debug) {
   const int gx = tiles_x(W), gy = tiles_y(H);
   const int n_tiles = gx * gy;
   if (capacity == 0) {
@@ -884,83 +1014,70 @@ int launch_binning_buckets(const GeomPtrs& g, const BinningPtrs& b, const ImageP
   const int tb = tile_id_bits((uint32_t)n_tiles);
   const int mb = tb < MSD_BITS_MAX ? tb : MSD_BITS_MAX;   // bucket digit = top mb bits of the tile id
   const int bucket_shift = tb - mb;
-  const int rem_bits = bucket_shift + 32;
   uint32_t* hist = b.hist;                 // [MSD_BINS]
   uint32_t* start = b.hist + MSD_BINS;     // [MSD_BINS + 1]
-  uint32_t* order = b.hist + 2 * MSD_BINS + 8;   // [MSD_BINS]
-  uint32_t* work_count = order + MSD_BINS;       // buckets listed in `order` for bucket_sort_kernel
-  static_assert(3 * MSD_BINS + 8 + 1 <= SORT_HIST_WORDS, "histogram area too small");
-  // presorted frames: the buckets that fit go through the register-resident split (EGS_SPLIT=0: A/B)
-  const char* sp = getenv("EGS_SPLIT");
-  const bool split_ran = gauss_order != nullptr && bucket_shift <= BS_MAX_BITS && !(sp && sp[0] == '0');
+  static_assert(2 * MSD_BINS + 1 <= SORT_HIST_WORDS, "histogram area too small");
+  const bool narrow = presorted && tb + ib <= 32;   // tile | index fits a 32-bit word
   {
     StageTimer timer(stream, ST_DUPLICATE);
     // histogram, ticket and the status words of the single partition pass (not the whole area the
     // five-pass paths need)
     const size_t zero = reinterpret_cast<char*>(b.status + b.sort_blocks * MSD_BINS) - reinterpret_cast<char*>(b.hist);
     EGS_CUDA_TRY(cudaMemsetAsync(b.hist, 0, zero, stream));
-    // 4 CTAs per SM, each warp strides over groups of 32 Gaussians; the bucket histogram comes out
-    // of the same kernel
-    // with the presort: sort_keys[1] is free again and holds the list of set-aside Gaussians, counted
-    // in meta[4] (zeroed with the rest of the aux words when the presort started)
-    uint32_t* big_list = gauss_order ? reinterpret_cast<uint32_t*>(g.sort_keys[1]) : nullptr;
-    uint32_t* big_count = gauss_order ? g.sort_aux + DO_META + 4 : nullptr;
-    duplicate_words_kernel<<<148 * 4, DUP_THREADS, 0, stream>>>(P, g.means2D, g.depths, g.point_offsets, radii,
-                                                             gauss_order, b.keys[1], gx, gy, ib, count, bucket_shift,
-                                                             hist, big_list, big_count);
-    EGS_AFTER_LAUNCH(stream, debug);
-    if (gauss_order) {
-      duplicate_big_kernel<<<148 * 4, DUP_THREADS, 0, stream>>>(g.means2D, g.depths, g.point_offsets, radii, gauss_order,
-                                                             b.keys[1], gx, gy, ib, count, bucket_shift, hist, big_list,
-                                                             big_count);
-      EGS_AFTER_LAUNCH(stream, debug);
-    }
-    bucket_scan_kernel<<<1, MSD_BINS, 0, stream>>>(hist, start, order, work_count, split_ran ? 0u : (uint32_t)MSD_BINS);
+    int rc;
+    if (narrow)
+      rc = launch_duplicate<uint32_t, false>(g, reinterpret_cast<uint32_t*>(b.keys[1]), radii, gauss_order, P, gx, gy, ib,
+                                             count, bucket_shift, hist, stream, debug);
+    else if (presorted)
+      rc = launch_duplicate<uint64_t, false>(g, b.keys[1], radii, gauss_order, P, gx, gy, ib, count, bucket_shift, hist,
+                                             stream, debug);
+    else
+      rc = launch_duplicate<uint64_t, true>(g, b.keys[1], radii, gauss_order, P, gx, gy, ib, count, bucket_shift, hist,
+                                            stream, debug);
+    if (rc) return rc;
+    bucket_scan_kernel<<<1, MSD_BINS, 0, stream>>>(hist, start);
     EGS_AFTER_LAUNCH(stream, debug);
   }
   {
     StageTimer timer(stream, ST_SORT_HIST);   // reported as the global partition pass
-    EGS_CUDA_TRY(cudaFuncSetAttribute(msd_partition_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                      (int)sizeof(MsdSmem)));
-    msd_partition_kernel<false><<<(int)b.sort_blocks, MSD_THREADS, sizeof(MsdSmem), stream>>>(
-        b.keys[1], b.keys[0], count, ib + 32 + bucket_shift, 0xffffffffu, start, b.ticket, b.status, nullptr, 0u);
-    EGS_AFTER_LAUNCH(stream, debug);
+    const int shift = ib + (presorted ? 0 : 32) + bucket_shift;
+    int rc;
+    if (narrow)
+      rc = launch_partition<uint32_t>(reinterpret_cast<const uint32_t*>(b.keys[1]), reinterpret_cast<uint32_t*>(b.keys[0]),
+                                      capacity, count, shift, start, b.ticket, b.status, stream, debug);
+    else
+      rc = launch_partition<uint64_t>(b.keys[1], b.keys[0], capacity, count, shift, start, b.ticket, b.status, stream, debug);
+    if (rc) return rc;
   }
   {
-    StageTimer timer(stream, ST_SORT_PASSES);   // reported as the per-bucket sort
-    // The sorter is issue-bound: the match.any instruction measured 12 % faster than one ballot per
-    // digit bit (0.269 vs 0.305 ms at C3). EGS_MATCH=ballot keeps the ballot form for A/B runs.
-    // emitted front to back, the stable partition left every bucket ordered by depth: only the tile
-    // bits below the bucket digit remain (one pass instead of four)
-    const int first_bit = gauss_order ? 32 : 0;
-    const uint32_t* presort_veto = gauss_order ? g.sort_aux + DO_META + 3 : nullptr;
-    if (split_ran) {
-      switch (bucket_shift) {
-        case 0: bucket_split_kernel<0><<<MSD_BINS, BS_THREADS, 0, stream>>>(b.keys[0], start, b.vals[0], im.ranges, n_tiles, ib, presort_veto, order, work_count); break;
-        case 1: bucket_split_kernel<1><<<MSD_BINS, BS_THREADS, 0, stream>>>(b.keys[0], start, b.vals[0], im.ranges, n_tiles, ib, presort_veto, order, work_count); break;
-        case 2: bucket_split_kernel<2><<<MSD_BINS, BS_THREADS, 0, stream>>>(b.keys[0], start, b.vals[0], im.ranges, n_tiles, ib, presort_veto, order, work_count); break;
-        default: bucket_split_kernel<3><<<MSD_BINS, BS_THREADS, 0, stream>>>(b.keys[0], start, b.vals[0], im.ranges, n_tiles, ib, presort_veto, order, work_count); break;
-      }
+    StageTimer timer(stream, ST_SORT_PASSES);   // reported as the per-bucket stage
+    if (presorted) {
+      // emitted front to back, the stable partition left every bucket ordered by depth: only the tile
+      // bits below the bucket digit remain
+      int rc;
+      if (narrow)
+        rc = launch_split<uint32_t>(reinterpret_cast<const uint32_t*>(b.keys[0]), start, b.vals[0], im.ranges, n_tiles, ib,
+                                    bucket_shift, stream, debug);
+      else
+        rc = launch_split<uint64_t>(b.keys[0], start, b.vals[0], im.ranges, n_tiles, ib, bucket_shift, stream, debug);
+      if (rc) return rc;
+    } else {
+      EGS_CUDA_TRY(cudaFuncSetAttribute(bucket_sort_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                        (int)sizeof(BucketSmem)));
+      bucket_sort_kernel<<<MSD_BINS, BK_THREADS, sizeof(BucketSmem), stream>>>(
+          b.keys[0], b.keys[1], start, b.vals[0], im.ranges, n_tiles, ib, bucket_shift, bucket_shift + 32);
       EGS_AFTER_LAUNCH(stream, debug);
     }
-    // after the split only its leftovers are listed: one CTA per SM walks the list
-    const int sort_grid = split_ran ? 148 : MSD_BINS;
-    const char* m = getenv("EGS_MATCH");
-    if (!(m && strcmp(m, "ballot") == 0)) {
-      EGS_CUDA_TRY(cudaFuncSetAttribute(bucket_sort_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                        (int)sizeof(BucketSmem)));
-      bucket_sort_kernel<true><<<sort_grid, BK_THREADS, sizeof(BucketSmem), stream>>>(
-          b.keys[0], b.keys[1], start, order, work_count, b.vals[0], im.ranges, n_tiles, ib, bucket_shift, rem_bits,
-          first_bit, presort_veto);
-    } else {
-      EGS_CUDA_TRY(cudaFuncSetAttribute(bucket_sort_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                        (int)sizeof(BucketSmem)));
-      bucket_sort_kernel<false><<<sort_grid, BK_THREADS, sizeof(BucketSmem), stream>>>(
-          b.keys[0], b.keys[1], start, order, work_count, b.vals[0], im.ranges, n_tiles, ib, bucket_shift, rem_bits,
-          first_bit, presort_veto);
-    }
-    EGS_AFTER_LAUNCH(stream, debug);
   }
+  return EGS_OK;
+}
+
+int launch_binning_keys(const GeomPtrs& g, const ImagePtrs& im, const uint32_t* point_list, uint64_t* keys, int W, int H,
+                        cudaStream_t stream) {
+  const int n_tiles = tiles_x(W) * tiles_y(H);
+  binning_keys_kernel<<<n_tiles < 148 * 8 ? n_tiles : 148 * 8, 256, 0, stream>>>(im.ranges, point_list, g.depths, keys,
+                                                                               n_tiles);
+  EGS_AFTER_LAUNCH(stream, false);
   return EGS_OK;
 }
 

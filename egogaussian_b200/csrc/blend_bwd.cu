@@ -17,9 +17,6 @@
 //     reductions (red.global.add.v4.f32) into the 48-byte per-Gaussian record.
 #include "common.cuh"
 
-#include <stdlib.h>
-#include <string.h>
-
 namespace egs {
 
 constexpr int BWD_BATCH = 256;
@@ -79,187 +76,32 @@ __device__ __forceinline__ int quantity_of_lane(unsigned lane) {
 //   q7 colour.r -> 8   q8 colour.g -> 9   q9 colour.b -> 10
 __device__ __forceinline__ int record_slot_of_quantity(int q) { return q < 7 ? q : q + 1; }
 
-__global__ void __launch_bounds__(TILE_PIXELS)
-blend_backward_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__ point_list,
-                      int W, int H, int grid_x, const float* __restrict__ bg_color,
-                      const float2* __restrict__ means2D, const float4* __restrict__ conic_opacity,
-                      const float4* __restrict__ rgb_depth, const float* __restrict__ alphas,
-                      const uint32_t* __restrict__ n_contrib, const float* __restrict__ dL_dpixels,
-                      const float* __restrict__ dL_dpixel_depths, const float* __restrict__ dL_dalphas,
-                      float4* __restrict__ acc) {
-  __shared__ uint32_t s_id[BWD_BATCH];
-  __shared__ float2 s_xy[BWD_BATCH];
-  __shared__ float4 s_co[BWD_BATCH];
-  __shared__ float4 s_cd[BWD_BATCH];
-  __shared__ float s_acc[BWD_BATCH * ACC_PITCH];
-  __shared__ uint32_t s_max_contrib;
-
-  const unsigned tid = threadIdx.x;
-  const unsigned warp = tid >> 5, lane = tid & 31;
-  const unsigned lx = (warp & 1) * 8 + (lane & 7);
-  const unsigned ly = (warp >> 1) * 4 + (lane >> 3);
-  const unsigned px = blockIdx.x * TILE_X + lx;
-  const unsigned py = blockIdx.y * TILE_Y + ly;
-  const bool inside = px < (unsigned)W && py < (unsigned)H;
-  const uint32_t pix_id = (uint32_t)W * py + px;
-  const float2 pixf = make_float2((float)px, (float)py);
-
-  const uint2 range = ranges[blockIdx.y * grid_x + blockIdx.x];
-
-  const float T_final = inside ? (1 - alphas[pix_id]) : 0;
-  float T = T_final;
-  const uint32_t last_contributor = inside ? n_contrib[pix_id] : 0;
-
-  if (tid == 0) s_max_contrib = 0;
-  __syncthreads();
-  {
-    uint32_t m = last_contributor;
-#pragma unroll
-    for (int d = 16; d > 0; d >>= 1) m = max(m, __shfl_xor_sync(0xffffffffu, m, d));
-    if (lane == 0 && m) atomicMax(&s_max_contrib, m);
-  }
-  __syncthreads();
-  const int walk = (int)s_max_contrib;  // positions [0, walk) of this tile's list matter
-  if (walk == 0) return;
-  uint32_t warp_last = last_contributor;
-#pragma unroll
-  for (int d = 16; d > 0; d >>= 1) warp_last = max(warp_last, __shfl_xor_sync(0xffffffffu, warp_last, d));
-
-  float accum_rec[3] = {0.f, 0.f, 0.f};
-  float dL_dpixel[3] = {0.f, 0.f, 0.f};
-  float accum_depth_rec = 0.f, dL_dpixel_depth = 0.f;
-  float accum_alpha_rec = 0.f, dL_dalpha = 0.f;
-  if (inside) {
-    const size_t plane = (size_t)H * W;
-#pragma unroll
-    for (int ch = 0; ch < 3; ++ch) dL_dpixel[ch] = dL_dpixels[ch * plane + pix_id];
-    dL_dpixel_depth = dL_dpixel_depths[pix_id];
-    dL_dalpha = dL_dalphas[pix_id];
-  }
-  float last_alpha = 0.f;
-  float last_color[3] = {0.f, 0.f, 0.f};
-  float last_depth = 0.f;
-  const float ddelx_dx = 0.5 * W;
-  const float ddely_dy = 0.5 * H;
-  float bg_dot_dpixel = 0;
-#pragma unroll
-  for (int ch = 0; ch < 3; ++ch) bg_dot_dpixel += bg_color[ch] * dL_dpixel[ch];
-
-  const int my_quantity = quantity_of_lane(lane);
-  const int my_slot = my_quantity >= 0 ? record_slot_of_quantity(my_quantity) : 0;
-  const bool i_add = my_quantity >= 0 && (lane & 1) == 0;
-
-  const int rounds = (walk + BWD_BATCH - 1) / BWD_BATCH;
-  for (int r = 0; r < rounds; ++r) {
-    __syncthreads();
-    // stage positions walk-1-(r*B + tid), i.e. back to front
-    const int pos = walk - 1 - (r * BWD_BATCH + (int)tid);
-    if (pos >= 0) {
-      const uint32_t id = point_list[range.x + pos];
-      s_id[tid] = id;
-      s_xy[tid] = means2D[id];
-      s_co[tid] = conic_opacity[id];
-      s_cd[tid] = rgb_depth[id];
-    }
-#pragma unroll
-    for (int k = 0; k < ACC_PITCH; ++k) s_acc[k * BWD_BATCH + tid] = 0.f;
-    __syncthreads();
-
-    const int n = min(BWD_BATCH, walk - r * BWD_BATCH);
-    for (int j = 0; j < n; ++j) {
-      const int jpos = walk - 1 - (r * BWD_BATCH + j);  // 0-based list position of this entry
-      if ((uint32_t)jpos >= warp_last) continue;        // warp-uniform
-      bool active = (uint32_t)jpos < last_contributor;
-      const float2 xy = s_xy[j];
-      const float2 d = make_float2(xy.x - pixf.x, xy.y - pixf.y);
-      const float4 con_o = s_co[j];
-      const float power = -0.5f * (con_o.x * d.x * d.x + con_o.z * d.y * d.y) - con_o.y * d.x * d.y;
-      active = active && !(power > 0.0f);
-      const float G = expf(power);
-      const float alpha = min(0.99f, con_o.w * G);
-      active = active && !(alpha < 1.0f / 255.0f);
-      if (!__any_sync(0xffffffffu, active)) continue;
-
-      float q[10];
-#pragma unroll
-      for (int k = 0; k < 10; ++k) q[k] = 0.f;
-      if (active) {
-        T = T / (1.f - alpha);
-        const float dchannel_dcolor = alpha * T;
-        const float4 cd = s_cd[j];
-        const float c[3] = {cd.x, cd.y, cd.z};
-        float dL_dopa = 0.0f;
-#pragma unroll
-        for (int ch = 0; ch < 3; ++ch) {
-          accum_rec[ch] = last_alpha * last_color[ch] + (1.f - last_alpha) * accum_rec[ch];
-          last_color[ch] = c[ch];
-          const float dL_dchannel = dL_dpixel[ch];
-          dL_dopa += (c[ch] - accum_rec[ch]) * dL_dchannel;
-          q[7 + ch] = dchannel_dcolor * dL_dchannel;
-        }
-        const float c_d = cd.w;
-        accum_depth_rec = last_alpha * last_depth + (1.f - last_alpha) * accum_depth_rec;
-        last_depth = c_d;
-        dL_dopa += (c_d - accum_depth_rec) * dL_dpixel_depth;
-        q[3] = dchannel_dcolor * dL_dpixel_depth;
-
-        accum_alpha_rec = last_alpha + (1.f - last_alpha) * accum_alpha_rec;
-        dL_dopa += (1 - accum_alpha_rec) * dL_dalpha;
-
-        dL_dopa *= T;
-        last_alpha = alpha;
-        dL_dopa += (-T_final / (1.f - alpha)) * bg_dot_dpixel;
-
-        const float dL_dG = con_o.w * dL_dopa;
-        const float gdx = G * d.x;
-        const float gdy = G * d.y;
-        const float dG_ddelx = -gdx * con_o.x - gdy * con_o.y;
-        const float dG_ddely = -gdy * con_o.z - gdx * con_o.y;
-        q[0] = dL_dG * dG_ddelx * ddelx_dx;
-        q[1] = dL_dG * dG_ddely * ddely_dy;
-        q[4] = -0.5f * gdx * d.x * dL_dG;
-        q[5] = -0.5f * gdx * d.y * dL_dG;
-        q[6] = -0.5f * gdy * d.y * dL_dG;
-        q[2] = G * dL_dopa;
-      }
-      const float total = warp_packed_reduce10(q, lane);
-      if (i_add) atomicAdd(&s_acc[j * ACC_PITCH + my_slot], total);
-    }
-    __syncthreads();
-
-    // flush: thread tid owns entry tid of the batch
-    if ((int)tid < n) {
-      float v[ACC_STRIDE];
-      bool any = false;
-#pragma unroll
-      for (int k = 0; k < ACC_STRIDE; ++k) {
-        v[k] = s_acc[tid * ACC_PITCH + k];
-        any = any || (v[k] != 0.f);
-      }
-      if (any) {
-        float4* dst = acc + (size_t)s_id[tid] * 3;
-        atomicAdd(dst + 0, make_float4(v[0], v[1], v[2], v[3]));
-        atomicAdd(dst + 1, make_float4(v[4], v[5], v[6], v[7]));
-        atomicAdd(dst + 2, make_float4(v[8], v[9], v[10], v[11]));
-      }
-    }
-  }
-}
-
 // ---------------------------------------------------------------------------------------------
-// v2: two pixels per thread, exp only for fragments that pass a log-domain test
+// two pixels per thread, exp only for fragments that pass a log-domain test
 // ---------------------------------------------------------------------------------------------
-// Same arithmetic per fragment as above, reorganised for throughput:
+// The per-fragment arithmetic of SURVEY.md App. A.8, organised for throughput:
 //   * 128 threads per tile, each owning the pixels (x, y) and (x, y + 4) of its warp's 8x8 block:
 //     a list entry costs 4 warp reductions per tile instead of 8, every staged entry is read from
 //     shared memory half as often, and the two pixel chains give the scheduler independent work;
 //   * whether a fragment contributes is decided without the exponential:
 //       alpha = o * exp(power) >= 1/255   <=>   power >= -log(255 * o) =: thr (staged per entry),
-//     so exp, the divide and everything after run only on warps where some lane contributes;
+//     so exp, the divide and everything after run only on warps where some lane contributes.
+//     The forward pass decides with min(0.99, o * expf(power)) >= 1/255 in fp32; a fragment whose
+//     power lies within CONTRIB_MARGIN of the threshold is therefore decided here with that very
+//     expression, so both passes always agree on a pixel's contributor set (one fragment more or
+//     less would shift T = T / (1 - alpha) for every earlier fragment of the pixel);
 //   * backward is tolerance-checked (1e-4 of the tensor maximum), not bit-checked, so the
 //     exponential and the reciprocal use the fast hardware approximations (ex2.approx, rcp.approx).
 constexpr int BWD2_THREADS = 128;
 constexpr int BWD2_BATCH = 128;
+// half-width of the band around -log(255 o) inside which the forward's exact test decides: covers
+// the error of __logf (~1e-6 here) and of the fp32 product o * expf(power) a hundred times over
+constexpr float CONTRIB_MARGIN = 1e-4f;
+
+// the forward's contribution test, bit for bit (blend_fwd.cu; forward.cu:336-343)
+__device__ __forceinline__ bool contributes_exact(float opac, float power) {
+  return !(fminf(0.99f, opac * expf(power)) < 1.0f / 255.0f);
+}
 
 // single-instruction hardware approximations (MUFU.EX2 / MUFU.RCP, flush-to-zero): the __expf and
 // __fdividef intrinsics wrap them in denormal-range fix-ups that cost more than the operation
@@ -429,8 +271,9 @@ blend_backward2_kernel(const uint2* __restrict__ ranges, const uint32_t* __restr
       const float4 co = conic_opacity[id];
       const float4 cd = rgb_depth[id];
       s_id[tid] = id;
-      // alpha >= 1/255  <=>  power >= -log(255 o); o <= 0 can never contribute
-      s_a[tid] = make_float4(xy.x, xy.y, co.w > 0.f ? -__logf(255.f * co.w) : 1.f, co.w);
+      // alpha >= 1/255  <=>  power >= -log(255 o), staged with the margin subtracted; o <= 0 can
+      // never contribute
+      s_a[tid] = make_float4(xy.x, xy.y, co.w > 0.f ? -__logf(255.f * co.w) - CONTRIB_MARGIN : 1.f, co.w);
       reach = footprint_mask<8, 8>(xy, co, (float)(blockIdx.x * TILE_X), (float)(blockIdx.y * TILE_Y));
       s_b[tid] = make_float4(co.x, co.y, co.z, cd.w);
       s_c[tid] = cd;
@@ -465,9 +308,13 @@ blend_backward2_kernel(const uint2* __restrict__ ranges, const uint32_t* __restr
       const float dx1 = a4.x - P1.px, dy1 = a4.y - P1.py;
       const float power0 = -0.5f * (b4.x * dx0 * dx0 + b4.z * dy0 * dy0) - b4.y * dx0 * dy0;
       const float power1 = -0.5f * (b4.x * dx1 * dx1 + b4.z * dy1 * dy1) - b4.y * dx1 * dy1;
-      const bool act0 = jpos < P0.last && power0 <= 0.0f && power0 >= a4.z;
-      const bool act1 = jpos < P1.last && power1 <= 0.0f && power1 >= a4.z;
+      bool act0 = jpos < P0.last && power0 <= 0.0f && power0 >= a4.z;
+      bool act1 = jpos < P1.last && power1 <= 0.0f && power1 >= a4.z;
       if (!__any_sync(0xffffffffu, act0 || act1)) continue;
+      // inside the band around the threshold the forward's own expression decides
+      const float band_hi = a4.z + 2.f * CONTRIB_MARGIN;
+      if (act0 && power0 < band_hi) act0 = contributes_exact(a4.w, power0);
+      if (act1 && power1 < band_hi) act1 = contributes_exact(a4.w, power1);
 
       float q[10];
 #pragma unroll
@@ -510,14 +357,7 @@ int launch_blend_backward(const EgsBackwardArgs& a, const GeomPtrs& g, const uin
                           const ImagePtrs& im, const BackwardScratch& s, cudaStream_t stream) {
   const dim3 grid(tiles_x(a.width), tiles_y(a.height), 1);
   StageTimer timer(stream, ST_BLEND_BWD);
-  // EGS_BWD=v1 selects the one-pixel-per-thread kernel with the reference's exact exp (A/B runs)
-  const char* sel = getenv("EGS_BWD");
-  if (sel && strcmp(sel, "v1") == 0) {
-    blend_backward_kernel<<<grid, TILE_PIXELS, 0, stream>>>(
-        im.ranges, point_list, a.width, a.height, (int)grid.x, a.background, g.means2D,
-        g.conic_opacity, g.rgb_depth, a.out_alpha, im.n_contrib, a.dL_dout_color, a.dL_dout_depth,
-        a.dL_dout_alpha, s.acc);
-  } else if (a.colors_only) {
+  if (a.colors_only) {
     blend_backward2_kernel<true><<<grid, BWD2_THREADS, 0, stream>>>(
         im.ranges, point_list, a.width, a.height, (int)grid.x, a.background, g.means2D,
         g.conic_opacity, g.rgb_depth, a.out_alpha, im.n_contrib, a.dL_dout_color, a.dL_dout_depth,

@@ -14,9 +14,6 @@
 //     transmittance thresholds make the image sensitive to the last bit of `power`.
 #include "common.cuh"
 
-#include <stdlib.h>
-#include <string.h>
-
 namespace egs {
 
 constexpr int BLEND_BATCH = 256;
@@ -258,11 +255,10 @@ int launch_blend_forward(const EgsForwardArgs& a, const GeomPtrs& g, const uint3
                          const ImagePtrs& im, cudaStream_t stream) {
   const dim3 grid(tiles_x(a.width), tiles_y(a.height), 1);
   StageTimer timer(stream, ST_BLEND_FWD);
-  // Default: one pixel per thread, per-warp bit lists. EGS_FWD=v2 selects the older
-  // two-pixels-per-thread kernel without bit lists, kept as an independent implementation for
-  // tests/test_parity_gpu.py::test_kernel_variants_agree (bit-identical results, slower).
-  const char* sel = getenv("EGS_FWD");
-  if (!(sel && strcmp(sel, "v2") == 0)) {
+  // Default: one pixel per thread, per-warp bit lists. egs_debug_option("blend_forward", "v2") selects
+  // the older two-pixels-per-thread kernel without bit lists, kept as an independent implementation
+  // for tests/test_parity_gpu.py::test_kernel_variants_agree (bit-identical results, slower).
+  if (!debug_options().fwd_v2) {
     blend_forward3_kernel<<<grid, TILE_PIXELS, 0, stream>>>(
         im.ranges, point_list, a.width, a.height, (int)grid.x, g.means2D, g.conic_opacity,
         g.rgb_depth, a.background, a.out_color, a.out_depth, a.out_alpha, im.n_contrib);

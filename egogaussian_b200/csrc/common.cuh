@@ -80,7 +80,7 @@ constexpr int SORT_TILE = SORT_THREADS * SORT_ITEMS;
 
 struct GeomLayout {
   size_t depths, means2D, conic_opacity, rgb_depth, clamped, tiles_touched, point_offsets,
-      scan_status, sort_keys[2], sort_vals[2], sort_aux, sort_blocks, sort_aux_bytes, total;
+      scan_status, sort_keys[2], sort_vals[2], sort_aux, sort_blocks, sort_aux_bytes, prefilter_fault, total;
   explicit GeomLayout(size_t P) {
     size_t o = 0;
     auto take = [&](size_t bytes) { size_t r = o; o = align_up(o + bytes); return r; };
@@ -102,6 +102,7 @@ struct GeomLayout {
     sort_blocks = (P + SORT_TILE - 1) / SORT_TILE;
     sort_aux_bytes = (DEPTH_ORDER_AUX_WORDS + 3 * sort_blocks * 1024) * 4;
     sort_aux = take(sort_aux_bytes);
+    prefilter_fault = take(4);   // set when a Gaussian is culled although `prefiltered` promised otherwise
     total = o + 256;
   }
 };
@@ -118,6 +119,7 @@ struct GeomPtrs {
   uint64_t* sort_keys[2];           // depth-order presort; the order ends in sort_vals[0]
   uint32_t* sort_vals[2];
   uint32_t* sort_aux;
+  uint32_t* prefilter_fault;
   size_t sort_blocks, sort_aux_bytes;
   GeomPtrs(void* base, size_t P) {
     GeomLayout L(P);
@@ -134,6 +136,7 @@ struct GeomPtrs {
     sort_vals[0] = reinterpret_cast<uint32_t*>(b + L.sort_vals[0]);
     sort_vals[1] = nullptr;
     sort_aux = reinterpret_cast<uint32_t*>(b + L.sort_aux);
+    prefilter_fault = reinterpret_cast<uint32_t*>(b + L.prefilter_fault);
     sort_blocks = L.sort_blocks;
     sort_aux_bytes = L.sort_aux_bytes;
   }
@@ -265,19 +268,43 @@ bool bucket_path_ok(int P, int R, int W, int H);
 // The number of instances as the device sees it: `n_dev` points at the last element of the
 // tiles_touched scan, `cap` is what the workspace was sized for. Kernels enqueued before the host
 // knows the count read it here and skip themselves when it does not fit.
+// `veto` (optional) is the flag the depth presort raises when its order is not the depth order (a
+// depth outside its key range): the presorted path then skips itself too and forward re-runs the
+// binning without relying on that order.
 struct InstanceCount {
   const uint32_t* n_dev;
   uint32_t cap;
+  const uint32_t* veto;
 #ifdef __CUDACC__
   __device__ __forceinline__ bool get(uint32_t& n) const {
     n = *n_dev;
-    return n <= cap;
+    return n <= cap && !(veto != nullptr && *veto != 0u);
   }
 #endif
 };
+// presorted: `order` is the front-to-back order of launch_depth_order and the instances carry no
+// depth bits (tile | index words of 32 or 64 bits: any number of Gaussians); otherwise full
+// tile | depth | index words, which need packed_path_fits().
+bool presorted_path_ok(int P, int W, int H);
+const uint32_t* presort_veto_flag(const GeomPtrs& g);
 int launch_binning_buckets(const GeomPtrs& g, const BinningPtrs& b, const ImagePtrs& im, const int* radii,
-                           const uint32_t* order, int P, int capacity, InstanceCount count, int W, int H,
-                           cudaStream_t stream, bool debug);
+                           const uint32_t* order, bool presorted, int P, int capacity, InstanceCount count, int W,
+                           int H, cudaStream_t stream, bool debug);
+// keys[i] = tile << 32 | depth bits of point_list[i], rebuilt from the tile ranges (tests only: no
+// kernel of the path reads the sorted keys, so the fast paths do not write them)
+int launch_binning_keys(const GeomPtrs& g, const ImagePtrs& im, const uint32_t* point_list, uint64_t* keys, int W,
+                        int H, cudaStream_t stream);
+
+// Switches for tests and A/B timing, set through egs_debug_option() only: the library never reads
+// the process environment, so nothing outside the caller's code can change which kernels run.
+enum SortPath { SORT_AUTO = 0, SORT_PACKED, SORT_PAIRS, SORT_PAIRS8 };
+struct DebugOptions {
+  int sort;               // SortPath
+  int presort;            // -1 automatic, 0 never, 1 whenever the scene has >= 64 Gaussians
+  int presort_scramble;   // 1: presort keys unrelated to depth + veto raised (exercises the fallback)
+  int fwd_v2;             // 1: the two-pixels-per-thread forward blend (independent implementation)
+};
+DebugOptions debug_options();
 int launch_tile_ranges(int R, const uint64_t* sorted_keys, const ImagePtrs& im, cudaStream_t stream,
                        bool debug);
 int launch_binning(const GeomPtrs& g, const BinningPtrs& b, const ImagePtrs& im, const int* radii,

@@ -18,6 +18,8 @@
 #include "adam_math.cuh"
 
 #include <math.h>
+#include <atomic>
+#include <mutex>
 
 namespace egs {
 
@@ -26,7 +28,8 @@ constexpr int EX_SLOT_IN = 0;                                   // [0, 8): "rank
 constexpr int EX_SLOT_OUT = EGS_MAX_PEERS;                      // [8, 16): "rank q finished exchange e"
 constexpr int EX_SLOT_COUNT = 2 * EGS_MAX_PEERS;                // CTAs of this rank that finished
 constexpr int EX_SLOT_ERROR = EGS_EXCHANGE_SIGNAL_WORDS - 1;    // set when a peer never showed up
-constexpr unsigned long long EX_TIMEOUT_NS = 20ull * 1000 * 1000 * 1000;
+// how long a kernel waits for a peer before it gives up (egs_exchange_set_timeout_ms)
+static std::atomic<unsigned long long> g_timeout_ns{20ull * 1000 * 1000 * 1000};
 
 struct ExSegmentDev {
   long long begin4, end4;   // in 4-float chunks
@@ -44,6 +47,7 @@ struct ExLaunch {
   long long lo4, hi4;   // this rank's slice, in 4-float chunks
   float scale;
   uint32_t epoch;
+  unsigned long long timeout_ns;
   // Adam
   float* exp_avg;
   float* exp_avg_sq;
@@ -79,31 +83,40 @@ __device__ __forceinline__ unsigned long long global_ns() {
   return t;
 }
 
-// threads [0, world) each wait for one peer's flag to reach `epoch`
-__device__ __forceinline__ void wait_peer_flags(const ExLaunch& L, int slot) {
+// threads [0, world) each wait for one peer's flag to reach `epoch`. Returns false (to every thread
+// of the CTA) when a peer did not show up in time; the error word of this rank is then set.
+__device__ __forceinline__ bool wait_peer_flags(const ExLaunch& L, int slot, int& s_timed_out) {
+  if (threadIdx.x == 0) s_timed_out = 0;
+  __syncthreads();
   if ((int)threadIdx.x < L.world) {
     const uint32_t* flag = L.signals[L.rank] + slot + threadIdx.x;
     const unsigned long long t0 = global_ns();
     while ((int)(ld_acquire_sys(flag) - L.epoch) < 0) {
-      if (global_ns() - t0 > EX_TIMEOUT_NS) {
+      if (global_ns() - t0 > L.timeout_ns) {
         L.signals[L.rank][EX_SLOT_ERROR] = 1u;
+        s_timed_out = 1;
         break;
       }
     }
   }
   __syncthreads();
+  return s_timed_out == 0;
 }
 
-// my backward is complete (this kernel follows it in stream order); wait until every peer's is
-__device__ __forceinline__ void barrier_in(const ExLaunch& L) {
+// my backward is complete (this kernel follows it in stream order); wait until every peer's is.
+// false: some peer never arrived. The caller then skips the data phase -- a straggler's buffer still
+// holds the previous iteration, and summing it (or, worse, stepping the optimiser on it and
+// broadcasting the result) would corrupt every rank -- but still runs barrier_out, so that peers
+// which did arrive are released.
+__device__ __forceinline__ bool barrier_in(const ExLaunch& L, int& s_timed_out) {
   if (blockIdx.x == 0 && (int)threadIdx.x < L.world)
     st_release_sys(L.signals[threadIdx.x] + EX_SLOT_IN + L.rank, L.epoch);
-  wait_peer_flags(L, EX_SLOT_IN);
+  return wait_peer_flags(L, EX_SLOT_IN, s_timed_out);
 }
 
 // all my stores are visible everywhere, then all peers' stores are visible here; the last CTA of the
 // grid speaks for the rank
-__device__ __forceinline__ void barrier_out(const ExLaunch& L, bool& s_last) {
+__device__ __forceinline__ void barrier_out(const ExLaunch& L, bool& s_last, int& s_timed_out) {
   __threadfence_system();
   __syncthreads();
   if (threadIdx.x == 0) {
@@ -116,7 +129,7 @@ __device__ __forceinline__ void barrier_out(const ExLaunch& L, bool& s_last) {
   __syncthreads();
   if (!s_last) return;
   if ((int)threadIdx.x < L.world) st_release_sys(L.signals[threadIdx.x] + EX_SLOT_OUT + L.rank, L.epoch);
-  wait_peer_flags(L, EX_SLOT_OUT);
+  wait_peer_flags(L, EX_SLOT_OUT, s_timed_out);
 }
 
 // multicast addresses (NVLink SHARP): one load returns the sum over all ranks, formed in the switch;
@@ -146,7 +159,7 @@ __device__ __forceinline__ float4 adam_chunk(const ExLaunch& L, const ExSegmentD
   float ns0 = S.neg_step_a, ns1 = S.neg_step_a, ns2 = S.neg_step_a, ns3 = S.neg_step_a;
   if (S.period > 0) {
     const int r0 = (int)(((c - S.begin4) * 4) % S.period);
-    auto pick = [&](int r) { return (r >= S.period ? r - S.period : r) < S.split ? S.neg_step_a : S.neg_step_b; };
+    auto pick = [&](int r) { return r % S.period < S.split ? S.neg_step_a : S.neg_step_b; };   // any period >= 1
     ns0 = pick(r0); ns1 = pick(r0 + 1); ns2 = pick(r0 + 2); ns3 = pick(r0 + 3);
   }
   const long long k4 = (c - L.lo4) * 4;
@@ -176,10 +189,11 @@ template <bool ADAM, int WMAX>
 __global__ void __launch_bounds__(EX_THREADS, 2) exchange_kernel(const __grid_constant__ ExLaunch L) {
   constexpr int U = 8 / WMAX;
   __shared__ bool s_last;
-  barrier_in(L);
+  __shared__ int s_timed_out;
+  const bool peers_ready = barrier_in(L, s_timed_out);
 
   const long long stride = (long long)gridDim.x * EX_THREADS * U;
-  for (long long c0 = L.lo4 + (long long)blockIdx.x * EX_THREADS * U + threadIdx.x; c0 < L.hi4; c0 += stride) {
+  for (long long c0 = L.lo4 + (long long)blockIdx.x * EX_THREADS * U + threadIdx.x; peers_ready && c0 < L.hi4; c0 += stride) {
     float4 part[U][WMAX];
 #pragma unroll
     for (int u = 0; u < U; ++u)
@@ -208,7 +222,7 @@ __global__ void __launch_bounds__(EX_THREADS, 2) exchange_kernel(const __grid_co
     }
   }
 
-  barrier_out(L, s_last);
+  barrier_out(L, s_last, s_timed_out);
 }
 
 // The same exchange through the switch: (world - 1) / world of the buffer crosses each link once per
@@ -217,9 +231,10 @@ template <bool ADAM>
 __global__ void __launch_bounds__(EX_THREADS, 2) exchange_mc_kernel(const __grid_constant__ ExLaunch L) {
   constexpr int U = 4;
   __shared__ bool s_last;
-  barrier_in(L);
+  __shared__ int s_timed_out;
+  const bool peers_ready = barrier_in(L, s_timed_out);
   const long long stride = (long long)gridDim.x * EX_THREADS * U;
-  for (long long c0 = L.lo4 + (long long)blockIdx.x * EX_THREADS * U + threadIdx.x; c0 < L.hi4; c0 += stride) {
+  for (long long c0 = L.lo4 + (long long)blockIdx.x * EX_THREADS * U + threadIdx.x; peers_ready && c0 < L.hi4; c0 += stride) {
     float4 g[U];
 #pragma unroll
     for (int u = 0; u < U; ++u)
@@ -239,7 +254,7 @@ __global__ void __launch_bounds__(EX_THREADS, 2) exchange_mc_kernel(const __grid
       st_mc_f4(L.grads_mc + 4 * c, g[u]);
     }
   }
-  barrier_out(L, s_last);
+  barrier_out(L, s_last, s_timed_out);
 }
 
 static int fill_group(const char* who, const EgsPeerGroup* g, long long n, ExLaunch& L) {
@@ -261,6 +276,7 @@ static int fill_group(const char* who, const EgsPeerGroup* g, long long n, ExLau
     return EGS_ERR_INVALID_ARGUMENT;
   }
   L.grads_mc = g->grads_multicast;
+  L.timeout_ns = g_timeout_ns.load(std::memory_order_relaxed);
   L.world = g->world;
   L.rank = g->rank;
   const long long n4 = n / 4, per = (n4 + g->world - 1) / g->world;
@@ -269,11 +285,60 @@ static int fill_group(const char* who, const EgsPeerGroup* g, long long n, ExLau
   return EGS_OK;
 }
 
-static unsigned exchange_grid(const ExLaunch& L, int max_ctas) {
+// The flag barriers need every CTA of the grid on an SM at the same time (a CTA that is not resident
+// cannot signal, and the resident ones spin for it). How many fit is a property of the device and of
+// the kernel's resources: SM count x CTAs per SM from the occupancy calculator, looked up once per
+// device and kernel. A caller's max_ctas beyond that is refused at once instead of timing out on the
+// GPU. (Other kernels holding SMs on other streams only delay the exchange: their CTAs retire.)
+template <typename K>
+static int resident_cta_limit(K kernel, int* limit) {
+  static std::mutex mu;
+  static int cached[64] = {};
+  int dev = 0;
+  EGS_CUDA_TRY(cudaGetDevice(&dev));
+  std::lock_guard<std::mutex> lk(mu);
+  if (dev < 0 || dev >= 64) {
+    set_error("exchange: device ordinal %d not supported", dev);
+    return EGS_ERR_INVALID_ARGUMENT;
+  }
+  if (cached[dev] == 0) {
+    int sms = 0, per_sm = 0;
+    EGS_CUDA_TRY(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
+    EGS_CUDA_TRY(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kernel, EX_THREADS, 0));
+    cached[dev] = sms * per_sm;
+    if (cached[dev] <= 0) {
+      set_error("exchange: the kernel does not fit on device %d", dev);
+      cached[dev] = 0;
+      return EGS_ERR_CUDA;
+    }
+  }
+  *limit = cached[dev];
+  return EGS_OK;
+}
+
+template <typename K>
+static int exchange_grid(const char* who, K kernel, const ExLaunch& L, int max_ctas, unsigned* grid) {
+  int limit = 0;
+  if (int rc = resident_cta_limit(kernel, &limit)) return rc;
+  if (max_ctas > limit) {
+    set_error("%s: max_ctas %d exceeds the %d CTAs of this kernel that can be resident at once on this device", who,
+              max_ctas, limit);
+    return EGS_ERR_INVALID_ARGUMENT;
+  }
   long long ctas = (L.hi4 - L.lo4 + EX_THREADS - 1) / EX_THREADS;   // (more than the unrolled loop needs: harmless)
-  const long long cap = max_ctas > 0 ? max_ctas : 148 * 2;
+  const long long cap = max_ctas > 0 ? max_ctas : limit;
   if (ctas > cap) ctas = cap;
-  return (unsigned)(ctas < 1 ? 1 : ctas);   // an empty slice still takes part in the barriers
+  *grid = (unsigned)(ctas < 1 ? 1 : ctas);   // an empty slice still takes part in the barriers
+  return EGS_OK;
+}
+
+template <typename K>
+static int launch_exchange(const char* who, K kernel, const ExLaunch& L, int max_ctas, cudaStream_t st) {
+  unsigned grid = 0;
+  if (int rc = exchange_grid(who, kernel, L, max_ctas, &grid)) return rc;
+  kernel<<<grid, EX_THREADS, 0, st>>>(L);
+  EGS_AFTER_LAUNCH(st, false);
+  return EGS_OK;
 }
 
 }  // namespace egs
@@ -292,12 +357,20 @@ extern "C" int egs_exchange_sum(const EgsPeerGroup* group, long long n_floats, f
   L.scale = scale;
   L.epoch = epoch;
   cudaStream_t st = static_cast<cudaStream_t>(stream);
-  const unsigned grid = exchange_grid(L, max_ctas);
-  if (L.grads_mc) exchange_mc_kernel<false><<<grid, EX_THREADS, 0, st>>>(L);
-  else if (L.world <= 2) exchange_kernel<false, 2><<<grid, EX_THREADS, 0, st>>>(L);
-  else if (L.world <= 4) exchange_kernel<false, 4><<<grid, EX_THREADS, 0, st>>>(L);
-  else exchange_kernel<false, 8><<<grid, EX_THREADS, 0, st>>>(L);
-  EGS_AFTER_LAUNCH(st, false);
+  static const char* who = "egs_exchange_sum";
+  if (L.grads_mc) return launch_exchange(who, exchange_mc_kernel<false>, L, max_ctas, st);
+  if (L.world <= 2) return launch_exchange(who, exchange_kernel<false, 2>, L, max_ctas, st);
+  if (L.world <= 4) return launch_exchange(who, exchange_kernel<false, 4>, L, max_ctas, st);
+  return launch_exchange(who, exchange_kernel<false, 8>, L, max_ctas, st);
+}
+
+extern "C" int egs_exchange_set_timeout_ms(unsigned long long ms) {
+  using namespace egs;
+  if (ms == 0) {
+    set_error("egs_exchange_set_timeout_ms: the timeout must be positive");
+    return EGS_ERR_INVALID_ARGUMENT;
+  }
+  g_timeout_ns.store(ms * 1000000ull, std::memory_order_relaxed);
   return EGS_OK;
 }
 
@@ -357,11 +430,8 @@ extern "C" int egs_exchange_adam_step(const EgsPeerGroup* group, const EgsExchan
   // through the switch only when both buffers have a multicast mapping
   L.params_mc = adam->params_multicast;
   if (!L.params_mc || (reinterpret_cast<uintptr_t>(L.params_mc) & 15u)) L.grads_mc = L.params_mc = nullptr;
-  const unsigned grid = exchange_grid(L, max_ctas);
-  if (L.grads_mc) exchange_mc_kernel<true><<<grid, EX_THREADS, 0, st>>>(L);
-  else if (L.world <= 2) exchange_kernel<true, 2><<<grid, EX_THREADS, 0, st>>>(L);
-  else if (L.world <= 4) exchange_kernel<true, 4><<<grid, EX_THREADS, 0, st>>>(L);
-  else exchange_kernel<true, 8><<<grid, EX_THREADS, 0, st>>>(L);
-  EGS_AFTER_LAUNCH(st, false);
-  return EGS_OK;
+  if (L.grads_mc) return launch_exchange(who, exchange_mc_kernel<true>, L, max_ctas, st);
+  if (L.world <= 2) return launch_exchange(who, exchange_kernel<true, 2>, L, max_ctas, st);
+  if (L.world <= 4) return launch_exchange(who, exchange_kernel<true, 4>, L, max_ctas, st);
+  return launch_exchange(who, exchange_kernel<true, 8>, L, max_ctas, st);
 }

@@ -133,7 +133,7 @@ preprocess_forward_kernel(RawModel raw, int P, int D, int M, const float* __rest
                           float* __restrict__ depths, float4* __restrict__ conic_opacity,
                           float4* __restrict__ rgb_depth, unsigned char* __restrict__ clamped,
                           uint32_t* __restrict__ tiles_touched, int prefiltered,
-                          int* __restrict__ prefilter_fault) {
+                          uint32_t* __restrict__ prefilter_fault) {
   __shared__ float s_view[16], s_proj[16], s_cam[3];
   if (threadIdx.x < 16) {
     s_view[threadIdx.x] = viewmatrix[threadIdx.x];
@@ -202,7 +202,9 @@ preprocess_forward_kernel(RawModel raw, int P, int D, int M, const float* __rest
 
   // near culling: z_view <= 0.2 (auxiliary.h:150); the x/y frustum test is disabled there too
   if (p_view.z <= 0.2f) {
-    if (prefiltered && prefilter_fault) *prefilter_fault = 1;
+    // the reference prints and traps here (auxiliary.h:154-161); forward reads the flag back with the
+    // instance count and returns EGS_ERR_PREFILTERED
+    if (prefiltered) *prefilter_fault = 1u;
   } else {
     const float4 p_hom = xform_point_4x4(p_orig, s_proj);
     const float p_w = 1.0f / (p_hom.w + 0.0000001f);
@@ -264,7 +266,8 @@ mark_visible_kernel(int P, const float* __restrict__ means3D, const float* __res
   if (idx >= P) return;
   const float3 p = make_float3(means3D[3 * idx], means3D[3 * idx + 1], means3D[3 * idx + 2]);
   const float3 pv = xform_point_4x3(p, view);
-  present[idx] = pv.z > 0.2f ? 1 : 0;
+  // the reference culls with `z <= 0.2` (auxiliary.h:150), so a NaN depth counts as visible
+  present[idx] = (pv.z <= 0.2f) ? 0 : 1;
 }
 
 int launch_preprocess_forward(const EgsForwardArgs& a, const EgsModelArgs* model, const GeomPtrs& g,
@@ -273,6 +276,7 @@ int launch_preprocess_forward(const EgsForwardArgs& a, const EgsModelArgs* model
   const float focal_y = a.height / (2.0f * a.tan_fovy);
   const float focal_x = a.width / (2.0f * a.tan_fovx);
   const int blocks = (P + PF_THREADS - 1) / PF_THREADS;
+  if (a.prefiltered) EGS_CUDA_TRY(cudaMemsetAsync(g.prefilter_fault, 0, sizeof(uint32_t), stream));
   StageTimer timer(stream, ST_PREPROCESS);
   const bool staged = a.shs != nullptr && a.sh_coeffs == 16 && (reinterpret_cast<uintptr_t>(a.shs) & 15u) == 0;
   RawModel raw{};
@@ -284,7 +288,7 @@ int launch_preprocess_forward(const EgsForwardArgs& a, const EgsModelArgs* model
       a.cov3D_precomp, a.colors_precomp, a.viewmatrix, a.projmatrix, a.campos, a.width, a.height,       \
       a.tan_fovx, a.tan_fovy, focal_x, focal_y, tiles_x(a.width), tiles_y(a.height), a.radii,           \
       g.means2D, g.depths, g.conic_opacity, g.rgb_depth, g.clamped, g.tiles_touched, a.prefiltered,     \
-      nullptr
+      g.prefilter_fault
   if (split)
     preprocess_forward_kernel<2, true><<<blocks, PF_THREADS, 0, stream>>>(EGS_PF_ARGS);
   else if (model != nullptr)

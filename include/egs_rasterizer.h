@@ -59,7 +59,10 @@ typedef enum EgsStatus {
   EGS_ERR_CUDA = -2,             /* a CUDA runtime call or kernel launch failed */
   EGS_ERR_ALLOC = -3,            /* a workspace callback returned NULL */
   EGS_ERR_TOO_LARGE = -4,        /* num_rendered or P beyond the supported range */
-  EGS_ERR_PREFILTERED = -5       /* debug only: a prefiltered point was culled (auxiliary.h:154-161) */
+  EGS_ERR_PREFILTERED = -5       /* args->prefiltered was set and a Gaussian was culled all the same. The
+                                    reference prints "Point is filtered although prefiltered is set" and
+                                    traps the kernel (auxiliary.h:154-161); here the forward returns this
+                                    code with the same message, read back with the instance count */
 } EgsStatus;
 
 /* Workspace callback: must return a device pointer to at least `bytes` bytes, 256-byte
@@ -195,7 +198,8 @@ int egs_backward(const EgsBackwardArgs* args, void* stream);
 #define EGS_STATIC_SCRATCH_MAX_GAUSSIANS 262144
 int egs_backward_static_scratch(const EgsBackwardArgs* args, void* stream);
 
-/* present[i] = (view-space z of means3D[i] > 0.2), 1 byte per Gaussian (rasterizer_impl.cu:54-66). */
+/* present[i] = !(view-space z of means3D[i] <= 0.2), 1 byte per Gaussian (rasterizer_impl.cu:54-66,
+ * auxiliary.h:150: a point whose depth is NaN is reported visible, as the reference does). */
 int egs_mark_visible(int P, const float* means3D, const float* viewmatrix,
                      const float* projmatrix, unsigned char* present, void* stream);
 
@@ -259,11 +263,17 @@ typedef struct EgsPeerGroup {
 
 /* grads[p][0..n) <- scale * sum over q of grads[q][0..n), on all ranks p. n_floats % 4 == 0.
  * `epoch` is the number of this exchange: the same on all ranks, 1 at the first call and one higher at
- * every call on the same signal words (both entry points count). `max_ctas` bounds the grid (0: two per
- * SM); all kernels of one exchange must be able to run at the same time. A peer that does not show up
- * within 20 s makes the kernel give up and set signals[rank][EGS_EXCHANGE_SIGNAL_WORDS - 1] to 1. */
+ * every call on the same signal words (both entry points count). `max_ctas` bounds the grid (0: as many
+ * CTAs as the device can hold at once, from its SM count and the occupancy calculator; more than that
+ * is refused, because the flag barriers need the whole grid resident). A peer that does not show up
+ * within the timeout makes the kernel skip the exchange, leave every buffer as it was and set
+ * signals[rank][EGS_EXCHANGE_SIGNAL_WORDS - 1] to 1. */
 int egs_exchange_sum(const EgsPeerGroup* group, long long n_floats, float scale, uint32_t epoch, int max_ctas,
                      void* stream);
+/* How long an exchange kernel waits for its peers before it gives up (default 20 000 ms; process-wide,
+ * read at launch). A kernel that gave up has skipped its data phase -- gradients and parameters are
+ * left as they were -- and set the error word; the caller must check it before trusting the step. */
+int egs_exchange_set_timeout_ms(unsigned long long ms);
 
 /* One parameter group inside the flat layout: floats [begin, end), both multiples of 4. Elements whose
  * offset from `begin`, modulo `period`, is below `split` use lr_a, the others lr_b (features_dc and
@@ -484,7 +494,7 @@ typedef struct EgsGeomView {
   const uint32_t* point_offsets; /* [P] inclusive scan */
 } EgsGeomView;
 typedef struct EgsBinningView {
-  const uint64_t* keys_sorted;   /* [R] */
+  const uint64_t* keys_sorted;   /* [R]  valid only after egs_binning_keys() */
   const uint32_t* values_sorted; /* [R] */
 } EgsBinningView;
 typedef struct EgsImageView {
@@ -496,6 +506,23 @@ int egs_geom_view(const void* geom_buffer, int P, EgsGeomView* out);
 int egs_binning_view(const void* binning_buffer, int num_rendered, int width, int height,
                      EgsBinningView* out);
 int egs_image_view(const void* image_buffer, int width, int height, EgsImageView* out);
+
+/* The sorted 64-bit key list of the reference (tile << 32 | depth bits, the sorted output of
+ * cub::DeviceRadixSort::SortPairs, rasterizer_impl.cu:301-309), written into the binning blob where
+ * egs_binning_view()'s keys_sorted points. No kernel of the path reads that list (the blends walk the
+ * index list and the tile ranges), so forward does not write it; this call rebuilds it from the tile
+ * ranges, the sorted index list and the depths for the parity tests. `num_rendered` selects the layout
+ * like in egs_binning_view. */
+int egs_binning_keys(const void* geom_buffer, int P, void* binning_buffer, int num_rendered,
+                     const void* image_buffer, int width, int height, void* stream);
+
+/* Process-wide switches for tests and A/B timing; the library never reads the environment. value NULL
+ * or "" restores the default. Results never change (the parity tests run every setting):
+ *   "sort"             "packed" | "pairs" | "pairs8"   force a binning path
+ *   "presort"          "0" | "1"                       never / always sort the Gaussians front to back first
+ *   "presort_scramble" "1"                             presort by keys unrelated to depth and raise its veto
+ *   "blend_forward"    "v2"                            the two-pixels-per-thread forward blend */
+int egs_debug_option(const char* name, const char* value);
 
 /* Built-in stage timing (the reference has no profiling hooks). While
  * enabled, every stage of egs_forward / egs_backward / egs_adam_step is bracketed by CUDA events

@@ -116,6 +116,58 @@ def test_exchange_adam_step_emulated_matches_sum_then_adam(built, cuda_device):
         torch.cuda.synchronize()
 
 
+def test_exchange_adam_short_periods(built, cuda_device):
+    """Two learning rates alternating with period 1, 2 and 3 inside a segment (a 4-float chunk then
+    wraps around the period more than once): against egs_adam_step run per learning rate."""
+    from egogaussian_b200 import cabi
+    from egogaussian_b200.diff_gaussian_rasterization import _C
+    world, n = 2, 4096
+    for period, split in ((1, 1), (2, 1), (3, 2)):
+        g = EmulatedGroup(world, n, cuda_device, seed=20 + period)
+        start = torch.randn(n, generator=torch.Generator().manual_seed(period)).to(cuda_device)
+        params = [start.clone() for _ in range(world)]
+        shard = int(cabi.load().egs_exchange_shard_floats(n, world))
+        moments = [(torch.zeros(shard, device=cuda_device), torch.zeros(shard, device=cuda_device)) for _ in range(world)]
+        la, lb = 1e-2, 3e-4
+        segs = [(0, n, la, lb, period, split)]
+        summed = rank_order_sum(g.grads)
+        use_b = (torch.arange(n, device=cuda_device) % period) >= split
+        want = start.clone()
+        for lr, pick in ((la, ~use_b), (lb, use_b)):
+            p, m, v = start.clone(), torch.zeros_like(start), torch.zeros_like(start)
+            _C.adam_step([p], [summed], [m], [v], [lr], [1], 0.9, 0.999, 1e-15)
+            want[pick] = p[pick]
+        g.each_rank(lambda r, grp, e: cabi.exchange_adam_step(
+            grp, [p.data_ptr() for p in params], moments[r][0], moments[r][1], segs, n, e, 1, max_ctas=4))
+        for r in range(world):
+            assert torch.equal(params[r], want), (period, r)
+
+
+def test_exchange_gives_up_without_touching_data(built, cuda_device):
+    """A rank whose peer never arrives must not sum (or step the optimiser on) a stale buffer: after the
+    timeout the kernel skips the data phase, leaves gradients and parameters as they were and raises
+    the error word."""
+    from egogaussian_b200 import cabi
+    n = 1 << 14
+    g = EmulatedGroup(2, n, cuda_device, seed=31)
+    before = [t.clone() for t in g.grads]
+    params = [torch.randn(n, device=cuda_device) for _ in range(2)]
+    p_before = [t.clone() for t in params]
+    m, v = torch.zeros(n // 2, device=cuda_device), torch.zeros(n // 2, device=cuda_device)
+    cabi.exchange_set_timeout_ms(200)
+    try:
+        with torch.cuda.stream(g.streams[0]):   # rank 1 never launches
+            cabi.exchange_adam_step(g.groups[0], [p.data_ptr() for p in params], m, v, [(0, n, 1e-2, 0, 0, 0)], n, 1, 1,
+                                    max_ctas=4)
+        torch.cuda.synchronize()
+    finally:
+        cabi.exchange_set_timeout_ms(20000)
+    assert int(g.signals[0][-1].item()) == 1, "the error word must be set"
+    for r in range(2):
+        assert torch.equal(g.grads[r], before[r]) and torch.equal(params[r], p_before[r])
+    assert float(m.abs().max()) == 0.0 and float(v.abs().max()) == 0.0
+
+
 def test_exchange_rejects_bad_arguments(built, cuda_device):
     from egogaussian_b200 import cabi
     g = EmulatedGroup(2, 64, cuda_device)
@@ -125,6 +177,8 @@ def test_exchange_rejects_bad_arguments(built, cuda_device):
     bad.world = 9
     with pytest.raises(cabi.EgsError):
         cabi.exchange_sum(bad, 64, 1)
+    with pytest.raises(cabi.EgsError, match="resident"):  # a grid that could never be co-resident
+        cabi.exchange_sum(g.groups[0], 64, 1, max_ctas=1 << 20)
     m = torch.zeros(32, device=cuda_device)
     with pytest.raises(cabi.EgsError):                   # overlapping segments
         cabi.exchange_adam_step(g.groups[0], [t.data_ptr() for t in g.grads], m, m.clone(),

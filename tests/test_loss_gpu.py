@@ -64,3 +64,32 @@ def test_loss_full_resolution_and_python_mirror(built, cuda_device):
     loss_utils.l1_loss(a, gt[:1]).backward()
     expect = torch.sign(a.detach() - gt[:1]) / a.numel()
     assert torch.allclose(a.grad, expect, rtol=1e-6, atol=0)
+
+
+def test_loss_argument_order_of_the_trainers(built, cuda_device):
+    """fine_all.py:99-100, fine_obj.py:142-147 and coarse_obj_pose.py:252-256 call l1_loss(gt, render),
+    ssim(gt, render), l1_loss(mask, alpha) and l2_loss(alpha, mask): the gradient must reach the render
+    whichever position it is in, and nothing may be detached silently."""
+    from egogaussian_b200 import loss_utils
+    dev = cuda_device
+    gen = torch.Generator().manual_seed(2)
+    gt = torch.rand(3, 96, 128, generator=gen).to(dev)
+    base = (gt + 0.05 * torch.randn(3, 96, 128, generator=gen).to(dev)).clamp(0, 1)
+    for fn in (loss_utils.l1_loss, loss_utils.ssim):
+        a = base.clone().requires_grad_(True)
+        b = base.clone().requires_grad_(True)
+        va = fn(a, gt)
+        vb = fn(gt, b)
+        va.backward()
+        vb.backward()
+        assert va.item() == vb.item()
+        assert b.grad is not None and torch.equal(a.grad, b.grad) and float(a.grad.abs().max()) > 0
+        with pytest.raises(NotImplementedError, match="both arguments"):
+            fn(a, b)
+    alpha = torch.rand(1, 96, 128, generator=gen).to(dev).requires_grad_(True)
+    mask = (torch.rand(1, 96, 128, generator=gen) < 0.5).float().to(dev)
+    loss = loss_utils.l1_loss(mask, alpha) + loss_utils.l2_loss(alpha, mask)
+    loss.backward()
+    d = alpha.detach() - mask
+    expect = (torch.sign(d) + 2 * d) / alpha.numel()
+    assert torch.allclose(alpha.grad, expect, rtol=1e-5, atol=1e-9)

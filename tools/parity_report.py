@@ -22,29 +22,13 @@ sys.path.insert(0, str(ROOT))
 sys.path.insert(0, str(ROOT / "tests"))
 
 from egogaussian_b200 import cabi, scenes  # noqa: E402
-from helpers import grad_rel_err, run_cuda, to_np  # noqa: E402
+from helpers import BASELINE_CASES, baseline_case, grad_rel_err, run_cuda, to_np  # noqa: E402
 from oracle import cpu_oracle, ref_dgr  # noqa: E402
 from golden.make_golden import CASES, case_inputs  # noqa: E402
 
 
 def big_case(name, P, deg, W, H, seed, geom, colour):
-    sc = scenes.make_scene(P, W, H, sh_degree=deg, seed=seed)
-    cam = sc.camera
-    kw = dict(means3D=sc.means3D, opacities=sc.opacities, bg=sc.bg, viewmatrix=cam.viewmatrix,
-              projmatrix=cam.projmatrix, campos=cam.campos, tanfovx=cam.tanfovx, tanfovy=cam.tanfovy,
-              image_height=H, image_width=W, sh_degree=deg)
-    if colour == "sh":
-        kw["shs"] = sc.shs
-    else:
-        kw["colors_precomp"] = sc.colors_precomp
-    if geom == "scale_rot":
-        kw["scales"], kw["rotations"] = sc.scales, sc.rotations
-    else:
-        kw["cov3D_precomp"] = sc.cov3D()
-    wc, wd, wa = scenes.upstream_weights(W, H, seed)
-    kw = {k: (v.cuda().contiguous() if isinstance(v, torch.Tensor) else v) for k, v in kw.items()}
-    ups = dict(dL_dcolor=wc.cuda(), dL_ddepth=wd.cuda(), dL_dalpha=wa.cuda())
-    return kw, ups
+    return baseline_case(P, deg, W, H, seed, geom, colour, "cuda")
 
 
 def time_fn(fn, iters=10, warm=3):
@@ -131,13 +115,7 @@ def main():
         kw, ups = case_inputs(case, "cuda")
         reports.append(compare(case[0], kw, ups, with_cpu=True, timing=False))
         print(json.dumps(reports[-1]), flush=True)
-    big = [("c1_sh0_scale", 10_000, 0, 256, 256, 1001, "scale_rot", "sh"),
-           ("c1_sh0_cov", 10_000, 0, 256, 256, 1001, "cov", "sh")]
-    if a.big:
-        big += [("c2_sh3_scale", 100_000, 3, 1920, 1080, 2001, "scale_rot", "sh"),
-                ("c3_sh3_scale", 1_000_000, 3, 1280, 720, 3001, "scale_rot", "sh"),
-                ("c3_sh0_cov", 1_000_000, 0, 1280, 720, 3001, "cov", "sh"),
-                ("c3_rgb_cov", 1_000_000, 0, 1280, 720, 3001, "cov", "rgb")]
+    big = BASELINE_CASES if a.big else BASELINE_CASES[:2]
     for name, P, deg, W, H, seed, geom, colour in big:
         kw, ups = big_case(name, P, deg, W, H, seed, geom, colour)
         reports.append(compare(name, kw, ups, with_cpu=(P <= 100_000), timing=True))
