@@ -54,6 +54,8 @@ def parse():
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--nccl", action="store_true", help="A/B at N>1: NCCL all-reduce instead of the peer-memory exchange kernel")
+    ap.add_argument("--full-exchange", action="store_true",
+                    help="A/B at N>1: exchange the expanded [P,M,3] SH gradient instead of its factored form")
     ap.add_argument("--no-hint", action="store_true", help="A/B: exact-size forward (host waits for the count mid-way)")
     return ap.parse_args()
 
@@ -368,9 +370,13 @@ def run_ours(a, rank, world, local_rank):
             exchange = "nccl all_reduce (peer mapping failed: %s)" % str(exc)[:120]
     elif dist_on:
         exchange = "nccl all_reduce"
-    flat = parallel.FlatGrads(P, M, device, allocate=ex.allocate if ex else None)
+    # the SH gradient travels in factored form (3 floats of dL/dRGB per Gaussian and view instead of 3 M;
+    # every rank rebuilds the summed [P,M,3] tensor from all ranks' factors: csrc/exchange.cu)
+    factored = ex is not None and not a.full_exchange and M > 1
+    flat = parallel.FlatGrads(P, M, device, allocate=ex.allocate if ex else None, factored=factored)
     if ex:
-        exchange = "egs_exchange_sum, " + ("switch multicast" if ex.multicast_pointer(flat.flat) else "peer loads/stores")
+        exchange = ("egs_exchange_sum_factored, " if factored else "egs_exchange_sum, ") + \
+            ("switch multicast" if ex.multicast_pointer(flat.flat) else "peer loads/stores")
     scratch = torch.empty((cabi.load().egs_backward_scratch_bytes(P),), dtype=torch.uint8, device=device)
     state = {}
 
@@ -385,11 +391,46 @@ def run_ours(a, rank, world, local_rank):
                    "cov3D": state.setdefault("cov", torch.empty((P, 6), device=device))}
         cabi.backward(fwd, out=out, scratch=scratch, **bkw, **ups)
         if dist_on and exchange_grads:
-            if ex:
+            if factored:
+                ex.sum_factored(flat, kw["means3D"], kw["campos"], a.sh_degree)
+            elif ex:
                 ex.sum(flat.flat)
             else:
                 parallel.allreduce_gradients(flat.flat)
         state["fwd"] = fwd
+
+    def exchange_check():
+        """One more step whose exchanged gradients are compared with NCCL's all-reduce of the same
+        backward's outputs (expanded SH rows), and whose bits are compared across the ranks."""
+        step(exchange_grads=False)
+        if factored:   # the expanded rows of this rank's view, from an ordinary backward of the same forward
+            ref = parallel.FlatGrads(P, M, device)
+            cabi.backward(state["fwd"], out=ref.as_backward_out(), scratch=scratch, **bkw, **ups)
+            step(exchange_grads=False)   # fresh factors (same inputs) for the exchange under test
+        else:
+            ref = parallel.FlatGrads(P, M, device)
+            ref.flat.copy_(flat.flat)
+        dist.all_reduce(ref.flat)
+        if factored:
+            ex.sum_factored(flat, kw["means3D"], kw["campos"], a.sh_degree)
+        elif ex:
+            ex.sum(flat.flat)
+        else:
+            parallel.allreduce_gradients(flat.flat)
+        torch.cuda.synchronize()
+        worst, sig = 0.0, torch.zeros(1, dtype=torch.int64, device=device)
+        for name, want in ref.views.items():
+            got = flat.views[name]
+            worst = max(worst, float((got - want.view_as(got)).abs().max() / want.abs().max().clamp_min(1e-30)))
+            sig += got.contiguous().view(torch.int32).to(torch.int64).sum()
+        w = torch.tensor([worst], device=device, dtype=torch.float64)
+        dist.all_reduce(w, op=dist.ReduceOp.MAX)
+        sigs = [torch.zeros_like(sig) for _ in range(world)]
+        dist.all_gather(sigs, sig)
+        failed = bool(ex.failed()) if ex else False
+        return {"max_rel_err": float(w.item()), "identical_across_ranks": all(int(x) == int(sigs[0]) for x in sigs),
+                "against": "torch.distributed all_reduce (NCCL) of the expanded gradients of the same step; two "
+                           "backward runs differ by atomic order (~1e-6)", "gave_up": failed}
 
     clocks = ClockSampler(local_rank) if rank == 0 else None
     cabi.profile_enable(True)
@@ -404,6 +445,7 @@ def run_ours(a, rank, world, local_rank):
     cabi.profile_enable(False)
     clk = clocks.stop() if clocks else None
     value = world * a.steps / sec
+    xcheck = exchange_check() if dist_on else None
 
     fwd = state["fwd"]
     R = fwd.num_rendered
@@ -445,6 +487,8 @@ def run_ours(a, rank, world, local_rank):
                                                                   "cov3D_precomp") if k in kw}
         loop = HostLoop(host, device)
         h2d = loop.bytes_in()
+        # the autograd surface returns the expanded SH gradient: its exchange uses a full-size buffer
+        flat_e2e = parallel.FlatGrads(P, M, device, allocate=ex.allocate) if (ex and factored) else flat
 
         def e2e_step():
             # the big host inputs (the upstream-gradient images, standing in for the ground-truth
@@ -462,8 +506,8 @@ def run_ours(a, rank, world, local_rank):
             loss.backward()
             if dist_on and ex and all(k in LEAF_TO_FLAT for k in leaves):   # gather the autograd gradients into the peer-mapped flat buffer, one exchange
                 for k, t in leaves.items():
-                    flat.views[LEAF_TO_FLAT[k]].copy_(t.grad.view_as(flat.views[LEAF_TO_FLAT[k]]))
-                ex.sum(flat.flat)
+                    flat_e2e.views[LEAF_TO_FLAT[k]].copy_(t.grad.view_as(flat_e2e.views[LEAF_TO_FLAT[k]]))
+                ex.sum(flat_e2e.flat)
             elif dist_on:
                 for t in leaves.values():
                     dist.all_reduce(t.grad)
@@ -494,7 +538,10 @@ def run_ours(a, rank, world, local_rank):
             stepc[0] += 1
             _C.adam_step(params, grads, ms_, vs_, lrs, [stepc[0]] * len(params), 0.9, 0.999, 1e-15)
 
-        if ex:   # exchange and update in one kernel: Adam on the rank's slice, moments sharded by rank
+        adam_floats = int(sum(p_.numel() for p_ in params))
+        if factored:
+            extra["train_step_exchange"] = "egs_exchange_sum_factored, then the replicated egs_adam_step on every rank"
+        elif ex:   # exchange and update in one kernel: Adam on the rank's slice, moments sharded by rank
             del params, ms_, vs_
             params_flat = ex.allocate(flat.flat.numel())
             params_flat.normal_()
@@ -512,7 +559,7 @@ def run_ours(a, rank, world, local_rank):
 
         sec3 = timed_region(train_step, a.steps, 3, dist_on, device)
         extra["train_step_iters_per_s"] = world * a.steps / sec3
-        extra["adam_floats"] = int(sum(flat.sizes[:5 if a.geom == "scale_rot" else 3]))
+        extra["adam_floats"] = adam_floats
         if ex and ex.failed():
             raise RuntimeError("a rank gave up waiting for its peers inside the exchange kernel")
     except Exception as exc:  # informational only
@@ -607,6 +654,9 @@ def run_ours(a, rank, world, local_rank):
                              "bwd": frag / (kernels["blend_bwd"]["ms_per_step"] * 1e3)},
         "extra": extra,
     }
+    if xcheck is not None:
+        line["exchange_check"] = xcheck
+        line["reference_n_gpus"] = 1   # --impl reference always runs on one GPU (the reference has no multi-GPU mode)
     if not a.no_cpu and world == 1:
         line["cpu_baseline"] = cpu_baseline(cpu_kw, weights)
     return line

@@ -55,7 +55,7 @@ class EgsBackwardArgs(C.Structure):
         ("dL_dmeans2D", c_float_p), ("dL_dcolors", c_float_p), ("dL_dopacity", c_float_p),
         ("dL_dmeans3D", c_float_p), ("dL_dcov3D", c_float_p), ("dL_dsh", c_float_p),
         ("dL_dscales", c_float_p), ("dL_drotations", c_float_p), ("debug", C.c_int),
-        ("binning_bytes", C.c_size_t), ("colors_only", C.c_int),
+        ("binning_bytes", C.c_size_t), ("colors_only", C.c_int), ("dL_drgb", C.c_void_p),
     ]
 
 
@@ -95,6 +95,11 @@ EGS_EXCHANGE_MAX_SEGMENTS = 8
 class EgsPeerGroup(C.Structure):
     _fields_ = [("world", C.c_int), ("rank", C.c_int), ("grads", C.c_void_p * EGS_MAX_PEERS),
                 ("signals", C.c_void_p * EGS_MAX_PEERS), ("grads_multicast", C.c_void_p)]
+
+
+class EgsShFactors(C.Structure):
+    _fields_ = [("P", C.c_int), ("sh_degree", C.c_int), ("sh_coeffs", C.c_int), ("means3D", C.c_void_p),
+                ("drgb", C.c_void_p * EGS_MAX_PEERS), ("campos", C.c_void_p * EGS_MAX_PEERS), ("dL_dsh", C.c_void_p)]
 
 
 class EgsExchangeSegment(C.Structure):
@@ -199,6 +204,9 @@ def load() -> C.CDLL:
     lib.egs_knn_mean_dist2.argtypes = [C.c_int, C.c_void_p, C.c_void_p, C.c_void_p, C.c_size_t, C.c_void_p]
     lib.egs_exchange_sum.restype = C.c_int
     lib.egs_exchange_sum.argtypes = [C.POINTER(EgsPeerGroup), C.c_longlong, C.c_float, C.c_uint32, C.c_int, C.c_void_p]
+    lib.egs_exchange_sum_factored.restype = C.c_int
+    lib.egs_exchange_sum_factored.argtypes = [C.POINTER(EgsPeerGroup), C.c_longlong, C.POINTER(EgsShFactors), C.c_float,
+                                              C.c_uint32, C.c_int, C.c_void_p]
     lib.egs_exchange_shard_floats.restype = C.c_longlong
     lib.egs_exchange_shard_floats.argtypes = [C.c_longlong, C.c_int]
     lib.egs_exchange_adam_step.restype = C.c_int
@@ -407,9 +415,11 @@ def forward(*, means3D, opacities, bg, viewmatrix, projmatrix, campos, tanfovx, 
 def backward(fwd: ForwardResult, *, means3D, bg, viewmatrix, projmatrix, campos, tanfovx,
              tanfovy, dL_dcolor, dL_ddepth, dL_dalpha, sh_degree=0, shs=None, colors_precomp=None,
              scales=None, rotations=None, cov3D_precomp=None, scale_modifier=1.0, debug=False,
-             stream=None, scratch=None, out=None):
+             stream=None, scratch=None, out=None, factored=False):
     """egs_backward; returns a dict of gradient tensors (absent inputs -> None). `out` may carry
-    preallocated gradient tensors under the same keys (e.g. views of one flat all-reduce buffer)."""
+    preallocated gradient tensors under the same keys (e.g. views of one flat all-reduce buffer).
+    `factored` (or an "rgb" entry in `out`): the SH gradient comes back as "rgb" [P,3], the clamp-masked
+    dL/dRGB (EgsBackwardArgs.dL_drgb), and "sh" is not written."""
     import torch
     lib = load()
     dev = means3D.device
@@ -421,11 +431,12 @@ def backward(fwd: ForwardResult, *, means3D, bg, viewmatrix, projmatrix, campos,
         "means3D": torch.empty((P, 3), **f),
         "colors": torch.empty((P, 3), **f) if colors_precomp is not None else None,
         "cov3D": torch.empty((P, 6), **f) if cov3D_precomp is not None else None,
-        "sh": torch.empty((P, M, 3), **f) if M else None,
+        "sh": torch.empty((P, M, 3), **f) if M and not factored else None,
+        "rgb": torch.empty((P, 3), **f) if M and factored else None,
         "scales": torch.empty((P, 3), **f) if scales is not None else None,
         "rotations": torch.empty((P, 4), **f) if rotations is not None else None,
     } if out is None else dict(out)
-    for key in ("colors", "cov3D", "sh", "scales", "rotations"):
+    for key in ("colors", "cov3D", "sh", "rgb", "scales", "rotations"):
         g.setdefault(key, None)
     if P == 0:
         return g
@@ -447,7 +458,7 @@ def backward(fwd: ForwardResult, *, means3D, bg, viewmatrix, projmatrix, campos,
     a.dL_dout_color, a.dL_dout_depth, a.dL_dout_alpha = _ptr(dL_dcolor), _ptr(dL_ddepth), _ptr(dL_dalpha)
     a.scratch = scratch.data_ptr()
     a.dL_dmeans2D, a.dL_dopacity, a.dL_dmeans3D = g["means2D"].data_ptr(), g["opacity"].data_ptr(), g["means3D"].data_ptr()
-    for key, field in (("colors", "dL_dcolors"), ("cov3D", "dL_dcov3D"), ("sh", "dL_dsh"),
+    for key, field in (("colors", "dL_dcolors"), ("cov3D", "dL_dcov3D"), ("sh", "dL_dsh"), ("rgb", "dL_drgb"),
                        ("scales", "dL_dscales"), ("rotations", "dL_drotations")):
         setattr(a, field, g[key].data_ptr() if g[key] is not None else None)
     a.debug = int(debug)
@@ -664,6 +675,19 @@ def exchange_sum(group: EgsPeerGroup, n_floats: int, epoch: int, scale: float = 
     """egs_exchange_sum: every rank's flat gradient buffer <- scale * the sum over ranks."""
     _check(load().egs_exchange_sum(C.byref(group), n_floats, scale, epoch, max_ctas, _stream_handle(stream)),
            "egs_exchange_sum")
+
+
+def exchange_sum_factored(group: EgsPeerGroup, n_floats: int, epoch: int, *, means3D, drgb_ptrs, campos_ptrs, dL_dsh,
+                          sh_degree: int, scale: float = 1.0, max_ctas: int = 0, stream=None) -> None:
+    """egs_exchange_sum_factored: the flat buffer of the small gradients is summed over the ranks, and
+    dL_dsh [P,M,3] (local) <- sum over ranks of basis(rank's camera) x rank's dL/dRGB."""
+    f = EgsShFactors()
+    f.P, f.sh_degree, f.sh_coeffs = int(dL_dsh.shape[0]), int(sh_degree), int(dL_dsh.shape[1])
+    f.means3D, f.dL_dsh = _ptr(means3D), dL_dsh.data_ptr()
+    for q in range(group.world):
+        f.drgb[q], f.campos[q] = int(drgb_ptrs[q]), int(campos_ptrs[q])
+    _check(load().egs_exchange_sum_factored(C.byref(group), n_floats, C.byref(f), scale, epoch, max_ctas,
+                                            _stream_handle(stream)), "egs_exchange_sum_factored")
 
 
 def exchange_adam_step(group: EgsPeerGroup, param_ptrs, exp_avg, exp_avg_sq, segments, n_floats: int, epoch: int,

@@ -383,7 +383,7 @@ static int backward_impl(const char* who, const EgsBackwardArgs* args, const Egs
       return rc;
     if (!grads || !grads->d_scaling_raw || !grads->d_rotation_raw || !grads->d_opacity_raw ||
         (reinterpret_cast<uintptr_t>(grads->d_rotation_raw) & 15u) != 0 ||
-        (!a.colors_precomp && (!grads->d_features_dc || (model->sh_coeffs > 1 && !grads->d_features_rest)))) {
+        (!a.colors_precomp && !a.dL_drgb && (!grads->d_features_dc || (model->sh_coeffs > 1 && !grads->d_features_rest)))) {
       set_error("%s: missing raw-parameter gradient output (d_rotation_raw must be 16-byte aligned)", who);
       return EGS_ERR_INVALID_ARGUMENT;
     }
@@ -398,12 +398,16 @@ static int backward_impl(const char* who, const EgsBackwardArgs* args, const Egs
     set_error("%s: NULL required argument", who);
     return EGS_ERR_INVALID_ARGUMENT;
   }
+  if (a.dL_drgb && (a.colors_precomp || a.colors_only)) {
+    set_error("%s: dL_drgb (factored SH gradient) needs SH colours", who);
+    return EGS_ERR_INVALID_ARGUMENT;
+  }
   if (a.colors_only && (!a.colors_precomp || model != nullptr)) {
     set_error("%s: colors_only needs colors_precomp (and is not a raw-parameter mode)", who);
     return EGS_ERR_INVALID_ARGUMENT;
   }
   if ((a.colors_precomp && !a.dL_dcolors) ||
-      (!a.colors_only && ((a.cov3D_precomp && !a.dL_dcov3D) || (a.shs && !a.dL_dsh) ||
+      (!a.colors_only && ((a.cov3D_precomp && !a.dL_dcov3D) || (a.shs && !a.dL_dsh && !a.dL_drgb) ||
                           (a.scales && (!a.dL_dscales || !a.dL_drotations))))) {
     set_error("%s: missing gradient output for a provided input", who);
     return EGS_ERR_INVALID_ARGUMENT;

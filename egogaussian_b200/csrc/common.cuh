@@ -338,6 +338,37 @@ __device__ constexpr float kSH3[7] = {-0.5900435899266435f, 2.890611442640554f,
                                       -0.4570457994644658f, 1.445305721320277f,
                                       -0.5900435899266435f};
 
+// Values of the real SH basis functions in the unit direction (x, y, z), coefficients 0 .. (deg+1)^2 - 1
+// (backward.cu:20-139 / forward.cu:20-71, grouped per coefficient). One definition for the two places
+// that need dL/dsh[k] = basis_k * dL/dRGB: the per-Gaussian backward kernel and the factored gradient
+// exchange, which must form bit-identical products.
+__device__ __forceinline__ void sh_basis_values(int deg, float x, float y, float z, float* b) {
+  b[0] = kSH0;
+  if (deg > 0) {
+    b[1] = -kSH1 * y;
+    b[2] = kSH1 * z;
+    b[3] = -kSH1 * x;
+    if (deg > 1) {
+      const float xx = x * x, yy = y * y, zz = z * z;
+      const float xy = x * y, yz = y * z, xz = x * z;
+      b[4] = kSH2[0] * xy;
+      b[5] = kSH2[1] * yz;
+      b[6] = kSH2[2] * (2.f * zz - xx - yy);
+      b[7] = kSH2[3] * xz;
+      b[8] = kSH2[4] * (xx - yy);
+      if (deg > 2) {
+        b[9] = kSH3[0] * y * (3.f * xx - yy);
+        b[10] = kSH3[1] * xy * z;
+        b[11] = kSH3[2] * y * (4.f * zz - xx - yy);
+        b[12] = kSH3[3] * z * (2.f * zz - 3.f * xx - 3.f * yy);
+        b[13] = kSH3[4] * x * (4.f * zz - xx - yy);
+        b[14] = kSH3[5] * z * (xx - yy);
+        b[15] = kSH3[6] * x * (xx - 3.f * yy);
+      }
+    }
+  }
+}
+
 // Column-major 3x3 with the same storage convention and the same product evaluation order as
 // the reference's matrix library (glm/detail/type_mat3x3.inl:486-520): entry (col c, row r) is
 // c[c][r], and (A*B)[c][r] = A[0][r]*B[c][0] + A[1][r]*B[c][1] + A[2][r]*B[c][2], summed left to

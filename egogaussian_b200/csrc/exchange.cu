@@ -19,7 +19,9 @@
 
 #include <math.h>
 #include <atomic>
+#include <map>
 #include <mutex>
+#include <utility>
 
 namespace egs {
 
@@ -71,6 +73,11 @@ __device__ __forceinline__ float4 ld_peer_f4(const float* p) {
                : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w)
                : "l"(p)
                : "memory");
+  return v;
+}
+__device__ __forceinline__ float ld_peer_f32(const float* p) {
+  float v;
+  asm volatile("ld.relaxed.sys.global.f32 %0, [%1];" : "=f"(v) : "l"(p) : "memory");
   return v;
 }
 __device__ __forceinline__ void st_peer_f4(float* p, float4 v) {
@@ -183,17 +190,14 @@ __device__ __forceinline__ int segment_of(const ExLaunch& L, long long c) {
   return si;
 }
 
-// WMAX: the smallest of 2, 4, 8 that holds `world`; a thread keeps 8 peer loads of 16 bytes in flight
-// (8 / WMAX chunks from every rank), which is what it takes to fill an NVLink with 1024 threads per SM
+// Data phase over peer loads / stores. WMAX: the smallest of 2, 4, 8 that holds `world`; a thread keeps 8
+// peer loads of 16 bytes in flight (8 / WMAX chunks from every rank), which is what it takes to fill an
+// NVLink with 1024 threads per SM.
 template <bool ADAM, int WMAX>
-__global__ void __launch_bounds__(EX_THREADS, 2) exchange_kernel(const __grid_constant__ ExLaunch L) {
+__device__ __forceinline__ void sum_slice_peer(const ExLaunch& L) {
   constexpr int U = 8 / WMAX;
-  __shared__ bool s_last;
-  __shared__ int s_timed_out;
-  const bool peers_ready = barrier_in(L, s_timed_out);
-
   const long long stride = (long long)gridDim.x * EX_THREADS * U;
-  for (long long c0 = L.lo4 + (long long)blockIdx.x * EX_THREADS * U + threadIdx.x; peers_ready && c0 < L.hi4; c0 += stride) {
+  for (long long c0 = L.lo4 + (long long)blockIdx.x * EX_THREADS * U + threadIdx.x; c0 < L.hi4; c0 += stride) {
     float4 part[U][WMAX];
 #pragma unroll
     for (int u = 0; u < U; ++u)
@@ -221,20 +225,15 @@ __global__ void __launch_bounds__(EX_THREADS, 2) exchange_kernel(const __grid_co
       store_to_all(L.grads, L.world, c, g);
     }
   }
-
-  barrier_out(L, s_last, s_timed_out);
 }
 
-// The same exchange through the switch: (world - 1) / world of the buffer crosses each link once per
-// direction instead of twice. Four reductions of 16 bytes in flight per thread.
+// The same through the switch: (world - 1) / world of the buffer crosses each link once per direction
+// instead of twice. Four reductions of 16 bytes in flight per thread.
 template <bool ADAM>
-__global__ void __launch_bounds__(EX_THREADS, 2) exchange_mc_kernel(const __grid_constant__ ExLaunch L) {
+__device__ __forceinline__ void sum_slice_mc(const ExLaunch& L) {
   constexpr int U = 4;
-  __shared__ bool s_last;
-  __shared__ int s_timed_out;
-  const bool peers_ready = barrier_in(L, s_timed_out);
   const long long stride = (long long)gridDim.x * EX_THREADS * U;
-  for (long long c0 = L.lo4 + (long long)blockIdx.x * EX_THREADS * U + threadIdx.x; peers_ready && c0 < L.hi4; c0 += stride) {
+  for (long long c0 = L.lo4 + (long long)blockIdx.x * EX_THREADS * U + threadIdx.x; c0 < L.hi4; c0 += stride) {
     float4 g[U];
 #pragma unroll
     for (int u = 0; u < U; ++u)
@@ -253,6 +252,134 @@ __global__ void __launch_bounds__(EX_THREADS, 2) exchange_mc_kernel(const __grid
       }
       st_mc_f4(L.grads_mc + 4 * c, g[u]);
     }
+  }
+}
+
+template <bool ADAM, int WMAX>
+__global__ void __launch_bounds__(EX_THREADS, 2) exchange_kernel(const __grid_constant__ ExLaunch L) {
+  __shared__ bool s_last;
+  __shared__ int s_timed_out;
+  if (barrier_in(L, s_timed_out)) sum_slice_peer<ADAM, WMAX>(L);
+  barrier_out(L, s_last, s_timed_out);
+}
+
+template <bool ADAM>
+__global__ void __launch_bounds__(EX_THREADS, 2) exchange_mc_kernel(const __grid_constant__ ExLaunch L) {
+  __shared__ bool s_last;
+  __shared__ int s_timed_out;
+  if (barrier_in(L, s_timed_out)) sum_slice_mc<ADAM>(L);
+  barrier_out(L, s_last, s_timed_out);
+}
+
+// ---------------------------------------------------------------------------------------------
+// factored SH gradient
+// ---------------------------------------------------------------------------------------------
+// dL/dsh is 12 M of the 4 (14 + 3 M) bytes a Gaussian's gradient takes (192 of 248 at SH degree 3), but
+// per view it has rank one: dL/dsh[k][c] = basis_k(direction from that view's camera) * dL/dRGB[c]. So
+// the backward of a view-data-parallel step writes the three floats of dL/dRGB (EgsBackwardArgs.dL_drgb),
+// and here every rank reads all ranks' 12 bytes per Gaussian over NVLink, evaluates each rank's basis from
+// the (replicated) positions and that rank's camera centre, and adds the products in rank order into
+// its own dL/dsh tensor. Per GPU (world - 1) * 12 bytes per Gaussian cross the link instead of 2 * 192
+// * (world - 1) / world; the products and the order of the additions are those of summing the expanded
+// rows rank by rank, so the result is the same bits. The other 14 floats per Gaussian go through the
+// ordinary slice exchange first, inside the same pair of barriers.
+struct ShFactorLaunch {
+  int P, D, M;
+  const float* means3D;
+  const float* drgb[EGS_MAX_PEERS];
+  const float* campos[EGS_MAX_PEERS];
+  float* dsh;
+};
+constexpr int SF_PITCH = 49;                         // odd: a lane walking its own row is conflict-free
+constexpr int SF_WARPS = EX_THREADS / 32;
+constexpr int SF_SMEM = SF_WARPS * (32 * SF_PITCH + EGS_MAX_PEERS * 96) * 4;
+
+__device__ __forceinline__ void expand_sh_sum(const ExLaunch& L, const ShFactorLaunch& F, float* smem) {
+  const unsigned lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  float* tile = smem + warp * (32 * SF_PITCH + EGS_MAX_PEERS * 96);
+  float* stage = tile + 32 * SF_PITCH;   // [world][96]: the warp's 32 dL/dRGB triples of every rank
+  float cam[EGS_MAX_PEERS][3];
+#pragma unroll
+  for (int q = 0; q < EGS_MAX_PEERS; ++q)
+    if (q < L.world) {
+      cam[q][0] = ld_peer_f32(F.campos[q]);   // written before the peer's flag, ordered by the acquire in barrier_in
+      cam[q][1] = ld_peer_f32(F.campos[q] + 1);
+      cam[q][2] = ld_peer_f32(F.campos[q] + 2);
+    }
+  const int groups = (F.P + 31) / 32;
+  const int row_floats = 3 * F.M;
+  for (int grp = blockIdx.x * SF_WARPS + warp; grp < groups; grp += gridDim.x * SF_WARPS) {
+    const int first = grp * 32;
+    const int rows = min(32, F.P - first);
+    // 96 floats per rank = 24 float4; the last 16-byte read of the last group may pass 3 P by up to
+    // three floats (the buffers carry four floats of padding)
+#pragma unroll
+    for (int q = 0; q < EGS_MAX_PEERS; ++q)
+      if (q < L.world && lane < 24 && (size_t)first * 3 + lane * 4 < (size_t)F.P * 3) {
+        const float4 v = ld_peer_f4(F.drgb[q] + (size_t)first * 3 + lane * 4);
+        *reinterpret_cast<float4*>(stage + q * 96 + lane * 4) = v;
+      }
+    const int idx = first + (int)lane;
+    float3 pos = make_float3(0.f, 0.f, 0.f);
+    if (idx < F.P) pos = make_float3(F.means3D[3 * idx], F.means3D[3 * idx + 1], F.means3D[3 * idx + 2]);
+    __syncwarp();
+    float acc[48];
+#pragma unroll
+    for (int k = 0; k < 48; ++k) acc[k] = 0.f;
+#pragma unroll
+    for (int q = 0; q < EGS_MAX_PEERS; ++q)
+      if (q < L.world) {
+        const float dr = stage[q * 96 + 3 * lane], dg = stage[q * 96 + 3 * lane + 1], db = stage[q * 96 + 3 * lane + 2];
+        // same expressions as sh_backward (preprocess_bwd.cu)
+        const float3 dir = make_float3(pos.x - cam[q][0], pos.y - cam[q][1], pos.z - cam[q][2]);
+        const float len = sqrtf(dir.x * dir.x + dir.y * dir.y + dir.z * dir.z);
+        const float x = dir.x / len, y = dir.y / len, z = dir.z / len;
+        float b[16];
+#pragma unroll
+        for (int k = 0; k < 16; ++k) b[k] = 0.f;
+        sh_basis_values(F.D, x, y, z, b);
+#pragma unroll
+        for (int k = 0; k < 16; ++k) {
+          // product and sum rounded separately: the sum of the ranks' expanded rows, not an FMA chain
+          const float pr = __fmul_rn(b[k], dr), pg = __fmul_rn(b[k], dg), pb = __fmul_rn(b[k], db);
+          if (q == 0) {
+            acc[3 * k] = pr; acc[3 * k + 1] = pg; acc[3 * k + 2] = pb;
+          } else {
+            acc[3 * k] = __fadd_rn(acc[3 * k], pr);
+            acc[3 * k + 1] = __fadd_rn(acc[3 * k + 1], pg);
+            acc[3 * k + 2] = __fadd_rn(acc[3 * k + 2], pb);
+          }
+        }
+      }
+    __syncwarp();   // everybody has read the staged triples
+#pragma unroll
+    for (int k = 0; k < 48; ++k)
+      if (k < row_floats) tile[lane * SF_PITCH + k] = L.scale == 1.f ? acc[k] : acc[k] * L.scale;
+    __syncwarp();
+    float* dst = F.dsh + (size_t)first * row_floats;
+    if (F.M == 16) {
+      for (int f = lane; f < rows * 12; f += 32) {
+        const int row = f / 12, k = (f % 12) * 4;
+        const float* srow = tile + row * SF_PITCH + k;
+        reinterpret_cast<float4*>(dst)[f] = make_float4(srow[0], srow[1], srow[2], srow[3]);
+      }
+    } else {
+      for (int e = lane; e < rows * row_floats; e += 32) dst[e] = tile[(e / row_floats) * SF_PITCH + e % row_floats];
+    }
+    __syncwarp();   // the tile is free for the next group
+  }
+}
+
+template <bool MC, int WMAX>
+__global__ void __launch_bounds__(EX_THREADS, 1)
+exchange_factored_kernel(const __grid_constant__ ExLaunch L, const __grid_constant__ ShFactorLaunch F) {
+  extern __shared__ __align__(16) float sf_smem[];
+  __shared__ bool s_last;
+  __shared__ int s_timed_out;
+  if (barrier_in(L, s_timed_out)) {
+    if (MC) sum_slice_mc<false>(L);
+    else sum_slice_peer<false, WMAX>(L);
+    expand_sh_sum(L, F, sf_smem);
   }
   barrier_out(L, s_last, s_timed_out);
 }
@@ -291,41 +418,41 @@ static int fill_group(const char* who, const EgsPeerGroup* g, long long n, ExLau
 // device and kernel. A caller's max_ctas beyond that is refused at once instead of timing out on the
 // GPU. (Other kernels holding SMs on other streams only delay the exchange: their CTAs retire.)
 template <typename K>
-static int resident_cta_limit(K kernel, int* limit) {
+static int resident_cta_limit(K kernel, int smem, int* limit) {
   static std::mutex mu;
-  static int cached[64] = {};
+  static std::map<std::pair<const void*, int>, int> cached;   // (kernel, device) -> CTAs
   int dev = 0;
   EGS_CUDA_TRY(cudaGetDevice(&dev));
   std::lock_guard<std::mutex> lk(mu);
-  if (dev < 0 || dev >= 64) {
-    set_error("exchange: device ordinal %d not supported", dev);
-    return EGS_ERR_INVALID_ARGUMENT;
-  }
-  if (cached[dev] == 0) {
+  const auto key = std::make_pair(reinterpret_cast<const void*>(kernel), dev);
+  auto it = cached.find(key);
+  if (it == cached.end()) {
     int sms = 0, per_sm = 0;
     EGS_CUDA_TRY(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
-    EGS_CUDA_TRY(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kernel, EX_THREADS, 0));
-    cached[dev] = sms * per_sm;
-    if (cached[dev] <= 0) {
+    if (smem > 0) EGS_CUDA_TRY(cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+    EGS_CUDA_TRY(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kernel, EX_THREADS, smem));
+    if (sms * per_sm <= 0) {
       set_error("exchange: the kernel does not fit on device %d", dev);
-      cached[dev] = 0;
       return EGS_ERR_CUDA;
     }
+    it = cached.emplace(key, sms * per_sm).first;
   }
-  *limit = cached[dev];
+  *limit = it->second;
   return EGS_OK;
 }
 
 template <typename K>
-static int exchange_grid(const char* who, K kernel, const ExLaunch& L, int max_ctas, unsigned* grid) {
+static int exchange_grid(const char* who, K kernel, int smem, const ExLaunch& L, int max_ctas, long long min_ctas,
+                         unsigned* grid) {
   int limit = 0;
-  if (int rc = resident_cta_limit(kernel, &limit)) return rc;
+  if (int rc = resident_cta_limit(kernel, smem, &limit)) return rc;
   if (max_ctas > limit) {
     set_error("%s: max_ctas %d exceeds the %d CTAs of this kernel that can be resident at once on this device", who,
               max_ctas, limit);
     return EGS_ERR_INVALID_ARGUMENT;
   }
   long long ctas = (L.hi4 - L.lo4 + EX_THREADS - 1) / EX_THREADS;   // (more than the unrolled loop needs: harmless)
+  if (ctas < min_ctas) ctas = min_ctas;
   const long long cap = max_ctas > 0 ? max_ctas : limit;
   if (ctas > cap) ctas = cap;
   *grid = (unsigned)(ctas < 1 ? 1 : ctas);   // an empty slice still takes part in the barriers
@@ -335,7 +462,7 @@ static int exchange_grid(const char* who, K kernel, const ExLaunch& L, int max_c
 template <typename K>
 static int launch_exchange(const char* who, K kernel, const ExLaunch& L, int max_ctas, cudaStream_t st) {
   unsigned grid = 0;
-  if (int rc = exchange_grid(who, kernel, L, max_ctas, &grid)) return rc;
+  if (int rc = exchange_grid(who, kernel, 0, L, max_ctas, 0, &grid)) return rc;
   kernel<<<grid, EX_THREADS, 0, st>>>(L);
   EGS_AFTER_LAUNCH(st, false);
   return EGS_OK;
@@ -362,6 +489,51 @@ extern "C" int egs_exchange_sum(const EgsPeerGroup* group, long long n_floats, f
   if (L.world <= 2) return launch_exchange(who, exchange_kernel<false, 2>, L, max_ctas, st);
   if (L.world <= 4) return launch_exchange(who, exchange_kernel<false, 4>, L, max_ctas, st);
   return launch_exchange(who, exchange_kernel<false, 8>, L, max_ctas, st);
+}
+
+template <typename K>
+static int launch_factored(const char* who, K kernel, const egs::ExLaunch& L, const egs::ShFactorLaunch& F, int max_ctas,
+                           cudaStream_t st) {
+  using namespace egs;
+  unsigned grid = 0;
+  const long long want = ((long long)F.P + 32 * SF_WARPS - 1) / (32 * SF_WARPS);   // one group of 32 Gaussians per warp
+  if (int rc = exchange_grid(who, kernel, SF_SMEM, L, max_ctas, want, &grid)) return rc;
+  kernel<<<grid, EX_THREADS, SF_SMEM, st>>>(L, F);
+  EGS_AFTER_LAUNCH(st, false);
+  return EGS_OK;
+}
+
+extern "C" int egs_exchange_sum_factored(const EgsPeerGroup* group, long long n_floats, const EgsShFactors* sh,
+                                         float scale, uint32_t epoch, int max_ctas, void* stream) {
+  using namespace egs;
+  static const char* who = "egs_exchange_sum_factored";
+  ExLaunch L = {};
+  if (int rc = fill_group(who, group, n_floats, L)) return rc;
+  if (!sh || sh->P < 0 || sh->sh_degree < 0 || sh->sh_degree > 3 || sh->sh_coeffs < (sh->sh_degree + 1) * (sh->sh_degree + 1) ||
+      sh->sh_coeffs > 16 || (sh->P > 0 && (!sh->means3D || !sh->dL_dsh)) ||
+      (reinterpret_cast<uintptr_t>(sh->dL_dsh) & 15u)) {
+    set_error("%s: bad SH description (degree 0..3, (degree+1)^2 <= sh_coeffs <= 16, means3D, 16-byte aligned dL_dsh)", who);
+    return EGS_ERR_INVALID_ARGUMENT;
+  }
+  ShFactorLaunch F = {};
+  F.P = sh->P; F.D = sh->sh_degree; F.M = sh->sh_coeffs;
+  F.means3D = sh->means3D;
+  F.dsh = sh->dL_dsh;
+  for (int q = 0; q < L.world; ++q) {
+    if (!sh->drgb[q] || !sh->campos[q] || (reinterpret_cast<uintptr_t>(sh->drgb[q]) & 15u)) {
+      set_error("%s: dL/dRGB buffer (16-byte aligned) or camera centre of rank %d missing", who, q);
+      return EGS_ERR_INVALID_ARGUMENT;
+    }
+    F.drgb[q] = sh->drgb[q];
+    F.campos[q] = sh->campos[q];
+  }
+  L.scale = scale;
+  L.epoch = epoch;
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  if (L.grads_mc) return launch_factored(who, exchange_factored_kernel<true, 2>, L, F, max_ctas, st);
+  if (L.world <= 2) return launch_factored(who, exchange_factored_kernel<false, 2>, L, F, max_ctas, st);
+  if (L.world <= 4) return launch_factored(who, exchange_factored_kernel<false, 4>, L, F, max_ctas, st);
+  return launch_factored(who, exchange_factored_kernel<false, 8>, L, F, max_ctas, st);
 }
 
 extern "C" int egs_exchange_set_timeout_ms(unsigned long long ms) {

@@ -47,8 +47,10 @@ __device__ __forceinline__ float dot(const F3& a, const F3& b) { return a.x * b.
 // dL/dmean caused by the view direction. Coefficient k is read before its gradient is written, so
 // `shp` and `dL_dsh_out` may be the same row (the staged kernel works in place in shared memory).
 // Basis functions and their derivatives are those of backward.cu:20-139, grouped per coefficient.
+// dL_dsh_out == NULL (factored mode): the rows are not formed; the caller keeps the clamp-masked
+// dL/dRGB (returned through dL_dRGB) and whoever needs dL/dsh multiplies it by the basis values.
 __device__ __forceinline__ float3 sh_backward(int deg, int M, const float3 pos, const float3 cam,
-                                              const float* shp, unsigned char clamp_bits, F3 dL_dRGB,
+                                              const float* shp, unsigned char clamp_bits, F3& dL_dRGB,
                                               float* dL_dsh_out) {
   const float3 dir_orig = make_float3(pos.x - cam.x, pos.y - cam.y, pos.z - cam.z);
   const float len = sqrtf(dir_orig.x * dir_orig.x + dir_orig.y * dir_orig.y + dir_orig.z * dir_orig.z);
@@ -58,48 +60,49 @@ __device__ __forceinline__ float3 sh_backward(int deg, int M, const float3 pos, 
   dL_dRGB.z *= (clamp_bits & 4) ? 0.f : 1.f;
 
   F3 dRGBdx = {0, 0, 0}, dRGBdy = {0, 0, 0}, dRGBdz = {0, 0, 0};
+  float basis[16];
+  sh_basis_values(deg, x, y, z, basis);
   // one coefficient: basis value b and its derivatives (bx, by, bz) with respect to the direction
   auto term = [&](int k, float b, float bx, float by, float bz) {
     const F3 c = {shp[3 * k], shp[3 * k + 1], shp[3 * k + 2]};
     dRGBdx = dRGBdx + bx * c;
     dRGBdy = dRGBdy + by * c;
     dRGBdz = dRGBdz + bz * c;
-    dL_dsh_out[3 * k] = b * dL_dRGB.x;
-    dL_dsh_out[3 * k + 1] = b * dL_dRGB.y;
-    dL_dsh_out[3 * k + 2] = b * dL_dRGB.z;
+    if (dL_dsh_out != nullptr) {
+      dL_dsh_out[3 * k] = b * dL_dRGB.x;
+      dL_dsh_out[3 * k + 1] = b * dL_dRGB.y;
+      dL_dsh_out[3 * k + 2] = b * dL_dRGB.z;
+    }
   };
-  term(0, kSH0, 0.f, 0.f, 0.f);
+  term(0, basis[0], 0.f, 0.f, 0.f);
   int written = 1;
   if (deg > 0) {
-    term(1, -kSH1 * y, 0.f, -kSH1, 0.f);
-    term(2, kSH1 * z, 0.f, 0.f, kSH1);
-    term(3, -kSH1 * x, -kSH1, 0.f, 0.f);
+    term(1, basis[1], 0.f, -kSH1, 0.f);
+    term(2, basis[2], 0.f, 0.f, kSH1);
+    term(3, basis[3], -kSH1, 0.f, 0.f);
     written = 4;
     if (deg > 1) {
       const float xx = x * x, yy = y * y, zz = z * z;
       const float xy = x * y, yz = y * z, xz = x * z;
-      term(4, kSH2[0] * xy, kSH2[0] * y, kSH2[0] * x, 0.f);
-      term(5, kSH2[1] * yz, 0.f, kSH2[1] * z, kSH2[1] * y);
-      term(6, kSH2[2] * (2.f * zz - xx - yy), kSH2[2] * 2.f * -x, kSH2[2] * 2.f * -y, kSH2[2] * 2.f * 2.f * z);
-      term(7, kSH2[3] * xz, kSH2[3] * z, 0.f, kSH2[3] * x);
-      term(8, kSH2[4] * (xx - yy), kSH2[4] * 2.f * x, kSH2[4] * 2.f * -y, 0.f);
+      term(4, basis[4], kSH2[0] * y, kSH2[0] * x, 0.f);
+      term(5, basis[5], 0.f, kSH2[1] * z, kSH2[1] * y);
+      term(6, basis[6], kSH2[2] * 2.f * -x, kSH2[2] * 2.f * -y, kSH2[2] * 2.f * 2.f * z);
+      term(7, basis[7], kSH2[3] * z, 0.f, kSH2[3] * x);
+      term(8, basis[8], kSH2[4] * 2.f * x, kSH2[4] * 2.f * -y, 0.f);
       written = 9;
       if (deg > 2) {
-        term(9, kSH3[0] * y * (3.f * xx - yy), kSH3[0] * 3.f * 2.f * xy, kSH3[0] * 3.f * (xx - yy), 0.f);
-        term(10, kSH3[1] * xy * z, kSH3[1] * yz, kSH3[1] * xz, kSH3[1] * xy);
-        term(11, kSH3[2] * y * (4.f * zz - xx - yy), kSH3[2] * -2.f * xy, kSH3[2] * (-3.f * yy + 4.f * zz - xx),
-             kSH3[2] * 4.f * 2.f * yz);
-        term(12, kSH3[3] * z * (2.f * zz - 3.f * xx - 3.f * yy), kSH3[3] * -3.f * 2.f * xz,
-             kSH3[3] * -3.f * 2.f * yz, kSH3[3] * 3.f * (2.f * zz - xx - yy));
-        term(13, kSH3[4] * x * (4.f * zz - xx - yy), kSH3[4] * (-3.f * xx + 4.f * zz - yy), kSH3[4] * -2.f * xy,
-             kSH3[4] * 4.f * 2.f * xz);
-        term(14, kSH3[5] * z * (xx - yy), kSH3[5] * 2.f * xz, kSH3[5] * -2.f * yz, kSH3[5] * (xx - yy));
-        term(15, kSH3[6] * x * (xx - 3.f * yy), kSH3[6] * 3.f * (xx - yy), kSH3[6] * -3.f * 2.f * xy, 0.f);
+        term(9, basis[9], kSH3[0] * 3.f * 2.f * xy, kSH3[0] * 3.f * (xx - yy), 0.f);
+        term(10, basis[10], kSH3[1] * yz, kSH3[1] * xz, kSH3[1] * xy);
+        term(11, basis[11], kSH3[2] * -2.f * xy, kSH3[2] * (-3.f * yy + 4.f * zz - xx), kSH3[2] * 4.f * 2.f * yz);
+        term(12, basis[12], kSH3[3] * -3.f * 2.f * xz, kSH3[3] * -3.f * 2.f * yz, kSH3[3] * 3.f * (2.f * zz - xx - yy));
+        term(13, basis[13], kSH3[4] * (-3.f * xx + 4.f * zz - yy), kSH3[4] * -2.f * xy, kSH3[4] * 4.f * 2.f * xz);
+        term(14, basis[14], kSH3[5] * 2.f * xz, kSH3[5] * -2.f * yz, kSH3[5] * (xx - yy));
+        term(15, basis[15], kSH3[6] * 3.f * (xx - yy), kSH3[6] * -3.f * 2.f * xy, 0.f);
         written = 16;
       }
     }
   }
-  for (int k = written; k < M; ++k) {
+  for (int k = written; k < M && dL_dsh_out != nullptr; ++k) {
     dL_dsh_out[3 * k] = 0.f;
     dL_dsh_out[3 * k + 1] = 0.f;
     dL_dsh_out[3 * k + 2] = 0.f;
@@ -189,7 +192,9 @@ gaussian_backward(int idx, int D, int M, const float* __restrict__ means3D, cons
                   float* __restrict__ dL_dmeans3D, float* __restrict__ dL_dcov3D,
                   float* __restrict__ dL_dscales, float* __restrict__ dL_drot,
                   // raw-parameter mode (egs_backward_raw): gradients go to the raw tensors
-                  const RawModel& raw, const float* s_rot, const EgsModelGrads& rg, float* dT, bool colors_only) {
+                  const RawModel& raw, const float* s_rot, const EgsModelGrads& rg, float* dT, bool colors_only,
+                  // factored SH gradient (EgsBackwardArgs.dL_drgb): [P,3] or NULL
+                  float* __restrict__ dL_drgb) {
   constexpr bool raw_geom = RAW;
   if (colors_only) {   // EgsBackwardArgs.colors_only: unpack the colour accumulators, nothing else
     const bool seen = radii[idx] > 0;
@@ -220,8 +225,12 @@ gaussian_backward(int idx, int D, int M, const float* __restrict__ means3D, cons
 #pragma unroll
       for (int k = 0; k < 6; ++k) dL_dcov3D[6 * idx + k] = 0.f;
     }
-    if (has_sh) {
+    if (has_sh && sh_out != nullptr) {
       for (int k = 0; k < 3 * M; ++k) sh_out[k] = 0.f;
+    }
+    if (dL_drgb != nullptr) {
+#pragma unroll
+      for (int k = 0; k < 3; ++k) dL_drgb[3 * idx + k] = 0.f;
     }
     if (scales != nullptr && !raw_geom) {
 #pragma unroll
@@ -350,9 +359,15 @@ gaussian_backward(int idx, int D, int M, const float* __restrict__ means3D, cons
   }
   // ---- colour part --------------------------------------------------------------------------
   if (has_sh) {
-    const float3 g = sh_backward(D, M, mean, make_float3(s_cam[0], s_cam[1], s_cam[2]), sh_in, clamped[idx],
-                                 F3{a2.x, a2.y, a2.z}, sh_out);
+    F3 drgb = {a2.x, a2.y, a2.z};
+    const float3 g = sh_backward(D, M, mean, make_float3(s_cam[0], s_cam[1], s_cam[2]), sh_in, clamped[idx], drgb,
+                                 sh_out);
     dmean.x += g.x; dmean.y += g.y; dmean.z += g.z;
+    if (dL_drgb != nullptr) {
+      dL_drgb[3 * idx + 0] = drgb.x;
+      dL_drgb[3 * idx + 1] = drgb.y;
+      dL_drgb[3 * idx + 2] = drgb.z;
+    }
   } else {
     dL_dcolors[3 * idx + 0] = a2.x;
     dL_dcolors[3 * idx + 1] = a2.y;
@@ -397,7 +412,9 @@ constexpr int SH_PITCH = 49;      // odd pitch: a lane walking its own row is co
 // SH_MODE as in the forward kernel: 0 = rows straight from global memory, 1 = staged float4 rows of
 // one contiguous [P,16,3] tensor, 2 = rows staged from / written back to the split features_dc /
 // features_rest tensors of the raw-parameter mode.
-template <int SH_MODE, bool RAW>
+// FACTORED: dL/dsh is not written (neither the rows in shared memory nor the 12 M bytes per Gaussian in
+// HBM); the clamp-masked dL/dRGB goes to dL_drgb instead (EgsBackwardArgs.dL_drgb).
+template <int SH_MODE, bool RAW, bool FACTORED>
 __global__ void __launch_bounds__(PB_THREADS, 6)
 preprocess_backward_kernel(RawModel raw, EgsModelGrads rg, int P, int D, int M, const float* __restrict__ means3D,
                            const int* __restrict__ radii, const float* __restrict__ shs,
@@ -411,7 +428,8 @@ preprocess_backward_kernel(RawModel raw, EgsModelGrads rg, int P, int D, int M, 
                            float* __restrict__ dL_dmeans2D, float* __restrict__ dL_dcolors,
                            float* __restrict__ dL_dopacity, float* __restrict__ dL_dmeans3D,
                            float* __restrict__ dL_dcov3D, float* __restrict__ dL_dsh,
-                           float* __restrict__ dL_dscales, float* __restrict__ dL_drot, bool colors_only) {
+                           float* __restrict__ dL_dscales, float* __restrict__ dL_drot, bool colors_only,
+                           float* __restrict__ dL_drgb) {
   __shared__ float view[16], proj[16], s_cam[3];
   __shared__ float s_sh[SH_MODE != 0 ? PB_WARPS * 32 * SH_PITCH : 1];
   __shared__ float s_rot[RAW ? 18 : 1];
@@ -432,7 +450,7 @@ preprocess_backward_kernel(RawModel raw, EgsModelGrads rg, int P, int D, int M, 
 #define EGS_GB_TAIL                                                                                          \
   clamped, scales, rotations, cov3D_precomp, colors_precomp, scale_modifier, view, proj, s_cam, h_x, h_y,     \
       tan_fovx, tan_fovy, acc, dL_dmeans2D, dL_dcolors, dL_dopacity, dL_dmeans3D, dL_dcov3D, dL_dscales,      \
-      dL_drot, raw, s_rot, rg, dT, colors_only
+      dL_drot, raw, s_rot, rg, dT, colors_only, FACTORED ? dL_drgb : nullptr
 
   if (SH_MODE != 0) {
     // rows [first, first + rows) of this warp
@@ -452,10 +470,10 @@ preprocess_backward_kernel(RawModel raw, EgsModelGrads rg, int P, int D, int M, 
     stage_rows_wait();
     if (idx < P) {
       float* row = tile + lane * SH_PITCH;
-      gaussian_backward<RAW>(idx, D, M, means3D, radii, row, row, true, EGS_GB_TAIL);
+      gaussian_backward<RAW>(idx, D, M, means3D, radii, row, FACTORED ? nullptr : row, true, EGS_GB_TAIL);
     }
     __syncwarp();
-    if (rows > 0) {
+    if (rows > 0 && !FACTORED) {
       if (SH_MODE == 1) {
         float4* dst = reinterpret_cast<float4*>(dL_dsh + (size_t)first * SH_ROW);
         for (int f = lane; f < rows * (SH_ROW / 4); f += 32) {
@@ -473,8 +491,8 @@ preprocess_backward_kernel(RawModel raw, EgsModelGrads rg, int P, int D, int M, 
   } else if (idx < P) {
     const bool has_sh = shs != nullptr;
     const size_t off = (size_t)idx * M * 3;
-    gaussian_backward<RAW>(idx, D, M, means3D, radii, has_sh ? shs + off : nullptr, has_sh ? dL_dsh + off : nullptr,
-                      has_sh, EGS_GB_TAIL);
+    gaussian_backward<RAW>(idx, D, M, means3D, radii, has_sh ? shs + off : nullptr,
+                           has_sh && !FACTORED ? dL_dsh + off : nullptr, has_sh, EGS_GB_TAIL);
   }
 #undef EGS_GB_TAIL
   // dL/d train_R: every thread of the CTA takes part (no early return above)
@@ -491,7 +509,7 @@ int launch_preprocess_backward(const EgsBackwardArgs& a, const EgsModelArgs* mod
   const int blocks = (a.P + PB_THREADS - 1) / PB_THREADS;
   const bool staged = a.shs != nullptr && a.sh_coeffs == 16 &&
                       (reinterpret_cast<uintptr_t>(a.shs) & 15u) == 0 &&
-                      (reinterpret_cast<uintptr_t>(a.dL_dsh) & 15u) == 0;
+                      (a.dL_drgb != nullptr || (reinterpret_cast<uintptr_t>(a.dL_dsh) & 15u) == 0);
   RawModel raw{};
   EgsModelGrads rg{};
   if (model != nullptr) {
@@ -506,15 +524,22 @@ int launch_preprocess_backward(const EgsBackwardArgs& a, const EgsModelArgs* mod
   raw, rg, a.P, a.sh_degree, sh_coeffs, a.means3D, a.radii, a.shs, g.clamped, a.scales, a.rotations,         \
       a.cov3D_precomp, a.colors_precomp, a.scale_modifier, a.viewmatrix, a.projmatrix, a.campos,      \
       focal_x, focal_y, a.tan_fovx, a.tan_fovy, s.acc, a.dL_dmeans2D, a.dL_dcolors, a.dL_dopacity,    \
-      a.dL_dmeans3D, a.dL_dcov3D, a.dL_dsh, a.dL_dscales, a.dL_drotations, a.colors_only != 0
+      a.dL_dmeans3D, a.dL_dcov3D, a.dL_dsh, a.dL_dscales, a.dL_drotations, a.colors_only != 0, a.dL_drgb
+  const bool factored = a.dL_drgb != nullptr;
+#define EGS_PB_LAUNCH(MODE, RAWMODE)                                                                          \
+  do {                                                                                                        \
+    if (factored) preprocess_backward_kernel<MODE, RAWMODE, true><<<blocks, PB_THREADS, 0, stream>>>(EGS_PB_ARGS); \
+    else preprocess_backward_kernel<MODE, RAWMODE, false><<<blocks, PB_THREADS, 0, stream>>>(EGS_PB_ARGS);     \
+  } while (0)
   if (split)
-    preprocess_backward_kernel<2, true><<<blocks, PB_THREADS, 0, stream>>>(EGS_PB_ARGS);
+    EGS_PB_LAUNCH(2, true);
   else if (model != nullptr)
-    preprocess_backward_kernel<0, true><<<blocks, PB_THREADS, 0, stream>>>(EGS_PB_ARGS);
+    EGS_PB_LAUNCH(0, true);
   else if (staged)
-    preprocess_backward_kernel<1, false><<<blocks, PB_THREADS, 0, stream>>>(EGS_PB_ARGS);
+    EGS_PB_LAUNCH(1, false);
   else
-    preprocess_backward_kernel<0, false><<<blocks, PB_THREADS, 0, stream>>>(EGS_PB_ARGS);
+    EGS_PB_LAUNCH(0, false);
+#undef EGS_PB_LAUNCH
 #undef EGS_PB_ARGS
   EGS_AFTER_LAUNCH(stream, a.debug);
   return EGS_OK;

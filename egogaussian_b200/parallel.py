@@ -24,10 +24,19 @@ class FlatGrads:
     densification statistic's input, gaussian_model.py:735-740) rides along at the end.
     """
 
-    def __init__(self, P: int, M: int, device, with_means2D: bool = True, allocate=None):
-        """`allocate(n_floats)` supplies the flat buffer (PeerExchange.allocate for peer-mapped memory)."""
-        self.layout: List[Tuple[str, Tuple[int, ...]]] = [
-            ("means3D", (P, 3)), ("sh", (P, M, 3)), ("opacity", (P, 1)), ("scales", (P, 3)), ("rotations", (P, 4))]
+    def __init__(self, P: int, M: int, device, with_means2D: bool = True, allocate=None, factored: bool = False):
+        """`allocate(n_floats)` supplies the flat buffer (PeerExchange.allocate for peer-mapped memory).
+
+        `factored`: the SH gradient leaves the flat buffer. Per view it has rank one (basis of the view
+        direction x dL/dRGB), so backward writes 3 floats per Gaussian into `rgb` (its own peer-visible
+        buffer, followed by this rank's camera centre) and PeerExchange.sum_factored rebuilds the summed
+        [P,M,3] tensor in `sh`, a plain local tensor: 17 instead of 14 + 3 M floats per Gaussian to move."""
+        self.factored = bool(factored)
+        self.P, self.M = P, M
+        self.layout: List[Tuple[str, Tuple[int, ...]]] = [("means3D", (P, 3))]
+        if not self.factored:
+            self.layout.append(("sh", (P, M, 3)))
+        self.layout += [("opacity", (P, 1)), ("scales", (P, 3)), ("rotations", (P, 4))]
         if with_means2D:
             self.layout.append(("means2D", (P, 3)))
         sizes = [int(torch.Size(s).numel()) for _, s in self.layout]
@@ -41,10 +50,22 @@ class FlatGrads:
         self.sizes = sizes
         self.views: Dict[str, torch.Tensor] = {
             name: self.flat[o:o + n].view(shape) for (name, shape), o, n in zip(self.layout, self.offsets, sizes)}
+        if self.factored:
+            # [P,3] dL/dRGB, then the camera centre (3 floats) and one float of padding: 16-byte reads of
+            # the last rows may pass 3 P
+            n_rgb = (3 * P + 3) // 4 * 4
+            self.rgb_block = (torch.zeros(n_rgb + 4, dtype=torch.float32, device=device) if allocate is None
+                              else allocate(n_rgb + 4))
+            self.views["rgb"] = self.rgb_block[:3 * P].view(P, 3)
+            self.campos = self.rgb_block[n_rgb:n_rgb + 3]
+            self.views["sh"] = torch.zeros((P, M, 3), dtype=torch.float32, device=device)
 
     def as_backward_out(self) -> Dict[str, torch.Tensor]:
+        """`out` of cabi.backward: in factored mode "rgb" replaces "sh" (which only the exchange writes)."""
         out = dict(self.views)
         out.setdefault("means2D", None)
+        if self.factored:
+            out["sh"] = None
         return out
 
     def nbytes(self) -> int:
@@ -153,6 +174,27 @@ class PeerExchange:
         self._cabi.exchange_sum(self._group_for(grads), grads.numel(), self.epoch,
                                 scale=1.0 / self.world if average else 1.0, max_ctas=max_ctas)
         return grads
+
+    def sum_factored(self, layout: "FlatGrads", means3D: torch.Tensor, campos: torch.Tensor, sh_degree: int,
+                     average: bool = False, max_ctas: int = 0) -> "FlatGrads":
+        """The exchange of a FlatGrads(factored=True) layout: the flat buffer of the small gradients is
+        summed in place on all ranks, and layout.views["sh"] <- sum over ranks of (SH basis in the
+        direction from that rank's camera) x (that rank's dL/dRGB). `campos` is this rank's camera
+        centre; `means3D` the replicated positions backward ran on."""
+        assert layout.factored
+        layout.campos.copy_(campos.reshape(3), non_blocking=True)
+        self.epoch += 1
+        key = ("factored", layout.rgb_block.data_ptr())
+        if key not in self._groups:
+            rgb_ptrs = self.peer_pointers(layout.rgb_block)
+            cam_off = (layout.campos.data_ptr() - layout.rgb_block.data_ptr())
+            self._groups[key] = (rgb_ptrs, [p_ + cam_off for p_ in rgb_ptrs])
+        rgb_ptrs, cam_ptrs = self._groups[key]
+        self._cabi.exchange_sum_factored(self._group_for(layout.flat), layout.flat.numel(), self.epoch,
+                                         means3D=means3D, drgb_ptrs=rgb_ptrs, campos_ptrs=cam_ptrs,
+                                         dL_dsh=layout.views["sh"], sh_degree=sh_degree,
+                                         scale=1.0 / self.world if average else 1.0, max_ctas=max_ctas)
+        return layout
 
     def moment_shards(self, n_floats: int):
         """This rank's zeroed Adam moments for a flat buffer of n_floats (1/world of it)."""

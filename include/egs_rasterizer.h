@@ -48,7 +48,7 @@
 extern "C" {
 #endif
 
-#define EGS_ABI_VERSION 1
+#define EGS_ABI_VERSION 2
 #define EGS_TILE_X 16          /* DGR/cuda_rasterizer/config.h:16 */
 #define EGS_TILE_Y 16          /* DGR/cuda_rasterizer/config.h:17 */
 #define EGS_NUM_CHANNELS 3     /* DGR/cuda_rasterizer/config.h:15 */
@@ -167,6 +167,13 @@ typedef struct EgsBackwardArgs {
    * NULL). This is the backward of the trainers' per-iteration label render
    * (gaussian_renderer/render_helper.py:40-66: geometry detached, the label as colour). */
   int colors_only;
+  /* Optional, with shs (or, in egs_backward_raw, the model's features): device [P,3]. When set, the
+   * SH gradient is returned in factored form: dL_drgb[i] = dL/dRGB of Gaussian i with the clamped
+   * channels zeroed, and dL_dsh (d_features_dc / d_features_rest) is NOT written and may be NULL.
+   * dL/dsh[i][k][c] = basis_k(direction from campos to means3D[i]) * dL_drgb[i][c]: 3 floats per
+   * Gaussian carry what 3 M floats would, which is what the view-data-parallel exchange sends
+   * (egs_exchange_sum_factored expands the sum over the ranks' views). */
+  float* dL_drgb;
 } EgsBackwardArgs;
 
 size_t egs_backward_scratch_bytes(int P);
@@ -270,6 +277,30 @@ typedef struct EgsPeerGroup {
  * signals[rank][EGS_EXCHANGE_SIGNAL_WORDS - 1] to 1. */
 int egs_exchange_sum(const EgsPeerGroup* group, long long n_floats, float scale, uint32_t epoch, int max_ctas,
                      void* stream);
+/* The same exchange with the SH gradient in factored form. Per view dL/dsh has rank one,
+ * dL/dsh[i][k][c] = basis_k(direction from the view's camera centre to means3D[i]) * dL/dRGB[i][c], so a
+ * view-data-parallel step lets egs_backward write the three floats of dL/dRGB (EgsBackwardArgs.dL_drgb)
+ * instead of the 3 M floats of dL/dsh, and this call
+ *   - sums the flat buffer of the OTHER gradients (group->grads, n_floats) over the ranks like
+ *     egs_exchange_sum, and
+ *   - reads every rank's dL/dRGB and camera centre, forms each rank's products with the basis evaluated
+ *     at this rank's own (replicated) means3D, and adds them in rank order into dL_dsh, a plain local
+ *     tensor: sum over ranks of the dL/dsh each rank would have written (the same products, the same
+ *     order of additions, hence the same bits as exchanging the expanded rows), times `scale`.
+ * Per GPU (world - 1) * 12 bytes per Gaussian cross NVLink for the SH part instead of about 2 * 12 M.
+ * drgb[q] / campos[q]: rank q's [P,3] (+ 4 floats of padding: the last 16-byte read may pass the end)
+ * and [3] floats in peer-mapped memory, as mapped on this rank, written before the call in stream order.
+ * Same epoch / max_ctas / timeout rules as egs_exchange_sum (one epoch counter for all three calls). */
+typedef struct EgsShFactors {
+  int P, sh_degree, sh_coeffs;
+  const float* means3D;                  /* device [P,3], this rank's copy */
+  const float* drgb[EGS_MAX_PEERS];
+  const float* campos[EGS_MAX_PEERS];
+  float* dL_dsh;                         /* device [P, sh_coeffs, 3], 16-byte aligned, every element written */
+} EgsShFactors;
+int egs_exchange_sum_factored(const EgsPeerGroup* group, long long n_floats, const EgsShFactors* sh, float scale,
+                              uint32_t epoch, int max_ctas, void* stream);
+
 /* How long an exchange kernel waits for its peers before it gives up (default 20 000 ms; process-wide,
  * read at launch). A kernel that gave up has skipped its data phase -- gradients and parameters are
  * left as they were -- and set the error word; the caller must check it before trusting the step. */

@@ -19,6 +19,7 @@ def main():
     dist.init_process_group("nccl", device_id=device)
     for multicast in (False, True):
         run(rank, world, device, multicast)
+        run_factored(rank, world, device, multicast)
     if rank == 0:
         print("exchange worker ok", flush=True)
     dist.barrier()
@@ -111,6 +112,66 @@ def run(rank, world, device, multicast):
         mb = n * 4 / 1e6
         print(f"exchange timing world={world} buffer={mb:.1f} MB {'switch multicast' if through_switch else 'peer loads/stores'}: "
               f"nccl all_reduce {t_nccl:.3f} ms, sum {t_peer:.3f} ms, sum+adam {t_fused:.3f} ms", flush=True)
+
+
+def run_factored(rank, world, device, multicast):
+    """The factored SH-gradient exchange between real GPUs: rank r renders view r; the rebuilt dL/dsh must
+    equal NCCL's all-reduce of the expanded tensors of an ordinary backward within 2e-5 of its maximum,
+    and be the same bits on every rank."""
+    from egogaussian_b200 import cabi, scenes
+    from egogaussian_b200.parallel import FlatGrads, PeerExchange
+    ex = PeerExchange(device, multicast=multicast)
+    P, deg, M, W, H = int(os.environ.get("EGS_EXCHANGE_P", "200000")), 3, 16, 640, 360
+    sc = scenes.make_scene(P, W, H, sh_degree=deg, seed=71, view=rank).to(device)
+    cam = sc.camera
+    kw = dict(means3D=sc.means3D, opacities=sc.opacities, bg=sc.bg, viewmatrix=cam.viewmatrix,
+              projmatrix=cam.projmatrix, campos=cam.campos, tanfovx=cam.tanfovx, tanfovy=cam.tanfovy,
+              image_height=H, image_width=W, sh_degree=deg, shs=sc.shs, scales=sc.scales, rotations=sc.rotations)
+    wc, wd, wa = [t.to(device) for t in scenes.upstream_weights(W, H, 71 + rank)]
+    ups = dict(dL_dcolor=wc, dL_ddepth=wd, dL_dalpha=wa)
+    bkw = {k: v for k, v in kw.items() if k not in ("opacities", "image_height", "image_width")}
+    fwd = cabi.forward(**kw)
+    full = cabi.backward(fwd, **bkw, **ups)
+    lay = FlatGrads(P, M, device, allocate=ex.allocate, factored=True)
+    if multicast and not ex.multicast_pointer(lay.flat):
+        return
+    cabi.backward(fwd, out=lay.as_backward_out(), **bkw, **ups)
+    ref_sh = full["sh"].clone()
+    dist.all_reduce(ref_sh)
+    ref_small = {k: full[k].clone() for k in ("means3D", "opacity", "scales", "rotations", "means2D")}
+    for t in ref_small.values():
+        dist.all_reduce(t)
+    ex.sum_factored(lay, sc.means3D, cam.campos, deg)
+    assert not ex.failed()
+    got = lay.views["sh"]
+    scale = ref_sh.abs().max().item()
+    # (the expanded rows come from another backward run than the factors: atomic order differs, ~1e-6)
+    assert (got - ref_sh).abs().max().item() <= 2e-5 * scale
+    for k, t in ref_small.items():
+        assert (lay.views[k] - t.view_as(lay.views[k])).abs().max().item() <= 2e-5 * max(t.abs().max().item(), 1e-30), k
+    gathered = [torch.empty_like(got) for _ in range(world)]
+    dist.all_gather(gathered, got.contiguous())
+    if not multicast:   # rank-order sums: the same bits everywhere
+        assert all(torch.equal(t, gathered[0]) for t in gathered)
+
+    def timed(fn, iters=20):
+        for _ in range(3):
+            fn()
+        torch.cuda.synchronize(); dist.barrier()
+        a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        a.record()
+        for _ in range(iters):
+            fn()
+        b.record(); torch.cuda.synchronize()
+        t = torch.tensor([a.elapsed_time(b) / iters], device=device)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return t.item()
+    t_f = timed(lambda: ex.sum_factored(lay, sc.means3D, cam.campos, deg))
+    assert not ex.failed()
+    if rank == 0:
+        print(f"factored exchange world={world} P={P} {'switch multicast' if multicast else 'peer loads/stores'}: "
+              f"{t_f:.3f} ms ({lay.flat.numel() * 4 / 1e6 + P * 12 / 1e6:.1f} MB per rank instead of "
+              f"{(lay.flat.numel() + 3 * M * P) * 4 / 1e6:.1f})", flush=True)
 
 
 if __name__ == "__main__":

@@ -24,7 +24,7 @@ def test_header_symbols_exported(built):
     for n in names:
         assert hasattr(lib, n), f"{n} declared in the header but not exported"
     assert set(cabi.EXPORTED_SYMBOLS) <= set(names)
-    assert lib.egs_abi_version() == 1
+    assert lib.egs_abi_version() == 2
 
 
 def test_workspace_sizes_are_pure_and_monotone(built):

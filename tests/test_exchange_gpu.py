@@ -116,6 +116,81 @@ def test_exchange_adam_step_emulated_matches_sum_then_adam(built, cuda_device):
         torch.cuda.synchronize()
 
 
+@pytest.mark.parametrize("world,deg,M", [(2, 3, 16), (3, 1, 4), (8, 3, 16), (4, 2, 16), (1, 0, 1)])
+def test_factored_sh_exchange_emulated(world, deg, M, built, cuda_device):
+    """egs_exchange_sum_factored against what it replaces. Every emulated rank renders another view of
+    the same scene and back-propagates twice: once the ordinary way (dL/dsh as [P,M,3]) and once in
+    factored form (dL/dRGB as [P,3]); two backward runs differ in the last bits (atomic order), so the
+    two are compared within 2e-5 of the tensor maximum. The exchange itself is exact: on every rank it
+    must give the rank-order sum of the ranks' own expansions (each taken from a one-rank exchange of
+    the same dL/dRGB), bit for bit, while the flat buffer of the other gradients is summed as by
+    egs_exchange_sum."""
+    from helpers import grad_rel_err
+    from egogaussian_b200 import cabi, scenes
+    from egogaussian_b200.parallel import FlatGrads
+    dev = cuda_device
+    P, W, H = 5000 + 7, 128, 96
+    full, rgbs, layouts, cams = [], [], [], []
+    means = None
+    for r in range(world):
+        sc = scenes.make_scene(P, W, H, sh_degree=deg, seed=61, view=r, max_sh_degree={16: 3, 4: 1, 1: 0}[M]).to(dev)
+        cam = sc.camera
+        means = sc.means3D
+        kw = dict(means3D=sc.means3D, opacities=sc.opacities, bg=sc.bg, viewmatrix=cam.viewmatrix,
+                  projmatrix=cam.projmatrix, campos=cam.campos, tanfovx=cam.tanfovx, tanfovy=cam.tanfovy,
+                  image_height=H, image_width=W, sh_degree=deg, shs=sc.shs,
+                  scales=(sc.scales * 2.0).contiguous(), rotations=sc.rotations)
+        wc, wd, wa = [t.to(dev) for t in scenes.upstream_weights(W, H, 61 + r)]
+        ups = dict(dL_dcolor=wc, dL_ddepth=wd, dL_dalpha=wa)
+        bkw = {k: v for k, v in kw.items() if k not in ("opacities", "image_height", "image_width")}
+        fwd = cabi.forward(**kw)
+        g_full = cabi.backward(fwd, **bkw, **ups)
+        lay = FlatGrads(P, M, dev, factored=True)
+        # poison: every element of the factored outputs must be written
+        for k in ("means3D", "opacity", "scales", "rotations", "means2D", "rgb"):   # (not the padding between views)
+            lay.views[k].fill_(float("nan"))
+        cabi.backward(fwd, out=lay.as_backward_out(), **bkw, **ups)
+        torch.cuda.synchronize()
+        for k in ("means3D", "opacity", "scales", "rotations", "means2D"):
+            assert grad_rel_err(lay.views[k], g_full[k].view_as(lay.views[k])) <= 2e-5, (r, k)
+        assert torch.isfinite(lay.views["rgb"]).all() and torch.isfinite(lay.flat).all()
+        full.append(g_full)
+        layouts.append(lay)
+        cams.append(cam.campos)
+        lay.campos.copy_(cam.campos)
+    assert sum(float(g["sh"].abs().max()) for g in full) > 0
+    # every rank's own expansion: a one-rank exchange of its dL/dRGB (flat buffer untouched: 0 floats)
+    own = []
+    for r in range(world):
+        sig = torch.zeros(cabi.EGS_EXCHANGE_SIGNAL_WORDS, dtype=torch.int32, device=dev)
+        solo = cabi.peer_group(1, 0, [layouts[r].flat.data_ptr()], [sig.data_ptr()])
+        out = torch.full((P, M, 3), float("nan"), device=dev)
+        cabi.exchange_sum_factored(solo, 0, 1, means3D=means, drgb_ptrs=[layouts[r].rgb_block.data_ptr()],
+                                   campos_ptrs=[layouts[r].campos.data_ptr()], dL_dsh=out, sh_degree=deg, max_ctas=2)
+        torch.cuda.synchronize()
+        assert int(sig[-1].item()) == 0
+        assert grad_rel_err(out, full[r]["sh"]) <= 2e-5, r     # the expansion is the dL/dsh backward writes
+        own.append(out)
+    want_sh = rank_order_sum(own)
+    want_flat = rank_order_sum([lay.flat for lay in layouts])
+    signals = [torch.zeros(cabi.EGS_EXCHANGE_SIGNAL_WORDS, dtype=torch.int32, device=dev) for _ in range(world)]
+    streams = [torch.cuda.Stream(dev) for _ in range(world)]
+    torch.cuda.synchronize()
+    for r in range(world):
+        grp = cabi.peer_group(world, r, [lay.flat.data_ptr() for lay in layouts], [s.data_ptr() for s in signals])
+        with torch.cuda.stream(streams[r]):
+            cabi.exchange_sum_factored(grp, layouts[r].flat.numel(), 1, means3D=means,
+                                       drgb_ptrs=[lay.rgb_block.data_ptr() for lay in layouts],
+                                       campos_ptrs=[lay.campos.data_ptr() for lay in layouts],
+                                       dL_dsh=layouts[r].views["sh"], sh_degree=deg, max_ctas=2)
+    torch.cuda.synchronize()
+    assert all(int(s[-1].item()) == 0 for s in signals)
+    for r in range(world):
+        assert torch.equal(layouts[r].flat, want_flat), r
+        got = layouts[r].views["sh"]
+        assert torch.equal(got, want_sh), (r, float((got - want_sh).abs().max()), float(want_sh.abs().max()))
+
+
 def test_exchange_adam_short_periods(built, cuda_device):
     """Two learning rates alternating with period 1, 2 and 3 inside a segment (a 4-float chunk then
     wraps around the period more than once): against egs_adam_step run per learning rate."""
