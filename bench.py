@@ -53,6 +53,7 @@ def parse():
     ap.add_argument("--geom", default="scale_rot", choices=["scale_rot", "cov"])
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
     ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--no-config3", action="store_true", help="skip the configs[3] batch step reported under extra")
     ap.add_argument("--nccl", action="store_true", help="A/B at N>1: NCCL all-reduce instead of the peer-memory exchange kernel")
     ap.add_argument("--full-exchange", action="store_true",
                     help="A/B at N>1: exchange the expanded [P,M,3] SH gradient instead of its factored form")
@@ -346,6 +347,117 @@ def cpu_baseline(cpu_kw, weights):
 
 
 # --------------------------------------------------------------------------------------------
+def run_config3(a, rank, world, device, ex):
+    """BASELINE configs[3], the fine_all dynamic stage (trainers/fine_all.py:88-128) as one optimiser
+    step over a FIXED batch of 8 views: rank r renders views r, r + N, ....
+
+        xyz' = R xyz + t on the object rows                    egs_se3_apply     (apply_trans_rot_new)
+        cov, opacity, shs = activations, L' = R L on them      egs_model_forward (get_rotated_covariance)
+        per local view: egs_forward / egs_backward on (xyz', cov, opacity, shs), factored SH gradient
+        ONE exchange over all 8 views in view order            egs_exchange_sum_factored (ViewBatch)
+        chain to the raw parameters                            egs_model_backward
+        xyz: gradient pulled back through the pose + Adam      egs_adam_se3_step (reverse_trans_rot_new)
+        the other five groups: Adam                            egs_adam_step
+
+    Returns timing, and a check of one step's summed gradients against the same batch accumulated on
+    ONE GPU (every rank renders all 8 views itself once): the sums run in view order through the same
+    kernel, so the two differ only by the atomic order inside each backward."""
+    import torch
+    import torch.distributed as dist
+    from egogaussian_b200 import cabi, parallel, scenes
+    from egogaussian_b200.diff_gaussian_rasterization import _C
+    NV = 8
+    if NV % world:
+        return {"skipped": "8 views do not divide over %d ranks" % world}
+    P, D = a.P, a.sh_degree
+    M = (D + 1) ** 2
+    sc = scenes.make_scene(P, a.width, a.height, sh_degree=D, seed=3001, view=None)
+    cams = [scenes.make_camera(a.width, a.height, yaw_deg=(k - 3.5) * 2.0, x_shift=(k - 3.5) * 0.05) for k in range(NV)]
+    op = sc.opacities.reshape(-1, 1).clamp(1e-5, 1 - 1e-5)
+    raw = {"xyz": sc.means3D, "f_dc": sc.shs[:, :1], "f_rest": sc.shs[:, 1:], "opacity": torch.log(op / (1 - op)),
+           "scaling": torch.log(sc.scales), "rotation": sc.rotations}
+    raw = {k: v.to(device).contiguous() for k, v in raw.items()}
+    is_obj = sc.is_object.to(device)
+    Rt = scenes.object_pose().to(device)
+    R_pose = Rt[:9].reshape(3, 3).contiguous()
+    bg = sc.bg.to(device)
+    model = dict(scaling_raw=raw["scaling"], rotation_raw=raw["rotation"], opacity_raw=raw["opacity"],
+                 features_dc=raw["f_dc"], features_rest=raw["f_rest"], is_object=is_obj, which_object=1, accum_R=R_pose)
+    dev_cams = [dict(viewmatrix=c.viewmatrix.to(device), projmatrix=c.projmatrix.to(device), campos=c.campos.to(device),
+                     tanfovx=c.tanfovx, tanfovy=c.tanfovy) for c in cams]
+    ups = []
+    for k in range(NV):
+        wc, wd, wa = scenes.upstream_weights(a.width, a.height, 3001 + k)
+        ups.append(dict(dL_dcolor=wc.to(device).contiguous(), dL_ddepth=wd.to(device).contiguous(),
+                        dL_dalpha=wa.to(device).contiguous()))
+    scratch = torch.empty((cabi.load().egs_backward_scratch_bytes(P),), dtype=torch.uint8, device=device)
+    names = ["f_dc", "f_rest", "opacity", "scaling", "rotation"]
+    lrs = {"xyz": 1.6e-4, "f_dc": 2.5e-3, "f_rest": 2.5e-3 / 20, "opacity": 0.05, "scaling": 5e-3, "rotation": 1e-3}
+    moments = {k: (torch.zeros_like(v), torch.zeros_like(v)) for k, v in raw.items()}
+    hints = {}
+
+    def batch_gradients(batch, views):
+        """Back-propagate `views` (global ids, one per layout of `batch`) and run the batch's one exchange."""
+        moved, _ = _C.se3_apply(raw["xyz"], is_obj, 1, Rt, torch.empty(0, device=device))
+        act = cabi.model_forward(**model)
+        for lay, v in zip(batch.layouts, views):
+            kw = dict(means3D=moved, opacities=act["opacity"], bg=bg, image_height=a.height, image_width=a.width,
+                      sh_degree=D, shs=act["shs"], cov3D_precomp=act["cov3D"], **dev_cams[v])
+            fwd = cabi.forward(num_rendered_hint=hints.get(v, 0), **kw)
+            hints[v] = int(fwd.num_rendered * 1.25) + 8192
+            bkw = {k: x for k, x in kw.items() if k not in ("opacities", "image_height", "image_width")}
+            cabi.backward(fwd, out=lay.as_backward_out(), scratch=scratch, **bkw, **ups[v])
+        res = batch.exchange(moved, [dev_cams[v]["campos"] for v in views], D)
+        return moved, res
+
+    def optimiser_step(res, step_no):
+        g = cabi.model_backward(dL_dcov3D=res.views["cov3D"], dL_dopacity=res.views["opacity"], dL_dshs=res.views["sh"],
+                                **model)
+        _C.adam_se3_step(raw["xyz"], res.views["means3D"], moments["xyz"][0], moments["xyz"][1], is_obj, 1, Rt,
+                         lrs["xyz"], step_no, 0.9, 0.999, 1e-15)
+        grads = {"f_dc": g["features_dc"], "f_rest": g["features_rest"], "opacity": g["opacity_raw"],
+                 "scaling": g["scaling_raw"], "rotation": g["rotation_raw"]}
+        _C.adam_step([raw[k] for k in names], [grads[k] for k in names], [moments[k][0] for k in names],
+                     [moments[k][1] for k in names], [lrs[k] for k in names], [step_no] * len(names), 0.9, 0.999, 1e-15)
+
+    batch = parallel.ViewBatch(NV, P, M, device, exchange=ex, geometry="cov")
+    my_views = batch.local_views
+
+    # ---- check: the distributed sums against the whole batch on this GPU alone ----
+    check = None
+    _, res = batch_gradients(batch, my_views)
+    torch.cuda.synchronize()
+    if world > 1:
+        solo = parallel.ViewBatch(NV, P, M, device, exchange=None, geometry="cov")
+        _, ref = batch_gradients(solo, list(range(NV)))
+        torch.cuda.synchronize()
+        worst = 0.0
+        for name in ("means3D", "cov3D", "opacity", "means2D", "sh"):
+            want, got = ref.views[name], res.views[name]
+            worst = max(worst, float((got - want).abs().max() / want.abs().max().clamp_min(1e-30)))
+        w = torch.tensor([worst], device=device, dtype=torch.float64)
+        dist.all_reduce(w, op=dist.ReduceOp.MAX)
+        check = {"max_rel_err_vs_single_gpu_batch": float(w.item()), "tolerance": 1e-4}
+        del solo, ref
+        torch.cuda.empty_cache()
+
+    stepc = [0]
+
+    def step():
+        _, r_ = batch_gradients(batch, my_views)
+        stepc[0] += 1
+        optimiser_step(r_, stepc[0])
+
+    steps = max(5, a.steps // 2)
+    sec = timed_region(step, steps, 3, world > 1, device)
+    if ex is not None and ex.failed():
+        raise RuntimeError("a rank gave up waiting for its peers inside the exchange kernel")
+    return {"workload": "configs[3]: 8-view batch, 10 %% object rows under the App. C pose, one exchange and one "
+                        "Adam step (xyz through the pose) per batch; %d view(s) per GPU" % (NV // world),
+            "ms_per_batch": sec / steps * 1e3, "views_per_s": NV * steps / sec, "batches_per_s": steps / sec,
+            "steps": steps, "check": check}
+
+
 LEAF_TO_FLAT = {"means3D": "means3D", "opacities": "opacity", "shs": "sh", "scales": "scales", "rotations": "rotations"}
 
 
@@ -636,6 +748,13 @@ def run_ours(a, rank, world, local_rank):
                                                                              fused_adam, False)
         except Exception as exc:  # informational only
             extra["trainer_error"] = str(exc)[:300]
+
+    if not a.no_config3:
+        try:
+            torch.cuda.empty_cache()
+            extra["config3"] = run_config3(a, rank, world, device, ex)
+        except Exception as exc:  # informational only
+            extra["config3"] = {"error": str(exc)[:300]}
 
     if rank != 0:
         return None

@@ -99,7 +99,8 @@ class EgsPeerGroup(C.Structure):
 
 class EgsShFactors(C.Structure):
     _fields_ = [("P", C.c_int), ("sh_degree", C.c_int), ("sh_coeffs", C.c_int), ("means3D", C.c_void_p),
-                ("drgb", C.c_void_p * EGS_MAX_PEERS), ("campos", C.c_void_p * EGS_MAX_PEERS), ("dL_dsh", C.c_void_p)]
+                ("drgb", C.c_void_p * EGS_MAX_PEERS), ("campos", C.c_void_p * EGS_MAX_PEERS), ("dL_dsh", C.c_void_p),
+                ("n_views", C.c_int), ("view_flat", C.c_void_p * EGS_MAX_PEERS)]
 
 
 class EgsExchangeSegment(C.Structure):
@@ -678,13 +679,18 @@ def exchange_sum(group: EgsPeerGroup, n_floats: int, epoch: int, scale: float = 
 
 
 def exchange_sum_factored(group: EgsPeerGroup, n_floats: int, epoch: int, *, means3D, drgb_ptrs, campos_ptrs, dL_dsh,
-                          sh_degree: int, scale: float = 1.0, max_ctas: int = 0, stream=None) -> None:
+                          sh_degree: int, scale: float = 1.0, max_ctas: int = 0, stream=None, view_flat_ptrs=None) -> None:
     """egs_exchange_sum_factored: the flat buffer of the small gradients is summed over the ranks, and
-    dL_dsh [P,M,3] (local) <- sum over ranks of basis(rank's camera) x rank's dL/dRGB."""
+    dL_dsh [P,M,3] (local) <- sum over ranks of basis(rank's camera) x rank's dL/dRGB. With
+    `view_flat_ptrs` the sums run over a batch of views (one entry per view in all three lists)."""
     f = EgsShFactors()
     f.P, f.sh_degree, f.sh_coeffs = int(dL_dsh.shape[0]), int(sh_degree), int(dL_dsh.shape[1])
     f.means3D, f.dL_dsh = _ptr(means3D), dL_dsh.data_ptr()
-    for q in range(group.world):
+    n = group.world if view_flat_ptrs is None else len(view_flat_ptrs)
+    f.n_views = 0 if view_flat_ptrs is None else n
+    for q in range(n):
+        if view_flat_ptrs is not None:
+            f.view_flat[q] = int(view_flat_ptrs[q])
         f.drgb[q], f.campos[q] = int(drgb_ptrs[q]), int(campos_ptrs[q])
     _check(load().egs_exchange_sum_factored(C.byref(group), n_floats, C.byref(f), scale, epoch, max_ctas,
                                             _stream_handle(stream)), "egs_exchange_sum_factored")

@@ -41,7 +41,9 @@ struct ExSegmentDev {
 
 struct ExLaunch {
   int world, rank;
-  float* grads[EGS_MAX_PEERS];
+  int n_src;                        // buffers summed: one per rank (src == grads), or one per view of a batch
+  const float* src[EGS_MAX_PEERS];
+  float* grads[EGS_MAX_PEERS];      // where the sums go: every rank's buffer
   float* params[EGS_MAX_PEERS];
   uint32_t* signals[EGS_MAX_PEERS];
   float* grads_mc;    // multicast mappings of the same buffers, or NULL
@@ -203,15 +205,15 @@ __device__ __forceinline__ void sum_slice_peer(const ExLaunch& L) {
     for (int u = 0; u < U; ++u)
 #pragma unroll
       for (int q = 0; q < WMAX; ++q)
-        if (q < L.world && c0 + u * EX_THREADS < L.hi4) part[u][q] = ld_peer_f4(L.grads[q] + 4 * (c0 + u * EX_THREADS));
+        if (q < L.n_src && c0 + u * EX_THREADS < L.hi4) part[u][q] = ld_peer_f4(L.src[q] + 4 * (c0 + u * EX_THREADS));
 #pragma unroll
     for (int u = 0; u < U; ++u) {
       const long long c = c0 + u * EX_THREADS;
       if (c >= L.hi4) break;
-      float4 g = part[u][0];   // rank order, whoever adds
+      float4 g = part[u][0];   // rank (view) order, whoever adds
 #pragma unroll
       for (int q = 1; q < WMAX; ++q)
-        if (q < L.world) {
+        if (q < L.n_src) {
           g.x += part[u][q].x; g.y += part[u][q].y; g.z += part[u][q].z; g.w += part[u][q].w;
         }
       g.x *= L.scale; g.y *= L.scale; g.z *= L.scale; g.w *= L.scale;
@@ -285,6 +287,7 @@ __global__ void __launch_bounds__(EX_THREADS, 2) exchange_mc_kernel(const __grid
 // ordinary slice exchange first, inside the same pair of barriers.
 struct ShFactorLaunch {
   int P, D, M;
+  int n;   // views: one per rank, or all views of a batch in their global order
   const float* means3D;
   const float* drgb[EGS_MAX_PEERS];
   const float* campos[EGS_MAX_PEERS];
@@ -301,7 +304,7 @@ __device__ __forceinline__ void expand_sh_sum(const ExLaunch& L, const ShFactorL
   float cam[EGS_MAX_PEERS][3];
 #pragma unroll
   for (int q = 0; q < EGS_MAX_PEERS; ++q)
-    if (q < L.world) {
+    if (q < F.n) {
       cam[q][0] = ld_peer_f32(F.campos[q]);   // written before the peer's flag, ordered by the acquire in barrier_in
       cam[q][1] = ld_peer_f32(F.campos[q] + 1);
       cam[q][2] = ld_peer_f32(F.campos[q] + 2);
@@ -315,7 +318,7 @@ __device__ __forceinline__ void expand_sh_sum(const ExLaunch& L, const ShFactorL
     // three floats (the buffers carry four floats of padding)
 #pragma unroll
     for (int q = 0; q < EGS_MAX_PEERS; ++q)
-      if (q < L.world && lane < 24 && (size_t)first * 3 + lane * 4 < (size_t)F.P * 3) {
+      if (q < F.n && lane < 24 && (size_t)first * 3 + lane * 4 < (size_t)F.P * 3) {
         const float4 v = ld_peer_f4(F.drgb[q] + (size_t)first * 3 + lane * 4);
         *reinterpret_cast<float4*>(stage + q * 96 + lane * 4) = v;
       }
@@ -328,7 +331,7 @@ __device__ __forceinline__ void expand_sh_sum(const ExLaunch& L, const ShFactorL
     for (int k = 0; k < 48; ++k) acc[k] = 0.f;
 #pragma unroll
     for (int q = 0; q < EGS_MAX_PEERS; ++q)
-      if (q < L.world) {
+      if (q < F.n) {
         const float dr = stage[q * 96 + 3 * lane], dg = stage[q * 96 + 3 * lane + 1], db = stage[q * 96 + 3 * lane + 2];
         // same expressions as sh_backward (preprocess_bwd.cu)
         const float3 dir = make_float3(pos.x - cam[q][0], pos.y - cam[q][1], pos.z - cam[q][2]);
@@ -396,8 +399,10 @@ static int fill_group(const char* who, const EgsPeerGroup* g, long long n, ExLau
       return EGS_ERR_INVALID_ARGUMENT;
     }
     L.grads[q] = g->grads[q];
+    L.src[q] = g->grads[q];
     L.signals[q] = g->signals[q];
   }
+  L.n_src = g->world;
   if (reinterpret_cast<uintptr_t>(g->grads_multicast) & 15u) {
     set_error("%s: multicast address not 16-byte aligned", who);
     return EGS_ERR_INVALID_ARGUMENT;
@@ -519,20 +524,36 @@ extern "C" int egs_exchange_sum_factored(const EgsPeerGroup* group, long long n_
   F.P = sh->P; F.D = sh->sh_degree; F.M = sh->sh_coeffs;
   F.means3D = sh->means3D;
   F.dsh = sh->dL_dsh;
-  for (int q = 0; q < L.world; ++q) {
+  if (sh->n_views < 0 || sh->n_views > EGS_MAX_PEERS) {
+    set_error("%s: n_views must be in [0, %d]", who, EGS_MAX_PEERS);
+    return EGS_ERR_INVALID_ARGUMENT;
+  }
+  F.n = sh->n_views > 0 ? sh->n_views : L.world;
+  for (int q = 0; q < F.n; ++q) {
     if (!sh->drgb[q] || !sh->campos[q] || (reinterpret_cast<uintptr_t>(sh->drgb[q]) & 15u)) {
-      set_error("%s: dL/dRGB buffer (16-byte aligned) or camera centre of rank %d missing", who, q);
+      set_error("%s: dL/dRGB buffer (16-byte aligned) or camera centre of view %d missing", who, q);
       return EGS_ERR_INVALID_ARGUMENT;
     }
     F.drgb[q] = sh->drgb[q];
     F.campos[q] = sh->campos[q];
   }
+  if (sh->n_views > 0) {   // a batch of views: their flat buffers are the sources, group->grads the destinations
+    for (int q = 0; q < F.n; ++q) {
+      if ((n_floats > 0 && !sh->view_flat[q]) || (reinterpret_cast<uintptr_t>(sh->view_flat[q]) & 15u)) {
+        set_error("%s: flat buffer of view %d missing or not 16-byte aligned", who, q);
+        return EGS_ERR_INVALID_ARGUMENT;
+      }
+      L.src[q] = sh->view_flat[q];
+    }
+    L.n_src = F.n;
+    L.grads_mc = nullptr;   // the switch reduces one buffer per rank only
+  }
   L.scale = scale;
   L.epoch = epoch;
   cudaStream_t st = static_cast<cudaStream_t>(stream);
   if (L.grads_mc) return launch_factored(who, exchange_factored_kernel<true, 2>, L, F, max_ctas, st);
-  if (L.world <= 2) return launch_factored(who, exchange_factored_kernel<false, 2>, L, F, max_ctas, st);
-  if (L.world <= 4) return launch_factored(who, exchange_factored_kernel<false, 4>, L, F, max_ctas, st);
+  if (L.n_src <= 2) return launch_factored(who, exchange_factored_kernel<false, 2>, L, F, max_ctas, st);
+  if (L.n_src <= 4) return launch_factored(who, exchange_factored_kernel<false, 4>, L, F, max_ctas, st);
   return launch_factored(who, exchange_factored_kernel<false, 8>, L, F, max_ctas, st);
 }
 

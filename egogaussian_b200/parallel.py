@@ -24,7 +24,8 @@ class FlatGrads:
     densification statistic's input, gaussian_model.py:735-740) rides along at the end.
     """
 
-    def __init__(self, P: int, M: int, device, with_means2D: bool = True, allocate=None, factored: bool = False):
+    def __init__(self, P: int, M: int, device, with_means2D: bool = True, allocate=None, factored: bool = False,
+                 geometry: str = "scale_rot"):
         """`allocate(n_floats)` supplies the flat buffer (PeerExchange.allocate for peer-mapped memory).
 
         `factored`: the SH gradient leaves the flat buffer. Per view it has rank one (basis of the view
@@ -36,7 +37,10 @@ class FlatGrads:
         self.layout: List[Tuple[str, Tuple[int, ...]]] = [("means3D", (P, 3))]
         if not self.factored:
             self.layout.append(("sh", (P, M, 3)))
-        self.layout += [("opacity", (P, 1)), ("scales", (P, 3)), ("rotations", (P, 4))]
+        # geometry "cov": the rasterizer ran on cov3D_precomp (the reference's production mode, train.py:49)
+        # and returns dL/dcov3D; the chain to scale / rotation is the model's backward (egs_model_backward)
+        self.layout.append(("opacity", (P, 1)))
+        self.layout += [("scales", (P, 3)), ("rotations", (P, 4))] if geometry == "scale_rot" else [("cov3D", (P, 6))]
         if with_means2D:
             self.layout.append(("means2D", (P, 3)))
         sizes = [int(torch.Size(s).numel()) for _, s in self.layout]
@@ -215,3 +219,63 @@ class PeerExchange:
         """True when a kernel gave up waiting for a peer (synchronises)."""
         torch.cuda.synchronize(self.device)
         return bool(self.signals.view(torch.int32)[self._cabi.EGS_EXCHANGE_SIGNAL_WORDS - 1].item())
+
+
+class ViewBatch:
+    """One training batch of `n_views` camera views spread over the ranks (BASELINE configs[3]; SURVEY.md
+    8e: rank r renders views r, r + world, ...), with ONE exchange per batch.
+
+    Every local view gets its own FlatGrads(factored=True) to back-propagate into (`layouts[j]` for the
+    rank's j-th view); `exchange()` then sums the small gradients over all views of all ranks into
+    `result.flat` views on every rank and rebuilds the summed SH gradient in `result.views["sh"]`, both in
+    the global view order, so the numbers do not depend on the number of GPUs. With one rank (or without
+    torch.distributed) it is the single-GPU accumulation of the batch through the same kernel."""
+
+    def __init__(self, n_views: int, P: int, M: int, device, exchange: "PeerExchange" = None,
+                 geometry: str = "scale_rot"):
+        from . import cabi
+        self._cabi = cabi
+        self.ex = exchange
+        self.world = exchange.world if exchange else 1
+        self.rank = exchange.rank if exchange else 0
+        if n_views > cabi.EGS_MAX_PEERS or n_views % self.world:
+            raise ValueError(f"a batch holds at most {cabi.EGS_MAX_PEERS} views, a multiple of the number of ranks")
+        self.n_views, self.device = n_views, torch.device(device)
+        self.local_views = list(views_for_rank(n_views, self.rank, self.world))
+        alloc = exchange.allocate if exchange else None
+        self.layouts = [FlatGrads(P, M, device, allocate=alloc, factored=True, geometry=geometry)
+                        for _ in self.local_views]
+        self.result = self.layouts[0]            # the sums land in the first local view's buffers
+        if exchange:
+            flat_ptrs = [exchange.peer_pointers(l.flat) for l in self.layouts]        # [local j][rank]
+            rgb_ptrs = [exchange.peer_pointers(l.rgb_block) for l in self.layouts]
+            self._signals = None
+            self._group = exchange._group_for(self.result.flat)
+        else:
+            flat_ptrs = [[l.flat.data_ptr()] for l in self.layouts]
+            rgb_ptrs = [[l.rgb_block.data_ptr()] for l in self.layouts]
+            self._signals = torch.zeros(cabi.EGS_EXCHANGE_SIGNAL_WORDS, dtype=torch.int32, device=device)
+            self._group = cabi.peer_group(1, 0, [self.result.flat.data_ptr()], [self._signals.data_ptr()])
+            self._epoch = 0
+        cam_off = self.layouts[0].campos.data_ptr() - self.layouts[0].rgb_block.data_ptr()
+        self._view_flat = [flat_ptrs[v // self.world][v % self.world] for v in range(n_views)]
+        self._view_rgb = [rgb_ptrs[v // self.world][v % self.world] for v in range(n_views)]
+        self._view_cam = [p_ + cam_off for p_ in self._view_rgb]
+
+    def exchange(self, means3D: torch.Tensor, campos: Sequence[torch.Tensor], sh_degree: int, average: bool = False,
+                 max_ctas: int = 0) -> FlatGrads:
+        """`campos[j]`: camera centre of this rank's j-th view; `means3D`: the positions backward ran on."""
+        for lay, c in zip(self.layouts, campos):
+            lay.campos.copy_(c.reshape(3), non_blocking=True)
+        if self.ex:
+            self.ex.epoch += 1
+            epoch = self.ex.epoch
+        else:
+            self._epoch += 1
+            epoch = self._epoch
+        self._cabi.exchange_sum_factored(self._group, self.result.flat.numel(), epoch, means3D=means3D,
+                                         drgb_ptrs=self._view_rgb, campos_ptrs=self._view_cam,
+                                         dL_dsh=self.result.views["sh"], sh_degree=sh_degree,
+                                         scale=1.0 / self.n_views if average else 1.0, max_ctas=max_ctas,
+                                         view_flat_ptrs=self._view_flat)
+        return self.result

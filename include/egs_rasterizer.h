@@ -290,13 +290,22 @@ int egs_exchange_sum(const EgsPeerGroup* group, long long n_floats, float scale,
  * Per GPU (world - 1) * 12 bytes per Gaussian cross NVLink for the SH part instead of about 2 * 12 M.
  * drgb[q] / campos[q]: rank q's [P,3] (+ 4 floats of padding: the last 16-byte read may pass the end)
  * and [3] floats in peer-mapped memory, as mapped on this rank, written before the call in stream order.
- * Same epoch / max_ctas / timeout rules as egs_exchange_sum (one epoch counter for all three calls). */
+ * Same epoch / max_ctas / timeout rules as egs_exchange_sum (one epoch counter for all three calls).
+ *
+ * A batch of views (BASELINE configs[3]: 8 views on 1, 2, 4 or 8 GPUs, rank r rendering views r, r + world,
+ * ...): set n_views to the size of the batch and give, for every view in its global order, the flat
+ * buffer, dL/dRGB buffer and camera centre that view's backward wrote (on whichever rank, as mapped
+ * here). The sums then run over the views in that order, so the result does not depend on how the batch
+ * was spread over the GPUs; the summed flat buffer lands in group->grads[r] on every rank r, which may be
+ * one of that rank's view buffers. world = 1 is the single-GPU accumulation of the batch. */
 typedef struct EgsShFactors {
   int P, sh_degree, sh_coeffs;
   const float* means3D;                  /* device [P,3], this rank's copy */
-  const float* drgb[EGS_MAX_PEERS];
+  const float* drgb[EGS_MAX_PEERS];      /* per rank, or per view when n_views > 0 */
   const float* campos[EGS_MAX_PEERS];
   float* dL_dsh;                         /* device [P, sh_coeffs, 3], 16-byte aligned, every element written */
+  int n_views;                           /* 0: one view per rank */
+  const float* view_flat[EGS_MAX_PEERS]; /* n_views > 0: the flat buffer of every view */
 } EgsShFactors;
 int egs_exchange_sum_factored(const EgsPeerGroup* group, long long n_floats, const EgsShFactors* sh, float scale,
                               uint32_t epoch, int max_ctas, void* stream);

@@ -191,6 +191,52 @@ def test_factored_sh_exchange_emulated(world, deg, M, built, cuda_device):
         assert torch.equal(got, want_sh), (r, float((got - want_sh).abs().max()), float(want_sh.abs().max()))
 
 
+@pytest.mark.parametrize("geometry", ["scale_rot", "cov"])
+def test_view_batch_on_one_gpu(geometry, built, cuda_device):
+    """parallel.ViewBatch without a process group: the batch of BASELINE configs[3] accumulated on one GPU
+    through the exchange kernel (world = 1, one source per view) against the view-order sum of ordinary
+    per-view backward calls."""
+    from helpers import grad_rel_err
+    from egogaussian_b200 import cabi, scenes
+    from egogaussian_b200.parallel import ViewBatch
+    dev = cuda_device
+    P, W, H, deg, NV = 6001, 160, 96, 2, 4
+    M = 9
+    sc = scenes.make_scene(P, W, H, sh_degree=deg, seed=81).to(dev)
+    cams = [scenes.make_camera(W, H, yaw_deg=(k - 1.5) * 3.0, x_shift=(k - 1.5) * 0.1) for k in range(NV)]
+    batch = ViewBatch(NV, P, M, dev, geometry=geometry)
+    assert batch.local_views == list(range(NV))
+    want = None
+    for k, (cam, lay) in enumerate(zip(cams, batch.layouts)):
+        kw = dict(means3D=sc.means3D, opacities=sc.opacities, bg=sc.bg, viewmatrix=cam.viewmatrix.to(dev),
+                  projmatrix=cam.projmatrix.to(dev), campos=cam.campos.to(dev), tanfovx=cam.tanfovx, tanfovy=cam.tanfovy,
+                  image_height=H, image_width=W, sh_degree=deg, shs=sc.shs)
+        if geometry == "scale_rot":
+            kw["scales"], kw["rotations"] = (sc.scales * 2).contiguous(), sc.rotations
+        else:
+            kw["cov3D_precomp"] = scenes.build_covariance(sc.scales * 2, sc.rotations)
+        wc, wd, wa = [t.to(dev) for t in scenes.upstream_weights(W, H, 81 + k)]
+        ups = dict(dL_dcolor=wc, dL_ddepth=wd, dL_dalpha=wa)
+        bkw = {n: v for n, v in kw.items() if n not in ("opacities", "image_height", "image_width")}
+        fwd = cabi.forward(**kw)
+        cabi.backward(fwd, out=lay.as_backward_out(), **bkw, **ups)
+        full = cabi.backward(fwd, **bkw, **ups)
+        if want is None:
+            want = {n: v.clone() for n, v in full.items() if v is not None}
+        else:
+            for n in want:
+                want[n] += full[n]
+    res = batch.exchange(sc.means3D, [c.campos.to(dev) for c in cams], deg)
+    torch.cuda.synchronize()
+    assert int(batch._signals[-1].item()) == 0
+    for n, v in want.items():
+        assert grad_rel_err(res.views[n], v.view_as(res.views[n])) <= 2e-5, n
+    # a second batch through the same buffers (the epoch advances)
+    res2 = batch.exchange(sc.means3D, [c.campos.to(dev) for c in cams], deg)
+    torch.cuda.synchronize()
+    assert grad_rel_err(res2.views["sh"], want["sh"]) <= 2e-5
+
+
 def test_exchange_adam_short_periods(built, cuda_device):
     """Two learning rates alternating with period 1, 2 and 3 inside a segment (a 4-float chunk then
     wraps around the period more than once): against egs_adam_step run per learning rate."""
