@@ -116,7 +116,7 @@ def run(rank, world, device, multicast):
 
 def run_factored(rank, world, device, multicast):
     """The factored SH-gradient exchange between real GPUs: rank r renders view r; the rebuilt dL/dsh must
-    equal NCCL's all-reduce of the expanded tensors of an ordinary backward within 2e-5 of its maximum,
+    equal NCCL's all-reduce of the expanded tensors of an ordinary backward within 1e-4 of its maximum,
     and be the same bits on every rank."""
     from egogaussian_b200 import cabi, scenes
     from egogaussian_b200.parallel import FlatGrads, PeerExchange
@@ -146,9 +146,9 @@ def run_factored(rank, world, device, multicast):
     got = lay.views["sh"]
     scale = ref_sh.abs().max().item()
     # (the expanded rows come from another backward run than the factors: atomic order differs, ~1e-6)
-    assert (got - ref_sh).abs().max().item() <= 2e-5 * scale
+    assert (got - ref_sh).abs().max().item() <= 1e-4 * scale   # north_star's gradient tolerance
     for k, t in ref_small.items():
-        assert (lay.views[k] - t.view_as(lay.views[k])).abs().max().item() <= 2e-5 * max(t.abs().max().item(), 1e-30), k
+        assert (lay.views[k] - t.view_as(lay.views[k])).abs().max().item() <= 1e-4 * max(t.abs().max().item(), 1e-30), k
     gathered = [torch.empty_like(got) for _ in range(world)]
     dist.all_gather(gathered, got.contiguous())
     if not multicast:   # rank-order sums: the same bits everywhere
