@@ -400,14 +400,14 @@ def run_config3(a, rank, world, device, ex):
         """Back-propagate `views` (global ids, one per layout of `batch`) and run the batch's one exchange."""
         moved, _ = _C.se3_apply(raw["xyz"], is_obj, 1, Rt, torch.empty(0, device=device))
         act = cabi.model_forward(**model)
-        for lay, v in zip(batch.layouts, views):
+        for j, v in enumerate(views):
             kw = dict(means3D=moved, opacities=act["opacity"], bg=bg, image_height=a.height, image_width=a.width,
                       sh_degree=D, shs=act["shs"], cov3D_precomp=act["cov3D"], **dev_cams[v])
             fwd = cabi.forward(num_rendered_hint=hints.get(v, 0), **kw)
             hints[v] = int(fwd.num_rendered * 1.25) + 8192
             bkw = {k: x for k, x in kw.items() if k not in ("opacities", "image_height", "image_width")}
-            cabi.backward(fwd, out=lay.as_backward_out(), scratch=scratch, **bkw, **ups[v])
-        res = batch.exchange(moved, [dev_cams[v]["campos"] for v in views], D)
+            cabi.backward(fwd, scratch=scratch, **batch.backward_args(j), **bkw, **ups[v])
+        res = batch.exchange(moved, D)
         return moved, res
 
     def optimiser_step(res, step_no):
@@ -485,7 +485,8 @@ def run_ours(a, rank, world, local_rank):
     # the SH gradient travels in factored form (3 floats of dL/dRGB per Gaussian and view instead of 3 M;
     # every rank rebuilds the summed [P,M,3] tensor from all ranks' factors: csrc/exchange.cu)
     factored = ex is not None and not a.full_exchange and M > 1
-    flat = parallel.FlatGrads(P, M, device, allocate=ex.allocate if ex else None, factored=factored)
+    batch = parallel.ViewBatch(world, P, M, device, exchange=ex) if factored else None
+    flat = batch.result if factored else parallel.FlatGrads(P, M, device, allocate=ex.allocate if ex else None)
     if ex:
         exchange = ("egs_exchange_sum_factored, " if factored else "egs_exchange_sum, ") + \
             ("switch multicast" if ex.multicast_pointer(flat.flat) else "peer loads/stores")
@@ -500,11 +501,12 @@ def run_ours(a, rank, world, local_rank):
         out = flat.as_backward_out()
         if a.geom != "scale_rot":
             out = {"means3D": out["means3D"], "sh": out["sh"], "opacity": out["opacity"], "means2D": out["means2D"],
-                   "cov3D": state.setdefault("cov", torch.empty((P, 6), device=device))}
-        cabi.backward(fwd, out=out, scratch=scratch, **bkw, **ups)
+                   "cov3D": state.setdefault("cov", torch.empty((P, 6), device=device)), "rgb": out.get("rgb")}
+        push = {k: v for k, v in batch.backward_args(0).items() if k != "out"} if factored else {}
+        cabi.backward(fwd, out=out, scratch=scratch, **push, **bkw, **ups)
         if dist_on and exchange_grads:
             if factored:
-                ex.sum_factored(flat, kw["means3D"], kw["campos"], a.sh_degree)
+                batch.exchange(kw["means3D"], a.sh_degree)
             elif ex:
                 ex.sum(flat.flat)
             else:
@@ -524,7 +526,7 @@ def run_ours(a, rank, world, local_rank):
             ref.flat.copy_(flat.flat)
         dist.all_reduce(ref.flat)
         if factored:
-            ex.sum_factored(flat, kw["means3D"], kw["campos"], a.sh_degree)
+            batch.exchange(kw["means3D"], a.sh_degree)
         elif ex:
             ex.sum(flat.flat)
         else:

@@ -56,6 +56,7 @@ class EgsBackwardArgs(C.Structure):
         ("dL_dmeans3D", c_float_p), ("dL_dcov3D", c_float_p), ("dL_dsh", c_float_p),
         ("dL_dscales", c_float_p), ("dL_drotations", c_float_p), ("debug", C.c_int),
         ("binning_bytes", C.c_size_t), ("colors_only", C.c_int), ("dL_drgb", C.c_void_p),
+        ("drgb_n_remote", C.c_int), ("drgb_remote", C.c_void_p * 8), ("drgb_multicast", C.c_void_p),
     ]
 
 
@@ -99,7 +100,7 @@ class EgsPeerGroup(C.Structure):
 
 class EgsShFactors(C.Structure):
     _fields_ = [("P", C.c_int), ("sh_degree", C.c_int), ("sh_coeffs", C.c_int), ("means3D", C.c_void_p),
-                ("drgb", C.c_void_p * EGS_MAX_PEERS), ("campos", C.c_void_p * EGS_MAX_PEERS), ("dL_dsh", C.c_void_p),
+                ("drgb", C.c_void_p * EGS_MAX_PEERS), ("dL_dsh", C.c_void_p),
                 ("n_views", C.c_int), ("view_flat", C.c_void_p * EGS_MAX_PEERS)]
 
 
@@ -416,11 +417,13 @@ def forward(*, means3D, opacities, bg, viewmatrix, projmatrix, campos, tanfovx, 
 def backward(fwd: ForwardResult, *, means3D, bg, viewmatrix, projmatrix, campos, tanfovx,
              tanfovy, dL_dcolor, dL_ddepth, dL_dalpha, sh_degree=0, shs=None, colors_precomp=None,
              scales=None, rotations=None, cov3D_precomp=None, scale_modifier=1.0, debug=False,
-             stream=None, scratch=None, out=None, factored=False):
+             stream=None, scratch=None, out=None, factored=False, rgb_remote=(), rgb_multicast=0):
     """egs_backward; returns a dict of gradient tensors (absent inputs -> None). `out` may carry
     preallocated gradient tensors under the same keys (e.g. views of one flat all-reduce buffer).
-    `factored` (or an "rgb" entry in `out`): the SH gradient comes back as "rgb" [P,3], the clamp-masked
-    dL/dRGB (EgsBackwardArgs.dL_drgb), and "sh" is not written."""
+    `factored` (or an "rgb" entry in `out`): the SH gradient comes back as "rgb", a slot of
+    drgb_slot_floats(P) floats holding the clamp-masked dL/dRGB rows [P,3] and the camera centre
+    (EgsBackwardArgs.dL_drgb), and "sh" is not written. `rgb_remote` / `rgb_multicast`: addresses of the
+    same slot in other ranks' gather buffers, written by the same kernel."""
     import torch
     lib = load()
     dev = means3D.device
@@ -433,7 +436,7 @@ def backward(fwd: ForwardResult, *, means3D, bg, viewmatrix, projmatrix, campos,
         "colors": torch.empty((P, 3), **f) if colors_precomp is not None else None,
         "cov3D": torch.empty((P, 6), **f) if cov3D_precomp is not None else None,
         "sh": torch.empty((P, M, 3), **f) if M and not factored else None,
-        "rgb": torch.empty((P, 3), **f) if M and factored else None,
+        "rgb": torch.empty((drgb_slot_floats(P),), **f) if M and factored else None,
         "scales": torch.empty((P, 3), **f) if scales is not None else None,
         "rotations": torch.empty((P, 4), **f) if rotations is not None else None,
     } if out is None else dict(out)
@@ -462,6 +465,10 @@ def backward(fwd: ForwardResult, *, means3D, bg, viewmatrix, projmatrix, campos,
     for key, field in (("colors", "dL_dcolors"), ("cov3D", "dL_dcov3D"), ("sh", "dL_dsh"), ("rgb", "dL_drgb"),
                        ("scales", "dL_dscales"), ("rotations", "dL_drotations")):
         setattr(a, field, g[key].data_ptr() if g[key] is not None else None)
+    a.drgb_n_remote = len(rgb_remote)
+    for q, ptr in enumerate(rgb_remote):
+        a.drgb_remote[q] = int(ptr)
+    a.drgb_multicast = int(rgb_multicast) or None
     a.debug = int(debug)
     with torch.cuda.device(dev):
         _check(lib.egs_backward(C.byref(a), _stream_handle(stream)), "egs_backward")
@@ -678,11 +685,17 @@ def exchange_sum(group: EgsPeerGroup, n_floats: int, epoch: int, scale: float = 
            "egs_exchange_sum")
 
 
-def exchange_sum_factored(group: EgsPeerGroup, n_floats: int, epoch: int, *, means3D, drgb_ptrs, campos_ptrs, dL_dsh,
+def drgb_slot_floats(P: int) -> int:
+    """EGS_DRGB_SLOT_FLOATS: [P,3] rows padded to a multiple of 4, then the camera centre and a spare float."""
+    return (3 * P + 3) // 4 * 4 + 4
+
+
+def exchange_sum_factored(group: EgsPeerGroup, n_floats: int, epoch: int, *, means3D, drgb_ptrs, dL_dsh,
                           sh_degree: int, scale: float = 1.0, max_ctas: int = 0, stream=None, view_flat_ptrs=None) -> None:
     """egs_exchange_sum_factored: the flat buffer of the small gradients is summed over the ranks, and
-    dL_dsh [P,M,3] (local) <- sum over ranks of basis(rank's camera) x rank's dL/dRGB. With
-    `view_flat_ptrs` the sums run over a batch of views (one entry per view in all three lists)."""
+    dL_dsh [P,M,3] (local) <- sum over views of basis(view's camera) x view's dL/dRGB, read from the
+    slots `drgb_ptrs` in this rank's memory. With `view_flat_ptrs` the sums run over a batch of views
+    (one entry per view in both lists)."""
     f = EgsShFactors()
     f.P, f.sh_degree, f.sh_coeffs = int(dL_dsh.shape[0]), int(sh_degree), int(dL_dsh.shape[1])
     f.means3D, f.dL_dsh = _ptr(means3D), dL_dsh.data_ptr()
@@ -691,7 +704,7 @@ def exchange_sum_factored(group: EgsPeerGroup, n_floats: int, epoch: int, *, mea
     for q in range(n):
         if view_flat_ptrs is not None:
             f.view_flat[q] = int(view_flat_ptrs[q])
-        f.drgb[q], f.campos[q] = int(drgb_ptrs[q]), int(campos_ptrs[q])
+        f.drgb[q] = int(drgb_ptrs[q])
     _check(load().egs_exchange_sum_factored(C.byref(group), n_floats, C.byref(f), scale, epoch, max_ctas,
                                             _stream_handle(stream)), "egs_exchange_sum_factored")
 

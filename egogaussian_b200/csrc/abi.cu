@@ -116,13 +116,14 @@ static HostCountSlot* host_count_slot() {
 }
 
 // ---- test / A-B switches (egs_debug_option) ---------------------------------------------------
-static std::atomic<int> g_dbg_sort{SORT_AUTO}, g_dbg_presort{-1}, g_dbg_scramble{0}, g_dbg_fwd_v2{0};
+static std::atomic<int> g_dbg_sort{SORT_AUTO}, g_dbg_presort{-1}, g_dbg_scramble{0}, g_dbg_fwd_v2{0}, g_dbg_xphases{0};
 DebugOptions debug_options() {
   DebugOptions o;
   o.sort = g_dbg_sort.load(std::memory_order_relaxed);
   o.presort = g_dbg_presort.load(std::memory_order_relaxed);
   o.presort_scramble = g_dbg_scramble.load(std::memory_order_relaxed);
   o.fwd_v2 = g_dbg_fwd_v2.load(std::memory_order_relaxed);
+  o.exchange_phases = g_dbg_xphases.load(std::memory_order_relaxed);
   return o;
 }
 
@@ -402,6 +403,17 @@ static int backward_impl(const char* who, const EgsBackwardArgs* args, const Egs
     set_error("%s: dL_drgb (factored SH gradient) needs SH colours", who);
     return EGS_ERR_INVALID_ARGUMENT;
   }
+  if (a.drgb_n_remote < 0 || a.drgb_n_remote > EGS_MAX_PEERS || ((a.drgb_n_remote > 0 || a.drgb_multicast) && !a.dL_drgb) ||
+      (reinterpret_cast<uintptr_t>(a.dL_drgb) & 15u) || (reinterpret_cast<uintptr_t>(a.drgb_multicast) & 15u)) {
+    set_error("%s: bad dL_drgb destinations (16-byte aligned slots, at most %d remote ones, dL_drgb itself set)", who,
+              EGS_MAX_PEERS);
+    return EGS_ERR_INVALID_ARGUMENT;
+  }
+  for (int q = 0; q < a.drgb_n_remote; ++q)
+    if (!a.drgb_remote[q] || (reinterpret_cast<uintptr_t>(a.drgb_remote[q]) & 15u)) {
+      set_error("%s: drgb_remote[%d] missing or not 16-byte aligned", who, q);
+      return EGS_ERR_INVALID_ARGUMENT;
+    }
   if (a.colors_only && (!a.colors_precomp || model != nullptr)) {
     set_error("%s: colors_only needs colors_precomp (and is not a raw-parameter mode)", who);
     return EGS_ERR_INVALID_ARGUMENT;
@@ -556,6 +568,8 @@ extern "C" int egs_debug_option(const char* name, const char* value) {
     g_dbg_scramble.store(unset || value[0] == '0' ? 0 : 1, std::memory_order_relaxed);
   } else if (strcmp(name, "blend_forward") == 0) {
     g_dbg_fwd_v2.store(!unset && strcmp(value, "v2") == 0 ? 1 : 0, std::memory_order_relaxed);
+  } else if (strcmp(name, "exchange_phases") == 0) {
+    g_dbg_xphases.store(unset ? 0 : (value[0] == 'a' ? 1 : 2), std::memory_order_relaxed);
   } else {
     set_error("egs_debug_option: unknown option '%s'", name);
     return EGS_ERR_INVALID_ARGUMENT;

@@ -303,6 +303,7 @@ struct DebugOptions {
   int presort;            // -1 automatic, 0 never, 1 whenever the scene has >= 64 Gaussians
   int presort_scramble;   // 1: presort keys unrelated to depth + veto raised (exercises the fallback)
   int fwd_v2;             // 1: the two-pixels-per-thread forward blend (independent implementation)
+  int exchange_phases;    // timing only: 1 = only the slice sum, 2 = only the SH expansion, 0 = both
 };
 DebugOptions debug_options();
 int launch_tile_ranges(int R, const uint64_t* sorted_keys, const ImagePtrs& im, cudaStream_t stream,

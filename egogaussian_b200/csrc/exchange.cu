@@ -231,9 +231,8 @@ __device__ __forceinline__ void sum_slice_peer(const ExLaunch& L) {
 
 // The same through the switch: (world - 1) / world of the buffer crosses each link once per direction
 // instead of twice. Four reductions of 16 bytes in flight per thread.
-template <bool ADAM>
+template <bool ADAM, int U>
 __device__ __forceinline__ void sum_slice_mc(const ExLaunch& L) {
-  constexpr int U = 4;
   const long long stride = (long long)gridDim.x * EX_THREADS * U;
   for (long long c0 = L.lo4 + (long long)blockIdx.x * EX_THREADS * U + threadIdx.x; c0 < L.hi4; c0 += stride) {
     float4 g[U];
@@ -269,7 +268,7 @@ template <bool ADAM>
 __global__ void __launch_bounds__(EX_THREADS, 2) exchange_mc_kernel(const __grid_constant__ ExLaunch L) {
   __shared__ bool s_last;
   __shared__ int s_timed_out;
-  if (barrier_in(L, s_timed_out)) sum_slice_mc<ADAM>(L);
+  if (barrier_in(L, s_timed_out)) sum_slice_mc<ADAM, 4>(L);
   barrier_out(L, s_last, s_timed_out);
 }
 
@@ -278,63 +277,91 @@ __global__ void __launch_bounds__(EX_THREADS, 2) exchange_mc_kernel(const __grid
 // ---------------------------------------------------------------------------------------------
 // dL/dsh is 12 M of the 4 (14 + 3 M) bytes a Gaussian's gradient takes (192 of 248 at SH degree 3), but
 // per view it has rank one: dL/dsh[k][c] = basis_k(direction from that view's camera) * dL/dRGB[c]. So
-// the backward of a view-data-parallel step writes the three floats of dL/dRGB (EgsBackwardArgs.dL_drgb),
-// and here every rank reads all ranks' 12 bytes per Gaussian over NVLink, evaluates each rank's basis from
-// the (replicated) positions and that rank's camera centre, and adds the products in rank order into
-// its own dL/dsh tensor. Per GPU (world - 1) * 12 bytes per Gaussian cross the link instead of 2 * 192
-// * (world - 1) / world; the products and the order of the additions are those of summing the expanded
-// rows rank by rank, so the result is the same bits. The other 14 floats per Gaussian go through the
-// ordinary slice exchange first, inside the same pair of barriers.
+// the backward of a view-data-parallel step writes the three floats of dL/dRGB (EgsBackwardArgs.dL_drgb)
+// and stores them, from inside its per-Gaussian kernel, into that view's slot of EVERY rank's gather
+// buffer (peer or multicast stores: fire and forget, overlapped with the kernel's own HBM traffic; pulling
+// them here with loads instead measured 0.5 ms at 8 GPUs, because remote loads need ~20 MB in flight to
+// fill the links and a load-then-compute loop has a fraction of that). Here every rank reads all views'
+// 12 bytes per Gaussian from its own memory, evaluates each view's basis from the (replicated) positions
+// and that view's camera centre, and adds the products in view order into its own dL/dsh tensor. Per GPU
+// (views - 1) * 12 bytes per Gaussian cross the link instead of 2 * 192 * (world - 1) / world; the
+// products and the order of the additions are those of summing the expanded rows view by view, so the
+// result is the same bits. The other 14 floats per Gaussian go through the ordinary slice exchange
+// first, inside the same pair of barriers.
 struct ShFactorLaunch {
   int P, D, M;
   int n;   // views: one per rank, or all views of a batch in their global order
+  int phases;   // timing hook: 0 both, 1 slice sum only, 2 expansion only
   const float* means3D;
-  const float* drgb[EGS_MAX_PEERS];
-  const float* campos[EGS_MAX_PEERS];
+  const float* drgb[EGS_MAX_PEERS];   // every view's slot (rows + camera centre) in THIS rank's memory
   float* dsh;
 };
 constexpr int SF_PITCH = 49;                         // odd: a lane walking its own row is conflict-free
 constexpr int SF_WARPS = EX_THREADS / 32;
-constexpr int SF_SMEM = SF_WARPS * (32 * SF_PITCH + EGS_MAX_PEERS * 96) * 4;
+constexpr int SF_STAGE = EGS_MAX_PEERS * 96;          // floats: a warp's 32 dL/dRGB triples of every view
+constexpr int SF_WARP_FLOATS = 32 * SF_PITCH + 2 * SF_STAGE;
+constexpr int SF_SMEM = (SF_WARPS * SF_WARP_FLOATS + EGS_MAX_PEERS * 4) * 4;
 
+// 16 bytes global -> shared without a register in between, cached at L2 only: the slots are written by
+// other GPUs through NVLink, and L2 is where this GPU's memory is coherent
+__device__ __forceinline__ void cp_async_16(float* smem_dst, const float* gmem_src) {
+  const uint32_t d = (uint32_t)__cvta_generic_to_shared(smem_dst);
+  asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(d), "l"(gmem_src) : "memory");
+}
+__device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
+template <int N>
+__device__ __forceinline__ void cp_async_wait() { asm volatile("cp.async.wait_group %0;" ::"n"(N) : "memory"); }
+
+// A warp takes 32 Gaussians at a time: their triples of every view (96 floats = 24 x 16 bytes per view)
+// arrive in a double-buffered stage by cp.async, one group ahead of the arithmetic; a lane accumulates
+// its Gaussian's 48 sums over the views in registers, the rows go through a tile and leave as 16-byte
+// stores.
 __device__ __forceinline__ void expand_sh_sum(const ExLaunch& L, const ShFactorLaunch& F, float* smem) {
   const unsigned lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-  float* tile = smem + warp * (32 * SF_PITCH + EGS_MAX_PEERS * 96);
-  float* stage = tile + 32 * SF_PITCH;   // [world][96]: the warp's 32 dL/dRGB triples of every rank
-  float cam[EGS_MAX_PEERS][3];
-#pragma unroll
-  for (int q = 0; q < EGS_MAX_PEERS; ++q)
-    if (q < F.n) {
-      cam[q][0] = ld_peer_f32(F.campos[q]);   // written before the peer's flag, ordered by the acquire in barrier_in
-      cam[q][1] = ld_peer_f32(F.campos[q] + 1);
-      cam[q][2] = ld_peer_f32(F.campos[q] + 2);
-    }
+  float* tile = smem + warp * SF_WARP_FLOATS;
+  float* stage = tile + 32 * SF_PITCH;                         // [2][views][96]
+  float* s_cam = smem + SF_WARPS * SF_WARP_FLOATS;             // [views][4]
+  if (threadIdx.x < (unsigned)F.n * 3) {
+    // the slots were written (by this rank's and the peers' backward kernels) before their ranks' flags:
+    // ordered by the acquire in barrier_in; sys-scope loads keep stale L1 lines out
+    const int q = threadIdx.x / 3, c = threadIdx.x % 3;
+    s_cam[4 * q + c] = ld_peer_f32(F.drgb[q] + ((size_t)F.P * 3 + 3) / 4 * 4 + c);
+  }
+  __syncthreads();
   const int groups = (F.P + 31) / 32;
   const int row_floats = 3 * F.M;
-  for (int grp = blockIdx.x * SF_WARPS + warp; grp < groups; grp += gridDim.x * SF_WARPS) {
+  const int step = gridDim.x * SF_WARPS;
+  auto fetch = [&](int grp, int buf) {
+    const size_t at = (size_t)grp * 96 + lane * 4;
+    if (grp < groups && lane < 24 && at < (size_t)F.P * 3) {   // the last 16 bytes may run into the slot's padding
+#pragma unroll
+      for (int q = 0; q < EGS_MAX_PEERS; ++q)
+        if (q < F.n) cp_async_16(stage + buf * SF_STAGE + q * 96 + lane * 4, F.drgb[q] + at);
+    }
+    cp_async_commit();
+  };
+  int grp = blockIdx.x * SF_WARPS + warp;
+  fetch(grp, 0);
+  for (int it = 0; grp < groups; grp += step, ++it) {
+    const int buf = it & 1;
+    fetch(grp + step, buf ^ 1);
     const int first = grp * 32;
     const int rows = min(32, F.P - first);
-    // 96 floats per rank = 24 float4; the last 16-byte read of the last group may pass 3 P by up to
-    // three floats (the buffers carry four floats of padding)
-#pragma unroll
-    for (int q = 0; q < EGS_MAX_PEERS; ++q)
-      if (q < F.n && lane < 24 && (size_t)first * 3 + lane * 4 < (size_t)F.P * 3) {
-        const float4 v = ld_peer_f4(F.drgb[q] + (size_t)first * 3 + lane * 4);
-        *reinterpret_cast<float4*>(stage + q * 96 + lane * 4) = v;
-      }
     const int idx = first + (int)lane;
     float3 pos = make_float3(0.f, 0.f, 0.f);
     if (idx < F.P) pos = make_float3(F.means3D[3 * idx], F.means3D[3 * idx + 1], F.means3D[3 * idx + 2]);
+    cp_async_wait<1>();   // this group's triples have landed (the next group's may still be in flight)
     __syncwarp();
+    const float* st = stage + buf * SF_STAGE;
     float acc[48];
 #pragma unroll
     for (int k = 0; k < 48; ++k) acc[k] = 0.f;
 #pragma unroll
     for (int q = 0; q < EGS_MAX_PEERS; ++q)
       if (q < F.n) {
-        const float dr = stage[q * 96 + 3 * lane], dg = stage[q * 96 + 3 * lane + 1], db = stage[q * 96 + 3 * lane + 2];
+        const float dr = st[q * 96 + 3 * lane], dg = st[q * 96 + 3 * lane + 1], db = st[q * 96 + 3 * lane + 2];
         // same expressions as sh_backward (preprocess_bwd.cu)
-        const float3 dir = make_float3(pos.x - cam[q][0], pos.y - cam[q][1], pos.z - cam[q][2]);
+        const float3 dir = make_float3(pos.x - s_cam[4 * q], pos.y - s_cam[4 * q + 1], pos.z - s_cam[4 * q + 2]);
         const float len = sqrtf(dir.x * dir.x + dir.y * dir.y + dir.z * dir.z);
         const float x = dir.x / len, y = dir.y / len, z = dir.z / len;
         float b[16];
@@ -343,7 +370,7 @@ __device__ __forceinline__ void expand_sh_sum(const ExLaunch& L, const ShFactorL
         sh_basis_values(F.D, x, y, z, b);
 #pragma unroll
         for (int k = 0; k < 16; ++k) {
-          // product and sum rounded separately: the sum of the ranks' expanded rows, not an FMA chain
+          // product and sum rounded separately: the sum of the views' expanded rows, not an FMA chain
           const float pr = __fmul_rn(b[k], dr), pg = __fmul_rn(b[k], dg), pb = __fmul_rn(b[k], db);
           if (q == 0) {
             acc[3 * k] = pr; acc[3 * k + 1] = pg; acc[3 * k + 2] = pb;
@@ -354,7 +381,6 @@ __device__ __forceinline__ void expand_sh_sum(const ExLaunch& L, const ShFactorL
           }
         }
       }
-    __syncwarp();   // everybody has read the staged triples
 #pragma unroll
     for (int k = 0; k < 48; ++k)
       if (k < row_floats) tile[lane * SF_PITCH + k] = L.scale == 1.f ? acc[k] : acc[k] * L.scale;
@@ -369,8 +395,9 @@ __device__ __forceinline__ void expand_sh_sum(const ExLaunch& L, const ShFactorL
     } else {
       for (int e = lane; e < rows * row_floats; e += 32) dst[e] = tile[(e / row_floats) * SF_PITCH + e % row_floats];
     }
-    __syncwarp();   // the tile is free for the next group
+    __syncwarp();   // the tile and this stage buffer are free for the group after next
   }
+  cp_async_wait<0>();
 }
 
 template <bool MC, int WMAX>
@@ -380,9 +407,11 @@ exchange_factored_kernel(const __grid_constant__ ExLaunch L, const __grid_consta
   __shared__ bool s_last;
   __shared__ int s_timed_out;
   if (barrier_in(L, s_timed_out)) {
-    if (MC) sum_slice_mc<false>(L);
-    else sum_slice_peer<false, WMAX>(L);
-    expand_sh_sum(L, F, sf_smem);
+    if (F.phases != 2) {
+      if (MC) sum_slice_mc<false, 8>(L);   // one CTA per SM here: twice the reductions in flight per thread
+      else sum_slice_peer<false, WMAX>(L);
+    }
+    if (F.phases != 1) expand_sh_sum(L, F, sf_smem);
   }
   barrier_out(L, s_last, s_timed_out);
 }
@@ -529,13 +558,13 @@ extern "C" int egs_exchange_sum_factored(const EgsPeerGroup* group, long long n_
     return EGS_ERR_INVALID_ARGUMENT;
   }
   F.n = sh->n_views > 0 ? sh->n_views : L.world;
+  F.phases = debug_options().exchange_phases;
   for (int q = 0; q < F.n; ++q) {
-    if (!sh->drgb[q] || !sh->campos[q] || (reinterpret_cast<uintptr_t>(sh->drgb[q]) & 15u)) {
-      set_error("%s: dL/dRGB buffer (16-byte aligned) or camera centre of view %d missing", who, q);
+    if (!sh->drgb[q] || (reinterpret_cast<uintptr_t>(sh->drgb[q]) & 15u)) {
+      set_error("%s: dL/dRGB slot of view %d missing or not 16-byte aligned", who, q);
       return EGS_ERR_INVALID_ARGUMENT;
     }
     F.drgb[q] = sh->drgb[q];
-    F.campos[q] = sh->campos[q];
   }
   if (sh->n_views > 0) {   // a batch of views: their flat buffers are the sources, group->grads the destinations
     for (int q = 0; q < F.n; ++q) {

@@ -193,9 +193,10 @@ gaussian_backward(int idx, int D, int M, const float* __restrict__ means3D, cons
                   float* __restrict__ dL_dscales, float* __restrict__ dL_drot,
                   // raw-parameter mode (egs_backward_raw): gradients go to the raw tensors
                   const RawModel& raw, const float* s_rot, const EgsModelGrads& rg, float* dT, bool colors_only,
-                  // factored SH gradient (EgsBackwardArgs.dL_drgb): [P,3] or NULL
-                  float* __restrict__ dL_drgb) {
+                  // factored SH gradient: this Gaussian's clamp-masked dL/dRGB (zero when culled)
+                  float3& drgb_out) {
   constexpr bool raw_geom = RAW;
+  drgb_out = make_float3(0.f, 0.f, 0.f);
   if (colors_only) {   // EgsBackwardArgs.colors_only: unpack the colour accumulators, nothing else
     const bool seen = radii[idx] > 0;
     const float4 a2 = seen ? acc[3 * (size_t)idx + 2] : make_float4(0.f, 0.f, 0.f, 0.f);
@@ -227,10 +228,6 @@ gaussian_backward(int idx, int D, int M, const float* __restrict__ means3D, cons
     }
     if (has_sh && sh_out != nullptr) {
       for (int k = 0; k < 3 * M; ++k) sh_out[k] = 0.f;
-    }
-    if (dL_drgb != nullptr) {
-#pragma unroll
-      for (int k = 0; k < 3; ++k) dL_drgb[3 * idx + k] = 0.f;
     }
     if (scales != nullptr && !raw_geom) {
 #pragma unroll
@@ -363,11 +360,7 @@ gaussian_backward(int idx, int D, int M, const float* __restrict__ means3D, cons
     const float3 g = sh_backward(D, M, mean, make_float3(s_cam[0], s_cam[1], s_cam[2]), sh_in, clamped[idx], drgb,
                                  sh_out);
     dmean.x += g.x; dmean.y += g.y; dmean.z += g.z;
-    if (dL_drgb != nullptr) {
-      dL_drgb[3 * idx + 0] = drgb.x;
-      dL_drgb[3 * idx + 1] = drgb.y;
-      dL_drgb[3 * idx + 2] = drgb.z;
-    }
+    drgb_out = make_float3(drgb.x, drgb.y, drgb.z);
   } else {
     dL_dcolors[3 * idx + 0] = a2.x;
     dL_dcolors[3 * idx + 1] = a2.y;
@@ -412,8 +405,36 @@ constexpr int SH_PITCH = 49;      // odd pitch: a lane walking its own row is co
 // SH_MODE as in the forward kernel: 0 = rows straight from global memory, 1 = staged float4 rows of
 // one contiguous [P,16,3] tensor, 2 = rows staged from / written back to the split features_dc /
 // features_rest tensors of the raw-parameter mode.
+// Destinations of the factored SH gradient (EgsBackwardArgs.dL_drgb, drgb_remote, drgb_multicast): the
+// local slot and this view's slot in the other ranks' gather buffers.
+struct DrgbSlots {
+  float* local;
+  float* remote[EGS_MAX_PEERS];
+  float* multicast;
+  int n_remote;
+};
+
+__device__ __forceinline__ void st_sys_f4(float* p, float4 v) {
+  asm volatile("st.relaxed.sys.global.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(p), "f"(v.x), "f"(v.y), "f"(v.z), "f"(v.w)
+               : "memory");
+}
+__device__ __forceinline__ void st_multicast_f4(float* p, float4 v) {
+  asm volatile("multimem.st.relaxed.sys.global.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(p), "f"(v.x), "f"(v.y),
+               "f"(v.z), "f"(v.w)
+               : "memory");
+}
+// 16 bytes of a slot to every destination (float offset `at`, a multiple of 4)
+__device__ __forceinline__ void store_slot_f4(const DrgbSlots& d, size_t at, float4 v) {
+  *reinterpret_cast<float4*>(d.local + at) = v;
+  if (d.multicast != nullptr) {
+    st_multicast_f4(d.multicast + at, v);
+  } else {
+    for (int q = 0; q < d.n_remote; ++q) st_sys_f4(d.remote[q] + at, v);
+  }
+}
+
 // FACTORED: dL/dsh is not written (neither the rows in shared memory nor the 12 M bytes per Gaussian in
-// HBM); the clamp-masked dL/dRGB goes to dL_drgb instead (EgsBackwardArgs.dL_drgb).
+// HBM); the clamp-masked dL/dRGB rows and the camera centre go to the slots instead.
 template <int SH_MODE, bool RAW, bool FACTORED>
 __global__ void __launch_bounds__(PB_THREADS, 6)
 preprocess_backward_kernel(RawModel raw, EgsModelGrads rg, int P, int D, int M, const float* __restrict__ means3D,
@@ -429,7 +450,7 @@ preprocess_backward_kernel(RawModel raw, EgsModelGrads rg, int P, int D, int M, 
                            float* __restrict__ dL_dopacity, float* __restrict__ dL_dmeans3D,
                            float* __restrict__ dL_dcov3D, float* __restrict__ dL_dsh,
                            float* __restrict__ dL_dscales, float* __restrict__ dL_drot, bool colors_only,
-                           float* __restrict__ dL_drgb) {
+                           const DrgbSlots slots) {
   __shared__ float view[16], proj[16], s_cam[3];
   __shared__ float s_sh[SH_MODE != 0 ? PB_WARPS * 32 * SH_PITCH : 1];
   __shared__ float s_rot[RAW ? 18 : 1];
@@ -446,11 +467,14 @@ preprocess_backward_kernel(RawModel raw, EgsModelGrads rg, int P, int D, int M, 
   float dT[RAW ? 9 : 1];
 #pragma unroll
   for (int k = 0; k < (RAW ? 9 : 1); ++k) dT[k] = 0.f;
+  float3 drgb = make_float3(0.f, 0.f, 0.f);
+  if (FACTORED && blockIdx.x == 0 && threadIdx.x == 0)   // the view's camera centre closes the slot
+    store_slot_f4(slots, ((size_t)P * 3 + 3) / 4 * 4, make_float4(s_cam[0], s_cam[1], s_cam[2], 0.f));
 
 #define EGS_GB_TAIL                                                                                          \
   clamped, scales, rotations, cov3D_precomp, colors_precomp, scale_modifier, view, proj, s_cam, h_x, h_y,     \
       tan_fovx, tan_fovy, acc, dL_dmeans2D, dL_dcolors, dL_dopacity, dL_dmeans3D, dL_dcov3D, dL_dscales,      \
-      dL_drot, raw, s_rot, rg, dT, colors_only, FACTORED ? dL_drgb : nullptr
+      dL_drot, raw, s_rot, rg, dT, colors_only, drgb
 
   if (SH_MODE != 0) {
     // rows [first, first + rows) of this warp
@@ -473,6 +497,17 @@ preprocess_backward_kernel(RawModel raw, EgsModelGrads rg, int P, int D, int M, 
       gaussian_backward<RAW>(idx, D, M, means3D, radii, row, FACTORED ? nullptr : row, true, EGS_GB_TAIL);
     }
     __syncwarp();
+    if (FACTORED && rows > 0) {
+      // the warp's 32 triples are 384 contiguous bytes of the slot: through the (now free) tile, then
+      // 24 lanes store 16 bytes each to every destination
+      tile[3 * lane] = drgb.x;
+      tile[3 * lane + 1] = drgb.y;
+      tile[3 * lane + 2] = drgb.z;
+      __syncwarp();
+      const size_t at = (size_t)first * 3 + lane * 4;
+      if (lane < 24 && at < (size_t)P * 3)   // the last 16 bytes may run into the slot's padding
+        store_slot_f4(slots, at, make_float4(tile[4 * lane], tile[4 * lane + 1], tile[4 * lane + 2], tile[4 * lane + 3]));
+    }
     if (rows > 0 && !FACTORED) {
       if (SH_MODE == 1) {
         float4* dst = reinterpret_cast<float4*>(dL_dsh + (size_t)first * SH_ROW);
@@ -493,6 +528,14 @@ preprocess_backward_kernel(RawModel raw, EgsModelGrads rg, int P, int D, int M, 
     const size_t off = (size_t)idx * M * 3;
     gaussian_backward<RAW>(idx, D, M, means3D, radii, has_sh ? shs + off : nullptr,
                            has_sh && !FACTORED ? dL_dsh + off : nullptr, has_sh, EGS_GB_TAIL);
+    if (FACTORED) {   // unstaged rows (sh_coeffs != 16): scalar stores to every destination
+      const float v[3] = {drgb.x, drgb.y, drgb.z};
+      for (int k = 0; k < 3; ++k) {
+        slots.local[3 * (size_t)idx + k] = v[k];
+        for (int q = 0; q < slots.n_remote; ++q)
+          asm volatile("st.relaxed.sys.global.f32 [%0], %1;" ::"l"(slots.remote[q] + 3 * (size_t)idx + k), "f"(v[k]) : "memory");
+      }
+    }
   }
 #undef EGS_GB_TAIL
   // dL/d train_R: every thread of the CTA takes part (no early return above)
@@ -524,8 +567,15 @@ int launch_preprocess_backward(const EgsBackwardArgs& a, const EgsModelArgs* mod
   raw, rg, a.P, a.sh_degree, sh_coeffs, a.means3D, a.radii, a.shs, g.clamped, a.scales, a.rotations,         \
       a.cov3D_precomp, a.colors_precomp, a.scale_modifier, a.viewmatrix, a.projmatrix, a.campos,      \
       focal_x, focal_y, a.tan_fovx, a.tan_fovy, s.acc, a.dL_dmeans2D, a.dL_dcolors, a.dL_dopacity,    \
-      a.dL_dmeans3D, a.dL_dcov3D, a.dL_dsh, a.dL_dscales, a.dL_drotations, a.colors_only != 0, a.dL_drgb
+      a.dL_dmeans3D, a.dL_dcov3D, a.dL_dsh, a.dL_dscales, a.dL_drotations, a.colors_only != 0, slots
   const bool factored = a.dL_drgb != nullptr;
+  DrgbSlots slots = {};
+  slots.local = a.dL_drgb;
+  slots.n_remote = a.drgb_n_remote;
+  for (int q = 0; q < a.drgb_n_remote && q < EGS_MAX_PEERS; ++q) slots.remote[q] = a.drgb_remote[q];
+  // one multicast store replaces the peer stores only where rows are stored 16 bytes at a time
+  slots.multicast = (staged || split) ? a.drgb_multicast : nullptr;
+  if (slots.multicast != nullptr) slots.n_remote = 0;
 #define EGS_PB_LAUNCH(MODE, RAWMODE)                                                                          \
   do {                                                                                                        \
     if (factored) preprocess_backward_kernel<MODE, RAWMODE, true><<<blocks, PB_THREADS, 0, stream>>>(EGS_PB_ARGS); \

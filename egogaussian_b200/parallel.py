@@ -25,13 +25,14 @@ class FlatGrads:
     """
 
     def __init__(self, P: int, M: int, device, with_means2D: bool = True, allocate=None, factored: bool = False,
-                 geometry: str = "scale_rot"):
+                 geometry: str = "scale_rot", rgb_slot: torch.Tensor = None):
         """`allocate(n_floats)` supplies the flat buffer (PeerExchange.allocate for peer-mapped memory).
 
         `factored`: the SH gradient leaves the flat buffer. Per view it has rank one (basis of the view
-        direction x dL/dRGB), so backward writes 3 floats per Gaussian into `rgb` (its own peer-visible
-        buffer, followed by this rank's camera centre) and PeerExchange.sum_factored rebuilds the summed
-        [P,M,3] tensor in `sh`, a plain local tensor: 17 instead of 14 + 3 M floats per Gaussian to move."""
+        direction x dL/dRGB), so backward writes 3 floats per Gaussian (and the camera centre behind them)
+        into `rgb_slot`, this view's slot of a gather buffer (ViewBatch; a private tensor when none is
+        given), and the exchange rebuilds the summed [P,M,3] tensor in `sh`, a plain local tensor: 17
+        instead of 14 + 3 M floats per Gaussian to move."""
         self.factored = bool(factored)
         self.P, self.M = P, M
         self.layout: List[Tuple[str, Tuple[int, ...]]] = [("means3D", (P, 3))]
@@ -55,13 +56,11 @@ class FlatGrads:
         self.views: Dict[str, torch.Tensor] = {
             name: self.flat[o:o + n].view(shape) for (name, shape), o, n in zip(self.layout, self.offsets, sizes)}
         if self.factored:
-            # [P,3] dL/dRGB, then the camera centre (3 floats) and one float of padding: 16-byte reads of
-            # the last rows may pass 3 P
-            n_rgb = (3 * P + 3) // 4 * 4
-            self.rgb_block = (torch.zeros(n_rgb + 4, dtype=torch.float32, device=device) if allocate is None
-                              else allocate(n_rgb + 4))
-            self.views["rgb"] = self.rgb_block[:3 * P].view(P, 3)
-            self.campos = self.rgb_block[n_rgb:n_rgb + 3]
+            from . import cabi
+            n_slot = cabi.drgb_slot_floats(P)
+            self.rgb_slot = rgb_slot if rgb_slot is not None else torch.zeros(n_slot, dtype=torch.float32, device=device)
+            assert self.rgb_slot.numel() == n_slot and self.rgb_slot.data_ptr() % 16 == 0
+            self.views["rgb"] = self.rgb_slot[:3 * P].view(P, 3)      # the slot's rows; the camera centre follows
             self.views["sh"] = torch.zeros((P, M, 3), dtype=torch.float32, device=device)
 
     def as_backward_out(self) -> Dict[str, torch.Tensor]:
@@ -179,27 +178,6 @@ class PeerExchange:
                                 scale=1.0 / self.world if average else 1.0, max_ctas=max_ctas)
         return grads
 
-    def sum_factored(self, layout: "FlatGrads", means3D: torch.Tensor, campos: torch.Tensor, sh_degree: int,
-                     average: bool = False, max_ctas: int = 0) -> "FlatGrads":
-        """The exchange of a FlatGrads(factored=True) layout: the flat buffer of the small gradients is
-        summed in place on all ranks, and layout.views["sh"] <- sum over ranks of (SH basis in the
-        direction from that rank's camera) x (that rank's dL/dRGB). `campos` is this rank's camera
-        centre; `means3D` the replicated positions backward ran on."""
-        assert layout.factored
-        layout.campos.copy_(campos.reshape(3), non_blocking=True)
-        self.epoch += 1
-        key = ("factored", layout.rgb_block.data_ptr())
-        if key not in self._groups:
-            rgb_ptrs = self.peer_pointers(layout.rgb_block)
-            cam_off = (layout.campos.data_ptr() - layout.rgb_block.data_ptr())
-            self._groups[key] = (rgb_ptrs, [p_ + cam_off for p_ in rgb_ptrs])
-        rgb_ptrs, cam_ptrs = self._groups[key]
-        self._cabi.exchange_sum_factored(self._group_for(layout.flat), layout.flat.numel(), self.epoch,
-                                         means3D=means3D, drgb_ptrs=rgb_ptrs, campos_ptrs=cam_ptrs,
-                                         dL_dsh=layout.views["sh"], sh_degree=sh_degree,
-                                         scale=1.0 / self.world if average else 1.0, max_ctas=max_ctas)
-        return layout
-
     def moment_shards(self, n_floats: int):
         """This rank's zeroed Adam moments for a flat buffer of n_floats (1/world of it)."""
         n = int(self._cabi.load().egs_exchange_shard_floats(n_floats, self.world))
@@ -223,13 +201,17 @@ class PeerExchange:
 
 class ViewBatch:
     """One training batch of `n_views` camera views spread over the ranks (BASELINE configs[3]; SURVEY.md
-    8e: rank r renders views r, r + world, ...), with ONE exchange per batch.
+    8e: rank r renders views r, r + world, ...; n_views = world is the one-view-per-rank step), with ONE
+    exchange per batch and the SH gradient in factored form.
 
-    Every local view gets its own FlatGrads(factored=True) to back-propagate into (`layouts[j]` for the
-    rank's j-th view); `exchange()` then sums the small gradients over all views of all ranks into
-    `result.flat` views on every rank and rebuilds the summed SH gradient in `result.views["sh"]`, both in
-    the global view order, so the numbers do not depend on the number of GPUs. With one rank (or without
-    torch.distributed) it is the single-GPU accumulation of the batch through the same kernel."""
+    Every rank holds a gather buffer with one slot per view (12 bytes per Gaussian + the camera centre).
+    `layouts[j]` is the FlatGrads(factored=True) of the rank's j-th view; `backward_args(j)` are the extra
+    arguments of cabi.backward that make its kernel store the view's slot into every rank's gather buffer
+    while it runs. `exchange()` then sums the small gradients over all views of all ranks into
+    `result.flat` on every rank and rebuilds the summed SH gradient in `result.views["sh"]` from the local
+    slots, both in the global view order, so the numbers do not depend on the number of GPUs. With one
+    rank (or without torch.distributed) it is the single-GPU accumulation of the batch through the same
+    kernel."""
 
     def __init__(self, n_views: int, P: int, M: int, device, exchange: "PeerExchange" = None,
                  geometry: str = "scale_rot"):
@@ -243,30 +225,37 @@ class ViewBatch:
         self.n_views, self.device = n_views, torch.device(device)
         self.local_views = list(views_for_rank(n_views, self.rank, self.world))
         alloc = exchange.allocate if exchange else None
-        self.layouts = [FlatGrads(P, M, device, allocate=alloc, factored=True, geometry=geometry)
-                        for _ in self.local_views]
+        slot = cabi.drgb_slot_floats(P)
+        self.gather = (alloc(n_views * slot) if alloc else torch.zeros(n_views * slot, dtype=torch.float32, device=device))
+        self.layouts = [FlatGrads(P, M, device, allocate=alloc, factored=True, geometry=geometry,
+                                  rgb_slot=self.gather[v * slot:(v + 1) * slot]) for v in self.local_views]
         self.result = self.layouts[0]            # the sums land in the first local view's buffers
+        self._slot_ptrs = [self.gather.data_ptr() + 4 * v * slot for v in range(n_views)]
+        self._push = []
         if exchange:
             flat_ptrs = [exchange.peer_pointers(l.flat) for l in self.layouts]        # [local j][rank]
-            rgb_ptrs = [exchange.peer_pointers(l.rgb_block) for l in self.layouts]
+            gather_ptrs = exchange.peer_pointers(self.gather)
+            mc = exchange.multicast_pointer(self.gather)
+            for v in self.local_views:
+                self._push.append(dict(rgb_remote=[g + 4 * v * slot for q, g in enumerate(gather_ptrs) if q != self.rank],
+                                       rgb_multicast=mc + 4 * v * slot if mc else 0))
             self._signals = None
             self._group = exchange._group_for(self.result.flat)
         else:
             flat_ptrs = [[l.flat.data_ptr()] for l in self.layouts]
-            rgb_ptrs = [[l.rgb_block.data_ptr()] for l in self.layouts]
+            self._push = [dict(rgb_remote=[], rgb_multicast=0) for _ in self.local_views]
             self._signals = torch.zeros(cabi.EGS_EXCHANGE_SIGNAL_WORDS, dtype=torch.int32, device=device)
             self._group = cabi.peer_group(1, 0, [self.result.flat.data_ptr()], [self._signals.data_ptr()])
             self._epoch = 0
-        cam_off = self.layouts[0].campos.data_ptr() - self.layouts[0].rgb_block.data_ptr()
         self._view_flat = [flat_ptrs[v // self.world][v % self.world] for v in range(n_views)]
-        self._view_rgb = [rgb_ptrs[v // self.world][v % self.world] for v in range(n_views)]
-        self._view_cam = [p_ + cam_off for p_ in self._view_rgb]
 
-    def exchange(self, means3D: torch.Tensor, campos: Sequence[torch.Tensor], sh_degree: int, average: bool = False,
-                 max_ctas: int = 0) -> FlatGrads:
-        """`campos[j]`: camera centre of this rank's j-th view; `means3D`: the positions backward ran on."""
-        for lay, c in zip(self.layouts, campos):
-            lay.campos.copy_(c.reshape(3), non_blocking=True)
+    def backward_args(self, j: int) -> Dict:
+        """Keyword arguments for cabi.backward of the rank's j-th view: its output tensors and the
+        addresses of its slot on the other ranks."""
+        return dict(out=self.layouts[j].as_backward_out(), **self._push[j])
+
+    def exchange(self, means3D: torch.Tensor, sh_degree: int, average: bool = False, max_ctas: int = 0) -> FlatGrads:
+        """`means3D`: the positions backward ran on (the same on every rank)."""
         if self.ex:
             self.ex.epoch += 1
             epoch = self.ex.epoch
@@ -274,8 +263,7 @@ class ViewBatch:
             self._epoch += 1
             epoch = self._epoch
         self._cabi.exchange_sum_factored(self._group, self.result.flat.numel(), epoch, means3D=means3D,
-                                         drgb_ptrs=self._view_rgb, campos_ptrs=self._view_cam,
-                                         dL_dsh=self.result.views["sh"], sh_degree=sh_degree,
+                                         drgb_ptrs=self._slot_ptrs, dL_dsh=self.result.views["sh"], sh_degree=sh_degree,
                                          scale=1.0 / self.n_views if average else 1.0, max_ctas=max_ctas,
                                          view_flat_ptrs=self._view_flat)
         return self.result

@@ -52,6 +52,7 @@ extern "C" {
 #define EGS_TILE_X 16          /* DGR/cuda_rasterizer/config.h:16 */
 #define EGS_TILE_Y 16          /* DGR/cuda_rasterizer/config.h:17 */
 #define EGS_NUM_CHANNELS 3     /* DGR/cuda_rasterizer/config.h:15 */
+#define EGS_MAX_PEERS 8        /* GPUs of one NVLink domain; also the largest batch of views of one exchange */
 
 typedef enum EgsStatus {
   EGS_OK = 0,
@@ -167,16 +168,27 @@ typedef struct EgsBackwardArgs {
    * NULL). This is the backward of the trainers' per-iteration label render
    * (gaussian_renderer/render_helper.py:40-66: geometry detached, the label as colour). */
   int colors_only;
-  /* Optional, with shs (or, in egs_backward_raw, the model's features): device [P,3]. When set, the
-   * SH gradient is returned in factored form: dL_drgb[i] = dL/dRGB of Gaussian i with the clamped
-   * channels zeroed, and dL_dsh (d_features_dc / d_features_rest) is NOT written and may be NULL.
-   * dL/dsh[i][k][c] = basis_k(direction from campos to means3D[i]) * dL_drgb[i][c]: 3 floats per
-   * Gaussian carry what 3 M floats would, which is what the view-data-parallel exchange sends
-   * (egs_exchange_sum_factored expands the sum over the ranks' views). */
+  /* Optional, with shs (or, in egs_backward_raw, the model's features): device, EGS_DRGB_SLOT_FLOATS(P)
+   * floats, 16-byte aligned. When set, the SH gradient is returned in factored form: rows [P,3] with
+   * dL_drgb[i] = dL/dRGB of Gaussian i, clamped channels zeroed, followed (at float offset 3 P rounded up
+   * to a multiple of 4) by the three floats of `campos`; dL_dsh (d_features_dc / d_features_rest) is NOT
+   * written and may be NULL. dL/dsh[i][k][c] = basis_k(direction from campos to means3D[i]) * dL_drgb[i][c]:
+   * 3 floats per Gaussian carry what 3 M floats would, which is what the view-data-parallel exchange
+   * moves (egs_exchange_sum_factored expands the sum over the views). */
   float* dL_drgb;
+  /* View-data-parallel: the same slot (rows + campos) is also written, by the same kernel, to
+   * drgb_remote[0 .. drgb_n_remote) -- this view's slot in the OTHER ranks' gather buffers, peer-mapped --
+   * or, when drgb_multicast is set, with one multicast store per 16 bytes that reaches every rank's
+   * buffer through the NVLink switch. The stores ride along with the kernel's HBM traffic, so after
+   * the backward every rank already holds every view's factors locally. */
+  int drgb_n_remote;
+  float* drgb_remote[EGS_MAX_PEERS];
+  float* drgb_multicast;
 } EgsBackwardArgs;
 
 size_t egs_backward_scratch_bytes(int P);
+/* floats in one dL_drgb slot: the rows, padded to a multiple of 4, then campos (3) and one spare */
+#define EGS_DRGB_SLOT_FLOATS(P) ((((long long)(P) * 3 + 3) / 4) * 4 + 4)
 
 int egs_backward(const EgsBackwardArgs* args, void* stream);
 
@@ -256,7 +268,6 @@ int egs_adam_se3_step(int P, float* xyz, const float* grad_moved, float* exp_avg
  * whole exchange: rank r sums slice r of all the buffers in rank order and writes the sums back into
  * every buffer, between two flag barriers that live in the signal words. No host synchronisation, no
  * staging copies; every rank ends with bit-identical sums. */
-#define EGS_MAX_PEERS 8
 #define EGS_EXCHANGE_SIGNAL_WORDS 64
 typedef struct EgsPeerGroup {
   int world, rank;
@@ -279,30 +290,32 @@ int egs_exchange_sum(const EgsPeerGroup* group, long long n_floats, float scale,
                      void* stream);
 /* The same exchange with the SH gradient in factored form. Per view dL/dsh has rank one,
  * dL/dsh[i][k][c] = basis_k(direction from the view's camera centre to means3D[i]) * dL/dRGB[i][c], so a
- * view-data-parallel step lets egs_backward write the three floats of dL/dRGB (EgsBackwardArgs.dL_drgb)
+ * view-data-parallel step lets egs_backward write the three floats of dL/dRGB (EgsBackwardArgs.dL_drgb,
+ * pushed to every rank's gather buffer by the backward kernel itself: drgb_remote / drgb_multicast)
  * instead of the 3 M floats of dL/dsh, and this call
  *   - sums the flat buffer of the OTHER gradients (group->grads, n_floats) over the ranks like
  *     egs_exchange_sum, and
- *   - reads every rank's dL/dRGB and camera centre, forms each rank's products with the basis evaluated
- *     at this rank's own (replicated) means3D, and adds them in rank order into dL_dsh, a plain local
- *     tensor: sum over ranks of the dL/dsh each rank would have written (the same products, the same
- *     order of additions, hence the same bits as exchanging the expanded rows), times `scale`.
- * Per GPU (world - 1) * 12 bytes per Gaussian cross NVLink for the SH part instead of about 2 * 12 M.
- * drgb[q] / campos[q]: rank q's [P,3] (+ 4 floats of padding: the last 16-byte read may pass the end)
- * and [3] floats in peer-mapped memory, as mapped on this rank, written before the call in stream order.
+ *   - reads every view's slot (rows of dL/dRGB + camera centre) from THIS rank's memory, forms each
+ *     view's products with the basis evaluated at this rank's own (replicated) means3D, and adds them
+ *     in view order into dL_dsh, a plain local tensor: sum over views of the dL/dsh each would have
+ *     written (the same products, the same order of additions, hence the same bits as exchanging the
+ *     expanded rows), times `scale`.
+ * Per GPU (views - 1) * 12 bytes per Gaussian cross NVLink for the SH part instead of about 2 * 12 M.
+ * The two barriers of the exchange also fence the slots: a view's slot is complete when its rank has
+ * entered, and nobody overwrites a slot before every rank has left.
  * Same epoch / max_ctas / timeout rules as egs_exchange_sum (one epoch counter for all three calls).
  *
  * A batch of views (BASELINE configs[3]: 8 views on 1, 2, 4 or 8 GPUs, rank r rendering views r, r + world,
- * ...): set n_views to the size of the batch and give, for every view in its global order, the flat
- * buffer, dL/dRGB buffer and camera centre that view's backward wrote (on whichever rank, as mapped
- * here). The sums then run over the views in that order, so the result does not depend on how the batch
- * was spread over the GPUs; the summed flat buffer lands in group->grads[r] on every rank r, which may be
- * one of that rank's view buffers. world = 1 is the single-GPU accumulation of the batch. */
+ * ...): set n_views to the size of the batch and give, for every view in its global order, its slot in
+ * this rank's gather buffer and the flat buffer its backward wrote (on whichever rank, as mapped here).
+ * The sums then run over the views in that order, so the result does not depend on how the batch was
+ * spread over the GPUs; the summed flat buffer lands in group->grads[r] on every rank r, which may be one
+ * of that rank's view buffers. world = 1 is the single-GPU accumulation of the batch. */
 typedef struct EgsShFactors {
   int P, sh_degree, sh_coeffs;
   const float* means3D;                  /* device [P,3], this rank's copy */
-  const float* drgb[EGS_MAX_PEERS];      /* per rank, or per view when n_views > 0 */
-  const float* campos[EGS_MAX_PEERS];
+  const float* drgb[EGS_MAX_PEERS];      /* per rank, or per view when n_views > 0: EGS_DRGB_SLOT_FLOATS(P)
+                                            floats each, in this rank's memory */
   float* dL_dsh;                         /* device [P, sh_coeffs, 3], 16-byte aligned, every element written */
   int n_views;                           /* 0: one view per rank */
   const float* view_flat[EGS_MAX_PEERS]; /* n_views > 0: the flat buffer of every view */

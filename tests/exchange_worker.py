@@ -119,7 +119,7 @@ def run_factored(rank, world, device, multicast):
     equal NCCL's all-reduce of the expanded tensors of an ordinary backward within 1e-4 of its maximum,
     and be the same bits on every rank."""
     from egogaussian_b200 import cabi, scenes
-    from egogaussian_b200.parallel import FlatGrads, PeerExchange
+    from egogaussian_b200.parallel import FlatGrads, PeerExchange, ViewBatch
     ex = PeerExchange(device, multicast=multicast)
     P, deg, M, W, H = int(os.environ.get("EGS_EXCHANGE_P", "200000")), 3, 16, 640, 360
     sc = scenes.make_scene(P, W, H, sh_degree=deg, seed=71, view=rank).to(device)
@@ -132,16 +132,17 @@ def run_factored(rank, world, device, multicast):
     bkw = {k: v for k, v in kw.items() if k not in ("opacities", "image_height", "image_width")}
     fwd = cabi.forward(**kw)
     full = cabi.backward(fwd, **bkw, **ups)
-    lay = FlatGrads(P, M, device, allocate=ex.allocate, factored=True)
+    batch = ViewBatch(world, P, M, device, exchange=ex)
+    lay = batch.result
     if multicast and not ex.multicast_pointer(lay.flat):
         return
-    cabi.backward(fwd, out=lay.as_backward_out(), **bkw, **ups)
+    cabi.backward(fwd, **batch.backward_args(0), **bkw, **ups)
     ref_sh = full["sh"].clone()
     dist.all_reduce(ref_sh)
     ref_small = {k: full[k].clone() for k in ("means3D", "opacity", "scales", "rotations", "means2D")}
     for t in ref_small.values():
         dist.all_reduce(t)
-    ex.sum_factored(lay, sc.means3D, cam.campos, deg)
+    batch.exchange(sc.means3D, deg)
     assert not ex.failed()
     got = lay.views["sh"]
     scale = ref_sh.abs().max().item()
@@ -166,7 +167,7 @@ def run_factored(rank, world, device, multicast):
         t = torch.tensor([a.elapsed_time(b) / iters], device=device)
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
         return t.item()
-    t_f = timed(lambda: ex.sum_factored(lay, sc.means3D, cam.campos, deg))
+    t_f = timed(lambda: batch.exchange(sc.means3D, deg))
     assert not ex.failed()
     if rank == 0:
         print(f"factored exchange world={world} P={P} {'switch multicast' if multicast else 'peer loads/stores'}: "

@@ -118,19 +118,22 @@ def test_exchange_adam_step_emulated_matches_sum_then_adam(built, cuda_device):
 
 @pytest.mark.parametrize("world,deg,M", [(2, 3, 16), (3, 1, 4), (8, 3, 16), (4, 2, 16), (1, 0, 1)])
 def test_factored_sh_exchange_emulated(world, deg, M, built, cuda_device):
-    """egs_exchange_sum_factored against what it replaces. Every emulated rank renders another view of
-    the same scene and back-propagates twice: once the ordinary way (dL/dsh as [P,M,3]) and once in
-    factored form (dL/dRGB as [P,3]); two backward runs differ in the last bits (atomic order), so the
-    two are compared within 2e-5 of the tensor maximum. The exchange itself is exact: on every rank it
-    must give the rank-order sum of the ranks' own expansions (each taken from a one-rank exchange of
-    the same dL/dRGB), bit for bit, while the flat buffer of the other gradients is summed as by
-    egs_exchange_sum."""
+    """egs_exchange_sum_factored against what it replaces. Every emulated rank owns a gather buffer with
+    one slot per rank, renders another view of the same scene and back-propagates twice: once the
+    ordinary way (dL/dsh as [P,M,3]) and once in factored form, where the backward kernel writes the
+    dL/dRGB rows and the camera centre into the rank's slot of EVERY gather buffer (drgb_remote). Two
+    backward runs differ in the last bits (atomic order), so the two forms are compared within 2e-5 of
+    the tensor maximum. The exchange itself is exact: on every rank it must give the rank-order sum of
+    the ranks' own expansions (each taken from a one-rank exchange of the same slot), bit for bit, while
+    the flat buffer of the other gradients is summed as by egs_exchange_sum."""
     from helpers import grad_rel_err
     from egogaussian_b200 import cabi, scenes
     from egogaussian_b200.parallel import FlatGrads
     dev = cuda_device
     P, W, H = 5000 + 7, 128, 96
-    full, rgbs, layouts, cams = [], [], [], []
+    slot = cabi.drgb_slot_floats(P)
+    gathers = [torch.full((world * slot,), float("nan"), device=dev) for _ in range(world)]
+    full, layouts = [], []
     means = None
     for r in range(world):
         sc = scenes.make_scene(P, W, H, sh_degree=deg, seed=61, view=r, max_sh_degree={16: 3, 4: 1, 1: 0}[M]).to(dev)
@@ -145,28 +148,30 @@ def test_factored_sh_exchange_emulated(world, deg, M, built, cuda_device):
         bkw = {k: v for k, v in kw.items() if k not in ("opacities", "image_height", "image_width")}
         fwd = cabi.forward(**kw)
         g_full = cabi.backward(fwd, **bkw, **ups)
-        lay = FlatGrads(P, M, dev, factored=True)
-        # poison: every element of the factored outputs must be written
-        for k in ("means3D", "opacity", "scales", "rotations", "means2D", "rgb"):   # (not the padding between views)
+        lay = FlatGrads(P, M, dev, factored=True, rgb_slot=gathers[r][r * slot:(r + 1) * slot])
+        for k in ("means3D", "opacity", "scales", "rotations", "means2D"):   # poison (not the padding between views)
             lay.views[k].fill_(float("nan"))
-        cabi.backward(fwd, out=lay.as_backward_out(), **bkw, **ups)
+        remote = [gathers[q].data_ptr() + 4 * r * slot for q in range(world) if q != r]
+        cabi.backward(fwd, out=lay.as_backward_out(), rgb_remote=remote, **bkw, **ups)
         torch.cuda.synchronize()
         for k in ("means3D", "opacity", "scales", "rotations", "means2D"):
             assert grad_rel_err(lay.views[k], g_full[k].view_as(lay.views[k])) <= 2e-5, (r, k)
-        assert torch.isfinite(lay.views["rgb"]).all() and torch.isfinite(lay.flat).all()
+        for q in range(world):   # the slot arrived everywhere, rows and camera centre
+            got = gathers[q][r * slot:(r + 1) * slot]
+            assert torch.equal(got[:3 * P], gathers[r][r * slot:r * slot + 3 * P]) and torch.isfinite(got[:3 * P]).all()
+            tail = (3 * P + 3) // 4 * 4
+            assert torch.equal(got[tail:tail + 3], cam.campos), (r, q)
         full.append(g_full)
         layouts.append(lay)
-        cams.append(cam.campos)
-        lay.campos.copy_(cam.campos)
     assert sum(float(g["sh"].abs().max()) for g in full) > 0
-    # every rank's own expansion: a one-rank exchange of its dL/dRGB (flat buffer untouched: 0 floats)
+    # every rank's own expansion: a one-rank exchange of its slot (flat buffer untouched: 0 floats)
     own = []
     for r in range(world):
         sig = torch.zeros(cabi.EGS_EXCHANGE_SIGNAL_WORDS, dtype=torch.int32, device=dev)
         solo = cabi.peer_group(1, 0, [layouts[r].flat.data_ptr()], [sig.data_ptr()])
         out = torch.full((P, M, 3), float("nan"), device=dev)
-        cabi.exchange_sum_factored(solo, 0, 1, means3D=means, drgb_ptrs=[layouts[r].rgb_block.data_ptr()],
-                                   campos_ptrs=[layouts[r].campos.data_ptr()], dL_dsh=out, sh_degree=deg, max_ctas=2)
+        cabi.exchange_sum_factored(solo, 0, 1, means3D=means, drgb_ptrs=[gathers[r].data_ptr() + 4 * r * slot],
+                                   dL_dsh=out, sh_degree=deg, max_ctas=2)
         torch.cuda.synchronize()
         assert int(sig[-1].item()) == 0
         assert grad_rel_err(out, full[r]["sh"]) <= 2e-5, r     # the expansion is the dL/dsh backward writes
@@ -180,8 +185,7 @@ def test_factored_sh_exchange_emulated(world, deg, M, built, cuda_device):
         grp = cabi.peer_group(world, r, [lay.flat.data_ptr() for lay in layouts], [s.data_ptr() for s in signals])
         with torch.cuda.stream(streams[r]):
             cabi.exchange_sum_factored(grp, layouts[r].flat.numel(), 1, means3D=means,
-                                       drgb_ptrs=[lay.rgb_block.data_ptr() for lay in layouts],
-                                       campos_ptrs=[lay.campos.data_ptr() for lay in layouts],
+                                       drgb_ptrs=[gathers[r].data_ptr() + 4 * q * slot for q in range(world)],
                                        dL_dsh=layouts[r].views["sh"], sh_degree=deg, max_ctas=2)
     torch.cuda.synchronize()
     assert all(int(s[-1].item()) == 0 for s in signals)
@@ -219,20 +223,20 @@ def test_view_batch_on_one_gpu(geometry, built, cuda_device):
         ups = dict(dL_dcolor=wc, dL_ddepth=wd, dL_dalpha=wa)
         bkw = {n: v for n, v in kw.items() if n not in ("opacities", "image_height", "image_width")}
         fwd = cabi.forward(**kw)
-        cabi.backward(fwd, out=lay.as_backward_out(), **bkw, **ups)
+        cabi.backward(fwd, **batch.backward_args(k), **bkw, **ups)
         full = cabi.backward(fwd, **bkw, **ups)
         if want is None:
             want = {n: v.clone() for n, v in full.items() if v is not None}
         else:
             for n in want:
                 want[n] += full[n]
-    res = batch.exchange(sc.means3D, [c.campos.to(dev) for c in cams], deg)
+    res = batch.exchange(sc.means3D, deg)
     torch.cuda.synchronize()
     assert int(batch._signals[-1].item()) == 0
     for n, v in want.items():
         assert grad_rel_err(res.views[n], v.view_as(res.views[n])) <= 2e-5, n
     # a second batch through the same buffers (the epoch advances)
-    res2 = batch.exchange(sc.means3D, [c.campos.to(dev) for c in cams], deg)
+    res2 = batch.exchange(sc.means3D, deg)
     torch.cuda.synchronize()
     assert grad_rel_err(res2.views["sh"], want["sh"]) <= 2e-5
 

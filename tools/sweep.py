@@ -48,16 +48,16 @@ def sweep_dp(a, rank, world):
         wc, wd, wa = [t.to(device) for t in scenes.upstream_weights(W, H, 3001 + rank)]
         ups = dict(dL_dcolor=wc, dL_ddepth=wd, dL_dalpha=wa)
         bkw = {k: v for k, v in kw.items() if k not in ("opacities", "image_height", "image_width")}
-        flat = parallel.FlatGrads(P, 16, device, allocate=ex.allocate, factored=True)
+        batch = parallel.ViewBatch(world, P, 16, device, exchange=ex)
         scratch = torch.empty((cabi.load().egs_backward_scratch_bytes(P),), dtype=torch.uint8, device=device)
         state = {"hint": 0}
 
         def step(exchange=True):
             fwd = cabi.forward(num_rendered_hint=state["hint"], **kw)
             state["hint"] = int(fwd.num_rendered * 1.25) + 8192
-            cabi.backward(fwd, out=flat.as_backward_out(), scratch=scratch, **bkw, **ups)
+            cabi.backward(fwd, scratch=scratch, **batch.backward_args(0), **bkw, **ups)
             if exchange:
-                ex.sum_factored(flat, kw["means3D"], kw["campos"], deg)
+                batch.exchange(kw["means3D"], deg)
             state["R"] = fwd.num_rendered
 
         def timed(fn, iters=10):
@@ -81,7 +81,7 @@ def sweep_dp(a, rank, world):
         out.append(rec)
         if rank == 0:
             print(json.dumps(rec), flush=True)
-        del flat, sc, kw, ups, bkw, scratch
+        del batch, sc, kw, ups, bkw, scratch
         torch.cuda.empty_cache()
     if rank == 0:
         Path(a.json).parent.mkdir(parents=True, exist_ok=True)
