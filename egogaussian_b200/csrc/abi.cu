@@ -116,7 +116,7 @@ static HostCountSlot* host_count_slot() {
 }
 
 // ---- test / A-B switches (egs_debug_option) ---------------------------------------------------
-static std::atomic<int> g_dbg_sort{SORT_AUTO}, g_dbg_presort{-1}, g_dbg_scramble{0}, g_dbg_fwd_v2{0}, g_dbg_xphases{0};
+static std::atomic<int> g_dbg_sort{SORT_AUTO}, g_dbg_presort{-1}, g_dbg_scramble{0}, g_dbg_fwd_v2{0}, g_dbg_xphases{0}, g_dbg_bwd_ppl{0};
 DebugOptions debug_options() {
   DebugOptions o;
   o.sort = g_dbg_sort.load(std::memory_order_relaxed);
@@ -124,6 +124,7 @@ DebugOptions debug_options() {
   o.presort_scramble = g_dbg_scramble.load(std::memory_order_relaxed);
   o.fwd_v2 = g_dbg_fwd_v2.load(std::memory_order_relaxed);
   o.exchange_phases = g_dbg_xphases.load(std::memory_order_relaxed);
+  o.bwd_ppl = g_dbg_bwd_ppl.load(std::memory_order_relaxed);
   return o;
 }
 
@@ -568,6 +569,8 @@ extern "C" int egs_debug_option(const char* name, const char* value) {
     g_dbg_scramble.store(unset || value[0] == '0' ? 0 : 1, std::memory_order_relaxed);
   } else if (strcmp(name, "blend_forward") == 0) {
     g_dbg_fwd_v2.store(!unset && strcmp(value, "v2") == 0 ? 1 : 0, std::memory_order_relaxed);
+  } else if (strcmp(name, "blend_backward") == 0) {
+    g_dbg_bwd_ppl.store(!unset && value[0] == '2' ? 2 : 0, std::memory_order_relaxed);
   } else if (strcmp(name, "exchange_phases") == 0) {
     g_dbg_xphases.store(unset ? 0 : (value[0] == 'a' ? 1 : 2), std::memory_order_relaxed);
   } else {

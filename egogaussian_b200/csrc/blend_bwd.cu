@@ -12,14 +12,13 @@
 //   * all 32 lanes of a warp look at the same list entry, so the ten partial sums are first
 //     reduced across the warp (a packed butterfly: 12 shuffles for 10 quantities) and only if
 //     some lane contributed at all;
-//   * the warp totals are added into a per-batch shared-memory accumulator (12 floats per list
-//     entry), and after the batch each thread flushes one entry with three 16-byte vector
+//   * the warp totals are stored into a per-warp shared-memory row (12 floats per list entry), and
+//     after the batch a thread sums an entry's rows and flushes it with three 16-byte vector
 //     reductions (red.global.add.v4.f32) into the 48-byte per-Gaussian record.
 #include "common.cuh"
 
 namespace egs {
 
-constexpr int BWD_BATCH = 256;
 constexpr int ACC_STRIDE = 12;
 constexpr int ACC_PITCH = 13;  // odd pitch: conflict-free both for the per-entry atomics and the flush
 
@@ -77,12 +76,14 @@ __device__ __forceinline__ int quantity_of_lane(unsigned lane) {
 __device__ __forceinline__ int record_slot_of_quantity(int q) { return q < 7 ? q : q + 1; }
 
 // ---------------------------------------------------------------------------------------------
-// two pixels per thread, exp only for fragments that pass a log-domain test
+// several pixels per thread, exp only for fragments that pass a log-domain test
 // ---------------------------------------------------------------------------------------------
-// The per-fragment arithmetic of SURVEY.md App. A.8, organised for throughput:
-//   * 128 threads per tile, each owning the pixels (x, y) and (x, y + 4) of its warp's 8x8 block:
-//     a list entry costs 4 warp reductions per tile instead of 8, every staged entry is read from
-//     shared memory half as often, and the two pixel chains give the scheduler independent work;
+// The per-fragment arithmetic of SURVEY.md App. A.8, organised for throughput (the kernel is bound by
+// instruction issue, so everything here is about instructions per fragment):
+//   * a warp covers an 8 x (4 PPL) block of the tile, a lane owning PPL pixels of one column (rows y,
+//     y + 4, ...): one warp reduction per list entry serves 32 PPL pixels, every staged entry is read
+//     from shared memory once per PPL pixels, and the PPL pixel chains give the scheduler independent
+//     work. PPL = 4: 64 threads per tile;
 //   * whether a fragment contributes is decided without the exponential:
 //       alpha = o * exp(power) >= 1/255   <=>   power >= -log(255 * o) =: thr (staged per entry),
 //     so exp, the divide and everything after run only on warps where some lane contributes.
@@ -90,10 +91,15 @@ __device__ __forceinline__ int record_slot_of_quantity(int q) { return q < 7 ? q
 //     power lies within CONTRIB_MARGIN of the threshold is therefore decided here with that very
 //     expression, so both passes always agree on a pixel's contributor set (one fragment more or
 //     less would shift T = T / (1 - alpha) for every earlier fragment of the pixel);
+//   * the "colour behind this fragment" recurrences are advanced right after a fragment has used them
+//     (the reference advances them at the start of the next one from a saved alpha and colour: the same
+//     expression evaluated one step earlier, five registers less per pixel);
+//   * the geometry gradients are accumulated as moments of v = G dL/dG over the pixels -- sum v, v dx,
+//     v dy, v dx^2, v dx dy, v dy^2 -- and turned into dL/dmean2D and dL/dconic once per entry after the
+//     reduction (9 instead of 17 instructions per fragment);
 //   * backward is tolerance-checked (1e-4 of the tensor maximum), not bit-checked, so the
 //     exponential and the reciprocal use the fast hardware approximations (ex2.approx, rcp.approx).
-constexpr int BWD2_THREADS = 128;
-constexpr int BWD2_BATCH = 128;
+constexpr int BWD_BATCH = 128;
 // half-width of the band around -log(255 o) inside which the forward's exact test decides: covers
 // the error of __logf (~1e-6 here) and of the fp32 product o * expf(power) a hundred times over
 constexpr float CONTRIB_MARGIN = 1e-4f;
@@ -116,130 +122,126 @@ __device__ __forceinline__ float rcp_approx(float x) {
   return y;
 }
 
+// What a pixel carries through the walk: transmittance, the colour / depth / alpha accumulated behind
+// the current fragment, its upstream gradients and tb = -T_final * (background . dL/dcolour).
 struct PixelState {
-  float T, T_final, accum_rec[3], accum_depth, accum_alpha, last_alpha, last_color[3], last_depth;
-  float dL_dpixel[3], dL_ddepth, dL_dalpha, bg_dot;
-  float px, py;
+  float T, ar, ag, ab, ad, aa;
+  float gr, gg, gb, gd, ga, tb;
   uint32_t last;
 };
 
-__device__ __forceinline__ void pixel_init(PixelState& s, bool inside, uint32_t pix_id, unsigned px, unsigned py,
-                                           int W, int H, const float* __restrict__ alphas,
-                                           const uint32_t* __restrict__ n_contrib,
+__device__ __forceinline__ void pixel_init(PixelState& s, bool inside, uint32_t pix_id, int W, int H,
+                                           const float* __restrict__ alphas, const uint32_t* __restrict__ n_contrib,
                                            const float* __restrict__ dL_dpixels,
                                            const float* __restrict__ dL_dpixel_depths,
                                            const float* __restrict__ dL_dalphas, const float* bg) {
-  s.px = (float)px;
-  s.py = (float)py;
-  s.T_final = inside ? (1 - alphas[pix_id]) : 0;
-  s.T = s.T_final;
+  const float T_final = inside ? (1 - alphas[pix_id]) : 0;   // backward.cu:463
+  s.T = T_final;
   s.last = inside ? n_contrib[pix_id] : 0;
   const size_t plane = (size_t)H * W;
-#pragma unroll
-  for (int ch = 0; ch < 3; ++ch) {
-    s.dL_dpixel[ch] = inside ? dL_dpixels[ch * plane + pix_id] : 0.f;
-    s.accum_rec[ch] = 0.f;
-    s.last_color[ch] = 0.f;
-  }
-  s.dL_ddepth = inside ? dL_dpixel_depths[pix_id] : 0.f;
-  s.dL_dalpha = inside ? dL_dalphas[pix_id] : 0.f;
-  s.accum_depth = s.accum_alpha = s.last_alpha = s.last_depth = 0.f;
-  s.bg_dot = bg[0] * s.dL_dpixel[0] + bg[1] * s.dL_dpixel[1] + bg[2] * s.dL_dpixel[2];
+  s.gr = inside ? dL_dpixels[pix_id] : 0.f;
+  s.gg = inside ? dL_dpixels[plane + pix_id] : 0.f;
+  s.gb = inside ? dL_dpixels[2 * plane + pix_id] : 0.f;
+  s.gd = inside ? dL_dpixel_depths[pix_id] : 0.f;
+  s.ga = inside ? dL_dalphas[pix_id] : 0.f;
+  s.ar = s.ag = s.ab = s.ad = s.aa = 0.f;
+  s.tb = -T_final * (bg[0] * s.gr + bg[1] * s.gg + bg[2] * s.gb);
 }
 
-// one contributing fragment: advances the pixel's recurrences and adds its ten partial sums to q.
+// Quantity order of the reduction and of the per-warp accumulator rows, with u = G dL/dalpha:
+//   q0 sum u dx   q1 sum u dy   q2 sum u (= dL/dopacity)   q3 depth
+//   q4 sum u dx^2   q5 sum u dx dy   q6 sum u dy^2   q7..q9 colour
+// One contributing fragment: advances the pixel's recurrences and adds its partial sums to q.
 // COLORS_ONLY (EgsBackwardArgs.colors_only): just the transmittance recurrence and the three colour
 // sums; nothing that feeds the geometry or opacity gradients is evaluated.
 template <bool COLORS_ONLY>
-__device__ __forceinline__ void fragment_backward(PixelState& s, float dx, float dy, float power,
-                                                  const float4 a4, const float4 b4, const float4 c4,
-                                                  float ddelx_dx, float ddely_dy, float (&q)[10]) {
-  const float opac = a4.w;
+__device__ __forceinline__ void fragment_backward(PixelState& s, float dx, float dy, float power, float opac,
+                                                  const float4 c4, float depth, float (&q)[10]) {
   const float G = ex2_approx(power * 1.4426950408889634f);
   const float alpha = fminf(0.99f, opac * G);
   const float rcp = rcp_approx(1.f - alpha);
   s.T = s.T * rcp;
   const float w = alpha * s.T;
-  if (COLORS_ONLY) {
-#pragma unroll
-    for (int ch = 0; ch < 3; ++ch) q[7 + ch] += w * s.dL_dpixel[ch];
-    return;
-  }
-  float dL_dopa = 0.0f;
-  const float c[3] = {c4.x, c4.y, c4.z};
-#pragma unroll
-  for (int ch = 0; ch < 3; ++ch) {
-    s.accum_rec[ch] = s.last_alpha * s.last_color[ch] + (1.f - s.last_alpha) * s.accum_rec[ch];
-    s.last_color[ch] = c[ch];
-    dL_dopa += (c[ch] - s.accum_rec[ch]) * s.dL_dpixel[ch];
-    q[7 + ch] += w * s.dL_dpixel[ch];
-  }
-  const float c_d = b4.w;
-  s.accum_depth = s.last_alpha * s.last_depth + (1.f - s.last_alpha) * s.accum_depth;
-  s.last_depth = c_d;
-  dL_dopa += (c_d - s.accum_depth) * s.dL_ddepth;
-  q[3] += w * s.dL_ddepth;
-  s.accum_alpha = s.last_alpha + (1.f - s.last_alpha) * s.accum_alpha;
-  dL_dopa += (1 - s.accum_alpha) * s.dL_dalpha;
-  dL_dopa *= s.T;
-  s.last_alpha = alpha;
-  dL_dopa += (-s.T_final * rcp) * s.bg_dot;
-
-  const float dL_dG = opac * dL_dopa;
-  const float gdx = G * dx;
-  const float gdy = G * dy;
-  const float dG_ddelx = -gdx * b4.x - gdy * b4.y;
-  const float dG_ddely = -gdy * b4.z - gdx * b4.y;
-  q[0] += dL_dG * dG_ddelx * ddelx_dx;
-  q[1] += dL_dG * dG_ddely * ddely_dy;
-  q[4] += -0.5f * gdx * dx * dL_dG;
-  q[5] += -0.5f * gdx * dy * dL_dG;
-  q[6] += -0.5f * gdy * dy * dL_dG;
-  q[2] += G * dL_dopa;
+  q[7] += w * s.gr;
+  q[8] += w * s.gg;
+  q[9] += w * s.gb;
+  if (COLORS_ONLY) return;
+  q[3] += w * s.gd;
+  // (this fragment's value) - (what lies behind it), per channel: feeds dL/dalpha, and advances the
+  // "behind" recurrence to the next fragment of this pixel (one closer to the eye):
+  // alpha c + (1 - alpha) a = a + alpha (c - a)
+  const float dr = c4.x - s.ar, dg = c4.y - s.ag, db = c4.z - s.ab, dd = depth - s.ad, da = 1.f - s.aa;
+  float dL_dopa = dr * s.gr;
+  dL_dopa += dg * s.gg;
+  dL_dopa += db * s.gb;
+  dL_dopa += dd * s.gd;
+  dL_dopa += da * s.ga;
+  s.ar += alpha * dr;
+  s.ag += alpha * dg;
+  s.ab += alpha * db;
+  s.ad += alpha * dd;
+  s.aa += alpha * da;
+  dL_dopa = dL_dopa * s.T + s.tb * rcp;
+  const float u = G * dL_dopa;          // the opacity factor of dL/dG = o dL/dalpha is applied once per entry
+  const float ux = u * dx, uy = u * dy;
+  q[2] += u;
+  q[0] += ux;
+  q[1] += uy;
+  q[4] += ux * dx;
+  q[5] += ux * dy;
+  q[6] += uy * dy;
 }
 
-template <bool COLORS_ONLY>
-__global__ void __launch_bounds__(BWD2_THREADS)
-blend_backward2_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__ point_list,
-                       int W, int H, int grid_x, const float* __restrict__ bg_color,
-                       const float2* __restrict__ means2D, const float4* __restrict__ conic_opacity,
-                       const float4* __restrict__ rgb_depth, const float* __restrict__ alphas,
-                       const uint32_t* __restrict__ n_contrib, const float* __restrict__ dL_dpixels,
-                       const float* __restrict__ dL_dpixel_depths, const float* __restrict__ dL_dalphas,
-                       float4* __restrict__ acc) {
-  __shared__ uint32_t s_id[BWD2_BATCH];
-  __shared__ float4 s_a[BWD2_BATCH];   // mean.x, mean.y, thr = -log(255 o), opacity
-  __shared__ float4 s_b[BWD2_BATCH];   // conic.x, conic.y, conic.z, depth
-  __shared__ float4 s_c[BWD2_BATCH];   // r, g, b, -
+// (PPL = 4 takes ~118 registers, 8 CTAs of 64 threads per SM; bounding it to 96 registers for 10 CTAs
+// measured slower, 0.346 against 0.336 ms at C3)
+template <int PPL, bool COLORS_ONLY>
+__global__ void __launch_bounds__(256 / PPL)
+blend_backward_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__ point_list,
+                      int W, int H, int grid_x, const float* __restrict__ bg_color,
+                      const float2* __restrict__ means2D, const float4* __restrict__ conic_opacity,
+                      const float4* __restrict__ rgb_depth, const float* __restrict__ alphas,
+                      const uint32_t* __restrict__ n_contrib, const float* __restrict__ dL_dpixels,
+                      const float* __restrict__ dL_dpixel_depths, const float* __restrict__ dL_dalphas,
+                      float4* __restrict__ acc) {
+  constexpr int THREADS = 256 / PPL;
+  constexpr int WARPS = THREADS / 32;
+  constexpr int STAGE = BWD_BATCH / THREADS;     // entries a thread stages per batch
+  constexpr int BLOCK_H = 4 * PPL;               // a warp's pixels: 8 wide, BLOCK_H tall
+  static_assert(STAGE >= 1 && STAGE * THREADS == BWD_BATCH, "batch");
+  __shared__ uint32_t s_id[BWD_BATCH];
+  __shared__ float4 s_a[BWD_BATCH];   // mean.x, mean.y, thr = -log(255 o) - margin, opacity
+  __shared__ float4 s_b[BWD_BATCH];   // conic.x, conic.y, conic.z, depth
+  __shared__ float4 s_c[BWD_BATCH];   // r, g, b, -
   // one accumulator row per warp: a warp meets each entry of a batch once, so its total is a plain
   // store (shared-memory float atomicAdd is a compare-and-swap loop on this architecture)
-  __shared__ float s_acc[(BWD2_THREADS / 32) * BWD2_BATCH * ACC_PITCH];
-  __shared__ uint32_t s_hit[BWD2_BATCH];   // bit w: warp w stored totals for this entry in this batch
-  // [pixel warp][32-entry chunk]: entries of the batch that can reach the warp's 8x8 pixels. A warp
+  __shared__ float s_acc[WARPS * BWD_BATCH * ACC_PITCH];
+  __shared__ unsigned char s_hit[WARPS][BWD_BATCH];   // warp w stored totals for this entry in this batch
+  // [pixel warp][32-entry chunk]: entries of the batch that can reach the warp's pixels. A warp
   // pops set bits in list order and never issues an instruction for the other entries.
-  __shared__ uint32_t s_bits[BWD2_THREADS / 32][BWD2_BATCH / 32];
+  __shared__ uint32_t s_bits[WARPS][BWD_BATCH / 32];
   __shared__ uint32_t s_max_contrib;
 
   const unsigned tid = threadIdx.x;
   const unsigned warp = tid >> 5, lane = tid & 31;
-  // 4 warps as 2x2 blocks of 8x8 pixels; a lane owns (lx, ly) and (lx, ly + 4) of its block
+  // warps as 2 x (WARPS / 2) blocks of 8 x BLOCK_H pixels; a lane owns (x, y + 4 s), s < PPL
   const unsigned bx = blockIdx.x * TILE_X + (warp & 1) * 8 + (lane & 7);
-  const unsigned by = blockIdx.y * TILE_Y + (warp >> 1) * 8 + (lane >> 3);
+  const unsigned by = blockIdx.y * TILE_Y + (warp >> 1) * BLOCK_H + (lane >> 3);
   const float bg[3] = {bg_color[0], bg_color[1], bg_color[2]};
-  PixelState P0, P1;
-  {
-    const bool in0 = bx < (unsigned)W && by < (unsigned)H;
-    const bool in1 = bx < (unsigned)W && (by + 4) < (unsigned)H;
-    pixel_init(P0, in0, (uint32_t)W * by + bx, bx, by, W, H, alphas, n_contrib, dL_dpixels, dL_dpixel_depths,
-               dL_dalphas, bg);
-    pixel_init(P1, in1, (uint32_t)W * (by + 4) + bx, bx, by + 4, W, H, alphas, n_contrib, dL_dpixels,
+  const float pxf = (float)bx, pyf = (float)by;
+  PixelState px[PPL];
+#pragma unroll
+  for (int s = 0; s < PPL; ++s) {
+    const unsigned y = by + 4 * s;
+    pixel_init(px[s], bx < (unsigned)W && y < (unsigned)H, (uint32_t)W * y + bx, W, H, alphas, n_contrib, dL_dpixels,
                dL_dpixel_depths, dL_dalphas, bg);
   }
   const uint2 range = ranges[blockIdx.y * grid_x + blockIdx.x];
 
   if (tid == 0) s_max_contrib = 0;
   __syncthreads();
-  uint32_t warp_last = max(P0.last, P1.last);
+  uint32_t warp_last = 0;
+#pragma unroll
+  for (int s = 0; s < PPL; ++s) warp_last = max(warp_last, px[s].last);
 #pragma unroll
   for (int d = 16; d > 0; d >>= 1) warp_last = max(warp_last, __shfl_xor_sync(0xffffffffu, warp_last, d));
   if (lane == 0 && warp_last) atomicMax(&s_max_contrib, warp_last);
@@ -256,44 +258,48 @@ blend_backward2_kernel(const uint2* __restrict__ ranges, const uint32_t* __restr
   // shared-window addresses formed once (see lds_f4 in common.cuh)
   uint32_t a_a = smem_addr(s_a), a_b = smem_addr(s_b), a_c = smem_addr(s_c);
   uint32_t a_bits = smem_addr(&s_bits[warp][0]);
-  uint32_t a_acc = smem_addr(&s_acc[warp * BWD2_BATCH * ACC_PITCH + my_slot]);   // this lane's slot, entry 0
+  uint32_t a_hit = smem_addr(&s_hit[warp][0]);
+  uint32_t a_acc = smem_addr(&s_acc[warp * BWD_BATCH * ACC_PITCH + my_slot]);   // this lane's slot, entry 0
   // opaque to the optimiser, or it re-derives the window addresses inside the loop
-  asm volatile("" : "+r"(a_a), "+r"(a_b), "+r"(a_c), "+r"(a_bits), "+r"(a_acc));
+  asm volatile("" : "+r"(a_a), "+r"(a_b), "+r"(a_c), "+r"(a_bits), "+r"(a_acc), "+r"(a_hit));
 
-  const int rounds = (walk + BWD2_BATCH - 1) / BWD2_BATCH;
+  const int rounds = (walk + BWD_BATCH - 1) / BWD_BATCH;
   for (int r = 0; r < rounds; ++r) {
     __syncthreads();
-    const int pos = walk - 1 - (r * BWD2_BATCH + (int)tid);
-    unsigned reach = 0u;
-    if (pos >= 0) {
-      const uint32_t id = point_list[range.x + pos];
-      const float2 xy = means2D[id];
-      const float4 co = conic_opacity[id];
-      const float4 cd = rgb_depth[id];
-      s_id[tid] = id;
-      // alpha >= 1/255  <=>  power >= -log(255 o), staged with the margin subtracted; o <= 0 can
-      // never contribute
-      s_a[tid] = make_float4(xy.x, xy.y, co.w > 0.f ? -__logf(255.f * co.w) - CONTRIB_MARGIN : 1.f, co.w);
-      reach = footprint_mask<8, 8>(xy, co, (float)(blockIdx.x * TILE_X), (float)(blockIdx.y * TILE_Y));
-      s_b[tid] = make_float4(co.x, co.y, co.z, cd.w);
-      s_c[tid] = cd;
-    }
-    s_hit[tid] = 0u;
-    {
+#pragma unroll
+    for (int h = 0; h < STAGE; ++h) {
+      const int slot = h * THREADS + (int)tid;      // staged back to front; its 32-entry chunk is h * WARPS + warp
+      const int pos = walk - 1 - (r * BWD_BATCH + slot);
+      unsigned reach = 0u;
+      if (pos >= 0) {
+        const uint32_t id = point_list[range.x + pos];
+        const float2 xy = means2D[id];
+        const float4 co = conic_opacity[id];
+        const float4 cd = rgb_depth[id];
+        s_id[slot] = id;
+        // alpha >= 1/255  <=>  power >= -log(255 o), staged with the margin subtracted; o <= 0 can
+        // never contribute
+        s_a[slot] = make_float4(xy.x, xy.y, co.w > 0.f ? -__logf(255.f * co.w) - CONTRIB_MARGIN : 1.f, co.w);
+        reach = footprint_mask<8, BLOCK_H>(xy, co, (float)(blockIdx.x * TILE_X), (float)(blockIdx.y * TILE_Y));
+        s_b[slot] = make_float4(co.x, co.y, co.z, cd.w);
+        s_c[slot] = cd;
+      }
+#pragma unroll
+      for (unsigned w = 0; w < WARPS; ++w) s_hit[w][slot] = 0;
       uint32_t mine = 0u;   // lane w ends up with pixel warp w's word for this staging warp's chunk
 #pragma unroll
-      for (unsigned w = 0; w < BWD2_THREADS / 32; ++w) {
+      for (unsigned w = 0; w < WARPS; ++w) {
         const uint32_t word = __ballot_sync(0xffffffffu, (reach >> w) & 1u);
         if (lane == w) mine = word;
       }
-      if (lane < BWD2_THREADS / 32) s_bits[lane][warp] = mine;
+      if (lane < WARPS) s_bits[lane][h * WARPS + warp] = mine;
     }
     __syncthreads();
 
-    const int n = min(BWD2_BATCH, walk - r * BWD2_BATCH);
+    const int n = min(BWD_BATCH, walk - r * BWD_BATCH);
     // entries j < jmin lie behind the last contributor of every pixel of this warp
-    const int jmin = walk - r * BWD2_BATCH - (int)warp_last;
-    for (int c = 0; c < BWD2_BATCH / 32; ++c) {
+    const int jmin = walk - r * BWD_BATCH - (int)warp_last;
+    for (int c = 0; c < BWD_BATCH / 32; ++c) {
      uint32_t bits = lds_u32(a_bits + 4u * c);
      const int lo = jmin - 32 * c;
      if (lo >= 32) continue;
@@ -301,54 +307,74 @@ blend_backward2_kernel(const uint2* __restrict__ ranges, const uint32_t* __restr
      while (bits != 0u) {   // warp-uniform: every lane holds the same word
       const int j = c * 32 + __ffs((int)bits) - 1;
       bits &= bits - 1u;
-      const uint32_t jpos = (uint32_t)(walk - 1 - (r * BWD2_BATCH + j));
+      const uint32_t jpos = (uint32_t)(walk - 1 - (r * BWD_BATCH + j));
       const float4 a4 = lds_f4(a_a + 16u * j);
       const float4 b4 = lds_f4(a_b + 16u * j);
-      const float dx0 = a4.x - P0.px, dy0 = a4.y - P0.py;
-      const float dx1 = a4.x - P1.px, dy1 = a4.y - P1.py;
-      const float power0 = -0.5f * (b4.x * dx0 * dx0 + b4.z * dy0 * dy0) - b4.y * dx0 * dy0;
-      const float power1 = -0.5f * (b4.x * dx1 * dx1 + b4.z * dy1 * dy1) - b4.y * dx1 * dy1;
-      bool act0 = jpos < P0.last && power0 <= 0.0f && power0 >= a4.z;
-      bool act1 = jpos < P1.last && power1 <= 0.0f && power1 >= a4.z;
-      if (!__any_sync(0xffffffffu, act0 || act1)) continue;
-      // inside the band around the threshold the forward's own expression decides
-      const float band_hi = a4.z + 2.f * CONTRIB_MARGIN;
-      if (act0 && power0 < band_hi) act0 = contributes_exact(a4.w, power0);
-      if (act1 && power1 < band_hi) act1 = contributes_exact(a4.w, power1);
-
+      const float dx = a4.x - pxf;
+      const float ax = __fmul_rn(b4.x, dx), bxm = __fmul_rn(b4.y, dx);   // shared by the lane's pixels (one column)
+      float dy[PPL], power[PPL];
+      bool act[PPL];
+      bool any = false;
+#pragma unroll
+      for (int s = 0; s < PPL; ++s) {
+        dy[s] = a4.y - (pyf + (float)(4 * s));
+        power[s] = splat_power_pre(ax, bxm, b4.z, dx, dy[s]);   // the forward's bits
+        act[s] = jpos < px[s].last && power[s] <= 0.0f && power[s] >= a4.z;
+        any = any || act[s];
+      }
+      if (!__any_sync(0xffffffffu, any)) continue;
       float q[10];
 #pragma unroll
       for (int k = 0; k < 10; ++k) q[k] = 0.f;
       const float4 c4 = lds_f4(a_c + 16u * j);
-      if (act0) fragment_backward<COLORS_ONLY>(P0, dx0, dy0, power0, a4, b4, c4, ddelx_dx, ddely_dy, q);
-      if (act1) fragment_backward<COLORS_ONLY>(P1, dx1, dy1, power1, a4, b4, c4, ddelx_dx, ddely_dy, q);
+      const float band_hi = a4.z + 2.f * CONTRIB_MARGIN;
+#pragma unroll
+      for (int s = 0; s < PPL; ++s) {
+        if (act[s]) {
+          // inside the band around the threshold the forward's own expression decides
+          if (power[s] >= band_hi || contributes_exact(a4.w, power[s]))
+            fragment_backward<COLORS_ONLY>(px[s], dx, dy[s], power[s], a4.w, c4, b4.w, q);
+        }
+      }
       const float total = warp_packed_reduce10(q, lane);
       if (i_add) sts_f32(a_acc + (uint32_t)(j * ACC_PITCH * 4), total);
-      if (lane == 0) atomicOr(&s_hit[j], 1u << warp);
+      if (lane == 0) asm volatile("st.shared.u8 [%0], %1;" ::"r"(a_hit + (uint32_t)j), "r"(1u) : "memory");
      }
     }
     __syncthreads();
 
-    if ((int)tid < n) {
+    // flush: a thread owns STAGE entries of the batch; moments -> dL/dmean2D, dL/dconic
+#pragma unroll
+    for (int h = 0; h < STAGE; ++h) {
+      const int e = h * THREADS + (int)tid;
+      if (e >= n) continue;
+      uint32_t hit = 0u;
+#pragma unroll
+      for (int w = 0; w < WARPS; ++w) hit |= (uint32_t)s_hit[w][e] << w;
+      if (!hit) continue;
       float v[ACC_STRIDE];
 #pragma unroll
       for (int k = 0; k < ACC_STRIDE; ++k) v[k] = 0.f;
-      const uint32_t hit = s_hit[tid];
 #pragma unroll
-      for (int w = 0; w < BWD2_THREADS / 32; ++w) {
+      for (int w = 0; w < WARPS; ++w) {
         if (hit & (1u << w)) {
-          const float* row = &s_acc[(w * BWD2_BATCH + tid) * ACC_PITCH];
+          const float* row = &s_acc[(w * BWD_BATCH + e) * ACC_PITCH];
 #pragma unroll
           for (int k = 0; k < ACC_STRIDE; ++k)
             if (k != 7 && k != 11) v[k] += row[k];   // slots 7 and 11 are padding, never written
         }
       }
-      if (hit) {
-        float4* dst = acc + (size_t)s_id[tid] * 3;
-        atomicAdd(dst + 0, make_float4(v[0], v[1], v[2], v[3]));
-        atomicAdd(dst + 1, make_float4(v[4], v[5], v[6], v[7]));
-        atomicAdd(dst + 2, make_float4(v[8], v[9], v[10], v[11]));
+      float4* dst = acc + (size_t)s_id[e] * 3;
+      if (!COLORS_ONLY) {
+        const float4 b4 = s_b[e];
+        const float o = s_a[e].w;
+        const float sx = o * v[0], sy = o * v[1];   // dL/dG = o dL/dalpha
+        // dG/ddx = -G (A dx + B dy), dG/ddy = -G (C dy + B dx); d(conic) = -0.5 G (dx^2, dx dy, dy^2)
+        atomicAdd(dst + 0, make_float4((-b4.x * sx - b4.y * sy) * ddelx_dx, (-b4.z * sy - b4.y * sx) * ddely_dy, v[2], v[3]));
+        const float h = -0.5f * o;
+        atomicAdd(dst + 1, make_float4(h * v[4], h * v[5], h * v[6], 0.f));
       }
+      atomicAdd(dst + 2, make_float4(v[8], v[9], v[10], 0.f));
     }
   }
 }
@@ -357,17 +383,18 @@ int launch_blend_backward(const EgsBackwardArgs& a, const GeomPtrs& g, const uin
                           const ImagePtrs& im, const BackwardScratch& s, cudaStream_t stream) {
   const dim3 grid(tiles_x(a.width), tiles_y(a.height), 1);
   StageTimer timer(stream, ST_BLEND_BWD);
+  // pixels per lane: 4 by default; egs_debug_option("blend_backward", "2") for the A/B
+  const int ppl = debug_options().bwd_ppl == 2 ? 2 : 4;
+#define EGS_BWD_LAUNCH(PPL, CO)                                                                                   \
+  blend_backward_kernel<PPL, CO><<<grid, 256 / PPL, 0, stream>>>(                                                 \
+      im.ranges, point_list, a.width, a.height, (int)grid.x, a.background, g.means2D, g.conic_opacity, g.rgb_depth, \
+      a.out_alpha, im.n_contrib, a.dL_dout_color, a.dL_dout_depth, a.dL_dout_alpha, s.acc)
   if (a.colors_only) {
-    blend_backward2_kernel<true><<<grid, BWD2_THREADS, 0, stream>>>(
-        im.ranges, point_list, a.width, a.height, (int)grid.x, a.background, g.means2D,
-        g.conic_opacity, g.rgb_depth, a.out_alpha, im.n_contrib, a.dL_dout_color, a.dL_dout_depth,
-        a.dL_dout_alpha, s.acc);
+    if (ppl == 2) EGS_BWD_LAUNCH(2, true); else EGS_BWD_LAUNCH(4, true);
   } else {
-    blend_backward2_kernel<false><<<grid, BWD2_THREADS, 0, stream>>>(
-        im.ranges, point_list, a.width, a.height, (int)grid.x, a.background, g.means2D,
-        g.conic_opacity, g.rgb_depth, a.out_alpha, im.n_contrib, a.dL_dout_color, a.dL_dout_depth,
-        a.dL_dout_alpha, s.acc);
+    if (ppl == 2) EGS_BWD_LAUNCH(2, false); else EGS_BWD_LAUNCH(4, false);
   }
+#undef EGS_BWD_LAUNCH
   EGS_AFTER_LAUNCH(stream, a.debug);
   return EGS_OK;
 }

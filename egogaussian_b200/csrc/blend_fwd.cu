@@ -94,7 +94,7 @@ blend_forward3_kernel(const uint2* __restrict__ ranges, const uint32_t* __restri
         const float2 xy = lds_f2(a_xy + 8u * j);
         const float4 con_o = lds_f4(a_co + 16u * j);
         const float2 d = make_float2(xy.x - pixf.x, xy.y - pixf.y);
-        const float power = -0.5f * (con_o.x * d.x * d.x + con_o.z * d.y * d.y) - con_o.y * d.x * d.y;
+        const float power = splat_power(con_o.x, con_o.y, con_o.z, d.x, d.y);
         if (power > 0.0f) continue;
         const float alpha = min(0.99f, con_o.w * expf(power));
         if (alpha < 1.0f / 255.0f) continue;
@@ -151,7 +151,7 @@ struct FwdPixel {
 __device__ __forceinline__ void fwd_fragment(FwdPixel& s, const float4 a4, const float4 con_o, const float4 cd,
                                              uint32_t contributor) {
   const float2 d = make_float2(a4.x - s.px, a4.y - s.py);
-  const float power = -0.5f * (con_o.x * d.x * d.x + con_o.z * d.y * d.y) - con_o.y * d.x * d.y;
+  const float power = splat_power(con_o.x, con_o.y, con_o.z, d.x, d.y);
   if (power > 0.0f) return;
   if (power < a4.z) return;   // certainly alpha < 1/255 (conservative margin, see above)
   const float alpha = min(0.99f, con_o.w * expf(power));

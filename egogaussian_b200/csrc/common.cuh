@@ -304,6 +304,7 @@ struct DebugOptions {
   int presort_scramble;   // 1: presort keys unrelated to depth + veto raised (exercises the fallback)
   int fwd_v2;             // 1: the two-pixels-per-thread forward blend (independent implementation)
   int exchange_phases;    // timing only: 1 = only the slice sum, 2 = only the SH expansion, 0 = both
+  int bwd_ppl;            // pixels per lane of the backward blend: 0 default (4), 2 for the A/B
 };
 DebugOptions debug_options();
 int launch_tile_ranges(int R, const uint64_t* sorted_keys, const ImagePtrs& im, cudaStream_t stream,
@@ -506,6 +507,25 @@ __device__ __forceinline__ unsigned footprint_mask(const float2 xy, const float4
     }
   }
   return mask;
+}
+
+// The exponent of a splat at offset (dx, dy) from its centre, conic (A, B, C):
+//   -0.5 (A dx^2 + C dy^2) - B dx dy        (forward.cu:330-331, backward.cu:505-506).
+// A long, rotated splat makes the three terms cancel (hundreds against a sum of a few units), so the
+// last bits of the result depend on where the compiler fuses multiplies and adds -- and alpha = o
+// exp(power) has to come out the same in the backward pass as in the forward pass, or T = T / (1 - alpha)
+// drifts along the pixel's list (measured: 2e-4 instead of 2e-6 of the gradient maximum on the big
+// splats of a 2M-Gaussian scene, flipping with the register allocation). The roundings are therefore
+// written out, in the order nvcc gives the reference's expression (checked in the SASS of its forward
+// kernel; the images stay bit-identical to the reference's), and every blend kernel uses this one
+// definition. ax = A dx and bx = B dx may be formed once per entry for several pixels of a column.
+__device__ __forceinline__ float splat_power_pre(float ax, float bx, float C, float dx, float dy) {
+  const float cyy = __fmul_rn(dy, __fmul_rn(C, dy));
+  const float bxy = __fmul_rn(dy, bx);
+  return __fmaf_rn(__fmaf_rn(dx, ax, cyy), -0.5f, -bxy);
+}
+__device__ __forceinline__ float splat_power(float A, float B, float C, float dx, float dy) {
+  return splat_power_pre(__fmul_rn(A, dx), __fmul_rn(B, dx), C, dx, dy);
 }
 
 // Shared-memory loads through a 32-bit shared-window address that is formed once outside the hot

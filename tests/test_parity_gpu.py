@@ -349,7 +349,7 @@ def debug_options():
     """Library switches (egs_debug_option) are process-wide: hand out the setter, restore the defaults after."""
     from egogaussian_b200 import cabi
     yield cabi.debug_option
-    for name in ("sort", "presort", "presort_scramble", "blend_forward"):
+    for name in ("sort", "presort", "presort_scramble", "blend_forward", "blend_backward"):
         cabi.debug_option(name, None)
 
 
@@ -530,6 +530,22 @@ def test_forward_kernel_variants_agree(built, cuda_device, debug_options):
     for k in ("color", "depth", "alpha"):
         assert torch.equal(getattr(f1, k), getattr(f2, k)), k
     assert torch.equal(f1.image_view()["n_contrib"], f2.image_view()["n_contrib"])
+
+
+def test_backward_kernel_variants_agree(built, cuda_device, debug_options):
+    """The backward blend with two pixels per thread (four warps per tile) and with four (two warps per
+    tile) sums the same fragments in another order: equal within the gradient tolerance, also for the
+    colour-only backward of the label render."""
+    from egogaussian_b200 import cabi
+    for case in (CASES[0], CASES[2]):
+        kw, ups = case_inputs(case, cuda_device)
+        _, g4 = run_cuda(kw, ups)
+        debug_options("blend_backward", "2")
+        _, g2 = run_cuda(kw, ups)
+        debug_options("blend_backward", None)
+        for k in ("means2D", "means3D", "opacity", "sh", "colors", "scales", "rotations", "cov3D"):
+            if g4.get(k) is not None:
+                assert grad_rel_err(g2[k], g4[k]) <= GRAD_RTOL, (case[0], k)
 
 
 def test_backward_contributor_set_matches_forward(built, cuda_device):
