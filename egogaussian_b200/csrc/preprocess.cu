@@ -111,7 +111,11 @@ __device__ __forceinline__ float3 sh_to_rgb(int deg, int M, const float3 pos, co
 // 192-byte row in global memory made the kernel L1-bound (ncu: l1tex 86 %, dram 29 %).
 constexpr int PF_THREADS = 128;
 constexpr int PF_SH_ROW = 48;
-constexpr int PF_SH_PITCH = 49;
+// pitch of a staged SH row: 52 floats (16-byte aligned rows, read with 16-byte shared loads) for the
+// contiguous tensor, 49 (odd: conflict-free scalar reads) for the split dc / rest rows, whose pieces
+// start at 12- and 180-byte offsets
+constexpr int PF_SH_PITCH = 52;
+constexpr int PF_SH_PITCH_SPLIT = 49;
 
 // SH_MODE: 0 = every thread reads its own row from global memory, 1 = rows staged with float4
 // loads from one contiguous [P,16,3] tensor, 2 = rows staged from the split features_dc /
@@ -140,7 +144,7 @@ preprocess_forward_kernel(RawModel raw, int P, int D, int M, const float* __rest
     s_proj[threadIdx.x] = projmatrix[threadIdx.x];
   }
   if (threadIdx.x < 3) s_cam[threadIdx.x] = campos[threadIdx.x];
-  __shared__ float s_sh[SH_MODE != 0 ? (PF_THREADS / 32) * 32 * PF_SH_PITCH : 1];
+  __shared__ __align__(16) float s_sh[SH_MODE != 0 ? (PF_THREADS / 32) * 32 * PF_SH_PITCH : 4];
   __shared__ float s_rot[RAW ? 18 : 1];
   if (RAW) stage_rotations(raw, s_rot);
   __syncthreads();
@@ -174,19 +178,19 @@ preprocess_forward_kernel(RawModel raw, int P, int D, int M, const float* __rest
     float* tile = s_sh + warp * 32 * PF_SH_PITCH;
     if (rows > 0) {
       const int wrest = 3 * M - 3;
-      stage_rows_async(tile, PF_SH_PITCH, 0, 3, raw.features_dc + (size_t)first * 3, rows * 3, lane);
+      stage_rows_async(tile, PF_SH_PITCH_SPLIT, 0, 3, raw.features_dc + (size_t)first * 3, rows * 3, lane);
       if (wrest > 0)
-        stage_rows_async(tile, PF_SH_PITCH, 3, wrest, raw.features_rest + (size_t)first * wrest, rows * wrest, lane);
+        stage_rows_async(tile, PF_SH_PITCH_SPLIT, 3, wrest, raw.features_rest + (size_t)first * wrest, rows * wrest, lane);
     }
     stage_rows_wait();
-    sh_row = tile + lane * PF_SH_PITCH;
+    sh_row = tile + lane * PF_SH_PITCH_SPLIT;
   } else if (SH_MODE == 1) {
     const unsigned lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const int first = blockIdx.x * blockDim.x + warp * 32;
     const int rows = min(32, P - first);
     float* tile = s_sh + warp * 32 * PF_SH_PITCH;
     if (rows > 0) {
-      stage_rows_async(tile, PF_SH_PITCH, 0, PF_SH_ROW, shs + (size_t)first * PF_SH_ROW, rows * PF_SH_ROW, lane);
+      stage_rows_async16(tile, PF_SH_PITCH, PF_SH_ROW, shs + (size_t)first * PF_SH_ROW, rows * PF_SH_ROW, lane);
     }
     stage_rows_wait();
     sh_row = tile + lane * PF_SH_PITCH;
@@ -239,7 +243,21 @@ preprocess_forward_kernel(RawModel raw, int P, int D, int M, const float* __rest
         float3 rgb;
         unsigned char cb = 0;
         if (colors_precomp == nullptr) {
-          rgb = sh_to_rgb(D, M, p_orig, make_float3(s_cam[0], s_cam[1], s_cam[2]), sh_row, cb);
+          if (SH_MODE == 1) {
+            // the staged row is 16-byte aligned: twelve 16-byte shared loads instead of 48 scalar ones
+            // (the kernel waited on the load/store queue, ncu mio_throttle); the values then sit in
+            // registers and the evaluation keeps the reference's expression shapes
+            const float4* r4 = reinterpret_cast<const float4*>(__builtin_assume_aligned(sh_row, 16));
+            float v[PF_SH_ROW];
+#pragma unroll
+            for (int c = 0; c < PF_SH_ROW / 4; ++c) {
+              const float4 t = r4[c];
+              v[4 * c] = t.x; v[4 * c + 1] = t.y; v[4 * c + 2] = t.z; v[4 * c + 3] = t.w;
+            }
+            rgb = sh_to_rgb(D, M, p_orig, make_float3(s_cam[0], s_cam[1], s_cam[2]), v, cb);
+          } else {
+            rgb = sh_to_rgb(D, M, p_orig, make_float3(s_cam[0], s_cam[1], s_cam[2]), sh_row, cb);
+          }
           clamped[idx] = cb;
         } else {
           rgb = make_float3(colors_precomp[3 * idx], colors_precomp[3 * idx + 1],

@@ -44,11 +44,14 @@ __device__ __forceinline__ F3 operator-(const F3& a) { return {-a.x, -a.y, -a.z}
 __device__ __forceinline__ float dot(const F3& a, const F3& b) { return a.x * b.x + a.y * b.y + a.z * b.z; }
 
 // SH backward: writes dL/dsh[0 .. M) (zeros above the active degree) and returns the part of
-// dL/dmean caused by the view direction. Coefficient k is read before its gradient is written, so
+// dL/dmean caused by the view direction. All coefficients are read before any gradient is written, so
 // `shp` and `dL_dsh_out` may be the same row (the staged kernel works in place in shared memory).
 // Basis functions and their derivatives are those of backward.cu:20-139, grouped per coefficient.
+// VEC: the row holds 16 coefficients and is 16-byte aligned (staged [P,16,3] rows, pitch 52): twelve
+// 16-byte shared loads and stores instead of 48 scalar ones each way.
 // dL_dsh_out == NULL (factored mode): the rows are not formed; the caller keeps the clamp-masked
 // dL/dRGB (returned through dL_dRGB) and whoever needs dL/dsh multiplies it by the basis values.
+template <bool VEC>
 __device__ __forceinline__ float3 sh_backward(int deg, int M, const float3 pos, const float3 cam,
                                               const float* shp, unsigned char clamp_bits, F3& dL_dRGB,
                                               float* dL_dsh_out) {
@@ -59,53 +62,80 @@ __device__ __forceinline__ float3 sh_backward(int deg, int M, const float3 pos, 
   dL_dRGB.y *= (clamp_bits & 2) ? 0.f : 1.f;
   dL_dRGB.z *= (clamp_bits & 4) ? 0.f : 1.f;
 
+  const int n_act = (deg + 1) * (deg + 1);   // coefficients of the active degree
+  float cf[48];
+  if (VEC) {
+    const float4* r4 = reinterpret_cast<const float4*>(__builtin_assume_aligned(shp, 16));
+#pragma unroll
+    for (int c = 0; c < 12; ++c) {
+      const float4 t = r4[c];
+      cf[4 * c] = t.x; cf[4 * c + 1] = t.y; cf[4 * c + 2] = t.z; cf[4 * c + 3] = t.w;
+    }
+  } else {
+#pragma unroll
+    for (int k = 0; k < 16; ++k)
+      if (k < n_act) {
+        cf[3 * k] = shp[3 * k]; cf[3 * k + 1] = shp[3 * k + 1]; cf[3 * k + 2] = shp[3 * k + 2];
+      }
+  }
   F3 dRGBdx = {0, 0, 0}, dRGBdy = {0, 0, 0}, dRGBdz = {0, 0, 0};
   float basis[16];
+#pragma unroll
+  for (int k = 0; k < 16; ++k) basis[k] = 0.f;
   sh_basis_values(deg, x, y, z, basis);
-  // one coefficient: basis value b and its derivatives (bx, by, bz) with respect to the direction
-  auto term = [&](int k, float b, float bx, float by, float bz) {
-    const F3 c = {shp[3 * k], shp[3 * k + 1], shp[3 * k + 2]};
+  // one coefficient: the derivatives (bx, by, bz) of its basis function with respect to the direction
+  auto term = [&](int k, float bx, float by, float bz) {
+    const F3 c = {cf[3 * k], cf[3 * k + 1], cf[3 * k + 2]};
     dRGBdx = dRGBdx + bx * c;
     dRGBdy = dRGBdy + by * c;
     dRGBdz = dRGBdz + bz * c;
-    if (dL_dsh_out != nullptr) {
-      dL_dsh_out[3 * k] = b * dL_dRGB.x;
-      dL_dsh_out[3 * k + 1] = b * dL_dRGB.y;
-      dL_dsh_out[3 * k + 2] = b * dL_dRGB.z;
-    }
   };
-  term(0, basis[0], 0.f, 0.f, 0.f);
-  int written = 1;
   if (deg > 0) {
-    term(1, basis[1], 0.f, -kSH1, 0.f);
-    term(2, basis[2], 0.f, 0.f, kSH1);
-    term(3, basis[3], -kSH1, 0.f, 0.f);
-    written = 4;
+    term(1, 0.f, -kSH1, 0.f);
+    term(2, 0.f, 0.f, kSH1);
+    term(3, -kSH1, 0.f, 0.f);
     if (deg > 1) {
       const float xx = x * x, yy = y * y, zz = z * z;
       const float xy = x * y, yz = y * z, xz = x * z;
-      term(4, basis[4], kSH2[0] * y, kSH2[0] * x, 0.f);
-      term(5, basis[5], 0.f, kSH2[1] * z, kSH2[1] * y);
-      term(6, basis[6], kSH2[2] * 2.f * -x, kSH2[2] * 2.f * -y, kSH2[2] * 2.f * 2.f * z);
-      term(7, basis[7], kSH2[3] * z, 0.f, kSH2[3] * x);
-      term(8, basis[8], kSH2[4] * 2.f * x, kSH2[4] * 2.f * -y, 0.f);
-      written = 9;
+      term(4, kSH2[0] * y, kSH2[0] * x, 0.f);
+      term(5, 0.f, kSH2[1] * z, kSH2[1] * y);
+      term(6, kSH2[2] * 2.f * -x, kSH2[2] * 2.f * -y, kSH2[2] * 2.f * 2.f * z);
+      term(7, kSH2[3] * z, 0.f, kSH2[3] * x);
+      term(8, kSH2[4] * 2.f * x, kSH2[4] * 2.f * -y, 0.f);
       if (deg > 2) {
-        term(9, basis[9], kSH3[0] * 3.f * 2.f * xy, kSH3[0] * 3.f * (xx - yy), 0.f);
-        term(10, basis[10], kSH3[1] * yz, kSH3[1] * xz, kSH3[1] * xy);
-        term(11, basis[11], kSH3[2] * -2.f * xy, kSH3[2] * (-3.f * yy + 4.f * zz - xx), kSH3[2] * 4.f * 2.f * yz);
-        term(12, basis[12], kSH3[3] * -3.f * 2.f * xz, kSH3[3] * -3.f * 2.f * yz, kSH3[3] * 3.f * (2.f * zz - xx - yy));
-        term(13, basis[13], kSH3[4] * (-3.f * xx + 4.f * zz - yy), kSH3[4] * -2.f * xy, kSH3[4] * 4.f * 2.f * xz);
-        term(14, basis[14], kSH3[5] * 2.f * xz, kSH3[5] * -2.f * yz, kSH3[5] * (xx - yy));
-        term(15, basis[15], kSH3[6] * 3.f * (xx - yy), kSH3[6] * -3.f * 2.f * xy, 0.f);
-        written = 16;
+        term(9, kSH3[0] * 3.f * 2.f * xy, kSH3[0] * 3.f * (xx - yy), 0.f);
+        term(10, kSH3[1] * yz, kSH3[1] * xz, kSH3[1] * xy);
+        term(11, kSH3[2] * -2.f * xy, kSH3[2] * (-3.f * yy + 4.f * zz - xx), kSH3[2] * 4.f * 2.f * yz);
+        term(12, kSH3[3] * -3.f * 2.f * xz, kSH3[3] * -3.f * 2.f * yz, kSH3[3] * 3.f * (2.f * zz - xx - yy));
+        term(13, kSH3[4] * (-3.f * xx + 4.f * zz - yy), kSH3[4] * -2.f * xy, kSH3[4] * 4.f * 2.f * xz);
+        term(14, kSH3[5] * 2.f * xz, kSH3[5] * -2.f * yz, kSH3[5] * (xx - yy));
+        term(15, kSH3[6] * 3.f * (xx - yy), kSH3[6] * -3.f * 2.f * xy, 0.f);
       }
     }
   }
-  for (int k = written; k < M && dL_dsh_out != nullptr; ++k) {
-    dL_dsh_out[3 * k] = 0.f;
-    dL_dsh_out[3 * k + 1] = 0.f;
-    dL_dsh_out[3 * k + 2] = 0.f;
+  // dL/dsh[k][c] = basis_k * dL/dRGB[c]; basis_k = 0 above the active degree
+  if (dL_dsh_out != nullptr) {
+    const float g[3] = {dL_dRGB.x, dL_dRGB.y, dL_dRGB.z};
+    if (VEC) {
+      float4* o4 = reinterpret_cast<float4*>(__builtin_assume_aligned(dL_dsh_out, 16));
+#pragma unroll
+      for (int c = 0; c < 12; ++c)
+        o4[c] = make_float4(basis[(4 * c) / 3] * g[(4 * c) % 3], basis[(4 * c + 1) / 3] * g[(4 * c + 1) % 3],
+                            basis[(4 * c + 2) / 3] * g[(4 * c + 2) % 3], basis[(4 * c + 3) / 3] * g[(4 * c + 3) % 3]);
+    } else {
+#pragma unroll
+      for (int k = 0; k < 16; ++k)
+        if (k < M) {
+          dL_dsh_out[3 * k] = basis[k] * g[0];
+          dL_dsh_out[3 * k + 1] = basis[k] * g[1];
+          dL_dsh_out[3 * k + 2] = basis[k] * g[2];
+        }
+      for (int k = 16; k < M; ++k) {   // storage beyond degree 3: no basis function, zero gradient
+        dL_dsh_out[3 * k] = 0.f;
+        dL_dsh_out[3 * k + 1] = 0.f;
+        dL_dsh_out[3 * k + 2] = 0.f;
+      }
+    }
   }
   const float3 dL_ddir = make_float3(dot(dRGBdx, dL_dRGB), dot(dRGBdy, dL_dRGB), dot(dRGBdz, dL_dRGB));
   return dnormalize(dir_orig, dL_ddir);
@@ -179,7 +209,7 @@ __device__ __forceinline__ void cov3d_recompute(const float3 s, float mod, const
 // Everything one Gaussian needs. `sh_in` / `sh_out` are this Gaussian's rows of SH coefficients
 // and of their gradients; they may be the same shared-memory row (staged mode) because every
 // coefficient is read before its gradient is written.
-template <bool RAW>
+template <bool RAW, bool VEC>
 __device__ __forceinline__ void
 gaussian_backward(int idx, int D, int M, const float* __restrict__ means3D, const int* __restrict__ radii,
                   const float* sh_in, float* sh_out, bool has_sh,
@@ -227,7 +257,13 @@ gaussian_backward(int idx, int D, int M, const float* __restrict__ means3D, cons
       for (int k = 0; k < 6; ++k) dL_dcov3D[6 * idx + k] = 0.f;
     }
     if (has_sh && sh_out != nullptr) {
-      for (int k = 0; k < 3 * M; ++k) sh_out[k] = 0.f;
+      if (VEC) {
+        float4* o4 = reinterpret_cast<float4*>(__builtin_assume_aligned(sh_out, 16));
+#pragma unroll
+        for (int c = 0; c < 12; ++c) o4[c] = make_float4(0.f, 0.f, 0.f, 0.f);
+      } else {
+        for (int k = 0; k < 3 * M; ++k) sh_out[k] = 0.f;
+      }
     }
     if (scales != nullptr && !raw_geom) {
 #pragma unroll
@@ -357,8 +393,8 @@ gaussian_backward(int idx, int D, int M, const float* __restrict__ means3D, cons
   // ---- colour part --------------------------------------------------------------------------
   if (has_sh) {
     F3 drgb = {a2.x, a2.y, a2.z};
-    const float3 g = sh_backward(D, M, mean, make_float3(s_cam[0], s_cam[1], s_cam[2]), sh_in, clamped[idx], drgb,
-                                 sh_out);
+    const float3 g = sh_backward<VEC>(D, M, mean, make_float3(s_cam[0], s_cam[1], s_cam[2]), sh_in, clamped[idx], drgb,
+                                      sh_out);
     dmean.x += g.x; dmean.y += g.y; dmean.z += g.z;
     drgb_out = make_float3(drgb.x, drgb.y, drgb.z);
   } else {
@@ -400,7 +436,11 @@ gaussian_backward(int idx, int D, int M, const float* __restrict__ means3D, cons
 constexpr int PB_THREADS = 128;
 constexpr int PB_WARPS = PB_THREADS / 32;
 constexpr int SH_ROW = 48;        // 16 coefficients x RGB
-constexpr int SH_PITCH = 49;      // odd pitch: a lane walking its own row is conflict-free
+// pitch of a staged row: 52 floats for the contiguous [P,16,3] tensor (16-byte aligned rows, read and
+// written with 16-byte shared accesses), 49 (odd: conflict-free scalar accesses) for the split dc /
+// rest rows, whose pieces start at 12- and 180-byte offsets
+constexpr int SH_PITCH = 52;
+constexpr int SH_PITCH_SPLIT = 49;
 
 // SH_MODE as in the forward kernel: 0 = rows straight from global memory, 1 = staged float4 rows of
 // one contiguous [P,16,3] tensor, 2 = rows staged from / written back to the split features_dc /
@@ -452,7 +492,8 @@ preprocess_backward_kernel(RawModel raw, EgsModelGrads rg, int P, int D, int M, 
                            float* __restrict__ dL_dscales, float* __restrict__ dL_drot, bool colors_only,
                            const DrgbSlots slots) {
   __shared__ float view[16], proj[16], s_cam[3];
-  __shared__ float s_sh[SH_MODE != 0 ? PB_WARPS * 32 * SH_PITCH : 1];
+  __shared__ __align__(16) float s_sh[SH_MODE != 0 ? PB_WARPS * 32 * SH_PITCH : 4];
+  constexpr int PITCH = SH_MODE == 1 ? SH_PITCH : SH_PITCH_SPLIT;
   __shared__ float s_rot[RAW ? 18 : 1];
   __shared__ float s_dT[RAW ? PB_WARPS : 1][9];
   if (threadIdx.x < 16) {
@@ -483,18 +524,18 @@ preprocess_backward_kernel(RawModel raw, EgsModelGrads rg, int P, int D, int M, 
     float* tile = s_sh + warp * 32 * SH_PITCH;
     const int wrest = 3 * M - 3;
     if (rows > 0) {
-      if (SH_MODE == 1) {   // one contiguous run of rows * 48 floats
-        stage_rows_async(tile, SH_PITCH, 0, SH_ROW, shs + (size_t)first * SH_ROW, rows * SH_ROW, lane);
+      if (SH_MODE == 1) {   // one contiguous run of rows * 48 floats, 16 bytes at a time
+        stage_rows_async16(tile, PITCH, SH_ROW, shs + (size_t)first * SH_ROW, rows * SH_ROW, lane);
       } else {              // two contiguous runs: rows * 3 and rows * (3M - 3) floats
-        stage_rows_async(tile, SH_PITCH, 0, 3, raw.features_dc + (size_t)first * 3, rows * 3, lane);
+        stage_rows_async(tile, PITCH, 0, 3, raw.features_dc + (size_t)first * 3, rows * 3, lane);
         if (wrest > 0)
-          stage_rows_async(tile, SH_PITCH, 3, wrest, raw.features_rest + (size_t)first * wrest, rows * wrest, lane);
+          stage_rows_async(tile, PITCH, 3, wrest, raw.features_rest + (size_t)first * wrest, rows * wrest, lane);
       }
     }
     stage_rows_wait();
     if (idx < P) {
-      float* row = tile + lane * SH_PITCH;
-      gaussian_backward<RAW>(idx, D, M, means3D, radii, row, FACTORED ? nullptr : row, true, EGS_GB_TAIL);
+      float* row = tile + lane * PITCH;
+      gaussian_backward<RAW, SH_MODE == 1>(idx, D, M, means3D, radii, row, FACTORED ? nullptr : row, true, EGS_GB_TAIL);
     }
     __syncwarp();
     if (FACTORED && rows > 0) {
@@ -513,21 +554,20 @@ preprocess_backward_kernel(RawModel raw, EgsModelGrads rg, int P, int D, int M, 
         float4* dst = reinterpret_cast<float4*>(dL_dsh + (size_t)first * SH_ROW);
         for (int f = lane; f < rows * (SH_ROW / 4); f += 32) {
           const int row = f / (SH_ROW / 4), k = (f % (SH_ROW / 4)) * 4;
-          const float* srow = tile + row * SH_PITCH + k;
-          dst[f] = make_float4(srow[0], srow[1], srow[2], srow[3]);
+          dst[f] = *reinterpret_cast<const float4*>(tile + row * PITCH + k);
         }
       } else {
-        warp_rows_copy<false>(tile, SH_PITCH, 0, 3, rg.d_features_dc + (size_t)first * 3, rows * 3, lane);
+        warp_rows_copy<false>(tile, PITCH, 0, 3, rg.d_features_dc + (size_t)first * 3, rows * 3, lane);
         if (wrest > 0)
-          warp_rows_copy<false>(tile, SH_PITCH, 3, wrest, rg.d_features_rest + (size_t)first * wrest, rows * wrest,
+          warp_rows_copy<false>(tile, PITCH, 3, wrest, rg.d_features_rest + (size_t)first * wrest, rows * wrest,
                                 lane);
       }
     }
   } else if (idx < P) {
     const bool has_sh = shs != nullptr;
     const size_t off = (size_t)idx * M * 3;
-    gaussian_backward<RAW>(idx, D, M, means3D, radii, has_sh ? shs + off : nullptr,
-                           has_sh && !FACTORED ? dL_dsh + off : nullptr, has_sh, EGS_GB_TAIL);
+    gaussian_backward<RAW, false>(idx, D, M, means3D, radii, has_sh ? shs + off : nullptr,
+                                  has_sh && !FACTORED ? dL_dsh + off : nullptr, has_sh, EGS_GB_TAIL);
     if (FACTORED) {   // unstaged rows (sh_coeffs != 16): scalar stores to every destination
       const float v[3] = {drgb.x, drgb.y, drgb.z};
       for (int k = 0; k < 3; ++k) {
