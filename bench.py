@@ -121,27 +121,31 @@ def algorithmic_bytes(P, V, R, N, Tn, M, D, geom, passes):
     c = 12 * (D + 1) ** 2
     g = 28 if geom == "scale_rot" else 24
     cov_store = 24 if geom == "scale_rot" else 0
-    # binning: packed single-word sort (9-bit digits) when tile|depth|index fits 64 bits, else pairs
+    # binning (csrc/binning_buckets.cu). Presorted frames (>= 3M expected instances, or the full word does
+    # not fit): tile | index words of w bytes (4 when tile and index bits fit 32, else 8); duplicate writes
+    # them, one global partition pass reads and writes them, the per-bucket split reads them and writes
+    # the 4-byte index list and the tile ranges. Full-word frames: 8-byte tile | depth | index words and
+    # one CTA sort per bucket; five global passes or a pair sort when that does not fit.
     ib, tb = max(P - 1, 1).bit_length(), Tn.bit_length()
     packed = ib + 32 + tb <= 64
+    presorted = (R >= 3_000_000 or not packed) and P >= 64 and tb - 10 <= 7
     pk_passes = (32 + tb + 8) // 9
-    if packed and R <= 1024 * 12288 * 8 // 10:
-        # MSD-bucket path (binning_buckets.cu): duplicate + one global partition pass (stage
-        # "sort_histogram") + one CTA per bucket that reads 8 B and writes index + key (stage
-        # "sort_passes"); tile ranges come out of the bucket kernel
-        binning = {"duplicate_keys": 24 * P + 8 * R, "sort_histogram": 16 * R, "sort_passes": 8 * R + 12 * R + 8 * Tn}
+    if presorted:
+        w = 4 if tb + ib <= 32 else 8
+        binning = {"duplicate_keys": 24 * P + w * R, "sort_histogram": 2 * w * R, "sort_passes": w * R + 4 * R + 8 * Tn,
+                   # front-to-back presort of the Gaussians: build the (depth key | index) words, three
+                   # stable partition passes over them, the last one writing the bare indices
+                   "depth_order": (8 + 8) * P + 2 * 16 * P + 12 * P}
+    elif packed and R <= 1024 * 12288 * 8 // 10:
+        binning = {"duplicate_keys": 24 * P + 8 * R, "sort_histogram": 16 * R, "sort_passes": 8 * R + 4 * R + 8 * Tn}
     else:
         binning = {"duplicate_keys": 20 * P + (8 if packed else 12) * R, "sort_histogram": 8 * R,
                    "sort_passes": (R * 16 * (pk_passes - 1) + R * 20) if packed else R * 24 * passes,
                    "tile_ranges": 8 * R + 16 * Tn}
-    if packed and P >= 4096:
-        # front-to-back presort of the Gaussians: build the (depth key | index) words, three stable
-        # partition passes over them, the last one writing the bare indices
-        binning["depth_order"] = (8 + 8) * P + 2 * 16 * P + 12 * P
     return {
         **binning,
         "preprocess_fwd": 20 * P + V * (g + 4 + c + 4 + 8 + 16 + 12 + 3 + cov_store),
-        "scan": (12 if packed and P >= 4096 else 8) * P,
+        "scan": (12 if presorted else 8) * P,
         "blend_fwd": 44 * R + 24 * N + 8 * Tn,
         "bwd_zero": 48 * P,
         "blend_bwd": 44 * R + 28 * N + 8 * Tn + 40 * R,
@@ -547,17 +551,23 @@ def run_ours(a, rank, world, local_rank):
                            "backward runs differ by atomic order (~1e-6)", "gave_up": failed}
 
     clocks = ClockSampler(local_rank) if rank == 0 else None
-    cabi.profile_enable(True)
-    for _ in range(a.warmup):       # warm the profiler's event pool too, then drop those records
+    for _ in range(a.warmup):
         step()
     torch.cuda.synchronize()
-    cabi.profile_read()
     l0 = cabi.launch_count()
     sec = timed_region(step, a.steps, 0, dist_on, device)
     launches = cabi.launch_count() - l0
+    clk = clocks.stop() if clocks else None
+    # Per-stage durations: the library's stage timers bracket every stage with a CUDA-event pair on the
+    # launching stream; 18 pairs per step cost 0.05 ms (5 %) of device time, so the headline region above
+    # runs without them and the same K steps are run once more with them for the table and the roofline.
+    cabi.profile_enable(True)
+    step()
+    torch.cuda.synchronize()
+    cabi.profile_read()
+    sec_prof = timed_region(step, a.steps, 0, dist_on, device)
     prof = cabi.profile_read()
     cabi.profile_enable(False)
-    clk = clocks.stop() if clocks else None
     value = world * a.steps / sec
     xcheck = exchange_check() if dist_on else None
 
@@ -579,20 +589,45 @@ def run_ours(a, rank, world, local_rank):
                          "alg_MB": round(alg[name] / 1e6, 2), "GBps": round(alg[name] / per / 1e6, 1),
                          "frac_hbm": round(alg[name] / per / 1e6 / peak, 4)}
     top = max(kernels, key=lambda k: kernels[k]["ms_per_step"])
-    traffic = issue_pct = None   # per launch, from a committed ncu --set full capture (tools/ncu_traffic.py)
+    # per launch, from the committed ncu --set full capture of this command's kernels (tools/ncu_traffic.py ->
+    # profiles/traffic.json): DRAM bytes, executed warp instructions, issue-slot and shared-memory utilisation
+    ncu = {}
     try:
         tj = json.loads((ROOT / "profiles" / "traffic.json").read_text())["stages"].get(top, {})
-        if tj:
-            traffic = sum(v["bytes_per_launch"] for v in tj.values()) / len(tj)
-            issue_pct = sum(v.get("issue_active_pct", 0.0) for v in tj.values()) / len(tj) or None
+        for v in tj.values():
+            ncu = v
     except Exception:
-        traffic = None
-    roofline = {"kernel": top, "bound": "hbm", "achieved": kernels[top]["GBps"], "peak": peak, "unit": "GB/s",
-                "frac": kernels[top]["frac_hbm"], "traffic": traffic, "peak_source": peak_src,
-                "ms_per_launch": kernels[top]["ms_per_step"] / max(kernels[top]["launches_per_step"], 1),
-                "issue_active_pct": issue_pct,   # ncu smsp__issue_active of the same kernel: its real limiter
-                "note": "the tile-blend kernels are bound by instruction issue (FP32 / MUFU / shuffles), not by "
-                        "HBM: their inputs are L2-resident (traffic << algorithmic bytes); see DESIGN.md"}
+        ncu = {}
+    sm_count = torch.cuda.get_device_properties(device).multi_processor_count
+    sm_mhz = (clk or {}).get("sm_mhz") or (clk or {}).get("sm_max_mhz") or 1965.0
+    ms_launch = kernels[top]["ms_per_step"] / max(kernels[top]["launches_per_step"], 1)
+    hbm = {"achieved": kernels[top]["GBps"], "peak": peak, "unit": "GB/s", "frac": kernels[top]["frac_hbm"],
+           "peak_source": peak_src, "alg_MB": kernels[top]["alg_MB"]}
+    inst = ncu.get("warp_instructions_per_launch")
+    if top in ("blend_fwd", "blend_bwd") and inst:
+        # The tile blends read L2-resident lists (DRAM traffic is a twentieth of the algorithmic bytes), so
+        # HBM is not what bounds them: they are bound by instruction issue. Ceiling: 4 schedulers per SM,
+        # one warp instruction per cycle each, at the SM clock sampled during the timed region.
+        issue_peak = sm_count * 4 * sm_mhz * 1e6 / 1e9                       # G warp-instructions / s
+        issue_ach = inst / (ms_launch * 1e-3) / 1e9
+        roofline = {"kernel": top, "bound": "issue", "achieved": round(issue_ach, 1), "peak": round(issue_peak, 1),
+                    "unit": "Gwarp-inst/s", "frac": round(issue_ach / issue_peak, 4), "traffic": ncu.get("bytes_per_launch"),
+                    "ms_per_launch": ms_launch, "warp_instructions_per_launch": inst,
+                    "instructions_source": "smsp__inst_executed.sum of the committed ncu capture (profiles/traffic.json); "
+                                           "duration live from this run's stage events",
+                    "issue_active_pct_ncu": ncu.get("issue_active_pct"), "hbm": hbm,
+                    "shared_wavefronts_pct_of_peak_ncu": ncu.get("shared_wavefronts_pct"),
+                    "global_red_requests_per_launch_ncu": ncu.get("global_red_requests_per_launch")}
+    else:
+        roofline = {"kernel": top, "bound": "hbm", **hbm, "traffic": ncu.get("bytes_per_launch"), "ms_per_launch": ms_launch,
+                    "issue_active_pct_ncu": ncu.get("issue_active_pct")}
+    # fragment-rate ceilings of the two blends: FP32 lanes / ~13 FMA-class operations per
+    # fragment, and one MUFU ex2 per fragment on 16 lanes per SM, both at the sampled clock
+    frag_ceiling = {"fp32_Gfrag_per_s": round(sm_count * 128 * sm_mhz * 1e6 / 13 / 1e9, 1),
+                    "mufu_Gfrag_per_s": round(sm_count * 16 * sm_mhz * 1e6 / 1e9, 1), "sm_count": sm_count, "sm_mhz": sm_mhz,
+                    "note": "a fragment = one (pixel, list entry) visit up to the pixel's last contributor; most visits "
+                            "are rejected by the footprint bit lists without an instruction, so the rates can pass "
+                            "the per-fragment ceilings"}
 
     # ---- end-to-end through the public Python API with host inputs -------------------------
     e2e = None
@@ -773,6 +808,9 @@ def run_ours(a, rank, world, local_rank):
         "e2e": e2e, "gpu_launches": int(launches), "roofline": roofline, "kernels": kernels, "clocks": clk,
         "mfragments_per_s": {"fwd": frag / (kernels["blend_fwd"]["ms_per_step"] * 1e3),
                              "bwd": frag / (kernels["blend_bwd"]["ms_per_step"] * 1e3)},
+        "fragment_ceilings": frag_ceiling,
+        "kernels_measured_in": "a second pass of the same %d steps with the per-stage event pairs on (%.4f ms per "
+                               "step there; the headline region runs without them)" % (a.steps, sec_prof / a.steps * 1e3),
         "extra": extra,
     }
     if xcheck is not None:
@@ -881,7 +919,7 @@ def run_reference(a, rank, world, local_rank):
             "cpu_baseline": {"value": value, "unit": UNIT, "cores": 0, "kind": "reference",
                              "sample": "the reference has no CPU implementation: its own CUDA kernels on the same GPU"},
             "e2e": {"value": a.steps / sec2, "unit": UNIT, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": 4,
-                    "ms_per_step": sec2 / a.steps * 1e3},
+                    "ms_per_step": sec2 / a.steps * 1e3, "python_layer": getattr(rast, "python_layer", None)},
             "clocks": clk}
 
 

@@ -22,7 +22,7 @@ OBJ = ROOT / "build" / "obj"
 LIB = PKG / "libegs_rasterizer.so"
 BINDING = PKG / "diff_gaussian_rasterization" / "_C.so"
 
-CUDA_SOURCES = ["preprocess", "binning", "binning_packed", "binning_buckets", "blend_fwd", "blend_bwd", "preprocess_bwd", "optim", "model", "loss", "compact", "knn", "exchange", "ply", "abi"]
+CUDA_SOURCES = ["preprocess", "binning", "binning_packed", "binning_buckets", "blend_fwd", "blend_bwd", "preprocess_bwd", "optim", "model", "loss", "compact", "densify", "knn", "exchange", "ply", "abi"]
 NVCC_FLAGS = ["-std=c++17", "-O3", *(os.environ.get("EGS_EXTRA_NVCC", "").split()), "-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo",
               "-Xcompiler", "-fPIC"]
 

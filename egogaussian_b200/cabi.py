@@ -82,6 +82,17 @@ class EgsRowTensor(C.Structure):
     _fields_ = [("src", C.c_void_p), ("dst", C.c_void_p), ("row_bytes", C.c_int)]
 
 
+class EgsDensifySelect(C.Structure):
+    _fields_ = [("P", C.c_int), ("n_graded", C.c_int), ("grad_accum", C.c_void_p), ("denom", C.c_void_p),
+                ("scaling_raw", C.c_void_p), ("grad_threshold", C.c_float), ("size_threshold", C.c_float),
+                ("split", C.c_int), ("is_object", C.c_void_p), ("which_object", C.c_int),
+                ("generation", C.c_void_p), ("only_generation", C.c_int)]
+
+
+class EgsAppendTensor(C.Structure):
+    _fields_ = [("src", C.c_void_p), ("dst", C.c_void_p), ("row_bytes", C.c_int), ("fill", C.c_int), ("value", C.c_int)]
+
+
 class EgsLossArgs(C.Structure):
     _fields_ = [("channels", C.c_int), ("height", C.c_int), ("width", C.c_int),
                 ("image", c_float_p), ("target", c_float_p), ("grad_mask", C.c_void_p),
@@ -202,6 +213,12 @@ def load() -> C.CDLL:
     lib.egs_compact_plan.argtypes = [C.c_int, C.c_void_p, C.c_void_p, C.c_size_t, C.POINTER(C.c_int), C.c_void_p]
     lib.egs_compact_rows.restype = C.c_int
     lib.egs_compact_rows.argtypes = [C.c_int, C.c_void_p, C.POINTER(EgsRowTensor), C.c_int, C.c_void_p]
+    lib.egs_densify_select.restype = C.c_int
+    lib.egs_densify_select.argtypes = [C.POINTER(EgsDensifySelect), C.c_void_p, C.c_void_p]
+    lib.egs_append_rows.restype = C.c_int
+    lib.egs_append_rows.argtypes = [C.c_int, C.c_void_p, C.c_int, C.c_int, C.POINTER(EgsAppendTensor), C.c_int, C.c_void_p]
+    lib.egs_split_samples.restype = C.c_int
+    lib.egs_split_samples.argtypes = [C.c_int, C.c_void_p, C.c_int, C.c_int] + [C.c_void_p] * 7
     lib.egs_knn_mean_dist2.restype = C.c_int
     lib.egs_knn_mean_dist2.argtypes = [C.c_int, C.c_void_p, C.c_void_p, C.c_void_p, C.c_size_t, C.c_void_p]
     lib.egs_exchange_sum.restype = C.c_int
@@ -637,8 +654,9 @@ def compact_rows(keep, tensors, stream=None):
                                     _stream_handle(stream)), "egs_compact_plan")
         n = count.value
         outs = [torch.empty((n,) + tuple(t.shape[1:]), dtype=t.dtype, device=dev) for t in tensors]
-        for first in range(0, len(tensors), 32):
-            chunk = list(zip(tensors[first:first + 32], outs[first:first + 32]))
+        work = [(t, o) for t, o in zip(tensors, outs) if t.numel()]   # zero-width rows (f_rest at SH degree 0)
+        for first in range(0, len(work), 32):
+            chunk = work[first:first + 32]
             arr = (EgsRowTensor * len(chunk))()
             for k, (t, o) in enumerate(chunk):
                 assert t.is_contiguous() and t.shape[0] == P
@@ -648,6 +666,75 @@ def compact_rows(keep, tensors, stream=None):
                 _check(lib.egs_compact_rows(P, scratch.data_ptr(), arr, len(chunk), _stream_handle(stream)),
                        "egs_compact_rows")
     return outs
+
+
+def densify_select(*, grad_accum, denom, scaling_raw, grad_threshold, size_threshold, split, is_object=None,
+                   which_object=None, generation=None, only_generation=None, stream=None):
+    """egs_densify_select: uint8 [P] mask of the rows densify_and_clone (split=False) / densify_and_split
+    (split=True) would pick. grad_accum / denom may be shorter than scaling_raw (rows appended since)."""
+    import torch
+    P = int(scaling_raw.shape[0])
+    a = EgsDensifySelect()
+    a.P, a.n_graded = P, int(grad_accum.shape[0])
+    a.grad_accum, a.denom, a.scaling_raw = _ptr(grad_accum), _ptr(denom), _ptr(scaling_raw)
+    a.grad_threshold, a.size_threshold, a.split = float(grad_threshold), float(size_threshold), int(bool(split))
+    a.is_object = _ptr(is_object) if which_object is not None else None
+    a.which_object = int(which_object) if which_object is not None else 0
+    a.generation = _ptr(generation) if only_generation is not None else None
+    a.only_generation = int(only_generation) if only_generation is not None else 0
+    out = torch.empty((P,), dtype=torch.uint8, device=scaling_raw.device)
+    if P:
+        with torch.cuda.device(out.device):
+            _check(load().egs_densify_select(C.byref(a), out.data_ptr(), _stream_handle(stream)), "egs_densify_select")
+    return out
+
+
+def append_selected_rows(selected, tensors, fills, copies=1, stream=None):
+    """egs_compact_plan + egs_append_rows: for every tensor t (first dimension P = len(selected)),
+    torch.cat((t, t[selected].repeat(copies, ...))) -- or zeros / a constant in the new rows: `fills[i]` is
+    "copy", "zero" or an int (4-byte rows only). Returns (outputs, count, plan) with `plan` reusable by
+    split_samples."""
+    import torch
+    lib = load()
+    P = int(selected.shape[0])
+    dev = selected.device
+    sel = selected.to(torch.uint8).contiguous() if selected.dtype != torch.uint8 else selected.contiguous()
+    nbytes = lib.egs_compact_scratch_bytes(P)
+    plan = torch.empty((nbytes,), dtype=torch.uint8, device=dev)
+    count = C.c_int()
+    outs = []
+    with torch.cuda.device(dev):
+        _check(lib.egs_compact_plan(P, _ptr(sel), plan.data_ptr(), nbytes, C.byref(count), _stream_handle(stream)),
+               "egs_compact_plan")
+        n = count.value
+        outs = [torch.empty((P + copies * n,) + tuple(t.shape[1:]), dtype=t.dtype, device=dev) for t in tensors]
+        work = [(t, o, f) for t, o, f in zip(tensors, outs, fills) if o.numel()]   # zero-width rows (f_rest at SH degree 0)
+        for first in range(0, len(work), 32):
+            chunk = work[first:first + 32]
+            arr = (EgsAppendTensor * len(chunk))()
+            for k, (t, o, f) in enumerate(chunk):
+                assert t.is_contiguous() and t.shape[0] == P
+                arr[k].src, arr[k].dst = _ptr(t), o.data_ptr() if o.numel() else None
+                arr[k].row_bytes = t.element_size() * (o.numel() // max(o.shape[0], 1))
+                arr[k].fill = 0 if f == "copy" else 1 if f == "zero" else 2
+                arr[k].value = int(f) if arr[k].fill == 2 else 0
+            if P + copies * n:
+                _check(lib.egs_append_rows(P, plan.data_ptr(), n, copies, arr, len(chunk), _stream_handle(stream)),
+                       "egs_append_rows")
+    return outs, n, plan
+
+
+def split_samples(P, plan, count, copies, xyz, scaling_raw, rotation_raw, noise, xyz_new, scaling_new, stream=None):
+    """egs_split_samples: positions and log-scales of the rows a split adds, written into xyz_new /
+    scaling_new ([copies * count, 3] views, e.g. the tails of the appended tensors)."""
+    import torch
+    if count == 0:
+        return
+    assert xyz_new.is_contiguous() and scaling_new.is_contiguous() and noise.is_contiguous()
+    with torch.cuda.device(xyz.device):
+        _check(load().egs_split_samples(P, plan.data_ptr(), count, copies, _ptr(xyz), _ptr(scaling_raw), _ptr(rotation_raw),
+                                        _ptr(noise), xyz_new.data_ptr(), scaling_new.data_ptr(), _stream_handle(stream)),
+               "egs_split_samples")
 
 
 def knn_mean_dist2(points, stream=None, exhaustive=False):

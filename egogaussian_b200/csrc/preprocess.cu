@@ -176,14 +176,15 @@ preprocess_forward_kernel(RawModel raw, int P, int D, int M, const float* __rest
     const int first = blockIdx.x * blockDim.x + warp * 32;
     const int rows = min(32, P - first);
     float* tile = s_sh + warp * 32 * PF_SH_PITCH;
+    const int pitch = M == 16 ? PF_SH_PITCH : PF_SH_PITCH_SPLIT;   // 16 coefficients: aligned rows, vector reads
     if (rows > 0) {
       const int wrest = 3 * M - 3;
-      stage_rows_async(tile, PF_SH_PITCH_SPLIT, 0, 3, raw.features_dc + (size_t)first * 3, rows * 3, lane);
+      stage_rows_async(tile, pitch, 0, 3, raw.features_dc + (size_t)first * 3, rows * 3, lane);
       if (wrest > 0)
-        stage_rows_async(tile, PF_SH_PITCH_SPLIT, 3, wrest, raw.features_rest + (size_t)first * wrest, rows * wrest, lane);
+        stage_rows_async(tile, pitch, 3, wrest, raw.features_rest + (size_t)first * wrest, rows * wrest, lane);
     }
     stage_rows_wait();
-    sh_row = tile + lane * PF_SH_PITCH_SPLIT;
+    sh_row = tile + lane * pitch;
   } else if (SH_MODE == 1) {
     const unsigned lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const int first = blockIdx.x * blockDim.x + warp * 32;
@@ -243,7 +244,7 @@ preprocess_forward_kernel(RawModel raw, int P, int D, int M, const float* __rest
         float3 rgb;
         unsigned char cb = 0;
         if (colors_precomp == nullptr) {
-          if (SH_MODE == 1) {
+          if (SH_MODE == 1 || (SH_MODE == 2 && M == 16)) {
             // the staged row is 16-byte aligned: twelve 16-byte shared loads instead of 48 scalar ones
             // (the kernel waited on the load/store queue, ncu mio_throttle); the values then sit in
             // registers and the evaluation keeps the reference's expression shapes

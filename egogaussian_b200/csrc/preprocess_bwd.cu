@@ -476,7 +476,7 @@ __device__ __forceinline__ void store_slot_f4(const DrgbSlots& d, size_t at, flo
 // FACTORED: dL/dsh is not written (neither the rows in shared memory nor the 12 M bytes per Gaussian in
 // HBM); the clamp-masked dL/dRGB rows and the camera centre go to the slots instead.
 template <int SH_MODE, bool RAW, bool FACTORED>
-__global__ void __launch_bounds__(PB_THREADS, 6)
+__global__ void __launch_bounds__(PB_THREADS, RAW ? 5 : 6)   // raw mode carries the activation chain: 102 registers
 preprocess_backward_kernel(RawModel raw, EgsModelGrads rg, int P, int D, int M, const float* __restrict__ means3D,
                            const int* __restrict__ radii, const float* __restrict__ shs,
                            const unsigned char* __restrict__ clamped,
@@ -493,7 +493,10 @@ preprocess_backward_kernel(RawModel raw, EgsModelGrads rg, int P, int D, int M, 
                            const DrgbSlots slots) {
   __shared__ float view[16], proj[16], s_cam[3];
   __shared__ __align__(16) float s_sh[SH_MODE != 0 ? PB_WARPS * 32 * SH_PITCH : 4];
-  constexpr int PITCH = SH_MODE == 1 ? SH_PITCH : SH_PITCH_SPLIT;
+  // 16 coefficients: 16-byte aligned rows and vector accesses (also for the split dc | rest rows, which
+  // sit side by side in one row); fewer: the odd pitch and scalar accesses
+  const bool vec = SH_MODE == 1 || M == 16;
+  const int PITCH = vec ? SH_PITCH : SH_PITCH_SPLIT;
   __shared__ float s_rot[RAW ? 18 : 1];
   __shared__ float s_dT[RAW ? PB_WARPS : 1][9];
   if (threadIdx.x < 16) {
@@ -535,7 +538,8 @@ preprocess_backward_kernel(RawModel raw, EgsModelGrads rg, int P, int D, int M, 
     stage_rows_wait();
     if (idx < P) {
       float* row = tile + lane * PITCH;
-      gaussian_backward<RAW, SH_MODE == 1>(idx, D, M, means3D, radii, row, FACTORED ? nullptr : row, true, EGS_GB_TAIL);
+      if (vec) gaussian_backward<RAW, true>(idx, D, M, means3D, radii, row, FACTORED ? nullptr : row, true, EGS_GB_TAIL);
+      else gaussian_backward<RAW, false>(idx, D, M, means3D, radii, row, FACTORED ? nullptr : row, true, EGS_GB_TAIL);
     }
     __syncwarp();
     if (FACTORED && rows > 0) {

@@ -24,6 +24,9 @@
  *   egs_knn_mean_dist2 <- distCUDA2                                submodules/simple-knn/spatial.cu:15-27
  *   egs_compact_plan / egs_compact_rows
  *                      <- prune_points / _prune_optimizer          scene/gaussian_model.py:506-557
+ *   egs_densify_select / egs_append_rows / egs_split_samples
+ *                      <- densify_and_clone / densify_and_split / cat_tensors_to_optimizer
+ *                                                                  scene/gaussian_model.py:243-272,559-677
  *
  * Conventions
  *   - plain C, no torch types, no exceptions; every pointer named `d_*` or documented as
@@ -467,6 +470,54 @@ typedef struct EgsRowTensor {
 size_t egs_compact_scratch_bytes(int P);
 int egs_compact_plan(int P, const unsigned char* keep, void* scratch, size_t scratch_bytes, int* count, void* stream);
 int egs_compact_rows(int P, const void* scratch, const EgsRowTensor* tensors, int n_tensors, void* stream);
+
+/* The growing half of densification (same SURVEY.md row): GaussianModel.densify_and_clone /
+ * densify_and_split with densification_postfix / cat_tensors_to_optimizer, scene/gaussian_model.py:243-272,
+ * 559-677. Three steps around egs_compact_plan:
+ *
+ * egs_densify_select marks the rows to clone or split: grads = xyz_gradient_accum / denom with NaN -> 0
+ * (:689-690; rows from n_graded on count as 0, the zero padding of :604-605), selected = grads >=
+ * grad_threshold and max(exp(scaling_raw)) <= size_threshold (clone, :650-651) or > size_threshold
+ * (split, :607-608), size_threshold = percent_dense * scene_extent; optionally only rows of one object
+ * (:614-616, :653-655) and of one generation (:609-611). */
+typedef struct EgsDensifySelect {
+  int P;
+  int n_graded;                  /* rows that have a gradient statistic (P before any append) */
+  const float* grad_accum;       /* device [n_graded]  xyz_gradient_accum */
+  const float* denom;            /* device [n_graded] */
+  const float* scaling_raw;      /* device [P,3]  _scaling (log scale) */
+  float grad_threshold, size_threshold;
+  int split;                     /* 0: the clone side of the size test, 1: the split side */
+  const int* is_object;          /* device [P] or NULL (which_object=None) */
+  int which_object;
+  const int* generation;         /* device [P] or NULL (split_prev_gen=True) */
+  int only_generation;
+} EgsDensifySelect;
+int egs_densify_select(const EgsDensifySelect* args, unsigned char* selected /* device [P] */, void* stream);
+
+/* After egs_compact_plan(P, selected, scratch, ..., &count): for every tensor at once,
+ *   dst [P + copies * count, row] = cat(src, src[selected].repeat(copies, 1))          fill 0
+ *                                   cat(src, zeros)     (Adam moments, :257-258)        fill 1
+ *                                   cat(src, `value`)   (the generation stamp, :630)    fill 2
+ * row_bytes a multiple of 4; src and dst must not overlap. */
+typedef struct EgsAppendTensor {
+  const void* src;   /* device [P, row_bytes] */
+  void* dst;         /* device [P + copies * count, row_bytes] */
+  int row_bytes;
+  int fill;
+  int value;         /* fill 2: the 4-byte pattern of the new rows */
+} EgsAppendTensor;
+int egs_append_rows(int P, const void* plan_scratch, int count, int copies, const EgsAppendTensor* tensors, int n_tensors,
+                    void* stream);
+
+/* Positions and scales of the rows a split adds (:619-622): for new row j (copy j / count of selected
+ * row k = j % count), with s = exp(scaling_raw[k]) and R = build_rotation(rotation_raw[k]) (normalised),
+ *   xyz_new[j] = R (noise[j] * s) + xyz[k],     scaling_new[j] = log(s / (0.8 * copies)).
+ * `noise` is device [copies * count, 3] standard normal: torch.normal(0, s) of :619 is s * noise, so the
+ * caller owns the random stream. xyz_new / scaling_new: device [copies * count, 3], e.g. the tail of the
+ * tensors egs_append_rows produced. */
+int egs_split_samples(int P, const void* plan_scratch, int count, int copies, const float* xyz, const float* scaling_raw,
+                      const float* rotation_raw, const float* noise, float* xyz_new, float* scaling_new, void* stream);
 
 /* Mean squared distance of every point to its three nearest neighbours, the point itself excluded
  * (distCUDA2 of submodules/simple-knn, used once at initialisation to set the

@@ -38,8 +38,26 @@ def knn_available() -> bool:
     return (OUT / f"{KNN_MODULE}.so").exists()
 
 
+# The reference's own Python layer (autograd Function, settings tuple, nn.Module) rides along as a build
+# artefact next to the .so, byte for byte: the `--impl reference` bench arm drives the compiled reference
+# through it (with ref_dgr_C standing in for its `_C`), not through a restatement.
+PY_LAYER = OUT / "dgr_py" / "diff_gaussian_rasterization" / "__init__.py"
+
+
+def stage_python_layer(force: bool = False) -> Path | None:
+    src = REF / "diff_gaussian_rasterization" / "__init__.py"
+    if PY_LAYER.exists() and not force:
+        return PY_LAYER
+    if not src.exists():
+        return None
+    PY_LAYER.parent.mkdir(parents=True, exist_ok=True)
+    PY_LAYER.write_bytes(src.read_bytes())
+    return PY_LAYER
+
+
 def build(force: bool = False) -> Path | None:
     build_knn(force)
+    stage_python_layer(force)
     return _build(MODULE, REF, SOURCES, [str(REF / "third_party/glm"), str(REF)], force)
 
 

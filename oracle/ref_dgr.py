@@ -125,13 +125,50 @@ def decode_buffers(fwd: Dict) -> Dict:
     return out
 
 
+def load_python_layer():
+    """The reference's OWN diff_gaussian_rasterization/__init__.py (staged unmodified into oracle/_ref by
+    build_ref.py), imported with the compiled reference standing in for its `_C`. None when the file did
+    not travel."""
+    py = HERE / "_ref" / "dgr_py" / "diff_gaussian_rasterization" / "__init__.py"
+    if not py.exists():
+        return None
+    name = "ref_dgr_py.diff_gaussian_rasterization"
+    if name in sys.modules:
+        return sys.modules[name]
+    import types
+    C = load()
+    parent = types.ModuleType("ref_dgr_py")
+    parent.__path__ = [str(py.parent.parent)]
+    sys.modules["ref_dgr_py"] = parent
+    spec = importlib.util.spec_from_file_location(name, str(py), submodule_search_locations=[str(py.parent)])
+    mod = importlib.util.module_from_spec(spec)
+    sys.modules[name] = mod
+    sys.modules[name + "._C"] = C          # `from . import _C` inside the reference file resolves to the build
+    spec.loader.exec_module(mod)
+    return mod
+
+
 def make_autograd_rasterizer():
-    """An autograd Function + callable that drives the reference's compiled functions the way its
-    own Python layer does (DGR/diff_gaussian_rasterization/__init__.py:44-158): used only by the
-    `--impl reference` bench arm so that its end-to-end number goes through the same kind of
-    public call (module(...) -> (color, radii, depth, alpha), loss.backward()) as ours."""
+    """The `--impl reference` bench arm's public call: rasterize(rs, ...) -> (color, radii, depth, alpha),
+    differentiable. Goes through the reference's own Python layer (GaussianRasterizationSettings,
+    GaussianRasterizer, _RasterizeGaussians of DGR/diff_gaussian_rasterization/__init__.py) whenever
+    that file travelled with the snapshot; otherwise through the restatement below, which passes the
+    arguments in the same order (DGR/diff_gaussian_rasterization/__init__.py:44-158)."""
     import torch
     C = load()
+    ref_py = load_python_layer()
+    if ref_py is not None:
+        def rasterize_stock(rs, *, means3D, means2D, opacities, shs=None, colors_precomp=None, scales=None,
+                            rotations=None, cov3D_precomp=None):
+            settings = ref_py.GaussianRasterizationSettings(
+                image_height=rs["image_height"], image_width=rs["image_width"], tanfovx=rs["tanfovx"], tanfovy=rs["tanfovy"],
+                bg=rs["bg"], scale_modifier=rs["scale_modifier"], viewmatrix=rs["viewmatrix"], projmatrix=rs["projmatrix"],
+                sh_degree=rs["sh_degree"], campos=rs["campos"], prefiltered=False, debug=False)
+            return ref_py.GaussianRasterizer(raster_settings=settings)(
+                means3D=means3D, means2D=means2D, opacities=opacities, shs=shs, colors_precomp=colors_precomp,
+                scales=scales, rotations=rotations, cov3D_precomp=cov3D_precomp)
+        rasterize_stock.python_layer = "reference's own diff_gaussian_rasterization/__init__.py"
+        return rasterize_stock
 
     class _Ref(torch.autograd.Function):
         @staticmethod
@@ -162,4 +199,5 @@ def make_autograd_rasterizer():
                           opacities, e if scales is None else scales, e if rotations is None else rotations,
                           e if cov3D_precomp is None else cov3D_precomp, rs)
 
+    rasterize.python_layer = "restatement in oracle/ref_dgr.py (the reference's file did not travel)"
     return rasterize
