@@ -195,11 +195,13 @@ __device__ __forceinline__ int segment_of(const ExLaunch& L, long long c) {
 // Data phase over peer loads / stores. WMAX: the smallest of 2, 4, 8 that holds `world`; a thread keeps 8
 // peer loads of 16 bytes in flight (8 / WMAX chunks from every rank), which is what it takes to fill an
 // NVLink with 1024 threads per SM.
+// `tid` / `threads`: index and number of the CTA's threads that take part (all of them, or the few warps
+// the factored exchange sets aside for this phase)
 template <bool ADAM, int WMAX>
-__device__ __forceinline__ void sum_slice_peer(const ExLaunch& L) {
+__device__ __forceinline__ void sum_slice_peer(const ExLaunch& L, int tid = (int)threadIdx.x, const int EX_THREADS = egs::EX_THREADS) {
   constexpr int U = 8 / WMAX;
   const long long stride = (long long)gridDim.x * EX_THREADS * U;
-  for (long long c0 = L.lo4 + (long long)blockIdx.x * EX_THREADS * U + threadIdx.x; c0 < L.hi4; c0 += stride) {
+  for (long long c0 = L.lo4 + (long long)blockIdx.x * EX_THREADS * U + tid; c0 < L.hi4; c0 += stride) {
     float4 part[U][WMAX];
 #pragma unroll
     for (int u = 0; u < U; ++u)
@@ -232,9 +234,9 @@ __device__ __forceinline__ void sum_slice_peer(const ExLaunch& L) {
 // The same through the switch: (world - 1) / world of the buffer crosses each link once per direction
 // instead of twice. Four reductions of 16 bytes in flight per thread.
 template <bool ADAM, int U>
-__device__ __forceinline__ void sum_slice_mc(const ExLaunch& L) {
+__device__ __forceinline__ void sum_slice_mc(const ExLaunch& L, int tid = (int)threadIdx.x, const int EX_THREADS = egs::EX_THREADS) {
   const long long stride = (long long)gridDim.x * EX_THREADS * U;
-  for (long long c0 = L.lo4 + (long long)blockIdx.x * EX_THREADS * U + threadIdx.x; c0 < L.hi4; c0 += stride) {
+  for (long long c0 = L.lo4 + (long long)blockIdx.x * EX_THREADS * U + tid; c0 < L.hi4; c0 += stride) {
     float4 g[U];
 #pragma unroll
     for (int u = 0; u < U; ++u)
@@ -312,14 +314,8 @@ __device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commi
 template <int N>
 __device__ __forceinline__ void cp_async_wait() { asm volatile("cp.async.wait_group %0;" ::"n"(N) : "memory"); }
 
-// A warp takes 32 Gaussians at a time: their triples of every view (96 floats = 24 x 16 bytes per view)
-// arrive in a double-buffered stage by cp.async, one group ahead of the arithmetic; a lane accumulates
-// its Gaussian's 48 sums over the views in registers, the rows go through a tile and leave as 16-byte
-// stores.
-__device__ __forceinline__ void expand_sh_sum(const ExLaunch& L, const ShFactorLaunch& F, float* smem) {
-  const unsigned lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-  float* tile = smem + warp * SF_WARP_FLOATS;
-  float* stage = tile + 32 * SF_PITCH;                         // [2][views][96]
+// Camera centres of all views into shared memory (every thread of the CTA calls this).
+__device__ __forceinline__ void load_view_cameras(const ShFactorLaunch& F, float* smem) {
   float* s_cam = smem + SF_WARPS * SF_WARP_FLOATS;             // [views][4]
   if (threadIdx.x < (unsigned)F.n * 3) {
     // the slots were written (by this rank's and the peers' backward kernels) before their ranks' flags:
@@ -328,23 +324,42 @@ __device__ __forceinline__ void expand_sh_sum(const ExLaunch& L, const ShFactorL
     s_cam[4 * q + c] = ld_peer_f32(F.drgb[q] + ((size_t)F.P * 3 + 3) / 4 * 4 + c);
   }
   __syncthreads();
+}
+
+// A warp takes 32 Gaussians at a time: their triples of every view (96 floats = 24 x 16 bytes per view)
+// arrive in a double-buffered stage by cp.async, one group ahead of the arithmetic; a lane accumulates
+// its Gaussian's 48 sums over the views in registers, the rows go through a tile and leave as 16-byte
+// stores. The CTA owns a contiguous range of groups and its warps draw from it through a shared counter,
+// so the warps that first ran the slice sum join in when they are done.
+__device__ __forceinline__ void expand_sh_sum(const ExLaunch& L, const ShFactorLaunch& F, float* smem, uint32_t* s_next) {
+  const unsigned lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  float* tile = smem + warp * SF_WARP_FLOATS;
+  float* stage = tile + 32 * SF_PITCH;                         // [2][views][96]
+  const float* s_cam = smem + SF_WARPS * SF_WARP_FLOATS;       // [views][4]
   const int groups = (F.P + 31) / 32;
+  const int per_cta = (groups + (int)gridDim.x - 1) / (int)gridDim.x;
+  const int g_lo = (int)blockIdx.x * per_cta, g_hi = min(groups, g_lo + per_cta);
   const int row_floats = 3 * F.M;
-  const int step = gridDim.x * SF_WARPS;
+  auto draw = [&]() -> int {   // the next group of this CTA, the same value on every lane
+    uint32_t v = 0;
+    if (lane == 0) v = atomicAdd(s_next, 1u);
+    return g_lo + (int)__shfl_sync(0xffffffffu, v, 0);
+  };
   auto fetch = [&](int grp, int buf) {
     const size_t at = (size_t)grp * 96 + lane * 4;
-    if (grp < groups && lane < 24 && at < (size_t)F.P * 3) {   // the last 16 bytes may run into the slot's padding
+    if (grp < g_hi && lane < 24 && at < (size_t)F.P * 3) {   // the last 16 bytes may run into the slot's padding
 #pragma unroll
       for (int q = 0; q < EGS_MAX_PEERS; ++q)
         if (q < F.n) cp_async_16(stage + buf * SF_STAGE + q * 96 + lane * 4, F.drgb[q] + at);
     }
     cp_async_commit();
   };
-  int grp = blockIdx.x * SF_WARPS + warp;
+  int grp = draw();
   fetch(grp, 0);
-  for (int it = 0; grp < groups; grp += step, ++it) {
+  for (int it = 0; grp < g_hi; ++it) {
     const int buf = it & 1;
-    fetch(grp + step, buf ^ 1);
+    const int next = draw();
+    fetch(next, buf ^ 1);
     const int first = grp * 32;
     const int rows = min(32, F.P - first);
     const int idx = first + (int)lane;
@@ -396,9 +411,18 @@ __device__ __forceinline__ void expand_sh_sum(const ExLaunch& L, const ShFactorL
       for (int e = lane; e < rows * row_floats; e += 32) dst[e] = tile[(e / row_floats) * SF_PITCH + e % row_floats];
     }
     __syncwarp();   // the tile and this stage buffer are free for the group after next
+    grp = next;
   }
   cp_async_wait<0>();
 }
+
+// Warps of a CTA that run the slice sum of the small gradients (NVLink-bound: a few warps with many
+// requests in flight each) while the others already expand the SH sums (local, arithmetic and latency);
+// they join the expansion when their part of the slice is done.
+// Through the switch the sum is bound by the switch's reduction rate whatever the number of warps (0.2 ms
+// for 56 MB at 8 ranks with 4 or with 16 warps); peer loads want more requests in flight.
+constexpr int SF_SUM_WARPS_MC = 4;
+constexpr int SF_SUM_WARPS_PEER = 8;
 
 template <bool MC, int WMAX>
 __global__ void __launch_bounds__(EX_THREADS, 1)
@@ -406,12 +430,16 @@ exchange_factored_kernel(const __grid_constant__ ExLaunch L, const __grid_consta
   extern __shared__ __align__(16) float sf_smem[];
   __shared__ bool s_last;
   __shared__ int s_timed_out;
+  __shared__ uint32_t s_next;
+  if (threadIdx.x == 0) s_next = 0u;
   if (barrier_in(L, s_timed_out)) {
-    if (F.phases != 2) {
-      if (MC) sum_slice_mc<false, 8>(L);   // one CTA per SM here: twice the reductions in flight per thread
-      else sum_slice_peer<false, WMAX>(L);
+    load_view_cameras(F, sf_smem);
+    constexpr int SUM_THREADS = (MC ? SF_SUM_WARPS_MC : SF_SUM_WARPS_PEER) * 32;
+    if (F.phases != 2 && threadIdx.x < SUM_THREADS) {
+      if (MC) sum_slice_mc<false, 16>(L, (int)threadIdx.x, SUM_THREADS);
+      else sum_slice_peer<false, WMAX>(L, (int)threadIdx.x, SUM_THREADS);
     }
-    if (F.phases != 1) expand_sh_sum(L, F, sf_smem);
+    if (F.phases != 1) expand_sh_sum(L, F, sf_smem, &s_next);
   }
   barrier_out(L, s_last, s_timed_out);
 }
