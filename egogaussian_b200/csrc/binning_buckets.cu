@@ -207,26 +207,6 @@ duplicate_big_kernel(const float2* __restrict__ means2D, const float* __restrict
   }
 }
 
-// exclusive scan of the bucket histogram; start[MSD_BINS] = total
-__global__ void __launch_bounds__(MSD_BINS)
-bucket_scan_kernel(const uint32_t* __restrict__ hist, uint32_t* __restrict__ start) {
-  __shared__ uint32_t s_w[MSD_BINS / 32];
-  const uint32_t v = hist[threadIdx.x];
-  const unsigned lane = lane_id(), warp = threadIdx.x >> 5;
-  uint32_t incl = v;
-#pragma unroll
-  for (int d = 1; d < 32; d <<= 1) {
-    const uint32_t t = __shfl_up_sync(0xffffffffu, incl, d);
-    if (lane >= d) incl += t;
-  }
-  if (lane == 31) s_w[warp] = incl;
-  __syncthreads();
-  uint32_t woff = 0;
-  for (unsigned w = 0; w < warp; ++w) woff += s_w[w];
-  start[threadIdx.x] = woff + incl - v;
-  if (threadIdx.x == MSD_BINS - 1) start[MSD_BINS] = woff + incl;
-}
-
 // ---------------------------------------------------------------------------------------------
 // global stable partition by bucket (one onesweep pass, 10-bit digit)
 // ---------------------------------------------------------------------------------------------
@@ -241,6 +221,7 @@ struct MsdSmem {
   uint16_t digit_local[MSD_BINS];            // first slot of each digit in exch (< TILE)
   uint32_t digit_global[MSD_BINS];
   uint32_t warp_sums[MSD_WARPS];
+  uint32_t hist_sums[MSD_WARPS];
   uint32_t tile;
 };
 
@@ -268,17 +249,36 @@ __device__ __forceinline__ void st_relaxed_v4(uint32_t* p, uint4 v) {
 template <typename WORD, bool EMIT_IDX>
 __global__ void __launch_bounds__(MSD_THREADS, 3)
 msd_partition_kernel(const WORD* __restrict__ in, WORD* __restrict__ out, InstanceCount count,
-                     int shift, uint32_t mask, const uint32_t* __restrict__ bucket_start,
+                     int shift, uint32_t mask, const uint32_t* __restrict__ digit_hist /* [MSD_BINS] counts of the whole input */,
+                     uint32_t* __restrict__ start_out /* NULL, or [MSD_BINS + 1]: their exclusive scan, for later kernels */,
                      uint32_t* __restrict__ ticket, uint32_t* __restrict__ status_raw,
                      uint32_t* __restrict__ out_idx, uint32_t idx_mask) {
   constexpr int ITEMS = MsdCfg<WORD>::ITEMS;
   constexpr int TILE = MsdCfg<WORD>::TILE;
   extern __shared__ __align__(16) unsigned char smem_raw[];
   MsdSmem<WORD>& S = *reinterpret_cast<MsdSmem<WORD>*>(smem_raw);
-  uint32_t n;
-  if (!count.get(n)) return;   // the guessed capacity was too small: forward re-runs this stage
   const unsigned tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-  if (tid == 0) S.tile = atomicAdd(ticket, 1u);
+  // Where every digit starts in the output: the exclusive scan of the histogram the producer counted.
+  // Every CTA forms it for itself (1024 values, a few instructions per thread: no scan kernel in
+  // between, no launch), CTA 0 also leaves it in memory for the kernels that finish the buckets. A frame
+  // that is being skipped has an all-zero histogram, so they see empty buckets.
+  uint32_t hcount[MSD_DPT], hstart;
+  {
+    const uint4 h = *reinterpret_cast<const uint4*>(digit_hist + tid * MSD_DPT);
+    hcount[0] = h.x; hcount[1] = h.y; hcount[2] = h.z; hcount[3] = h.w;
+    const uint32_t mine = h.x + h.y + h.z + h.w;
+    uint32_t incl = mine;
+#pragma unroll
+    for (int s = 1; s < 32; s <<= 1) {
+      const uint32_t t = __shfl_up_sync(0xffffffffu, incl, s);
+      if (lane >= s) incl += t;
+    }
+    if (lane == 31) S.hist_sums[warp] = incl;
+    hstart = incl - mine;
+  }
+  uint32_t n;
+  const bool run = count.get(n);   // false: the guessed capacity was too small, forward re-runs this stage
+  if (run && tid == 0) S.tile = atomicAdd(ticket, 1u);
   {
     uint4* z = reinterpret_cast<uint4*>(&S.warp_hist[0][0]);
     constexpr int VEC = (int)(sizeof(S.warp_hist) / sizeof(uint4));
@@ -286,6 +286,17 @@ msd_partition_kernel(const WORD* __restrict__ in, WORD* __restrict__ out, Instan
     for (int i = 0; i < VEC / MSD_THREADS; ++i) z[i * MSD_THREADS + tid] = make_uint4(0u, 0u, 0u, 0u);
   }
   __syncthreads();
+  for (unsigned w = 0; w < warp; ++w) hstart += S.hist_sums[w];
+  if (blockIdx.x == 0 && start_out != nullptr) {
+    uint32_t run_start = hstart;
+#pragma unroll
+    for (int k = 0; k < MSD_DPT; ++k) {
+      start_out[tid * MSD_DPT + k] = run_start;
+      run_start += hcount[k];
+    }
+    if (tid == MSD_THREADS - 1) start_out[MSD_BINS] = run_start;
+  }
+  if (!run) return;
   const uint32_t tile = S.tile;
   const unsigned lt_mask = (1u << lane) - 1u;
   const size_t block_base = (size_t)tile * TILE;
@@ -382,8 +393,12 @@ msd_partition_kernel(const WORD* __restrict__ in, WORD* __restrict__ out, Instan
     }
     st_relaxed_v4(st, make_uint4(MSD_FLAG_PREFIX | (excl[0] + block_count[0]), MSD_FLAG_PREFIX | (excl[1] + block_count[1]),
                                  MSD_FLAG_PREFIX | (excl[2] + block_count[2]), MSD_FLAG_PREFIX | (excl[3] + block_count[3])));
+    uint32_t global_start = hstart;
 #pragma unroll
-    for (int k = 0; k < MSD_DPT; ++k) S.digit_global[d0 + k] = bucket_start[d0 + k] + excl[k] - local_start[k];
+    for (int k = 0; k < MSD_DPT; ++k) {
+      S.digit_global[d0 + k] = global_start + excl[k] - local_start[k];
+      global_start += hcount[k];
+    }
   }
   __syncthreads();
 #pragma unroll
@@ -879,25 +894,6 @@ depth_words_kernel(int P, const float* __restrict__ depths, const int* __restric
   }
 }
 
-// exclusive scan of the three digit histograms, one block each
-__global__ void __launch_bounds__(MSD_BINS)
-depth_scan_kernel(const uint32_t* __restrict__ hist, uint32_t* __restrict__ start) {
-  __shared__ uint32_t s_w[MSD_BINS / 32];
-  const uint32_t v = hist[blockIdx.x * MSD_BINS + threadIdx.x];
-  const unsigned lane = lane_id(), warp = threadIdx.x >> 5;
-  uint32_t incl = v;
-#pragma unroll
-  for (int d = 1; d < 32; d <<= 1) {
-    const uint32_t t = __shfl_up_sync(0xffffffffu, incl, d);
-    if (lane >= d) incl += t;
-  }
-  if (lane == 31) s_w[warp] = incl;
-  __syncthreads();
-  uint32_t woff = 0;
-  for (unsigned w = 0; w < warp; ++w) woff += s_w[w];
-  start[blockIdx.x * MSD_BINS + threadIdx.x] = woff + incl - v;
-}
-
 const uint32_t* presort_veto_flag(const GeomPtrs& g) { return g.sort_aux + DO_META + 3; }
 
 int launch_depth_order(const GeomPtrs& g, int P, const int* radii, cudaStream_t stream, bool debug) {
@@ -911,8 +907,6 @@ int launch_depth_order(const GeomPtrs& g, int P, const int* radii, cudaStream_t 
   depth_words_kernel<<<blocks, 256, 0, stream>>>(P, g.depths, radii, ib, g.sort_keys[0], aux + DO_HIST, aux + DO_META,
                                                  scramble);
   EGS_AFTER_LAUNCH(stream, debug);
-  depth_scan_kernel<<<3, MSD_BINS, 0, stream>>>(aux + DO_HIST, aux + DO_START);
-  EGS_AFTER_LAUNCH(stream, debug);
   constexpr int SMEM = (int)sizeof(MsdSmem<uint64_t>);
   EGS_CUDA_TRY(cudaFuncSetAttribute(msd_partition_kernel<uint64_t, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM));
   EGS_CUDA_TRY(cudaFuncSetAttribute(msd_partition_kernel<uint64_t, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM));
@@ -920,15 +914,15 @@ int launch_depth_order(const GeomPtrs& g, int P, const int* radii, cudaStream_t 
   const int grid = (int)g.sort_blocks;
   const size_t status_stride = g.sort_blocks * MSD_BINS;
   msd_partition_kernel<uint64_t, false><<<grid, MSD_THREADS, SMEM, stream>>>(
-      g.sort_keys[0], g.sort_keys[1], count, ib, MSD_BINS - 1, aux + DO_START, aux + DO_TICKET, aux + DO_STATUS,
+      g.sort_keys[0], g.sort_keys[1], count, ib, MSD_BINS - 1, aux + DO_HIST, nullptr, aux + DO_TICKET, aux + DO_STATUS,
       nullptr, 0u);
   EGS_AFTER_LAUNCH(stream, debug);
   msd_partition_kernel<uint64_t, false><<<grid, MSD_THREADS, SMEM, stream>>>(
-      g.sort_keys[1], g.sort_keys[0], count, ib + 10, MSD_BINS - 1, aux + DO_START + MSD_BINS, aux + DO_TICKET + 1,
+      g.sort_keys[1], g.sort_keys[0], count, ib + 10, MSD_BINS - 1, aux + DO_HIST + MSD_BINS, nullptr, aux + DO_TICKET + 1,
       aux + DO_STATUS + status_stride, nullptr, 0u);
   EGS_AFTER_LAUNCH(stream, debug);
   msd_partition_kernel<uint64_t, true><<<grid, MSD_THREADS, SMEM, stream>>>(
-      g.sort_keys[0], nullptr, count, ib + 20, MSD_BINS - 1, aux + DO_START + 2 * MSD_BINS, aux + DO_TICKET + 2,
+      g.sort_keys[0], nullptr, count, ib + 20, MSD_BINS - 1, aux + DO_HIST + 2 * MSD_BINS, nullptr, aux + DO_TICKET + 2,
       aux + DO_STATUS + 2 * status_stride, g.sort_vals[0], (uint32_t)((1ull << ib) - 1ull));
   EGS_AFTER_LAUNCH(stream, debug);
   return EGS_OK;
@@ -971,13 +965,13 @@ static int launch_duplicate(const GeomPtrs& g, WORD* words, const int* radii, co
 }
 
 template <typename WORD>
-static int launch_partition(const WORD* in, WORD* out, int capacity, InstanceCount count, int shift, const uint32_t* start,
-                            uint32_t* ticket, uint32_t* status, cudaStream_t stream, bool debug) {
+static int launch_partition(const WORD* in, WORD* out, int capacity, InstanceCount count, int shift, const uint32_t* hist,
+                            uint32_t* start, uint32_t* ticket, uint32_t* status, cudaStream_t stream, bool debug) {
   constexpr int SMEM = (int)sizeof(MsdSmem<WORD>);
   EGS_CUDA_TRY(cudaFuncSetAttribute(msd_partition_kernel<WORD, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM));
   const int grid = (capacity + MsdCfg<WORD>::TILE - 1) / MsdCfg<WORD>::TILE;
-  msd_partition_kernel<WORD, false><<<grid, MSD_THREADS, SMEM, stream>>>(in, out, count, shift, 0xffffffffu, start, ticket,
-                                                                        status, nullptr, 0u);
+  msd_partition_kernel<WORD, false><<<grid, MSD_THREADS, SMEM, stream>>>(in, out, count, shift, 0xffffffffu, hist, start,
+                                                                        ticket, status, nullptr, 0u);
   EGS_AFTER_LAUNCH(stream, debug);
   return EGS_OK;
 }
@@ -1038,8 +1032,6 @@ int launch_binning_buckets(const GeomPtrs& g, const BinningPtrs& b, const ImageP
       rc = launch_duplicate<uint64_t, true>(g, b.keys[1], radii, gauss_order, P, gx, gy, ib, count, bucket_shift, hist,
                                             stream, debug);
     if (rc) return rc;
-    bucket_scan_kernel<<<1, MSD_BINS, 0, stream>>>(hist, start);
-    EGS_AFTER_LAUNCH(stream, debug);
   }
   {
     StageTimer timer(stream, ST_SORT_HIST);   // reported as the global partition pass
@@ -1047,9 +1039,10 @@ int launch_binning_buckets(const GeomPtrs& g, const BinningPtrs& b, const ImageP
     int rc;
     if (narrow)
       rc = launch_partition<uint32_t>(reinterpret_cast<const uint32_t*>(b.keys[1]), reinterpret_cast<uint32_t*>(b.keys[0]),
-                                      capacity, count, shift, start, b.ticket, b.status, stream, debug);
+                                      capacity, count, shift, hist, start, b.ticket, b.status, stream, debug);
     else
-      rc = launch_partition<uint64_t>(b.keys[1], b.keys[0], capacity, count, shift, start, b.ticket, b.status, stream, debug);
+      rc = launch_partition<uint64_t>(b.keys[1], b.keys[0], capacity, count, shift, hist, start, b.ticket, b.status, stream,
+                                      debug);
     if (rc) return rc;
   }
   {

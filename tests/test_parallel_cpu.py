@@ -5,6 +5,7 @@ import os
 import socket
 
 import numpy as np
+import pytest
 import torch
 import torch.distributed as dist
 import torch.multiprocessing as mp
@@ -95,3 +96,30 @@ def test_exchange_shards_tile_the_buffer():
     assert lib.egs_exchange_shard_floats(16, 0) == 0
     g = cabi.peer_group(2, 1, [16, 32], [64, 128], grads_multicast=0)
     assert g.world == 2 and g.rank == 1 and g.grads[1] == 32 and g.signals[0] == 64 and not g.grads_multicast
+
+
+def test_factored_layout_and_view_batch_bookkeeping():
+    """FlatGrads(factored=True): the SH gradient leaves the flat buffer (14 floats per Gaussian stay), its
+    factors go to a slot of EGS_DRGB_SLOT_FLOATS floats (rows, padding to 16 bytes, camera centre) and the
+    rebuilt [P,M,3] tensor is a plain local one; ViewBatch hands every local view its own slot of the gather
+    buffer and lists all views' buffers in the global view order (host logic only: no kernel runs here)."""
+    from egogaussian_b200 import cabi
+    P, M = 1001, 16
+    assert cabi.drgb_slot_floats(P) == (3 * P + 3) // 4 * 4 + 4 and cabi.drgb_slot_floats(P) % 4 == 0
+    fg = parallel.FlatGrads(P, M, "cpu", factored=True)
+    assert [n for n, _ in fg.layout] == ["means3D", "opacity", "scales", "rotations", "means2D"]
+    assert fg.views["rgb"].shape == (P, 3) and fg.views["sh"].shape == (P, M, 3)
+    assert fg.views["rgb"].data_ptr() == fg.rgb_slot.data_ptr() and fg.rgb_slot.numel() == cabi.drgb_slot_floats(P)
+    out = fg.as_backward_out()
+    assert out["sh"] is None and out["rgb"] is fg.views["rgb"]
+    cov = parallel.FlatGrads(P, M, "cpu", factored=True, geometry="cov")
+    assert "cov3D" in cov.views and "scales" not in cov.views and cov.views["cov3D"].shape == (P, 6)
+    batch = parallel.ViewBatch(8, P, M, "cpu")
+    assert batch.local_views == list(range(8)) and len(batch.layouts) == 8 and batch.result is batch.layouts[0]
+    slot = cabi.drgb_slot_floats(P)
+    for v, lay in enumerate(batch.layouts):
+        assert lay.rgb_slot.data_ptr() == batch.gather.data_ptr() + 4 * v * slot
+        assert batch._slot_ptrs[v] == lay.rgb_slot.data_ptr() and batch._view_flat[v] == lay.flat.data_ptr()
+        assert batch.backward_args(v)["rgb_remote"] == [] and batch.backward_args(v)["out"]["rgb"] is lay.views["rgb"]
+    with pytest.raises(ValueError):
+        parallel.ViewBatch(9, P, M, "cpu")
