@@ -570,7 +570,7 @@ extern "C" int egs_debug_option(const char* name, const char* value) {
   } else if (strcmp(name, "blend_forward") == 0) {
     g_dbg_fwd_v2.store(!unset && strcmp(value, "v2") == 0 ? 1 : 0, std::memory_order_relaxed);
   } else if (strcmp(name, "blend_backward") == 0) {
-    g_dbg_bwd_ppl.store(!unset && value[0] == '2' ? 2 : 0, std::memory_order_relaxed);
+    g_dbg_bwd_ppl.store(unset ? 0 : value[0] == '2' ? 2 : 4, std::memory_order_relaxed);
   } else if (strcmp(name, "exchange_phases") == 0) {
     g_dbg_xphases.store(unset ? 0 : (value[0] == 'a' ? 1 : 2), std::memory_order_relaxed);
   } else {

@@ -383,8 +383,11 @@ int launch_blend_backward(const EgsBackwardArgs& a, const GeomPtrs& g, const uin
                           const ImagePtrs& im, const BackwardScratch& s, cudaStream_t stream) {
   const dim3 grid(tiles_x(a.width), tiles_y(a.height), 1);
   StageTimer timer(stream, ST_BLEND_BWD);
-  // pixels per lane: 4 by default; egs_debug_option("blend_backward", "2") for the A/B
-  const int ppl = debug_options().bwd_ppl == 2 ? 2 : 4;
+  // pixels per lane: 4 (two warps per tile), except on images with so few tiles that two warps each would
+  // leave most of the GPU's warp slots empty (256 x 256: 0.106 against 0.081 ms);
+  // egs_debug_option("blend_backward", "2" | "4") forces either for the A/B
+  const int forced = debug_options().bwd_ppl;
+  const int ppl = forced ? forced : ((long long)grid.x * grid.y < 148 * 8 ? 2 : 4);
 #define EGS_BWD_LAUNCH(PPL, CO)                                                                                   \
   blend_backward_kernel<PPL, CO><<<grid, 256 / PPL, 0, stream>>>(                                                 \
       im.ranges, point_list, a.width, a.height, (int)grid.x, a.background, g.means2D, g.conic_opacity, g.rgb_depth, \

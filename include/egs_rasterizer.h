@@ -626,7 +626,7 @@ int egs_binning_keys(const void* geom_buffer, int P, void* binning_buffer, int n
  *   "presort"          "0" | "1"                       never / always sort the Gaussians front to back first
  *   "presort_scramble" "1"                             presort by keys unrelated to depth and raise its veto
  *   "blend_forward"    "v2"                            the two-pixels-per-thread forward blend
- *   "blend_backward"   "2"                             two instead of four pixels per thread in the backward blend
+ *   "blend_backward"   "2" | "4"                       pixels per thread in the backward blend (default: by image size)
  *   "exchange_phases"  "a" | "b"                       timing only: run one phase of egs_exchange_sum_factored */
 int egs_debug_option(const char* name, const char* value);
 

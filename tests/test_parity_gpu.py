@@ -539,6 +539,7 @@ def test_backward_kernel_variants_agree(built, cuda_device, debug_options):
     from egogaussian_b200 import cabi
     for case in (CASES[0], CASES[2]):
         kw, ups = case_inputs(case, cuda_device)
+        debug_options("blend_backward", "4")
         _, g4 = run_cuda(kw, ups)
         debug_options("blend_backward", "2")
         _, g2 = run_cuda(kw, ups)
