@@ -166,9 +166,10 @@ def build_inputs(a, view, device):
     else:
         kw["cov3D_precomp"] = sc.cov3D()
     wc, wd, wa = scenes.upstream_weights(a.width, a.height, 3001 + (view or 0))
-    host = {"viewmatrix": cam.viewmatrix.pin_memory(), "projmatrix": cam.projmatrix.pin_memory(),
-            "campos": cam.campos.pin_memory(), "wc": wc.contiguous().pin_memory(), "wd": wd.contiguous().pin_memory(),
-            "wa": wa.contiguous().pin_memory()} if device.type == "cuda" else None
+    # host side of a step: the camera as one 35-float record (view | projection | centre) and the three
+    # upstream-gradient images as one [5,H,W] block, both in pinned memory
+    host = {"cam": torch.cat((cam.viewmatrix.reshape(-1), cam.projmatrix.reshape(-1), cam.campos.reshape(-1))).float().pin_memory(),
+            "w": torch.cat((wc, wd, wa)).contiguous().pin_memory()} if device.type == "cuda" else None
     cpu_kw = dict(kw)
     kw = {k: (v.to(device).contiguous() if isinstance(v, torch.Tensor) else v) for k, v in kw.items()}
     ups = dict(dL_dcolor=wc.to(device).contiguous(), dL_ddepth=wd.to(device).contiguous(),
@@ -178,38 +179,55 @@ def build_inputs(a, view, device):
 
 class HostLoop:
     """Per-step host<->device traffic of the e2e region, two steps in flight, the way a training loop
-    feeds frames and logs its loss: step k's inputs are copied from pinned memory into buffer k % 2
-    (images on a side stream, camera on the main one), its loss is copied back asynchronously, and the
-    host reads the loss of step k - 1 once step k is enqueued. Every step still pays its own copies
-    and its own read; the host just does not idle the GPU between steps. Used by both arms."""
+    feeds frames and logs its loss: step k's inputs are copied from pinned memory into buffer k % 2 on a
+    copy stream (the camera first, then the images), its loss is copied back on a third stream, and the
+    host reads the loss of step k - 1 once step k is enqueued. Every step still pays its own copies and
+    its own read; they just do not sit between two kernels of the main stream. Used by both arms."""
 
     def __init__(self, host, device):
         import torch
         self.torch, self.host = torch, host
-        self.dv = [{k: torch.empty_like(v, device=device) for k, v in host.items()} for _ in range(2)]
+        self.dv = []
+        for _ in range(2):
+            cam = torch.empty_like(host["cam"], device=device)
+            self.dv.append({"cam": cam, "w": torch.empty_like(host["w"], device=device), "viewmatrix": cam[0:16].view(4, 4),
+                            "projmatrix": cam[16:32].view(4, 4), "campos": cam[32:35]})
         self.loss_host = [torch.empty((), dtype=torch.float32).pin_memory() for _ in range(2)]
         self.done = [torch.cuda.Event() for _ in range(2)]
         self.copied = [torch.cuda.Event() for _ in range(2)]
+        self.cam_ready = [torch.cuda.Event() for _ in range(2)]
+        self.loss_ready = [torch.cuda.Event() for _ in range(2)]
         self.copy_stream = torch.cuda.Stream(device=device)
+        self.back_stream = torch.cuda.Stream(device=device)
         self.k, self.last_loss = 0, None
 
     def begin(self):
-        """Enqueue this step's host->device copies; returns (device buffers, event of the image copies).
+        """Enqueue this step's host->device copies; returns (device buffers, event of the image copy).
         Buffer k % 2 is free: step k - 2 finished before its loss was read at the end of step k - 1."""
         b = self.k % 2
         dv = self.dv[b]
         with self.torch.cuda.stream(self.copy_stream):
-            for k in ("wc", "wd", "wa"):
-                dv[k].copy_(self.host[k], non_blocking=True)
+            dv["cam"].copy_(self.host["cam"], non_blocking=True)
+            self.cam_ready[b].record()
+            dv["w"].copy_(self.host["w"], non_blocking=True)
             self.copied[b].record()
-        for k in ("viewmatrix", "projmatrix", "campos"):
-            dv[k].copy_(self.host[k], non_blocking=True)
+        self.torch.cuda.current_stream().wait_event(self.cam_ready[b])
         return dv, self.copied[b]
+
+    @staticmethod
+    def loss(color, depth, alpha, w):
+        """<(color, depth, alpha), w>: the scalar both arms differentiate."""
+        import torch
+        return torch.dot(torch.cat((color, depth, alpha)).view(-1), w.view(-1))
 
     def end(self, loss):
         b = self.k % 2
-        self.loss_host[b].copy_(loss.detach(), non_blocking=True)
-        self.done[b].record()
+        self.loss_ready[b].record()
+        with self.torch.cuda.stream(self.back_stream):
+            self.back_stream.wait_event(self.loss_ready[b])
+            loss.record_stream(self.back_stream)
+            self.loss_host[b].copy_(loss.detach(), non_blocking=True)
+            self.done[b].record()
         if self.k > 0:
             self.done[1 - b].synchronize()                  # the previous step's result is on the host
             self.last_loss = float(self.loss_host[1 - b])
@@ -683,9 +701,9 @@ def run_ours(a, rank, world, local_rank):
         flat_e2e = parallel.FlatGrads(P, M, device, allocate=ex.allocate) if (ex and factored) else flat
 
         def e2e_step():
-            # the big host inputs (the upstream-gradient images, standing in for the ground-truth
-            # frame) are not needed before the loss: they are prefetched on a side stream while the
-            # forward runs; the camera matrices are needed at once and go on the main stream
+            # the host inputs travel on a copy stream: the camera record first (the forward waits for it),
+            # then the upstream-gradient images (standing in for the ground-truth frame), which are not
+            # needed before the loss
             dv, copied = loop.begin()
             rs = GaussianRasterizationSettings(a.height, a.width, kw["tanfovx"], kw["tanfovy"], kw["bg"], 1.0,
                                                dv["viewmatrix"], dv["projmatrix"], a.sh_degree, dv["campos"], False, False)
@@ -694,7 +712,7 @@ def run_ours(a, rank, world, local_rank):
                 means3D=leaves["means3D"], means2D=means2D, opacities=leaves["opacities"], shs=leaves["shs"],
                 scales=leaves.get("scales"), rotations=leaves.get("rotations"), cov3D_precomp=leaves.get("cov3D_precomp"))
             torch.cuda.current_stream().wait_event(copied)
-            loss = (color * dv["wc"]).sum() + (depth * dv["wd"]).sum() + (alpha * dv["wa"]).sum()
+            loss = loop.loss(color, depth, alpha, dv["w"])
             loss.backward()
             if dist_on and ex and all(k in LEAF_TO_FLAT for k in leaves):   # gather the autograd gradients into the peer-mapped flat buffer, one exchange
                 for k, t in leaves.items():
@@ -913,7 +931,7 @@ def run_reference(a, rank, world, local_rank):
                                           shs=leaves["shs"], scales=leaves.get("scales"), rotations=leaves.get("rotations"),
                                           cov3D_precomp=leaves.get("cov3D_precomp"))
         torch.cuda.current_stream().wait_event(copied)
-        loss = (color * dv["wc"]).sum() + (depth * dv["wd"]).sum() + (alpha * dv["wa"]).sum()
+        loss = loop.loss(color, depth, alpha, dv["w"])
         loss.backward()
         loop.end(loss)
         for t in leaves.values():

@@ -96,7 +96,8 @@ static const char* kStageNames[ST_COUNT] = {"preprocess_fwd", "scan", "duplicate
 constexpr int kMaxDevices = 64;
 struct HostCountSlot {
   uint32_t* host = nullptr;
-  cudaEvent_t arrived = nullptr;
+  cudaEvent_t scanned = nullptr, arrived = nullptr;
+  cudaStream_t side = nullptr;   // the read-back copy runs beside the caller's stream, not in it
 };
 static HostCountSlot* host_count_slot() {
   static thread_local HostCountSlot slots[kMaxDevices];
@@ -106,7 +107,12 @@ static HostCountSlot* host_count_slot() {
   if (!slot.host) {
     void* p = nullptr;
     if (cudaHostAlloc(&p, 64, cudaHostAllocDefault) != cudaSuccess) return nullptr;
-    if (cudaEventCreateWithFlags(&slot.arrived, cudaEventDisableTiming) != cudaSuccess) {
+    if (cudaEventCreateWithFlags(&slot.arrived, cudaEventDisableTiming) != cudaSuccess ||
+        cudaEventCreateWithFlags(&slot.scanned, cudaEventDisableTiming) != cudaSuccess ||
+        cudaStreamCreateWithFlags(&slot.side, cudaStreamNonBlocking) != cudaSuccess) {
+      if (slot.arrived) cudaEventDestroy(slot.arrived);
+      if (slot.scanned) cudaEventDestroy(slot.scanned);
+      slot.arrived = slot.scanned = nullptr;
       cudaFreeHost(p);
       return nullptr;
     }
@@ -239,8 +245,6 @@ static int forward_impl(const char* who, const EgsForwardArgs* args, const EgsMo
   const GeomPtrs g(geom_mem, (size_t)a.P);
   const ImagePtrs im(img_mem, a.width, a.height);
 
-  if (int rc = launch_preprocess_forward(a, model, g, stream)) return rc;
-
   const DebugOptions dbg = debug_options();
   const bool fits = packed_path_fits(a.P, a.width, a.height);   // tile | depth | index in one 64-bit word
   const bool forced = dbg.sort != SORT_AUTO;
@@ -258,46 +262,56 @@ static int forward_impl(const char* who, const EgsForwardArgs* args, const EgsMo
                                                         : a.P >= 300000;
   const bool presort = presort_wanted && !forced && presorted_path_ok(a.P, a.width, a.height);
   const uint32_t* order = presort ? g.sort_vals[0] : nullptr;
-  if (presort)
-    if (int rc = launch_depth_order(g, a.P, a.radii, stream, a.debug)) return rc;
-  if (int rc = launch_scan_tiles(g, a.P, order, stream, a.debug)) return rc;
-
-  // The one device->host read per forward (the reference's is rasterizer_impl.cu:281-282): the
-  // instance count (and, next to it, the presort's veto and the prefilter fault) lands in a pinned
-  // slot and an event marks its arrival.
-  HostCountSlot* slot = host_count_slot();
-  if (!slot) {
-    set_error("%s: cannot allocate the pinned read-back slot", who);
-    return EGS_ERR_CUDA;
-  }
-  const uint32_t* n_dev = g.point_offsets + (a.P - 1);
-  const uint32_t* veto_dev = presort ? presort_veto_flag(g) : nullptr;
-  slot->host[1] = slot->host[2] = 0u;
-  EGS_CUDA_TRY(cudaMemcpyAsync(slot->host, n_dev, sizeof(uint32_t), cudaMemcpyDeviceToHost, stream));
-  if (veto_dev)
-    EGS_CUDA_TRY(cudaMemcpyAsync(slot->host + 1, veto_dev, sizeof(uint32_t), cudaMemcpyDeviceToHost, stream));
-  if (a.prefiltered)
-    EGS_CUDA_TRY(cudaMemcpyAsync(slot->host + 2, g.prefilter_fault, sizeof(uint32_t), cudaMemcpyDeviceToHost, stream));
-  EGS_CUDA_TRY(cudaEventRecord(slot->arrived, stream));
 
   // Speculative run: with a caller-provided guess the binning workspace is sized from the guess and
   // binning + blend are enqueued before the count is known; the kernels read the count (and the veto)
   // on the device and skip themselves if it does not fit. Only the bucket path takes part.
+  const bool speculate = a.num_rendered_hint > 0 && !forced && !a.debug &&
+                         (presort || bucket_path_ok(a.P, a.num_rendered_hint, a.width, a.height));
   int capacity = 0;
   void* bin_mem = nullptr;
-  bool enqueued = false;
-  if (a.num_rendered_hint > 0 && !forced && !a.debug &&
-      (presort || bucket_path_ok(a.P, a.num_rendered_hint, a.width, a.height))) {
+  if (speculate) {
     capacity = a.num_rendered_hint;
     bin_mem = a.binning_alloc(a.binning_ctx, egs_binning_bytes(capacity, a.width, a.height));
     if (!bin_mem) {
       set_error("%s: binning workspace callback returned NULL", who);
       return EGS_ERR_ALLOC;
     }
+  }
+
+  // Everything that must start from zero is cleared here, in front of the first kernel: a memset
+  // between two kernels costs the stream ~4 us each time.
+  EGS_CUDA_TRY(cudaMemsetAsync(g.zero_begin, 0, g.zero_bytes, stream));
+  if (speculate)
+    if (int rc = zero_binning_buckets(BinningPtrs(bin_mem, (size_t)capacity), stream)) return rc;
+
+  if (int rc = launch_preprocess_forward(a, model, g, stream)) return rc;
+  if (presort)
+    if (int rc = launch_depth_order(g, a.P, a.radii, stream, a.debug)) return rc;
+  if (int rc = launch_scan_tiles(g, a.P, order, stream, a.debug)) return rc;
+
+  // The one device->host read per forward (the reference's is rasterizer_impl.cu:281-282): the
+  // instance count, the presort's veto and the prefilter fault are one 12-byte record; it is copied
+  // to a pinned slot on a side stream that waits for the scan, so that the caller's stream runs on
+  // into the binning kernels instead of idling through the copy.
+  HostCountSlot* slot = host_count_slot();
+  if (!slot) {
+    set_error("%s: cannot allocate the pinned read-back slot", who);
+    return EGS_ERR_CUDA;
+  }
+  const uint32_t* n_dev = g.readback;
+  const uint32_t* veto_dev = presort ? presort_veto_flag(g) : nullptr;
+  EGS_CUDA_TRY(cudaEventRecord(slot->scanned, stream));
+  EGS_CUDA_TRY(cudaStreamWaitEvent(slot->side, slot->scanned, 0));
+  EGS_CUDA_TRY(cudaMemcpyAsync(slot->host, g.readback, 3 * sizeof(uint32_t), cudaMemcpyDeviceToHost, slot->side));
+  EGS_CUDA_TRY(cudaEventRecord(slot->arrived, slot->side));
+
+  bool enqueued = false;
+  if (speculate) {
     const BinningPtrs b(bin_mem, (size_t)capacity);
     const InstanceCount count{n_dev, (uint32_t)capacity, veto_dev};
     if (int rc = launch_binning_buckets(g, b, im, a.radii, order, presort, a.P, capacity, count, a.width, a.height, stream,
-                                        false))
+                                        false, /*zeroed=*/true))
       return rc;
     if (int rc = launch_blend_forward(a, g, b.vals[0], im, stream)) return rc;
     enqueued = true;
@@ -340,12 +354,14 @@ static int forward_impl(const char* who, const EgsForwardArgs* args, const EgsMo
   if (dbg.sort == SORT_PAIRS8) {
     if (int rc = launch_binning(g, b, im, a.radii, a.P, R, a.width, a.height, stream, a.debug)) return rc;
   } else if (presort && !vetoed) {
-    if (int rc = launch_binning_buckets(g, b, im, a.radii, order, true, a.P, R, count, a.width, a.height, stream, a.debug))
+    if (int rc = launch_binning_buckets(g, b, im, a.radii, order, true, a.P, R, count, a.width, a.height, stream, a.debug,
+                                        false))
       return rc;
   } else if (!fits || dbg.sort == SORT_PAIRS) {
     if (int rc = launch_binning_packed(g, b, im, a.radii, order, a.P, R, a.width, a.height, true, stream, a.debug)) return rc;
   } else if (bucket_path_ok(a.P, R, a.width, a.height) && dbg.sort != SORT_PACKED) {
-    if (int rc = launch_binning_buckets(g, b, im, a.radii, order, false, a.P, R, count, a.width, a.height, stream, a.debug))
+    if (int rc = launch_binning_buckets(g, b, im, a.radii, order, false, a.P, R, count, a.width, a.height, stream, a.debug,
+                                        false))
       return rc;
   } else {
     if (int rc = launch_binning_packed(g, b, im, a.radii, order, a.P, R, a.width, a.height, false, stream, a.debug)) return rc;

@@ -30,7 +30,7 @@ constexpr unsigned long long SCAN_VALUE_MASK = (1ull << 62) - 1;
 template <bool GATHER>
 __global__ void __launch_bounds__(SCAN_THREADS)
 scan_tiles_kernel(const uint32_t* __restrict__ in, const uint32_t* __restrict__ perm, uint32_t* __restrict__ out,
-                  int n, unsigned long long* __restrict__ status) {
+                  int n, unsigned long long* __restrict__ status, uint32_t* __restrict__ total /* may be null */) {
   __shared__ uint32_t s_tile;
   __shared__ uint32_t s_warp_sums[SCAN_THREADS / 32];
   __shared__ uint32_t s_block_prefix;
@@ -119,18 +119,24 @@ scan_tiles_kernel(const uint32_t* __restrict__ in, const uint32_t* __restrict__ 
     for (int k = 0; k < SCAN_ITEMS; ++k)
       if (base + k < (size_t)n) out[base + k] = v[k] + off;
   }
+  // the sum of everything, next to the other words the host reads back
+  if (total != nullptr) {
+#pragma unroll
+    for (int k = 0; k < SCAN_ITEMS; ++k)
+      if (base + k + 1 == (size_t)n) *total = v[k] + off;
+  }
 }
 
 int launch_scan_tiles(const GeomPtrs& g, int P, const uint32_t* order, cudaStream_t stream, bool debug) {
   const int blocks = (P + SCAN_TILE - 1) / SCAN_TILE;
   StageTimer timer(stream, ST_SCAN);
-  EGS_CUDA_TRY(cudaMemsetAsync(g.scan_status, 0, (size_t)(blocks + 1) * 8, stream));
+  // g.scan_status was cleared with the rest of the zeroed run when the forward began
   if (order)
     scan_tiles_kernel<true><<<blocks, SCAN_THREADS, 0, stream>>>(g.tiles_touched, order, g.point_offsets, P,
-                                                                 g.scan_status);
+                                                                 g.scan_status, g.readback);
   else
     scan_tiles_kernel<false><<<blocks, SCAN_THREADS, 0, stream>>>(g.tiles_touched, nullptr, g.point_offsets, P,
-                                                                  g.scan_status);
+                                                                  g.scan_status, g.readback);
   EGS_AFTER_LAUNCH(stream, debug);
   return EGS_OK;
 }
@@ -139,7 +145,7 @@ int launch_scan_tiles(const GeomPtrs& g, int P, const uint32_t* order, cudaStrea
 int launch_inclusive_scan(const uint32_t* in, uint32_t* out, int n, unsigned long long* status, cudaStream_t stream) {
   const int blocks = (n + SCAN_TILE - 1) / SCAN_TILE;
   EGS_CUDA_TRY(cudaMemsetAsync(status, 0, (size_t)(blocks + 1) * 8, stream));
-  scan_tiles_kernel<false><<<blocks, SCAN_THREADS, 0, stream>>>(in, nullptr, out, n, status);
+  scan_tiles_kernel<false><<<blocks, SCAN_THREADS, 0, stream>>>(in, nullptr, out, n, status, nullptr);
   EGS_AFTER_LAUNCH(stream, false);
   return EGS_OK;
 }

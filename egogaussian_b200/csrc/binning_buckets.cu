@@ -64,7 +64,7 @@ constexpr int BK_CAP = 12288;                      // words per bucket held in s
 // small and large rectangles, makes every store coalesced, and lets the warp count a bucket once
 // per 32 slots (match.any) for the histogram, which therefore needs no pass of its own.
 // words of GeomPtrs::sort_aux (depth presort): three digit histograms, their exclusive scans, tickets,
-// meta (2: P for the partition kernel, 3: veto flag), then three status areas
+// meta (2: P for the partition kernel, 4: count of set-aside Gaussians), then three status areas
 constexpr int DO_HIST = 0, DO_START = 3 * 1024, DO_TICKET = 6 * 1024, DO_META = DO_TICKET + 8,
               DO_STATUS = DO_META + 8;
 static_assert(DO_STATUS == DEPTH_ORDER_AUX_WORDS, "aux layout");
@@ -864,7 +864,8 @@ constexpr uint32_t DEPTH_KEY_MAX = (1u << 30) - 1u;
 __global__ void __launch_bounds__(256)
 depth_words_kernel(int P, const float* __restrict__ depths, const int* __restrict__ radii, int idx_bits,
                    uint64_t* __restrict__ words, uint32_t* __restrict__ hist /* [3][MSD_BINS] */,
-                   uint32_t* __restrict__ meta, bool scramble /* test: keys unrelated to depth + veto */) {
+                   uint32_t* __restrict__ meta, uint32_t* __restrict__ veto_flag,
+                   bool scramble /* test: keys unrelated to depth + veto */) {
   __shared__ uint32_t s_hist[3 * MSD_BINS];
   for (int i = threadIdx.x; i < 3 * MSD_BINS; i += 256) s_hist[i] = 0;
   __syncthreads();
@@ -885,7 +886,7 @@ depth_words_kernel(int P, const float* __restrict__ depths, const int* __restric
     atomicAdd(&s_hist[MSD_BINS + ((key >> 10) & (MSD_BINS - 1))], 1u);
     atomicAdd(&s_hist[2 * MSD_BINS + (key >> 20)], 1u);
   }
-  if (veto) meta[3] = 1u;
+  if (veto) *veto_flag = 1u;
   if (blockIdx.x == 0 && threadIdx.x == 0) meta[2] = (uint32_t)P;
   __syncthreads();
   for (int i = threadIdx.x; i < 3 * MSD_BINS; i += 256) {
@@ -894,18 +895,18 @@ depth_words_kernel(int P, const float* __restrict__ depths, const int* __restric
   }
 }
 
-const uint32_t* presort_veto_flag(const GeomPtrs& g) { return g.sort_aux + DO_META + 3; }
+const uint32_t* presort_veto_flag(const GeomPtrs& g) { return g.readback + 1; }
 
 int launch_depth_order(const GeomPtrs& g, int P, const int* radii, cudaStream_t stream, bool debug) {
   StageTimer timer(stream, ST_DEPTH_ORDER);
   uint32_t* aux = g.sort_aux;
   const int ib = tile_id_bits((uint32_t)(P > 1 ? P - 1 : 1));
-  EGS_CUDA_TRY(cudaMemsetAsync(aux, 0, g.sort_aux_bytes, stream));
+  // the aux words were cleared with the rest of the zeroed run when the forward began
   const int blocks = P < 148 * 4 * 256 ? (P + 255) / 256 : 148 * 4;
   // test hook (egs_debug_option "presort_scramble"): an order unrelated to depth + the veto raised
   const bool scramble = debug_options().presort_scramble != 0;
   depth_words_kernel<<<blocks, 256, 0, stream>>>(P, g.depths, radii, ib, g.sort_keys[0], aux + DO_HIST, aux + DO_META,
-                                                 scramble);
+                                                 g.readback + 1, scramble);
   EGS_AFTER_LAUNCH(stream, debug);
   constexpr int SMEM = (int)sizeof(MsdSmem<uint64_t>);
   EGS_CUDA_TRY(cudaFuncSetAttribute(msd_partition_kernel<uint64_t, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM));
@@ -995,12 +996,20 @@ static int launch_split(const WORD* words, const uint32_t* start, uint32_t* poin
   return EGS_OK;
 }
 
+// histogram, ticket and the status words of the single partition pass (not the whole area the
+// five-pass paths need)
+int zero_binning_buckets(const BinningPtrs& b, cudaStream_t stream) {
+  const size_t zero = reinterpret_cast<char*>(b.status + b.sort_blocks * MSD_BINS) - reinterpret_cast<char*>(b.hist);
+  EGS_CUDA_TRY(cudaMemsetAsync(b.hist, 0, zero, stream));
+  return EGS_OK;
+}
+
 // `capacity` sizes the grids and the workspace `b`; the real number of instances is read on the
 // device through `count` (it may still be in flight when this is enqueued). capacity == 0 means
-// the count is known to be 0.
+// the count is known to be 0. `zeroed`: the caller already ran zero_binning_buckets on this stream.
 int launch_binning_buckets(const GeomPtrs& g, const BinningPtrs& b, const ImagePtrs& im, const int* radii,
                            const uint32_t* gauss_order, bool presorted, int P, int capacity, InstanceCount count, int W,
-                           int H, cudaStream_t stream, bool debug) {
+                           int H, cudaStream_t stream, bool debug, bool zeroed) {
   const int gx = tiles_x(W), gy = tiles_y(H);
   const int n_tiles = gx * gy;
   if (capacity == 0) {
@@ -1017,10 +1026,8 @@ int launch_binning_buckets(const GeomPtrs& g, const BinningPtrs& b, const ImageP
   const bool narrow = presorted && tb + ib <= 32;   // tile | index fits a 32-bit word
   {
     StageTimer timer(stream, ST_DUPLICATE);
-    // histogram, ticket and the status words of the single partition pass (not the whole area the
-    // five-pass paths need)
-    const size_t zero = reinterpret_cast<char*>(b.status + b.sort_blocks * MSD_BINS) - reinterpret_cast<char*>(b.hist);
-    EGS_CUDA_TRY(cudaMemsetAsync(b.hist, 0, zero, stream));
+    if (!zeroed)
+      if (int rc0 = zero_binning_buckets(b, stream)) return rc0;
     int rc;
     if (narrow)
       rc = launch_duplicate<uint32_t, false>(g, reinterpret_cast<uint32_t*>(b.keys[1]), radii, gauss_order, P, gx, gy, ib,

@@ -80,7 +80,7 @@ constexpr int SORT_TILE = SORT_THREADS * SORT_ITEMS;
 
 struct GeomLayout {
   size_t depths, means2D, conic_opacity, rgb_depth, clamped, tiles_touched, point_offsets,
-      scan_status, sort_keys[2], sort_vals[2], sort_aux, sort_blocks, sort_aux_bytes, prefilter_fault, total;
+      scan_status, sort_keys[2], sort_vals[2], sort_aux, sort_blocks, sort_aux_bytes, readback, zero_bytes, total;
   explicit GeomLayout(size_t P) {
     size_t o = 0;
     auto take = [&](size_t bytes) { size_t r = o; o = align_up(o + bytes); return r; };
@@ -91,18 +91,23 @@ struct GeomLayout {
     clamped = take(P);
     tiles_touched = take(P * 4);
     point_offsets = take(P * 4);
+    // Everything a forward needs zeroed lies in one run, cleared by ONE memset before the first kernel
+    // (every memset between two kernels costs the stream ~4 us): the look-back words of the scan, the
+    // presort's aux words (digit histograms, tickets, flags, the status words of three partition passes)
+    // and the 16-byte record the host reads back: [0] instance count (written by the scan), [1] the
+    // presort's veto, [2] set when a Gaussian is culled although `prefiltered` promised otherwise.
     scan_status = take(((P + SCAN_TILE - 1) / SCAN_TILE + 1) * 8 + 256);
+    sort_blocks = (P + SORT_TILE - 1) / SORT_TILE;
+    sort_aux_bytes = (DEPTH_ORDER_AUX_WORDS + 3 * sort_blocks * 1024) * 4;
+    sort_aux = take(sort_aux_bytes);
+    readback = take(16);
+    zero_bytes = readback + 16 - scan_status;
     // front-to-back order of the Gaussians (binning presort, binning_buckets.cu): packed words
-    // (30-bit depth key | index) in two buffers, the resulting order, and aux = digit histograms,
-    // their scans, tickets, flags and the status words of three partition passes
+    // (30-bit depth key | index) in two buffers and the resulting order
     sort_keys[0] = take(P * 8);
     sort_keys[1] = take(P * 8);
     sort_vals[0] = take(P * 4);
     sort_vals[1] = 0;
-    sort_blocks = (P + SORT_TILE - 1) / SORT_TILE;
-    sort_aux_bytes = (DEPTH_ORDER_AUX_WORDS + 3 * sort_blocks * 1024) * 4;
-    sort_aux = take(sort_aux_bytes);
-    prefilter_fault = take(4);   // set when a Gaussian is culled although `prefiltered` promised otherwise
     total = o + 256;
   }
 };
@@ -119,8 +124,10 @@ struct GeomPtrs {
   uint64_t* sort_keys[2];           // depth-order presort; the order ends in sort_vals[0]
   uint32_t* sort_vals[2];
   uint32_t* sort_aux;
+  uint32_t* readback;               // [0] instance count, [1] presort veto, [2] prefilter fault
   uint32_t* prefilter_fault;
-  size_t sort_blocks, sort_aux_bytes;
+  void* zero_begin;                 // scan_status .. readback: cleared by one memset per forward
+  size_t sort_blocks, sort_aux_bytes, zero_bytes;
   GeomPtrs(void* base, size_t P) {
     GeomLayout L(P);
     char* b = static_cast<char*>(base);
@@ -136,7 +143,10 @@ struct GeomPtrs {
     sort_vals[0] = reinterpret_cast<uint32_t*>(b + L.sort_vals[0]);
     sort_vals[1] = nullptr;
     sort_aux = reinterpret_cast<uint32_t*>(b + L.sort_aux);
-    prefilter_fault = reinterpret_cast<uint32_t*>(b + L.prefilter_fault);
+    readback = reinterpret_cast<uint32_t*>(b + L.readback);
+    prefilter_fault = readback + 2;
+    zero_begin = b + L.scan_status;
+    zero_bytes = L.zero_bytes;
     sort_blocks = L.sort_blocks;
     sort_aux_bytes = L.sort_aux_bytes;
   }
@@ -289,7 +299,8 @@ bool presorted_path_ok(int P, int W, int H);
 const uint32_t* presort_veto_flag(const GeomPtrs& g);
 int launch_binning_buckets(const GeomPtrs& g, const BinningPtrs& b, const ImagePtrs& im, const int* radii,
                            const uint32_t* order, bool presorted, int P, int capacity, InstanceCount count, int W,
-                           int H, cudaStream_t stream, bool debug);
+                           int H, cudaStream_t stream, bool debug, bool zeroed);
+int zero_binning_buckets(const BinningPtrs& b, cudaStream_t stream);
 // keys[i] = tile << 32 | depth bits of point_list[i], rebuilt from the tile ranges (tests only: no
 // kernel of the path reads the sorted keys, so the fast paths do not write them)
 int launch_binning_keys(const GeomPtrs& g, const ImagePtrs& im, const uint32_t* point_list, uint64_t* keys, int W,

@@ -295,7 +295,6 @@ int launch_preprocess_forward(const EgsForwardArgs& a, const EgsModelArgs* model
   const float focal_y = a.height / (2.0f * a.tan_fovy);
   const float focal_x = a.width / (2.0f * a.tan_fovx);
   const int blocks = (P + PF_THREADS - 1) / PF_THREADS;
-  if (a.prefiltered) EGS_CUDA_TRY(cudaMemsetAsync(g.prefilter_fault, 0, sizeof(uint32_t), stream));
   StageTimer timer(stream, ST_PREPROCESS);
   const bool staged = a.shs != nullptr && a.sh_coeffs == 16 && (reinterpret_cast<uintptr_t>(a.shs) & 15u) == 0;
   RawModel raw{};

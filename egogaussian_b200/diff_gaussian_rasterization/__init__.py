@@ -81,6 +81,9 @@ class _RasterizeGaussians(torch.autograd.Function):
         ctx.save_for_backward(colors_precomp, means3D, scales, rotations, cov3Ds_precomp, radii, sh,
                               geom_blob, binning_blob, image_blob, alpha)
         ctx.mark_non_differentiable(radii)
+        # backward fills in the missing upstream gradients itself; left on, autograd would also
+        # zero-fill a "gradient" for the integer radii on every iteration
+        ctx.set_materialize_grads(False)
         return color, radii, depth, alpha
 
     @staticmethod

@@ -150,12 +150,17 @@ class _RasterizeRaw(torch.autograd.Function):
         ctx.save_for_backward(means3D, colors, scaling_raw, rotation_raw, opacity_raw, features_dc, features_rest,
                               mask, accum_R, train_R, radii, geom, binning, img, alpha)
         ctx.mark_non_differentiable(radii)
+        ctx.set_materialize_grads(False)   # no zero-filled "gradient" for the integer radii
         return color, radii, depth, alpha
 
     @staticmethod
     def backward(ctx, g_color, _g_radii, g_depth, g_alpha):
         (means3D, colors, scaling_raw, rotation_raw, opacity_raw, features_dc, features_rest, mask, accum_R, train_R,
          radii, geom, binning, img, alpha) = ctx.saved_tensors
+        if g_color is None:
+            g_color = torch.zeros_like(alpha.expand(3, -1, -1))
+        g_depth = torch.zeros_like(alpha) if g_depth is None else g_depth
+        g_alpha = torch.zeros_like(alpha) if g_alpha is None else g_alpha
         rs = ctx.rs
         num_rendered, which, copies = ctx.meta
         need = ctx.needs_input_grad
