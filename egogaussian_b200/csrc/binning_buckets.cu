@@ -78,10 +78,17 @@ constexpr int DUP_CTAS_PER_SM = 8;
 // went from 0.08 to 0.18 ms on two of the eight bench views).
 constexpr uint32_t DUP_BIG = 512;
 
-__device__ __forceinline__ void count_bucket(uint32_t* s_hist, bool live, uint32_t bucket, unsigned lane) {
-  const uint32_t peers = __match_any_sync(0xffffffffu, live ? bucket : 0xffffffffu);
-  if (live && (peers & ((1u << lane) - 1u)) == 0u) atomicAdd(&s_hist[bucket], (uint32_t)__popc(peers));
+// One shared-memory reduction per word into the CTA's bucket histogram. No match.any to count equal
+// lanes once: on sm_100 a match.any occupies its SM for about two cycles per DISTINCT value in the warp
+// (63 cycles for 32 distinct 10-bit values, 15 for 8; tools/micro/match_bench.cu), several times what
+// the atomics it saved cost (duplicate_words_kernel at C3: 0.077 -> 0.047 ms).
+__device__ __forceinline__ void count_bucket(uint32_t* s_hist, bool live, uint32_t bucket) {
+  if (live) atomicAdd(&s_hist[bucket], 1u);
 }
+
+// floor(n / d) for n * d < 2^32 with m = ceil(2^32 / d) (d >= 2; d == 1 is passed as m == 0)
+__device__ __forceinline__ uint32_t div_by(uint32_t n, uint32_t m) { return m ? __umulhi(n, m) : n; }
+__device__ __forceinline__ uint32_t div_magic(uint32_t d) { return d > 1u ? 0xffffffffu / d + 1u : 0u; }
 
 // DEPTH: tile | depth bits | index (64-bit words only); otherwise tile | index
 template <typename WORD, bool DEPTH>
@@ -112,14 +119,17 @@ duplicate_words_kernel(int P, const float2* __restrict__ means2D, const float* _
     const bool valid = slot < P;
     const int idx = !valid ? 0 : order ? (int)order[slot] : slot;
     const int r = valid ? radii[idx] : 0;
-    uint32_t lox = 0, loy = 0, w = 1, cnt = 0, dbits = 0;
+    // the rectangle as: first tile id, tiles per row (as the multiplier of div_by), tile-id step from one
+    // row to the next minus the row length
+    uint32_t first = 0, magic = 0, skip = 0, cnt = 0, dbits = 0;
     if (r > 0) {
       uint2 lo, hi;
       tile_rect(means2D[idx], r, grid_x, grid_y, lo, hi);
-      lox = lo.x;
-      loy = lo.y;
-      w = max(hi.x - lo.x, 1u);   // never 0: slots outside the run still divide by it
-      cnt = (hi.x - lo.x) * (hi.y - lo.y);
+      const uint32_t w = hi.x - lo.x;
+      first = lo.y * (uint32_t)grid_x + lo.x;
+      magic = div_magic(w);
+      skip = (uint32_t)grid_x - w;
+      cnt = w * (hi.y - lo.y);
       if (DEPTH) dbits = __float_as_uint(depths[idx]);
     }
     // first output slot of this Gaussian; the warp's own runs, big ones taken out, are numbered
@@ -147,17 +157,17 @@ duplicate_words_kernel(int P, const float2* __restrict__ means2D, const float* _
       }
       const uint32_t o_mine = __shfl_sync(0xffffffffu, mine, L);
       const uint32_t o_start = __shfl_sync(0xffffffffu, start, L);
-      const uint32_t o_lox = __shfl_sync(0xffffffffu, lox, L);
-      const uint32_t o_loy = __shfl_sync(0xffffffffu, loy, L);
-      const uint32_t o_w = __shfl_sync(0xffffffffu, w, L);
+      const uint32_t o_first = __shfl_sync(0xffffffffu, first, L);
+      const uint32_t o_magic = __shfl_sync(0xffffffffu, magic, L);
+      const uint32_t o_skip = __shfl_sync(0xffffffffu, skip, L);
       const uint32_t o_d = DEPTH ? __shfl_sync(0xffffffffu, dbits, L) : 0u;
       const uint32_t o_idx = __shfl_sync(0xffffffffu, (uint32_t)idx, L);
       const bool live = o < total;
-      const uint32_t local = o - o_mine;
-      const uint32_t dy = local / o_w;
-      const uint32_t tile = (o_loy + dy) * (uint32_t)grid_x + o_lox + (local - dy * o_w);
+      const uint32_t local = live ? o - o_mine : 0u;
+      // row dy, column local - dy w of the rectangle: tile = first + dy grid_x + (local - dy w)
+      const uint32_t tile = o_first + local + div_by(local, o_magic) * o_skip;
       if (live) words[o_start + local] = make_word<WORD, DEPTH>(tile, o_d, o_idx, idx_bits);
-      count_bucket(s_hist, live, tile >> bucket_shift, lane);
+      count_bucket(s_hist, live, tile >> bucket_shift);
     }
   }
   __syncthreads();
@@ -183,21 +193,21 @@ duplicate_big_kernel(const float2* __restrict__ means2D, const float* __restrict
   __shared__ uint32_t s_hist[MSD_BINS];
   for (int i = threadIdx.x; i < MSD_BINS; i += DUP_THREADS) s_hist[i] = 0;
   __syncthreads();
-  const unsigned lane = threadIdx.x & 31;
   for (uint32_t b = blockIdx.x; b < n_big; b += gridDim.x) {
     const uint32_t slot = big_list[b];
     const uint32_t idx = order[slot];
     uint2 lo, hi;
     tile_rect(means2D[idx], radii[idx], grid_x, grid_y, lo, hi);
     const uint32_t w = hi.x - lo.x, cnt = w * (hi.y - lo.y);
+    const uint32_t first = lo.y * (uint32_t)grid_x + lo.x, magic = div_magic(w), skip = (uint32_t)grid_x - w;
     const uint32_t start = offsets[slot] - cnt;
     const uint32_t dbits = DEPTH ? __float_as_uint(depths[idx]) : 0u;
     for (uint32_t t = threadIdx.x; t - threadIdx.x < cnt; t += DUP_THREADS) {   // CTA-uniform trip count
       const bool live = t < cnt;
-      const uint32_t dy = t / w;
-      const uint32_t tile = (lo.y + dy) * (uint32_t)grid_x + lo.x + (t - dy * w);
+      const uint32_t local = live ? t : 0u;
+      const uint32_t tile = first + local + div_by(local, magic) * skip;
       if (live) words[start + t] = make_word<WORD, DEPTH>(tile, dbits, idx, idx_bits);
-      count_bucket(s_hist, live, tile >> bucket_shift, lane);
+      count_bucket(s_hist, live, tile >> bucket_shift);
     }
   }
   __syncthreads();
@@ -216,7 +226,7 @@ constexpr uint32_t MSD_VALUE_MASK = (1u << 30) - 1u;
 
 template <typename WORD>
 struct MsdSmem {
-  uint16_t warp_hist[MSD_WARPS][MSD_BINS];   // 16 KB (a warp holds at most 1024 items)
+  uint32_t warp_hist[MSD_WARPS][MSD_BINS];   // 32 KB: per-warp digit counters (shared-memory atomics)
   WORD exch[MsdCfg<WORD>::TILE];             // 32 KB
   uint16_t digit_local[MSD_BINS];            // first slot of each digit in exch (< TILE)
   uint32_t digit_global[MSD_BINS];
@@ -307,42 +317,62 @@ msd_partition_kernel(const WORD* __restrict__ in, WORD* __restrict__ out, Instan
 
   WORD word[ITEMS];
   uint32_t rank2[ITEMS / 2];   // two 16-bit ranks per register
+  // words of this warp that exist (the last tile is ragged)
+  const uint32_t lim = (size_t)n > warp_base ? (uint32_t)min((size_t)(32 * ITEMS), (size_t)n - warp_base) : 0u;
+  {
+    const WORD* src = in + warp_base + lane;
 #pragma unroll
-  for (int i = 0; i < ITEMS; ++i) {
-    const size_t g = warp_base + (size_t)i * 32 + lane;
-    word[i] = g < (size_t)n ? in[g] : ~(WORD)0;
+    for (int i = 0; i < ITEMS; ++i) word[i] = (uint32_t)(i * 32) + lane < lim ? src[i * 32] : ~(WORD)0;
   }
+  // Rank of every word among the warp's words of the same digit, in load order. The lanes holding a
+  // digit are found with match.any; the lowest of them adds their number to the warp's counter of
+  // that digit with ONE shared-memory atomic and hands the old value to the others. The counter is
+  // only touched by atomics of this warp, which take effect in issue order, so nothing has to wait
+  // between two words: the rounds of a batch overlap instead of forming a chain of
+  // read - synchronise - write - synchronise (32 rounds of ~130 cycles each, which was most of the
+  // kernel's time).
+  constexpr int BATCH = 8;
+  uint32_t* my_hist = &S.warp_hist[warp][0];
 #pragma unroll
-  for (int i = 0; i < ITEMS; ++i) {
-    const size_t g = warp_base + (size_t)i * 32 + lane;
-    const bool ok = g < (size_t)n;
-    const uint32_t d = (uint32_t)(word[i] >> shift) & mask;
-    const uint32_t peers = __match_any_sync(0xffffffffu, ok ? d : (0x10000u + lane));
-    const uint32_t before = ok ? S.warp_hist[warp][d] : 0u;
-    __syncwarp();
-    if (ok && (peers & lt_mask) == 0u) S.warp_hist[warp][d] = (uint16_t)(before + __popc(peers));
-    __syncwarp();
-    const uint32_t rk = before + __popc(peers & lt_mask);
-    if (i & 1) rank2[i / 2] |= rk << 16; else rank2[i / 2] = rk;
+  for (int i0 = 0; i0 < ITEMS; i0 += BATCH) {
+    uint32_t peers[BATCH], before[BATCH];
+#pragma unroll
+    for (int k = 0; k < BATCH; ++k) {
+      const bool ok = (uint32_t)((i0 + k) * 32) + lane < lim;
+      const uint32_t d = (uint32_t)(word[i0 + k] >> shift) & mask;
+      peers[k] = __match_any_sync(0xffffffffu, ok ? d : (0x10000u + lane));
+    }
+#pragma unroll
+    for (int k = 0; k < BATCH; ++k) {
+      const bool ok = (uint32_t)((i0 + k) * 32) + lane < lim;
+      const uint32_t d = (uint32_t)(word[i0 + k] >> shift) & mask;
+      before[k] = 0u;
+      if (ok && (peers[k] & lt_mask) == 0u) before[k] = atomicAdd(&my_hist[d], (uint32_t)__popc(peers[k]));
+    }
+#pragma unroll
+    for (int k = 0; k < BATCH; ++k) {
+      const uint32_t rk = __shfl_sync(0xffffffffu, before[k], __ffs((int)peers[k]) - 1) + __popc(peers[k] & lt_mask);
+      const int i = i0 + k;
+      if (i & 1) rank2[i / 2] |= rk << 16; else rank2[i / 2] = rk;
+    }
   }
   __syncthreads();
   {
     // digits d0 .. d0 + 3 of this thread: per-warp counts -> exclusive warp offsets, block counts
     const uint32_t d0 = tid * MSD_DPT;
-    uint32_t block_count[MSD_DPT];
-    uint32_t mine = 0;
+    uint32_t block_count[MSD_DPT] = {0u, 0u, 0u, 0u};
+    {
+      // the thread's four counters of one warp are one 16-byte shared access
+      uint4 c[MSD_WARPS];
 #pragma unroll
-    for (int k = 0; k < MSD_DPT; ++k) {
-      uint32_t run = 0;
+      for (int w = 0; w < MSD_WARPS; ++w) c[w] = *reinterpret_cast<const uint4*>(&S.warp_hist[w][d0]);
 #pragma unroll
       for (int w = 0; w < MSD_WARPS; ++w) {
-        const uint32_t c = S.warp_hist[w][d0 + k];
-        S.warp_hist[w][d0 + k] = (uint16_t)run;
-        run += c;
+        *reinterpret_cast<uint4*>(&S.warp_hist[w][d0]) = make_uint4(block_count[0], block_count[1], block_count[2], block_count[3]);
+        block_count[0] += c[w].x; block_count[1] += c[w].y; block_count[2] += c[w].z; block_count[3] += c[w].w;
       }
-      block_count[k] = run;
-      mine += run;
     }
+    const uint32_t mine = block_count[0] + block_count[1] + block_count[2] + block_count[3];
     uint32_t* st = status_raw + (size_t)tile * MSD_BINS + d0;
     static_assert(MSD_DPT == 4, "a thread's digits are one 16-byte status vector");
     if (tile != 0)
@@ -403,11 +433,10 @@ msd_partition_kernel(const WORD* __restrict__ in, WORD* __restrict__ out, Instan
   __syncthreads();
 #pragma unroll
   for (int i = 0; i < ITEMS; ++i) {
-    const size_t g = warp_base + (size_t)i * 32 + lane;
-    if (g < (size_t)n) {
+    if ((uint32_t)(i * 32) + lane < lim) {
       const uint32_t d = (uint32_t)(word[i] >> shift) & mask;
       const uint32_t rk = (i & 1) ? rank2[i / 2] >> 16 : rank2[i / 2] & 0xffffu;
-      S.exch[S.digit_local[d] + S.warp_hist[warp][d] + rk] = word[i];
+      S.exch[S.digit_local[d] + my_hist[d] + rk] = word[i];
     }
   }
   __syncthreads();
@@ -949,7 +978,7 @@ static int launch_duplicate(const GeomPtrs& g, WORD* words, const int* radii, co
                             bool debug) {
   // each warp strides over groups of 32 Gaussians; the bucket histogram comes out of the
   // same kernel. With the presort, sort_keys[1] is free again and holds the list of set-aside
-  // Gaussians, counted in meta[4] (zeroed with the rest of the aux words when the presort started).
+  // Gaussians, counted in meta[4] (zeroed with the rest of the aux words when the forward began).
   uint32_t* big_list = gauss_order ? reinterpret_cast<uint32_t*>(g.sort_keys[1]) : nullptr;
   uint32_t* big_count = gauss_order ? g.sort_aux + DO_META + 4 : nullptr;
   duplicate_words_kernel<WORD, DEPTH><<<148 * DUP_CTAS_PER_SM, DUP_THREADS, 0, stream>>>(

@@ -1,6 +1,6 @@
 """Instructions executed per source line of one kernel from an .ncu-rep (read here, no GPU).
 
-  python tools/ncu_lines.py <rep> <kernel regex> [N]
+  python tools/ncu_lines.py <rep> <kernel regex> [N] [samples]     ("samples": sort by stall samples)
 """
 import csv
 import io
@@ -40,6 +40,10 @@ for r in rows:
     per_line[key][1] += smp
     per_line[key][2] = r[1]
 tot = sum(v[0] for v in per_line.values())
-print("kernel", pat, "instructions executed", tot)
-for (f, ln), (inst, smp, src) in sorted(per_line.items(), key=lambda kv: -kv[1][0])[:n]:
-    print("%5.1f%% %9d  %s:%d  %s" % (100.0 * inst / max(tot, 1), inst, f, ln, src.strip()[:100]))
+tot_s = sum(v[1] for v in per_line.values())
+by = 1 if (len(sys.argv) > 4 and sys.argv[4] == "samples") else 0
+print("kernel", pat, "instructions executed", tot, "stall samples", tot_s, "(sorted by %s)" % ("samples" if by else "instructions"))
+print(" inst%  samples%  instructions  location")
+for (f, ln), (inst, smp, src) in sorted(per_line.items(), key=lambda kv: -kv[1][by])[:n]:
+    print("%5.1f%% %7.1f%% %9d  %s:%d  %s" % (100.0 * inst / max(tot, 1), 100.0 * smp / max(tot_s, 1), inst, f, ln,
+                                            src.strip()[:100]))
