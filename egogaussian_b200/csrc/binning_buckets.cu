@@ -256,7 +256,25 @@ __device__ __forceinline__ void st_relaxed_v4(uint32_t* p, uint4 v) {
 // The digit is (word >> shift) & mask: the top bits of the word for the bucket partition (mask all
 // ones), any 10-bit field for the stable LSD passes of the depth presort. EMIT_IDX: the pass writes
 // only the low index bits of every word, as 32-bit values (last pass of the presort).
-template <typename WORD, bool EMIT_IDX>
+// Lanes of the warp holding the same 10-bit digit as this one. match.any costs its SM ~2 cycles per
+// distinct value among the lanes (tools/micro/match_bench.cu): cheap for the instance words, whose
+// neighbours share tiles (~12 distinct digits in 32 words), 63 cycles for the depth keys of the presort,
+// whose digits are as good as random. For those, ten ballots (2.3 cycles each) and a few logic
+// operations give the same mask.
+template <bool BALLOTS>
+__device__ __forceinline__ uint32_t digit_peers(uint32_t d, bool ok, unsigned lane) {
+  if (!BALLOTS) return __match_any_sync(0xffffffffu, ok ? d : (0x10000u + lane));
+  uint32_t p = __ballot_sync(0xffffffffu, ok);
+#pragma unroll
+  for (int k = 0; k < MSD_BITS_MAX; ++k) {
+    const bool bit = (d >> k) & 1u;
+    const uint32_t b = __ballot_sync(0xffffffffu, bit);
+    p &= bit ? b : ~b;
+  }
+  return ok ? p : (1u << lane);
+}
+
+template <typename WORD, bool EMIT_IDX, bool BALLOTS = false>
 __global__ void __launch_bounds__(MSD_THREADS, 3)
 msd_partition_kernel(const WORD* __restrict__ in, WORD* __restrict__ out, InstanceCount count,
                      int shift, uint32_t mask, const uint32_t* __restrict__ digit_hist /* [MSD_BINS] counts of the whole input */,
@@ -340,7 +358,7 @@ msd_partition_kernel(const WORD* __restrict__ in, WORD* __restrict__ out, Instan
     for (int k = 0; k < BATCH; ++k) {
       const bool ok = (uint32_t)((i0 + k) * 32) + lane < lim;
       const uint32_t d = (uint32_t)(word[i0 + k] >> shift) & mask;
-      peers[k] = __match_any_sync(0xffffffffu, ok ? d : (0x10000u + lane));
+      peers[k] = digit_peers<BALLOTS>(d, ok, lane);
     }
 #pragma unroll
     for (int k = 0; k < BATCH; ++k) {
@@ -938,20 +956,20 @@ int launch_depth_order(const GeomPtrs& g, int P, const int* radii, cudaStream_t 
                                                  g.readback + 1, scramble);
   EGS_AFTER_LAUNCH(stream, debug);
   constexpr int SMEM = (int)sizeof(MsdSmem<uint64_t>);
-  EGS_CUDA_TRY(cudaFuncSetAttribute(msd_partition_kernel<uint64_t, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM));
-  EGS_CUDA_TRY(cudaFuncSetAttribute(msd_partition_kernel<uint64_t, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM));
+  EGS_CUDA_TRY(cudaFuncSetAttribute(msd_partition_kernel<uint64_t, false, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM));
+  EGS_CUDA_TRY(cudaFuncSetAttribute(msd_partition_kernel<uint64_t, true, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM));
   const InstanceCount count{aux + DO_META + 2, (uint32_t)P, nullptr};
   const int grid = (int)g.sort_blocks;
   const size_t status_stride = g.sort_blocks * MSD_BINS;
-  msd_partition_kernel<uint64_t, false><<<grid, MSD_THREADS, SMEM, stream>>>(
+  msd_partition_kernel<uint64_t, false, true><<<grid, MSD_THREADS, SMEM, stream>>>(
       g.sort_keys[0], g.sort_keys[1], count, ib, MSD_BINS - 1, aux + DO_HIST, nullptr, aux + DO_TICKET, aux + DO_STATUS,
       nullptr, 0u);
   EGS_AFTER_LAUNCH(stream, debug);
-  msd_partition_kernel<uint64_t, false><<<grid, MSD_THREADS, SMEM, stream>>>(
+  msd_partition_kernel<uint64_t, false, true><<<grid, MSD_THREADS, SMEM, stream>>>(
       g.sort_keys[1], g.sort_keys[0], count, ib + 10, MSD_BINS - 1, aux + DO_HIST + MSD_BINS, nullptr, aux + DO_TICKET + 1,
       aux + DO_STATUS + status_stride, nullptr, 0u);
   EGS_AFTER_LAUNCH(stream, debug);
-  msd_partition_kernel<uint64_t, true><<<grid, MSD_THREADS, SMEM, stream>>>(
+  msd_partition_kernel<uint64_t, true, true><<<grid, MSD_THREADS, SMEM, stream>>>(
       g.sort_keys[0], nullptr, count, ib + 20, MSD_BINS - 1, aux + DO_HIST + 2 * MSD_BINS, nullptr, aux + DO_TICKET + 2,
       aux + DO_STATUS + 2 * status_stride, g.sort_vals[0], (uint32_t)((1ull << ib) - 1ull));
   EGS_AFTER_LAUNCH(stream, debug);
