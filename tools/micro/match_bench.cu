@@ -1,4 +1,4 @@
-// Scratch microbenchmark: cycles per warp instruction of match.any / shared atomics / shuffles on sm_100a,
+// Microbenchmark (nvcc -O3 -gencode arch=compute_100a,code=sm_100a -o tools/micro/match_bench tools/micro/match_bench.cu): cycles per warp instruction of match.any / shared atomics / shuffles on sm_100a,
 // with W warps per SM issuing independent (ILP) or dependent (chain) operations.
 #include <cstdio>
 #include <cstdint>
