@@ -510,8 +510,8 @@ def run_ours(a, rank, world, local_rank):
     batch = parallel.ViewBatch(world, P, M, device, exchange=ex) if factored else None
     flat = batch.result if factored else parallel.FlatGrads(P, M, device, allocate=ex.allocate if ex else None)
     if ex:
-        exchange = ("egs_exchange_sum_factored, " if factored else "egs_exchange_sum, ") + \
-            ("switch multicast" if ex.multicast_pointer(flat.flat) else "peer loads/stores")
+        exchange = ("egs_exchange_sum_factored, " + batch.path) if factored else \
+            ("egs_exchange_sum, " + ("switch multicast" if ex.multicast_pointer(flat.flat) else "peer loads/stores"))
     scratch = torch.empty((cabi.load().egs_backward_scratch_bytes(P),), dtype=torch.uint8, device=device)
     state = {}
 

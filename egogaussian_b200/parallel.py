@@ -248,6 +248,10 @@ class ViewBatch:
             self._group = cabi.peer_group(1, 0, [self.result.flat.data_ptr()], [self._signals.data_ptr()])
             self._epoch = 0
         self._view_flat = [flat_ptrs[v // self.world][v % self.world] for v in range(n_views)]
+        #: how the small gradients are summed: inside the NVLink switch (one view per rank and a multicast
+        #: mapping of the flat buffers) or by loads from the peers
+        self.path = ("switch multicast" if (exchange and n_views == self.world and exchange.multicast_pointer(self.result.flat))
+                     else "peer loads/stores")
 
     def backward_args(self, j: int) -> Dict:
         """Keyword arguments for cabi.backward of the rank's j-th view: its output tensors and the

@@ -22,6 +22,7 @@ def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--steps", type=int, default=30)
     ap.add_argument("--full", action="store_true", help="exchange the expanded SH gradient (egs_exchange_sum)")
+    ap.add_argument("--no-multicast", action="store_true", help="peer loads and stores even where the switch could reduce")
     x = ap.parse_args()
     sys.argv = sys.argv[:1]
     a = bench.parse()
@@ -32,7 +33,7 @@ def main():
     kw, ups, host, cpu_kw, weights = bench.build_inputs(a, rank, device)
     P, M = a.P, (a.sh_degree + 1) ** 2
     bkw = {k: v for k, v in kw.items() if k not in ("opacities", "image_height", "image_width")}
-    ex = parallel.PeerExchange(device)
+    ex = parallel.PeerExchange(device, multicast=False if x.no_multicast else None)
     batch = None if x.full else parallel.ViewBatch(world, P, M, device, exchange=ex)
     flat = parallel.FlatGrads(P, M, device, allocate=ex.allocate) if x.full else batch.result
     bw = dict(out=flat.as_backward_out()) if x.full else batch.backward_args(0)
@@ -92,7 +93,7 @@ def main():
     out = [torch.empty_like(t) for _ in range(world)]
     dist.all_gather(out, t)
     if rank == 0:
-        print("exchange:", "egs_exchange_sum (expanded SH rows)" if x.full else "egs_exchange_sum_factored")
+        print("exchange:", "egs_exchange_sum (expanded SH rows)" if x.full else "egs_exchange_sum_factored, small gradients by " + batch.path)
         for r, o in enumerate(out):
             print(f"  rank {r}: fwd+bwd {o[0]:.3f} ms, exchange (incl. waiting) {o[1]:.3f} ms, step {o[2]:.3f} ms, "
                   f"R {int(o[3])}, exchange alone {o[4]:.3f} ms")
