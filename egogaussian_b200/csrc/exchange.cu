@@ -354,17 +354,22 @@ __device__ __forceinline__ void expand_sh_sum(const ExLaunch& L, const ShFactorL
     }
     cp_async_commit();
   };
+  auto position = [&](int g) -> float3 {   // this lane's Gaussian of group g
+    const int i = g * 32 + (int)lane;
+    return (g < g_hi && i < F.P) ? make_float3(F.means3D[3 * i], F.means3D[3 * i + 1], F.means3D[3 * i + 2])
+                                 : make_float3(0.f, 0.f, 0.f);
+  };
   int grp = draw();
   fetch(grp, 0);
+  float3 pos_next = position(grp);
   for (int it = 0; grp < g_hi; ++it) {
     const int buf = it & 1;
     const int next = draw();
     fetch(next, buf ^ 1);
     const int first = grp * 32;
     const int rows = min(32, F.P - first);
-    const int idx = first + (int)lane;
-    float3 pos = make_float3(0.f, 0.f, 0.f);
-    if (idx < F.P) pos = make_float3(F.means3D[3 * idx], F.means3D[3 * idx + 1], F.means3D[3 * idx + 2]);
+    const float3 pos = pos_next;
+    pos_next = position(next);   // a group ahead, like the triples: the load is not waited for here
     cp_async_wait<1>();   // this group's triples have landed (the next group's may still be in flight)
     __syncwarp();
     const float* st = stage + buf * SF_STAGE;
