@@ -61,8 +61,9 @@ constexpr int BK_CAP = 12288;                      // words per bucket held in s
 // output slots base + 32 c + l. A slot finds its Gaussian by a 5-step binary search over the 32
 // start offsets (shuffles) and its tile from the slot's position inside that Gaussian's rectangle.
 // Compared with one thread looping over its own rectangle this removes the divergence between
-// small and large rectangles, makes every store coalesced, and lets the warp count a bucket once
-// per 32 slots (match.any) for the histogram, which therefore needs no pass of its own.
+// small and large rectangles and makes every store coalesced; the bucket histogram is counted on the
+// way (count_bucket below), so it needs no pass of its own.
+//
 // words of GeomPtrs::sort_aux (depth presort): three digit histograms, their exclusive scans, tickets,
 // meta (2: P for the partition kernel, 4: count of set-aside Gaussians), then three status areas
 constexpr int DO_HIST = 0, DO_START = 3 * 1024, DO_TICKET = 6 * 1024, DO_META = DO_TICKET + 8,
