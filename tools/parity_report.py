@@ -64,8 +64,9 @@ def compare(name, kw, ups, with_cpu, timing):
             rep["means2D_bitdiff"] = int((gv["means2D"][vis].view(torch.int32) != dec["means2D"][vis].view(torch.int32)).sum())
             rep["depths_bitdiff"] = int((gv["depths"][vis].view(torch.int32) != dec["depths"][vis].view(torch.int32)).sum())
             rep["conic_bitdiff"] = int((gv["conic_opacity"][vis].view(torch.int32) != dec["conic_opacity"][vis].view(torch.int32)).sum())
-            rep["rgb_maxabs"] = float((gv["rgb_depth"][vis][:, :3] - dec["rgb"][vis]).abs().max())
-            rep["rgb_bitdiff"] = int((gv["rgb_depth"][vis][:, :3].contiguous().view(torch.int32) != dec["rgb"][vis].contiguous().view(torch.int32)).sum())
+            if kw.get("colors_precomp") is None:   # with precomputed colours the reference never writes geom.rgb
+                rep["rgb_maxabs"] = float((gv["rgb_depth"][vis][:, :3] - dec["rgb"][vis]).abs().max())
+                rep["rgb_bitdiff"] = int((gv["rgb_depth"][vis][:, :3].contiguous().view(torch.int32) != dec["rgb"][vis].contiguous().view(torch.int32)).sum())
             rep["tiles_mismatch"] = int((gv["tiles_touched"] != dec["tiles_touched"]).sum())
         if fwd.num_rendered == rf["num_rendered"]:
             rep["keys_mismatch"] = int((bv["keys"] != dec["keys"]).sum())
