@@ -83,6 +83,9 @@ def compare(name, kw, ups, with_cpu, timing):
         # the reference's own run-to-run atomic noise
         rg2 = ref_dgr.backward(rf, **bkw, **ups)
         rep["ref_self_noise_means3D"] = grad_rel_err(rg2["means3D"], rg["means3D"])
+        for k, v in rg.items():   # the same figure for every tensor: what two runs of the reference differ by
+            if v is not None and rg2.get(k) is not None and k != "means3D":
+                rep[f"ref_self_noise_{k}"] = grad_rel_err(rg2[k], v)
         if timing:
             rep["ref_fwd_ms"] = time_fn(lambda: ref_dgr.forward(**kw))
             rep["ref_bwd_ms"] = time_fn(lambda: ref_dgr.backward(rf, **bkw, **ups))
