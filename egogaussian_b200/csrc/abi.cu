@@ -409,8 +409,7 @@ static int backward_impl(const char* who, const EgsBackwardArgs* args, const Egs
     return rc;
   }
   if (!a.means3D || !a.radii || !a.out_alpha || !a.geom_buffer || !a.image_buffer ||
-      (a.num_rendered > 0 && !a.binning_buffer) || !a.dL_dout_color || !a.dL_dout_depth ||
-      !a.dL_dout_alpha || !a.scratch ||
+      (a.num_rendered > 0 && !a.binning_buffer) || !a.dL_dout_color || !a.scratch ||
       (!a.colors_only && (!a.dL_dmeans2D || (!a.dL_dopacity && !model) || !a.dL_dmeans3D)) ||
       !a.background || !a.viewmatrix || !a.projmatrix || !a.campos) {
     set_error("%s: NULL required argument", who);

@@ -142,8 +142,8 @@ __device__ __forceinline__ void pixel_init(PixelState& s, bool inside, uint32_t 
   s.gr = inside ? dL_dpixels[pix_id] : 0.f;
   s.gg = inside ? dL_dpixels[plane + pix_id] : 0.f;
   s.gb = inside ? dL_dpixels[2 * plane + pix_id] : 0.f;
-  s.gd = inside ? dL_dpixel_depths[pix_id] : 0.f;
-  s.ga = inside ? dL_dalphas[pix_id] : 0.f;
+  s.gd = inside && dL_dpixel_depths != nullptr ? dL_dpixel_depths[pix_id] : 0.f;   // absent = zero
+  s.ga = inside && dL_dalphas != nullptr ? dL_dalphas[pix_id] : 0.f;
   s.ar = s.ag = s.ab = s.ad = s.aa = 0.f;
   s.tb = -T_final * (bg[0] * s.gr + bg[1] * s.gg + bg[2] * s.gb);
 }
@@ -154,7 +154,9 @@ __device__ __forceinline__ void pixel_init(PixelState& s, bool inside, uint32_t 
 // One contributing fragment: advances the pixel's recurrences and adds its partial sums to q.
 // COLORS_ONLY (EgsBackwardArgs.colors_only): just the transmittance recurrence and the three colour
 // sums; nothing that feeds the geometry or opacity gradients is evaluated.
-template <bool COLORS_ONLY>
+// DA = false: no upstream gradient for the depth and alpha images (a loss on the colour image only, the
+// trainers' usual case): their recurrences and their terms of dL/dalpha are left out.
+template <bool COLORS_ONLY, bool DA>
 __device__ __forceinline__ void fragment_backward(PixelState& s, float dx, float dy, float power, float opac,
                                                   const float4 c4, float depth, float (&q)[10]) {
   const float G = ex2_approx(power * 1.4426950408889634f);
@@ -166,21 +168,24 @@ __device__ __forceinline__ void fragment_backward(PixelState& s, float dx, float
   q[8] += w * s.gg;
   q[9] += w * s.gb;
   if (COLORS_ONLY) return;
-  q[3] += w * s.gd;
+  if (DA) q[3] += w * s.gd;
   // (this fragment's value) - (what lies behind it), per channel: feeds dL/dalpha, and advances the
   // "behind" recurrence to the next fragment of this pixel (one closer to the eye):
   // alpha c + (1 - alpha) a = a + alpha (c - a)
-  const float dr = c4.x - s.ar, dg = c4.y - s.ag, db = c4.z - s.ab, dd = depth - s.ad, da = 1.f - s.aa;
+  const float dr = c4.x - s.ar, dg = c4.y - s.ag, db = c4.z - s.ab;
   float dL_dopa = dr * s.gr;
   dL_dopa += dg * s.gg;
   dL_dopa += db * s.gb;
-  dL_dopa += dd * s.gd;
-  dL_dopa += da * s.ga;
   s.ar += alpha * dr;
   s.ag += alpha * dg;
   s.ab += alpha * db;
-  s.ad += alpha * dd;
-  s.aa += alpha * da;
+  if (DA) {
+    const float dd = depth - s.ad, da = 1.f - s.aa;
+    dL_dopa += dd * s.gd;
+    dL_dopa += da * s.ga;
+    s.ad += alpha * dd;
+    s.aa += alpha * da;
+  }
   dL_dopa = dL_dopa * s.T + s.tb * rcp;
   const float u = G * dL_dopa;          // the opacity factor of dL/dG = o dL/dalpha is applied once per entry
   const float ux = u * dx, uy = u * dy;
@@ -194,7 +199,7 @@ __device__ __forceinline__ void fragment_backward(PixelState& s, float dx, float
 
 // (PPL = 4 takes ~118 registers, 8 CTAs of 64 threads per SM; bounding it to 96 registers for 10 CTAs
 // measured slower, 0.346 against 0.336 ms at C3)
-template <int PPL, bool COLORS_ONLY>
+template <int PPL, bool COLORS_ONLY, bool DA>
 __global__ void __launch_bounds__(256 / PPL)
 blend_backward_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__ point_list,
                       int W, int H, int grid_x, const float* __restrict__ bg_color,
@@ -333,7 +338,7 @@ blend_backward_kernel(const uint2* __restrict__ ranges, const uint32_t* __restri
         if (act[s]) {
           // inside the band around the threshold the forward's own expression decides
           if (power[s] >= band_hi || contributes_exact(a4.w, power[s]))
-            fragment_backward<COLORS_ONLY>(px[s], dx, dy[s], power[s], a4.w, c4, b4.w, q);
+            fragment_backward<COLORS_ONLY, DA>(px[s], dx, dy[s], power[s], a4.w, c4, b4.w, q);
         }
       }
       const float total = warp_packed_reduce10(q, lane);
@@ -388,14 +393,18 @@ int launch_blend_backward(const EgsBackwardArgs& a, const GeomPtrs& g, const uin
   // egs_debug_option("blend_backward", "2" | "4") forces either for the A/B
   const int forced = debug_options().bwd_ppl;
   const int ppl = forced ? forced : ((long long)grid.x * grid.y < 148 * 8 ? 2 : 4);
-#define EGS_BWD_LAUNCH(PPL, CO)                                                                                   \
-  blend_backward_kernel<PPL, CO><<<grid, 256 / PPL, 0, stream>>>(                                                 \
+  // no upstream gradient for depth and alpha (both NULL): the kernel without their terms
+  const bool da = a.dL_dout_depth != nullptr || a.dL_dout_alpha != nullptr;
+#define EGS_BWD_LAUNCH(PPL, CO, DA)                                                                               \
+  blend_backward_kernel<PPL, CO, DA><<<grid, 256 / PPL, 0, stream>>>(                                             \
       im.ranges, point_list, a.width, a.height, (int)grid.x, a.background, g.means2D, g.conic_opacity, g.rgb_depth, \
       a.out_alpha, im.n_contrib, a.dL_dout_color, a.dL_dout_depth, a.dL_dout_alpha, s.acc)
   if (a.colors_only) {
-    if (ppl == 2) EGS_BWD_LAUNCH(2, true); else EGS_BWD_LAUNCH(4, true);
+    if (ppl == 2) EGS_BWD_LAUNCH(2, true, false); else EGS_BWD_LAUNCH(4, true, false);
+  } else if (da) {
+    if (ppl == 2) EGS_BWD_LAUNCH(2, false, true); else EGS_BWD_LAUNCH(4, false, true);
   } else {
-    if (ppl == 2) EGS_BWD_LAUNCH(2, false); else EGS_BWD_LAUNCH(4, false);
+    if (ppl == 2) EGS_BWD_LAUNCH(2, false, false); else EGS_BWD_LAUNCH(4, false, false);
   }
 #undef EGS_BWD_LAUNCH
   EGS_AFTER_LAUNCH(stream, a.debug);

@@ -210,8 +210,8 @@ rasterize_backward_impl(bool colors_only, const torch::Tensor& background, const
     a.binning_buffer = binningBuffer.numel() ? binningBuffer.data_ptr() : nullptr;
     a.image_buffer = imageBuffer.data_ptr();
     a.dL_dout_color = req_ptr(dL_dout_color, k[12], dev, "dL_dout_color");
-    a.dL_dout_depth = req_ptr(dL_dout_depth, k[13], dev, "dL_dout_depth");
-    a.dL_dout_alpha = req_ptr(dL_dout_alpha, k[14], dev, "dL_dout_alpha");
+    a.dL_dout_depth = opt_ptr(dL_dout_depth, k[13], dev, "dL_dout_depth");   // empty: no gradient flows into it
+    a.dL_dout_alpha = opt_ptr(dL_dout_alpha, k[14], dev, "dL_dout_alpha");
     a.scratch = scratch.data_ptr();
     auto out = [](torch::Tensor& t) { return t.numel() ? t.data_ptr<float>() : nullptr; };
     a.dL_dmeans2D = out(dL_dmeans2D);
@@ -560,8 +560,8 @@ std::vector<torch::Tensor> rasterize_gaussians_raw_backward(
     a.binning_buffer = binningBuffer.numel() ? binningBuffer.data_ptr() : nullptr;
     a.image_buffer = imageBuffer.data_ptr();
     a.dL_dout_color = req_ptr(dL_dout_color, k[8], dev, "dL_dout_color");
-    a.dL_dout_depth = req_ptr(dL_dout_depth, k[9], dev, "dL_dout_depth");
-    a.dL_dout_alpha = req_ptr(dL_dout_alpha, k[10], dev, "dL_dout_alpha");
+    a.dL_dout_depth = opt_ptr(dL_dout_depth, k[9], dev, "dL_dout_depth");
+    a.dL_dout_alpha = opt_ptr(dL_dout_alpha, k[10], dev, "dL_dout_alpha");
     a.scratch = scratch.data_ptr();
     a.dL_dmeans2D = dL_dmeans2D.data_ptr<float>();
     a.dL_dmeans3D = dL_dmeans3D.data_ptr<float>();

@@ -91,12 +91,14 @@ class _RasterizeGaussians(torch.autograd.Function):
         rs = ctx.raster_settings
         (colors_precomp, means3D, scales, rotations, cov3Ds_precomp, radii, sh, geom_blob,
          binning_blob, image_blob, alpha) = ctx.saved_tensors
-        # autograd hands None (or a broadcast view) for outputs that took no part in the loss
-        def dense(g, like):
-            return torch.zeros_like(like) if g is None else g
-        grad_color = dense(grad_color, alpha.expand(3, -1, -1))
-        grad_depth = dense(grad_depth, alpha)
-        grad_alpha = dense(grad_alpha, alpha)
+        # autograd hands None for outputs that took no part in the loss: the colour gradient is then
+        # zeros; depth and alpha go to the binding as empty tensors, and the tile kernel leaves their
+        # terms out (the reference zero-fills all three, __init__.py:100-158)
+        if grad_color is None:
+            grad_color = torch.zeros_like(alpha.expand(3, -1, -1))
+        empty = alpha.new_empty(0)
+        grad_depth = empty if grad_depth is None else grad_depth
+        grad_alpha = empty if grad_alpha is None else grad_alpha
 
         args = (rs.bg, means3D, radii, colors_precomp, scales, rotations, rs.scale_modifier,
                 cov3Ds_precomp, rs.viewmatrix, rs.projmatrix, rs.tanfovx, rs.tanfovy, grad_color,

@@ -159,8 +159,9 @@ class _RasterizeRaw(torch.autograd.Function):
          radii, geom, binning, img, alpha) = ctx.saved_tensors
         if g_color is None:
             g_color = torch.zeros_like(alpha.expand(3, -1, -1))
-        g_depth = torch.zeros_like(alpha) if g_depth is None else g_depth
-        g_alpha = torch.zeros_like(alpha) if g_alpha is None else g_alpha
+        empty = alpha.new_empty(0)   # "no gradient": the tile kernel then leaves the depth / alpha terms out
+        g_depth = empty if g_depth is None else g_depth
+        g_alpha = empty if g_alpha is None else g_alpha
         rs = ctx.rs
         num_rendered, which, copies = ctx.meta
         need = ctx.needs_input_grad

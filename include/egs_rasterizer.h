@@ -148,8 +148,9 @@ typedef struct EgsBackwardArgs {
   const void* binning_buffer;
   const void* image_buffer;
   const float* dL_dout_color;  /* [3,H,W] */
-  const float* dL_dout_depth;  /* [1,H,W] */
-  const float* dL_dout_alpha;  /* [1,H,W] */
+  const float* dL_dout_depth;  /* [1,H,W], or NULL: no gradient flows into the depth image */
+  const float* dL_dout_alpha;  /* [1,H,W], or NULL likewise; with both NULL (a loss on the colour image only)
+                                  the tile kernel leaves their recurrences out */
   /* scratch: egs_backward_scratch_bytes(P) bytes, device, 256-byte aligned; contents are
    * overwritten (zeroed by the call, then used as atomic accumulators). */
   void* scratch;

@@ -552,6 +552,47 @@ def test_backward_kernel_variants_agree(built, cuda_device, debug_options):
                 assert grad_rel_err(g2[k], g4[k]) <= GRAD_RTOL, (case[0], k)
 
 
+@pytest.mark.parametrize("ppl", ["2", "4"])
+def test_backward_without_depth_and_alpha_gradients(ppl, built, cuda_device, debug_options):
+    """A loss on the colour image only: the C-ABI takes NULL for dL/ddepth and dL/dalpha (the tile kernel
+    then leaves their recurrences out) and the autograd surface passes exactly that when autograd hands it
+    None. Both must give what zero-filled gradients give (the reference's way), also when only one of
+    the two is absent."""
+    from egogaussian_b200 import cabi
+    from egogaussian_b200.diff_gaussian_rasterization import GaussianRasterizationSettings, GaussianRasterizer
+    debug_options("blend_backward", ppl)
+    for case in (CASES[0], CASES[2]):
+        kw, ups = case_inputs(case, cuda_device)
+        zero = dict(ups, dL_ddepth=torch.zeros_like(ups["dL_ddepth"]), dL_dalpha=torch.zeros_like(ups["dL_dalpha"]))
+        _, want = run_cuda(kw, zero)
+        fwd = cabi.forward(**kw)
+        bkw = {k: v for k, v in kw.items() if k not in ("opacities", "image_height", "image_width")}
+        got = cabi.backward(fwd, dL_dcolor=ups["dL_dcolor"], dL_ddepth=None, dL_dalpha=None, **bkw)
+        for k, v in want.items():
+            if v is not None:
+                assert grad_rel_err(got[k], v) <= 2e-5, (case[0], k)
+        # only the alpha gradient absent
+        _, want1 = run_cuda(kw, dict(ups, dL_dalpha=torch.zeros_like(ups["dL_dalpha"])))
+        got1 = cabi.backward(fwd, dL_dcolor=ups["dL_dcolor"], dL_ddepth=ups["dL_ddepth"], dL_dalpha=None, **bkw)
+        for k, v in want1.items():
+            if v is not None:
+                assert grad_rel_err(got1[k], v) <= 2e-5, (case[0], k, "alpha absent")
+        # through autograd: a loss that touches the colour image only
+        leaves = {k: kw[k].clone().requires_grad_(True) for k in ("means3D", "opacities", "shs", "colors_precomp", "scales",
+                                                                  "rotations", "cov3D_precomp") if kw.get(k) is not None}
+        rs = GaussianRasterizationSettings(kw["image_height"], kw["image_width"], kw["tanfovx"], kw["tanfovy"], kw["bg"], 1.0,
+                                           kw["viewmatrix"], kw["projmatrix"], kw["sh_degree"], kw["campos"], False, False)
+        color, _, _, _ = GaussianRasterizer(rs)(
+            means3D=leaves["means3D"], means2D=torch.zeros_like(leaves["means3D"], requires_grad=True),
+            opacities=leaves["opacities"], shs=leaves.get("shs"), colors_precomp=leaves.get("colors_precomp"),
+            scales=leaves.get("scales"), rotations=leaves.get("rotations"), cov3D_precomp=leaves.get("cov3D_precomp"))
+        (color * ups["dL_dcolor"]).sum().backward()
+        names = {"means3D": "means3D", "opacities": "opacity", "shs": "sh", "colors_precomp": "colors", "scales": "scales",
+                 "rotations": "rotations", "cov3D_precomp": "cov3D"}
+        for k, t in leaves.items():
+            assert grad_rel_err(t.grad.reshape(want[names[k]].shape), want[names[k]]) <= 2e-5, (case[0], k, "autograd")
+
+
 def test_backward_contributor_set_matches_forward(built, cuda_device):
     """A fragment sitting exactly on the alpha = 1/255 threshold must be in or out in BOTH passes: the
     backward decides in the log domain, the forward with o * expf(power); inside a small band around
