@@ -91,9 +91,10 @@ __device__ __forceinline__ int record_slot_of_quantity(int q) { return q < 7 ? q
 //     power lies within CONTRIB_MARGIN of the threshold is therefore decided here with that very
 //     expression, so both passes always agree on a pixel's contributor set (one fragment more or
 //     less would shift T = T / (1 - alpha) for every earlier fragment of the pixel);
-//   * the "colour behind this fragment" recurrences are advanced right after a fragment has used them
-//     (the reference advances them at the start of the next one from a saved alpha and colour: the same
-//     expression evaluated one step earlier, five registers less per pixel);
+//   * what lies behind a fragment enters dL/dalpha only through its dot product with the pixel's upstream
+//     gradients, so ONE running number per pixel replaces the reference's five accumulated values
+//     (PixelState::S): seven instead of fifteen instructions per fragment and sixteen registers per lane
+//     less (0.335 -> 0.307 ms at C3); it is advanced right after a fragment has used it;
 //   * the geometry gradients are accumulated as moments of v = G dL/dG over the pixels -- sum v, v dx,
 //     v dy, v dx^2, v dx dy, v dy^2 -- and turned into dL/dmean2D and dL/dconic once per entry after the
 //     reduction (9 instead of 17 instructions per fragment);
@@ -122,10 +123,13 @@ __device__ __forceinline__ float rcp_approx(float x) {
   return y;
 }
 
-// What a pixel carries through the walk: transmittance, the colour / depth / alpha accumulated behind
-// the current fragment, its upstream gradients and tb = -T_final * (background . dL/dcolour).
+// What a pixel carries through the walk: transmittance, its upstream gradients, tb = -T_final *
+// (background . dL/dcolour), and S = (what lies behind the current fragment) . (upstream gradients):
+// the reference keeps the colour, depth and alpha accumulated behind a fragment (five numbers) only to
+// form sum_c (c_c - behind_c) g_c, which is (c . g) - S, and behind' = behind + alpha (c - behind) dotted
+// with g is S' = S + alpha ((c . g) - S): one number per pixel does it.
 struct PixelState {
-  float T, ar, ag, ab, ad, aa;
+  float T, S;
   float gr, gg, gb, gd, ga, tb;
   uint32_t last;
 };
@@ -144,7 +148,7 @@ __device__ __forceinline__ void pixel_init(PixelState& s, bool inside, uint32_t 
   s.gb = inside ? dL_dpixels[2 * plane + pix_id] : 0.f;
   s.gd = inside && dL_dpixel_depths != nullptr ? dL_dpixel_depths[pix_id] : 0.f;   // absent = zero
   s.ga = inside && dL_dalphas != nullptr ? dL_dalphas[pix_id] : 0.f;
-  s.ar = s.ag = s.ab = s.ad = s.aa = 0.f;
+  s.S = 0.f;
   s.tb = -T_final * (bg[0] * s.gr + bg[1] * s.gg + bg[2] * s.gb);
 }
 
@@ -169,23 +173,17 @@ __device__ __forceinline__ void fragment_backward(PixelState& s, float dx, float
   q[9] += w * s.gb;
   if (COLORS_ONLY) return;
   if (DA) q[3] += w * s.gd;
-  // (this fragment's value) - (what lies behind it), per channel: feeds dL/dalpha, and advances the
-  // "behind" recurrence to the next fragment of this pixel (one closer to the eye):
-  // alpha c + (1 - alpha) a = a + alpha (c - a)
-  const float dr = c4.x - s.ar, dg = c4.y - s.ag, db = c4.z - s.ab;
-  float dL_dopa = dr * s.gr;
-  dL_dopa += dg * s.gg;
-  dL_dopa += db * s.gb;
-  s.ar += alpha * dr;
-  s.ag += alpha * dg;
-  s.ab += alpha * db;
+  // (this fragment's value) - (what lies behind it), dotted with the upstream gradients: feeds dL/dalpha,
+  // and advances S to the next fragment of this pixel (one closer to the eye)
+  float X = c4.x * s.gr;
+  X = fmaf(c4.y, s.gg, X);
+  X = fmaf(c4.z, s.gb, X);
   if (DA) {
-    const float dd = depth - s.ad, da = 1.f - s.aa;
-    dL_dopa += dd * s.gd;
-    dL_dopa += da * s.ga;
-    s.ad += alpha * dd;
-    s.aa += alpha * da;
+    X = fmaf(depth, s.gd, X);
+    X += s.ga;
   }
+  float dL_dopa = X - s.S;
+  s.S = fmaf(alpha, dL_dopa, s.S);
   dL_dopa = dL_dopa * s.T + s.tb * rcp;
   const float u = G * dL_dopa;          // the opacity factor of dL/dG = o dL/dalpha is applied once per entry
   const float ux = u * dx, uy = u * dy;
@@ -197,8 +195,8 @@ __device__ __forceinline__ void fragment_backward(PixelState& s, float dx, float
   q[6] += uy * dy;
 }
 
-// (PPL = 4 takes ~118 registers, 8 CTAs of 64 threads per SM; bounding it to 96 registers for 10 CTAs
-// measured slower, 0.346 against 0.336 ms at C3)
+// (PPL = 4 takes 96 registers, 10 CTAs of 64 threads per SM, since the "behind" state is one number per
+// pixel; with the reference's five it took 118 and 8 CTAs, and forcing that form into 96 measured slower)
 template <int PPL, bool COLORS_ONLY, bool DA>
 __global__ void __launch_bounds__(256 / PPL)
 blend_backward_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__ point_list,

@@ -116,7 +116,11 @@ def test_against_live_reference_at_baseline_sizes(case, hint, built, cuda_device
     bkw = {k: v for k, v in kw.items() if k not in ("opacities", "image_height", "image_width")}
     rf = ref_dgr.forward(**kw)
     dec = ref_dgr.decode_buffers(rf)
-    rg = ref_dgr.backward(rf, **bkw, **ups)
+    # the reference's atomics make two of its own runs differ by up to 6e-5 of the maximum at these sizes
+    # (the scale gradient at configs[1]; profiles/r2_parity_vs_reference.json lists it per tensor): the
+    # mean of three runs is the target, so that the 1e-4 bound is spent on this implementation
+    runs = [ref_dgr.backward(rf, **bkw, **ups) for _ in range(3)]
+    rg = {k: (None if v is None else sum(r[k] for r in runs) / len(runs)) for k, v in runs[0].items()}
     R = rf["num_rendered"]
     fwd = cabi.forward(num_rendered_hint=int(R * 1.2) + 1 if hint else 0, **kw)
     grads = cabi.backward(fwd, **bkw, **ups)
