@@ -49,6 +49,10 @@ for r in rows[2:]:
     stage = STAGE_OF.get(name)
     if stage is None:
         continue
+    # the backward blend of the bench step has all three upstream gradients (<PPL, 0, 1>); the training
+    # iteration's launch without depth / alpha gradients (<PPL, 0, 0>) is another kernel
+    if name == "blend_backward_kernel" and ", 0>(" in r[kn].split("(")[0] + "(":
+        continue
     acc[(stage, name)].append(float(r[rd]) * scale[units[rd]] + float(r[wr]) * scale[units[wr]])
     util[(stage, name)].append((float(r[issue]), float(r[active])))
     extra[(stage, name)].append(tuple(float(r[c].replace(",", "")) if c is not None and r[c] not in ("", "n/a") else None
